@@ -1,0 +1,133 @@
+/* tksm_seq.h — C ABI of the B200-native `tksm sequence` (Seq exit module) hot path.
+ *
+ * Drop-in boundary.  Every entry point names the reference interface it replaces
+ * (paths relative to the vpc-ccg/tksm tree):
+ *
+ *   tksm_sequence_main          Sequencer_module{argc-1, argv+1}.run()   src/tksm.cpp:164-166,
+ *                               src/sequence.cpp:30-54, src/python_runner.h:44-73 (argv[0] == "sequence")
+ *   tksm_seq_create/_destroy    parse_args() state + Identities(...)      py/sequence.py:34-165, 331-336
+ *   tksm_seq_load_references    get_reference_seqs()                      py/sequence.py:189-194
+ *   tksm_seq_load_models        ErrorModel(...), QScoreModel(...),
+ *                               KDE_noise_generator.load(...)             py/sequence.py:337-345
+ *   tksm_seq_run_files          the __main__ loop                         py/sequence.py:347-376
+ *   tksm_seq_simulate_text      mdf_generator + mdf_to_seq + formatter    py/sequence.py:197-320
+ *
+ * Conventions: plain pointers and sizes only; the caller owns every buffer it passes in;
+ * buffers returned by the library are released with tksm_seq_free(); no exception crosses
+ * the boundary; functions return 0 on success, 1 on a runtime/input error, 2 on a usage
+ * error (same codes `tksm sequence` exits with) and tksm_seq_last_error() describes the
+ * failure.  There is no CPU fallback: without a CUDA device tksm_seq_create() fails.
+ */
+#ifndef TKSM_SEQ_H
+#define TKSM_SEQ_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct tksm_seq tksm_seq;
+typedef struct tksm_seq_batch tksm_seq_batch;
+
+typedef struct tksm_seq_config {
+    int device;               /* CUDA device ordinal */
+    uint64_t seed;            /* -s/--seed (src/module.h:88-91); default 42 */
+    double identity_mean;     /* --badread-identity mean,max,stdev (percent); default 84,99,5.5 */
+    double identity_max;
+    double identity_stdev;
+    int skip_qual_compute;    /* --skip-qual-compute */
+    double corr0, corr1;      /* identity calibration, NaN => built-in default for the model */
+    uint64_t batch_reads;     /* streaming batch limits, 0 => defaults */
+    uint64_t batch_bases;
+    int host_only;            /* 1 => no device (table packing / parsing only; run calls fail) */
+} tksm_seq_config;
+
+/* which outputs a run produces */
+enum { TKSM_SEQ_BADREAD = 1, TKSM_SEQ_PERFECT = 2 };
+/* record formats (py/sequence.py:291-300: chosen per output file by its extension);
+ * bit 0 = badread output is FASTQ, bit 1 = perfect output is FASTQ */
+enum { TKSM_SEQ_FASTA = 0, TKSM_SEQ_FASTQ_BADREAD = 1, TKSM_SEQ_FASTQ_PERFECT = 2, TKSM_SEQ_FASTQ = 3 };
+
+typedef struct tksm_seq_stats {
+    uint64_t reads;
+    uint64_t raw_bases;        /* sum of error-free lengths */
+    uint64_t read_bases;       /* sum of simulated read lengths (badread output) */
+    uint64_t out_bytes[2];     /* [0] badread, [1] perfect */
+    uint64_t algorithmic_bytes;/* inputs read + records written */
+    uint64_t h2d_bytes, d2h_bytes;
+    double kernel_ms;          /* CUDA-event time of the kernel sequence */
+    double simulate_ms;        /* of which: simulate kernels */
+    uint32_t kernel_launches;
+    uint32_t status_or;        /* OR of per-read status words (0 = clean) */
+} tksm_seq_stats;
+
+/* host copies of the packed model tables, for the parity tests and the CPU twin */
+typedef struct tksm_seq_tables {
+    int k, has_err_table;
+    const uint16_t* q16; size_t n_q16;
+    const uint32_t* err_alias; size_t n_err_alias;
+    const uint64_t* err_alts; size_t n_err_alts;
+    int ident_const; float ident_mean;
+    const float* ident_tab; size_t n_ident_tab;
+    const float* delta_tab; size_t n_delta_tab;
+    float corr0, corr1;
+    int kq;
+    const uint32_t* q_direct; size_t n_q_direct; uint32_t q_direct_off[5];
+    const uint64_t* q_hash; size_t n_q_hash;      /* entries of 2 x u64: key, row */
+    uint32_t q_hash_shift, q_hash_mask;
+    const uint32_t* q_rows; size_t n_q_rows;      /* pairs: alias offset, log2 columns */
+    const uint32_t* q_alias; size_t n_q_alias;
+    uint64_t seed;
+    int compute_qual;
+} tksm_seq_tables;
+
+void tksm_seq_default_config(tksm_seq_config* cfg);
+tksm_seq* tksm_seq_create(const tksm_seq_config* cfg);   /* NULL on failure, see tksm_seq_last_error(NULL) */
+void tksm_seq_destroy(tksm_seq* h);
+const char* tksm_seq_last_error(const tksm_seq* h);
+void tksm_seq_free(void* p);
+
+int tksm_seq_load_references(tksm_seq* h, const char* const* fasta_paths, int n_paths);
+int tksm_seq_add_reference_text(tksm_seq* h, const char* fasta_text, size_t len);
+/* synthetic reference generated on the device: contig i is named names[i] and holds lengths[i]
+ * uniform ACGT bases with n_frac of them replaced by 'N' runs (bench helper) */
+int tksm_seq_synth_reference(tksm_seq* h, const char* const* names, const uint64_t* lengths, int n_contigs,
+                             double n_frac, uint64_t seed);
+/* copies the upper-cased bytes of contig[start, start+len) into out (tests) */
+int tksm_seq_fetch_reference(tksm_seq* h, const char* contig, uint64_t start, uint64_t len, char* out);
+int tksm_seq_commit_reference(tksm_seq* h);   /* upload; implicit on first run */
+
+/* names are looked up in $TKSM_MODELS (py/sequence.py:17-31) unless they are paths;
+ * NULL selects the reference defaults (nanopore2020 if found else random; no_noise) */
+int tksm_seq_load_models(tksm_seq* h, const char* error_model, const char* qscore_model, const char* tail_model);
+int tksm_seq_get_tables(tksm_seq* h, tksm_seq_tables* out);
+
+/* MDF file (or FIFO) -> output files; NULL path => that output is not produced */
+int tksm_seq_run_files(tksm_seq* h, const char* mdf_path, const char* badread_path, const char* perfect_path,
+                       tksm_seq_stats* stats);
+
+/* MDF text in host memory -> records in host memory (library-owned *out) */
+int tksm_seq_simulate_text(tksm_seq* h, const char* mdf, size_t mdf_len, int which, int format, uint64_t ordinal_base,
+                           char** out, size_t* out_len, tksm_seq_stats* stats);
+
+/* device-resident path: parse + upload once, run the kernel sequence any number of times */
+tksm_seq_batch* tksm_seq_batch_create(tksm_seq* h, const char* mdf, size_t mdf_len, uint64_t ordinal_base);
+int tksm_seq_batch_run(tksm_seq* h, tksm_seq_batch* b, int which, int format, tksm_seq_stats* stats);
+int tksm_seq_batch_fetch(tksm_seq* h, tksm_seq_batch* b, int which, char** out, size_t* out_len);
+void tksm_seq_batch_destroy(tksm_seq* h, tksm_seq_batch* b);
+
+/* synthetic MDF text in the emitter format of src/interval.h:898-905 (bench / tests);
+ * shape: 0 = Tsb only (depth >= 1), 1 = Tsb->Trc->plA->Flp->Tag (README bulk), 2 = single long
+ * intervals with log-uniform lengths in [min_len, max_len] */
+int tksm_seq_synth_mdf(tksm_seq* h, int shape, uint64_t n_molecules, uint64_t seed, uint32_t min_len,
+                       uint32_t max_len, char** out, size_t* out_len);
+
+/* the module entry point: argv[0] == "sequence" */
+int tksm_sequence_main(int argc, char** argv);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

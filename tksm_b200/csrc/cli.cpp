@@ -1,0 +1,260 @@
+// `tksm sequence` command line: same flags, defaults, messages and exit codes as the argparse
+// front-end of the reference (py/sequence.py:34-165), in front of the C ABI.
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/tksm_seq.h"
+#include "sequence.h"
+
+namespace {
+
+struct Opt {
+    const char* dest;     // argparse dest, printed by --list
+    const char* long_;    // long flag without dashes
+    char short_;          // 0 if none
+    int nargs;            // 0 flag, 1 one value, -1 one or more
+};
+
+const Opt OPTS[] = {
+    {"help", "help", 'h', 0},
+    {"input", "input", 'i', 1},
+    {"references", "references", 'r', -1},
+    {"badread", "badread", 'o', 1},
+    {"perfect", "perfect", 0, 1},
+    {"skip_qual_compute", "skip-qual-compute", 0, 0},
+    {"output_format", "output-format", 'O', 1},
+    {"threads", "threads", 't', 1},
+    {"badread_identity", "badread-identity", 0, 1},
+    {"badread_error_model", "badread-error-model", 0, 1},
+    {"badread_qscore_model", "badread-qscore-model", 0, 1},
+    {"badread_tail_model", "badread-tail-model", 0, 1},
+    {"list", "list", 0, 0},
+    // extensions without a reference counterpart
+    {"seed", "seed", 's', 1},
+    {"gpus", "gpus", 0, 1},
+    {"device", "device", 0, 1},
+};
+const int N_OPTS = sizeof(OPTS) / sizeof(OPTS[0]);
+
+void usage(FILE* f) {
+    fprintf(f,
+            "usage: sequence [-h] -i INPUT [-r REFERENCES [REFERENCES ...]] [-o BADREAD] [--perfect PERFECT]\n"
+            "                [--skip-qual-compute] [-O {fastq,fasta}] [-t THREADS]\n"
+            "                [--badread-identity BADREAD_IDENTITY] [--badread-error-model BADREAD_ERROR_MODEL]\n"
+            "                [--badread-qscore-model BADREAD_QSCORE_MODEL] [--badread-tail-model BADREAD_TAIL_MODEL]\n"
+            "                [--list] [-s SEED] [--device DEVICE]\n");
+}
+
+int usage_error(const std::string& msg) {
+    usage(stderr);
+    fprintf(stderr, "sequence: error: %s\n", msg.c_str());
+    return 2;
+}
+
+}  // namespace
+
+extern "C" int tksm_sequence_main(int argc, char** argv) {
+    std::string input, badread, perfect, identity = "84.0,99.0,5.5", err_model, qs_model, tail_model, out_fmt;
+    std::vector<std::string> refs;
+    bool have_err = false, have_qs = false, have_tail = false, skip_qual = false, have_input = false;
+    long long seed = 42;
+    int device = 0;
+    for (int a = 1; a < argc; a++) {
+        std::string arg = argv[a];
+        const Opt* opt = nullptr;
+        std::string inline_val;
+        bool has_inline = false;
+        if (arg.size() >= 3 && arg[0] == '-' && arg[1] == '-') {
+            std::string name = arg.substr(2);
+            size_t eq = name.find('=');
+            if (eq != std::string::npos) {
+                inline_val = name.substr(eq + 1);
+                name = name.substr(0, eq);
+                has_inline = true;
+            }
+            // exact match, else unique prefix (argparse allow_abbrev)
+            int hits = 0;
+            for (int i = 0; i < N_OPTS; i++)
+                if (name == OPTS[i].long_) {
+                    opt = &OPTS[i];
+                    hits = 1;
+                    break;
+                }
+            if (!opt)
+                for (int i = 0; i < N_OPTS; i++)
+                    if (strncmp(OPTS[i].long_, name.c_str(), name.size()) == 0) {
+                        opt = &OPTS[i];
+                        hits++;
+                    }
+            if (hits > 1) return usage_error("ambiguous option: --" + name);
+            if (!opt) return usage_error("unrecognized arguments: " + arg);
+        } else if (arg.size() >= 2 && arg[0] == '-' && arg[1] != '-') {
+            for (int i = 0; i < N_OPTS; i++)
+                if (OPTS[i].short_ && OPTS[i].short_ == arg[1]) opt = &OPTS[i];
+            if (!opt) return usage_error("unrecognized arguments: " + arg);
+            if (arg.size() > 2) {
+                inline_val = arg.substr(2);
+                has_inline = true;
+            }
+        } else {
+            return usage_error("unrecognized arguments: " + arg);
+        }
+        std::vector<std::string> vals;
+        if (opt->nargs == 0) {
+            if (has_inline) return usage_error(std::string("ignored explicit argument '") + inline_val + "'");
+        } else if (has_inline) {
+            vals.push_back(inline_val);
+        } else if (opt->nargs == 1) {
+            if (a + 1 >= argc) return usage_error(std::string("argument --") + opt->long_ + ": expected one argument");
+            vals.push_back(argv[++a]);
+        } else {
+            while (a + 1 < argc && !(argv[a + 1][0] == '-' && argv[a + 1][1] != 0)) vals.push_back(argv[++a]);
+            if (vals.empty())
+                return usage_error(std::string("argument --") + opt->long_ + ": expected at least one argument");
+        }
+        std::string d = opt->dest;
+        if (d == "help") {
+            usage(stdout);
+            printf(
+                "\nSequencer module of tksm. Generates FASTQ/A file from MDF (molecule description file) and "
+                "reference FASTA files. Note: tksm looks for sequencing model names in colon sperated paths in "
+                "$TKSM_MODELS environment variable. Current $TKSM_MODELS value: %s\n",
+                getenv("TKSM_MODELS") ? getenv("TKSM_MODELS") : "None");
+            return 0;
+        } else if (d == "list") {
+            for (int i = 0; i < N_OPTS; i++) printf("%s\n", OPTS[i].dest);  // py/sequence.py:116-122
+            return 0;
+        } else if (d == "input") {
+            input = vals[0];
+            have_input = true;
+        } else if (d == "references") {
+            refs = vals;
+        } else if (d == "badread") {
+            badread = vals[0];
+        } else if (d == "perfect") {
+            perfect = vals[0];
+        } else if (d == "skip_qual_compute") {
+            skip_qual = true;
+        } else if (d == "output_format") {
+            if (vals[0] != "fastq" && vals[0] != "fasta")
+                return usage_error("argument -O/--output-format: invalid choice: '" + vals[0] +
+                                   "' (choose from 'fastq', 'fasta')");
+            out_fmt = vals[0];  // parsed and never used, like the reference
+        } else if (d == "threads") {
+            char* e = nullptr;
+            strtol(vals[0].c_str(), &e, 10);
+            if (*e) return usage_error("argument -t/--threads: invalid int value: '" + vals[0] + "'");
+        } else if (d == "badread_identity") {
+            identity = vals[0];
+        } else if (d == "badread_error_model") {
+            err_model = vals[0];
+            have_err = true;
+        } else if (d == "badread_qscore_model") {
+            qs_model = vals[0];
+            have_qs = true;
+        } else if (d == "badread_tail_model") {
+            tail_model = vals[0];
+            have_tail = true;
+        } else if (d == "seed") {
+            char* e = nullptr;
+            seed = strtoll(vals[0].c_str(), &e, 10);
+            if (*e) return usage_error("argument -s/--seed: invalid int value: '" + vals[0] + "'");
+        } else if (d == "gpus") {
+            // accepted for forward compatibility; one process drives one device
+        } else if (d == "device") {
+            device = atoi(vals[0].c_str());
+        }
+    }
+    if (!have_input) return usage_error("the following arguments are required: -i/--input");
+
+    // py/sequence.py:134-164
+    double idp[3];
+    {
+        int n = 0;
+        size_t pos = 0;
+        bool bad = false;
+        while (true) {
+            size_t c = identity.find(',', pos);
+            std::string item = identity.substr(pos, c == std::string::npos ? std::string::npos : c - pos);
+            char* e = nullptr;
+            double v = strtod(item.c_str(), &e);
+            while (e && *e == ' ') e++;
+            if (item.empty() || (e && *e)) bad = true;
+            if (n < 3) idp[n] = v;
+            n++;
+            if (c == std::string::npos) break;
+            pos = c + 1;
+        }
+        if (bad) {
+            fprintf(stderr, "Error: could not parse --identity values\n");
+            return 1;
+        }
+        if (n != 3) {
+            fprintf(stderr, "AssertionError: Must specify 3 values for --badread-identity\n");
+            return 1;
+        }
+    }
+    const double mean = idp[0], mx = idp[1], sd = idp[2];
+    auto die = [](const std::string& m) {
+        fprintf(stderr, "%s\n", m.c_str());
+        return 1;
+    };
+    if (mean > 100.0) return die("Error: mean read identity cannot be more than 100");
+    if (mx > 100.0) return die("Error: max read identity cannot be more than 100");
+    if (mean <= 50) return die("Error: mean read identity must be at least 50");
+    if (mx <= 50) return die("Error: max read identity must be at least 50");
+    if (mean > mx) {
+        char b[256];
+        snprintf(b, sizeof b, "Error: mean identity (%g) cannot be larger than max identity (%g)", mean, mx);
+        return die(b);
+    }
+    if (sd < 0.0) return die("Error: read identity stdev cannot be negative");
+    if (badread.empty() && perfect.empty()) return usage_error("Must specify either --output or --perfect.");
+    if (refs.empty()) return die("TypeError: 'NoneType' object is not iterable (no -r/--references given)");
+
+    tksm_seq_config cfg;
+    tksm_seq_default_config(&cfg);
+    cfg.device = device;
+    cfg.seed = (uint64_t)seed;
+    cfg.identity_mean = mean;
+    cfg.identity_max = mx;
+    cfg.identity_stdev = sd;
+    cfg.skip_qual_compute = skip_qual;
+    tksm_seq* h = tksm_seq_create(&cfg);
+    if (!h) return die(std::string("Error: ") + tksm_seq_last_error(nullptr));
+    int rc = 0;
+    std::vector<const char*> paths;
+    for (auto& r : refs) paths.push_back(r.c_str());
+    rc = tksm_seq_load_references(h, paths.data(), (int)paths.size());
+    if (!rc && !badread.empty())
+        rc = tksm_seq_load_models(h, have_err ? err_model.c_str() : nullptr, have_qs ? qs_model.c_str() : nullptr,
+                                  have_tail ? tail_model.c_str() : nullptr);
+    else if (!rc)
+        rc = tksm_seq_load_models(h, "random", "random", nullptr);  // perfect only: models are not consulted
+    tksm_seq_stats st;
+    if (!rc)
+        rc = tksm_seq_run_files(h, input.c_str(), badread.empty() ? nullptr : badread.c_str(),
+                                perfect.empty() ? nullptr : perfect.c_str(), &st);
+    if (rc) {
+        fprintf(stderr, "Error: %s\n", tksm_seq_last_error(h));
+    } else {
+        fprintf(stderr, "Sequencing: %llu reads, %llu bases, %.1f ms on device\n", (unsigned long long)st.reads,
+                (unsigned long long)st.read_bases, st.kernel_ms);
+    }
+    tksm_seq_destroy(h);
+    return rc ? 1 : 0;
+}
+
+class Sequencer_module::impl {
+public:
+    int argc;
+    char** argv;
+    impl(int c, char** v) : argc(c), argv(v) {}
+};
+Sequencer_module::Sequencer_module(int argc, char** argv) : pimpl{std::make_unique<impl>(argc, argv)} {}
+Sequencer_module::~Sequencer_module() = default;
+int Sequencer_module::run() { return tksm_sequence_main(pimpl->argc, pimpl->argv); }

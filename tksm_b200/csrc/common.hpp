@@ -1,0 +1,128 @@
+// Shared host/device definitions for the tksm Seq hot path (B200 build).
+//
+// Everything in here is plain data: packed model tables, the molecule batch
+// (structure-of-arrays) and the constants of the "PB1" stochastic model
+// (Poissonised Badread).  The CPU twin in oracle/twin.c
+// restates the same constants independently; tests assert both agree.
+#pragma once
+#include <cstdint>
+
+namespace tk {
+
+// ---------------------------------------------------------------- Philox tags
+// counter = (c0 = index, c1 = tag word, c2 = read ordinal lo, c3 = read ordinal hi)
+// key     = (seed lo, seed hi)
+enum : uint32_t {
+    TAG_READ = 0,    // c0 = 0: identity draw (w0); c0 = 1: uuid (w0..w3); c0 = 2: flanks (w0 left, w1 right)
+    TAG_ARRIVE = 1,  // | epoch << 8 ; c0 = start position >> 2 ; word = start position & 3
+    TAG_TRIAL = 2,   // | epoch << 8 | trial << 20 ; c0 = start position
+    TAG_QUAL = 3,    // c0 = untrimmed read base index >> 2 ; word = index & 3
+};
+
+constexpr int MAX_K = 7;             // error-model k-mer size supported (4^7 rows)
+constexpr int ERR_ALIAS_COLS = 32;   // alias columns per k-mer row
+constexpr int ERR_ALT_STRIDE = 32;   // alt words per k-mer row
+constexpr uint32_t ERR_OUTCOME_RANDOM = 31;
+constexpr int MAX_TRIALS_PER_EPOCH = 8;   // Poisson count cap per start position and epoch
+constexpr int MAX_SLOT_LEN = 5;      // bases one fragment slot can hold after an edit
+constexpr int IDENT_TAB_BINS = 4096;
+constexpr int DELTA_TAB_BINS = 64;
+constexpr float TIME_CAP = 100.0f;   // py/tksm_badread.py:354 (loop_count > 100 * frag_len)
+constexpr uint32_t KEY_UNTOUCHED = 0xFFFFFFFFu;
+
+// content16 (low half of a slot key)
+//   [15:13] len (0..5)   [12:11] kind   [10:1] bases, 2 bits each, first base lowest   [0] zero
+// kind 0: literal bases; kind 1: original byte followed by one inserted base;
+// kind 2: one inserted base followed by the original byte.
+constexpr uint32_t CONTENT_LEN_SHIFT = 13;
+constexpr uint32_t CONTENT_KIND_SHIFT = 11;
+
+// cigar symbols used by the qscore stage
+enum : uint32_t { OP_EQ = 0, OP_X = 1, OP_I = 2, OP_D = 3 };
+
+// ------------------------------------------------------------ qscore tables
+struct QRow {
+    uint32_t off;   // first alias column
+    uint32_t lg;    // log2 of the column count
+};
+
+struct QHashEntry {
+    uint64_t key;   // 0 = empty; else sentinel-1-prefixed 2-bit symbol string
+    uint32_t row;
+    uint32_t pad;
+};
+
+// ------------------------------------------------------------- device views
+struct DevTables {
+    // genome
+    const uint32_t* genome;       // 2-bit codes, 16 bases per word, A=0 C=1 G=2 T=3
+    const uint64_t* exc_start;    // sorted run starts (global base coordinate)
+    const uint32_t* exc_len;
+    const uint8_t* exc_chr;       // upper-cased byte of the run
+    uint32_t n_exc;
+    // error model
+    int k;                        // k-mer size (1 for the "random" model)
+    int has_err_table;            // 0 => every trial is a random change
+    const uint16_t* q16;          // 4^k: P(trial changes something) * 65536, saturated
+    const uint32_t* err_alias;    // 4^k * 32: thr22 | a << 22 | b << 27
+    const uint64_t* err_alts;     // 4^k * 32 edit words
+    // identity
+    int ident_const;              // 1 => every read gets ident_mean
+    float ident_mean;
+    const float* ident_tab;       // IDENT_TAB_BINS + 1 quantiles (already times max identity)
+    const float* delta_tab;       // DELTA_TAB_BINS epoch lengths over target in [0.5, 1]
+    float corr0, corr1;           // effective target = target + corr0 + corr1 * (1 - target)
+    // qscore model
+    int kq;                       // odd, <= 9
+    const uint32_t* q_direct;     // concatenated direct maps for widths 1,3,5,7,9 (3^w entries each)
+    uint32_t q_direct_off[5];
+    const QHashEntry* q_hash;
+    uint32_t q_hash_shift;        // 64 - log2(size)
+    uint32_t q_hash_mask;
+    const QRow* q_rows;
+    const uint32_t* q_alias;      // thr18 | qa << 18 | qb << 25
+    uint32_t seed_lo, seed_hi;
+};
+
+// seg_src layout
+constexpr uint64_t SEG_LITERAL = 1ull << 63;
+constexpr uint64_t SEG_MINUS = 1ull << 62;
+constexpr uint64_t SEG_HAS_EXC = 1ull << 61;
+constexpr uint64_t SEG_OFF_MASK = (1ull << 56) - 1;
+
+struct DevBatch {
+    uint32_t n_reads;
+    uint64_t ordinal_base;
+    const uint32_t* read_mol;      // molecule index per read (depth expansion)
+    const uint32_t* mol_seg_begin; // M + 1
+    const uint32_t* mol_raw_len;   // M
+    const uint32_t* mol_id_begin;  // M + 1, into id_pool
+    const uint64_t* seg_src;
+    const uint32_t* seg_len;
+    const uint32_t* seg_mod_begin; // S + 1 or nullptr when the batch has no mods
+    const uint32_t* mod_pos;
+    const uint8_t* mod_chr;
+    const uint8_t* lit_pool;       // literal segments as fragment codes
+    const uint8_t* id_pool;
+    // per-read scratch produced by the simulate kernel
+    const uint64_t* scr_off;       // R + 1; read r owns [scr_off[r], scr_off[r+1]) in each arena
+    uint8_t* scr_seq;
+    uint8_t* scr_qual;
+    uint8_t* scr_raw;              // error-free sequence (perfect output) or nullptr
+    const uint64_t* raw_off;       // R + 1 when scr_raw != nullptr
+    uint32_t* read_len;            // L'
+    uint32_t* ident_num;           // matches
+    uint32_t* ident_den;           // alignment columns
+    uint32_t* status;              // 0 ok, else error bits
+};
+
+enum : uint32_t { ST_OK = 0, ST_OPS_OVERFLOW = 1, ST_SCRATCH_OVERFLOW = 2, ST_EPOCH_CAP = 4 };
+
+// run flags
+enum : uint32_t {
+    RUN_ERRORS = 1,     // inject errors (badread output requested)
+    RUN_QUAL = 2,       // compute qscores
+    RUN_RAW = 4,        // also store the error-free sequence
+};
+
+}  // namespace tk

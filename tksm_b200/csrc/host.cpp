@@ -1,0 +1,427 @@
+// Reference genome store, MDF parser and molecule batch (see host.hpp for the reference mapping).
+#include "host.hpp"
+
+#include <algorithm>
+#include <cstring>
+#include <stdexcept>
+#include <string_view>
+
+#include "model.hpp"  // read_text_maybe_gz
+
+namespace tk {
+
+// ------------------------------------------------------------------ genome
+
+void GenomeStore::add_contig(const std::string& name, const char* seq, size_t len) {
+    // every contig starts on a 64-base boundary so 128-bit loads of a contig prefix stay aligned
+    n_bases = (n_bases + 63) & ~uint64_t(63);
+    const uint64_t off = n_bases;
+    words.resize((size_t)((off + len + 63) / 64) * 4 + 4, 0);
+    uint64_t run_start = 0;
+    uint32_t run_len = 0;
+    uint8_t run_chr = 0;
+    auto flush = [&]() {
+        if (run_len) {
+            exc_start.push_back(run_start);
+            exc_len.push_back(run_len);
+            exc_chr.push_back(run_chr);
+            run_len = 0;
+        }
+    };
+    for (size_t i = 0; i < len; i++) {
+        uint8_t c = ascii_upper((uint8_t)seq[i]);
+        uint8_t code = frag_code(c);
+        uint64_t g = off + i;
+        if (code < 4) {
+            words[(size_t)(g >> 4)] |= (uint32_t)code << (2 * (g & 15));
+            flush();
+        } else {
+            if (run_len && run_chr == c && run_start + run_len == g && run_len < 0xFFFFFFFFu) {
+                run_len++;
+            } else {
+                flush();
+                run_start = g;
+                run_len = 1;
+                run_chr = c;
+            }
+        }
+    }
+    flush();
+    n_bases = off + len;
+    contigs[name] = Contig{off, (uint64_t)len};  // later files override earlier names (dict.update)
+}
+
+void GenomeStore::load_fasta_text(const char* text, size_t len) {
+    // py/sequence.py:168-186 in text mode: universal newlines, name = header up to the first space,
+    // a header that follows a header without sequence replaces it, an empty line raises.
+    std::string name, seq;
+    bool have_seq_lines = false;
+    size_t pos = 0;
+    auto emit = [&]() { add_contig(name, seq.data(), seq.size()); };
+    while (pos < len) {
+        const char* p = text + pos;
+        const char* nl = (const char*)memchr(p, '\n', len - pos);
+        size_t eol = nl ? (size_t)(nl - text) : len;
+        size_t next = nl ? eol + 1 : len;
+        const char* cr = (const char*)memchr(p, '\r', eol - pos);
+        if (cr) {
+            size_t r = (size_t)(cr - text);
+            next = (r + 1 == eol && nl) ? eol + 1 : r + 1;
+            eol = r;
+        }
+        if (eol == pos) throw std::runtime_error("IndexError: empty line in FASTA (py/sequence.py:177)");
+        if (text[pos] == '>') {
+            std::string_view hdr(text + pos + 1, eol - pos - 1);
+            size_t sp = hdr.find(' ');
+            std::string nm(hdr.substr(0, sp));
+            if (!have_seq_lines) {
+                name = nm;
+            } else {
+                emit();
+                seq.clear();
+                have_seq_lines = false;
+                name = nm;
+            }
+        } else {
+            seq.append(text + pos, eol - pos);
+            have_seq_lines = true;
+        }
+        pos = next;
+    }
+    emit();
+}
+
+void GenomeStore::load_fasta(const std::string& path) {
+    std::string text = read_text_maybe_gz(path);
+    load_fasta_text(text.data(), text.size());
+}
+
+bool GenomeStore::overlaps_exception(uint64_t start, uint64_t len) const {
+    if (exc_start.empty() || len == 0) return false;
+    // first run with start >= `start`; the run before it may still reach into the range
+    size_t i = (size_t)(std::lower_bound(exc_start.begin(), exc_start.end(), start) - exc_start.begin());
+    if (i < exc_start.size() && exc_start[i] < start + len) return true;
+    if (i > 0 && exc_start[i - 1] + exc_len[i - 1] > start) return true;
+    return false;
+}
+
+std::string GenomeStore::fetch(uint64_t start, uint64_t len) const {
+    std::string s((size_t)len, '?');
+    for (uint64_t i = 0; i < len; i++) {
+        uint64_t g = start + i;
+        s[(size_t)i] = "ACGT"[(words[(size_t)(g >> 4)] >> (2 * (g & 15))) & 3];
+    }
+    size_t r = (size_t)(std::lower_bound(exc_start.begin(), exc_start.end(), start) - exc_start.begin());
+    if (r > 0) r--;
+    for (; r < exc_start.size() && exc_start[r] < start + len; r++) {
+        uint64_t a = std::max(exc_start[r], start), b = std::min(exc_start[r] + exc_len[r], start + len);
+        for (uint64_t g = a; g < b; g++) s[(size_t)(g - start)] = (char)exc_chr[r];
+    }
+    return s;
+}
+
+// ------------------------------------------------------------------- batch
+
+void HostBatch::clear() {
+    read_mol.clear();
+    mol_seg_begin.assign(1, 0);
+    mol_raw_len.clear();
+    mol_id_begin.assign(1, 0);
+    seg_src.clear();
+    seg_len.clear();
+    seg_mod_begin.assign(1, 0);
+    mod_pos.clear();
+    mod_chr.clear();
+    lit_pool.clear();
+    id_pool.clear();
+    lit_index.clear();
+    total_raw_bases = genomic_bases = literal_bases = 0;
+}
+
+void HostBatch::append(const HostBatch& o) {
+    const uint32_t mol0 = (uint32_t)n_mols(), seg0 = (uint32_t)seg_src.size(), mod0 = (uint32_t)mod_pos.size();
+    const uint64_t lit0 = lit_pool.size();
+    const uint32_t id0 = (uint32_t)id_pool.size();
+    for (uint32_t m : o.read_mol) read_mol.push_back(m + mol0);
+    for (size_t i = 1; i < o.mol_seg_begin.size(); i++) mol_seg_begin.push_back(o.mol_seg_begin[i] + seg0);
+    mol_raw_len.insert(mol_raw_len.end(), o.mol_raw_len.begin(), o.mol_raw_len.end());
+    for (size_t i = 1; i < o.mol_id_begin.size(); i++) mol_id_begin.push_back(o.mol_id_begin[i] + id0);
+    for (uint64_t s : o.seg_src) seg_src.push_back((s & SEG_LITERAL) ? s + lit0 : s);
+    seg_len.insert(seg_len.end(), o.seg_len.begin(), o.seg_len.end());
+    for (size_t i = 1; i < o.seg_mod_begin.size(); i++) seg_mod_begin.push_back(o.seg_mod_begin[i] + mod0);
+    mod_pos.insert(mod_pos.end(), o.mod_pos.begin(), o.mod_pos.end());
+    mod_chr.insert(mod_chr.end(), o.mod_chr.begin(), o.mod_chr.end());
+    lit_pool.insert(lit_pool.end(), o.lit_pool.begin(), o.lit_pool.end());
+    id_pool.insert(id_pool.end(), o.id_pool.begin(), o.id_pool.end());
+    total_raw_bases += o.total_raw_bases;
+    genomic_bases += o.genomic_bases;
+    literal_bases += o.literal_bases;
+}
+
+// -------------------------------------------------------------------- MDF
+
+namespace {
+
+struct Line {
+    const char* b;
+    const char* e;
+};
+
+// universal-newline line splitter; returns false at end of input
+inline bool next_line(const char* text, size_t len, size_t& pos, Line& out, bool& terminated) {
+    if (pos >= len) return false;
+    const char* p = text + pos;
+    const char* nl = (const char*)memchr(p, '\n', len - pos);
+    size_t eol = nl ? (size_t)(nl - text) : len;
+    size_t next = nl ? eol + 1 : len;
+    terminated = nl != nullptr;
+    const char* cr = (const char*)memchr(p, '\r', eol - pos);
+    if (cr) {
+        size_t r = (size_t)(cr - text);
+        if (r + 1 == eol && nl) {
+            next = eol + 1;
+        } else {
+            next = r + 1;
+            terminated = true;
+        }
+        eol = r;
+    }
+    out.b = p;
+    out.e = text + eol;
+    pos = next;
+    return true;
+}
+
+// Python int(): optional surrounding whitespace, sign, digits with single underscores
+long long py_int(const char* b, const char* e) {
+    auto fail = [&]() -> long long {
+        throw std::runtime_error("ValueError: invalid literal for int() with base 10: '" + std::string(b, e) + "'");
+    };
+    while (b < e && isspace((unsigned char)*b)) b++;
+    while (e > b && isspace((unsigned char)e[-1])) e--;
+    if (b == e) return fail();
+    bool neg = false;
+    if (*b == '+' || *b == '-') {
+        neg = *b == '-';
+        b++;
+    }
+    if (b == e || !isdigit((unsigned char)*b)) return fail();
+    long long v = 0;
+    bool prev_us = false;
+    for (; b < e; b++) {
+        if (*b == '_') {
+            if (prev_us) return fail();
+            prev_us = true;
+            continue;
+        }
+        if (!isdigit((unsigned char)*b)) return fail();
+        prev_us = false;
+        if (v > (long long)4e17) throw std::runtime_error("MDF integer out of range");
+        v = v * 10 + (*b - '0');
+    }
+    if (prev_us) return fail();
+    return neg ? -v : v;
+}
+
+inline void py_slice(long long start, long long end, long long n, long long& s, long long& e) {
+    auto norm = [n](long long i) {
+        if (i < 0) {
+            i += n;
+            if (i < 0) i = 0;
+        } else if (i > n) {
+            i = n;
+        }
+        return i;
+    };
+    s = norm(start);
+    e = norm(end);
+    if (e < s) e = s;
+}
+
+struct SvHash {
+    using is_transparent = void;
+    size_t operator()(std::string_view s) const { return std::hash<std::string_view>{}(s); }
+};
+
+}  // namespace
+
+size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out, size_t max_reads,
+                       uint64_t max_bases) {
+    size_t pos = 0, consumed = 0;
+    // state of the record being assembled
+    bool have = false;
+    long long depth = 0;
+    uint32_t raw_len = 0;
+    uint64_t gen_b = 0, lit_b = 0;
+    size_t rec_start = 0;
+    // roll-back marks
+    size_t m_seg = 0, m_mod = 0, m_lit = 0, m_id = 0;
+
+    std::string last_chrom;
+    const Contig* last_contig = nullptr;
+    bool last_known = false;
+
+    auto mark = [&]() {
+        m_seg = out.seg_src.size();
+        m_mod = out.mod_pos.size();
+        m_lit = out.lit_pool.size();
+        m_id = out.id_pool.size();
+    };
+    auto rollback = [&]() {
+        out.seg_src.resize(m_seg);
+        out.seg_len.resize(m_seg);
+        out.seg_mod_begin.resize(m_seg + 1);
+        out.mod_pos.resize(m_mod);
+        out.mod_chr.resize(m_mod);
+        // literals appended by the rolled-back record may be indexed: drop the index entries lazily
+        if (out.lit_pool.size() != m_lit) {
+            for (auto it = out.lit_index.begin(); it != out.lit_index.end();)
+                it = it->second >= m_lit ? out.lit_index.erase(it) : std::next(it);
+            out.lit_pool.resize(m_lit);
+        }
+        out.id_pool.resize(m_id);
+    };
+    auto commit = [&]() {
+        // py/sequence.py:208-210: the record is yielded `depth` times
+        if (depth > 0) {
+            uint32_t mol = (uint32_t)out.n_mols();
+            out.mol_raw_len.push_back(raw_len);
+            out.mol_seg_begin.push_back((uint32_t)out.seg_src.size());
+            out.mol_id_begin.push_back((uint32_t)out.id_pool.size());
+            for (long long d = 0; d < depth; d++) out.read_mol.push_back(mol);
+            out.total_raw_bases += (uint64_t)raw_len * (uint64_t)depth;
+            out.genomic_bases += gen_b * (uint64_t)depth;
+            out.literal_bases += lit_b * (uint64_t)depth;
+        } else {
+            rollback();
+        }
+        have = false;
+    };
+
+    Line ln;
+    bool terminated = false;
+    while (true) {
+        size_t line_start = pos;
+        if (!next_line(text, len, pos, ln, terminated)) break;
+        if (!final && !terminated) {  // partial last line: wait for more data
+            pos = line_start;
+            break;
+        }
+        if (ln.b == ln.e) throw std::runtime_error("IndexError: empty line in MDF (py/sequence.py:207)");
+        if (*ln.b == '+') {
+            if (have) {
+                commit();
+                consumed = line_start;
+                if (out.n_reads() >= max_reads || out.total_raw_bases >= max_bases) return consumed;
+            } else {
+                consumed = line_start;
+            }
+            const char* t1 = (const char*)memchr(ln.b, '\t', (size_t)(ln.e - ln.b));
+            if (!t1) throw std::runtime_error("IndexError: MDF header without depth field");
+            const char* t2 = (const char*)memchr(t1 + 1, '\t', (size_t)(ln.e - t1 - 1));
+            depth = py_int(t1 + 1, t2 ? t2 : ln.e);
+            mark();
+            out.id_pool.insert(out.id_pool.end(), (const uint8_t*)ln.b + 1, (const uint8_t*)t1);
+            have = true;
+            raw_len = 0;
+            gen_b = lit_b = 0;
+            rec_start = line_start;
+            (void)rec_start;
+            continue;
+        }
+        // interval line: chr, start, end, strand[, mods]
+        const char* f[6];
+        int nf = 0;
+        f[0] = ln.b;
+        for (const char* p = ln.b; p < ln.e && nf < 5;) {
+            const char* t = (const char*)memchr(p, '\t', (size_t)(ln.e - p));
+            if (!t) break;
+            f[++nf] = t + 1;
+            p = t + 1;
+        }
+        nf++;  // number of fields seen (capped at 6)
+        if (nf < 4) throw std::runtime_error("ValueError: not enough values to unpack (MDF interval line)");
+        if (nf > 5) throw std::runtime_error("ValueError: too many values to unpack (MDF interval line)");
+        auto fend = [&](int i) { return i + 1 < nf ? f[i + 1] - 1 : ln.e; };
+        long long start = py_int(f[1], fend(1)), end = py_int(f[2], fend(2));
+        bool plus = (fend(3) - f[3] == 1) && *f[3] == '+';
+        if (!have) continue;  // intervals before the first header are parsed and dropped (py:213)
+
+        std::string_view chrom(f[0], (size_t)(fend(0) - f[0]));
+        if (!(last_known && chrom == last_chrom)) {
+            last_chrom.assign(chrom);
+            auto it = genome->contigs.find(last_chrom);
+            last_contig = it == genome->contigs.end() ? nullptr : &it->second;
+            last_known = true;
+        }
+        long long s, e;
+        uint64_t src;
+        uint32_t slen;
+        if (last_contig) {
+            py_slice(start, end, (long long)last_contig->length, s, e);
+            slen = (uint32_t)(e - s);
+            uint64_t g = last_contig->offset + (uint64_t)s;
+            src = g;
+            if (genome->overlaps_exception(g, slen)) src |= SEG_HAS_EXC;
+            gen_b += slen;
+        } else {
+            // unknown contig: the name itself is the sequence (py/sequence.py:307)
+            py_slice(start, end, (long long)chrom.size(), s, e);
+            slen = (uint32_t)(e - s);
+            std::string lit((size_t)slen, 0);
+            for (uint32_t i = 0; i < slen; i++) lit[i] = (char)frag_code(ascii_upper((uint8_t)chrom[(size_t)s + i]));
+            uint32_t off;
+            auto it = out.lit_index.find(lit);
+            if (it != out.lit_index.end()) {
+                off = it->second;
+            } else {
+                off = (uint32_t)out.lit_pool.size();
+                out.lit_pool.insert(out.lit_pool.end(), lit.begin(), lit.end());
+                if (out.lit_index.size() < (1u << 20)) out.lit_index.emplace(std::move(lit), off);
+            }
+            src = SEG_LITERAL | off;
+            lit_b += slen;
+        }
+        if (!plus) src |= SEG_MINUS;
+        // modifications: applied to the forward slice before the strand flip (py/sequence.py:229-239, 308)
+        if (nf == 5 && fend(4) > f[4]) {
+            size_t m0 = out.mod_pos.size();
+            for (const char* p = f[4]; p <= ln.e;) {
+                const char* c = (const char*)memchr(p, ',', (size_t)(ln.e - p));
+                const char* ie = c ? c : ln.e;
+                if (ie == p) throw std::runtime_error("IndexError: empty modification entry");
+                long long mp = py_int(p, ie - 1);
+                if (mp < 0) mp += slen;
+                if (mp < 0 || mp >= (long long)slen)
+                    throw std::runtime_error("IndexError: list assignment index out of range (modification position)");
+                uint8_t ch = (uint8_t)ie[-1];
+                bool dup = false;
+                for (size_t x = m0; x < out.mod_pos.size(); x++)
+                    if (out.mod_pos[x] == (uint32_t)mp) {
+                        out.mod_chr[x] = ch;  // listed order: the last one wins
+                        dup = true;
+                    }
+                if (!dup) {
+                    out.mod_pos.push_back((uint32_t)mp);
+                    out.mod_chr.push_back(ch);
+                }
+                if (!c) break;
+                p = c + 1;
+            }
+        }
+        out.seg_src.push_back(src);
+        out.seg_len.push_back(slen);
+        out.seg_mod_begin.push_back((uint32_t)out.mod_pos.size());
+        raw_len += slen;
+    }
+    if (final) {
+        if (have) commit();
+        consumed = len;
+    } else if (have) {
+        // incomplete record: undo its partial contents, the caller will feed it again
+        rollback();
+    }
+    return consumed;
+}
+
+}  // namespace tk

@@ -1,0 +1,87 @@
+// Host-side data model of the Seq hot path: reference genome store, MDF parser, molecule batch.
+//
+// Replaces (reference, /root/reference):
+//   generate_fasta / get_reference_seqs   py/sequence.py:168-194
+//   mdf_generator                         py/sequence.py:197-221
+//   the host part of mdf_to_seq           py/sequence.py:303-313 (contig lookup, slice clamping,
+//                                         modification parsing; the byte work runs on the GPU)
+#pragma once
+#include <cstdint>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "common.hpp"
+
+namespace tk {
+
+struct Contig {
+    uint64_t offset;  // global base coordinate of base 0
+    uint64_t length;
+};
+
+// Whole reference as 2-bit codes plus a sorted run list for every byte that is not ACGT
+// after upper-casing (N runs, IUPAC codes, anything else the FASTA holds).
+struct GenomeStore {
+    std::unordered_map<std::string, Contig> contigs;
+    std::vector<uint32_t> words;        // 16 bases per word
+    uint64_t n_bases = 0;               // global coordinate space used so far
+    std::vector<uint64_t> exc_start;
+    std::vector<uint32_t> exc_len;
+    std::vector<uint8_t> exc_chr;
+
+    void add_contig(const std::string& name, const char* seq, size_t len);
+    void load_fasta(const std::string& path);              // plain or .gz
+    void load_fasta_text(const char* text, size_t len);
+    bool overlaps_exception(uint64_t start, uint64_t len) const;
+    // test / oracle helper: the upper-cased bytes of [start, start + len)
+    std::string fetch(uint64_t start, uint64_t len) const;
+};
+
+struct HostBatch {
+    uint64_t ordinal_base = 0;
+    std::vector<uint32_t> read_mol;
+    std::vector<uint32_t> mol_seg_begin{0};
+    std::vector<uint32_t> mol_raw_len;
+    std::vector<uint32_t> mol_id_begin{0};
+    std::vector<uint64_t> seg_src;
+    std::vector<uint32_t> seg_len;
+    std::vector<uint32_t> seg_mod_begin{0};
+    std::vector<uint32_t> mod_pos;
+    std::vector<uint8_t> mod_chr;
+    std::vector<uint8_t> lit_pool;
+    std::vector<uint8_t> id_pool;
+    uint64_t total_raw_bases = 0;   // over reads (depth expanded)
+    uint64_t genomic_bases = 0, literal_bases = 0;  // over reads, for the algorithmic-bytes figure
+    std::unordered_map<std::string, uint32_t> lit_index;
+
+    size_t n_reads() const { return read_mol.size(); }
+    size_t n_mols() const { return mol_raw_len.size(); }
+    void clear();
+    void append(const HostBatch& other);  // concatenates another batch parsed from the next text range
+};
+
+// Streaming MDF parser.  feed() consumes complete records only and returns the number of bytes
+// consumed; the caller keeps the tail and calls again with more data (FIFO-safe, never seeks).
+// With `final` set the remaining bytes are parsed as the last record(s).
+// Throws std::runtime_error where the reference would raise (py/sequence.py:205-218, 229-239).
+struct MdfParser {
+    const GenomeStore* genome;
+    explicit MdfParser(const GenomeStore* g) : genome(g) {}
+    size_t feed(const char* text, size_t len, bool final, HostBatch& out, size_t max_reads = SIZE_MAX,
+                uint64_t max_bases = UINT64_MAX);
+};
+
+// Fragment code of one byte: ACGT -> 0..3, anything else keeps its (ASCII) value.
+inline uint8_t frag_code(uint8_t c) {
+    switch (c) {
+        case 'A': return 0;
+        case 'C': return 1;
+        case 'G': return 2;
+        case 'T': return 3;
+        default: return c;
+    }
+}
+inline uint8_t ascii_upper(uint8_t c) { return (c >= 'a' && c <= 'z') ? (uint8_t)(c - 32) : c; }
+
+}  // namespace tk

@@ -1,0 +1,926 @@
+// sm_100a kernels of the Seq hot path.
+//
+//   simulate_kernel<W>   one team of W warps per read: materialise the molecule from the 2-bit
+//                        genome (interval fetch, base mods, reverse-complement, literal segments;
+//                        py/sequence.py:303-313), inject Badread-model errors with the PB1
+//                        Philox-keyed restatement of sequence_fragment (py/tksm_badread.py:324-451),
+//                        scan slot lengths into read offsets, sample CIGAR-window qscores
+//                        (py/tksm_badread.py:584-655) and store read + quals in scratch.
+//   reclen_kernel        FASTQ/FASTA record length per read (py/sequence.py:242-288).
+//   scan kernels         device-wide exclusive scan of record lengths -> output offsets.
+//   format_kernel        header text + sequence + quals into the contiguous output buffer.
+//
+// No tensor cores: nothing here is a contraction.  The kernels are byte/integer work staged in
+// shared memory; DESIGN.md §4 has the per-kernel byte accounting.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <type_traits>
+
+#include "common.hpp"
+
+namespace tk {
+
+// ------------------------------------------------------------------ Philox
+__device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+                                               uint32_t k1) {
+#pragma unroll
+    for (int r = 0; r < 10; r++) {
+        uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+        c0 = n0;
+        c1 = lo1;
+        c2 = n2;
+        c3 = lo0;
+        k0 += 0x9E3779B9u;
+        k1 += 0xBB67AE85u;
+    }
+    return make_uint4(c0, c1, c2, c3);
+}
+
+__device__ __forceinline__ uint32_t word_of(const uint4& v, uint32_t i) {
+    return i == 0 ? v.x : i == 1 ? v.y : i == 2 ? v.z : v.w;
+}
+
+// exp(-x) for x >= 0 from IEEE fma/mul only, so the CPU twin reproduces it bit for bit.
+__device__ __forceinline__ float expneg(float x) {
+    float y = __fmul_rn(x, 1.44269504f);
+    if (y >= 120.0f) return 0.0f;
+    int i = (int)y;
+    float f = __fsub_rn(y, (float)i);
+    // 2^-f = exp(-f ln2), Taylor to degree 9 on [0, 1)
+    float t = __fmul_rn(f, -0.693147181f);
+    float p = 2.75573192e-6f;
+    p = __fmaf_rn(p, t, 2.48015873e-5f);
+    p = __fmaf_rn(p, t, 1.98412698e-4f);
+    p = __fmaf_rn(p, t, 1.38888889e-3f);
+    p = __fmaf_rn(p, t, 8.33333333e-3f);
+    p = __fmaf_rn(p, t, 4.16666667e-2f);
+    p = __fmaf_rn(p, t, 1.66666667e-1f);
+    p = __fmaf_rn(p, t, 0.5f);
+    p = __fmaf_rn(p, t, 1.0f);
+    p = __fmaf_rn(p, t, 1.0f);
+    return __fmul_rn(p, __uint_as_float((uint32_t)(127 - i) << 23));
+}
+
+// ------------------------------------------------------------------- teams
+template <int W>
+struct Team {
+    static constexpr int SIZE = W * 32;
+    int rank;  // thread rank inside the team
+    int id;    // team index inside the CTA
+    __device__ __forceinline__ void sync() const {
+        if (W == 1)
+            __syncwarp();
+        else
+            asm volatile("bar.sync %0, %1;" ::"r"(id + 1), "n"(W * 32) : "memory");
+    }
+};
+
+__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v) {
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t o = __shfl_up_sync(0xffffffffu, v, d);
+        if (lane >= d) v += o;
+    }
+    return v;
+}
+__device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
+#pragma unroll
+    for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    return v;
+}
+
+// Exclusive scan of one value per thread over the team; `total` gets the team sum.
+// `wsum` is W + 1 words of team-private shared memory.
+template <int W>
+__device__ __forceinline__ uint32_t team_excl_scan(const Team<W>& tm, uint32_t v, uint32_t* wsum, uint32_t& total) {
+    uint32_t inc = warp_incl_scan(v);
+    if (W == 1) {
+        total = __shfl_sync(0xffffffffu, inc, 31);
+        return inc - v;
+    }
+    const int w = tm.rank >> 5;
+    if ((tm.rank & 31) == 31) wsum[w] = inc;
+    tm.sync();
+    uint32_t base = 0, tot = 0;
+#pragma unroll
+    for (int i = 0; i < W; i++) {
+        uint32_t s = wsum[i];
+        if (i < w) base += s;
+        tot += s;
+    }
+    tm.sync();
+    total = tot;
+    return base + inc - v;
+}
+
+template <int W>
+__device__ __forceinline__ uint32_t team_sum(const Team<W>& tm, uint32_t v, uint32_t* wsum) {
+    uint32_t s = warp_sum(v);
+    if (W == 1) return s;
+    if ((tm.rank & 31) == 0) wsum[tm.rank >> 5] = s;
+    tm.sync();
+    uint32_t tot = 0;
+#pragma unroll
+    for (int i = 0; i < W; i++) tot += wsum[i];
+    tm.sync();
+    return tot;
+}
+
+// --------------------------------------------------------------- content16
+__device__ __forceinline__ uint32_t content_len(uint32_t c) { return (c >> CONTENT_LEN_SHIFT) & 7u; }
+__device__ __forceinline__ uint32_t content_kind(uint32_t c) { return (c >> CONTENT_KIND_SHIFT) & 3u; }
+__device__ __forceinline__ uint32_t content_base(uint32_t c, uint32_t i) { return (c >> (1 + 2 * i)) & 3u; }
+
+// (match lost, inserted bases) of a changed slot whose original fragment code is b
+__device__ __forceinline__ void slot_weights(uint32_t c, uint32_t b, uint32_t& loss, uint32_t& ins) {
+    uint32_t len = content_len(c);
+    if (len <= 1) {
+        loss = 1;
+        ins = 0;
+        return;
+    }
+    ins = len - 1;
+    if (content_kind(c) != 0) {
+        loss = 0;
+        return;
+    }
+    loss = !(b < 4 && (content_base(c, 0) == b || content_base(c, len - 1) == b));
+}
+
+__device__ __forceinline__ uint8_t code_ascii(uint32_t c) { return c < 4 ? (uint8_t)(0x54474341u >> (8 * c)) : (uint8_t)c; }
+__device__ __forceinline__ uint32_t ascii_code(uint32_t ch) {
+    return ch == 'A' ? 0u : ch == 'C' ? 1u : ch == 'G' ? 2u : ch == 'T' ? 3u : ch;
+}
+
+// crossing test: estimated identity (n - loss) / (n + ins) <= effective target (tq / 2^24)
+__device__ __forceinline__ bool crossed(uint32_t n, uint32_t loss, uint32_t ins, uint32_t tq) {
+    return ((uint64_t)(n - loss) << 24) <= (uint64_t)tq * (uint64_t)(n + ins);
+}
+
+struct SimParams {
+    DevTables T;
+    DevBatch B;
+    const uint32_t* work;   // read indices of this length class
+    uint32_t n_work;
+    uint32_t* counter;      // dynamic work counter
+    uint32_t flags;         // RUN_*
+    uint32_t ncap;          // fragment capacity of one team workspace
+    uint32_t slab_bytes;    // bytes of one team workspace
+    uint8_t* gws;           // global workspaces (one per CTA) when GWS
+};
+
+// workspace layout (team private): hist[256] (HistT) | misc[32] u32 | key[ncap] u32 | frag[ncap + 16] u8
+template <typename HistT>
+__device__ __forceinline__ uint32_t ws_misc_off() { return 256 * (uint32_t)sizeof(HistT); }
+
+// Finds the first of 256 bins at which the cumulative (loss, ins) crosses the target.
+// Executed by the first warp of the team; results broadcast through misc[].
+//   misc[0] = bin (256 when no crossing), misc[1] = cum loss before bin, misc[2] = cum ins before bin,
+//   misc[3] = total loss, misc[4] = total ins
+template <typename HistT>
+__device__ __forceinline__ void hist_scan_warp(const HistT* hist, uint32_t* misc, uint32_t n, uint32_t loss0,
+                                               uint32_t ins0, uint32_t tq) {
+    const int lane = threadIdx.x & 31;
+    uint32_t la[8], li[8];
+    uint32_t sa = 0, si = 0;
+#pragma unroll
+    for (int b = 0; b < 8; b++) {
+        HistT h = hist[lane * 8 + b];
+        uint32_t a, i;
+        if (sizeof(HistT) == 4) {
+            a = (uint32_t)h & 0xFFFFu;
+            i = (uint32_t)h >> 16;
+        } else {
+            a = (uint32_t)((uint64_t)h & 0xFFFFFFFFull);
+            i = (uint32_t)((uint64_t)h >> 32);
+        }
+        sa += a;
+        si += i;
+        la[b] = sa;
+        li[b] = si;
+    }
+    uint32_t ea = warp_incl_scan(sa) - sa, ei = warp_incl_scan(si) - si;  // exclusive over lanes
+    int first = 8;
+#pragma unroll
+    for (int b = 7; b >= 0; b--)
+        if (crossed(n, loss0 + ea + la[b], ins0 + ei + li[b], tq)) first = b;
+    uint32_t ball = __ballot_sync(0xffffffffu, first < 8);
+    uint32_t tot_a = __shfl_sync(0xffffffffu, ea + sa, 31), tot_i = __shfl_sync(0xffffffffu, ei + si, 31);
+    if (ball == 0) {
+        if (lane == 0) {
+            misc[0] = 256;
+            misc[1] = misc[2] = 0;
+            misc[3] = tot_a;
+            misc[4] = tot_i;
+        }
+    } else {
+        int src = __ffs(ball) - 1;
+        if (lane == src) {
+            misc[0] = (uint32_t)(lane * 8 + first);
+            misc[1] = ea + (first ? la[first - 1] : 0);
+            misc[2] = ei + (first ? li[first - 1] : 0);
+            misc[3] = tot_a;
+            misc[4] = tot_i;
+        }
+    }
+}
+
+template <typename HistT>
+__device__ __forceinline__ void hist_add(HistT* hist, uint32_t bin, uint32_t loss, uint32_t ins) {
+    if (sizeof(HistT) == 4)
+        atomicAdd((uint32_t*)&hist[bin], loss | (ins << 16));
+    else
+        atomicAdd((unsigned long long*)&hist[bin], (unsigned long long)loss | ((unsigned long long)ins << 32));
+}
+
+// ---------------------------------------------------------- qscore lookup
+// ops byte: op | dcount << 2 ; stored in the upper halves of the slot keys
+__device__ __forceinline__ uint32_t ops_at(const uint8_t* keyb, uint32_t j) { return keyb[4 * (j >> 1) + 2 + (j & 1)]; }
+__device__ __forceinline__ void ops_put(uint8_t* keyb, uint32_t j, uint32_t v) { keyb[4 * (j >> 1) + 2 + (j & 1)] = (uint8_t)v; }
+
+__device__ __forceinline__ uint32_t qscore_row(const DevTables& T, const uint8_t* keyb, int start, int end) {
+    // py/tksm_badread.py:584-598 with the window given in read coordinates [start, end]
+    while (true) {
+        const int w = end - start + 1;
+        uint32_t code3 = 0, mul = 1, anyd = 0;
+        uint64_t key = 1;
+        uint32_t nsym = 0;
+        for (int c = start; c <= end; c++) {
+            uint32_t o = ops_at(keyb, (uint32_t)c);
+            uint32_t op = o & 3u, dc = c > start ? (o >> 2) : 0u;
+            anyd |= dc;
+            code3 += op * mul;
+            mul *= 3;
+            nsym += dc + 1;
+            if (nsym <= 31) {
+                key = (key << (2 * dc)) | ((1ull << (2 * dc)) - 1);  // dc times 'D' (3)
+                key = (key << 2) | op;
+            }
+        }
+        if (!anyd) return T.q_direct[T.q_direct_off[w >> 1] + code3];
+        if (nsym <= 31) {
+            uint32_t h = (uint32_t)((key * 0x9E3779B97F4A7C15ull) >> T.q_hash_shift);
+            while (true) {
+                QHashEntry e = T.q_hash[h];
+                if (e.key == key) return e.row;
+                if (e.key == 0) break;
+                h = (h + 1) & T.q_hash_mask;
+            }
+        }
+        start++;
+        end--;
+    }
+}
+
+// ------------------------------------------------------------ simulate one
+template <int W, bool GWS>
+__device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams& P, uint32_t r, uint8_t* ws,
+                                              const uint16_t* q16s) {
+    using HistT = typename std::conditional<(GWS || W >= 8), uint64_t, uint32_t>::type;
+    constexpr int SIZE = Team<W>::SIZE;
+    const DevTables& T = P.T;
+    const DevBatch& B = P.B;
+
+    HistT* hist = (HistT*)ws;
+    uint32_t* misc = (uint32_t*)(ws + ws_misc_off<HistT>());
+    uint32_t* wsum = misc + 8;
+    uint32_t* key = misc + 32;
+    uint8_t* keyb = (uint8_t*)key;
+    uint8_t* frag = (uint8_t*)(key + P.ncap);
+    const uint32_t* fragw = (const uint32_t*)frag;
+
+    const uint32_t mol = B.read_mol[r];
+    const uint32_t L = B.mol_raw_len[mol];
+    const uint32_t k = (uint32_t)T.k;
+    const uint32_t n = L + 2 * k;
+    const uint64_t ordinal = B.ordinal_base + r;
+    const uint32_t olo = (uint32_t)ordinal, ohi = (uint32_t)(ordinal >> 32);
+    const uint32_t k0 = T.seed_lo, k1 = T.seed_hi;
+
+    // ---- 1. materialise flank + molecule + flank as fragment codes
+    {
+        uint4 fl = philox4x32_10(2, TAG_READ, olo, ohi, k0, k1);
+        if (tm.rank < (int)k) {
+            frag[tm.rank] = (uint8_t)((fl.x >> (2 * tm.rank)) & 3u);
+            frag[k + L + tm.rank] = (uint8_t)((fl.y >> (2 * tm.rank)) & 3u);
+        }
+        if (tm.rank < 16) frag[n + tm.rank] = 0;
+        const uint32_t s0 = B.mol_seg_begin[mol], s1 = B.mol_seg_begin[mol + 1];
+        uint32_t off = k;
+        for (uint32_t s = s0; s < s1; s++) {
+            const uint64_t src = B.seg_src[s];
+            const uint32_t len = B.seg_len[s];
+            const bool minus = src & SEG_MINUS;
+            const uint64_t so = src & SEG_OFF_MASK;
+            if (src & SEG_LITERAL) {
+                for (uint32_t x = tm.rank; x < len; x += SIZE) {
+                    uint32_t c = B.lit_pool[so + (minus ? len - 1 - x : x)];
+                    if (minus && c < 4) c ^= 3u;
+                    frag[off + x] = (uint8_t)c;
+                }
+            } else {
+                const bool exc = src & SEG_HAS_EXC;
+                for (uint32_t x = tm.rank; x < len; x += SIZE) {
+                    uint64_t g = so + (minus ? len - 1 - x : x);
+                    uint32_t c = (__ldg(&T.genome[g >> 4]) >> (2 * (uint32_t)(g & 15))) & 3u;
+                    if (minus) c ^= 3u;
+                    if (exc) {
+                        // last run starting at or before g
+                        int lo = 0, hi = (int)T.n_exc;
+                        while (lo < hi) {
+                            int mid = (lo + hi) >> 1;
+                            if (T.exc_start[mid] <= g) lo = mid + 1; else hi = mid;
+                        }
+                        if (lo > 0 && g < T.exc_start[lo - 1] + T.exc_len[lo - 1]) c = T.exc_chr[lo - 1];
+                    }
+                    frag[off + x] = (uint8_t)c;
+                }
+            }
+            if (B.seg_mod_begin) {
+                const uint32_t m0 = B.seg_mod_begin[s], m1 = B.seg_mod_begin[s + 1];
+                if (m1 > m0) {
+                    tm.sync();
+                    for (uint32_t m = m0 + tm.rank; m < m1; m += SIZE) {
+                        uint32_t pos = B.mod_pos[m];
+                        uint32_t c = ascii_code(B.mod_chr[m]);
+                        if (minus && c < 4) c ^= 3u;
+                        frag[off + (minus ? len - 1 - pos : pos)] = (uint8_t)c;
+                    }
+                }
+            }
+            off += len;
+        }
+    }
+    // key init
+    for (uint32_t p = tm.rank; p < n; p += SIZE) key[p] = KEY_UNTOUCHED;
+    tm.sync();
+
+    const uint64_t sbase = B.scr_off[r];
+    const uint32_t scap = (uint32_t)(B.scr_off[r + 1] - sbase);
+    if ((P.flags & RUN_RAW) && B.scr_raw) {
+        uint8_t* raw = B.scr_raw + B.raw_off[r];
+        for (uint32_t x = tm.rank; x < L; x += SIZE) raw[x] = code_ascii(frag[k + x]);
+    }
+    if (!(P.flags & RUN_ERRORS)) {
+        if (tm.rank == 0) {
+            B.read_len[r] = L;
+            B.ident_num[r] = 1;
+            B.ident_den[r] = 1;
+            B.status[r] = ST_OK;
+        }
+        return;
+    }
+
+    // ---- 2. per-read target identity, effective target and epoch length
+    float target;
+    if (T.ident_const) {
+        target = T.ident_mean;
+    } else {
+        uint32_t u = philox4x32_10(0, TAG_READ, olo, ohi, k0, k1).x;
+        uint32_t idx = u >> 20;
+        float f = __fmul_rn((float)(u & 0xFFFFFu), 9.5367431640625e-07f);  // 2^-20
+        float a = T.ident_tab[idx], b = T.ident_tab[idx + 1];
+        target = __fmaf_rn(f, __fsub_rn(b, a), a);
+    }
+    float teff = __fadd_rn(target, __fmaf_rn(T.corr1, __fsub_rn(1.0f, target), T.corr0));
+    uint32_t tq;
+    if (!(teff > 0.0f))
+        tq = 0;
+    else if (teff >= 1.0f)
+        tq = 1u << 24;
+    else
+        tq = (uint32_t)__fmul_rn(teff, 16777216.0f);
+    float delta;
+    {
+        int bin = (int)__fmul_rn(__fsub_rn(teff, 0.5f), 128.0f);
+        bin = bin < 0 ? 0 : bin > DELTA_TAB_BINS - 1 ? DELTA_TAB_BINS - 1 : bin;
+        delta = T.delta_tab[bin];
+    }
+
+    // ---- 3. error injection epochs
+    uint32_t loss_c = 0, ins_c = 0, changed_c = 0;  // committed totals
+    uint32_t status = ST_OK;
+    const uint32_t npos = n - k;
+    const uint32_t nquad = (npos + 3) >> 2;
+    const uint32_t vm0 = k >= 4 ? 0xFCFCFCFCu : (0xFCFCFCFCu >> (8 * (4 - k)));
+    const uint32_t vm1 = k <= 4 ? 0u : (0xFCFCFCFCu >> (8 * (8 - k)));
+    const uint32_t codemask = (1u << (2 * k)) - 1;
+    if (!crossed(n, 0, 0, tq)) {
+        for (uint32_t epoch = 0;; epoch++) {
+            for (uint32_t b = tm.rank; b < 256; b += SIZE) hist[b] = 0;
+            tm.sync();
+            for (uint32_t qd = tm.rank; qd < nquad; qd += SIZE) {
+                const uint32_t w0 = fragw[qd], w1 = fragw[qd + 1], w2 = fragw[qd + 2];
+                const uint4 ur = philox4x32_10(qd, TAG_ARRIVE | (epoch << 8), olo, ohi, k0, k1);
+#pragma unroll
+                for (uint32_t t = 0; t < 4; t++) {
+                    const uint32_t i = 4 * qd + t;
+                    if (i >= npos) break;
+                    const uint32_t x0 = __funnelshift_r(w0, w1, 8 * t), x1 = __funnelshift_r(w1, w2, 8 * t);
+                    const bool valid = T.has_err_table && (((x0 & vm0) | (x1 & vm1)) == 0);
+                    uint32_t code = 0;
+                    float q = 1.0f;
+                    if (valid) {
+                        uint32_t c0 = (x0 | (x0 >> 6)) & 0x000F000Fu;
+                        c0 = (c0 | (c0 >> 12)) & 0xFFu;
+                        uint32_t c1 = (x1 | (x1 >> 6)) & 0x000F000Fu;
+                        c1 = (c1 | (c1 >> 12)) & 0xFFu;
+                        code = (c0 | (c1 << 8)) & codemask;
+                        q = __fmul_rn((float)q16s[code], 1.52587890625e-05f);  // 2^-16
+                    }
+                    const float x = __fmul_rn(q, delta);
+                    const float U = __fmul_rn((float)(word_of(ur, t) >> 8), 5.9604644775390625e-08f);  // 2^-24
+                    float term = expneg(x), cum = term;
+                    if (U < cum) continue;
+                    int N = 1;
+                    for (; N < MAX_TRIALS_PER_EPOCH; N++) {
+                        term = __fmul_rn(__fmul_rn(term, x), __frcp_rn((float)N));
+                        cum = __fadd_rn(cum, term);
+                        if (U < cum) break;
+                    }
+                    for (int tr = 0; tr < N; tr++) {
+                        const uint4 wr = philox4x32_10(i, TAG_TRIAL | (epoch << 8) | ((uint32_t)tr << 20), olo, ohi, k0, k1);
+                        uint32_t tm16 = wr.x >> 16;
+                        tm16 += tm16 == 0;
+                        uint32_t outcome = ERR_OUTCOME_RANDOM;
+                        if (valid) {
+                            uint32_t e = T.err_alias[code * ERR_ALIAS_COLS + (wr.y >> 27)];
+                            uint32_t fr = (wr.y >> 5) & 0x3FFFFFu;
+                            outcome = fr < (e & 0x3FFFFFu) ? ((e >> 22) & 31u) : (e >> 27);
+                        }
+                        if (outcome != ERR_OUTCOME_RANDOM) {
+                            const uint64_t aw = T.err_alts[code * ERR_ALT_STRIDE + outcome];
+                            uint32_t boff = 28;
+                            for (uint32_t j = 0; j < k; j++) {
+                                uint32_t len = (uint32_t)(aw >> (3 * j)) & 7u;
+                                if ((aw >> (21 + j)) & 1ull) {
+                                    uint32_t bases = (uint32_t)(aw >> boff) & ((1u << (2 * len)) - 1);
+                                    uint32_t cand = (tm16 << 16) | (len << CONTENT_LEN_SHIFT) | (bases << 1);
+                                    atomicMin(&key[i + j], cand);
+                                }
+                                boff += 2 * len;
+                            }
+                        } else {
+                            // py/tksm_badread.py:199-213
+                            uint32_t type = __umulhi(wr.z, 3u);
+                            uint32_t pos = __umulhi(wr.w, k);
+                            uint32_t r2 = wr.z & 0xFFFFu;
+                            uint32_t ob = (pos < 4 ? (x0 >> (8 * pos)) : (x1 >> (8 * (pos - 4)))) & 0xFFu;
+                            uint32_t content;
+                            if (type == 0) {
+                                uint32_t nb = ob < 4 ? ((ob + 1 + ((r2 * 3u) >> 16)) & 3u) : (r2 & 3u);
+                                content = (1u << CONTENT_LEN_SHIFT) | (nb << 1);
+                            } else if (type == 1) {
+                                uint32_t nb = r2 & 3u;
+                                uint32_t before = (r2 >> 2) & 1u;
+                                content = (2u << CONTENT_LEN_SHIFT) | ((before ? 2u : 1u) << CONTENT_KIND_SHIFT) | (nb << 1);
+                            } else {
+                                content = 0;
+                            }
+                            atomicMin(&key[i + pos], (tm16 << 16) | content);
+                        }
+                    }
+                }
+            }
+            tm.sync();
+            // histogram of candidate change times, high byte
+            for (uint32_t p = tm.rank; p < n; p += SIZE) {
+                uint32_t kv = key[p];
+                if (kv != KEY_UNTOUCHED && (kv >> 16) != 0) {
+                    uint32_t a, in;
+                    slot_weights(kv & 0xFFFFu, frag[p], a, in);
+                    hist_add<HistT>(hist, kv >> 24, a, in);
+                }
+            }
+            tm.sync();
+            if (tm.rank < 32) hist_scan_warp<HistT>(hist, misc, n, loss_c, ins_c, tq);
+            tm.sync();
+            const uint32_t bin = misc[0], pa = misc[1], pi = misc[2], ta = misc[3], ti = misc[4];
+            if (bin < 256) {
+                // refine inside the crossing bin on the low time byte
+                tm.sync();
+                for (uint32_t b = tm.rank; b < 256; b += SIZE) hist[b] = 0;
+                tm.sync();
+                for (uint32_t p = tm.rank; p < n; p += SIZE) {
+                    uint32_t kv = key[p];
+                    if (kv != KEY_UNTOUCHED && (kv >> 24) == bin && (kv >> 16) != 0) {
+                        uint32_t a, in;
+                        slot_weights(kv & 0xFFFFu, frag[p], a, in);
+                        hist_add<HistT>(hist, (kv >> 16) & 255u, a, in);
+                    }
+                }
+                tm.sync();
+                if (tm.rank < 32) hist_scan_warp<HistT>(hist, misc, n, loss_c + pa, ins_c + pi, tq);
+                tm.sync();
+                const uint32_t lo = misc[0];
+                const uint32_t tstar = (bin << 8) | (lo < 256 ? lo : 255u);
+                tm.sync();
+                // drop later candidates, total up the kept ones
+                uint32_t la = 0, li = 0;
+                for (uint32_t p = tm.rank; p < n; p += SIZE) {
+                    uint32_t kv = key[p];
+                    if (kv != KEY_UNTOUCHED && (kv >> 16) != 0) {
+                        if ((kv >> 16) > tstar) {
+                            key[p] = KEY_UNTOUCHED;
+                        } else {
+                            uint32_t a, in;
+                            slot_weights(kv & 0xFFFFu, frag[p], a, in);
+                            la += a;
+                            li += in;
+                        }
+                    }
+                }
+                loss_c += team_sum<W>(tm, la, wsum);
+                ins_c += team_sum<W>(tm, li, wsum);
+                break;
+            }
+            // no crossing in this epoch: commit every candidate and go on
+            uint32_t cnt = 0;
+            for (uint32_t p = tm.rank; p < n; p += SIZE) {
+                uint32_t kv = key[p];
+                if (kv != KEY_UNTOUCHED && (kv >> 16) != 0) {
+                    key[p] = kv & 0xFFFFu;
+                    cnt++;
+                }
+            }
+            loss_c += ta;
+            ins_c += ti;
+            changed_c += team_sum<W>(tm, cnt, wsum);
+            tm.sync();
+            // py/tksm_badread.py:354-361
+            if ((uint64_t)changed_c * 10 > (uint64_t)n * 9) break;
+            if (__fmul_rn((float)(epoch + 1), delta) > TIME_CAP) {
+                status |= ST_EPOCH_CAP;
+                break;
+            }
+        }
+    }
+    tm.sync();
+
+    // ---- 4. final slot contents: low half = content16 or 0xFFFF (unchanged); high half free for ops
+    for (uint32_t p = tm.rank; p < n; p += SIZE) {
+        uint32_t kv = key[p];
+        key[p] = kv == KEY_UNTOUCHED ? 0x0000FFFFu : (kv & 0xFFFFu);
+    }
+    tm.sync();
+    const uint16_t* key16 = (const uint16_t*)key;
+    auto slot_len = [&](uint32_t p) -> uint32_t {
+        uint32_t c = key16[2 * p];
+        return c == 0xFFFFu ? 1u : content_len(c);
+    };
+    uint32_t start_trim = 0, end_trim = 0;
+    for (uint32_t j = 0; j < k; j++) {
+        start_trim += slot_len(j);
+        end_trim += slot_len(n - k + j);
+    }
+
+    // ---- 5. slot lengths -> read offsets; write read bases and per-base cigar ops
+    uint8_t* oseq = B.scr_seq + sbase;
+    uint32_t carry = 0;
+    const uint32_t opcap = 2 * n;
+    for (uint32_t base = 0; base < n; base += 4 * SIZE) {
+        const uint32_t p0 = base + 4 * tm.rank;
+        uint32_t c[4], len[4], s = 0;
+#pragma unroll
+        for (int t = 0; t < 4; t++) {
+            uint32_t p = p0 + t;
+            c[t] = p < n ? key16[2 * p] : 0u;
+            len[t] = p < n ? (c[t] == 0xFFFFu ? 1u : content_len(c[t])) : 0u;
+            s += len[t];
+        }
+        uint32_t tot;
+        uint32_t o = carry + team_excl_scan<W>(tm, s, wsum, tot);
+        carry += tot;
+#pragma unroll
+        for (int t = 0; t < 4; t++) {
+            const uint32_t p = p0 + t;
+            if (p < n && len[t]) {
+                const uint32_t b = frag[p];
+                // deleted slots right before this one
+                uint32_t dc = 0;
+                for (uint32_t q = p; q > 0 && dc < 15; q--) {
+                    if (key16[2 * (q - 1)] >> CONTENT_LEN_SHIFT != 0) break;  // 0xFFFF and len >= 1 both stop
+                    dc++;
+                }
+                const bool body = p >= k && p < n - k;
+                const uint32_t kind = c[t] == 0xFFFFu ? 3u : content_kind(c[t]);
+                uint32_t eqpos = 0xFFu;  // index inside the slot that aligns to the original base
+                bool first_x = false;
+                if (kind == 3u) eqpos = 0;
+                else if (kind == 1u) eqpos = 0;
+                else if (kind == 2u) eqpos = 1;
+                else if (len[t] >= 2 && b < 4 && content_base(c[t], 0) == b) eqpos = 0;
+                else if (len[t] >= 2 && b < 4 && content_base(c[t], len[t] - 1) == b) eqpos = len[t] - 1;
+                else first_x = true;
+                for (uint32_t u = 0; u < len[t]; u++) {
+                    const uint32_t j = o + u;
+                    uint32_t ch;
+                    if (kind == 3u) ch = code_ascii(b);
+                    else if (kind == 0u) ch = code_ascii(content_base(c[t], u));
+                    else if (kind == 1u) ch = u == 0 ? code_ascii(b) : code_ascii(content_base(c[t], 0));
+                    else ch = u == 0 ? code_ascii(content_base(c[t], 0)) : code_ascii(b);
+                    if (body) {
+                        uint32_t d = j - start_trim;
+                        if (d < scap) oseq[d] = (uint8_t)ch;
+                    }
+                    uint32_t op = u == eqpos ? OP_EQ : (first_x && u == 0) ? OP_X : OP_I;
+                    if (j < opcap) ops_put(keyb, j, op | ((u == 0 ? dc : 0u) << 2));
+                }
+                o += len[t];
+            }
+        }
+    }
+    const uint32_t Ttot = carry;
+    const uint32_t Lp = Ttot - start_trim - end_trim;
+    if (Ttot > opcap) status |= ST_OPS_OVERFLOW;
+    if (Lp > scap) status |= ST_SCRATCH_OVERFLOW;
+    if (tm.rank == 0) {
+        B.read_len[r] = Lp;
+        B.ident_num[r] = n - loss_c;
+        B.ident_den[r] = n + ins_c;
+        B.status[r] = status;
+    }
+    tm.sync();
+
+    // ---- 6. qscores for the read bases that survive trimming
+    if ((P.flags & RUN_QUAL) && !(status & (ST_OPS_OVERFLOW | ST_SCRATCH_OVERFLOW))) {
+        uint8_t* oq = B.scr_qual + sbase;
+        const int margin = (T.kq - 1) >> 1;
+        const uint32_t jb = start_trim, je = Ttot - end_trim;
+        for (uint32_t qd = (jb >> 2) + tm.rank; 4 * qd < je; qd += SIZE) {
+            const uint4 ur = philox4x32_10(qd, TAG_QUAL, olo, ohi, k0, k1);
+#pragma unroll
+            for (uint32_t t = 0; t < 4; t++) {
+                const uint32_t j = 4 * qd + t;
+                if (j < jb || j >= je) continue;
+                int start = (int)j - margin, end = (int)j + margin;
+                while (start < 0 || end >= (int)Ttot) {
+                    start++;
+                    end--;
+                }
+                const uint32_t row = qscore_row(T, keyb, start, end);
+                const QRow rw = T.q_rows[row];
+                const uint32_t u = word_of(ur, t);
+                const uint32_t col = rw.lg ? (u >> (32 - rw.lg)) : 0u;
+                const uint32_t e = T.q_alias[rw.off + col];
+                const uint32_t fr = (uint32_t)(u << rw.lg) >> 14;
+                const uint32_t q = fr < (e & 0x3FFFFu) ? ((e >> 18) & 127u) : (e >> 25);
+                oq[j - jb] = (uint8_t)(q + 33);
+            }
+        }
+    }
+    tm.sync();
+}
+
+template <int W, bool GWS>
+__global__ void __launch_bounds__(512, 1) simulate_kernel(const SimParams P) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    constexpr int TEAMS = 16 / W;
+    Team<W> tm;
+    tm.rank = threadIdx.x % (W * 32);
+    tm.id = threadIdx.x / (W * 32);
+    // k-mer change probabilities staged in shared memory for the whole CTA
+    const uint32_t nq = P.T.has_err_table ? (1u << (2 * P.T.k)) : 0u;
+    uint16_t* q16s = (uint16_t*)smem;
+    for (uint32_t i = threadIdx.x; i < nq; i += blockDim.x) q16s[i] = P.T.q16[i];
+    __syncthreads();
+    uint8_t* ws;
+    if (GWS)
+        ws = P.gws + (size_t)blockIdx.x * P.slab_bytes;
+    else
+        ws = smem + ((nq * 2 + 15) & ~15u) + (size_t)tm.id * P.slab_bytes;
+    uint32_t* ticket = (uint32_t*)(smem + ((nq * 2 + 15) & ~15u) + (GWS ? 0 : (size_t)TEAMS * P.slab_bytes)) + tm.id;
+    while (true) {
+        if (tm.rank == 0) *ticket = atomicAdd(P.counter, 1u);
+        tm.sync();
+        const uint32_t wi = *ticket;
+        tm.sync();
+        if (wi >= P.n_work) break;
+        simulate_read<W, GWS>(tm, P, P.work[wi], ws, q16s);
+    }
+}
+
+// -------------------------------------------------------------- formatting
+struct FmtParams {
+    uint32_t n_reads;
+    uint64_t ordinal_base;
+    uint32_t seed_lo, seed_hi;
+    const uint32_t* read_mol;
+    const uint32_t* mol_raw_len;
+    const uint32_t* mol_id_begin;
+    const uint8_t* id_pool;
+    const uint32_t* read_len;     // nullptr => perfect output (length = raw length)
+    const uint32_t* ident_num;
+    const uint32_t* ident_den;
+    const uint8_t* seq;           // scratch arena
+    const uint64_t* seq_off;
+    const uint8_t* qual;          // nullptr => 'K' * len
+    uint32_t fastq;               // 1 FASTQ, 0 FASTA
+    uint32_t* rec_len;
+    const uint64_t* rec_off;
+    uint8_t* out;
+};
+
+__device__ __forceinline__ uint32_t dec_digits(uint32_t v) {
+    uint32_t d = 1;
+    while (v >= 10) {
+        v /= 10;
+        d++;
+    }
+    return d;
+}
+
+// round-half-even of (num / den * 100.0) * 100 computed on the exact binary value of the double,
+// i.e. the digits Python's f"{x * 100.0:.2f}" prints (py/sequence.py:255)
+__device__ __forceinline__ uint32_t pct_hundredths(uint32_t num, uint32_t den) {
+    double y = __dmul_rn(__ddiv_rn((double)num, (double)den), 100.0);
+    uint64_t bits = (uint64_t)__double_as_longlong(y);
+    int ex = (int)((bits >> 52) & 0x7FF);
+    if (ex == 0) return 0;
+    uint64_t M = (bits & 0xFFFFFFFFFFFFFull) | (1ull << 52);
+    int sh = 1075 - ex;  // y = M * 2^-sh
+    if (sh <= 0) return 10000;  // cannot happen for y <= 100
+    uint64_t v = M * 100ull;   // < 2^60
+    if (sh >= 64) return 0;
+    uint64_t q = v >> sh, rem = v & ((1ull << sh) - 1), half = 1ull << (sh - 1);
+    if (rem > half || (rem == half && (q & 1))) q++;
+    return (uint32_t)q;
+}
+
+__device__ __forceinline__ uint32_t pct_len(uint32_t h) { return h >= 10000 ? 6u : h >= 1000 ? 5u : 4u; }
+
+__device__ __forceinline__ uint32_t record_len(const FmtParams& F, uint32_t r) {
+    const uint32_t mol = F.read_mol[r];
+    const uint32_t L = F.mol_raw_len[mol];
+    const uint32_t Lp = F.read_len ? F.read_len[r] : L;
+    const uint32_t h = F.read_len ? pct_hundredths(F.ident_num[r], F.ident_den[r]) : 10000u;
+    const uint32_t idl = F.mol_id_begin[mol + 1] - F.mol_id_begin[mol];
+    // "@" uuid " length=" Lp " error_free_length=" L " read_identity=" pct "% molecule_id=" id "\n" seq "\n"
+    uint32_t len = 1 + 36 + 8 + dec_digits(Lp) + 19 + dec_digits(L) + 15 + pct_len(h) + 14 + idl + 1 + Lp + 1;
+    if (F.fastq) len += 2 + Lp + 1;  // "+\n" qual "\n"
+    return len;
+}
+
+__global__ void reclen_kernel(const FmtParams F) {
+    uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < F.n_reads) F.rec_len[r] = record_len(F, r);
+}
+
+// exclusive scan of u32 -> u64, three small kernels (block sums, scan of sums, final)
+constexpr int SCAN_BLOCK = 1024;
+constexpr int SCAN_ITEMS = 4;
+__global__ void scan_block_sums(const uint32_t* in, uint32_t n, uint64_t* sums) {
+    __shared__ uint64_t sh[32];
+    uint64_t s = 0;
+    uint32_t base = blockIdx.x * SCAN_BLOCK * SCAN_ITEMS;
+    for (int t = 0; t < SCAN_ITEMS; t++) {
+        uint32_t i = base + t * SCAN_BLOCK + threadIdx.x;
+        if (i < n) s += in[i];
+    }
+    for (int d = 16; d; d >>= 1) s += __shfl_xor_sync(0xffffffffu, s, d);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        s = sh[threadIdx.x];
+        for (int d = 16; d; d >>= 1) s += __shfl_xor_sync(0xffffffffu, s, d);
+        if (threadIdx.x == 0) sums[blockIdx.x] = s;
+    }
+}
+__global__ void scan_sums(uint64_t* sums, uint32_t nb, uint64_t* total) {
+    // single block; serial over chunks of 1024
+    __shared__ uint64_t sh[32];
+    __shared__ uint64_t carry_s;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < nb; base += 1024) {
+        uint32_t i = base + threadIdx.x;
+        uint64_t v = i < nb ? sums[i] : 0, inc = v;
+        const int lane = threadIdx.x & 31;
+        for (int d = 1; d < 32; d <<= 1) {
+            uint64_t o = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += o;
+        }
+        if (lane == 31) sh[threadIdx.x >> 5] = inc;
+        __syncthreads();
+        uint64_t wb = 0;
+        for (int w = 0; w < (int)(threadIdx.x >> 5); w++) wb += sh[w];
+        uint64_t c = carry_s;
+        if (i < nb) sums[i] = c + wb + inc - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry_s = c + wb + inc;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *total = carry_s;
+}
+__global__ void scan_final(const uint32_t* in, uint32_t n, const uint64_t* sums, uint64_t* out) {
+    __shared__ uint64_t sh[32];
+    __shared__ uint64_t carry_s;
+    if (threadIdx.x == 0) carry_s = sums[blockIdx.x];
+    __syncthreads();
+    uint32_t base = blockIdx.x * SCAN_BLOCK * SCAN_ITEMS;
+    for (int t = 0; t < SCAN_ITEMS; t++) {
+        uint32_t i = base + t * SCAN_BLOCK + threadIdx.x;
+        uint64_t v = i < n ? in[i] : 0, inc = v;
+        const int lane = threadIdx.x & 31;
+        for (int d = 1; d < 32; d <<= 1) {
+            uint64_t o = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += o;
+        }
+        if (lane == 31) sh[threadIdx.x >> 5] = inc;
+        __syncthreads();
+        uint64_t wb = 0;
+        for (int w = 0; w < (int)(threadIdx.x >> 5); w++) wb += sh[w];
+        uint64_t c = carry_s;
+        if (i < n) out[i] = c + wb + inc - v;
+        __syncthreads();
+        if (threadIdx.x == SCAN_BLOCK - 1) carry_s = c + wb + inc;
+        __syncthreads();
+    }
+}
+
+__device__ __forceinline__ char hexdig(uint32_t v) { return (char)(v < 10 ? '0' + v : 'a' + (v - 10)); }
+
+// one warp per read
+__global__ void __launch_bounds__(256) format_kernel(const FmtParams F) {
+    __shared__ uint8_t hdr_s[8][160];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint8_t* hdr = hdr_s[warp];
+    for (uint32_t r = blockIdx.x * 8 + warp; r < F.n_reads; r += gridDim.x * 8) {
+        const uint32_t mol = F.read_mol[r];
+        const uint32_t L = F.mol_raw_len[mol];
+        const uint32_t Lp = F.read_len ? F.read_len[r] : L;
+        const uint32_t id0 = F.mol_id_begin[mol], idl = F.mol_id_begin[mol + 1] - id0;
+        uint32_t hl = 0;
+        if (lane == 0) {
+            const uint64_t ordinal = F.ordinal_base + r;
+            uint4 u = philox4x32_10(1, TAG_READ, (uint32_t)ordinal, (uint32_t)(ordinal >> 32), F.seed_lo, F.seed_hi);
+            uint32_t w[4] = {u.x, u.y, u.z, u.w};
+            uint32_t p = 0;
+            hdr[p++] = F.fastq ? '@' : '>';
+            for (int d = 0; d < 32; d++) {
+                if (d == 8 || d == 12 || d == 16 || d == 20) hdr[p++] = '-';
+                hdr[p++] = (uint8_t)hexdig((w[d >> 3] >> (28 - 4 * (d & 7))) & 15u);
+            }
+            auto puts_ = [&](const char* s) {
+                while (*s) hdr[p++] = (uint8_t)*s++;
+            };
+            auto putu = [&](uint32_t v) {
+                uint32_t nd = dec_digits(v);
+                for (uint32_t d = 0; d < nd; d++) {
+                    hdr[p + nd - 1 - d] = (uint8_t)('0' + v % 10);
+                    v /= 10;
+                }
+                p += nd;
+            };
+            puts_(" length=");
+            putu(Lp);
+            puts_(" error_free_length=");
+            putu(L);
+            puts_(" read_identity=");
+            uint32_t h = F.read_len ? pct_hundredths(F.ident_num[r], F.ident_den[r]) : 10000u;
+            putu(h / 100);
+            hdr[p++] = '.';
+            hdr[p++] = (uint8_t)('0' + (h / 10) % 10);
+            hdr[p++] = (uint8_t)('0' + h % 10);
+            puts_("% molecule_id=");
+            hl = p;
+        }
+        hl = __shfl_sync(0xffffffffu, hl, 0);
+        __syncwarp();
+        uint8_t* o = F.out + F.rec_off[r];
+        for (uint32_t x = lane; x < hl; x += 32) o[x] = hdr[x];
+        o += hl;
+        for (uint32_t x = lane; x < idl; x += 32) o[x] = F.id_pool[id0 + x];
+        o += idl;
+        if (lane == 0) o[0] = '\n';
+        o += 1;
+        const uint8_t* s = F.seq + F.seq_off[r];
+        for (uint32_t x = lane; x < Lp; x += 32) o[x] = s[x];
+        o += Lp;
+        if (lane == 0) o[0] = '\n';
+        o += 1;
+        if (F.fastq) {
+            if (lane == 0) {
+                o[0] = '+';
+                o[1] = '\n';
+            }
+            o += 2;
+            if (F.qual) {
+                const uint8_t* q = F.qual + F.seq_off[r];
+                for (uint32_t x = lane; x < Lp; x += 32) o[x] = q[x];
+            } else {
+                for (uint32_t x = lane; x < Lp; x += 32) o[x] = 'K';
+            }
+            o += Lp;
+            if (lane == 0) o[0] = '\n';
+        }
+        __syncwarp();
+    }
+}
+
+}  // namespace tk
