@@ -1,0 +1,201 @@
+"""GPU parity: the CUDA path, called through the C ABI, against the oracles on the same inputs.
+
+* perfect output (interval fetch, mods, reverse-complement, literal segments, ordering, record text)
+  must equal the Python restatement of the reference byte for byte;
+* badread output must equal the CPU twin of the PB1 model bit for bit (oracle/twin.c).
+"""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import seq_oracle as so
+
+pytestmark = pytest.mark.gpu
+
+HAVE_MODELS = os.path.exists(os.path.join(os.environ["TKSM_MODELS"], "badread", "nanopore2020.error.gz"))
+
+
+def make_fasta(rng, contigs, n_rate=0.01, lower=True):
+    out = []
+    for name, length in contigs:
+        seq = rng.choice(np.frombuffer(b"ACGT", np.uint8), size=length)
+        # N runs, a few IUPAC codes, soft-masked stretches
+        pos = 0
+        while pos < length:
+            if rng.random() < n_rate:
+                run = int(rng.integers(1, 400))
+                seq[pos:pos + run] = ord("N")
+                pos += run
+            pos += int(rng.integers(50, 3000))
+        for p in rng.integers(0, length, size=5):
+            seq[p] = rng.choice(np.frombuffer(b"RYKMSW", np.uint8))
+        s = seq.tobytes().decode()
+        if lower:
+            a = int(rng.integers(0, max(1, length - 500)))
+            s = s[:a] + s[a:a + 400].lower() + s[a + 400:]
+        out.append(f">{name} synthetic contig\n" + "\n".join(s[i:i + 60] for i in range(0, len(s), 60)))
+    return "\n".join(out) + "\n"
+
+
+def first_diff(got, want, fastq=True):
+    if got == want:
+        return None
+    try:
+        g, w = so.parse_records(got, fastq), so.parse_records(want, fastq)
+    except AssertionError as e:
+        return f"unparseable output ({e}); sizes {len(got)} vs {len(want)}"
+    if len(g) != len(w):
+        return f"record count {len(g)} vs {len(w)}"
+    for i, (a, b) in enumerate(zip(g, w)):
+        if a != b:
+            msg = [f"record {i}:"]
+            if a[0] != b[0]:
+                msg.append(f" header\n   got  {a[0]}\n   want {b[0]}")
+            if a[1] != b[1]:
+                j = next((x for x in range(min(len(a[1]), len(b[1]))) if a[1][x] != b[1][x]), min(len(a[1]), len(b[1])))
+                msg.append(f" seq differs at {j} (len {len(a[1])} vs {len(b[1])}): "
+                           f"got {a[1][max(0, j - 10):j + 10]} want {b[1][max(0, j - 10):j + 10]}")
+            if fastq and a[2] != b[2]:
+                j = next((x for x in range(min(len(a[2]), len(b[2]))) if a[2][x] != b[2][x]), min(len(a[2]), len(b[2])))
+                nd = sum(1 for x, y in zip(a[2], b[2]) if x != y)
+                msg.append(f" qual differs at {j} ({nd} positions; len {len(a[2])} vs {len(b[2])}): "
+                           f"got {a[2][max(0, j - 10):j + 10]} want {b[2][max(0, j - 10):j + 10]}")
+            return "".join(msg)
+    return "records equal but bytes differ"
+
+
+@pytest.fixture(scope="module")
+def world(built):
+    from tksm_b200.sequence import Sequencer
+    rng = np.random.default_rng(2024)
+    fasta = make_fasta(rng, [("chr1", 300000), ("chr2", 120000), ("scaffold_3", 30000)])
+    return {"fasta": fasta, "refs": so.load_fasta(fasta), "Sequencer": Sequencer}
+
+
+def oracle_inputs(world, mdf):
+    mols = so.parse_mdf(mdf)
+    seqs = [so.molecule_sequence(world["refs"], iv) for _, iv in mols]
+    return seqs, [m for m, _ in mols]
+
+
+def handmade_mdf():
+    """Edge cases of the deterministic stage (SURVEY.md §4 vectors and §8a footnotes)."""
+    return (
+        "+m1\t1\tinfo=x;\n"
+        "chr1\t10\t14\t+\t2C,3T\n"
+        "chr1\t16\t19\t+\t1G\n"
+        "+lit\t1\t\n"
+        "TT\t0\t2\t+\t\n"
+        "chr1\t0\t4\t+\t\n"
+        "+minus\t2\tdepth2;\n"
+        "chr1\t100\t160\t-\t\n"
+        "+clamp\t1\t\n"
+        "chr2\t119990\t999999\t+\t\n"
+        "+lower_lit\t1\t\n"
+        "acgtn\t0\t5\t-\t0r\n"
+        "+nomods4\t1\t\n"
+        "chr2\t5\t45\t-\n"
+        "+multi\t3\tCB=ACGT;tid=T1;\n"
+        "AATGTACTTCGTTCAGTTACGTATTGCT\t0\t28\t+\t\n"
+        "chr2\t5000\t5400\t-\t5A,17c,399T\n"
+        "chr2\t3000\t3200\t-\t\n"
+        "AAAAAAAAAAAAAAAAAAA\t0\t19\t+\t\n"
+        "+zero_depth\t0\t\n"
+        "chr1\t0\t10\t+\t\n"
+        "+single\t1\t\n"
+        "chr1\t77\t78\t+\t\n"
+        "+empty_slice\t1\t\n"
+        "chr1\t50\t50\t+\t\n"
+        "chr1\t200\t260\t+\t\n"
+        "+negative\t1\t\n"
+        "chr1\t-20\t-5\t+\t-1G\n"
+    )
+
+
+def test_perfect_handmade_matches_python_oracle(world):
+    s = world["Sequencer"](seed=5)
+    s.add_reference_text(world["fasta"])
+    s.load_models("random", "random")
+    from tksm_b200.sequence import PERFECT
+    mdf = handmade_mdf()
+    seqs, ids = oracle_inputs(world, mdf)
+    for fastq in (False, True):
+        got = so.parse_records(s.simulate(mdf, PERFECT, fastq=fastq), fastq)
+        assert len(got) == len(seqs)
+        for (hdr, seq, qual), want, mid in zip(got, seqs, ids):
+            uuid = hdr.split(" ")[0][1:]
+            assert len(uuid) == 36
+            assert (hdr + "\n").encode() + seq + b"\n" + (b"+\n" + qual + b"\n" if fastq else b"") == \
+                so.perfect_record(uuid, mid, want, fastq)
+
+
+@pytest.mark.parametrize("shape,n", [(0, 400), (1, 1500), (2, 60)])
+def test_perfect_synthetic_matches_python_oracle(world, shape, n):
+    from tksm_b200.sequence import PERFECT
+    s = world["Sequencer"](seed=9)
+    s.add_reference_text(world["fasta"])
+    s.load_models("random", "random")
+    mdf = s.synth_mdf(shape, n, seed=shape + 1, min_len=200, max_len=60000)
+    seqs, ids = oracle_inputs(world, mdf)
+    got = s.simulate(mdf, PERFECT, fastq=False)
+    want = so.twin_simulate(s.tables(), seqs, ids, badread=False, fastq=False)
+    assert first_diff(got, want, False) is None
+
+
+CASES = [
+    # error model, qscore model, identity, skip_qual, shape, n
+    ("random", "random", (84.0, 99.0, 5.5), False, 1, 300),
+    ("random", "ideal", (90.0, 98.0, 3.0), False, 1, 200),
+]
+if HAVE_MODELS:
+    CASES += [
+        ("nanopore2020", "nanopore2020", (84.0, 99.0, 5.5), False, 1, 1200),
+        ("nanopore2020", "nanopore2020", (84.0, 99.0, 5.5), True, 0, 300),
+        ("nanopore2018", "nanopore2018", (87.0, 97.0, 4.0), False, 1, 300),
+        ("pacbio2016", "pacbio2016", (99.0, 99.9, 0.5), False, 1, 300),
+        ("nanopore2020", "nanopore2020", (95.0, 95.0, 0.0), False, 0, 200),
+        ("nanopore2020", "nanopore2020", (60.0, 80.0, 8.0), False, 1, 200),
+        ("nanopore2020", "nanopore2020", (84.0, 99.0, 5.5), False, 2, 80),
+    ]
+
+
+@pytest.mark.parametrize("em,qm,ident,skip,shape,n", CASES)
+def test_badread_matches_cpu_twin(world, em, qm, ident, skip, shape, n):
+    from tksm_b200.sequence import BADREAD
+    s = world["Sequencer"](identity=ident, seed=1234, skip_qual_compute=skip)
+    s.add_reference_text(world["fasta"])
+    s.load_models(em, qm)
+    mdf = s.synth_mdf(shape, n, seed=17 + shape, min_len=300, max_len=70000)
+    if shape == 1:
+        mdf += handmade_mdf().encode()
+    seqs, ids = oracle_inputs(world, mdf)
+    for fastq in (True, False):
+        got = s.simulate(mdf, BADREAD, fastq=fastq, ordinal_base=1000)
+        want = so.twin_simulate(s.tables(), seqs, ids, ordinal_base=1000, badread=True, fastq=fastq)
+        d = first_diff(got, want, fastq)
+        assert d is None, d
+    assert s.last_stats["status_or"] & 3 == 0
+
+
+def test_device_batch_rerun_is_deterministic_and_ordinal_keyed(world):
+    from tksm_b200.sequence import BADREAD, FASTQ
+    s = world["Sequencer"](seed=77)
+    s.add_reference_text(world["fasta"])
+    s.load_models("random", "random")
+    mdf = s.synth_mdf(1, 500, seed=5)
+    b = s.batch(mdf)
+    st1 = b.run(BADREAD, FASTQ)
+    out1 = b.fetch(BADREAD)
+    st2 = b.run(BADREAD, FASTQ)
+    out2 = b.fetch(BADREAD)
+    assert out1 == out2 and st1["out_bytes"] == st2["out_bytes"]
+    # splitting the stream in two batches gives the same bytes: results depend on the read
+    # ordinal only, not on batch or GPU boundaries
+    recs = mdf.split(b"\n+M")          # record boundaries (a strand field is never at line start)
+    half = len(recs) // 2
+    a = b"\n+M".join(recs[:half]) + b"\n"
+    c = b"+M" + b"\n+M".join(recs[half:])
+    na = len(so.parse_mdf(a))
+    out_split = s.simulate(a, BADREAD, True, 0) + s.simulate(c, BADREAD, True, na)
+    assert out_split == out1
