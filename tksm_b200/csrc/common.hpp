@@ -80,6 +80,9 @@ struct DevTables {
     uint32_t q_hash_shift;        // 64 - log2(size)
     uint32_t q_hash_mask;
     const QRow* q_rows;
+    // fast path for 9-wide windows (kq == 9), entries = alias offset << 3 | log2 columns; 0 pointers when kq != 9
+    const uint32_t* q_t9;         // 3^9: D-free windows, base-3 code of the ops (first op lowest)
+    const uint32_t* q_t9d1;       // 3^9 * 24: one D run of 1..3 at gap g: code + 19683 * (3 g + dc - 1)
     const uint32_t* q_alias;      // thr18 | qa << 18 | qb << 25
     uint32_t seed_lo, seed_hi;
 };

@@ -128,7 +128,7 @@ struct tksm_seq {
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     int num_sms = 148;
     DBuf d_genome, d_exc_start, d_exc_len, d_exc_chr;
-    DBuf d_q16, d_alias, d_alts, d_ident, d_delta, d_qdirect, d_qhash, d_qrows, d_qalias;
+    DBuf d_q16, d_alias, d_alts, d_ident, d_delta, d_qdirect, d_qhash, d_qrows, d_qalias, d_t9, d_t9d1;
     DevTables dt{};
     HBuf stage, stage_out;
     uint32_t ncap[N_CLASSES] = {0, 0, 0, 0};
@@ -138,7 +138,7 @@ struct tksm_seq {
 
     ~tksm_seq() {
         for (DBuf* d : {&d_genome, &d_exc_start, &d_exc_len, &d_exc_chr, &d_q16, &d_alias, &d_alts, &d_ident, &d_delta,
-                        &d_qdirect, &d_qhash, &d_qrows, &d_qalias})
+                        &d_qdirect, &d_qhash, &d_qrows, &d_qalias, &d_t9, &d_t9d1})
             d->release();
         stage.release();
         stage_out.release();
@@ -182,17 +182,17 @@ void commit_reference(tksm_seq* h) {
 void compute_classes(tksm_seq* h) {
     const size_t nq = h->em.has_table ? ((size_t)1 << (2 * h->em.k)) : 0;
     const size_t q16_bytes = (nq * 2 + 15) & ~size_t(15);
-    const size_t pool = SMEM_TOTAL - q16_bytes - 64;
+    const size_t pool = SMEM_TOTAL - q16_bytes - 128;
     for (int c = 0; c < 3; c++) {
         const int W = CLASS_W[c], teams = 16 / W;
         const size_t hist = 256 * (W >= 8 ? 8 : 4);
         size_t slab = (pool / teams) & ~size_t(15);
-        size_t ncap = ((slab - hist - 128 - 16) / 5) & ~size_t(3);
+        size_t ncap = ((slab - hist - 128 - (size_t)W * 512 - 16) / 5) & ~size_t(3);
         h->slab[c] = (uint32_t)slab;
         h->ncap[c] = (uint32_t)ncap;
-        h->smem_bytes[c] = q16_bytes + slab * teams + 64;
+        h->smem_bytes[c] = q16_bytes + slab * teams + 128;
     }
-    h->smem_bytes[3] = q16_bytes + 64;
+    h->smem_bytes[3] = q16_bytes + 128;
 }
 
 void upload_models(tksm_seq* h) {
@@ -207,6 +207,8 @@ void upload_models(tksm_seq* h) {
     upload_vec(h->d_qhash, h->qm.hash, h->stream);
     upload_vec(h->d_qrows, h->qm.rows, h->stream);
     upload_vec(h->d_qalias, h->qm.alias, h->stream);
+    upload_vec(h->d_t9, h->qm.t9, h->stream);
+    upload_vec(h->d_t9d1, h->qm.t9d1, h->stream);
     CK(cudaStreamSynchronize(h->stream));
     DevTables& T = h->dt;
     T.k = h->em.k;
@@ -228,6 +230,8 @@ void upload_models(tksm_seq* h) {
     T.q_hash_mask = h->qm.hash_mask;
     T.q_rows = h->d_qrows.as<QRow>();
     T.q_alias = h->d_qalias.as<uint32_t>();
+    T.q_t9 = h->qm.t9.empty() ? nullptr : h->d_t9.as<uint32_t>();
+    T.q_t9d1 = h->qm.t9d1.empty() ? nullptr : h->d_t9d1.as<uint32_t>();
     T.seed_lo = (uint32_t)h->cfg.seed;
     T.seed_hi = (uint32_t)(h->cfg.seed >> 32);
 }
@@ -408,7 +412,7 @@ void batch_run(tksm_seq* h, tksm_seq_batch* b, int which, int format, tksm_seq_s
         }
     if (b->max_n_gws) {
         size_t ncap = align_up(b->max_n_gws + 16, 16);
-        size_t slab = align_up(256 * 8 + 128 + 5 * ncap + 16, 16);
+        size_t slab = align_up(256 * 8 + 128 + 16 * 512 + 5 * ncap + 16, 16);
         h->ncap[3] = (uint32_t)ncap;
         h->slab[3] = (uint32_t)slab;
         b->gws.ensure(slab * h->num_sms);

@@ -174,7 +174,8 @@ struct SimParams {
     uint8_t* gws;           // global workspaces (one per CTA) when GWS
 };
 
-// workspace layout (team private): hist[256] (HistT) | misc[32] u32 | key[ncap] u32 | frag[ncap + 16] u8
+// workspace layout (team private):
+//   hist[256] (HistT) | misc[32] u32 | per-warp queues W x (64 + 64) u32 | key[ncap] u32 | frag[ncap + 16] u8
 template <typename HistT>
 __device__ __forceinline__ uint32_t ws_misc_off() { return 256 * (uint32_t)sizeof(HistT); }
 
@@ -277,10 +278,48 @@ __device__ __forceinline__ uint32_t qscore_row(const DevTables& T, const uint8_t
     }
 }
 
+
+// ------------------------------------------------------- warp compaction
+// Rare, divergent work (a trial at a start position; a qscore window that misses the direct
+// tables) is not done where it is found: the lanes that found some push it to a 64-entry ring in
+// shared memory and the warp drains 32 entries at a time with every lane busy.
+struct WarpQueue {
+    uint32_t* a;
+    uint32_t* b;
+    uint32_t head, tail;  // warp-uniform
+    __device__ __forceinline__ void push(bool pred, uint32_t va, uint32_t vb) {
+        const uint32_t m = __ballot_sync(0xffffffffu, pred);
+        if (pred) {
+            const uint32_t slot = (tail + __popc(m & ((1u << (threadIdx.x & 31)) - 1))) & 63u;
+            a[slot] = va;
+            b[slot] = vb;
+        }
+        tail += __popc(m);
+        __syncwarp();
+    }
+    // number of entries the next drain handles: 32 when at least that many are queued, or the
+    // remainder when `flush`
+    __device__ __forceinline__ uint32_t ready(bool flush) const {
+        const uint32_t cnt = tail - head;
+        return cnt >= 32 ? 32u : (flush ? cnt : 0u);
+    }
+    __device__ __forceinline__ bool take(uint32_t cnt, uint32_t& va, uint32_t& vb) {
+        const uint32_t lane = threadIdx.x & 31;
+        const bool mine = lane < cnt;
+        if (mine) {
+            va = a[(head + lane) & 63u];
+            vb = b[(head + lane) & 63u];
+        }
+        __syncwarp();
+        head += cnt;
+        return mine;
+    }
+};
+
 // ------------------------------------------------------------ simulate one
 template <int W, bool GWS>
 __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams& P, uint32_t r, uint8_t* ws,
-                                              const uint16_t* q16s) {
+                                              const uint16_t* q16s, const uint8_t* lut3) {
     using HistT = typename std::conditional<(GWS || W >= 8), uint64_t, uint32_t>::type;
     constexpr int SIZE = Team<W>::SIZE;
     const DevTables& T = P.T;
@@ -289,7 +328,9 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
     HistT* hist = (HistT*)ws;
     uint32_t* misc = (uint32_t*)(ws + ws_misc_off<HistT>());
     uint32_t* wsum = misc + 8;
-    uint32_t* key = misc + 32;
+    uint32_t* wq_a = misc + 32 + (tm.rank >> 5) * 128;  // this warp's compaction queue (two lanes of payload)
+    uint32_t* wq_b = wq_a + 64;
+    uint32_t* key = misc + 32 + W * 128;
     uint8_t* keyb = (uint8_t*)key;
     uint8_t* frag = (uint8_t*)(key + P.ncap);
     const uint32_t* fragw = (const uint32_t*)frag;
@@ -414,79 +455,112 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
         for (uint32_t epoch = 0;; epoch++) {
             for (uint32_t b = tm.rank; b < 256; b += SIZE) hist[b] = 0;
             tm.sync();
-            for (uint32_t qd = tm.rank; qd < nquad; qd += SIZE) {
-                const uint32_t w0 = fragw[qd], w1 = fragw[qd + 1], w2 = fragw[qd + 2];
-                const uint4 ur = philox4x32_10(qd, TAG_ARRIVE | (epoch << 8), olo, ohi, k0, k1);
-#pragma unroll
-                for (uint32_t t = 0; t < 4; t++) {
-                    const uint32_t i = 4 * qd + t;
-                    if (i >= npos) break;
-                    const uint32_t x0 = __funnelshift_r(w0, w1, 8 * t), x1 = __funnelshift_r(w1, w2, 8 * t);
-                    const bool valid = T.has_err_table && (((x0 & vm0) | (x1 & vm1)) == 0);
-                    uint32_t code = 0;
-                    float q = 1.0f;
+            // --- arrivals: Poisson(q * delta) trials per start position; found ones are queued
+            WarpQueue tq_{wq_a, wq_b, 0, 0};
+            auto run_trials = [&](uint32_t cnt) {
+                uint32_t ent = 0, dummy = 0;
+                if (!tq_.take(cnt, ent, dummy)) return;
+                const uint32_t i = ent & 0x0FFFFFFFu;
+                const int N = (int)(ent >> 28) + 1;
+                const uint32_t qw = i >> 2, sh = 8 * (i & 3u);
+                const uint32_t x0 = __funnelshift_r(fragw[qw], fragw[qw + 1], sh);
+                const uint32_t x1 = __funnelshift_r(fragw[qw + 1], fragw[qw + 2], sh);
+                const bool valid = T.has_err_table && (((x0 & vm0) | (x1 & vm1)) == 0);
+                uint32_t code = 0;
+                if (valid) {
+                    uint32_t c0 = (x0 | (x0 >> 6)) & 0x000F000Fu;
+                    c0 = (c0 | (c0 >> 12)) & 0xFFu;
+                    uint32_t c1 = (x1 | (x1 >> 6)) & 0x000F000Fu;
+                    c1 = (c1 | (c1 >> 12)) & 0xFFu;
+                    code = (c0 | (c1 << 8)) & codemask;
+                }
+                for (int tr = 0; tr < N; tr++) {
+                    const uint4 wr = philox4x32_10(i, TAG_TRIAL | (epoch << 8) | ((uint32_t)tr << 20), olo, ohi, k0, k1);
+                    uint32_t tm16 = wr.x >> 16;
+                    tm16 += tm16 == 0;
+                    uint32_t outcome = ERR_OUTCOME_RANDOM;
                     if (valid) {
-                        uint32_t c0 = (x0 | (x0 >> 6)) & 0x000F000Fu;
-                        c0 = (c0 | (c0 >> 12)) & 0xFFu;
-                        uint32_t c1 = (x1 | (x1 >> 6)) & 0x000F000Fu;
-                        c1 = (c1 | (c1 >> 12)) & 0xFFu;
-                        code = (c0 | (c1 << 8)) & codemask;
-                        q = __fmul_rn((float)q16s[code], 1.52587890625e-05f);  // 2^-16
+                        uint32_t e = T.err_alias[code * ERR_ALIAS_COLS + (wr.y >> 27)];
+                        uint32_t fr = (wr.y >> 5) & 0x3FFFFFu;
+                        outcome = fr < (e & 0x3FFFFFu) ? ((e >> 22) & 31u) : (e >> 27);
                     }
-                    const float x = __fmul_rn(q, delta);
-                    const float U = __fmul_rn((float)(word_of(ur, t) >> 8), 5.9604644775390625e-08f);  // 2^-24
-                    float term = expneg(x), cum = term;
-                    if (U < cum) continue;
-                    int N = 1;
-                    for (; N < MAX_TRIALS_PER_EPOCH; N++) {
-                        term = __fmul_rn(__fmul_rn(term, x), __frcp_rn((float)N));
-                        cum = __fadd_rn(cum, term);
-                        if (U < cum) break;
-                    }
-                    for (int tr = 0; tr < N; tr++) {
-                        const uint4 wr = philox4x32_10(i, TAG_TRIAL | (epoch << 8) | ((uint32_t)tr << 20), olo, ohi, k0, k1);
-                        uint32_t tm16 = wr.x >> 16;
-                        tm16 += tm16 == 0;
-                        uint32_t outcome = ERR_OUTCOME_RANDOM;
-                        if (valid) {
-                            uint32_t e = T.err_alias[code * ERR_ALIAS_COLS + (wr.y >> 27)];
-                            uint32_t fr = (wr.y >> 5) & 0x3FFFFFu;
-                            outcome = fr < (e & 0x3FFFFFu) ? ((e >> 22) & 31u) : (e >> 27);
-                        }
-                        if (outcome != ERR_OUTCOME_RANDOM) {
-                            const uint64_t aw = T.err_alts[code * ERR_ALT_STRIDE + outcome];
-                            uint32_t boff = 28;
-                            for (uint32_t j = 0; j < k; j++) {
-                                uint32_t len = (uint32_t)(aw >> (3 * j)) & 7u;
-                                if ((aw >> (21 + j)) & 1ull) {
-                                    uint32_t bases = (uint32_t)(aw >> boff) & ((1u << (2 * len)) - 1);
-                                    uint32_t cand = (tm16 << 16) | (len << CONTENT_LEN_SHIFT) | (bases << 1);
-                                    atomicMin(&key[i + j], cand);
-                                }
-                                boff += 2 * len;
+                    if (outcome != ERR_OUTCOME_RANDOM) {
+                        const uint64_t aw = T.err_alts[code * ERR_ALT_STRIDE + outcome];
+                        uint32_t boff = 28;
+                        for (uint32_t j = 0; j < k; j++) {
+                            uint32_t len = (uint32_t)(aw >> (3 * j)) & 7u;
+                            if ((aw >> (21 + j)) & 1ull) {
+                                uint32_t bases = (uint32_t)(aw >> boff) & ((1u << (2 * len)) - 1);
+                                uint32_t cand = (tm16 << 16) | (len << CONTENT_LEN_SHIFT) | (bases << 1);
+                                atomicMin(&key[i + j], cand);
                             }
+                            boff += 2 * len;
+                        }
+                    } else {
+                        // py/tksm_badread.py:199-213
+                        uint32_t type = __umulhi(wr.z, 3u);
+                        uint32_t pos = __umulhi(wr.w, k);
+                        uint32_t r2 = wr.z & 0xFFFFu;
+                        uint32_t ob = (pos < 4 ? (x0 >> (8 * pos)) : (x1 >> (8 * (pos - 4)))) & 0xFFu;
+                        uint32_t content;
+                        if (type == 0) {
+                            uint32_t nb = ob < 4 ? ((ob + 1 + ((r2 * 3u) >> 16)) & 3u) : (r2 & 3u);
+                            content = (1u << CONTENT_LEN_SHIFT) | (nb << 1);
+                        } else if (type == 1) {
+                            uint32_t nb = r2 & 3u;
+                            uint32_t before = (r2 >> 2) & 1u;
+                            content = (2u << CONTENT_LEN_SHIFT) | ((before ? 2u : 1u) << CONTENT_KIND_SHIFT) | (nb << 1);
                         } else {
-                            // py/tksm_badread.py:199-213
-                            uint32_t type = __umulhi(wr.z, 3u);
-                            uint32_t pos = __umulhi(wr.w, k);
-                            uint32_t r2 = wr.z & 0xFFFFu;
-                            uint32_t ob = (pos < 4 ? (x0 >> (8 * pos)) : (x1 >> (8 * (pos - 4)))) & 0xFFu;
-                            uint32_t content;
-                            if (type == 0) {
-                                uint32_t nb = ob < 4 ? ((ob + 1 + ((r2 * 3u) >> 16)) & 3u) : (r2 & 3u);
-                                content = (1u << CONTENT_LEN_SHIFT) | (nb << 1);
-                            } else if (type == 1) {
-                                uint32_t nb = r2 & 3u;
-                                uint32_t before = (r2 >> 2) & 1u;
-                                content = (2u << CONTENT_LEN_SHIFT) | ((before ? 2u : 1u) << CONTENT_KIND_SHIFT) | (nb << 1);
-                            } else {
-                                content = 0;
-                            }
-                            atomicMin(&key[i + pos], (tm16 << 16) | content);
+                            content = 0;
                         }
+                        atomicMin(&key[i + pos], (tm16 << 16) | content);
                     }
                 }
+            };
+            const uint32_t nquad_r = (nquad + 31u) & ~31u;  // whole warps iterate together
+            for (uint32_t qd = tm.rank; qd < nquad_r; qd += SIZE) {
+                const bool live = qd < nquad;
+                uint32_t w0 = 0, w1 = 0, w2 = 0;
+                uint4 ur = make_uint4(0, 0, 0, 0);
+                if (live) {
+                    w0 = fragw[qd];
+                    w1 = fragw[qd + 1];
+                    w2 = fragw[qd + 2];
+                    ur = philox4x32_10(qd, TAG_ARRIVE | (epoch << 8), olo, ohi, k0, k1);
+                }
+#pragma unroll 1
+                for (uint32_t t = 0; t < 4; t++) {
+                    const uint32_t i = 4 * qd + t;
+                    int N = 0;
+                    if (live && i < npos) {
+                        const uint32_t x0 = __funnelshift_r(w0, w1, 8 * t), x1 = __funnelshift_r(w1, w2, 8 * t);
+                        const bool valid = T.has_err_table && (((x0 & vm0) | (x1 & vm1)) == 0);
+                        float q = 1.0f;
+                        if (valid) {
+                            uint32_t c0 = (x0 | (x0 >> 6)) & 0x000F000Fu;
+                            c0 = (c0 | (c0 >> 12)) & 0xFFu;
+                            uint32_t c1 = (x1 | (x1 >> 6)) & 0x000F000Fu;
+                            c1 = (c1 | (c1 >> 12)) & 0xFFu;
+                            const uint32_t code = (c0 | (c1 << 8)) & codemask;
+                            q = __fmul_rn((float)q16s[code], 1.52587890625e-05f);  // 2^-16
+                        }
+                        const float x = __fmul_rn(q, delta);
+                        const float U = __fmul_rn((float)(word_of(ur, t) >> 8), 5.9604644775390625e-08f);  // 2^-24
+                        float term = expneg(x), cum = term;
+                        if (!(U < cum)) {
+                            for (N = 1; N < MAX_TRIALS_PER_EPOCH; N++) {
+                                term = __fmul_rn(__fmul_rn(term, x), __frcp_rn((float)N));
+                                cum = __fadd_rn(cum, term);
+                                if (U < cum) break;
+                            }
+                        }
+                    }
+                    tq_.push(N > 0, i | ((uint32_t)(N - 1) << 28), 0u);
+                    const uint32_t cnt = tq_.ready(false);
+                    if (cnt) run_trials(cnt);
+                }
             }
+            for (uint32_t cnt; (cnt = tq_.ready(true)) != 0;) run_trials(cnt);
             tm.sync();
             // histogram of candidate change times, high byte
             for (uint32_t p = tm.rank; p < n; p += SIZE) {
@@ -652,27 +726,81 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
         uint8_t* oq = B.scr_qual + sbase;
         const int margin = (T.kq - 1) >> 1;
         const uint32_t jb = start_trim, je = Ttot - end_trim;
-        for (uint32_t qd = (jb >> 2) + tm.rank; 4 * qd < je; qd += SIZE) {
-            const uint4 ur = philox4x32_10(qd, TAG_QUAL, olo, ohi, k0, k1);
-#pragma unroll
+        WarpQueue sq{wq_a, wq_b, 0, 0};
+        auto sample = [&](uint32_t off, uint32_t lg, uint32_t u, uint32_t j) {
+            const uint32_t col = lg ? (u >> (32 - lg)) : 0u;
+            const uint32_t e = T.q_alias[off + col];
+            const uint32_t fr = (uint32_t)(u << lg) >> 14;
+            const uint32_t q = fr < (e & 0x3FFFFu) ? ((e >> 18) & 127u) : (e >> 25);
+            oq[j - jb] = (uint8_t)(q + 33);
+        };
+        // windows the direct tables do not cover: generic trim-and-retry lookup, 32 at a time
+        auto run_slow = [&](uint32_t cnt) {
+            uint32_t j = 0, u = 0;
+            if (!sq.take(cnt, j, u)) return;
+            int start = (int)j - margin, end = (int)j + margin;
+            while (start < 0 || end >= (int)Ttot) {
+                start++;
+                end--;
+            }
+            const QRow rw = T.q_rows[qscore_row(T, keyb, start, end)];
+            sample(rw.off, rw.lg, u, j);
+        };
+        const uint32_t qd0 = jb >> 2, qd1 = (je + 3) >> 2;  // quads [qd0, qd1)
+        const uint32_t nq_r = (qd1 - qd0 + 31u) & ~31u;
+        for (uint32_t it = tm.rank; it < nq_r; it += SIZE) {
+            const uint32_t qd = qd0 + it, j0 = 4 * qd;
+            const bool live = qd < qd1;
+            // 9-wide windows of j0..j0+3 read the ops of j0-4 .. j0+7
+            const bool fast = live && T.q_t9 && j0 >= 4 && j0 + 7 < Ttot;
+            uint4 ur = make_uint4(0, 0, 0, 0);
+            uint32_t x0 = 0, x1 = 0, x2 = 0, opsP = 0, dmask = 0;
+            if (live) ur = philox4x32_10(qd, TAG_QUAL, olo, ohi, k0, k1);
+            if (fast) {
+                const uint2* kp = (const uint2*)(key + ((j0 - 4) >> 1));
+                const uint2 a = kp[0], b = kp[1], c = kp[2];
+                x0 = __byte_perm(a.x, a.y, 0x7632);
+                x1 = __byte_perm(b.x, b.y, 0x7632);
+                x2 = __byte_perm(c.x, c.y, 0x7632);
+                auto pack2 = [](uint32_t x) {
+                    x &= 0x03030303u;
+                    x = (x | (x >> 6)) & 0x000F000Fu;
+                    return (x | (x >> 12)) & 0xFFu;
+                };
+                auto nz4 = [](uint32_t x) { return ((__vcmpne4(x & 0x3C3C3C3Cu, 0u) & 0x08040201u) * 0x01010101u) >> 24; };
+                opsP = pack2(x0) | (pack2(x1) << 8) | (pack2(x2) << 16);
+                dmask = nz4(x0) | (nz4(x1) << 4) | (nz4(x2) << 8);
+            }
+#pragma unroll 1
             for (uint32_t t = 0; t < 4; t++) {
-                const uint32_t j = 4 * qd + t;
-                if (j < jb || j >= je) continue;
-                int start = (int)j - margin, end = (int)j + margin;
-                while (start < 0 || end >= (int)Ttot) {
-                    start++;
-                    end--;
+                const uint32_t j = j0 + t;
+                const bool want = live && j >= jb && j < je;
+                bool slow = want;
+                if (want && fast) {
+                    const uint32_t ops18 = (opsP >> (2 * t)) & 0x3FFFFu;
+                    const uint32_t gm = (dmask >> (t + 1)) & 0xFFu;
+                    const uint32_t code3 = lut3[ops18 & 63u] + 27u * lut3[(ops18 >> 6) & 63u] + 729u * lut3[ops18 >> 12];
+                    uint32_t ent = 0;
+                    if (gm == 0) {
+                        ent = T.q_t9[code3];
+                        slow = false;
+                    } else if ((gm & (gm - 1)) == 0) {
+                        const uint32_t g = __ffs(gm) - 1, bi = t + 1 + g;
+                        const uint32_t w = bi < 4 ? x0 : bi < 8 ? x1 : x2;
+                        const uint32_t dc = (w >> (8 * (bi & 3u) + 2)) & 15u;
+                        if (dc <= 3) {
+                            ent = T.q_t9d1[code3 + 19683u * (3 * g + dc - 1)];
+                            slow = false;
+                        }
+                    }
+                    if (!slow) sample(ent >> 3, ent & 7u, word_of(ur, t), j);
                 }
-                const uint32_t row = qscore_row(T, keyb, start, end);
-                const QRow rw = T.q_rows[row];
-                const uint32_t u = word_of(ur, t);
-                const uint32_t col = rw.lg ? (u >> (32 - rw.lg)) : 0u;
-                const uint32_t e = T.q_alias[rw.off + col];
-                const uint32_t fr = (uint32_t)(u << rw.lg) >> 14;
-                const uint32_t q = fr < (e & 0x3FFFFu) ? ((e >> 18) & 127u) : (e >> 25);
-                oq[j - jb] = (uint8_t)(q + 33);
+                sq.push(slow, j, word_of(ur, t));
+                const uint32_t cnt = sq.ready(false);
+                if (cnt) run_slow(cnt);
             }
         }
+        for (uint32_t cnt; (cnt = sq.ready(true)) != 0;) run_slow(cnt);
     }
     tm.sync();
 }
@@ -684,24 +812,28 @@ __global__ void __launch_bounds__(512, 1) simulate_kernel(const SimParams P) {
     Team<W> tm;
     tm.rank = threadIdx.x % (W * 32);
     tm.id = threadIdx.x / (W * 32);
-    // k-mer change probabilities staged in shared memory for the whole CTA
+    // k-mer change probabilities staged in shared memory for the whole CTA, then a 64-entry
+    // table turning three packed cigar ops into their base-3 code
     const uint32_t nq = P.T.has_err_table ? (1u << (2 * P.T.k)) : 0u;
     uint16_t* q16s = (uint16_t*)smem;
     for (uint32_t i = threadIdx.x; i < nq; i += blockDim.x) q16s[i] = P.T.q16[i];
+    const uint32_t q16_bytes = (nq * 2 + 15) & ~15u;
+    uint8_t* lut3 = smem + q16_bytes;
+    if (threadIdx.x < 64) lut3[threadIdx.x] = (uint8_t)((threadIdx.x & 3) + 3 * ((threadIdx.x >> 2) & 3) + 9 * (threadIdx.x >> 4));
     __syncthreads();
     uint8_t* ws;
     if (GWS)
         ws = P.gws + (size_t)blockIdx.x * P.slab_bytes;
     else
-        ws = smem + ((nq * 2 + 15) & ~15u) + (size_t)tm.id * P.slab_bytes;
-    uint32_t* ticket = (uint32_t*)(smem + ((nq * 2 + 15) & ~15u) + (GWS ? 0 : (size_t)TEAMS * P.slab_bytes)) + tm.id;
+        ws = smem + q16_bytes + 64 + (size_t)tm.id * P.slab_bytes;
+    uint32_t* ticket = (uint32_t*)(smem + q16_bytes + 64 + (GWS ? 0 : (size_t)TEAMS * P.slab_bytes)) + tm.id;
     while (true) {
         if (tm.rank == 0) *ticket = atomicAdd(P.counter, 1u);
         tm.sync();
         const uint32_t wi = *ticket;
         tm.sync();
         if (wi >= P.n_work) break;
-        simulate_read<W, GWS>(tm, P, P.work[wi], ws, q16s);
+        simulate_read<W, GWS>(tm, P, P.work[wi], ws, q16s, lut3);
     }
 }
 

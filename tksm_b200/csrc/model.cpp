@@ -391,6 +391,35 @@ QScoreModelHost pack_qscore_model(
             qm.direct.push_back(row_of[s]);
         }
     }
+    // fast-path closures for 9-wide windows: no D, or a single D run of 1..3 columns
+    if (qm.kq == 9) {
+        auto ent = [&](const std::string& start) {
+            std::string s = start;
+            while (!row_of.count(s)) {
+                s = s.substr(1, s.size() - 2);
+                size_t a = s.find_first_not_of('D'), b = s.find_last_not_of('D');
+                s = s.substr(a, b - a + 1);
+            }
+            uint32_t row = row_of[s];
+            return (qm.rows[2 * row] << 3) | qm.rows[2 * row + 1];
+        };
+        qm.t9.resize(19683);
+        qm.t9d1.assign((size_t)19683 * 24, 0);
+        for (uint32_t code = 0; code < 19683; code++) {
+            std::string s(9, '=');
+            uint32_t c = code;
+            for (int x = 0; x < 9; x++) {
+                s[(size_t)x] = sym[c % 3];
+                c /= 3;
+            }
+            qm.t9[code] = ent(s);
+            for (int g = 0; g < 8; g++)
+                for (int dc = 1; dc <= 3; dc++) {
+                    std::string d = s.substr(0, (size_t)g + 1) + std::string((size_t)dc, 'D') + s.substr((size_t)g + 1);
+                    qm.t9d1[code + (size_t)19683 * (3 * g + dc - 1)] = ent(d);
+                }
+        }
+    }
     // hash of D-bearing cigars
     size_t nD = 0;
     for (auto& kv : row_of) nD += kv.first.find('D') != std::string::npos;
