@@ -1,0 +1,215 @@
+"""CPU tests of the host side of libtksm_seq.so: the C ABI surface, loud failure without a device,
+model packing (csrc/model.cpp) against the oracle restatement, FASTA store, MDF parser error
+behaviour and the `tksm sequence` command line.  No compute call is made (no GPU here)."""
+import ctypes as C
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from oracle import model_oracle as mo
+from oracle import seq_oracle as so
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+MODELS = os.path.join(os.environ["TKSM_MODELS"], "badread")
+HAVE_MODELS = os.path.exists(os.path.join(MODELS, "nanopore2020.error.gz"))
+needs_models = pytest.mark.skipif(not HAVE_MODELS, reason="model files not staged by build()")
+
+
+@pytest.fixture(scope="module")
+def Sequencer(built):
+    from tksm_b200.sequence import Sequencer
+    return Sequencer
+
+
+def test_c_abi_exports_every_declared_symbol(built):
+    from tksm_b200 import _lib
+    hdr = open(os.path.join(ROOT, "include", "tksm_seq.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(tksm_seq(?:uence)?_[a-z_]+)\s*\(", hdr))
+    assert len(declared) >= 20
+    assert declared == set(_lib.EXPORTS)
+    lib = C.CDLL(_lib.LIB_PATH)
+    for name in declared:
+        assert hasattr(lib, name), name
+    # the reference-shaped C++ class is exported too (src/tksm.cpp:164-166 links against it)
+    syms = subprocess.run(["nm", "-DC", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    assert "Sequencer_module::run()" in syms and "Sequencer_module::Sequencer_module(int, char**)" in syms
+
+
+def test_product_never_imports_the_oracle():
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "tksm_b200")):
+        for f in files:
+            if f.endswith((".py", ".cpp", ".cu", ".cuh", ".hpp", ".h")):
+                text = open(os.path.join(dirpath, f), errors="replace").read()
+                assert not re.search(r"^\s*(from|import)\s+oracle|#include\s+\"[^\"]*oracle/|dlopen\(.*oracle", text, re.M), f
+
+
+def test_create_fails_loudly_without_a_device(Sequencer):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a device is present")
+    from tksm_b200.sequence import SeqError
+    with pytest.raises(SeqError, match="no CPU fallback"):
+        Sequencer()
+    s = Sequencer(host_only=True)
+    s.add_reference_text(">c\nACGT\n")
+    s.load_models("random", "random")
+    with pytest.raises(SeqError, match="host_only"):
+        s.simulate("+m\t1\t\nc\t0\t4\t+\t\n")
+
+
+def test_genome_store_keeps_every_byte(Sequencer):
+    fasta = ">chr1 some description\nACGTNNNNacgtnRYKM\nacgtACGT\r\n>chr2\nTTTT\n>chr1x\nGG\n"
+    s = Sequencer(host_only=True)
+    s.add_reference_text(fasta)
+    refs = so.load_fasta(fasta)
+    for name, seq in refs.items():
+        assert s.fetch_reference(name, 0, len(seq)) == seq.upper().encode("latin-1"), name
+    from tksm_b200.sequence import SeqError
+    with pytest.raises(SeqError):
+        s.add_reference_text(">a\nAC\n\nGT\n")     # IndexError in the reference (py/sequence.py:177)
+
+
+@needs_models
+@pytest.mark.parametrize("model", ["nanopore2020", "nanopore2018", "pacbio2016"])
+def test_packed_error_table_matches_oracle_distribution(Sequencer, model):
+    s = Sequencer(host_only=True)
+    s.load_models(model, "random")
+    tn = s.tables_numpy()
+    assert tn["k"] == 7 and tn["has_err_table"] == 1
+    rng = np.random.default_rng(1)
+    rows = list(mo.iter_error_model(os.path.join(MODELS, f"{model}.error.gz")))
+    assert len(rows) == 4 ** 7
+    for idx in [0, len(rows) - 1] + list(rng.integers(0, len(rows), size=120)):
+        kmer, alts = rows[int(idx)]
+        pc, dist, prand = mo.trial_distribution(kmer, alts)
+        q, pdist, prandp = mo.decode_error_row(tn, kmer)
+        assert q == pytest.approx(pc, abs=2e-5), kmer
+        assert prandp == pytest.approx(prand, abs=2e-5), kmer
+        assert set(pdist) == set(dist), kmer
+        for slots, p in dist.items():
+            assert pdist[slots] == pytest.approx(p, abs=2e-5), (kmer, slots)
+
+
+@needs_models
+@pytest.mark.parametrize("model", ["nanopore2020", "pacbio2016", "ideal", "random"])
+def test_packed_qscore_rows_match_oracle(Sequencer, model):
+    s = Sequencer(host_only=True)
+    s.load_models("random", model)
+    tn = s.tables_numpy()
+    m = mo.builtin_qscore_model(model) if model in ("ideal", "random") else \
+        mo.load_qscore_model(os.path.join(MODELS, f"{model}.qscore.gz"))
+    assert tn["kq"] == mo.qscore_kmer_size(m)
+    import random
+    rng = random.Random(5)
+    cigars = list(m)[:50]
+    for _ in range(400):
+        w = min(rng.choice([1, 3, 5, 7, 9]), tn["kq"])
+        ops = [rng.choices("=XI", weights=[0.8, 0.1, 0.1])[0] for _ in range(w)]
+        cig = ops[0]
+        for o in ops[1:]:
+            if rng.random() < 0.15:
+                cig += "D" * rng.choice([1, 1, 2, 3, 6])
+            cig += o
+        cigars.append(cig)
+    for cig in cigars:
+        if cig[0] == "D" or cig[-1] == "D":
+            continue
+        scores, probs = m[mo.resolve_cigar(m, cig)]
+        want = {q: p for q, p in zip(scores, probs) if p > 0}
+        tot = sum(want.values())
+        got = mo.decode_qrow(tn, mo.packed_row_for(tn, cig))
+        assert set(got) <= set(want), cig
+        for q, p in want.items():
+            assert got.get(q, 0.0) == pytest.approx(p / tot, abs=3e-5), (cig, q)
+
+
+def test_identity_table_follows_the_beta_quantiles(Sequencer):
+    from scipy import stats
+    s = Sequencer(identity=(84.0, 99.0, 5.5), host_only=True)
+    s.load_models("random", "random")
+    tab = s.tables_numpy()["ident_tab"]
+    a, b = mo.beta_parameters(84.0, 5.5, 99.0)
+    qs = np.linspace(0, 1, len(tab))
+    want = 0.99 * stats.beta.ppf(qs[1:-1], a, b)
+    assert np.abs(tab[1:-1] - want).max() < 2e-4
+    s2 = Sequencer(identity=(90.0, 90.0, 3.0), host_only=True)
+    s2.load_models("random", "random")
+    t2 = s2.tables_numpy()
+    assert t2["ident_const"] == 1 and t2["ident_mean"] == pytest.approx(0.9)
+
+
+def test_mdf_parser_raises_where_the_reference_raises(Sequencer):
+    from tksm_b200.sequence import SeqError
+    s = Sequencer(host_only=True)
+    s.add_reference_text(">c\nACGTACGTAC\n")
+    s.load_models("random", "random")
+    good = "+m\t2\tk=v;\nc\t0\t4\t+\t1G\nAAAA\t0\t4\t-\t\n"
+    s.batch(good).close()
+    for bad in ("+m\t1\t\nc\t0\t4\n",                  # not enough values to unpack
+                "+m\t1\t\nc\t0\t4\t+\t\textra\n",       # too many values
+                "+m\t1\t\nc\tx\t4\t+\t\n",             # int()
+                "+m\tone\t\nc\t0\t4\t+\t\n",           # depth
+                "+m\t1\t\nc\t0\t4\t+\t9G\n",           # modification out of range
+                "+m\t1\t\n\nc\t0\t4\t+\t\n"):          # empty line
+        with pytest.raises(SeqError):
+            s.batch(bad)
+
+
+def run_cli(args, env=None):
+    exe = os.path.join(ROOT, "tksm_b200", "tksm")
+    e = dict(os.environ)
+    e.update(env or {})
+    return subprocess.run([exe, "sequence"] + args, capture_output=True, text=True, env=e)
+
+
+def test_cli_flags_and_exit_codes(built, tmp_path):
+    # py/sequence.py:34-165: usage errors exit 2, validation errors exit 1 with the same messages
+    p = run_cli(["--list"])
+    assert p.returncode == 0
+    dests = p.stdout.split()
+    for d in ["input", "references", "badread", "perfect", "skip_qual_compute", "output_format", "threads",
+              "badread_identity", "badread_error_model", "badread_qscore_model", "badread_tail_model", "list"]:
+        assert d in dests
+    assert run_cli([]).returncode == 2
+    assert run_cli(["-i", "x.mdf", "-r", "g.fa"]).returncode == 2            # neither -o nor --perfect
+    assert run_cli(["-i", "x.mdf", "-r", "g.fa", "-o", "o.fq", "--bogus"]).returncode == 2
+    p = run_cli(["-i", "x.mdf", "-r", "g.fa", "-o", "o.fq", "--badread-identity", "101,99,5"])
+    assert p.returncode == 1 and "mean read identity cannot be more than 100" in p.stderr
+    p = run_cli(["-i", "x.mdf", "-r", "g.fa", "-o", "o.fq", "--badread-identity", "90,85,5"])
+    assert p.returncode == 1 and "cannot be larger than max identity" in p.stderr
+    p = run_cli(["-i", "x.mdf", "-r", "g.fa", "-o", "o.fq", "-O", "bam"])
+    assert p.returncode == 2 and "invalid choice" in p.stderr
+    p = run_cli(["-h"])
+    assert p.returncode == 0 and "TKSM_MODELS" in p.stdout
+    # a valid command line gets as far as needing the device
+    import torch
+    if not torch.cuda.is_available():
+        fa = tmp_path / "g.fa"
+        fa.write_text(">c\nACGT\n")
+        mdf = tmp_path / "x.mdf"
+        mdf.write_text("+m\t1\t\nc\t0\t4\t+\t\n")
+        p = run_cli(["-i", str(mdf), "-r", str(fa), "--perfect", str(tmp_path / "o.fasta")])
+        assert p.returncode == 1 and "no CPU fallback" in p.stderr
+
+
+def test_model_lookup_first_directory_wins(Sequencer, tmp_path):
+    # py/sequence.py:21-31: directories are scanned in reverse, so the first entry wins on a clash
+    for d, line in (("a", "=;1;5:1.0,\nX;1;5:1.0,\nI;1;5:1.0,\n"), ("b", "=;1;7:1.0,\nX;1;7:1.0,\nI;1;7:1.0,\n")):
+        os.makedirs(tmp_path / d / "badread")
+        import gzip
+        with gzip.open(tmp_path / d / "badread" / "toy.qscore.gz", "wt") as f:
+            f.write("overall;3;1:1.0,\n" + line)
+    old = os.environ["TKSM_MODELS"]
+    try:
+        os.environ["TKSM_MODELS"] = f"{tmp_path / 'a'}:{tmp_path / 'b'}"
+        s = Sequencer(host_only=True)
+        s.load_models("random", "toy")
+        tn = s.tables_numpy()
+        assert set(mo.decode_qrow(tn, mo.packed_row_for(tn, "="))) == {5}
+    finally:
+        os.environ["TKSM_MODELS"] = old
