@@ -81,6 +81,9 @@ typedef struct tksm_seq_tables {
     const uint32_t* q_alias; size_t n_q_alias;
     uint64_t seed;
     int compute_qual;
+    const uint8_t* qcls; size_t n_qcls;           /* 4^k change-probability classes (0 entries without a table) */
+    const double* qrep; size_t n_qrep;            /* 256 class representatives */
+    const uint16_t* thr; size_t n_thr;            /* [64 delta bins][256 classes][8]: P(N >= m) * 65536 */
 } tksm_seq_tables;
 
 void tksm_seq_default_config(tksm_seq_config* cfg);

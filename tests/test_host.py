@@ -125,7 +125,8 @@ def test_packed_qscore_rows_match_oracle(Sequencer, model):
         got = mo.decode_qrow(tn, mo.packed_row_for(tn, cig))
         assert set(got) <= set(want), cig
         for q, p in want.items():
-            assert got.get(q, 0.0) == pytest.approx(p / tot, abs=3e-5), (cig, q)
+            # one 16-bit uniform per read base: alias thresholds carry 16 - lg fraction bits
+            assert got.get(q, 0.0) == pytest.approx(p / tot, abs=1e-4), (cig, q)
 
 
 def test_identity_table_follows_the_beta_quantiles(Sequencer):

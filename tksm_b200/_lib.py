@@ -65,6 +65,9 @@ class Tables(C.Structure):
         ("q_alias", C.POINTER(C.c_uint32)), ("n_q_alias", C.c_size_t),
         ("seed", C.c_uint64),
         ("compute_qual", C.c_int),
+        ("qcls", C.POINTER(C.c_uint8)), ("n_qcls", C.c_size_t),
+        ("qrep", C.POINTER(C.c_double)), ("n_qrep", C.c_size_t),
+        ("thr", C.POINTER(C.c_uint16)), ("n_thr", C.c_size_t),
     ]
 
 

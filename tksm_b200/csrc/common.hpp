@@ -14,9 +14,9 @@ namespace tk {
 // key     = (seed lo, seed hi)
 enum : uint32_t {
     TAG_READ = 0,    // c0 = 0: identity draw (w0); c0 = 1: uuid (w0..w3); c0 = 2: flanks (w0 left, w1 right)
-    TAG_ARRIVE = 1,  // | epoch << 8 ; c0 = start position >> 2 ; word = start position & 3
+    TAG_ARRIVE = 1,  // | epoch << 8 ; c0 = start position >> 3 ; 16-bit lane (position & 7) of the 128 bits
     TAG_TRIAL = 2,   // | epoch << 8 | trial << 20 ; c0 = start position
-    TAG_QUAL = 3,    // c0 = untrimmed read base index >> 2 ; word = index & 3
+    TAG_QUAL = 3,    // c0 = untrimmed read base index >> 3 ; 16-bit lane (index & 7) of the 128 bits
 };
 
 constexpr int MAX_K = 7;             // error-model k-mer size supported (4^7 rows)
@@ -27,6 +27,9 @@ constexpr int MAX_TRIALS_PER_EPOCH = 8;   // Poisson count cap per start positio
 constexpr int MAX_SLOT_LEN = 5;      // bases one fragment slot can hold after an edit
 constexpr int IDENT_TAB_BINS = 4096;
 constexpr int DELTA_TAB_BINS = 64;
+constexpr int Q_CLASSES = 256;       // change-probability classes of the k-mers; class 255 = "not in the table" (q = 1)
+constexpr uint32_t Q_CLASS_RANDOM = 255;
+constexpr int THR_PER_CLASS = 8;     // P(N >= m), m = 1..8, as u16 thresholds (== MAX_TRIALS_PER_EPOCH)
 constexpr float TIME_CAP = 100.0f;   // py/tksm_badread.py:354 (loop_count > 100 * frag_len)
 constexpr uint32_t KEY_UNTOUCHED = 0xFFFFFFFFu;
 
@@ -63,7 +66,8 @@ struct DevTables {
     // error model
     int k;                        // k-mer size (1 for the "random" model)
     int has_err_table;            // 0 => every trial is a random change
-    const uint16_t* q16;          // 4^k: P(trial changes something) * 65536, saturated
+    const uint8_t* qcls;          // 4^k: change-probability class of the k-mer
+    const uint16_t* thr;          // [DELTA_TAB_BINS][Q_CLASSES][THR_PER_CLASS]: P(Poisson(q delta) >= m) * 65536
     const uint32_t* err_alias;    // 4^k * 32: thr22 | a << 22 | b << 27
     const uint64_t* err_alts;     // 4^k * 32 edit words
     // identity
@@ -83,7 +87,7 @@ struct DevTables {
     // fast path for 9-wide windows (kq == 9), entries = alias offset << 3 | log2 columns; 0 pointers when kq != 9
     const uint32_t* q_t9;         // 3^9: D-free windows, base-3 code of the ops (first op lowest)
     const uint32_t* q_t9d1;       // 3^9 * 24: one D run of 1..3 at gap g: code + 19683 * (3 g + dc - 1)
-    const uint32_t* q_alias;      // thr18 | qa << 18 | qb << 25
+    const uint32_t* q_alias;      // thr16 | qa << 16 | qb << 23
     uint32_t seed_lo, seed_hi;
 };
 

@@ -84,8 +84,10 @@ __global__ void synth_genome_kernel(uint32_t* words, uint64_t nwords, uint32_t s
 }
 
 constexpr size_t SMEM_TOTAL = 232448;  // 227 KB opt-in maximum per CTA on sm_100
-constexpr int N_CLASSES = 4;           // W = 1, 4, 16 in shared memory; W = 16 with a global workspace
-const int CLASS_W[N_CLASSES] = {1, 4, 16, 16};
+constexpr int N_CLASSES = 6;           // teams of 1, 2, 4, 8, 24 warps in shared memory; 24 warps with a global workspace
+constexpr int GWS_CLASS = N_CLASSES - 1;
+const int CLASS_W[N_CLASSES] = {1, 2, 4, 8, 24, 24};
+inline uint32_t list_capacity(uint32_t ncap) { return ncap / 5 * 2 + 64; }
 
 }  // namespace
 
@@ -96,7 +98,7 @@ struct tksm_seq_batch {
     DevBatch db{};
     std::vector<uint64_t> scr_off, raw_off;
     std::vector<uint32_t> work[N_CLASSES];
-    uint32_t* d_work[N_CLASSES] = {nullptr, nullptr, nullptr, nullptr};
+    uint32_t* d_work[N_CLASSES] = {};
     uint32_t max_n_gws = 0;
     DBuf scr_seq, scr_qual, scr_raw, per_read, out[2], rec_len[2], rec_off[2], sums, gws, counters;
     uint64_t out_bytes[2] = {0, 0};
@@ -128,16 +130,18 @@ struct tksm_seq {
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     int num_sms = 148;
     DBuf d_genome, d_exc_start, d_exc_len, d_exc_chr;
-    DBuf d_q16, d_alias, d_alts, d_ident, d_delta, d_qdirect, d_qhash, d_qrows, d_qalias, d_t9, d_t9d1;
+    DBuf d_qcls, d_thr, d_alias, d_alts, d_ident, d_delta, d_qdirect, d_qhash, d_qrows, d_qalias, d_t9, d_t9d1;
     DevTables dt{};
     HBuf stage, stage_out;
-    uint32_t ncap[N_CLASSES] = {0, 0, 0, 0};
-    uint32_t slab[N_CLASSES] = {0, 0, 0, 0};
-    size_t smem_bytes[N_CLASSES] = {0, 0, 0, 0};
+    uint32_t ncap[N_CLASSES] = {};
+    uint32_t cap_list[N_CLASSES] = {};
+    uint32_t slab[N_CLASSES] = {};
+    size_t smem_bytes[N_CLASSES] = {};
+    std::vector<uint16_t> thr;
     bool attrs_set = false;
 
     ~tksm_seq() {
-        for (DBuf* d : {&d_genome, &d_exc_start, &d_exc_len, &d_exc_chr, &d_q16, &d_alias, &d_alts, &d_ident, &d_delta,
+        for (DBuf* d : {&d_genome, &d_exc_start, &d_exc_len, &d_exc_chr, &d_qcls, &d_thr, &d_alias, &d_alts, &d_ident, &d_delta,
                         &d_qdirect, &d_qhash, &d_qrows, &d_qalias, &d_t9, &d_t9d1})
             d->release();
         stage.release();
@@ -181,24 +185,27 @@ void commit_reference(tksm_seq* h) {
 
 void compute_classes(tksm_seq* h) {
     const size_t nq = h->em.has_table ? ((size_t)1 << (2 * h->em.k)) : 0;
-    const size_t q16_bytes = (nq * 2 + 15) & ~size_t(15);
-    const size_t pool = SMEM_TOTAL - q16_bytes - 128;
-    for (int c = 0; c < 3; c++) {
-        const int W = CLASS_W[c], teams = 16 / W;
-        const size_t hist = 256 * (W >= 8 ? 8 : 4);
-        size_t slab = (pool / teams) & ~size_t(15);
-        size_t ncap = ((slab - hist - 128 - (size_t)W * 512 - 16) / 5) & ~size_t(3);
-        h->slab[c] = (uint32_t)slab;
-        h->ncap[c] = (uint32_t)ncap;
-        h->smem_bytes[c] = q16_bytes + slab * teams + 128;
+    const size_t qcls_bytes = (nq + 15) & ~size_t(15);
+    const size_t pool = SMEM_TOTAL - qcls_bytes - 64 - 128;
+    for (int c = 0; c < GWS_CLASS; c++) {
+        const int W = CLASS_W[c], teams = SIM_WARPS / W;
+        const uint32_t hist_elem = W >= 8 ? 8 : 4;
+        const size_t budget = (pool / teams) & ~size_t(15);
+        uint32_t ncap = 16;
+        while (slab_layout(W, hist_elem, ncap + 16, list_capacity(ncap + 16)).bytes <= budget) ncap += 16;
+        h->ncap[c] = ncap;
+        h->cap_list[c] = list_capacity(ncap);
+        h->slab[c] = slab_layout(W, hist_elem, ncap, h->cap_list[c]).bytes;
+        h->smem_bytes[c] = qcls_bytes + 64 + (size_t)h->slab[c] * teams + 128;
     }
-    h->smem_bytes[3] = q16_bytes + 128;
+    h->smem_bytes[GWS_CLASS] = qcls_bytes + 64 + 128;
 }
 
 void upload_models(tksm_seq* h) {
     if (h->cfg.host_only) return;
     CK(cudaSetDevice(h->cfg.device));
-    upload_vec(h->d_q16, h->em.q16, h->stream);
+    upload_vec(h->d_qcls, h->em.qcls, h->stream);
+    upload_vec(h->d_thr, h->thr, h->stream);
     upload_vec(h->d_alias, h->em.alias, h->stream);
     upload_vec(h->d_alts, h->em.alts, h->stream);
     upload_vec(h->d_ident, h->idh.tab, h->stream);
@@ -213,7 +220,8 @@ void upload_models(tksm_seq* h) {
     DevTables& T = h->dt;
     T.k = h->em.k;
     T.has_err_table = h->em.has_table;
-    T.q16 = h->d_q16.as<uint16_t>();
+    T.qcls = h->d_qcls.as<uint8_t>();
+    T.thr = h->d_thr.as<uint16_t>();
     T.err_alias = h->d_alias.as<uint32_t>();
     T.err_alts = h->d_alts.as<uint64_t>();
     T.ident_const = h->idh.constant;
@@ -240,7 +248,7 @@ template <int W, bool GWS>
 void launch_sim(tksm_seq* h, const SimParams& P, size_t smem, int grid) {
     auto kern = simulate_kernel<W, GWS>;
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<grid, 512, smem, h->stream>>>(P);
+    kern<<<grid, SIM_THREADS, smem, h->stream>>>(P);
     CK(cudaGetLastError());
 }
 
@@ -268,9 +276,9 @@ void batch_upload(tksm_seq* h, tksm_seq_batch* b) {
         ro += align_up((size_t)L, 16);
         uint32_t n = L + 2 * k;
         int c = 0;
-        while (c < 3 && n > h->ncap[c]) c++;
+        while (c < GWS_CLASS && n > h->ncap[c]) c++;
         b->work[c].push_back((uint32_t)r);
-        if (c == 3) b->max_n_gws = std::max(b->max_n_gws, n);
+        if (c == GWS_CLASS) b->max_n_gws = std::max(b->max_n_gws, n);
     }
     b->scr_off[R] = so;
     b->raw_off[R] = ro;
@@ -411,11 +419,11 @@ void batch_run(tksm_seq* h, tksm_seq_batch* b, int which, int format, tksm_seq_s
             b->rec_off[o].ensure((size_t)R * 8);
         }
     if (b->max_n_gws) {
-        size_t ncap = align_up(b->max_n_gws + 16, 16);
-        size_t slab = align_up(256 * 8 + 128 + 16 * 512 + 5 * ncap + 16, 16);
-        h->ncap[3] = (uint32_t)ncap;
-        h->slab[3] = (uint32_t)slab;
-        b->gws.ensure(slab * h->num_sms);
+        const uint32_t ncap = (uint32_t)align_up(b->max_n_gws + 16, 16);
+        h->ncap[GWS_CLASS] = ncap;
+        h->cap_list[GWS_CLASS] = ncap / 2 + 64;
+        h->slab[GWS_CLASS] = slab_layout(CLASS_W[GWS_CLASS], 8, ncap, h->cap_list[GWS_CLASS]).bytes;
+        b->gws.ensure((size_t)h->slab[GWS_CLASS] * h->num_sms);
     }
     uint64_t* d_totals = (uint64_t*)((char*)b->counters.p + 32);
     CK(cudaMemsetAsync(b->counters.p, 0, 64, h->stream));
@@ -432,15 +440,18 @@ void batch_run(tksm_seq* h, tksm_seq_batch* b, int which, int format, tksm_seq_s
         P.counter = b->counters.as<uint32_t>() + c;
         P.flags = flags;
         P.ncap = h->ncap[c];
+        P.cap_list = h->cap_list[c];
         P.slab_bytes = h->slab[c];
         P.gws = b->gws.as<uint8_t>();
-        const int teams = 16 / CLASS_W[c];
+        const int teams = c == GWS_CLASS ? 1 : SIM_WARPS / CLASS_W[c];
         int grid = (int)std::min<size_t>((size_t)h->num_sms, (P.n_work + teams - 1) / teams);
         switch (c) {
             case 0: launch_sim<1, false>(h, P, h->smem_bytes[c], grid); break;
-            case 1: launch_sim<4, false>(h, P, h->smem_bytes[c], grid); break;
-            case 2: launch_sim<16, false>(h, P, h->smem_bytes[c], grid); break;
-            default: launch_sim<16, true>(h, P, h->smem_bytes[c], grid); break;
+            case 1: launch_sim<2, false>(h, P, h->smem_bytes[c], grid); break;
+            case 2: launch_sim<4, false>(h, P, h->smem_bytes[c], grid); break;
+            case 3: launch_sim<8, false>(h, P, h->smem_bytes[c], grid); break;
+            case 4: launch_sim<24, false>(h, P, h->smem_bytes[c], grid); break;
+            default: launch_sim<24, true>(h, P, h->smem_bytes[c], grid); break;
         }
         launches++;
     }
@@ -705,6 +716,7 @@ int tksm_seq_load_models(tksm_seq* h, const char* error_model, const char* qscor
     fprintf(stderr, "Loading qscore model %s\n", qm.c_str());
     h->qm = load_qscore_model(qm, names.qscore);
     h->delta = make_delta_table(h->em);
+    h->thr = make_threshold_table(h->em, h->delta);
     h->corr0 = std::isnan(h->cfg.corr0) ? 0.0f : (float)h->cfg.corr0;
     h->corr1 = std::isnan(h->cfg.corr1) ? 0.0f : (float)h->cfg.corr1;
     compute_classes(h);
@@ -747,6 +759,12 @@ int tksm_seq_get_tables(tksm_seq* h, tksm_seq_tables* t) {
     t->n_q_alias = h->qm.alias.size();
     t->seed = h->cfg.seed;
     t->compute_qual = !h->cfg.skip_qual_compute;
+    t->qcls = h->em.qcls.data();
+    t->n_qcls = h->em.qcls.size();
+    t->qrep = h->em.qrep.data();
+    t->n_qrep = h->em.qrep.size();
+    t->thr = h->thr.data();
+    t->n_thr = h->thr.size();
     API_END(h)
 }
 

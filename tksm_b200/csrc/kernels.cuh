@@ -162,6 +162,13 @@ __device__ __forceinline__ bool crossed(uint32_t n, uint32_t loss, uint32_t ins,
     return ((uint64_t)(n - loss) << 24) <= (uint64_t)tq * (uint64_t)(n + ins);
 }
 
+constexpr int SIM_THREADS = 768;     // 24 warps per CTA, one CTA per SM
+constexpr int SIM_WARPS = SIM_THREADS / 32;
+constexpr uint32_t MISC_WORDS = 64;  // per-team scratch words
+constexpr uint32_t MISC_WSUM = 8;    // W + 1 words of scan partials
+constexpr uint32_t MISC_LISTN = 40;  // touched-list length (teams of more than one warp)
+constexpr uint32_t QUEUE_BYTES = 64 * 4 + 64 * 2;  // per-warp compaction queue: 64 x (u32, u16)
+
 struct SimParams {
     DevTables T;
     DevBatch B;
@@ -169,15 +176,28 @@ struct SimParams {
     uint32_t n_work;
     uint32_t* counter;      // dynamic work counter
     uint32_t flags;         // RUN_*
-    uint32_t ncap;          // fragment capacity of one team workspace
+    uint32_t ncap;          // fragment capacity of one team workspace (multiple of 16)
+    uint32_t cap_list;      // touched-list capacity
     uint32_t slab_bytes;    // bytes of one team workspace
     uint8_t* gws;           // global workspaces (one per CTA) when GWS
 };
 
-// workspace layout (team private):
-//   hist[256] (HistT) | misc[32] u32 | per-warp queues W x (64 + 64) u32 | key[ncap] u32 | frag[ncap + 16] u8
-template <typename HistT>
-__device__ __forceinline__ uint32_t ws_misc_off() { return 256 * (uint32_t)sizeof(HistT); }
+// Team workspace layout, shared by the host (sizing) and the kernel:
+//   T1[256] u16 | hist[256] HistT | misc[64] u32 | W queues | list[cap_list] u32 | key[ncap] u32 | frag[ncap + 32] u8
+struct SlabLayout {
+    uint32_t off_hist, off_misc, off_queue, off_list, off_key, off_frag, bytes;
+};
+__host__ __device__ inline SlabLayout slab_layout(int W, uint32_t hist_elem_bytes, uint32_t ncap, uint32_t cap_list) {
+    SlabLayout L;
+    L.off_hist = 512;
+    L.off_misc = L.off_hist + 256 * hist_elem_bytes;
+    L.off_queue = L.off_misc + MISC_WORDS * 4;
+    L.off_list = L.off_queue + (uint32_t)W * QUEUE_BYTES;
+    L.off_key = (L.off_list + 4 * cap_list + 15u) & ~15u;
+    L.off_frag = L.off_key + 4 * ncap;
+    L.bytes = (L.off_frag + ncap + 32 + 15u) & ~15u;
+    return L;
+}
 
 // Finds the first of 256 bins at which the cumulative (loss, ins) crosses the target.
 // Executed by the first warp of the team; results broadcast through misc[].
@@ -187,31 +207,37 @@ template <typename HistT>
 __device__ __forceinline__ void hist_scan_warp(const HistT* hist, uint32_t* misc, uint32_t n, uint32_t loss0,
                                                uint32_t ins0, uint32_t tq) {
     const int lane = threadIdx.x & 31;
-    uint32_t la[8], li[8];
     uint32_t sa = 0, si = 0;
+    uint32_t va[8], vi[8];
 #pragma unroll
     for (int b = 0; b < 8; b++) {
         HistT h = hist[lane * 8 + b];
-        uint32_t a, i;
         if (sizeof(HistT) == 4) {
-            a = (uint32_t)h & 0xFFFFu;
-            i = (uint32_t)h >> 16;
+            va[b] = (uint32_t)h & 0xFFFFu;
+            vi[b] = (uint32_t)h >> 16;
         } else {
-            a = (uint32_t)((uint64_t)h & 0xFFFFFFFFull);
-            i = (uint32_t)((uint64_t)h >> 32);
+            va[b] = (uint32_t)((uint64_t)h & 0xFFFFFFFFull);
+            vi[b] = (uint32_t)((uint64_t)h >> 32);
         }
-        sa += a;
-        si += i;
-        la[b] = sa;
-        li[b] = si;
+        sa += va[b];
+        si += vi[b];
     }
-    uint32_t ea = warp_incl_scan(sa) - sa, ei = warp_incl_scan(si) - si;  // exclusive over lanes
+    const uint32_t ea = warp_incl_scan(sa) - sa, ei = warp_incl_scan(si) - si;  // exclusive over lanes
     int first = 8;
+    uint32_t ca = ea, ci = ei, fa = 0, fi = 0;
 #pragma unroll
-    for (int b = 7; b >= 0; b--)
-        if (crossed(n, loss0 + ea + la[b], ins0 + ei + li[b], tq)) first = b;
-    uint32_t ball = __ballot_sync(0xffffffffu, first < 8);
-    uint32_t tot_a = __shfl_sync(0xffffffffu, ea + sa, 31), tot_i = __shfl_sync(0xffffffffu, ei + si, 31);
+    for (int b = 0; b < 8; b++) {
+        const uint32_t na = ca + va[b], ni = ci + vi[b];
+        if (first == 8 && crossed(n, loss0 + na, ins0 + ni, tq)) {
+            first = b;
+            fa = ca;
+            fi = ci;
+        }
+        ca = na;
+        ci = ni;
+    }
+    const uint32_t ball = __ballot_sync(0xffffffffu, first < 8);
+    const uint32_t tot_a = __shfl_sync(0xffffffffu, ea + sa, 31), tot_i = __shfl_sync(0xffffffffu, ei + si, 31);
     if (ball == 0) {
         if (lane == 0) {
             misc[0] = 256;
@@ -220,11 +246,11 @@ __device__ __forceinline__ void hist_scan_warp(const HistT* hist, uint32_t* misc
             misc[4] = tot_i;
         }
     } else {
-        int src = __ffs(ball) - 1;
+        const int src = __ffs(ball) - 1;
         if (lane == src) {
             misc[0] = (uint32_t)(lane * 8 + first);
-            misc[1] = ea + (first ? la[first - 1] : 0);
-            misc[2] = ei + (first ? li[first - 1] : 0);
+            misc[1] = fa;
+            misc[2] = fi;
             misc[3] = tot_a;
             misc[4] = tot_i;
         }
@@ -278,24 +304,22 @@ __device__ __forceinline__ uint32_t qscore_row(const DevTables& T, const uint8_t
     }
 }
 
-
 // ------------------------------------------------------- warp compaction
 // Rare, divergent work (a trial at a start position; a qscore window that misses the direct
 // tables) is not done where it is found: the lanes that found some push it to a 64-entry ring in
 // shared memory and the warp drains 32 entries at a time with every lane busy.
 struct WarpQueue {
     uint32_t* a;
-    uint32_t* b;
+    uint16_t* b;
     uint32_t head, tail;  // warp-uniform
     __device__ __forceinline__ void push(bool pred, uint32_t va, uint32_t vb) {
         const uint32_t m = __ballot_sync(0xffffffffu, pred);
         if (pred) {
             const uint32_t slot = (tail + __popc(m & ((1u << (threadIdx.x & 31)) - 1))) & 63u;
             a[slot] = va;
-            b[slot] = vb;
+            b[slot] = (uint16_t)vb;
         }
         tail += __popc(m);
-        __syncwarp();
     }
     // number of entries the next drain handles: 32 when at least that many are queued, or the
     // remainder when `flush`
@@ -306,6 +330,7 @@ struct WarpQueue {
     __device__ __forceinline__ bool take(uint32_t cnt, uint32_t& va, uint32_t& vb) {
         const uint32_t lane = threadIdx.x & 31;
         const bool mine = lane < cnt;
+        __syncwarp();
         if (mine) {
             va = a[(head + lane) & 63u];
             vb = b[(head + lane) & 63u];
@@ -316,24 +341,38 @@ struct WarpQueue {
     }
 };
 
+// four fragment bytes -> their 2-bit codes packed in 8 bits / a 4-bit mask of the bytes that are not ACGT codes
+__device__ __forceinline__ uint32_t pack4(uint32_t x) {
+    x &= 0x03030303u;
+    x = (x | (x >> 6)) & 0x000F000Fu;
+    return (x | (x >> 12)) & 0xFFu;
+}
+__device__ __forceinline__ uint32_t nz4(uint32_t x, uint32_t mask) {
+    return ((__vcmpne4(x & mask, 0u) & 0x08040201u) * 0x01010101u) >> 24;
+}
+
 // ------------------------------------------------------------ simulate one
 template <int W, bool GWS>
 __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams& P, uint32_t r, uint8_t* ws,
-                                              const uint16_t* q16s, const uint8_t* lut3) {
+                                              const uint8_t* qcls_s, const uint8_t* lut3) {
     using HistT = typename std::conditional<(GWS || W >= 8), uint64_t, uint32_t>::type;
     constexpr int SIZE = Team<W>::SIZE;
     const DevTables& T = P.T;
     const DevBatch& B = P.B;
+    const SlabLayout LY = slab_layout(W, (uint32_t)sizeof(HistT), P.ncap, P.cap_list);
 
-    HistT* hist = (HistT*)ws;
-    uint32_t* misc = (uint32_t*)(ws + ws_misc_off<HistT>());
-    uint32_t* wsum = misc + 8;
-    uint32_t* wq_a = misc + 32 + (tm.rank >> 5) * 128;  // this warp's compaction queue (two lanes of payload)
-    uint32_t* wq_b = wq_a + 64;
-    uint32_t* key = misc + 32 + W * 128;
+    uint16_t* T1 = (uint16_t*)ws;
+    HistT* hist = (HistT*)(ws + LY.off_hist);
+    uint32_t* misc = (uint32_t*)(ws + LY.off_misc);
+    uint32_t* wsum = misc + MISC_WSUM;
+    uint32_t* wq_a = (uint32_t*)(ws + LY.off_queue + (uint32_t)(tm.rank >> 5) * QUEUE_BYTES);
+    uint16_t* wq_b = (uint16_t*)(wq_a + 64);
+    uint32_t* list = (uint32_t*)(ws + LY.off_list);
+    uint32_t* key = (uint32_t*)(ws + LY.off_key);
     uint8_t* keyb = (uint8_t*)key;
-    uint8_t* frag = (uint8_t*)(key + P.ncap);
+    uint8_t* frag = ws + LY.off_frag;
     const uint32_t* fragw = (const uint32_t*)frag;
+    const int lane = tm.rank & 31;
 
     const uint32_t mol = B.read_mol[r];
     const uint32_t L = B.mol_raw_len[mol];
@@ -350,7 +389,7 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
             frag[tm.rank] = (uint8_t)((fl.x >> (2 * tm.rank)) & 3u);
             frag[k + L + tm.rank] = (uint8_t)((fl.y >> (2 * tm.rank)) & 3u);
         }
-        if (tm.rank < 16) frag[n + tm.rank] = 0;
+        if (tm.rank < 32) frag[n + tm.rank] = 0;
         const uint32_t s0 = B.mol_seg_begin[mol], s1 = B.mol_seg_begin[mol + 1];
         uint32_t off = k;
         for (uint32_t s = s0; s < s1; s++) {
@@ -397,8 +436,12 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
             off += len;
         }
     }
-    // key init
-    for (uint32_t p = tm.rank; p < n; p += SIZE) key[p] = KEY_UNTOUCHED;
+    // key init (16 bytes per store; the array is a multiple of 16 slots long)
+    {
+        uint4* k4 = (uint4*)key;
+        const uint32_t n4 = (n + 3) >> 2;
+        for (uint32_t p = tm.rank; p < n4; p += SIZE) k4[p] = make_uint4(KEY_UNTOUCHED, KEY_UNTOUCHED, KEY_UNTOUCHED, KEY_UNTOUCHED);
+    }
     tm.sync();
 
     const uint64_t sbase = B.scr_off[r];
@@ -417,7 +460,7 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
         return;
     }
 
-    // ---- 2. per-read target identity, effective target and epoch length
+    // ---- 2. per-read target identity, effective target and epoch length class
     float target;
     if (T.ident_const) {
         target = T.ident_mean;
@@ -436,169 +479,212 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
         tq = 1u << 24;
     else
         tq = (uint32_t)__fmul_rn(teff, 16777216.0f);
-    float delta;
-    {
-        int bin = (int)__fmul_rn(__fsub_rn(teff, 0.5f), 128.0f);
-        bin = bin < 0 ? 0 : bin > DELTA_TAB_BINS - 1 ? DELTA_TAB_BINS - 1 : bin;
-        delta = T.delta_tab[bin];
-    }
+    int bin = (int)__fmul_rn(__fsub_rn(teff, 0.5f), 128.0f);
+    bin = bin < 0 ? 0 : bin > DELTA_TAB_BINS - 1 ? DELTA_TAB_BINS - 1 : bin;
+    const float delta = T.delta_tab[bin];
+    const uint16_t* thr_bin = T.thr + (size_t)bin * Q_CLASSES * THR_PER_CLASS;
+    for (uint32_t c = tm.rank; c < Q_CLASSES; c += SIZE) T1[c] = thr_bin[c * THR_PER_CLASS];
+    if (tm.rank == 0) misc[MISC_LISTN] = 0;
 
     // ---- 3. error injection epochs
     uint32_t loss_c = 0, ins_c = 0, changed_c = 0;  // committed totals
     uint32_t status = ST_OK;
+    uint32_t list_n = 0;  // W == 1: the touched-list length lives in a (warp-uniform) register
     const uint32_t npos = n - k;
-    const uint32_t nquad = (npos + 3) >> 2;
     const uint32_t vm0 = k >= 4 ? 0xFCFCFCFCu : (0xFCFCFCFCu >> (8 * (4 - k)));
     const uint32_t vm1 = k <= 4 ? 0u : (0xFCFCFCFCu >> (8 * (8 - k)));
     const uint32_t codemask = (1u << (2 * k)) - 1;
+    const uint32_t kbits = (1u << k) - 1;
+    const bool has_table = T.has_err_table != 0;
+
+    // runs `f(p)` for every touched slot (every slot when the list overflowed)
+    auto for_touched = [&](uint32_t cnt, auto&& f) {
+        if (cnt <= P.cap_list) {
+            for (uint32_t e = tm.rank; e < cnt; e += SIZE) f(list[e]);
+        } else {
+            for (uint32_t p = tm.rank; p < n; p += SIZE)
+                if (key[p] != KEY_UNTOUCHED) f(p);
+        }
+    };
+
     if (!crossed(n, 0, 0, tq)) {
         for (uint32_t epoch = 0;; epoch++) {
             for (uint32_t b = tm.rank; b < 256; b += SIZE) hist[b] = 0;
             tm.sync();
-            // --- arrivals: Poisson(q * delta) trials per start position; found ones are queued
+            // --- arrivals: N ~ Poisson(q * delta) trials per start position, found ones are queued
             WarpQueue tq_{wq_a, wq_b, 0, 0};
             auto run_trials = [&](uint32_t cnt) {
-                uint32_t ent = 0, dummy = 0;
-                if (!tq_.take(cnt, ent, dummy)) return;
-                const uint32_t i = ent & 0x0FFFFFFFu;
-                const int N = (int)(ent >> 28) + 1;
-                const uint32_t qw = i >> 2, sh = 8 * (i & 3u);
-                const uint32_t x0 = __funnelshift_r(fragw[qw], fragw[qw + 1], sh);
-                const uint32_t x1 = __funnelshift_r(fragw[qw + 1], fragw[qw + 2], sh);
-                const bool valid = T.has_err_table && (((x0 & vm0) | (x1 & vm1)) == 0);
-                uint32_t code = 0;
-                if (valid) {
-                    uint32_t c0 = (x0 | (x0 >> 6)) & 0x000F000Fu;
-                    c0 = (c0 | (c0 >> 12)) & 0xFFu;
-                    uint32_t c1 = (x1 | (x1 >> 6)) & 0x000F000Fu;
-                    c1 = (c1 | (c1 >> 12)) & 0xFFu;
-                    code = (c0 | (c1 << 8)) & codemask;
-                }
-                for (int tr = 0; tr < N; tr++) {
-                    const uint4 wr = philox4x32_10(i, TAG_TRIAL | (epoch << 8) | ((uint32_t)tr << 20), olo, ohi, k0, k1);
-                    uint32_t tm16 = wr.x >> 16;
-                    tm16 += tm16 == 0;
-                    uint32_t outcome = ERR_OUTCOME_RANDOM;
+                uint32_t i = 0, u16 = 0;
+                const bool mine = tq_.take(cnt, i, u16);
+                uint32_t x0 = 0, x1 = 0, code = 0;
+                bool valid = false;
+                int N = 0;
+                if (mine) {
+                    const uint32_t qw = i >> 2, sh = 8 * (i & 3u);
+                    x0 = __funnelshift_r(fragw[qw], fragw[qw + 1], sh);
+                    x1 = __funnelshift_r(fragw[qw + 1], fragw[qw + 2], sh);
+                    valid = has_table && (((x0 & vm0) | (x1 & vm1)) == 0);
+                    uint32_t cls = Q_CLASS_RANDOM;
                     if (valid) {
-                        uint32_t e = T.err_alias[code * ERR_ALIAS_COLS + (wr.y >> 27)];
-                        uint32_t fr = (wr.y >> 5) & 0x3FFFFFu;
-                        outcome = fr < (e & 0x3FFFFFu) ? ((e >> 22) & 31u) : (e >> 27);
+                        code = (pack4(x0) | (pack4(x1) << 8)) & codemask;
+                        cls = qcls_s[code];
                     }
-                    if (outcome != ERR_OUTCOME_RANDOM) {
-                        const uint64_t aw = T.err_alts[code * ERR_ALT_STRIDE + outcome];
-                        uint32_t boff = 28;
-                        for (uint32_t j = 0; j < k; j++) {
-                            uint32_t len = (uint32_t)(aw >> (3 * j)) & 7u;
-                            if ((aw >> (21 + j)) & 1ull) {
-                                uint32_t bases = (uint32_t)(aw >> boff) & ((1u << (2 * len)) - 1);
-                                uint32_t cand = (tm16 << 16) | (len << CONTENT_LEN_SHIFT) | (bases << 1);
-                                atomicMin(&key[i + j], cand);
-                            }
-                            boff += 2 * len;
+                    const uint4 th = __ldg((const uint4*)(thr_bin + cls * THR_PER_CLASS));
+                    const uint32_t uu = u16 | (u16 << 16);
+                    // halves of th hold P(N >= m): count those above the uniform
+                    N = __popc(__vcmpgtu2(th.x, uu) & 0x00010001u) + __popc(__vcmpgtu2(th.y, uu) & 0x00010001u) +
+                        __popc(__vcmpgtu2(th.z, uu) & 0x00010001u) + __popc(__vcmpgtu2(th.w, uu) & 0x00010001u);
+                }
+                const int Nmax = __reduce_max_sync(0xffffffffu, N);
+                for (int tr = 0; tr < Nmax; tr++) {
+                    // per lane: up to k slot updates (cm = mask of slots to update)
+                    uint32_t cm = 0, tm16 = 0, rc_content = 0;
+                    uint64_t aw = 0;
+                    bool table_alt = false;
+                    if (tr < N) {
+                        const uint4 wr = philox4x32_10(i, TAG_TRIAL | (epoch << 8) | ((uint32_t)tr << 20), olo, ohi, k0, k1);
+                        tm16 = wr.x >> 16;
+                        tm16 += tm16 == 0;
+                        uint32_t outcome = ERR_OUTCOME_RANDOM;
+                        if (valid) {
+                            uint32_t e = __ldg(&T.err_alias[code * ERR_ALIAS_COLS + (wr.y >> 27)]);
+                            uint32_t fr = (wr.y >> 5) & 0x3FFFFFu;
+                            outcome = fr < (e & 0x3FFFFFu) ? ((e >> 22) & 31u) : (e >> 27);
                         }
-                    } else {
-                        // py/tksm_badread.py:199-213
-                        uint32_t type = __umulhi(wr.z, 3u);
-                        uint32_t pos = __umulhi(wr.w, k);
-                        uint32_t r2 = wr.z & 0xFFFFu;
-                        uint32_t ob = (pos < 4 ? (x0 >> (8 * pos)) : (x1 >> (8 * (pos - 4)))) & 0xFFu;
-                        uint32_t content;
-                        if (type == 0) {
-                            uint32_t nb = ob < 4 ? ((ob + 1 + ((r2 * 3u) >> 16)) & 3u) : (r2 & 3u);
-                            content = (1u << CONTENT_LEN_SHIFT) | (nb << 1);
-                        } else if (type == 1) {
-                            uint32_t nb = r2 & 3u;
-                            uint32_t before = (r2 >> 2) & 1u;
-                            content = (2u << CONTENT_LEN_SHIFT) | ((before ? 2u : 1u) << CONTENT_KIND_SHIFT) | (nb << 1);
+                        if (outcome != ERR_OUTCOME_RANDOM) {
+                            aw = __ldg(&T.err_alts[code * ERR_ALT_STRIDE + outcome]);
+                            cm = (uint32_t)(aw >> 21) & 0x7Fu;
+                            table_alt = true;
                         } else {
-                            content = 0;
+                            // py/tksm_badread.py:199-213
+                            uint32_t type = __umulhi(wr.z, 3u);
+                            uint32_t pos = __umulhi(wr.w, k);
+                            uint32_t r2 = wr.z & 0xFFFFu;
+                            uint32_t ob = (pos < 4 ? (x0 >> (8 * pos)) : (x1 >> (8 * (pos - 4)))) & 0xFFu;
+                            if (type == 0) {
+                                uint32_t nb = ob < 4 ? ((ob + 1 + ((r2 * 3u) >> 16)) & 3u) : (r2 & 3u);
+                                rc_content = (1u << CONTENT_LEN_SHIFT) | (nb << 1);
+                            } else if (type == 1) {
+                                uint32_t nb = r2 & 3u;
+                                uint32_t before = (r2 >> 2) & 1u;
+                                rc_content = (2u << CONTENT_LEN_SHIFT) | ((before ? 2u : 1u) << CONTENT_KIND_SHIFT) | (nb << 1);
+                            } else {
+                                rc_content = 0;
+                            }
+                            cm = 1u << pos;
                         }
-                        atomicMin(&key[i + pos], (tm16 << 16) | content);
+                    }
+                    while (__any_sync(0xffffffffu, cm != 0)) {
+                        bool fresh = false;
+                        uint32_t p = 0;
+                        if (cm) {
+                            const uint32_t j = __ffs(cm) - 1;
+                            cm &= cm - 1;
+                            uint32_t content = rc_content;
+                            if (table_alt) {
+                                const uint32_t lens = (uint32_t)aw & 0x1FFFFFu;
+                                const uint32_t len = (lens >> (3 * j)) & 7u;
+                                // bases before slot j: sum of the 3-bit length fields below it
+                                uint32_t below = lens & ((1u << (3 * j)) - 1);
+                                uint32_t t2 = (below & 0x1C71C7u) + ((below >> 3) & 0x1C71C7u);
+                                const uint32_t nb = ((t2 * 0x41041u) >> 18) & 0x3Fu;
+                                const uint32_t bases = (uint32_t)(aw >> (28 + 2 * nb)) & ((1u << (2 * len)) - 1);
+                                content = (len << CONTENT_LEN_SHIFT) | (bases << 1);
+                            }
+                            p = i + j;
+                            const uint32_t old = atomicMin(&key[p], (tm16 << 16) | content);
+                            fresh = old == KEY_UNTOUCHED;
+                        }
+                        // first touch of a slot: remember it
+                        const uint32_t fm = __ballot_sync(0xffffffffu, fresh);
+                        if (fm) {
+                            uint32_t base;
+                            if (W == 1) {
+                                base = list_n;
+                                list_n += __popc(fm);
+                            } else {
+                                if (lane == 0) base = atomicAdd(&misc[MISC_LISTN], (uint32_t)__popc(fm));
+                                base = __shfl_sync(0xffffffffu, base, 0);
+                            }
+                            if (fresh) {
+                                const uint32_t e = base + __popc(fm & ((1u << lane) - 1));
+                                if (e < P.cap_list) list[e] = p;
+                            }
+                        }
                     }
                 }
             };
-            const uint32_t nquad_r = (nquad + 31u) & ~31u;  // whole warps iterate together
-            for (uint32_t qd = tm.rank; qd < nquad_r; qd += SIZE) {
-                const bool live = qd < nquad;
-                uint32_t w0 = 0, w1 = 0, w2 = 0;
+            const uint32_t nblk = (npos + 7) >> 3;
+            const uint32_t nblk_r = (nblk + 31u) & ~31u;  // whole warps iterate together
+            for (uint32_t blk = tm.rank; blk < nblk_r; blk += SIZE) {
+                const bool live = blk < nblk;
+                uint32_t codes = 0, bad = 0xFFFFu;
                 uint4 ur = make_uint4(0, 0, 0, 0);
                 if (live) {
-                    w0 = fragw[qd];
-                    w1 = fragw[qd + 1];
-                    w2 = fragw[qd + 2];
-                    ur = philox4x32_10(qd, TAG_ARRIVE | (epoch << 8), olo, ohi, k0, k1);
+                    const uint2* fp = (const uint2*)(frag + 8 * blk);
+                    const uint2 fa = fp[0], fb = fp[1];
+                    if (has_table) {
+                        codes = pack4(fa.x) | (pack4(fa.y) << 8) | (pack4(fb.x) << 16) | (pack4(fb.y) << 24);
+                        bad = nz4(fa.x, 0xFCFCFCFCu) | (nz4(fa.y, 0xFCFCFCFCu) << 4) | (nz4(fb.x, 0xFCFCFCFCu) << 8) |
+                              (nz4(fb.y, 0xFCFCFCFCu) << 12);
+                    }
+                    ur = philox4x32_10(blk, TAG_ARRIVE | (epoch << 8), olo, ohi, k0, k1);
                 }
 #pragma unroll 1
-                for (uint32_t t = 0; t < 4; t++) {
-                    const uint32_t i = 4 * qd + t;
-                    int N = 0;
+                for (uint32_t t = 0; t < 8; t++) {
+                    const uint32_t i = 8 * blk + t;
+                    const uint32_t wsel = t < 4 ? (t < 2 ? ur.x : ur.y) : (t < 6 ? ur.z : ur.w);
+                    const uint32_t u16 = (wsel >> (16 * (t & 1u))) & 0xFFFFu;
+                    bool hit = false;
                     if (live && i < npos) {
-                        const uint32_t x0 = __funnelshift_r(w0, w1, 8 * t), x1 = __funnelshift_r(w1, w2, 8 * t);
-                        const bool valid = T.has_err_table && (((x0 & vm0) | (x1 & vm1)) == 0);
-                        float q = 1.0f;
-                        if (valid) {
-                            uint32_t c0 = (x0 | (x0 >> 6)) & 0x000F000Fu;
-                            c0 = (c0 | (c0 >> 12)) & 0xFFu;
-                            uint32_t c1 = (x1 | (x1 >> 6)) & 0x000F000Fu;
-                            c1 = (c1 | (c1 >> 12)) & 0xFFu;
-                            const uint32_t code = (c0 | (c1 << 8)) & codemask;
-                            q = __fmul_rn((float)q16s[code], 1.52587890625e-05f);  // 2^-16
-                        }
-                        const float x = __fmul_rn(q, delta);
-                        const float U = __fmul_rn((float)(word_of(ur, t) >> 8), 5.9604644775390625e-08f);  // 2^-24
-                        float term = expneg(x), cum = term;
-                        if (!(U < cum)) {
-                            for (N = 1; N < MAX_TRIALS_PER_EPOCH; N++) {
-                                term = __fmul_rn(__fmul_rn(term, x), __frcp_rn((float)N));
-                                cum = __fadd_rn(cum, term);
-                                if (U < cum) break;
-                            }
-                        }
+                        const uint32_t cls = ((bad >> t) & kbits) ? Q_CLASS_RANDOM : qcls_s[(codes >> (2 * t)) & codemask];
+                        hit = u16 < T1[cls];
                     }
-                    tq_.push(N > 0, i | ((uint32_t)(N - 1) << 28), 0u);
+                    tq_.push(hit, i, u16);
                     const uint32_t cnt = tq_.ready(false);
                     if (cnt) run_trials(cnt);
                 }
             }
             for (uint32_t cnt; (cnt = tq_.ready(true)) != 0;) run_trials(cnt);
             tm.sync();
+            const uint32_t ncand = W == 1 ? list_n : misc[MISC_LISTN];
             // histogram of candidate change times, high byte
-            for (uint32_t p = tm.rank; p < n; p += SIZE) {
-                uint32_t kv = key[p];
-                if (kv != KEY_UNTOUCHED && (kv >> 16) != 0) {
+            for_touched(ncand, [&](uint32_t p) {
+                const uint32_t kv = key[p];
+                if ((kv >> 16) != 0) {
                     uint32_t a, in;
                     slot_weights(kv & 0xFFFFu, frag[p], a, in);
                     hist_add<HistT>(hist, kv >> 24, a, in);
                 }
-            }
+            });
             tm.sync();
             if (tm.rank < 32) hist_scan_warp<HistT>(hist, misc, n, loss_c, ins_c, tq);
             tm.sync();
-            const uint32_t bin = misc[0], pa = misc[1], pi = misc[2], ta = misc[3], ti = misc[4];
-            if (bin < 256) {
+            const uint32_t hbin = misc[0], pa = misc[1], pi = misc[2], ta = misc[3], ti = misc[4];
+            if (hbin < 256) {
                 // refine inside the crossing bin on the low time byte
                 tm.sync();
                 for (uint32_t b = tm.rank; b < 256; b += SIZE) hist[b] = 0;
                 tm.sync();
-                for (uint32_t p = tm.rank; p < n; p += SIZE) {
-                    uint32_t kv = key[p];
-                    if (kv != KEY_UNTOUCHED && (kv >> 24) == bin && (kv >> 16) != 0) {
+                for_touched(ncand, [&](uint32_t p) {
+                    const uint32_t kv = key[p];
+                    if ((kv >> 24) == hbin && (kv >> 16) != 0) {
                         uint32_t a, in;
                         slot_weights(kv & 0xFFFFu, frag[p], a, in);
                         hist_add<HistT>(hist, (kv >> 16) & 255u, a, in);
                     }
-                }
+                });
                 tm.sync();
                 if (tm.rank < 32) hist_scan_warp<HistT>(hist, misc, n, loss_c + pa, ins_c + pi, tq);
                 tm.sync();
                 const uint32_t lo = misc[0];
-                const uint32_t tstar = (bin << 8) | (lo < 256 ? lo : 255u);
+                const uint32_t tstar = (hbin << 8) | (lo < 256 ? lo : 255u);
                 tm.sync();
                 // drop later candidates, total up the kept ones
                 uint32_t la = 0, li = 0;
-                for (uint32_t p = tm.rank; p < n; p += SIZE) {
-                    uint32_t kv = key[p];
-                    if (kv != KEY_UNTOUCHED && (kv >> 16) != 0) {
+                for_touched(ncand, [&](uint32_t p) {
+                    const uint32_t kv = key[p];
+                    if ((kv >> 16) != 0) {
                         if ((kv >> 16) > tstar) {
                             key[p] = KEY_UNTOUCHED;
                         } else {
@@ -608,20 +694,20 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
                             li += in;
                         }
                     }
-                }
+                });
                 loss_c += team_sum<W>(tm, la, wsum);
                 ins_c += team_sum<W>(tm, li, wsum);
                 break;
             }
             // no crossing in this epoch: commit every candidate and go on
             uint32_t cnt = 0;
-            for (uint32_t p = tm.rank; p < n; p += SIZE) {
-                uint32_t kv = key[p];
-                if (kv != KEY_UNTOUCHED && (kv >> 16) != 0) {
+            for_touched(ncand, [&](uint32_t p) {
+                const uint32_t kv = key[p];
+                if ((kv >> 16) != 0) {
                     key[p] = kv & 0xFFFFu;
                     cnt++;
                 }
-            }
+            });
             loss_c += ta;
             ins_c += ti;
             changed_c += team_sum<W>(tm, cnt, wsum);
@@ -636,12 +722,8 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
     }
     tm.sync();
 
-    // ---- 4. final slot contents: low half = content16 or 0xFFFF (unchanged); high half free for ops
-    for (uint32_t p = tm.rank; p < n; p += SIZE) {
-        uint32_t kv = key[p];
-        key[p] = kv == KEY_UNTOUCHED ? 0x0000FFFFu : (kv & 0xFFFFu);
-    }
-    tm.sync();
+    // ---- 4. slot contents are the low halves of the keys: content16, or 0xFFFF for an unchanged slot
+    //         (dropped candidates were reset); the high halves are free for the cigar ops from here on
     const uint16_t* key16 = (const uint16_t*)key;
     auto slot_len = [&](uint32_t p) -> uint32_t {
         uint32_t c = key16[2 * p];
@@ -660,33 +742,60 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
     for (uint32_t base = 0; base < n; base += 4 * SIZE) {
         const uint32_t p0 = base + 4 * tm.rank;
         uint32_t c[4], len[4], s = 0;
+        uint32_t fb4 = 0;
+        if (p0 < n) {
+            const uint4 kq4 = *(const uint4*)(key + p0);  // the key array is padded to a multiple of 4 slots
+            c[0] = kq4.x & 0xFFFFu;
+            c[1] = kq4.y & 0xFFFFu;
+            c[2] = kq4.z & 0xFFFFu;
+            c[3] = kq4.w & 0xFFFFu;
+            fb4 = fragw[p0 >> 2];
+        } else {
+            c[0] = c[1] = c[2] = c[3] = 0;
+        }
 #pragma unroll
         for (int t = 0; t < 4; t++) {
-            uint32_t p = p0 + t;
-            c[t] = p < n ? key16[2 * p] : 0u;
+            const uint32_t p = p0 + t;
             len[t] = p < n ? (c[t] == 0xFFFFu ? 1u : content_len(c[t])) : 0u;
             s += len[t];
         }
         uint32_t tot;
         uint32_t o = carry + team_excl_scan<W>(tm, s, wsum, tot);
         carry += tot;
+        // deleted slots right before this lane's first slot
+        uint32_t pend = 0;
+        if (p0 < n) {
+            for (uint32_t q = p0; q > 0 && pend < 15; q--) {
+                if (key16[2 * (q - 1)] >> CONTENT_LEN_SHIFT != 0) break;  // 0xFFFF and len >= 1 both stop
+                pend++;
+            }
+        }
 #pragma unroll
         for (int t = 0; t < 4; t++) {
             const uint32_t p = p0 + t;
-            if (p < n && len[t]) {
-                const uint32_t b = frag[p];
-                // deleted slots right before this one
-                uint32_t dc = 0;
-                for (uint32_t q = p; q > 0 && dc < 15; q--) {
-                    if (key16[2 * (q - 1)] >> CONTENT_LEN_SHIFT != 0) break;  // 0xFFFF and len >= 1 both stop
-                    dc++;
+            if (p < n) {
+                if (len[t] == 0) {
+                    pend = pend < 15 ? pend + 1 : 15;
+                    continue;
                 }
+                const uint32_t b = (fb4 >> (8 * t)) & 0xFFu;
+                const uint32_t dc = pend;
+                pend = 0;
                 const bool body = p >= k && p < n - k;
-                const uint32_t kind = c[t] == 0xFFFFu ? 3u : content_kind(c[t]);
+                if (c[t] == 0xFFFFu) {
+                    // unchanged slot: one '=' column
+                    if (body) {
+                        const uint32_t d = o - start_trim;
+                        if (d < scap) oseq[d] = code_ascii(b);
+                    }
+                    if (o < opcap) ops_put(keyb, o, OP_EQ | (dc << 2));
+                    o += 1;
+                    continue;
+                }
+                const uint32_t kind = content_kind(c[t]);
                 uint32_t eqpos = 0xFFu;  // index inside the slot that aligns to the original base
                 bool first_x = false;
-                if (kind == 3u) eqpos = 0;
-                else if (kind == 1u) eqpos = 0;
+                if (kind == 1u) eqpos = 0;
                 else if (kind == 2u) eqpos = 1;
                 else if (len[t] >= 2 && b < 4 && content_base(c[t], 0) == b) eqpos = 0;
                 else if (len[t] >= 2 && b < 4 && content_base(c[t], len[t] - 1) == b) eqpos = len[t] - 1;
@@ -694,8 +803,7 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
                 for (uint32_t u = 0; u < len[t]; u++) {
                     const uint32_t j = o + u;
                     uint32_t ch;
-                    if (kind == 3u) ch = code_ascii(b);
-                    else if (kind == 0u) ch = code_ascii(content_base(c[t], u));
+                    if (kind == 0u) ch = code_ascii(content_base(c[t], u));
                     else if (kind == 1u) ch = u == 0 ? code_ascii(b) : code_ascii(content_base(c[t], 0));
                     else ch = u == 0 ? code_ascii(content_base(c[t], 0)) : code_ascii(b);
                     if (body) {
@@ -721,17 +829,17 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
     }
     tm.sync();
 
-    // ---- 6. qscores for the read bases that survive trimming
+    // ---- 6. qscores for the read bases that survive trimming: 8 bases per Philox call
     if ((P.flags & RUN_QUAL) && !(status & (ST_OPS_OVERFLOW | ST_SCRATCH_OVERFLOW))) {
         uint8_t* oq = B.scr_qual + sbase;
         const int margin = (T.kq - 1) >> 1;
         const uint32_t jb = start_trim, je = Ttot - end_trim;
         WarpQueue sq{wq_a, wq_b, 0, 0};
         auto sample = [&](uint32_t off, uint32_t lg, uint32_t u, uint32_t j) {
-            const uint32_t col = lg ? (u >> (32 - lg)) : 0u;
-            const uint32_t e = T.q_alias[off + col];
-            const uint32_t fr = (uint32_t)(u << lg) >> 14;
-            const uint32_t q = fr < (e & 0x3FFFFu) ? ((e >> 18) & 127u) : (e >> 25);
+            const uint32_t col = lg ? (u >> (16 - lg)) : 0u;
+            const uint32_t e = __ldg(&T.q_alias[off + col]);
+            const uint32_t fr = (u << lg) & 0xFFFFu;
+            const uint32_t q = fr < (e & 0xFFFFu) ? ((e >> 16) & 127u) : ((e >> 23) & 127u);
             oq[j - jb] = (uint8_t)(q + 33);
         };
         // windows the direct tables do not cover: generic trim-and-retry lookup, 32 at a time
@@ -746,35 +854,33 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
             const QRow rw = T.q_rows[qscore_row(T, keyb, start, end)];
             sample(rw.off, rw.lg, u, j);
         };
-        const uint32_t qd0 = jb >> 2, qd1 = (je + 3) >> 2;  // quads [qd0, qd1)
-        const uint32_t nq_r = (qd1 - qd0 + 31u) & ~31u;
-        for (uint32_t it = tm.rank; it < nq_r; it += SIZE) {
-            const uint32_t qd = qd0 + it, j0 = 4 * qd;
-            const bool live = qd < qd1;
-            // 9-wide windows of j0..j0+3 read the ops of j0-4 .. j0+7
-            const bool fast = live && T.q_t9 && j0 >= 4 && j0 + 7 < Ttot;
+        const uint32_t g0 = jb >> 3, g1 = (je + 7) >> 3;  // groups of 8 read bases [g0, g1)
+        const uint32_t ng_r = (g1 - g0 + 31u) & ~31u;
+        for (uint32_t it = tm.rank; it < ng_r; it += SIZE) {
+            const uint32_t g = g0 + it, j0 = 8 * g;
+            const bool live = g < g1;
+            // 9-wide windows of j0..j0+7 read the ops of j0-4 .. j0+11
+            const bool fast = live && T.q_t9 && j0 >= 4 && j0 + 11 < Ttot;
             uint4 ur = make_uint4(0, 0, 0, 0);
-            uint32_t x0 = 0, x1 = 0, x2 = 0, opsP = 0, dmask = 0;
-            if (live) ur = philox4x32_10(qd, TAG_QUAL, olo, ohi, k0, k1);
+            uint32_t x0 = 0, x1 = 0, x2 = 0, x3 = 0, opsP = 0, dmask = 0;
+            if (live) ur = philox4x32_10(g, TAG_QUAL, olo, ohi, k0, k1);
             if (fast) {
                 const uint2* kp = (const uint2*)(key + ((j0 - 4) >> 1));
-                const uint2 a = kp[0], b = kp[1], c = kp[2];
+                const uint2 a = kp[0], b = kp[1], c = kp[2], d = kp[3];
                 x0 = __byte_perm(a.x, a.y, 0x7632);
                 x1 = __byte_perm(b.x, b.y, 0x7632);
                 x2 = __byte_perm(c.x, c.y, 0x7632);
-                auto pack2 = [](uint32_t x) {
-                    x &= 0x03030303u;
-                    x = (x | (x >> 6)) & 0x000F000Fu;
-                    return (x | (x >> 12)) & 0xFFu;
-                };
-                auto nz4 = [](uint32_t x) { return ((__vcmpne4(x & 0x3C3C3C3Cu, 0u) & 0x08040201u) * 0x01010101u) >> 24; };
-                opsP = pack2(x0) | (pack2(x1) << 8) | (pack2(x2) << 16);
-                dmask = nz4(x0) | (nz4(x1) << 4) | (nz4(x2) << 8);
+                x3 = __byte_perm(d.x, d.y, 0x7632);
+                opsP = pack4(x0) | (pack4(x1) << 8) | (pack4(x2) << 16) | (pack4(x3) << 24);
+                dmask = nz4(x0, 0x3C3C3C3Cu) | (nz4(x1, 0x3C3C3C3Cu) << 4) | (nz4(x2, 0x3C3C3C3Cu) << 8) |
+                        (nz4(x3, 0x3C3C3C3Cu) << 12);
             }
 #pragma unroll 1
-            for (uint32_t t = 0; t < 4; t++) {
+            for (uint32_t t = 0; t < 8; t++) {
                 const uint32_t j = j0 + t;
                 const bool want = live && j >= jb && j < je;
+                const uint32_t wsel = t < 4 ? (t < 2 ? ur.x : ur.y) : (t < 6 ? ur.z : ur.w);
+                const uint32_t u16 = (wsel >> (16 * (t & 1u))) & 0xFFFFu;
                 bool slow = want;
                 if (want && fast) {
                     const uint32_t ops18 = (opsP >> (2 * t)) & 0x3FFFFu;
@@ -782,20 +888,20 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
                     const uint32_t code3 = lut3[ops18 & 63u] + 27u * lut3[(ops18 >> 6) & 63u] + 729u * lut3[ops18 >> 12];
                     uint32_t ent = 0;
                     if (gm == 0) {
-                        ent = T.q_t9[code3];
+                        ent = __ldg(&T.q_t9[code3]);
                         slow = false;
                     } else if ((gm & (gm - 1)) == 0) {
-                        const uint32_t g = __ffs(gm) - 1, bi = t + 1 + g;
-                        const uint32_t w = bi < 4 ? x0 : bi < 8 ? x1 : x2;
+                        const uint32_t gpos = __ffs(gm) - 1, bi = t + 1 + gpos;
+                        const uint32_t w = bi < 4 ? x0 : bi < 8 ? x1 : bi < 12 ? x2 : x3;
                         const uint32_t dc = (w >> (8 * (bi & 3u) + 2)) & 15u;
                         if (dc <= 3) {
-                            ent = T.q_t9d1[code3 + 19683u * (3 * g + dc - 1)];
+                            ent = __ldg(&T.q_t9d1[code3 + 19683u * (3 * gpos + dc - 1)]);
                             slow = false;
                         }
                     }
-                    if (!slow) sample(ent >> 3, ent & 7u, word_of(ur, t), j);
+                    if (!slow) sample(ent >> 3, ent & 7u, u16, j);
                 }
-                sq.push(slow, j, word_of(ur, t));
+                sq.push(slow, j, u16);
                 const uint32_t cnt = sq.ready(false);
                 if (cnt) run_slow(cnt);
             }
@@ -806,34 +912,34 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
 }
 
 template <int W, bool GWS>
-__global__ void __launch_bounds__(512, 1) simulate_kernel(const SimParams P) {
+__global__ void __launch_bounds__(SIM_THREADS, 1) simulate_kernel(const SimParams P) {
     extern __shared__ __align__(16) uint8_t smem[];
-    constexpr int TEAMS = 16 / W;
+    constexpr int TEAMS = SIM_WARPS / W;
     Team<W> tm;
     tm.rank = threadIdx.x % (W * 32);
     tm.id = threadIdx.x / (W * 32);
-    // k-mer change probabilities staged in shared memory for the whole CTA, then a 64-entry
+    // k-mer change-probability classes staged in shared memory for the whole CTA, then a 64-entry
     // table turning three packed cigar ops into their base-3 code
     const uint32_t nq = P.T.has_err_table ? (1u << (2 * P.T.k)) : 0u;
-    uint16_t* q16s = (uint16_t*)smem;
-    for (uint32_t i = threadIdx.x; i < nq; i += blockDim.x) q16s[i] = P.T.q16[i];
-    const uint32_t q16_bytes = (nq * 2 + 15) & ~15u;
-    uint8_t* lut3 = smem + q16_bytes;
+    uint8_t* qcls_s = smem;
+    for (uint32_t i = threadIdx.x; i < nq; i += blockDim.x) qcls_s[i] = P.T.qcls[i];
+    const uint32_t qcls_bytes = (nq + 15) & ~15u;
+    uint8_t* lut3 = smem + qcls_bytes;
     if (threadIdx.x < 64) lut3[threadIdx.x] = (uint8_t)((threadIdx.x & 3) + 3 * ((threadIdx.x >> 2) & 3) + 9 * (threadIdx.x >> 4));
     __syncthreads();
     uint8_t* ws;
     if (GWS)
         ws = P.gws + (size_t)blockIdx.x * P.slab_bytes;
     else
-        ws = smem + q16_bytes + 64 + (size_t)tm.id * P.slab_bytes;
-    uint32_t* ticket = (uint32_t*)(smem + q16_bytes + 64 + (GWS ? 0 : (size_t)TEAMS * P.slab_bytes)) + tm.id;
+        ws = smem + qcls_bytes + 64 + (size_t)tm.id * P.slab_bytes;
+    uint32_t* ticket = (uint32_t*)(smem + qcls_bytes + 64 + (GWS ? 0 : (size_t)TEAMS * P.slab_bytes)) + tm.id;
     while (true) {
         if (tm.rank == 0) *ticket = atomicAdd(P.counter, 1u);
         tm.sync();
         const uint32_t wi = *ticket;
         tm.sync();
         if (wi >= P.n_work) break;
-        simulate_read<W, GWS>(tm, P, P.work[wi], ws, q16s, lut3);
+        simulate_read<W, GWS>(tm, P, P.work[wi], ws, qcls_s, lut3);
     }
 }
 

@@ -157,9 +157,54 @@ std::vector<AliasCol> build_alias(const std::vector<double>& p_in, int ncols, in
 
 }  // namespace
 
+// Groups the 4^k change probabilities into Q_CLASSES - 1 classes (1-D Lloyd iteration from a
+// quantile start; representative = class mean, so the total trial rate is preserved) so that the
+// arrival test of the kernels is two shared-memory look-ups: class of the k-mer, threshold of the
+// class.  Class 255 is reserved for k-mers that are not in the table (q = 1).
+static void build_q_classes(ErrorModelHost& em) {
+    em.qrep.assign(Q_CLASSES, 1.0);
+    if (!em.has_table) return;
+    const size_t rows = em.q16.size();
+    std::vector<std::pair<uint16_t, uint32_t>> order(rows);
+    for (size_t c = 0; c < rows; c++) order[c] = {em.q16[c], (uint32_t)c};
+    std::sort(order.begin(), order.end());
+    const int K = Q_CLASSES - 1;
+    std::vector<double> cent((size_t)K);
+    for (int c = 0; c < K; c++) cent[(size_t)c] = order[std::min(rows - 1, (size_t)((c + 0.5) * rows / K))].first;
+    std::vector<int> assign(rows, 0);
+    for (int it = 0; it < 40; it++) {
+        // sorted values: boundaries are the mid-points between consecutive centroids
+        std::sort(cent.begin(), cent.end());
+        int c = 0;
+        std::vector<double> sum((size_t)K, 0.0);
+        std::vector<size_t> cnt((size_t)K, 0);
+        for (size_t i = 0; i < rows; i++) {
+            double v = order[i].first;
+            while (c + 1 < K && std::fabs(cent[(size_t)c + 1] - v) <= std::fabs(cent[(size_t)c] - v)) c++;
+            assign[i] = c;
+            sum[(size_t)c] += v;
+            cnt[(size_t)c]++;
+        }
+        for (int j = 0; j < K; j++)
+            if (cnt[(size_t)j]) cent[(size_t)j] = sum[(size_t)j] / (double)cnt[(size_t)j];
+    }
+    em.qcls.assign(rows, 0);
+    std::vector<double> sum((size_t)K, 0.0);
+    std::vector<size_t> cnt((size_t)K, 0);
+    for (size_t i = 0; i < rows; i++) {
+        em.qcls[order[i].second] = (uint8_t)assign[i];
+        sum[(size_t)assign[i]] += order[i].first;
+        cnt[(size_t)assign[i]]++;
+    }
+    for (int j = 0; j < K; j++) em.qrep[(size_t)j] = cnt[(size_t)j] ? sum[(size_t)j] / (double)cnt[(size_t)j] / 65536.0 : 0.0;
+}
+
 ErrorModelHost load_error_model(const std::string& name_or_path, const std::map<std::string, std::string>& names) {
     ErrorModelHost em;
-    if (name_or_path == "random") return em;  // k = 1, every trial is a random change
+    if (name_or_path == "random") {  // k = 1, every trial is a random change
+        build_q_classes(em);
+        return em;
+    }
     std::string path = name_or_path;
     auto it = names.find(name_or_path);
     if (it != names.end()) path = it->second;
@@ -298,6 +343,7 @@ ErrorModelHost load_error_model(const std::string& name_or_path, const std::map<
     em.rate_loss = (s_loss + missing * 2.0 / 3.0) / (double)rows;
     em.rate_ins = (s_ins + missing / 3.0) / (double)rows;
     em.rate_slots = (s_slots + missing) / (double)rows;
+    build_q_classes(em);
     return em;
 }
 
@@ -343,12 +389,14 @@ QScoreModelHost pack_qscore_model(
         int lg = 0;
         while ((1u << lg) < p.size()) lg++;
         if (lg > 7) throw std::runtime_error("qscore model: more than 128 scores for " + cigar);
-        std::vector<AliasCol> cols = build_alias(p, 1 << lg, 18);
+        // one 16-bit uniform per read base: lg bits pick the column, 16 - lg bits are the fraction;
+        // thresholds are stored left-aligned in 16 bits
+        std::vector<AliasCol> cols = build_alias(p, 1 << lg, 16 - lg);
         uint32_t off = (uint32_t)qm.alias.size();
         for (auto& ac : cols) {
             uint32_t qa = ac.a < qs.size() ? qs[ac.a] : qs[ac.b];
             uint32_t qb = ac.b < qs.size() ? qs[ac.b] : qa;
-            qm.alias.push_back(ac.thr | (qa << 18) | (qb << 25));
+            qm.alias.push_back((ac.thr << lg) | (qa << 16) | (qb << 23));
         }
         // later duplicates override earlier ones, as dict assignment does
         auto it = row_of.find(cigar);
@@ -578,6 +626,23 @@ std::vector<float> make_delta_table(const ErrorModelHost& em) {
         double d = 1.3 * t + 0.02;
         tab[(size_t)b] = (float)std::min(d, 50.0);
     }
+    return tab;
+}
+
+std::vector<uint16_t> make_threshold_table(const ErrorModelHost& em, const std::vector<float>& delta) {
+    std::vector<uint16_t> tab((size_t)DELTA_TAB_BINS * Q_CLASSES * THR_PER_CLASS);
+    for (int b = 0; b < DELTA_TAB_BINS; b++)
+        for (int c = 0; c < Q_CLASSES; c++) {
+            const double x = em.qrep[(size_t)c] * (double)delta[(size_t)b];
+            double term = std::exp(-x), cum = 0.0;  // cum = P(N < m)
+            for (int m = 1; m <= THR_PER_CLASS; m++) {
+                cum += term;                         // P(N <= m - 1)
+                term *= x / (double)m;
+                double p = std::max(0.0, 1.0 - cum); // P(N >= m)
+                tab[((size_t)b * Q_CLASSES + (size_t)c) * THR_PER_CLASS + (size_t)(m - 1)] =
+                    (uint16_t)std::min(65535.0, std::floor(p * 65536.0 + 0.5));
+            }
+        }
     return tab;
 }
 

@@ -18,7 +18,9 @@ namespace tk {
 struct ErrorModelHost {
     int k = 1;
     bool has_table = false;
-    std::vector<uint16_t> q16;
+    std::vector<uint16_t> q16;       // 4^k exact change probabilities * 65536 (host side: tests, class building)
+    std::vector<uint8_t> qcls;       // 4^k change-probability class (device table)
+    std::vector<double> qrep;        // Q_CLASSES representative probabilities; [255] = 1 (k-mer not in the table)
     std::vector<uint32_t> alias;
     std::vector<uint64_t> alts;
     // model averages per trial over uniformly random k-mers (drive the epoch-length table)
@@ -64,6 +66,8 @@ QScoreModelHost load_qscore_model(const std::string& name_or_path,
 QScoreModelHost pack_qscore_model(const std::vector<std::pair<std::string, std::vector<std::pair<int, double>>>>& dists);
 IdentityHost make_identities(double mean_pct, double stdev_pct, double max_pct);
 std::vector<float> make_delta_table(const ErrorModelHost& em);
+// [DELTA_TAB_BINS][Q_CLASSES][THR_PER_CLASS] thresholds: P(Poisson(qrep[c] * delta[b]) >= m) * 65536, m = 1..8
+std::vector<uint16_t> make_threshold_table(const ErrorModelHost& em, const std::vector<float>& delta);
 
 // py/sequence.py:17-31 ($TKSM_MODELS lookup; first directory in the list wins on a clash)
 struct ModelNames {

@@ -108,6 +108,9 @@ class Sequencer:
             "q_rows": view(t.q_rows, 2 * t.n_q_rows, np.uint32),
             "q_alias": view(t.q_alias, t.n_q_alias, np.uint32),
             "seed": t.seed, "compute_qual": t.compute_qual,
+            "qcls": view(t.qcls, t.n_qcls, np.uint8),
+            "qrep": view(t.qrep, t.n_qrep, np.float64),
+            "thr": view(t.thr, t.n_thr, np.uint16),
         }
 
     # ---- mdf_generator + mdf_to_seq + formatter on host buffers (py/sequence.py:197-320)
