@@ -159,6 +159,7 @@ def main():
     barrier()
     e2e_t0 = time.perf_counter()
     e2e_bases = 0
+    out, e2e_stats = None, {"h2d_bytes": 0, "d2h_bytes": 0}
     for _ in range(args.e2e_steps):
         out = s.simulate(mdf, BADREAD, fastq=True, ordinal_base=ordinal_base)
         e2e_bases += s.last_stats["read_bases"]
@@ -191,7 +192,7 @@ def main():
             "data": "synthetic", "config": config,
             "reads_per_s": total_reads_step * args.steps / (dev_ms_max / 1e3),
             "clocks": clocks,
-            "e2e": {"value": total_e2e_bases / e2e_wall_max, "unit": "bases/s",
+            "e2e": {"value": total_e2e_bases / e2e_wall_max if args.e2e_steps else None, "unit": "bases/s",
                     "h2d_bytes_per_step": e2e_stats["h2d_bytes"] + len(mdf) * 0,
                     "d2h_bytes_per_step": e2e_stats["d2h_bytes"],
                     "note": "MDF text parse (host) + H2D + kernels + D2H of the FASTQ bytes, per step"},
