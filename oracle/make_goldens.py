@@ -249,16 +249,34 @@ def make_dist(which=None):
     for name, c in configs.items():
         if which and name not in which:
             continue
+        # The reference draws read identities from numpy's global RandomState, which fork() copies
+        # into every Pool worker unchanged (py/sequence.py:363-365, py/tksm_badread.py:741-745): with
+        # `-t N` the N workers replay the same identity sequence.  Independent samples need `-t 1`,
+        # so the MDF is cut into chunks that separate single-threaded reference processes simulate.
+        recs = mdf.split("\n+")
+        recs = [recs[0]] + ["+" + r for r in recs[1:]]
+        nproc = max(1, min(os.cpu_count() or 1, 8))
+        per = (len(recs) + nproc - 1) // nproc
         with tempfile.TemporaryDirectory() as td:
             open(os.path.join(td, "g.fa"), "w").write(fasta)
             open(os.path.join(td, "in.mdf"), "w").write(mdf)
-            args = ["-i", "in.mdf", "-r", "g.fa", "-o", "out.fastq", "-t", str(os.cpu_count() or 1),
-                    "--badread-identity", c["ident"], "--badread-error-model", c["em"],
-                    "--badread-qscore-model", c["qm"]]
-            p = run_reference(args, td)
-            if p.returncode != 0:
-                raise SystemExit(f"reference failed on dist/{name}: {p.stderr[-3000:]}")
-            fq = open(os.path.join(td, "out.fastq"), "rb").read()
+            procs = []
+            for w in range(nproc):
+                part = recs[w * per:(w + 1) * per]
+                if not part:
+                    continue
+                open(os.path.join(td, f"in{w}.mdf"), "w").write("\n".join(x.rstrip("\n") for x in part) + "\n")
+                cmd = [sys.executable, os.path.join(REF, "py", "sequence.py"), "-i", f"in{w}.mdf", "-r", "g.fa",
+                       "-o", f"out{w}.fastq", "-t", "1", "--badread-identity", c["ident"],
+                       "--badread-error-model", c["em"], "--badread-qscore-model", c["qm"]]
+                procs.append((w, subprocess.Popen(cmd, cwd=td, env=ref_env(), stdout=subprocess.PIPE,
+                                                  stderr=subprocess.PIPE, text=True)))
+            fq = b""
+            for w, p in procs:
+                _, err = p.communicate()
+                if p.returncode != 0:
+                    raise SystemExit(f"reference failed on dist/{name}: {err[-3000:]}")
+                fq += open(os.path.join(td, f"out{w}.fastq"), "rb").read()
             p2 = run_reference(["-i", "in.mdf", "-r", "g.fa", "--perfect", "perf.fasta"], td)
             assert p2.returncode == 0
             perf = open(os.path.join(td, "perf.fasta"), "rb").read()
