@@ -38,7 +38,8 @@ typedef struct tksm_seq_config {
     double identity_max;
     double identity_stdev;
     int skip_qual_compute;    /* --skip-qual-compute */
-    double corr0, corr1;      /* identity calibration, NaN => built-in default for the model */
+    double calib_overshoot;  /* identity calibration: reference overshoot in errors per read, */
+    double calib_kappa;      /* alignment explain-away coefficient; NaN => built-in default for the model */
     uint64_t batch_reads;     /* streaming batch limits, 0 => defaults */
     uint64_t batch_bases;
     int host_only;            /* 1 => no device (table packing / parsing only; run calls fail) */
@@ -72,7 +73,7 @@ typedef struct tksm_seq_tables {
     int ident_const; float ident_mean;
     const float* ident_tab; size_t n_ident_tab;
     const float* delta_tab; size_t n_delta_tab;
-    float corr0, corr1;
+    float calib_overshoot, calib_kappa;
     int kq;
     const uint32_t* q_direct; size_t n_q_direct; uint32_t q_direct_off[5];
     const uint64_t* q_hash; size_t n_q_hash;      /* entries of 2 x u64: key, row */

@@ -67,6 +67,7 @@ def summarise(fastq_bytes, perfect_bytes, max_reads=None):
         reads = reads[:max_reads]
     E, X, I, D = ord("="), ord("X"), ord("I"), ord("D")
     len_ratio, identity, hdr_identity, sub, ins, dele, meanq, rawlen = [], [], [], [], [], [], [], []
+    hp_err, hp_del, mq_cls = [], [], [[], [], []]   # per read: the unit the samples are independent in
     hp = np.zeros((HP_MAX + 1, HP_OBS), np.int64)
     qh = np.zeros((3, 3, 94), np.int64)           # [position class][op class =,X,I][q]
     ins_len = np.zeros(12, np.int64)
@@ -101,6 +102,9 @@ def summarise(fastq_bytes, perfect_bytes, max_reads=None):
         pos[:POS_EDGE] = 0
         pos[max(len(q) - POS_EDGE, 0):] = 2
         np.add.at(qh, (pos, cls, np.clip(q, 0, 93)), 1)
+        for oc in range(3):
+            sel = q[cls == oc]
+            mq_cls[oc].append(float(sel.mean()) if len(sel) else -1.0)
         # homopolymer spectrum: per run of the molecule, count read bases of the run's base inside its columns
         rawa = np.frombuffer(raw, np.uint8)
         seqa = np.frombuffer(seq, np.uint8)
@@ -110,6 +114,7 @@ def summarise(fastq_bytes, perfect_bytes, max_reads=None):
         starts = np.concatenate(([0], bnd))
         ends = np.concatenate((bnd, [L]))
         colbase = np.where(ops != D, seqa[np.clip(qidx, 0, len(seqa) - 1)], 0)
+        n_hp = n_hp_err = n_hp_del = 0
         for a, b in zip(starts, ends):
             rl = b - a
             if rl < 3:
@@ -123,6 +128,11 @@ def summarise(fastq_bytes, perfect_bytes, max_reads=None):
                 c1 += 1
             obs = int((colbase[c0:c1 + 1] == rawa[a]).sum())
             hp[min(rl, HP_MAX), min(obs, HP_OBS - 1)] += 1
+            n_hp += 1
+            n_hp_err += obs != rl
+            n_hp_del += obs < rl
+        hp_err.append(n_hp_err / n_hp if n_hp else -1.0)
+        hp_del.append(n_hp_del / n_hp if n_hp else -1.0)
     n_cols = int(tot.sum())
     n_raw = int(tot[0] + tot[1] + tot[3])
     return {
@@ -132,6 +142,7 @@ def summarise(fastq_bytes, perfect_bytes, max_reads=None):
         "identity": identity,
         "hdr_identity": hdr_identity,
         "sub_rate": sub, "ins_rate": ins, "del_rate": dele, "mean_q": meanq,
+        "hp_err": hp_err, "hp_del": hp_del, "mean_q_eq": mq_cls[0], "mean_q_x": mq_cls[1], "mean_q_i": mq_cls[2],
         "rates": {"X": tot[1] / n_raw, "I": tot[2] / n_raw, "D": tot[3] / n_raw, "identity": tot[0] / n_cols},
         "hp": hp.tolist(), "qhist": qh.tolist(), "ins_len": ins_len.tolist(), "del_len": del_len.tolist(),
     }

@@ -16,8 +16,8 @@ class Config(C.Structure):
         ("identity_max", C.c_double),
         ("identity_stdev", C.c_double),
         ("skip_qual_compute", C.c_int),
-        ("corr0", C.c_double),
-        ("corr1", C.c_double),
+        ("calib_overshoot", C.c_double),
+        ("calib_kappa", C.c_double),
         ("batch_reads", C.c_uint64),
         ("batch_bases", C.c_uint64),
         ("host_only", C.c_int),
@@ -56,7 +56,7 @@ class Tables(C.Structure):
         ("ident_const", C.c_int), ("ident_mean", C.c_float),
         ("ident_tab", C.POINTER(C.c_float)), ("n_ident_tab", C.c_size_t),
         ("delta_tab", C.POINTER(C.c_float)), ("n_delta_tab", C.c_size_t),
-        ("corr0", C.c_float), ("corr1", C.c_float),
+        ("calib_overshoot", C.c_float), ("calib_kappa", C.c_float),
         ("kq", C.c_int),
         ("q_direct", C.POINTER(C.c_uint32)), ("n_q_direct", C.c_size_t), ("q_direct_off", C.c_uint32 * 5),
         ("q_hash", C.POINTER(C.c_uint64)), ("n_q_hash", C.c_size_t),

@@ -75,7 +75,7 @@ struct DevTables {
     float ident_mean;
     const float* ident_tab;       // IDENT_TAB_BINS + 1 quantiles (already times max identity)
     const float* delta_tab;       // DELTA_TAB_BINS epoch lengths over target in [0.5, 1]
-    float corr0, corr1;           // effective target = target + corr0 + corr1 * (1 - target)
+    float calib_overshoot, calib_kappa;           // effective target: 1 - g, g - kappa g^2 = (1 - target) + overshoot / n
     // qscore model
     int kq;                       // odd, <= 9
     const uint32_t* q_direct;     // concatenated direct maps for widths 1,3,5,7,9 (3^w entries each)

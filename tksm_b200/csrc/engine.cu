@@ -123,7 +123,7 @@ struct tksm_seq {
     QScoreModelHost qm;
     IdentityHost idh;
     std::vector<float> delta;
-    float corr0 = 0, corr1 = 0;
+    float calib_overshoot = 0, calib_kappa = 0;
     bool models_loaded = false;
     // device
     cudaStream_t stream = nullptr;
@@ -228,8 +228,8 @@ void upload_models(tksm_seq* h) {
     T.ident_mean = h->idh.mean;
     T.ident_tab = h->d_ident.as<float>();
     T.delta_tab = h->d_delta.as<float>();
-    T.corr0 = h->corr0;
-    T.corr1 = h->corr1;
+    T.calib_overshoot = h->calib_overshoot;
+    T.calib_kappa = h->calib_kappa;
     T.kq = h->qm.kq;
     T.q_direct = h->d_qdirect.as<uint32_t>();
     for (int i = 0; i < 5; i++) T.q_direct_off[i] = h->qm.direct_off[i];
@@ -481,6 +481,7 @@ void batch_run(tksm_seq* h, tksm_seq_batch* b, int which, int format, tksm_seq_s
             F.qual = nullptr;
         }
         F.fastq = fastq_o[o];
+        F.kappa = (double)h->calib_kappa;
         F.rec_len = b->rec_len[o].as<uint32_t>();
         F.rec_off = b->rec_off[o].as<uint64_t>();
         F.out = b->out[o].as<uint8_t>();
@@ -549,8 +550,8 @@ void tksm_seq_default_config(tksm_seq_config* c) {
     c->identity_max = 99.0;
     c->identity_stdev = 5.5;
     c->skip_qual_compute = 0;
-    c->corr0 = NAN;
-    c->corr1 = NAN;
+    c->calib_overshoot = NAN;
+    c->calib_kappa = NAN;
     c->batch_reads = 0;
     c->batch_bases = 0;
     c->host_only = 0;
@@ -717,8 +718,20 @@ int tksm_seq_load_models(tksm_seq* h, const char* error_model, const char* qscor
     h->qm = load_qscore_model(qm, names.qscore);
     h->delta = make_delta_table(h->em);
     h->thr = make_threshold_table(h->em, h->delta);
-    h->corr0 = std::isnan(h->cfg.corr0) ? 0.0f : (float)h->cfg.corr0;
-    h->corr1 = std::isnan(h->cfg.corr1) ? 0.0f : (float)h->cfg.corr1;
+    // alignment explain-away coefficient of the PB1 edit statistics per error model
+    // (oracle/fit_calibration.py measures it with the CPU twin) and the reference's mean overshoot
+    // in errors for fragments it re-aligns whole (py/tksm_badread.py:408-413)
+    {
+        std::string base = em.substr(em.find_last_of('/') == std::string::npos ? 0 : em.find_last_of('/') + 1);
+        base = base.substr(0, base.find('.'));
+        double kappa = 0.45;
+        if (base == "nanopore2020") kappa = 0.43;
+        else if (base == "nanopore2018") kappa = 0.40;
+        else if (base == "pacbio2016") kappa = 0.58;
+        else if (base == "random") kappa = 0.44;
+        h->calib_overshoot = std::isnan(h->cfg.calib_overshoot) ? 0.8f : (float)h->cfg.calib_overshoot;
+        h->calib_kappa = std::isnan(h->cfg.calib_kappa) ? (float)kappa : (float)h->cfg.calib_kappa;
+    }
     compute_classes(h);
     upload_models(h);
     h->models_loaded = true;
@@ -743,8 +756,8 @@ int tksm_seq_get_tables(tksm_seq* h, tksm_seq_tables* t) {
     t->n_ident_tab = h->idh.tab.size();
     t->delta_tab = h->delta.data();
     t->n_delta_tab = h->delta.size();
-    t->corr0 = h->corr0;
-    t->corr1 = h->corr1;
+    t->calib_overshoot = h->calib_overshoot;
+    t->calib_kappa = h->calib_kappa;
     t->kq = h->qm.kq;
     t->q_direct = h->qm.direct.data();
     t->n_q_direct = h->qm.direct.size();

@@ -471,7 +471,22 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
         float a = T.ident_tab[idx], b = T.ident_tab[idx + 1];
         target = __fmaf_rn(f, __fsub_rn(b, a), a);
     }
-    float teff = __fadd_rn(target, __fmaf_rn(T.corr1, __fsub_rn(1.0f, target), T.corr0));
+    // generative error g with g - kappa g^2 = (1 - target) + overshoot / n
+    float teff;
+    {
+        float a = __fsub_rn(1.0f, target);
+        if (n <= 1000) {  // py/tksm_badread.py:408; the overshoot grows with the error level up to 10 %
+            float s = __fmul_rn(a, 10.0f);
+            if (s > 1.0f) s = 1.0f;
+            a = __fadd_rn(a, __fdiv_rn(__fmul_rn(T.calib_overshoot, s), (float)n));
+        }
+        if (T.calib_kappa > 0.0f) {
+            float x = __fsub_rn(1.0f, __fmul_rn(__fmul_rn(4.0f, T.calib_kappa), a));
+            if (!(x > 0.0f)) x = 0.0f;
+            teff = __fsub_rn(1.0f, __fdiv_rn(__fsub_rn(1.0f, __fsqrt_rn(x)), __fmul_rn(2.0f, T.calib_kappa)));
+        } else
+            teff = __fsub_rn(1.0f, a);
+    }
     uint32_t tq;
     if (!(teff > 0.0f))
         tq = 0;
@@ -959,6 +974,7 @@ struct FmtParams {
     const uint64_t* seq_off;
     const uint8_t* qual;          // nullptr => 'K' * len
     uint32_t fastq;               // 1 FASTQ, 0 FASTA
+    double kappa;                 // identity calibration (header text)
     uint32_t* rec_len;
     const uint64_t* rec_off;
     uint8_t* out;
@@ -975,8 +991,12 @@ __device__ __forceinline__ uint32_t dec_digits(uint32_t v) {
 
 // round-half-even of (num / den * 100.0) * 100 computed on the exact binary value of the double,
 // i.e. the digits Python's f"{x * 100.0:.2f}" prints (py/sequence.py:255)
-__device__ __forceinline__ uint32_t pct_hundredths(uint32_t num, uint32_t den) {
-    double y = __dmul_rn(__ddiv_rn((double)num, (double)den), 100.0);
+// The identity printed is the aligned identity the generative one corresponds to:
+// a = g - kappa g^2 with g = 1 - num / den.
+__device__ __forceinline__ uint32_t pct_hundredths(uint32_t num, uint32_t den, double kappa) {
+    const double g = __dsub_rn(1.0, __ddiv_rn((double)num, (double)den));
+    const double a = __dsub_rn(g, __dmul_rn(__dmul_rn(kappa, g), g));
+    double y = __dmul_rn(__dsub_rn(1.0, a), 100.0);
     uint64_t bits = (uint64_t)__double_as_longlong(y);
     int ex = (int)((bits >> 52) & 0x7FF);
     if (ex == 0) return 0;
@@ -996,7 +1016,7 @@ __device__ __forceinline__ uint32_t record_len(const FmtParams& F, uint32_t r) {
     const uint32_t mol = F.read_mol[r];
     const uint32_t L = F.mol_raw_len[mol];
     const uint32_t Lp = F.read_len ? F.read_len[r] : L;
-    const uint32_t h = F.read_len ? pct_hundredths(F.ident_num[r], F.ident_den[r]) : 10000u;
+    const uint32_t h = F.read_len ? pct_hundredths(F.ident_num[r], F.ident_den[r], F.kappa) : 10000u;
     const uint32_t idl = F.mol_id_begin[mol + 1] - F.mol_id_begin[mol];
     // "@" uuid " length=" Lp " error_free_length=" L " read_identity=" pct "% molecule_id=" id "\n" seq "\n"
     uint32_t len = 1 + 36 + 8 + dec_digits(Lp) + 19 + dec_digits(L) + 15 + pct_len(h) + 14 + idl + 1 + Lp + 1;
@@ -1120,7 +1140,7 @@ __global__ void __launch_bounds__(256) format_kernel(const FmtParams F) {
             puts_(" error_free_length=");
             putu(L);
             puts_(" read_identity=");
-            uint32_t h = F.read_len ? pct_hundredths(F.ident_num[r], F.ident_den[r]) : 10000u;
+            uint32_t h = F.read_len ? pct_hundredths(F.ident_num[r], F.ident_den[r], F.kappa) : 10000u;
             putu(h / 100);
             hdr[p++] = '.';
             hdr[p++] = (uint8_t)('0' + (h / 10) % 10);

@@ -38,7 +38,7 @@ class Sequencer:
         cfg.batch_reads = batch_reads
         cfg.batch_bases = batch_bases
         if corr is not None:
-            cfg.corr0, cfg.corr1 = corr
+            cfg.calib_overshoot, cfg.calib_kappa = corr
         self._h = self._L.tksm_seq_create(C.byref(cfg))
         if not self._h:
             raise SeqError(self._L.tksm_seq_last_error(None).decode())
@@ -100,7 +100,7 @@ class Sequencer:
             "ident_const": t.ident_const, "ident_mean": t.ident_mean,
             "ident_tab": view(t.ident_tab, t.n_ident_tab, np.float32),
             "delta_tab": view(t.delta_tab, t.n_delta_tab, np.float32),
-            "corr0": t.corr0, "corr1": t.corr1, "kq": t.kq,
+            "calib_overshoot": t.calib_overshoot, "calib_kappa": t.calib_kappa, "kq": t.kq,
             "q_direct": view(t.q_direct, t.n_q_direct, np.uint32),
             "q_direct_off": list(t.q_direct_off),
             "q_hash": view(t.q_hash, 2 * t.n_q_hash, np.uint64),
