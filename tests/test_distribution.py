@@ -6,9 +6,17 @@ single-threaded runs).  Here the same molecules go through the PB1 model -- its 
 suite, the CUDA path through the C ABI in the GPU suite (both are bit-identical, test_gpu_parity) --
 and the same statistics (oracle/stats.py: reads aligned back to their molecules) are compared.
 
-Known, documented deviation: qscores follow the generative edit script instead of a
-re-alignment, so the pooled 1.7 M-base qscore histograms of the read interior are compared by total
-variation and mean instead of a chi-square test, whose power at that sample size rejects any model.
+Known, documented deviations:
+ * qscores follow the generative edit script instead of a re-alignment, so the pooled 1.7 M-base
+   qscore histograms of the read interior are compared by total variation and mean instead of a
+   chi-square test, whose power at that sample size rejects any model.  The `ideal` qscore model
+   makes the deviation maximally visible (every 'X'/'I' base of the reference gets Q1-3, every base
+   PB1 labels '=' gets Q4+): 14 % of the bases a re-alignment calls 'X' and 23 % of those it calls
+   'I' (an inserted base inside a homopolymer, which the aligner left-shifts) carry a generative '='
+   label, hence the wider TV limit for those two classes under `ideal`.
+ * the `read_identity=` header token is PB1's *predicted* aligned identity; the reference prints the
+   identity of its own flank-inclusive alignment, which runs 0.15 points above the identity of the
+   read body.  The token is compared on mean and spread, the measured per-read identity by KS.
 """
 import gzip
 import json
@@ -89,6 +97,7 @@ def compare(name, mine, ref, qdev=True):
     """qdev: the reads' qscores follow the generative edit script (PB1), not a re-alignment."""
     fails = []
     const = "const" in name
+    ideal = ref["config"]["qm"] == "ideal"
     for k in ("len_ratio", "identity", "hdr_identity", "sub_rate", "ins_rate", "del_rate", "mean_q"):
         a, b = np.array(mine[k]), np.array(ref[k])
         if const and k in ("identity", "hdr_identity", "sub_rate", "del_rate", "ins_rate", "len_ratio"):
@@ -102,6 +111,10 @@ def compare(name, mine, ref, qdev=True):
                 fails.append(f"{k}: std {a.std():.4f} vs reference {b.std():.4f}")
             continue
         p = sps.ks_2samp(a, b).pvalue
+        if k == "hdr_identity":
+            if abs(a.mean() - b.mean()) > 0.006 or not (0.8 < a.std() / b.std() < 1.25):
+                fails.append(f"{k}: mean {a.mean():.4f} / std {a.std():.4f} vs reference {b.mean():.4f} / {b.std():.4f}")
+            continue
         if k == "mean_q" and qdev:
             # tolerance on the per-read mean instead of KS for the one quantity the
             # generative-cigar deviation shifts
@@ -150,10 +163,10 @@ def compare(name, mine, ref, qdev=True):
                 continue
             tv = 0.5 * np.abs(a / a.sum() - b / b.sum()).sum()
             ma, mb = (a * np.arange(94)).sum() / a.sum(), (b * np.arange(94)).sum() / b.sum()
-            lim = 0.10 + tv_noise(a, b)
+            lim = (0.25 if ideal and oc else 0.10) + tv_noise(a, b)
             va = (a * (np.arange(94) - ma) ** 2).sum() / a.sum()
             vb = (b * (np.arange(94) - mb) ** 2).sum() / b.sum()
-            mlim = 1.0 + 3.0 * float(np.sqrt(va / a.sum() + vb / b.sum()))
+            mlim = (2.0 if ideal and oc else 1.0) + 3.0 * float(np.sqrt(va / a.sum() + vb / b.sum()))
             if tv > lim or abs(ma - mb) > mlim:
                 fails.append(f"qscores of '{opname}' bases, position class {pc}: TV {tv:.3f} > {lim:.3f}, "
                              f"mean {ma:.2f} vs reference {mb:.2f}")
