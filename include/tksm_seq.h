@@ -43,6 +43,7 @@ typedef struct tksm_seq_config {
     uint64_t batch_reads;     /* streaming batch limits, 0 => defaults */
     uint64_t batch_bases;
     int host_only;            /* 1 => no device (table packing / parsing only; run calls fail) */
+    int threads;              /* -t/--threads: host threads parsing MDF chunks; 0 => all hardware threads (max 32) */
 } tksm_seq_config;
 
 /* which outputs a run produces */

@@ -199,3 +199,39 @@ def test_device_batch_rerun_is_deterministic_and_ordinal_keyed(world):
     na = len(so.parse_mdf(a))
     out_split = s.simulate(a, BADREAD, True, 0) + s.simulate(c, BADREAD, True, na)
     assert out_split == out1
+
+
+def test_streaming_pipeline_is_chunking_invariant(world, tmp_path, monkeypatch):
+    """The pipelined path (host parser threads -> upload -> kernels -> download, three device slots)
+    must produce the bytes of a single device batch whatever the text chunk size, the device chunk
+    size (batch_reads) or the sink (host buffer, plain file, .gz file)."""
+    import gzip
+    from tksm_b200.sequence import BADREAD, FASTQ, PERFECT
+    s = world["Sequencer"](seed=99)
+    s.add_reference_text(world["fasta"])
+    s.load_models("random", "random")
+    mdf = s.synth_mdf(1, 3000, seed=21) + handmade_mdf().encode()
+    b = s.batch(mdf)
+    b.run(BADREAD | PERFECT, FASTQ)
+    want, want_perf = b.fetch(BADREAD), b.fetch(PERFECT)
+    assert s.simulate(mdf, BADREAD, True) == want
+    for chunk_bytes, batch_reads in ((4096, 0), (50_000, 37), (1, 0)):
+        monkeypatch.setenv("TKSM_SEQ_CHUNK_BYTES", str(chunk_bytes))
+        s2 = world["Sequencer"](seed=99, batch_reads=batch_reads)
+        s2.add_reference_text(world["fasta"])
+        s2.load_models("random", "random")
+        assert s2.simulate(mdf, BADREAD, True) == want
+        assert s2.simulate(mdf, PERFECT, True) == want_perf
+        with s2.simulate_view(mdf, BADREAD, True) as rb:
+            assert rb.tobytes() == want
+        assert s2.last_stats["reads"] == len(so.parse_mdf(mdf))
+        src = tmp_path / "in.mdf"
+        src.write_bytes(mdf)
+        s2.run_files(str(src), badread=str(tmp_path / "o.fastq"), perfect=str(tmp_path / "p.fq.gz"))
+        assert (tmp_path / "o.fastq").read_bytes() == want
+        assert gzip.open(tmp_path / "p.fq.gz").read() == want_perf
+    monkeypatch.delenv("TKSM_SEQ_CHUNK_BYTES")
+    # an input error surfaces as an error of the call, after which the handle keeps working
+    with pytest.raises(Exception):
+        s.simulate(mdf + b"chr1\t0\t5\n", BADREAD, True)
+    assert s.simulate(mdf, BADREAD, True) == want

@@ -21,6 +21,7 @@ class Config(C.Structure):
         ("batch_reads", C.c_uint64),
         ("batch_bases", C.c_uint64),
         ("host_only", C.c_int),
+        ("threads", C.c_int),
     ]
 
 

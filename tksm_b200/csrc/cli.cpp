@@ -1,5 +1,6 @@
 // `tksm sequence` command line: same flags, defaults, messages and exit codes as the argparse
 // front-end of the reference (py/sequence.py:34-165), in front of the C ABI.
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -61,6 +62,7 @@ extern "C" int tksm_sequence_main(int argc, char** argv) {
     std::string input, badread, perfect, identity = "84.0,99.0,5.5", err_model, qs_model, tail_model, out_fmt;
     std::vector<std::string> refs;
     bool have_err = false, have_qs = false, have_tail = false, skip_qual = false, have_input = false;
+    long threads = 1;
     long long seed = 42;
     int device = 0;
     for (int a = 1; a < argc; a++) {
@@ -146,7 +148,7 @@ extern "C" int tksm_sequence_main(int argc, char** argv) {
             out_fmt = vals[0];  // parsed and never used, like the reference
         } else if (d == "threads") {
             char* e = nullptr;
-            strtol(vals[0].c_str(), &e, 10);
+            threads = strtol(vals[0].c_str(), &e, 10);
             if (*e) return usage_error("argument -t/--threads: invalid int value: '" + vals[0] + "'");
         } else if (d == "badread_identity") {
             identity = vals[0];
@@ -224,6 +226,7 @@ extern "C" int tksm_sequence_main(int argc, char** argv) {
     cfg.identity_max = mx;
     cfg.identity_stdev = sd;
     cfg.skip_qual_compute = skip_qual;
+    cfg.threads = threads > 0 ? (int)std::min<long>(threads, 256) : 1;  // -t: host parser threads (default 1)
     tksm_seq* h = tksm_seq_create(&cfg);
     if (!h) return die(std::string("Error: ") + tksm_seq_last_error(nullptr));
     int rc = 0;

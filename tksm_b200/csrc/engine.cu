@@ -4,6 +4,12 @@
 #include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <condition_variable>
+#include <deque>
+#include <functional>
+#include <future>
+#include <mutex>
+#include <thread>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -91,25 +97,54 @@ inline uint32_t list_capacity(uint32_t ncap) { return ncap / 5 * 2 + 64; }
 
 }  // namespace
 
-struct tksm_seq_batch {
+// One parsed MDF chunk with everything the device needs, built by host threads only
+// (no CUDA call): scratch layout, length-class work lists and the upload blob.
+struct Prepared {
     HostBatch hb;
-    // device copies
-    DBuf blob;
-    DevBatch db{};
     std::vector<uint64_t> scr_off, raw_off;
     std::vector<uint32_t> work[N_CLASSES];
-    uint32_t* d_work[N_CLASSES] = {};
     uint32_t max_n_gws = 0;
+    uint64_t alg_in_bytes = 0, idsum = 0;
+    bool mods = false;
+    std::unique_ptr<char[]> blob;
+    size_t blob_bytes = 0;
+    size_t o_read_mol = 0, o_msb = 0, o_mrl = 0, o_mib = 0, o_src = 0, o_len = 0, o_smb = 0, o_mp = 0, o_mc = 0, o_lit = 0,
+           o_id = 0, o_so = 0, o_ro = 0, o_work[N_CLASSES] = {};
+};
+
+// A device slot: the buffers of one chunk in flight.  The same object backs the device-resident
+// batch of the C ABI (tksm_seq_batch_create / _run / _fetch).
+struct tksm_seq_batch {
+    Prepared prep;
+    DBuf blob;
+    DevBatch db{};
+    uint32_t* d_work[N_CLASSES] = {};
     DBuf scr_seq, scr_qual, scr_raw, per_read, out[2], rec_len[2], rec_off[2], sums, gws, counters;
+    HBuf stage;           // pinned upload staging
+    HBuf host_out[2];     // pinned download staging (streaming to files)
+    HBuf h_tot;           // pinned: record bytes per output, read bases, status
+    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // kernels begin, simulate end, kernels end, downloads end, totals on host
     uint64_t out_bytes[2] = {0, 0};
     uint64_t out_cap[2] = {0, 0};
-    uint64_t alg_in_bytes = 0;
-    bool uploaded = false;
+    uint32_t launches = 0;
+    int which = 0;
+    bool bound = false;
+    bool d2h_pending = false;
     size_t h2d_bytes = 0;
+    void ensure_events() {
+        for (auto& e : ev)
+            if (!e) CK(cudaEventCreate(&e));
+    }
     ~tksm_seq_batch() {
         for (DBuf* d : {&blob, &scr_seq, &scr_qual, &scr_raw, &per_read, &out[0], &out[1], &rec_len[0], &rec_len[1],
                         &rec_off[0], &rec_off[1], &sums, &gws, &counters})
             d->release();
+        stage.release();
+        host_out[0].release();
+        host_out[1].release();
+        h_tot.release();
+        for (auto& e : ev)
+            if (e) cudaEventDestroy(e);
     }
 };
 
@@ -126,13 +161,13 @@ struct tksm_seq {
     float calib_overshoot = 0, calib_kappa = 0;
     bool models_loaded = false;
     // device
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaStream_t stream = nullptr;       // uploads + kernels
+    cudaStream_t copy_stream = nullptr;  // record downloads, overlapped with the next chunk's kernels
+    std::vector<std::unique_ptr<tksm_seq_batch>> slots;  // streaming pipeline (engine_stream)
     int num_sms = 148;
     DBuf d_genome, d_exc_start, d_exc_len, d_exc_chr;
     DBuf d_qcls, d_thr, d_alias, d_alts, d_ident, d_delta, d_qdirect, d_qhash, d_qrows, d_qalias, d_t9, d_t9d1;
     DevTables dt{};
-    HBuf stage, stage_out;
     uint32_t ncap[N_CLASSES] = {};
     uint32_t cap_list[N_CLASSES] = {};
     uint32_t slab[N_CLASSES] = {};
@@ -144,10 +179,8 @@ struct tksm_seq {
         for (DBuf* d : {&d_genome, &d_exc_start, &d_exc_len, &d_exc_chr, &d_qcls, &d_thr, &d_alias, &d_alts, &d_ident, &d_delta,
                         &d_qdirect, &d_qhash, &d_qrows, &d_qalias, &d_t9, &d_t9d1})
             d->release();
-        stage.release();
-        stage_out.release();
-        for (auto& e : ev)
-            if (e) cudaEventDestroy(e);
+        slots.clear();
+        if (copy_stream) cudaStreamDestroy(copy_stream);
         if (stream) cudaStreamDestroy(stream);
     }
 };
@@ -254,41 +287,48 @@ void launch_sim(tksm_seq* h, const SimParams& P, size_t smem, int grid) {
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-// builds the upload blob and per-read scratch layout; uploads once
-void batch_upload(tksm_seq* h, tksm_seq_batch* b) {
-    if (b->uploaded) return;
-    need_device(h);
-    if (!h->models_loaded) throw std::runtime_error("models not loaded");
-    commit_reference(h);
-    HostBatch& hb = b->hb;
+// Host-only preparation of a parsed chunk: per-read scratch layout, length classes, upload blob.
+// Thread-safe with respect to the handle (reads the class capacities and k only).
+void prepare_host(const tksm_seq* h, Prepared& p) {
+    HostBatch& hb = p.hb;
     const size_t R = hb.n_reads(), M = hb.n_mols(), S = hb.seg_src.size();
     const uint32_t k = (uint32_t)h->em.k;
-    b->scr_off.resize(R + 1);
-    b->raw_off.resize(R + 1);
+    p.scr_off.resize(R + 1);
+    p.raw_off.resize(R + 1);
     uint64_t so = 0, ro = 0;
-    for (int c = 0; c < N_CLASSES; c++) b->work[c].clear();
-    b->max_n_gws = 0;
+    p.max_n_gws = 0;
+    p.mods = !hb.mod_pos.empty();
+    // (length, read) keys per class, sorted longest first: the tail of the dynamic schedule is then
+    // made of short reads, and neighbouring work items have near-equal lengths
+    std::vector<uint64_t> keys[N_CLASSES];
+    uint64_t per_read_segs = 0, per_read_mods = 0, idsum = 0;
     for (size_t r = 0; r < R; r++) {
-        uint32_t L = hb.mol_raw_len[hb.read_mol[r]];
-        b->scr_off[r] = so;
-        b->raw_off[r] = ro;
+        const uint32_t m = hb.read_mol[r];
+        const uint32_t L = hb.mol_raw_len[m];
+        p.scr_off[r] = so;
+        p.raw_off[r] = ro;
         so += align_up((size_t)2 * L + 32, 16);
         ro += align_up((size_t)L, 16);
-        uint32_t n = L + 2 * k;
+        const uint32_t n = L + 2 * k;
         int c = 0;
         while (c < GWS_CLASS && n > h->ncap[c]) c++;
-        b->work[c].push_back((uint32_t)r);
-        if (c == GWS_CLASS) b->max_n_gws = std::max(b->max_n_gws, n);
+        keys[c].push_back(((uint64_t)(0xFFFFFFFFu - L) << 32) | (uint32_t)r);
+        if (c == GWS_CLASS) p.max_n_gws = std::max(p.max_n_gws, n);
+        per_read_segs += hb.mol_seg_begin[m + 1] - hb.mol_seg_begin[m];
+        if (p.mods) per_read_mods += hb.seg_mod_begin[hb.mol_seg_begin[m + 1]] - hb.seg_mod_begin[hb.mol_seg_begin[m]];
+        idsum += hb.mol_id_begin[m + 1] - hb.mol_id_begin[m];
     }
-    b->scr_off[R] = so;
-    b->raw_off[R] = ro;
-    // longest first inside a class: the tail of a dynamic schedule is then made of short reads
-    for (int c = 0; c < N_CLASSES; c++)
-        std::stable_sort(b->work[c].begin(), b->work[c].end(), [&](uint32_t a, uint32_t d) {
-            return hb.mol_raw_len[hb.read_mol[a]] > hb.mol_raw_len[hb.read_mol[d]];
-        });
+    p.scr_off[R] = so;
+    p.raw_off[R] = ro;
+    p.idsum = idsum;
+    for (int c = 0; c < N_CLASSES; c++) {
+        std::sort(keys[c].begin(), keys[c].end());
+        p.work[c].resize(keys[c].size());
+        for (size_t i = 0; i < keys[c].size(); i++) p.work[c][i] = (uint32_t)keys[c][i];
+    }
+    // SURVEY.md 8(d): ceil(L_genomic / 4) + L_literal + 24 per interval + 5 per mod
+    p.alg_in_bytes = (hb.genomic_bases + 3) / 4 + hb.literal_bases + 24 * per_read_segs + 5 * per_read_mods;
 
-    const bool mods = !hb.mod_pos.empty();
     struct Part {
         const void* src;
         size_t bytes;
@@ -296,70 +336,73 @@ void batch_upload(tksm_seq* h, tksm_seq_batch* b) {
     };
     std::vector<Part> parts;
     size_t total = 0;
-    auto add = [&](const void* p, size_t bytes) {
+    auto add = [&](const void* src, size_t bytes) {
         size_t off = total;
-        parts.push_back({p, bytes, off});
+        parts.push_back({src, bytes, off});
         total = align_up(total + std::max<size_t>(bytes, 1), 256);
         return off;
     };
-    size_t o_read_mol = add(hb.read_mol.data(), R * 4);
-    size_t o_msb = add(hb.mol_seg_begin.data(), (M + 1) * 4);
-    size_t o_mrl = add(hb.mol_raw_len.data(), M * 4);
-    size_t o_mib = add(hb.mol_id_begin.data(), (M + 1) * 4);
-    size_t o_src = add(hb.seg_src.data(), S * 8);
-    size_t o_len = add(hb.seg_len.data(), S * 4);
-    size_t o_smb = add(hb.seg_mod_begin.data(), mods ? (S + 1) * 4 : 0);
-    size_t o_mp = add(hb.mod_pos.data(), hb.mod_pos.size() * 4);
-    size_t o_mc = add(hb.mod_chr.data(), hb.mod_chr.size());
-    size_t o_lit = add(hb.lit_pool.data(), hb.lit_pool.size());
-    size_t o_id = add(hb.id_pool.data(), hb.id_pool.size());
-    size_t o_so = add(b->scr_off.data(), (R + 1) * 8);
-    size_t o_ro = add(b->raw_off.data(), (R + 1) * 8);
-    size_t o_work[N_CLASSES];
-    for (int c = 0; c < N_CLASSES; c++) o_work[c] = add(b->work[c].data(), b->work[c].size() * 4);
+    p.o_read_mol = add(hb.read_mol.data(), R * 4);
+    p.o_msb = add(hb.mol_seg_begin.data(), (M + 1) * 4);
+    p.o_mrl = add(hb.mol_raw_len.data(), M * 4);
+    p.o_mib = add(hb.mol_id_begin.data(), (M + 1) * 4);
+    p.o_src = add(hb.seg_src.data(), S * 8);
+    p.o_len = add(hb.seg_len.data(), S * 4);
+    p.o_smb = add(hb.seg_mod_begin.data(), p.mods ? (S + 1) * 4 : 0);
+    p.o_mp = add(hb.mod_pos.data(), hb.mod_pos.size() * 4);
+    p.o_mc = add(hb.mod_chr.data(), hb.mod_chr.size());
+    p.o_lit = add(hb.lit_pool.data(), hb.lit_pool.size());
+    p.o_id = add(hb.id_pool.data(), hb.id_pool.size());
+    p.o_so = add(p.scr_off.data(), (R + 1) * 8);
+    p.o_ro = add(p.raw_off.data(), (R + 1) * 8);
+    for (int c = 0; c < N_CLASSES; c++) p.o_work[c] = add(p.work[c].data(), p.work[c].size() * 4);
+    p.blob.reset(new char[total]);
+    p.blob_bytes = total;
+    for (auto& q : parts)
+        if (q.bytes) memcpy(p.blob.get() + q.off, q.src, q.bytes);
+}
 
+// Uploads the prepared chunk of slot `b` (asynchronously on the compute stream).
+void slot_bind(tksm_seq* h, tksm_seq_batch* b) {
+    need_device(h);
+    if (!h->models_loaded) throw std::runtime_error("models not loaded");
+    commit_reference(h);
     CK(cudaSetDevice(h->cfg.device));
-    h->stage.ensure(total);
-    for (auto& p : parts)
-        if (p.bytes) memcpy((char*)h->stage.p + p.off, p.src, p.bytes);
-    b->blob.ensure(total);
-    CK(cudaMemcpyAsync(b->blob.p, h->stage.p, total, cudaMemcpyHostToDevice, h->stream));
-    b->h2d_bytes = total;
+    Prepared& p = b->prep;
+    const size_t R = p.hb.n_reads();
+    b->stage.ensure(p.blob_bytes);
+    memcpy(b->stage.p, p.blob.get(), p.blob_bytes);
+    p.blob.reset();
+    b->blob.ensure(p.blob_bytes);
+    CK(cudaMemcpyAsync(b->blob.p, b->stage.p, p.blob_bytes, cudaMemcpyHostToDevice, h->stream));
+    b->h2d_bytes = p.blob_bytes;
     char* base = (char*)b->blob.p;
     DevBatch& D = b->db;
     D.n_reads = (uint32_t)R;
-    D.ordinal_base = hb.ordinal_base;
-    D.read_mol = (const uint32_t*)(base + o_read_mol);
-    D.mol_seg_begin = (const uint32_t*)(base + o_msb);
-    D.mol_raw_len = (const uint32_t*)(base + o_mrl);
-    D.mol_id_begin = (const uint32_t*)(base + o_mib);
-    D.seg_src = (const uint64_t*)(base + o_src);
-    D.seg_len = (const uint32_t*)(base + o_len);
-    D.seg_mod_begin = mods ? (const uint32_t*)(base + o_smb) : nullptr;
-    D.mod_pos = (const uint32_t*)(base + o_mp);
-    D.mod_chr = (const uint8_t*)(base + o_mc);
-    D.lit_pool = (const uint8_t*)(base + o_lit);
-    D.id_pool = (const uint8_t*)(base + o_id);
-    D.scr_off = (const uint64_t*)(base + o_so);
-    D.raw_off = (const uint64_t*)(base + o_ro);
-    for (int c = 0; c < N_CLASSES; c++) b->d_work[c] = (uint32_t*)(base + o_work[c]);
-
+    D.ordinal_base = p.hb.ordinal_base;
+    D.read_mol = (const uint32_t*)(base + p.o_read_mol);
+    D.mol_seg_begin = (const uint32_t*)(base + p.o_msb);
+    D.mol_raw_len = (const uint32_t*)(base + p.o_mrl);
+    D.mol_id_begin = (const uint32_t*)(base + p.o_mib);
+    D.seg_src = (const uint64_t*)(base + p.o_src);
+    D.seg_len = (const uint32_t*)(base + p.o_len);
+    D.seg_mod_begin = p.mods ? (const uint32_t*)(base + p.o_smb) : nullptr;
+    D.mod_pos = (const uint32_t*)(base + p.o_mp);
+    D.mod_chr = (const uint8_t*)(base + p.o_mc);
+    D.lit_pool = (const uint8_t*)(base + p.o_lit);
+    D.id_pool = (const uint8_t*)(base + p.o_id);
+    D.scr_off = (const uint64_t*)(base + p.o_so);
+    D.raw_off = (const uint64_t*)(base + p.o_ro);
+    for (int c = 0; c < N_CLASSES; c++) b->d_work[c] = (uint32_t*)(base + p.o_work[c]);
     b->per_read.ensure(std::max<size_t>(R, 1) * 16);
     D.read_len = b->per_read.as<uint32_t>();
     D.ident_num = D.read_len + R;
     D.ident_den = D.ident_num + R;
     D.status = D.ident_den + R;
     b->counters.ensure(64);
-    // SURVEY.md 8(d): ceil(L_genomic / 4) + L_literal + 24 per interval + 5 per mod
-    uint64_t per_read_segs = 0, per_read_mods = 0;
-    for (size_t r = 0; r < R; r++) {
-        uint32_t m = hb.read_mol[r];
-        per_read_segs += hb.mol_seg_begin[m + 1] - hb.mol_seg_begin[m];
-        if (mods) per_read_mods += hb.seg_mod_begin[hb.mol_seg_begin[m + 1]] - hb.seg_mod_begin[hb.mol_seg_begin[m]];
-    }
-    b->alg_in_bytes = (hb.genomic_bases + 3) / 4 + hb.literal_bases + 24 * per_read_segs + 5 * per_read_mods;
-    CK(cudaStreamSynchronize(h->stream));
-    b->uploaded = true;
+    b->h_tot.ensure(64);
+    b->ensure_events();
+    b->bound = true;
 }
 
 void run_scan(tksm_seq* h, tksm_seq_batch* b, int o, uint32_t R, uint64_t* d_total) {
@@ -373,20 +416,20 @@ void run_scan(tksm_seq* h, tksm_seq_batch* b, int o, uint32_t R, uint64_t* d_tot
     CK(cudaGetLastError());
 }
 
-void batch_run(tksm_seq* h, tksm_seq_batch* b, int which, int format, tksm_seq_stats* st) {
-    batch_upload(h, b);
+// counters buffer (64 bytes): u32 work tickets [0..5] | +32: u64 record bytes [2] | +48: u64 read bases | +56: u32 status OR
+constexpr size_t CNT_TOTALS = 32, CNT_READ_BASES = 48, CNT_STATUS = 56;
+
+// Enqueues the kernel sequence of the bound chunk on the compute stream; no host synchronisation.
+void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
+    if (!b->bound) throw std::runtime_error("batch not uploaded");
     CK(cudaSetDevice(h->cfg.device));
-    HostBatch& hb = b->hb;
+    Prepared& p = b->prep;
+    HostBatch& hb = p.hb;
     const uint32_t R = (uint32_t)hb.n_reads();
-    tksm_seq_stats s{};
-    s.reads = R;
-    s.raw_bases = hb.total_raw_bases;
-    s.h2d_bytes = b->h2d_bytes;
+    b->which = which;
     b->out_bytes[0] = b->out_bytes[1] = 0;
-    if (R == 0) {
-        if (st) *st = s;
-        return;
-    }
+    b->launches = 0;
+    if (R == 0) return;
     const bool want_bad = which & TKSM_SEQ_BADREAD, want_perf = which & TKSM_SEQ_PERFECT;
     const bool fastq_o[2] = {(format & TKSM_SEQ_FASTQ_BADREAD) != 0, (format & TKSM_SEQ_FASTQ_PERFECT) != 0};
     const bool fastq = fastq_o[0];
@@ -396,52 +439,53 @@ void batch_run(tksm_seq* h, tksm_seq_batch* b, int which, int format, tksm_seq_s
     if (want_bad && fastq && !h->cfg.skip_qual_compute) flags |= RUN_QUAL;  // py/sequence.py:349-353
     if (want_perf) flags |= RUN_RAW;
     if (want_bad) {
-        b->scr_seq.ensure(b->scr_off[R]);
-        if (flags & RUN_QUAL) b->scr_qual.ensure(b->scr_off[R]);
+        b->scr_seq.ensure(p.scr_off[R]);
+        if (flags & RUN_QUAL) b->scr_qual.ensure(p.scr_off[R]);
     }
-    if (want_perf) b->scr_raw.ensure(std::max<uint64_t>(b->raw_off[R], 16));
+    if (want_perf) b->scr_raw.ensure(std::max<uint64_t>(p.raw_off[R], 16));
     D.scr_seq = b->scr_seq.as<uint8_t>();
     D.scr_qual = b->scr_qual.as<uint8_t>();
     D.scr_raw = want_perf ? b->scr_raw.as<uint8_t>() : nullptr;
     // output upper bounds
-    uint64_t idsum = 0;
-    for (uint32_t r = 0; r < R; r++) {
-        uint32_t m = hb.read_mol[r];
-        idsum += hb.mol_id_begin[m + 1] - hb.mol_id_begin[m];
-    }
-    uint64_t cap_bad = (uint64_t)R * 128 + idsum + b->scr_off[R] * (fastq ? 2 : 1);
-    uint64_t cap_perf = (uint64_t)R * 128 + idsum + hb.total_raw_bases * (fastq_o[1] ? 2 : 1);
-    if (want_bad) b->out[0].ensure(cap_bad);
-    if (want_perf) b->out[1].ensure(cap_perf);
+    b->out_cap[0] = want_bad ? (uint64_t)R * 128 + p.idsum + p.scr_off[R] * (fastq ? 2 : 1) : 0;
+    b->out_cap[1] = want_perf ? (uint64_t)R * 128 + p.idsum + hb.total_raw_bases * (fastq_o[1] ? 2 : 1) : 0;
+    if (want_bad) b->out[0].ensure(b->out_cap[0]);
+    if (want_perf) b->out[1].ensure(b->out_cap[1]);
     for (int o = 0; o < 2; o++)
         if ((o == 0 && want_bad) || (o == 1 && want_perf)) {
             b->rec_len[o].ensure((size_t)R * 4);
             b->rec_off[o].ensure((size_t)R * 8);
         }
-    if (b->max_n_gws) {
-        const uint32_t ncap = (uint32_t)align_up(b->max_n_gws + 16, 16);
-        h->ncap[GWS_CLASS] = ncap;
-        h->cap_list[GWS_CLASS] = ncap / 2 + 64;
-        h->slab[GWS_CLASS] = slab_layout(CLASS_W[GWS_CLASS], 8, ncap, h->cap_list[GWS_CLASS]).bytes;
-        b->gws.ensure((size_t)h->slab[GWS_CLASS] * h->num_sms);
+    uint32_t ncap_c[N_CLASSES], cap_list_c[N_CLASSES], slab_c[N_CLASSES];
+    for (int c = 0; c < N_CLASSES; c++) {
+        ncap_c[c] = h->ncap[c];
+        cap_list_c[c] = h->cap_list[c];
+        slab_c[c] = h->slab[c];
     }
-    uint64_t* d_totals = (uint64_t*)((char*)b->counters.p + 32);
+    if (p.max_n_gws) {
+        const uint32_t ncap = (uint32_t)align_up(p.max_n_gws + 16, 16);
+        ncap_c[GWS_CLASS] = ncap;
+        cap_list_c[GWS_CLASS] = ncap / 2 + 64;
+        slab_c[GWS_CLASS] = slab_layout(CLASS_W[GWS_CLASS], 8, ncap, cap_list_c[GWS_CLASS]).bytes;
+        b->gws.ensure((size_t)slab_c[GWS_CLASS] * h->num_sms);
+    }
+    uint64_t* d_totals = (uint64_t*)((char*)b->counters.p + CNT_TOTALS);
     CK(cudaMemsetAsync(b->counters.p, 0, 64, h->stream));
 
-    CK(cudaEventRecord(h->ev[0], h->stream));
+    CK(cudaEventRecord(b->ev[0], h->stream));
     uint32_t launches = 0;
     for (int c = 0; c < N_CLASSES; c++) {
-        if (b->work[c].empty()) continue;
+        if (p.work[c].empty()) continue;
         SimParams P;
         P.T = h->dt;
         P.B = D;
         P.work = b->d_work[c];
-        P.n_work = (uint32_t)b->work[c].size();
+        P.n_work = (uint32_t)p.work[c].size();
         P.counter = b->counters.as<uint32_t>() + c;
         P.flags = flags;
-        P.ncap = h->ncap[c];
-        P.cap_list = h->cap_list[c];
-        P.slab_bytes = h->slab[c];
+        P.ncap = ncap_c[c];
+        P.cap_list = cap_list_c[c];
+        P.slab_bytes = slab_c[c];
         P.gws = b->gws.as<uint8_t>();
         const int teams = c == GWS_CLASS ? 1 : SIM_WARPS / CLASS_W[c];
         int grid = (int)std::min<size_t>((size_t)h->num_sms, (P.n_work + teams - 1) / teams);
@@ -455,7 +499,7 @@ void batch_run(tksm_seq* h, tksm_seq_batch* b, int which, int format, tksm_seq_s
         }
         launches++;
     }
-    CK(cudaEventRecord(h->ev[1], h->stream));
+    CK(cudaEventRecord(b->ev[1], h->stream));
     for (int o = 0; o < 2; o++) {
         if (!((o == 0 && want_bad) || (o == 1 && want_perf))) continue;
         FmtParams F{};
@@ -474,6 +518,9 @@ void batch_run(tksm_seq* h, tksm_seq_batch* b, int which, int format, tksm_seq_s
             F.seq = D.scr_seq;
             F.seq_off = D.scr_off;
             F.qual = (flags & RUN_QUAL) ? D.scr_qual : nullptr;
+            F.status = D.status;
+            F.sum_read_len = (unsigned long long*)((char*)b->counters.p + CNT_READ_BASES);
+            F.status_or = (uint32_t*)((char*)b->counters.p + CNT_STATUS);
         } else {
             F.read_len = nullptr;
             F.seq = D.scr_raw;
@@ -492,36 +539,44 @@ void batch_run(tksm_seq* h, tksm_seq_batch* b, int which, int format, tksm_seq_s
         CK(cudaGetLastError());
         launches += 5;
     }
-    CK(cudaEventRecord(h->ev[2], h->stream));
-    uint64_t totals[2] = {0, 0};
-    CK(cudaMemcpyAsync(totals, d_totals, 16, cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaEventRecord(b->ev[2], h->stream));
+    CK(cudaMemcpyAsync(b->h_tot.p, d_totals, 32, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaEventRecord(b->ev[4], h->stream));
+    b->launches = launches;
+}
+
+// Waits for the kernels of slot `b` and fills the statistics of the chunk.
+void slot_wait(tksm_seq* h, tksm_seq_batch* b, tksm_seq_stats* st) {
+    Prepared& p = b->prep;
+    HostBatch& hb = p.hb;
+    tksm_seq_stats s{};
+    s.reads = hb.n_reads();
+    s.raw_bases = hb.total_raw_bases;
+    s.h2d_bytes = b->h2d_bytes;
+    if (s.reads == 0) {
+        CK(cudaStreamSynchronize(h->stream));
+        if (st) *st = s;
+        return;
+    }
+    CK(cudaEventSynchronize(b->ev[4]));
+    const bool want_bad = b->which & TKSM_SEQ_BADREAD, want_perf = b->which & TKSM_SEQ_PERFECT;
+    const uint64_t* tot = (const uint64_t*)b->h_tot.p;
     float ms_all = 0, ms_sim = 0;
-    CK(cudaEventElapsedTime(&ms_all, h->ev[0], h->ev[2]));
-    CK(cudaEventElapsedTime(&ms_sim, h->ev[0], h->ev[1]));
-    b->out_bytes[0] = want_bad ? totals[0] : 0;
-    b->out_bytes[1] = want_perf ? totals[1] : 0;
-    if (b->out_bytes[0] > cap_bad || b->out_bytes[1] > cap_perf) throw std::runtime_error("output exceeds its bound");
+    CK(cudaEventElapsedTime(&ms_all, b->ev[0], b->ev[2]));
+    CK(cudaEventElapsedTime(&ms_sim, b->ev[0], b->ev[1]));
+    b->out_bytes[0] = want_bad ? tot[0] : 0;
+    b->out_bytes[1] = want_perf ? tot[1] : 0;
+    if (b->out_bytes[0] > b->out_cap[0] || b->out_bytes[1] > b->out_cap[1]) throw std::runtime_error("output exceeds its bound");
     s.out_bytes[0] = b->out_bytes[0];
     s.out_bytes[1] = b->out_bytes[1];
     s.kernel_ms = ms_all;
     s.simulate_ms = ms_sim;
-    s.kernel_launches = launches;
-    s.algorithmic_bytes = b->alg_in_bytes + b->out_bytes[0] + b->out_bytes[1];
-    // read_bases and status: small reductions on the host side of the per-read arrays
+    s.kernel_launches = b->launches;
+    s.algorithmic_bytes = p.alg_in_bytes + b->out_bytes[0] + b->out_bytes[1];
     if (want_bad) {
-        std::vector<uint32_t> tmp((size_t)R * 4);
-        CK(cudaMemcpy(tmp.data(), D.read_len, (size_t)R * 16, cudaMemcpyDeviceToHost));
-        s.d2h_bytes += (size_t)R * 16;
-        uint64_t rb = 0;
-        uint32_t stor = 0;
-        for (uint32_t r = 0; r < R; r++) {
-            rb += tmp[r];
-            stor |= tmp[(size_t)3 * R + r];
-        }
-        s.read_bases = rb;
-        s.status_or = stor;
-        if (stor & (ST_OPS_OVERFLOW | ST_SCRATCH_OVERFLOW))
+        s.read_bases = tot[2];
+        s.status_or = (uint32_t)tot[3];
+        if (s.status_or & (ST_OPS_OVERFLOW | ST_SCRATCH_OVERFLOW))
             throw std::runtime_error("a read outgrew its scratch slot (insertion-heavy read); rerun unsupported");
     } else {
         s.read_bases = hb.total_raw_bases;
@@ -535,6 +590,328 @@ void batch_fetch(tksm_seq* h, tksm_seq_batch* b, int o, char* dst) {
     CK(cudaMemcpyAsync(dst, b->out[o].p, b->out_bytes[o], cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
 }
+
+void add_stats(tksm_seq_stats& total, const tksm_seq_stats& s) {
+    total.reads += s.reads;
+    total.raw_bases += s.raw_bases;
+    total.read_bases += s.read_bases;
+    total.out_bytes[0] += s.out_bytes[0];
+    total.out_bytes[1] += s.out_bytes[1];
+    total.algorithmic_bytes += s.algorithmic_bytes;
+    total.h2d_bytes += s.h2d_bytes;
+    total.d2h_bytes += s.d2h_bytes;
+    total.kernel_ms += s.kernel_ms;
+    total.simulate_ms += s.simulate_ms;
+    total.kernel_launches += s.kernel_launches;
+    total.status_or |= s.status_or;
+}
+
+// ---------------------------------------------------------------- pinned arena pool
+// Record buffers handed to the caller by tksm_seq_simulate_text are page-locked so the device
+// writes them directly; tksm_seq_free() returns them here and the next call reuses them.
+struct ArenaPool {
+    struct Block {
+        void* p;
+        size_t cap;
+        bool used;
+    };
+    std::mutex mu;
+    std::vector<Block> blocks;
+    void* acquire(size_t bytes) {
+        std::lock_guard<std::mutex> g(mu);
+        int best = -1;
+        for (size_t i = 0; i < blocks.size(); i++)
+            if (!blocks[i].used && blocks[i].cap >= bytes && (best < 0 || blocks[i].cap < blocks[(size_t)best].cap)) best = (int)i;
+        if (best >= 0) {
+            blocks[(size_t)best].used = true;
+            return blocks[(size_t)best].p;
+        }
+        // drop free blocks that are too small before growing
+        for (size_t i = 0; i < blocks.size();)
+            if (!blocks[i].used) {
+                cudaFreeHost(blocks[i].p);
+                blocks.erase(blocks.begin() + (long)i);
+            } else
+                i++;
+        void* p = nullptr;
+        size_t want = bytes + bytes / 8 + 4096;
+        CK(cudaMallocHost(&p, want));
+        blocks.push_back({p, want, true});
+        return p;
+    }
+    size_t capacity(void* p) {
+        std::lock_guard<std::mutex> g(mu);
+        for (auto& b : blocks)
+            if (b.p == p) return b.cap;
+        return 0;
+    }
+    bool release(void* p) {
+        std::lock_guard<std::mutex> g(mu);
+        for (auto& b : blocks)
+            if (b.p == p) {
+                b.used = false;
+                return true;
+            }
+        return false;
+    }
+};
+ArenaPool& arena_pool() {
+    static ArenaPool* pool = new ArenaPool();  // never destroyed: outlives the CUDA context teardown order
+    return *pool;
+}
+
+// ---------------------------------------------------------------- host worker pool
+class WorkerPool {
+  public:
+    explicit WorkerPool(int n) {
+        for (int i = 0; i < n; i++) th_.emplace_back([this] { loop(); });
+    }
+    ~WorkerPool() {
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            stop_ = true;
+        }
+        cv_.notify_all();
+        for (auto& t : th_) t.join();
+    }
+    template <typename F>
+    auto submit(F&& f) -> std::future<decltype(f())> {
+        auto task = std::make_shared<std::packaged_task<decltype(f())()>>(std::forward<F>(f));
+        auto fut = task->get_future();
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            q_.emplace_back([task] { (*task)(); });
+        }
+        cv_.notify_one();
+        return fut;
+    }
+
+  private:
+    void loop() {
+        while (true) {
+            std::function<void()> job;
+            {
+                std::unique_lock<std::mutex> g(mu_);
+                cv_.wait(g, [this] { return stop_ || !q_.empty(); });
+                if (q_.empty()) return;
+                job = std::move(q_.front());
+                q_.pop_front();
+            }
+            job();
+        }
+    }
+    std::mutex mu_;
+    std::condition_variable cv_;
+    std::deque<std::function<void()>> q_;
+    std::vector<std::thread> th_;
+    bool stop_ = false;
+};
+
+int host_threads(const tksm_seq* h) {
+    if (h->cfg.threads > 0) return h->cfg.threads;
+    unsigned hc = std::thread::hardware_concurrency();
+    return (int)std::min<unsigned>(std::max<unsigned>(hc, 1), 32);
+}
+
+using PreparedList = std::vector<std::unique_ptr<Prepared>>;
+
+// one text chunk (complete records) -> one or more prepared device chunks
+PreparedList parse_chunk(const tksm_seq* h, const tk::TextChunk& tc) {
+    const size_t max_reads = h->cfg.batch_reads ? (size_t)h->cfg.batch_reads : ((size_t)1 << 18);
+    const uint64_t max_bases = h->cfg.batch_bases ? h->cfg.batch_bases : (1ull << 28);
+    PreparedList out;
+    MdfParser parser(&h->genome);
+    size_t pos = 0;
+    while (true) {
+        std::unique_ptr<Prepared> p(new Prepared());
+        size_t used = parser.feed(tc.p + pos, tc.n - pos, true, p->hb, max_reads, max_bases);
+        pos += used;
+        if (p->hb.n_reads()) {
+            prepare_host(h, *p);
+            out.push_back(std::move(p));
+        }
+        if (pos >= tc.n || used == 0) break;
+    }
+    return out;
+}
+
+}  // namespace
+
+namespace tk {
+
+// Streaming pipeline: text chunks are parsed and packed by host threads while the device works on
+// earlier chunks; record downloads run on their own stream behind the kernels of the next chunk.
+//   arena mode (sink == nullptr): the records of `which` (one output) are downloaded straight into a
+//     page-locked buffer that is handed to the caller (*arena_out, released with tksm_seq_free).
+//   sink mode: records go through the slot's pinned staging to sink->write(), in MDF order.
+void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_t ordinal_base, OutputSink* sink,
+                   char** arena_out, size_t* arena_len, tksm_seq_stats* stats) {
+    need_device(h);
+    if (!h->models_loaded) throw std::runtime_error("models not loaded");
+    commit_reference(h);
+    CK(cudaSetDevice(h->cfg.device));
+    const int NS = 3;
+    while ((int)h->slots.size() < NS) h->slots.emplace_back(new tksm_seq_batch());
+    const int nthreads = host_threads(h);
+    tksm_seq_stats total{};
+    uint64_t ordinal = ordinal_base;
+    const int o_arena = which == TKSM_SEQ_PERFECT ? 1 : 0;
+    char* arena = nullptr;
+    size_t arena_cap = 0, arena_pos = 0;
+    uint64_t text_total = 0, text_done = 0, cap_done = 0;  // for the arena size estimate
+
+    struct Pending {
+        std::future<PreparedList> fut;
+        size_t text_bytes;
+    };
+    std::deque<Pending> pending;
+    bool src_done = false;
+    struct InFlight {
+        tksm_seq_batch* b;
+    };
+    std::deque<InFlight> inflight;  // launched, not yet finished (at most 2)
+    size_t issued = 0;
+
+    auto release_arena = [&]() {
+        if (arena) arena_pool().release(arena);
+        arena = nullptr;
+    };
+    auto slot_reusable = [&](tksm_seq_batch* b) {
+        if (b->d2h_pending) {
+            CK(cudaEventSynchronize(b->ev[3]));
+            b->d2h_pending = false;
+            if (sink)
+                for (int o = 0; o < 2; o++)
+                    if (b->out_bytes[o]) sink->write(o, (const char*)b->host_out[o].p, b->out_bytes[o]);
+        }
+    };
+    auto finish = [&](tksm_seq_batch* b) {
+        tksm_seq_stats s{};
+        slot_wait(h, b, &s);
+        if (sink) {
+            for (int o = 0; o < 2; o++) {
+                if (!b->out_bytes[o]) continue;
+                b->host_out[o].ensure(b->out_bytes[o]);
+                CK(cudaMemcpyAsync(b->host_out[o].p, b->out[o].p, b->out_bytes[o], cudaMemcpyDeviceToHost, h->copy_stream));
+                s.d2h_bytes += b->out_bytes[o];
+            }
+        } else {
+            const size_t nbytes = b->out_bytes[o_arena];
+            if (arena_pos + nbytes > arena_cap) {
+                // estimate the whole output from the bound of the chunks seen so far
+                size_t want = arena_pos + nbytes;
+                if (text_done && text_total > text_done)
+                    want = std::max<size_t>(want, (size_t)((double)cap_done / (double)text_done * (double)text_total * 1.05));
+                char* bigger = (char*)arena_pool().acquire(want);
+                if (arena) {
+                    CK(cudaStreamSynchronize(h->copy_stream));
+                    memcpy(bigger, arena, arena_pos);
+                    arena_pool().release(arena);
+                }
+                arena = bigger;
+                arena_cap = arena_pool().capacity(arena);
+            }
+            if (nbytes)
+                CK(cudaMemcpyAsync(arena + arena_pos, b->out[o_arena].p, nbytes, cudaMemcpyDeviceToHost, h->copy_stream));
+            arena_pos += nbytes;
+            s.d2h_bytes += nbytes;
+        }
+        CK(cudaEventRecord(b->ev[3], h->copy_stream));
+        b->d2h_pending = true;
+        add_stats(total, s);
+    };
+
+    try {
+        WorkerPool pool(nthreads);
+        const size_t max_pending = (size_t)nthreads * 2 + 2;
+        while (true) {
+            // keep the parser threads fed
+            while (!src_done && pending.size() < max_pending) {
+                TextChunk tc;
+                if (!src.next(tc)) {
+                    src_done = true;
+                    break;
+                }
+                text_total = std::max<uint64_t>(text_total, src.total_bytes_hint());
+                const tksm_seq* hc = h;
+                pending.push_back({pool.submit([hc, tc]() { return parse_chunk(hc, tc); }), tc.n});
+            }
+            if (pending.empty()) break;
+            PreparedList list = pending.front().fut.get();
+            text_done += pending.front().text_bytes;
+            pending.pop_front();
+            for (auto& pp : list) {
+                tksm_seq_batch* b = h->slots[issued % NS].get();
+                slot_reusable(b);
+                b->prep = std::move(*pp);
+                b->prep.hb.ordinal_base = ordinal;
+                ordinal += b->prep.hb.n_reads();
+                const uint64_t R = b->prep.hb.n_reads();
+                cap_done += R * 128 + b->prep.idsum +
+                            (o_arena == 0 ? b->prep.scr_off[R] * ((format & TKSM_SEQ_FASTQ_BADREAD) ? 2 : 1)
+                                          : b->prep.hb.total_raw_bases * ((format & TKSM_SEQ_FASTQ_PERFECT) ? 2 : 1));
+                slot_bind(h, b);
+                slot_launch(h, b, which, format);
+                issued++;
+                inflight.push_back({b});
+                if (inflight.size() >= 2) {
+                    finish(inflight.front().b);
+                    inflight.pop_front();
+                }
+            }
+        }
+        while (!inflight.empty()) {
+            finish(inflight.front().b);
+            inflight.pop_front();
+        }
+        // flush the last downloads in chunk order
+        for (size_t j = issued > (size_t)NS ? issued - NS : 0; j < issued; j++) slot_reusable(h->slots[j % NS].get());
+        CK(cudaStreamSynchronize(h->copy_stream));
+    } catch (...) {
+        cudaStreamSynchronize(h->stream);
+        cudaStreamSynchronize(h->copy_stream);
+        for (auto& sl : h->slots) sl->d2h_pending = false;
+        release_arena();
+        throw;
+    }
+    if (!sink) {
+        if (!arena) arena = (char*)arena_pool().acquire(1);
+        *arena_out = arena;
+        *arena_len = arena_pos;
+    }
+    if (stats) *stats = total;
+}
+
+}  // namespace tk
+
+namespace {
+
+// single-buffer chunker over text in memory: cuts at record boundaries ("\n+"), small chunks first
+// so the device starts early
+struct MemorySource : tk::ChunkSource {
+    const char* text;
+    size_t len, pos = 0, target;
+    size_t max_target;
+    MemorySource(const char* t, size_t n, size_t first = (size_t)1 << 20, size_t max_t = (size_t)8 << 20)
+        : text(t), len(n), target(first), max_target(max_t) {}
+    bool next(tk::TextChunk& tc) override {
+        if (pos >= len) return false;
+        size_t end = pos + target;
+        if (end >= len) {
+            end = len;
+        } else {
+            const char* q = end > 0 ? (const char*)memmem(text + end - 1, len - end + 1, "\n+", 2) : nullptr;
+            end = q ? (size_t)(q - text) + 1 : len;
+        }
+        tc.p = text + pos;
+        tc.n = end - pos;
+        tc.keep.reset();
+        pos = end;
+        target = std::min(target * 2, max_target);
+        return true;
+    }
+    uint64_t total_bytes_hint() const override { return len; }
+};
 
 }  // namespace
 
@@ -555,6 +932,7 @@ void tksm_seq_default_config(tksm_seq_config* c) {
     c->batch_reads = 0;
     c->batch_bases = 0;
     c->host_only = 0;
+    c->threads = 0;
 }
 
 #define API_BEGIN try {
@@ -586,7 +964,7 @@ tksm_seq* tksm_seq_create(const tksm_seq_config* cfg) {
                 throw std::runtime_error(std::string("device ") + prop.name + " is not sm_100; this build targets B200 only");
             h->num_sms = prop.multiProcessorCount;
             CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-            for (auto& e2 : h->ev) CK(cudaEventCreate(&e2));
+            CK(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
         }
     } catch (const std::exception& e) {
         g_create_error = e.what();
@@ -599,7 +977,9 @@ void tksm_seq_destroy(tksm_seq* h) { delete h; }
 
 const char* tksm_seq_last_error(const tksm_seq* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
 
-void tksm_seq_free(void* p) { free(p); }
+void tksm_seq_free(void* p) {
+    if (p && !arena_pool().release(p)) free(p);
+}
 
 int tksm_seq_load_references(tksm_seq* h, const char* const* paths, int n) {
     API_BEGIN
@@ -785,9 +1165,13 @@ tksm_seq_batch* tksm_seq_batch_create(tksm_seq* h, const char* mdf, size_t mdf_l
     std::unique_ptr<tksm_seq_batch> b(new tksm_seq_batch());
     try {
         MdfParser parser(&h->genome);
-        b->hb.ordinal_base = ordinal_base;
-        parser.feed(mdf, mdf_len, true, b->hb);
-        if (!h->cfg.host_only) batch_upload(h, b.get());
+        b->prep.hb.ordinal_base = ordinal_base;
+        parser.feed(mdf, mdf_len, true, b->prep.hb);
+        prepare_host(h, b->prep);
+        if (!h->cfg.host_only) {
+            slot_bind(h, b.get());
+            CK(cudaStreamSynchronize(h->stream));
+        }
     } catch (const std::exception& e) {
         h->err = e.what();
         return nullptr;
@@ -797,7 +1181,9 @@ tksm_seq_batch* tksm_seq_batch_create(tksm_seq* h, const char* mdf, size_t mdf_l
 
 int tksm_seq_batch_run(tksm_seq* h, tksm_seq_batch* b, int which, int format, tksm_seq_stats* stats) {
     API_BEGIN
-    batch_run(h, b, which, format, stats);
+    need_device(h);
+    slot_launch(h, b, which, format);
+    slot_wait(h, b, stats);
     API_END(h)
 }
 
@@ -818,22 +1204,11 @@ int tksm_seq_simulate_text(tksm_seq* h, const char* mdf, size_t mdf_len, int whi
     API_BEGIN
     if (which != TKSM_SEQ_BADREAD && which != TKSM_SEQ_PERFECT)
         throw std::runtime_error("simulate_text produces one output: TKSM_SEQ_BADREAD or TKSM_SEQ_PERFECT");
-    tksm_seq_batch b;
-    MdfParser parser(&h->genome);
-    b.hb.ordinal_base = ordinal_base;
-    parser.feed(mdf, mdf_len, true, b.hb);
-    tksm_seq_stats s{};
-    batch_run(h, &b, which, format, &s);
-    int o = which == TKSM_SEQ_PERFECT ? 1 : 0;
-    *out_len = b.out_bytes[o];
-    *out = (char*)malloc(std::max<size_t>(*out_len, 1));
-    if (!*out) throw std::runtime_error("out of host memory");
-    // pinned staging keeps the device->host copy at full PCIe rate
-    h->stage_out.ensure(std::max<size_t>(*out_len, 1));
-    batch_fetch(h, &b, o, (char*)h->stage_out.p);
-    memcpy(*out, h->stage_out.p, *out_len);
-    s.d2h_bytes += *out_len;
-    if (stats) *stats = s;
+    // text chunk size: starts at 1 MiB and doubles up to 8 MiB; TKSM_SEQ_CHUNK_BYTES pins it (tests)
+    size_t first = (size_t)1 << 20, max_t = (size_t)8 << 20;
+    if (const char* e = getenv("TKSM_SEQ_CHUNK_BYTES")) first = max_t = std::max<size_t>((size_t)atoll(e), 1);
+    MemorySource src(mdf, mdf_len, first, max_t);
+    tk::engine_stream(h, src, which, format, ordinal_base, nullptr, out, out_len, stats);
     API_END(h)
 }
 
@@ -849,24 +1224,6 @@ int tksm_seq_run_files(tksm_seq* h, const char* mdf_path, const char* badread_pa
 
 // ---------------------------------------------------------------- engine.hpp glue
 namespace tk {
-
-void engine_run_batch(tksm_seq* h, HostBatch& hb, int which, int format, std::vector<char>* out_bad,
-                      std::vector<char>* out_perf, tksm_seq_stats* st) {
-    tksm_seq_batch b;
-    b.hb = std::move(hb);
-    batch_run(h, &b, which, format, st);
-    if (out_bad && (which & TKSM_SEQ_BADREAD)) {
-        out_bad->resize(b.out_bytes[0]);
-        batch_fetch(h, &b, 0, out_bad->data());
-        if (st) st->d2h_bytes += b.out_bytes[0];
-    }
-    if (out_perf && (which & TKSM_SEQ_PERFECT)) {
-        out_perf->resize(b.out_bytes[1]);
-        batch_fetch(h, &b, 1, out_perf->data());
-        if (st) st->d2h_bytes += b.out_bytes[1];
-    }
-    hb = std::move(b.hb);
-}
 
 const GenomeStore* engine_genome(const tksm_seq* h) { return &h->genome; }
 const tksm_seq_config* engine_config(const tksm_seq* h) { return &h->cfg; }

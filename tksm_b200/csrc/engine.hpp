@@ -1,5 +1,6 @@
 // Internal glue between the device engine (engine.cu) and the host runner (runner.cpp).
 #pragma once
+#include <memory>
 #include <vector>
 
 #include "../../include/tksm_seq.h"
@@ -7,10 +8,27 @@
 
 namespace tk {
 
-// Runs one molecule batch through the kernels and copies the requested outputs to the host.
-// `hb` is moved in and handed back so its buffers can be reused.
-void engine_run_batch(tksm_seq* h, HostBatch& hb, int which, int format, std::vector<char>* out_badread,
-                      std::vector<char>* out_perfect, tksm_seq_stats* stats);
+// A run of complete MDF records (starts at a '+' header line or at the beginning of the input).
+struct TextChunk {
+    const char* p = nullptr;
+    size_t n = 0;
+    std::shared_ptr<void> keep;  // owner of the bytes, when the source does not outlive the pipeline
+};
+
+struct ChunkSource {
+    virtual ~ChunkSource() = default;
+    virtual bool next(TextChunk& out) = 0;                  // chunks in MDF order; false at end of input
+    virtual uint64_t total_bytes_hint() const { return 0; }  // whole input size when known (arena estimate)
+};
+
+struct OutputSink {
+    virtual ~OutputSink() = default;
+    virtual void write(int output /* 0 badread, 1 perfect */, const char* p, size_t n) = 0;  // called in MDF order
+};
+
+// engine.cu: the streaming pipeline (host parser threads -> upload -> kernels -> download)
+void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_t ordinal_base, OutputSink* sink,
+                   char** arena_out, size_t* arena_len, tksm_seq_stats* stats);
 const GenomeStore* engine_genome(const tksm_seq* h);
 const tksm_seq_config* engine_config(const tksm_seq* h);
 

@@ -1,6 +1,8 @@
 // Reference genome store, MDF parser and molecule batch (see host.hpp for the reference mapping).
 #include "host.hpp"
 
+#include <emmintrin.h>
+
 #include <algorithm>
 #include <cstring>
 #include <stdexcept>
@@ -192,6 +194,70 @@ inline bool next_line(const char* text, size_t len, size_t& pos, Line& out, bool
     return true;
 }
 
+// One pass over a line: its end (universal newlines, as next_line) and the positions of its first
+// tabs.  16 bytes at a time where the buffer allows.
+struct LineScan {
+    const char* b;
+    const char* e;
+    const char* tab[5];
+    int ntab;        // tabs seen, capped at 6
+    size_t next;
+    bool terminated;
+};
+inline bool scan_line(const char* text, size_t len, size_t pos, LineScan& L) {
+    if (pos >= len) return false;
+    const char* p = text + pos;
+    const char* const end = text + len;
+    L.b = p;
+    L.ntab = 0;
+    const __m128i vt = _mm_set1_epi8('\t'), vn = _mm_set1_epi8('\n'), vr = _mm_set1_epi8('\r');
+    const char* stop = nullptr;
+    while (!stop) {
+        if (end - p >= 16) {
+            const __m128i v = _mm_loadu_si128((const __m128i*)p);
+            unsigned m = (unsigned)_mm_movemask_epi8(
+                _mm_or_si128(_mm_or_si128(_mm_cmpeq_epi8(v, vt), _mm_cmpeq_epi8(v, vn)), _mm_cmpeq_epi8(v, vr)));
+            while (m) {
+                const int i = __builtin_ctz(m);
+                m &= m - 1;
+                if (p[i] == '\t') {
+                    if (L.ntab < 5) L.tab[L.ntab] = p + i;
+                    if (L.ntab < 6) L.ntab++;
+                } else {
+                    stop = p + i;
+                    break;
+                }
+            }
+            if (!stop) p += 16;
+        } else {
+            for (; p < end; p++) {
+                const char c = *p;
+                if (c == '\t') {
+                    if (L.ntab < 5) L.tab[L.ntab] = p;
+                    if (L.ntab < 6) L.ntab++;
+                } else if (c == '\n' || c == '\r') {
+                    stop = p;
+                    break;
+                }
+            }
+            if (!stop) break;
+        }
+    }
+    if (!stop) {
+        L.e = end;
+        L.next = len;
+        L.terminated = false;
+        return true;
+    }
+    L.e = stop;
+    L.terminated = true;
+    if (*stop == '\r' && stop + 1 < end && stop[1] == '\n')
+        L.next = (size_t)(stop - text) + 2;
+    else
+        L.next = (size_t)(stop - text) + 1;
+    return true;
+}
+
 // Python int(): optional surrounding whitespace, sign, digits with single underscores
 long long py_int(const char* b, const char* e) {
     auto fail = [&]() -> long long {
@@ -221,6 +287,21 @@ long long py_int(const char* b, const char* e) {
     }
     if (prev_us) return fail();
     return neg ? -v : v;
+}
+
+// plain decimal digits (the emitter's format); anything else goes through py_int
+inline long long mdf_int(const char* b, const char* e) {
+    if (b < e && e - b <= 18) {
+        long long v = 0;
+        const char* p = b;
+        for (; p < e; p++) {
+            unsigned d = (unsigned)(*p - '0');
+            if (d > 9) break;
+            v = v * 10 + d;
+        }
+        if (p == e) return v;
+    }
+    return py_int(b, e);
 }
 
 inline void py_slice(long long start, long long end, long long n, long long& s, long long& e) {
@@ -253,13 +334,38 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
     long long depth = 0;
     uint32_t raw_len = 0;
     uint64_t gen_b = 0, lit_b = 0;
-    size_t rec_start = 0;
     // roll-back marks
     size_t m_seg = 0, m_mod = 0, m_lit = 0, m_id = 0;
 
-    std::string last_chrom;
-    const Contig* last_contig = nullptr;
-    bool last_known = false;
+    // The first field of recent interval lines, resolved once: contig (or "the name is the sequence",
+    // py/sequence.py:307) and, for literals, the pool offset of the last slice taken from it.  Tags,
+    // adapters and the current chromosome alternate inside every molecule, so a few entries avoid
+    // nearly all string hashing.
+    struct TokEntry {
+        std::string tok;
+        const Contig* contig = nullptr;
+        long long lit_s = -1, lit_e = -1;
+        size_t lit_epoch = 0;
+        uint32_t lit_off = 0;
+    };
+    constexpr int NTOK = 8;
+    TokEntry toks[NTOK];
+    int tok_next = 0;
+    size_t lit_epoch = 1;  // bumped when a rollback may have dropped pool bytes
+    auto resolve = [&](std::string_view chrom) -> TokEntry& {
+        for (int i = 0; i < NTOK; i++)
+            if (toks[i].tok.size() == chrom.size() && memcmp(toks[i].tok.data(), chrom.data(), chrom.size()) == 0 &&
+                (!chrom.empty() || toks[i].lit_epoch))
+                return toks[i];
+        TokEntry& t = toks[tok_next];
+        tok_next = (tok_next + 1) % NTOK;
+        t.tok.assign(chrom);
+        auto it = genome->contigs.find(t.tok);
+        t.contig = it == genome->contigs.end() ? nullptr : &it->second;
+        t.lit_s = t.lit_e = -1;
+        t.lit_epoch = lit_epoch;
+        return t;
+    };
 
     auto mark = [&]() {
         m_seg = out.seg_src.size();
@@ -278,6 +384,7 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
             for (auto it = out.lit_index.begin(); it != out.lit_index.end();)
                 it = it->second >= m_lit ? out.lit_index.erase(it) : std::next(it);
             out.lit_pool.resize(m_lit);
+            lit_epoch++;
         }
         out.id_pool.resize(m_id);
     };
@@ -298,15 +405,12 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
         have = false;
     };
 
-    Line ln;
-    bool terminated = false;
+    LineScan ln;
     while (true) {
         size_t line_start = pos;
-        if (!next_line(text, len, pos, ln, terminated)) break;
-        if (!final && !terminated) {  // partial last line: wait for more data
-            pos = line_start;
-            break;
-        }
+        if (!scan_line(text, len, pos, ln)) break;
+        if (!final && !ln.terminated) break;  // partial last line: wait for more data
+        pos = ln.next;
         if (ln.b == ln.e) throw std::runtime_error("IndexError: empty line in MDF (py/sequence.py:207)");
         if (*ln.b == '+') {
             if (have) {
@@ -316,51 +420,37 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
             } else {
                 consumed = line_start;
             }
-            const char* t1 = (const char*)memchr(ln.b, '\t', (size_t)(ln.e - ln.b));
-            if (!t1) throw std::runtime_error("IndexError: MDF header without depth field");
-            const char* t2 = (const char*)memchr(t1 + 1, '\t', (size_t)(ln.e - t1 - 1));
-            depth = py_int(t1 + 1, t2 ? t2 : ln.e);
+            if (ln.ntab == 0) throw std::runtime_error("IndexError: MDF header without depth field");
+            const char* t1 = ln.tab[0];
+            depth = mdf_int(t1 + 1, ln.ntab > 1 ? ln.tab[1] : ln.e);
             mark();
             out.id_pool.insert(out.id_pool.end(), (const uint8_t*)ln.b + 1, (const uint8_t*)t1);
             have = true;
             raw_len = 0;
             gen_b = lit_b = 0;
-            rec_start = line_start;
-            (void)rec_start;
             continue;
         }
         // interval line: chr, start, end, strand[, mods]
         const char* f[6];
-        int nf = 0;
         f[0] = ln.b;
-        for (const char* p = ln.b; p < ln.e && nf < 5;) {
-            const char* t = (const char*)memchr(p, '\t', (size_t)(ln.e - p));
-            if (!t) break;
-            f[++nf] = t + 1;
-            p = t + 1;
-        }
-        nf++;  // number of fields seen (capped at 6)
+        for (int i = 0; i < ln.ntab && i < 5; i++) f[i + 1] = ln.tab[i] + 1;
+        const int nf = ln.ntab + 1;  // number of fields seen (capped at 7)
         if (nf < 4) throw std::runtime_error("ValueError: not enough values to unpack (MDF interval line)");
         if (nf > 5) throw std::runtime_error("ValueError: too many values to unpack (MDF interval line)");
         auto fend = [&](int i) { return i + 1 < nf ? f[i + 1] - 1 : ln.e; };
-        long long start = py_int(f[1], fend(1)), end = py_int(f[2], fend(2));
+        long long start = mdf_int(f[1], fend(1)), end = mdf_int(f[2], fend(2));
         bool plus = (fend(3) - f[3] == 1) && *f[3] == '+';
         if (!have) continue;  // intervals before the first header are parsed and dropped (py:213)
 
         std::string_view chrom(f[0], (size_t)(fend(0) - f[0]));
-        if (!(last_known && chrom == last_chrom)) {
-            last_chrom.assign(chrom);
-            auto it = genome->contigs.find(last_chrom);
-            last_contig = it == genome->contigs.end() ? nullptr : &it->second;
-            last_known = true;
-        }
+        TokEntry& te = resolve(chrom);
         long long s, e;
         uint64_t src;
         uint32_t slen;
-        if (last_contig) {
-            py_slice(start, end, (long long)last_contig->length, s, e);
+        if (te.contig) {
+            py_slice(start, end, (long long)te.contig->length, s, e);
             slen = (uint32_t)(e - s);
-            uint64_t g = last_contig->offset + (uint64_t)s;
+            uint64_t g = te.contig->offset + (uint64_t)s;
             src = g;
             if (genome->overlaps_exception(g, slen)) src |= SEG_HAS_EXC;
             gen_b += slen;
@@ -368,16 +458,24 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
             // unknown contig: the name itself is the sequence (py/sequence.py:307)
             py_slice(start, end, (long long)chrom.size(), s, e);
             slen = (uint32_t)(e - s);
-            std::string lit((size_t)slen, 0);
-            for (uint32_t i = 0; i < slen; i++) lit[i] = (char)frag_code(ascii_upper((uint8_t)chrom[(size_t)s + i]));
             uint32_t off;
-            auto it = out.lit_index.find(lit);
-            if (it != out.lit_index.end()) {
-                off = it->second;
+            if (te.lit_s == s && te.lit_e == e && te.lit_epoch == lit_epoch) {
+                off = te.lit_off;
             } else {
-                off = (uint32_t)out.lit_pool.size();
-                out.lit_pool.insert(out.lit_pool.end(), lit.begin(), lit.end());
-                if (out.lit_index.size() < (1u << 20)) out.lit_index.emplace(std::move(lit), off);
+                std::string lit((size_t)slen, 0);
+                for (uint32_t i = 0; i < slen; i++) lit[i] = (char)frag_code(ascii_upper((uint8_t)chrom[(size_t)s + i]));
+                auto it = out.lit_index.find(lit);
+                if (it != out.lit_index.end()) {
+                    off = it->second;
+                } else {
+                    off = (uint32_t)out.lit_pool.size();
+                    out.lit_pool.insert(out.lit_pool.end(), lit.begin(), lit.end());
+                    if (out.lit_index.size() < (1u << 20)) out.lit_index.emplace(std::move(lit), off);
+                }
+                te.lit_s = s;
+                te.lit_e = e;
+                te.lit_off = off;
+                te.lit_epoch = lit_epoch;
             }
             src = SEG_LITERAL | off;
             lit_b += slen;

@@ -978,6 +978,10 @@ struct FmtParams {
     uint32_t* rec_len;
     const uint64_t* rec_off;
     uint8_t* out;
+    // batch totals accumulated by reclen_kernel (badread output only; nullptr otherwise)
+    const uint32_t* status;
+    unsigned long long* sum_read_len;
+    uint32_t* status_or;
 };
 
 __device__ __forceinline__ uint32_t dec_digits(uint32_t v) {
@@ -1026,7 +1030,22 @@ __device__ __forceinline__ uint32_t record_len(const FmtParams& F, uint32_t r) {
 
 __global__ void reclen_kernel(const FmtParams F) {
     uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r < F.n_reads) F.rec_len[r] = record_len(F, r);
+    uint32_t lp = 0, stt = 0;
+    if (r < F.n_reads) {
+        F.rec_len[r] = record_len(F, r);
+        if (F.sum_read_len) {
+            lp = F.read_len[r];
+            stt = F.status[r];
+        }
+    }
+    if (F.sum_read_len) {
+        lp = warp_sum(lp);
+        stt = __reduce_or_sync(0xffffffffu, stt);
+        if ((threadIdx.x & 31) == 0) {
+            atomicAdd(F.sum_read_len, (unsigned long long)lp);
+            if (stt) atomicOr(F.status_or, stt);
+        }
+    }
 }
 
 // exclusive scan of u32 -> u64, three small kernels (block sums, scan of sums, final)

@@ -3,8 +3,11 @@
 // handling (get_output_file, py/sequence.py:291-300).
 #include <zlib.h>
 
+#include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -65,11 +68,61 @@ bool path_is_fastq(const char* path) {
     return ends_with(p, ".fastq") || ends_with(p, ".fq");
 }
 
+namespace {
+
+// Reads the MDF (file or FIFO, never seeks) in blocks and hands out chunks cut at record
+// boundaries.  A record larger than the block size grows the chunk until its end is seen.
+struct FileSource : ChunkSource {
+    FILE* in;
+    std::string carry;   // bytes after the last record boundary of the previous block
+    bool eof = false;
+    size_t target = (size_t)1 << 20, max_target = (size_t)8 << 20;
+    explicit FileSource(FILE* f) : in(f) {
+        if (const char* e = getenv("TKSM_SEQ_CHUNK_BYTES")) target = max_target = std::max<size_t>((size_t)atoll(e), 1);
+    }
+    bool next(TextChunk& tc) override {
+        while (true) {
+            if (eof && carry.empty()) return false;
+            auto buf = std::make_shared<std::string>();
+            buf->swap(carry);
+            while (!eof) {
+                size_t have = buf->size();
+                buf->resize(have + target);
+                size_t n = fread(&(*buf)[have], 1, target, in);
+                buf->resize(have + n);
+                if (n == 0) {
+                    eof = true;
+                    break;
+                }
+                // last record boundary inside the buffer ("\n+"); everything before it is complete
+                size_t cut = buf->rfind("\n+");
+                if (cut != std::string::npos && cut > 0) {
+                    carry.assign(*buf, cut + 1, std::string::npos);
+                    buf->resize(cut + 1);
+                    break;
+                }
+            }
+            target = std::min(target * 2, max_target);
+            if (buf->empty()) continue;
+            tc.p = buf->data();
+            tc.n = buf->size();
+            tc.keep = buf;
+            return true;
+        }
+    }
+};
+
+struct FileSinks : OutputSink {
+    Sink* s[2];
+    void write(int o, const char* p, size_t n) override {
+        if (s[o]) s[o]->write(p, n);
+    }
+};
+
+}  // namespace
+
 void run_files(tksm_seq* h, const char* mdf_path, const char* badread_path, const char* perfect_path,
                tksm_seq_stats* stats) {
-    const tksm_seq_config* cfg = engine_config(h);
-    const size_t max_reads = cfg->batch_reads ? (size_t)cfg->batch_reads : ((size_t)1 << 22);
-    const uint64_t max_bases = cfg->batch_bases ? cfg->batch_bases : (1ull << 30);
     Sink bad, perf;
     // the output files exist even when the MDF is empty (py/sequence.py:347, 356)
     if (badread_path) bad.open(badread_path);
@@ -84,61 +137,12 @@ void run_files(tksm_seq* h, const char* mdf_path, const char* badread_path, cons
         ~Closer() { fclose(f); }
     } closer{in};
 
-    MdfParser parser(engine_genome(h));
-    HostBatch hb;
-    std::vector<char> buf, out_bad, out_perf;
-    const size_t CHUNK = (size_t)64 << 20;
-    size_t have = 0;
-    bool eof = false;
-    uint64_t ordinal = 0;
+    FileSource src(in);
+    FileSinks sinks;
+    sinks.s[0] = badread_path ? &bad : nullptr;
+    sinks.s[1] = perfect_path ? &perf : nullptr;
     tksm_seq_stats total{};
-    auto flush = [&]() {
-        if (hb.n_reads() == 0) {
-            hb.clear();
-            return;
-        }
-        hb.ordinal_base = ordinal;
-        tksm_seq_stats s{};
-        engine_run_batch(h, hb, which, format, badread_path ? &out_bad : nullptr, perfect_path ? &out_perf : nullptr, &s);
-        ordinal += s.reads;
-        bad.write(out_bad.data(), badread_path ? out_bad.size() : 0);
-        perf.write(out_perf.data(), perfect_path ? out_perf.size() : 0);
-        total.reads += s.reads;
-        total.raw_bases += s.raw_bases;
-        total.read_bases += s.read_bases;
-        total.out_bytes[0] += s.out_bytes[0];
-        total.out_bytes[1] += s.out_bytes[1];
-        total.algorithmic_bytes += s.algorithmic_bytes;
-        total.h2d_bytes += s.h2d_bytes;
-        total.d2h_bytes += s.d2h_bytes;
-        total.kernel_ms += s.kernel_ms;
-        total.simulate_ms += s.simulate_ms;
-        total.kernel_launches += s.kernel_launches;
-        total.status_or |= s.status_or;
-        hb.clear();
-    };
-    while (true) {
-        if (!eof) {
-            buf.resize(have + CHUNK);
-            size_t n = fread(buf.data() + have, 1, CHUNK, in);
-            have += n;
-            if (n == 0) eof = true;
-        }
-        size_t pos = 0;
-        while (true) {
-            size_t used = parser.feed(buf.data() + pos, have - pos, eof, hb, max_reads, max_bases);
-            pos += used;
-            if (hb.n_reads() >= max_reads || hb.total_raw_bases >= max_bases)
-                flush();
-            else
-                break;
-            if (used == 0) break;
-        }
-        memmove(buf.data(), buf.data() + pos, have - pos);
-        have -= pos;
-        if (eof) break;
-    }
-    flush();
+    engine_stream(h, src, which, format, 0, &sinks, nullptr, nullptr, &total);
     bad.close();
     perf.close();
     if (stats) *stats = total;

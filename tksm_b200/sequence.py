@@ -127,6 +127,17 @@ class Sequencer:
         self.last_stats = st.as_dict()
         return data
 
+    def simulate_view(self, mdf_text, which=BADREAD, fastq=True, ordinal_base=0):
+        """Same call without the copy into a Python bytes object: returns a RecordBuffer that views the
+        library-owned (page-locked) record buffer; release it with .close() or a `with` block."""
+        b = mdf_text.encode() if isinstance(mdf_text, str) else mdf_text
+        out, n, st = C.c_void_p(), C.c_size_t(), Stats()
+        fmt = FASTQ if fastq else FASTA
+        self._ck(self._L.tksm_seq_simulate_text(self._h, b, len(b), which, fmt, ordinal_base, C.byref(out), C.byref(n),
+                                                C.byref(st)))
+        self.last_stats = st.as_dict()
+        return RecordBuffer(self._L, out, n.value)
+
     # ---- the __main__ loop (py/sequence.py:347-376)
     def run_files(self, mdf_path, badread=None, perfect=None):
         st = Stats()
@@ -148,6 +159,36 @@ class Sequencer:
             return C.string_at(out, n.value)
         finally:
             self._L.tksm_seq_free(out)
+
+
+class RecordBuffer:
+    """FASTQ/FASTA bytes owned by the library (tksm_seq_free releases them)."""
+
+    def __init__(self, L, ptr, n):
+        self._L, self._ptr, self.nbytes = L, ptr, n
+
+    def array(self):
+        return np.ctypeslib.as_array(C.cast(self._ptr, C.POINTER(C.c_uint8)), shape=(max(self.nbytes, 1),))[:self.nbytes]
+
+    def tobytes(self):
+        return C.string_at(self._ptr, self.nbytes)
+
+    def close(self):
+        if self._ptr:
+            self._L.tksm_seq_free(self._ptr)
+            self._ptr = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 class Batch:
