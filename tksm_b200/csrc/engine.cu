@@ -200,6 +200,7 @@ void need_device(tksm_seq* h) {
 void commit_reference(tksm_seq* h) {
     need_device(h);
     if (!h->genome_dirty) return;
+    h->genome.index_exceptions();
     CK(cudaSetDevice(h->cfg.device));
     if (!h->genome_synthetic) {
         upload_vec(h->d_genome, h->genome.words, h->stream);
@@ -322,9 +323,22 @@ void prepare_host(const tksm_seq* h, Prepared& p) {
     p.raw_off[R] = ro;
     p.idsum = idsum;
     for (int c = 0; c < N_CLASSES; c++) {
-        std::sort(keys[c].begin(), keys[c].end());
-        p.work[c].resize(keys[c].size());
-        for (size_t i = 0; i < keys[c].size(); i++) p.work[c][i] = (uint32_t)keys[c][i];
+        // keys are (~length, read): two 16-bit counting passes over the length half keep read order stable
+        std::vector<uint64_t>& k = keys[c];
+        const size_t nk = k.size();
+        p.work[c].resize(nk);
+        if (nk == 0) continue;
+        std::vector<uint64_t> tmp(nk);
+        std::vector<uint32_t> cnt(65537);
+        for (int pass = 0; pass < 2; pass++) {
+            const int sh = 32 + 16 * pass;
+            std::fill(cnt.begin(), cnt.end(), 0u);
+            for (size_t i = 0; i < nk; i++) cnt[((k[i] >> sh) & 0xFFFFu) + 1]++;
+            for (size_t i = 0; i < 65536; i++) cnt[i + 1] += cnt[i];
+            for (size_t i = 0; i < nk; i++) tmp[cnt[(k[i] >> sh) & 0xFFFFu]++] = k[i];
+            k.swap(tmp);
+        }
+        for (size_t i = 0; i < nk; i++) p.work[c][i] = (uint32_t)k[i];
     }
     // ceil(L_genomic / 4) + L_literal + 24 per interval + 5 per mod
     p.alg_in_bytes = (hb.genomic_bases + 3) / 4 + hb.literal_bases + 24 * per_read_segs + 5 * per_read_mods;
@@ -487,6 +501,10 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         P.cap_list = cap_list_c[c];
         P.slab_bytes = slab_c[c];
         P.gws = b->gws.as<uint8_t>();
+        {
+            static const int mode = getenv("TKSM_SIM_LOCKSTEP") ? atoi(getenv("TKSM_SIM_LOCKSTEP")) : 1;
+            P.lockstep = (uint32_t)mode;
+        }
         const int teams = c == GWS_CLASS ? 1 : SIM_WARPS / CLASS_W[c];
         int grid = (int)std::min<size_t>((size_t)h->num_sms, (P.n_work + teams - 1) / teams);
         switch (c) {
@@ -714,24 +732,53 @@ int host_threads(const tksm_seq* h) {
 }
 
 using PreparedList = std::vector<std::unique_ptr<Prepared>>;
+using HostBatchList = std::vector<std::unique_ptr<HostBatch>>;
 
-// one text chunk (complete records) -> one or more prepared device chunks
-PreparedList parse_chunk(const tksm_seq* h, const tk::TextChunk& tc) {
-    const size_t max_reads = h->cfg.batch_reads ? (size_t)h->cfg.batch_reads : ((size_t)1 << 18);
-    const uint64_t max_bases = h->cfg.batch_bases ? h->cfg.batch_bases : (1ull << 28);
-    PreparedList out;
+inline size_t limit_reads(const tksm_seq* h) { return h->cfg.batch_reads ? (size_t)h->cfg.batch_reads : ((size_t)1 << 18); }
+inline uint64_t limit_bases(const tksm_seq* h) { return h->cfg.batch_bases ? h->cfg.batch_bases : (1ull << 28); }
+
+// stage 1 (host threads): one text chunk of complete records -> molecule batches
+HostBatchList parse_chunk(const tksm_seq* h, const tk::TextChunk& tc) {
+    HostBatchList out;
     MdfParser parser(&h->genome);
     size_t pos = 0;
     while (true) {
-        std::unique_ptr<Prepared> p(new Prepared());
-        size_t used = parser.feed(tc.p + pos, tc.n - pos, true, p->hb, max_reads, max_bases);
+        std::unique_ptr<HostBatch> hb(new HostBatch());
+        size_t used = parser.feed(tc.p + pos, tc.n - pos, true, *hb, limit_reads(h), limit_bases(h));
         pos += used;
-        if (p->hb.n_reads()) {
-            prepare_host(h, *p);
-            out.push_back(std::move(p));
-        }
+        if (hb->n_reads()) out.push_back(std::move(hb));
         if (pos >= tc.n || used == 0) break;
     }
+    return out;
+}
+
+// stage 2 (host threads): the batches of consecutive text chunks, concatenated up to the device
+// batch limits, with scratch layout, work lists and upload blob
+PreparedList assemble_group(const tksm_seq* h, std::vector<std::shared_future<std::shared_ptr<HostBatchList>>>& parts) {
+    PreparedList out;
+    std::unique_ptr<Prepared> cur;
+    auto flush = [&]() {
+        if (cur && cur->hb.n_reads()) {
+            prepare_host(h, *cur);
+            out.push_back(std::move(cur));
+        }
+        cur.reset();
+    };
+    for (auto& f : parts) {
+        std::shared_ptr<HostBatchList> list = f.get();
+        for (auto& hb : *list) {
+            if (cur && (cur->hb.n_reads() + hb->n_reads() > limit_reads(h) ||
+                        cur->hb.total_raw_bases + hb->total_raw_bases > limit_bases(h)))
+                flush();
+            if (!cur) {
+                cur.reset(new Prepared());
+                cur->hb = std::move(*hb);
+            } else {
+                cur->hb.append(*hb);
+            }
+        }
+    }
+    flush();
     return out;
 }
 
@@ -821,28 +868,51 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
         add_stats(total, s);
     };
 
+    const bool trace = getenv("TKSM_SEQ_TRACE") != nullptr;
+    const auto t_begin = std::chrono::steady_clock::now();
+    auto now_ms = [&]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count(); };
+    double w_parse = 0, w_bind = 0, w_launch = 0, w_finish = 0, w_reuse = 0, dev_ms = 0;
     try {
         WorkerPool pool(nthreads);
-        const size_t max_pending = (size_t)nthreads * 2 + 2;
+        std::vector<std::shared_future<std::shared_ptr<HostBatchList>>> group;
+        size_t group_text = 0, group_target = 1, groups_made = 0;
+        const size_t max_group = 32;  // text chunks per device batch in steady state (1 MiB each)
+        auto close_group = [&]() {
+            if (group.empty()) return;
+            const tksm_seq* hc = h;
+            auto parts = std::make_shared<std::vector<std::shared_future<std::shared_ptr<HostBatchList>>>>(std::move(group));
+            pending.push_back({pool.submit([hc, parts]() { return assemble_group(hc, *parts); }), group_text});
+            group.clear();
+            group_text = 0;
+            groups_made++;
+            group_target = std::min(group_target * 2, max_group);  // small batches first: the device starts early
+        };
         while (true) {
             // keep the parser threads fed
-            while (!src_done && pending.size() < max_pending) {
+            while (!src_done && pending.size() < 4) {
                 TextChunk tc;
                 if (!src.next(tc)) {
                     src_done = true;
+                    close_group();
                     break;
                 }
                 text_total = std::max<uint64_t>(text_total, src.total_bytes_hint());
                 const tksm_seq* hc = h;
-                pending.push_back({pool.submit([hc, tc]() { return parse_chunk(hc, tc); }), tc.n});
+                group.push_back(pool.submit([hc, tc]() { return std::make_shared<HostBatchList>(parse_chunk(hc, tc)); }).share());
+                group_text += tc.n;
+                if (group.size() >= group_target) close_group();
             }
             if (pending.empty()) break;
+            double t0 = now_ms();
             PreparedList list = pending.front().fut.get();
+            w_parse += now_ms() - t0;
             text_done += pending.front().text_bytes;
             pending.pop_front();
             for (auto& pp : list) {
                 tksm_seq_batch* b = h->slots[issued % NS].get();
+                t0 = now_ms();
                 slot_reusable(b);
+                w_reuse += now_ms() - t0;
                 b->prep = std::move(*pp);
                 b->prep.hb.ordinal_base = ordinal;
                 ordinal += b->prep.hb.n_reads();
@@ -850,23 +920,35 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
                 cap_done += R * 128 + b->prep.idsum +
                             (o_arena == 0 ? b->prep.scr_off[R] * ((format & TKSM_SEQ_FASTQ_BADREAD) ? 2 : 1)
                                           : b->prep.hb.total_raw_bases * ((format & TKSM_SEQ_FASTQ_PERFECT) ? 2 : 1));
+                t0 = now_ms();
                 slot_bind(h, b);
+                double t1 = now_ms();
                 slot_launch(h, b, which, format);
+                double t2 = now_ms();
+                w_bind += t1 - t0;
+                w_launch += t2 - t1;
                 issued++;
                 inflight.push_back({b});
                 if (inflight.size() >= 2) {
                     finish(inflight.front().b);
                     inflight.pop_front();
                 }
+                w_finish += now_ms() - t2;
+                if (trace) fprintf(stderr, "[trace] chunk %zu reads %zu issued at %.2f ms\n", issued - 1, b->prep.hb.n_reads(), t0);
             }
         }
         while (!inflight.empty()) {
             finish(inflight.front().b);
             inflight.pop_front();
         }
+        if (trace)
+            fprintf(stderr, "[trace] drained at %.2f ms: wait parse %.2f, slot reuse %.2f, bind %.2f, launch %.2f, finish %.2f, kernels %.2f ms\n",
+                    now_ms(), w_parse, w_reuse, w_bind, w_launch, w_finish, total.kernel_ms);
         // flush the last downloads in chunk order
         for (size_t j = issued > (size_t)NS ? issued - NS : 0; j < issued; j++) slot_reusable(h->slots[j % NS].get());
         CK(cudaStreamSynchronize(h->copy_stream));
+        if (trace) fprintf(stderr, "[trace] done at %.2f ms\n", now_ms());
+        (void)dev_ms;
     } catch (...) {
         cudaStreamSynchronize(h->stream);
         cudaStreamSynchronize(h->copy_stream);
@@ -1204,8 +1286,9 @@ int tksm_seq_simulate_text(tksm_seq* h, const char* mdf, size_t mdf_len, int whi
     API_BEGIN
     if (which != TKSM_SEQ_BADREAD && which != TKSM_SEQ_PERFECT)
         throw std::runtime_error("simulate_text produces one output: TKSM_SEQ_BADREAD or TKSM_SEQ_PERFECT");
-    // text chunk size: starts at 1 MiB and doubles up to 8 MiB; TKSM_SEQ_CHUNK_BYTES pins it (tests)
-    size_t first = (size_t)1 << 20, max_t = (size_t)8 << 20;
+    // text is parsed in 1 MiB chunks (TKSM_SEQ_CHUNK_BYTES overrides, tests); consecutive chunks are
+    // grouped into device batches by the pipeline
+    size_t first = (size_t)1 << 20, max_t = (size_t)1 << 20;
     if (const char* e = getenv("TKSM_SEQ_CHUNK_BYTES")) first = max_t = std::max<size_t>((size_t)atoll(e), 1);
     MemorySource src(mdf, mdf_len, first, max_t);
     tk::engine_stream(h, src, which, format, ordinal_base, nullptr, out, out_len, stats);

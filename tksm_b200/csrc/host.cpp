@@ -98,8 +98,26 @@ void GenomeStore::load_fasta(const std::string& path) {
     load_fasta_text(text.data(), text.size());
 }
 
+void GenomeStore::index_exceptions() {
+    const uint64_t nblk = (n_bases >> EXC_BLOCK_SHIFT) + 2;
+    exc_block_bits.assign((size_t)((nblk + 63) / 64), 0);
+    for (size_t i = 0; i < exc_start.size(); i++) {
+        const uint64_t b0 = exc_start[i] >> EXC_BLOCK_SHIFT, b1 = (exc_start[i] + exc_len[i] - 1) >> EXC_BLOCK_SHIFT;
+        for (uint64_t b = b0; b <= b1; b++) exc_block_bits[(size_t)(b >> 6)] |= 1ull << (b & 63);
+    }
+    exc_indexed = exc_start.size();
+}
+
 bool GenomeStore::overlaps_exception(uint64_t start, uint64_t len) const {
     if (exc_start.empty() || len == 0) return false;
+    if (exc_indexed == exc_start.size() && !exc_block_bits.empty()) {
+        const uint64_t b0 = start >> EXC_BLOCK_SHIFT, b1 = (start + len - 1) >> EXC_BLOCK_SHIFT;
+        if (b1 - b0 < 8 && (b1 >> 6) < exc_block_bits.size()) {
+            bool any = false;
+            for (uint64_t b = b0; b <= b1; b++) any |= (exc_block_bits[(size_t)(b >> 6)] >> (b & 63)) & 1;
+            if (!any) return false;
+        }
+    }
     // first run with start >= `start`; the run before it may still reach into the range
     size_t i = (size_t)(std::lower_bound(exc_start.begin(), exc_start.end(), start) - exc_start.begin());
     if (i < exc_start.size() && exc_start[i] < start + len) return true;
@@ -144,6 +162,14 @@ void HostBatch::append(const HostBatch& o) {
     const uint32_t mol0 = (uint32_t)n_mols(), seg0 = (uint32_t)seg_src.size(), mod0 = (uint32_t)mod_pos.size();
     const uint64_t lit0 = lit_pool.size();
     const uint32_t id0 = (uint32_t)id_pool.size();
+    auto grow = [](auto& v, size_t extra) {
+        if (v.capacity() < v.size() + extra) v.reserve(std::max(v.capacity() * 2, v.size() + extra));
+    };
+    grow(read_mol, o.read_mol.size());
+    grow(mol_seg_begin, o.mol_seg_begin.size());
+    grow(mol_id_begin, o.mol_id_begin.size());
+    grow(seg_src, o.seg_src.size());
+    grow(seg_mod_begin, o.seg_mod_begin.size());
     for (uint32_t m : o.read_mol) read_mol.push_back(m + mol0);
     for (size_t i = 1; i < o.mol_seg_begin.size(); i++) mol_seg_begin.push_back(o.mol_seg_begin[i] + seg0);
     mol_raw_len.insert(mol_raw_len.end(), o.mol_raw_len.begin(), o.mol_raw_len.end());

@@ -29,6 +29,12 @@ struct GenomeStore {
     std::vector<uint64_t> exc_start;
     std::vector<uint32_t> exc_len;
     std::vector<uint8_t> exc_chr;
+    // one bit per 2^EXC_BLOCK_SHIFT bases: set when an exception run touches the block (built lazily by
+    // index_exceptions(); lets overlaps_exception() answer "no" without a search for most intervals)
+    static constexpr int EXC_BLOCK_SHIFT = 14;
+    std::vector<uint64_t> exc_block_bits;
+    size_t exc_indexed = 0;   // number of runs covered by exc_block_bits
+    void index_exceptions();
 
     void add_contig(const std::string& name, const char* seq, size_t len);
     void load_fasta(const std::string& path);              // plain or .gz

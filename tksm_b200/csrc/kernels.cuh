@@ -180,6 +180,7 @@ struct SimParams {
     uint32_t cap_list;      // touched-list capacity
     uint32_t slab_bytes;    // bytes of one team workspace
     uint8_t* gws;           // global workspaces (one per CTA) when GWS
+    uint32_t lockstep;      // 1: CTA-wide tickets, teams start their reads together
 };
 
 // Team workspace layout, shared by the host (sizing) and the kernel:
@@ -948,6 +949,21 @@ __global__ void __launch_bounds__(SIM_THREADS, 1) simulate_kernel(const SimParam
     else
         ws = smem + qcls_bytes + 64 + (size_t)tm.id * P.slab_bytes;
     uint32_t* ticket = (uint32_t*)(smem + qcls_bytes + 64 + (GWS ? 0 : (size_t)TEAMS * P.slab_bytes)) + tm.id;
+    if (P.lockstep) {
+        // The CTA takes TEAMS consecutive work items (near-equal lengths: the list is sorted) and its
+        // teams start each of them together, so the warps of a scheduler walk the same code at about
+        // the same time and share the instruction cache lines.
+        uint32_t* cta_ticket = ticket - tm.id;
+        while (true) {
+            if (threadIdx.x == 0) *cta_ticket = atomicAdd(P.counter, (uint32_t)TEAMS);
+            __syncthreads();
+            const uint32_t wi = *cta_ticket + (uint32_t)tm.id;
+            __syncthreads();
+            if (wi - (uint32_t)tm.id >= P.n_work) break;
+            if (wi < P.n_work) simulate_read<W, GWS>(tm, P, P.work[wi], ws, qcls_s, lut3);
+        }
+        return;
+    }
     while (true) {
         if (tm.rank == 0) *ticket = atomicAdd(P.counter, 1u);
         tm.sync();

@@ -76,7 +76,7 @@ struct FileSource : ChunkSource {
     FILE* in;
     std::string carry;   // bytes after the last record boundary of the previous block
     bool eof = false;
-    size_t target = (size_t)1 << 20, max_target = (size_t)8 << 20;
+    size_t target = (size_t)1 << 20, max_target = (size_t)1 << 20;
     explicit FileSource(FILE* f) : in(f) {
         if (const char* e = getenv("TKSM_SEQ_CHUNK_BYTES")) target = max_target = std::max<size_t>((size_t)atoll(e), 1);
     }
