@@ -2,6 +2,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <condition_variable>
@@ -100,9 +101,11 @@ inline uint32_t list_capacity(uint32_t ncap) { return ncap / 5 * 2 + 64; }
 // One parsed MDF chunk with everything the device needs, built by host threads only
 // (no CUDA call): scratch layout, length-class work lists and the upload blob.
 struct Prepared {
-    HostBatch hb;
-    std::vector<uint64_t> scr_off, raw_off;
-    std::vector<uint32_t> work[N_CLASSES];
+    uint64_t n_reads = 0, n_mols = 0;
+    uint64_t ordinal_base = 0;
+    uint64_t total_raw_bases = 0;
+    uint64_t scr_total = 0, raw_total = 0;   // bytes of the per-read scratch arenas
+    uint32_t n_work[N_CLASSES] = {};
     uint32_t max_n_gws = 0;
     uint64_t alg_in_bytes = 0, idsum = 0;
     bool mods = false;
@@ -288,92 +291,156 @@ void launch_sim(tksm_seq* h, const SimParams& P, size_t smem, int grid) {
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-// Host-only preparation of a parsed chunk: per-read scratch layout, length classes, upload blob.
-// Thread-safe with respect to the handle (reads the class capacities and k only).
-void prepare_host(const tksm_seq* h, Prepared& p) {
-    HostBatch& hb = p.hb;
-    const size_t R = hb.n_reads(), M = hb.n_mols(), S = hb.seg_src.size();
+// Host-only preparation of one device batch from the molecule batches of consecutive text chunks:
+// per-read scratch layout, length classes and the upload blob, written in one pass (the parts are
+// concatenated straight into the blob with their indices rebased).  Thread-safe with respect to
+// the handle (reads the class capacities and k only).
+void prepare_host(const tksm_seq* h, const std::vector<const HostBatch*>& parts, Prepared& p) {
     const uint32_t k = (uint32_t)h->em.k;
-    p.scr_off.resize(R + 1);
-    p.raw_off.resize(R + 1);
-    uint64_t so = 0, ro = 0;
-    p.max_n_gws = 0;
-    p.mods = !hb.mod_pos.empty();
-    // (length, read) keys per class, sorted longest first: the tail of the dynamic schedule is then
-    // made of short reads, and neighbouring work items have near-equal lengths
-    std::vector<uint64_t> keys[N_CLASSES];
-    uint64_t per_read_segs = 0, per_read_mods = 0, idsum = 0;
-    for (size_t r = 0; r < R; r++) {
-        const uint32_t m = hb.read_mol[r];
-        const uint32_t L = hb.mol_raw_len[m];
-        p.scr_off[r] = so;
-        p.raw_off[r] = ro;
-        so += align_up((size_t)2 * L + 32, 16);
-        ro += align_up((size_t)L, 16);
-        const uint32_t n = L + 2 * k;
-        int c = 0;
-        while (c < GWS_CLASS && n > h->ncap[c]) c++;
-        keys[c].push_back(((uint64_t)(0xFFFFFFFFu - L) << 32) | (uint32_t)r);
-        if (c == GWS_CLASS) p.max_n_gws = std::max(p.max_n_gws, n);
-        per_read_segs += hb.mol_seg_begin[m + 1] - hb.mol_seg_begin[m];
-        if (p.mods) per_read_mods += hb.seg_mod_begin[hb.mol_seg_begin[m + 1]] - hb.seg_mod_begin[hb.mol_seg_begin[m]];
-        idsum += hb.mol_id_begin[m + 1] - hb.mol_id_begin[m];
+    size_t R = 0, M = 0, S = 0, NM = 0, LIT = 0, ID = 0;
+    uint64_t raw = 0, gen = 0, litb = 0;
+    for (const HostBatch* hb : parts) {
+        R += hb->n_reads();
+        M += hb->n_mols();
+        S += hb->seg_src.size();
+        NM += hb->mod_pos.size();
+        LIT += hb->lit_pool.size();
+        ID += hb->id_pool.size();
+        raw += hb->total_raw_bases;
+        gen += hb->genomic_bases;
+        litb += hb->literal_bases;
     }
-    p.scr_off[R] = so;
-    p.raw_off[R] = ro;
-    p.idsum = idsum;
-    for (int c = 0; c < N_CLASSES; c++) {
-        // keys are (~length, read): two 16-bit counting passes over the length half keep read order stable
-        std::vector<uint64_t>& k = keys[c];
-        const size_t nk = k.size();
-        p.work[c].resize(nk);
-        if (nk == 0) continue;
-        std::vector<uint64_t> tmp(nk);
-        std::vector<uint32_t> cnt(65537);
-        for (int pass = 0; pass < 2; pass++) {
-            const int sh = 32 + 16 * pass;
-            std::fill(cnt.begin(), cnt.end(), 0u);
-            for (size_t i = 0; i < nk; i++) cnt[((k[i] >> sh) & 0xFFFFu) + 1]++;
-            for (size_t i = 0; i < 65536; i++) cnt[i + 1] += cnt[i];
-            for (size_t i = 0; i < nk; i++) tmp[cnt[(k[i] >> sh) & 0xFFFFu]++] = k[i];
-            k.swap(tmp);
-        }
-        for (size_t i = 0; i < nk; i++) p.work[c][i] = (uint32_t)k[i];
-    }
-    // SURVEY.md 8(d): ceil(L_genomic / 4) + L_literal + 24 per interval + 5 per mod
-    p.alg_in_bytes = (hb.genomic_bases + 3) / 4 + hb.literal_bases + 24 * per_read_segs + 5 * per_read_mods;
-
-    struct Part {
-        const void* src;
-        size_t bytes;
-        size_t off;
-    };
-    std::vector<Part> parts;
+    if (R > 0xFFFFFFF0ull || S > 0xFFFFFFF0ull || ID > 0xFFFFFFF0ull) throw std::runtime_error("device batch too large");
+    p.n_reads = R;
+    p.n_mols = M;
+    p.total_raw_bases = raw;
+    p.mods = NM > 0;
     size_t total = 0;
-    auto add = [&](const void* src, size_t bytes) {
+    auto add = [&](size_t bytes) {
         size_t off = total;
-        parts.push_back({src, bytes, off});
         total = align_up(total + std::max<size_t>(bytes, 1), 256);
         return off;
     };
-    p.o_read_mol = add(hb.read_mol.data(), R * 4);
-    p.o_msb = add(hb.mol_seg_begin.data(), (M + 1) * 4);
-    p.o_mrl = add(hb.mol_raw_len.data(), M * 4);
-    p.o_mib = add(hb.mol_id_begin.data(), (M + 1) * 4);
-    p.o_src = add(hb.seg_src.data(), S * 8);
-    p.o_len = add(hb.seg_len.data(), S * 4);
-    p.o_smb = add(hb.seg_mod_begin.data(), p.mods ? (S + 1) * 4 : 0);
-    p.o_mp = add(hb.mod_pos.data(), hb.mod_pos.size() * 4);
-    p.o_mc = add(hb.mod_chr.data(), hb.mod_chr.size());
-    p.o_lit = add(hb.lit_pool.data(), hb.lit_pool.size());
-    p.o_id = add(hb.id_pool.data(), hb.id_pool.size());
-    p.o_so = add(p.scr_off.data(), (R + 1) * 8);
-    p.o_ro = add(p.raw_off.data(), (R + 1) * 8);
-    for (int c = 0; c < N_CLASSES; c++) p.o_work[c] = add(p.work[c].data(), p.work[c].size() * 4);
+    p.o_read_mol = add(R * 4);
+    p.o_msb = add((M + 1) * 4);
+    p.o_mrl = add(M * 4);
+    p.o_mib = add((M + 1) * 4);
+    p.o_src = add(S * 8);
+    p.o_len = add(S * 4);
+    p.o_smb = add(p.mods ? (S + 1) * 4 : 0);
+    p.o_mp = add(NM * 4);
+    p.o_mc = add(NM);
+    p.o_lit = add(LIT);
+    p.o_id = add(ID);
+    p.o_so = add((R + 1) * 8);
+    p.o_ro = add((R + 1) * 8);
+    const size_t o_work_area = add(R * 4 + (size_t)N_CLASSES * 256);
     p.blob.reset(new char[total]);
     p.blob_bytes = total;
-    for (auto& q : parts)
-        if (q.bytes) memcpy(p.blob.get() + q.off, q.src, q.bytes);
+    char* B = p.blob.get();
+    uint32_t* read_mol = (uint32_t*)(B + p.o_read_mol);
+    uint32_t* msb = (uint32_t*)(B + p.o_msb);
+    uint32_t* mrl = (uint32_t*)(B + p.o_mrl);
+    uint32_t* mib = (uint32_t*)(B + p.o_mib);
+    uint64_t* src = (uint64_t*)(B + p.o_src);
+    uint32_t* slen = (uint32_t*)(B + p.o_len);
+    uint32_t* smb = (uint32_t*)(B + p.o_smb);
+    uint32_t* mp = (uint32_t*)(B + p.o_mp);
+    uint8_t* mc = (uint8_t*)(B + p.o_mc);
+    uint8_t* lit = (uint8_t*)(B + p.o_lit);
+    uint8_t* idp = (uint8_t*)(B + p.o_id);
+    uint64_t* scr_off = (uint64_t*)(B + p.o_so);
+    uint64_t* raw_off = (uint64_t*)(B + p.o_ro);
+
+    // (length, read) keys per class, sorted longest first: the tail of the dynamic schedule is then
+    // made of short reads, and neighbouring work items have near-equal lengths
+    std::vector<uint64_t> keys[N_CLASSES];
+    for (int c = 0; c < 2; c++) keys[c].reserve(R);
+    uint64_t so = 0, ro = 0, per_read_segs = 0, per_read_mods = 0, idsum = 0;
+    p.max_n_gws = 0;
+    size_t r0 = 0, m0 = 0, s0 = 0, nm0 = 0, lit0 = 0, id0 = 0;
+    msb[0] = 0;
+    mib[0] = 0;
+    if (p.mods) smb[0] = 0;
+    for (const HostBatch* hbp : parts) {
+        const HostBatch& hb = *hbp;
+        const size_t r_n = hb.n_reads(), m_n = hb.n_mols(), s_n = hb.seg_src.size(), nm_n = hb.mod_pos.size();
+        for (size_t r = 0; r < r_n; r++) {
+            const uint32_t m = hb.read_mol[r];
+            const uint32_t L = hb.mol_raw_len[m];
+            read_mol[r0 + r] = (uint32_t)(m0 + m);
+            scr_off[r0 + r] = so;
+            raw_off[r0 + r] = ro;
+            so += align_up((size_t)2 * L + 32, 16);
+            ro += align_up((size_t)L, 16);
+            const uint32_t n = L + 2 * k;
+            int c = 0;
+            while (c < GWS_CLASS && n > h->ncap[c]) c++;
+            keys[c].push_back(((uint64_t)(0xFFFFFFFFu - L) << 32) | (uint32_t)(r0 + r));
+            if (c == GWS_CLASS) p.max_n_gws = std::max(p.max_n_gws, n);
+            per_read_segs += hb.mol_seg_begin[m + 1] - hb.mol_seg_begin[m];
+            if (nm_n) per_read_mods += hb.seg_mod_begin[hb.mol_seg_begin[m + 1]] - hb.seg_mod_begin[hb.mol_seg_begin[m]];
+            idsum += hb.mol_id_begin[m + 1] - hb.mol_id_begin[m];
+        }
+        for (size_t m = 0; m < m_n; m++) {
+            msb[m0 + m + 1] = (uint32_t)(s0 + hb.mol_seg_begin[m + 1]);
+            mib[m0 + m + 1] = (uint32_t)(id0 + hb.mol_id_begin[m + 1]);
+        }
+        if (m_n) memcpy(mrl + m0, hb.mol_raw_len.data(), m_n * 4);
+        if (lit0 == 0) {
+            if (s_n) memcpy(src + s0, hb.seg_src.data(), s_n * 8);
+        } else {
+            for (size_t i = 0; i < s_n; i++) {
+                const uint64_t v = hb.seg_src[i];
+                src[s0 + i] = (v & SEG_LITERAL) ? v + lit0 : v;
+            }
+        }
+        if (s_n) memcpy(slen + s0, hb.seg_len.data(), s_n * 4);
+        if (p.mods)
+            for (size_t i = 0; i < s_n; i++) smb[s0 + i + 1] = (uint32_t)(nm0 + hb.seg_mod_begin[i + 1]);
+        if (nm_n) {
+            memcpy(mp + nm0, hb.mod_pos.data(), nm_n * 4);
+            memcpy(mc + nm0, hb.mod_chr.data(), nm_n);
+        }
+        if (!hb.lit_pool.empty()) memcpy(lit + lit0, hb.lit_pool.data(), hb.lit_pool.size());
+        if (!hb.id_pool.empty()) memcpy(idp + id0, hb.id_pool.data(), hb.id_pool.size());
+        r0 += r_n;
+        m0 += m_n;
+        s0 += s_n;
+        nm0 += nm_n;
+        lit0 += hb.lit_pool.size();
+        id0 += hb.id_pool.size();
+    }
+    scr_off[R] = so;
+    raw_off[R] = ro;
+    p.scr_total = so;
+    p.raw_total = ro;
+    p.idsum = idsum;
+    size_t wpos = o_work_area;
+    std::vector<uint64_t> tmp;
+    std::vector<uint32_t> cnt(65537);
+    for (int c = 0; c < N_CLASSES; c++) {
+        // keys are (~length, read): two 16-bit counting passes over the length half keep read order stable
+        std::vector<uint64_t>& kk = keys[c];
+        const size_t nk = kk.size();
+        p.n_work[c] = (uint32_t)nk;
+        p.o_work[c] = wpos;
+        wpos = align_up(wpos + nk * 4, 256);
+        if (nk == 0) continue;
+        tmp.resize(nk);
+        for (int pass = 0; pass < 2; pass++) {
+            const int sh = 32 + 16 * pass;
+            std::fill(cnt.begin(), cnt.end(), 0u);
+            for (size_t i = 0; i < nk; i++) cnt[((kk[i] >> sh) & 0xFFFFu) + 1]++;
+            for (size_t i = 0; i < 65536; i++) cnt[i + 1] += cnt[i];
+            for (size_t i = 0; i < nk; i++) tmp[cnt[(kk[i] >> sh) & 0xFFFFu]++] = kk[i];
+            kk.swap(tmp);
+        }
+        uint32_t* w = (uint32_t*)(B + p.o_work[c]);
+        for (size_t i = 0; i < nk; i++) w[i] = (uint32_t)kk[i];
+    }
+    // SURVEY.md 8(d): ceil(L_genomic / 4) + L_literal + 24 per interval + 5 per mod
+    p.alg_in_bytes = (gen + 3) / 4 + litb + 24 * per_read_segs + 5 * per_read_mods;
 }
 
 // Uploads the prepared chunk of slot `b` (asynchronously on the compute stream).
@@ -383,7 +450,7 @@ void slot_bind(tksm_seq* h, tksm_seq_batch* b) {
     commit_reference(h);
     CK(cudaSetDevice(h->cfg.device));
     Prepared& p = b->prep;
-    const size_t R = p.hb.n_reads();
+    const size_t R = p.n_reads;
     b->stage.ensure(p.blob_bytes);
     memcpy(b->stage.p, p.blob.get(), p.blob_bytes);
     p.blob.reset();
@@ -393,7 +460,7 @@ void slot_bind(tksm_seq* h, tksm_seq_batch* b) {
     char* base = (char*)b->blob.p;
     DevBatch& D = b->db;
     D.n_reads = (uint32_t)R;
-    D.ordinal_base = p.hb.ordinal_base;
+    D.ordinal_base = p.ordinal_base;
     D.read_mol = (const uint32_t*)(base + p.o_read_mol);
     D.mol_seg_begin = (const uint32_t*)(base + p.o_msb);
     D.mol_raw_len = (const uint32_t*)(base + p.o_mrl);
@@ -438,8 +505,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
     if (!b->bound) throw std::runtime_error("batch not uploaded");
     CK(cudaSetDevice(h->cfg.device));
     Prepared& p = b->prep;
-    HostBatch& hb = p.hb;
-    const uint32_t R = (uint32_t)hb.n_reads();
+    const uint32_t R = (uint32_t)p.n_reads;
     b->which = which;
     b->out_bytes[0] = b->out_bytes[1] = 0;
     b->launches = 0;
@@ -453,16 +519,16 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
     if (want_bad && fastq && !h->cfg.skip_qual_compute) flags |= RUN_QUAL;  // py/sequence.py:349-353
     if (want_perf) flags |= RUN_RAW;
     if (want_bad) {
-        b->scr_seq.ensure(p.scr_off[R]);
-        if (flags & RUN_QUAL) b->scr_qual.ensure(p.scr_off[R]);
+        b->scr_seq.ensure(p.scr_total);
+        if (flags & RUN_QUAL) b->scr_qual.ensure(p.scr_total);
     }
-    if (want_perf) b->scr_raw.ensure(std::max<uint64_t>(p.raw_off[R], 16));
+    if (want_perf) b->scr_raw.ensure(std::max<uint64_t>(p.raw_total, 16));
     D.scr_seq = b->scr_seq.as<uint8_t>();
     D.scr_qual = b->scr_qual.as<uint8_t>();
     D.scr_raw = want_perf ? b->scr_raw.as<uint8_t>() : nullptr;
     // output upper bounds
-    b->out_cap[0] = want_bad ? (uint64_t)R * 128 + p.idsum + p.scr_off[R] * (fastq ? 2 : 1) : 0;
-    b->out_cap[1] = want_perf ? (uint64_t)R * 128 + p.idsum + hb.total_raw_bases * (fastq_o[1] ? 2 : 1) : 0;
+    b->out_cap[0] = want_bad ? (uint64_t)R * 128 + p.idsum + p.scr_total * (fastq ? 2 : 1) : 0;
+    b->out_cap[1] = want_perf ? (uint64_t)R * 128 + p.idsum + p.total_raw_bases * (fastq_o[1] ? 2 : 1) : 0;
     if (want_bad) b->out[0].ensure(b->out_cap[0]);
     if (want_perf) b->out[1].ensure(b->out_cap[1]);
     for (int o = 0; o < 2; o++)
@@ -489,12 +555,12 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
     CK(cudaEventRecord(b->ev[0], h->stream));
     uint32_t launches = 0;
     for (int c = 0; c < N_CLASSES; c++) {
-        if (p.work[c].empty()) continue;
+        if (p.n_work[c] == 0) continue;
         SimParams P;
         P.T = h->dt;
         P.B = D;
         P.work = b->d_work[c];
-        P.n_work = (uint32_t)p.work[c].size();
+        P.n_work = p.n_work[c];
         P.counter = b->counters.as<uint32_t>() + c;
         P.flags = flags;
         P.ncap = ncap_c[c];
@@ -522,7 +588,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         if (!((o == 0 && want_bad) || (o == 1 && want_perf))) continue;
         FmtParams F{};
         F.n_reads = R;
-        F.ordinal_base = hb.ordinal_base;
+        F.ordinal_base = p.ordinal_base;
         F.seed_lo = h->dt.seed_lo;
         F.seed_hi = h->dt.seed_hi;
         F.read_mol = D.read_mol;
@@ -566,10 +632,9 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
 // Waits for the kernels of slot `b` and fills the statistics of the chunk.
 void slot_wait(tksm_seq* h, tksm_seq_batch* b, tksm_seq_stats* st) {
     Prepared& p = b->prep;
-    HostBatch& hb = p.hb;
     tksm_seq_stats s{};
-    s.reads = hb.n_reads();
-    s.raw_bases = hb.total_raw_bases;
+    s.reads = p.n_reads;
+    s.raw_bases = p.total_raw_bases;
     s.h2d_bytes = b->h2d_bytes;
     if (s.reads == 0) {
         CK(cudaStreamSynchronize(h->stream));
@@ -597,7 +662,7 @@ void slot_wait(tksm_seq* h, tksm_seq_batch* b, tksm_seq_stats* st) {
         if (s.status_or & (ST_OPS_OVERFLOW | ST_SCRATCH_OVERFLOW))
             throw std::runtime_error("a read outgrew its scratch slot (insertion-heavy read); rerun unsupported");
     } else {
-        s.read_bases = hb.total_raw_bases;
+        s.read_bases = p.total_raw_bases;
     }
     if (st) *st = s;
 }
@@ -731,6 +796,14 @@ int host_threads(const tksm_seq* h) {
     return (int)std::min<unsigned>(std::max<unsigned>(hc, 1), 32);
 }
 
+std::atomic<uint64_t> g_ns_parse{0}, g_ns_append{0}, g_ns_prepare{0};
+struct ScopedNs {
+    std::atomic<uint64_t>& acc;
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    explicit ScopedNs(std::atomic<uint64_t>& a) : acc(a) {}
+    ~ScopedNs() { acc += (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count(); }
+};
+
 using PreparedList = std::vector<std::unique_ptr<Prepared>>;
 using HostBatchList = std::vector<std::unique_ptr<HostBatch>>;
 
@@ -739,11 +812,23 @@ inline uint64_t limit_bases(const tksm_seq* h) { return h->cfg.batch_bases ? h->
 
 // stage 1 (host threads): one text chunk of complete records -> molecule batches
 HostBatchList parse_chunk(const tksm_seq* h, const tk::TextChunk& tc) {
+    ScopedNs timer(g_ns_parse);
     HostBatchList out;
     MdfParser parser(&h->genome);
     size_t pos = 0;
     while (true) {
         std::unique_ptr<HostBatch> hb(new HostBatch());
+        if (pos == 0) {  // typical shapes: ~25 text bytes per interval line, ~8 lines per molecule
+            const size_t lines = tc.n / 22 + 16;
+            hb->seg_src.reserve(lines);
+            hb->seg_len.reserve(lines);
+            hb->seg_mod_begin.reserve(lines + 1);
+            hb->read_mol.reserve(lines / 4);
+            hb->mol_raw_len.reserve(lines / 4);
+            hb->mol_seg_begin.reserve(lines / 4 + 1);
+            hb->mol_id_begin.reserve(lines / 4 + 1);
+            hb->id_pool.reserve(tc.n / 16);
+        }
         size_t used = parser.feed(tc.p + pos, tc.n - pos, true, *hb, limit_reads(h), limit_bases(h));
         pos += used;
         if (hb->n_reads()) out.push_back(std::move(hb));
@@ -756,26 +841,27 @@ HostBatchList parse_chunk(const tksm_seq* h, const tk::TextChunk& tc) {
 // batch limits, with scratch layout, work lists and upload blob
 PreparedList assemble_group(const tksm_seq* h, std::vector<std::shared_future<std::shared_ptr<HostBatchList>>>& parts) {
     PreparedList out;
-    std::unique_ptr<Prepared> cur;
+    std::vector<std::shared_ptr<HostBatchList>> lists;
+    std::vector<const HostBatch*> cur;
+    uint64_t cur_reads = 0, cur_bases = 0;
     auto flush = [&]() {
-        if (cur && cur->hb.n_reads()) {
-            prepare_host(h, *cur);
-            out.push_back(std::move(cur));
+        if (!cur.empty()) {
+            ScopedNs timer(g_ns_prepare);
+            std::unique_ptr<Prepared> p(new Prepared());
+            prepare_host(h, cur, *p);
+            out.push_back(std::move(p));
         }
-        cur.reset();
+        cur.clear();
+        cur_reads = cur_bases = 0;
     };
     for (auto& f : parts) {
-        std::shared_ptr<HostBatchList> list = f.get();
-        for (auto& hb : *list) {
-            if (cur && (cur->hb.n_reads() + hb->n_reads() > limit_reads(h) ||
-                        cur->hb.total_raw_bases + hb->total_raw_bases > limit_bases(h)))
+        lists.push_back(f.get());
+        for (auto& hb : *lists.back()) {
+            if (!cur.empty() && (cur_reads + hb->n_reads() > limit_reads(h) || cur_bases + hb->total_raw_bases > limit_bases(h)))
                 flush();
-            if (!cur) {
-                cur.reset(new Prepared());
-                cur->hb = std::move(*hb);
-            } else {
-                cur->hb.append(*hb);
-            }
+            cur.push_back(hb.get());
+            cur_reads += hb->n_reads();
+            cur_bases += hb->total_raw_bases;
         }
     }
     flush();
@@ -914,12 +1000,12 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
                 slot_reusable(b);
                 w_reuse += now_ms() - t0;
                 b->prep = std::move(*pp);
-                b->prep.hb.ordinal_base = ordinal;
-                ordinal += b->prep.hb.n_reads();
-                const uint64_t R = b->prep.hb.n_reads();
+                b->prep.ordinal_base = ordinal;
+                ordinal += b->prep.n_reads;
+                const uint64_t R = b->prep.n_reads;
                 cap_done += R * 128 + b->prep.idsum +
-                            (o_arena == 0 ? b->prep.scr_off[R] * ((format & TKSM_SEQ_FASTQ_BADREAD) ? 2 : 1)
-                                          : b->prep.hb.total_raw_bases * ((format & TKSM_SEQ_FASTQ_PERFECT) ? 2 : 1));
+                            (o_arena == 0 ? b->prep.scr_total * ((format & TKSM_SEQ_FASTQ_BADREAD) ? 2 : 1)
+                                          : b->prep.total_raw_bases * ((format & TKSM_SEQ_FASTQ_PERFECT) ? 2 : 1));
                 t0 = now_ms();
                 slot_bind(h, b);
                 double t1 = now_ms();
@@ -934,7 +1020,7 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
                     inflight.pop_front();
                 }
                 w_finish += now_ms() - t2;
-                if (trace) fprintf(stderr, "[trace] chunk %zu reads %zu issued at %.2f ms\n", issued - 1, b->prep.hb.n_reads(), t0);
+                if (trace) fprintf(stderr, "[trace] chunk %zu reads %zu issued at %.2f ms\n", issued - 1, (size_t)b->prep.n_reads, t0);
             }
         }
         while (!inflight.empty()) {
@@ -947,7 +1033,9 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
         // flush the last downloads in chunk order
         for (size_t j = issued > (size_t)NS ? issued - NS : 0; j < issued; j++) slot_reusable(h->slots[j % NS].get());
         CK(cudaStreamSynchronize(h->copy_stream));
-        if (trace) fprintf(stderr, "[trace] done at %.2f ms\n", now_ms());
+        if (trace)
+            fprintf(stderr, "[trace] done at %.2f ms; host thread time: parse %.1f ms, append %.1f ms, prepare %.1f ms (cumulative)\n",
+                    now_ms(), g_ns_parse.load() / 1e6, g_ns_append.load() / 1e6, g_ns_prepare.load() / 1e6);
         (void)dev_ms;
     } catch (...) {
         cudaStreamSynchronize(h->stream);
@@ -1247,9 +1335,10 @@ tksm_seq_batch* tksm_seq_batch_create(tksm_seq* h, const char* mdf, size_t mdf_l
     std::unique_ptr<tksm_seq_batch> b(new tksm_seq_batch());
     try {
         MdfParser parser(&h->genome);
-        b->prep.hb.ordinal_base = ordinal_base;
-        parser.feed(mdf, mdf_len, true, b->prep.hb);
-        prepare_host(h, b->prep);
+        HostBatch hb;
+        parser.feed(mdf, mdf_len, true, hb);
+        prepare_host(h, {&hb}, b->prep);
+        b->prep.ordinal_base = ordinal_base;
         if (!h->cfg.host_only) {
             slot_bind(h, b.get());
             CK(cudaStreamSynchronize(h->stream));
