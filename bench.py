@@ -96,6 +96,7 @@ def main():
     ap.add_argument("--molecules", type=int, default=1_000_000)
     ap.add_argument("--genome-scale", type=float, default=1.0, help="fraction of the 3.1 Gbp genome (tests)")
     ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--identity", default="84,99,5.5", help="--badread-identity mean,max,stdev (experiments)")
     ap.add_argument("--cpu-sample", type=int, default=0, help="molecules in the CPU baseline sample (0 = auto)")
     args = ap.parse_args()
 
@@ -104,7 +105,7 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     config = {"workload": "BASELINE configs[1]: README bulk Tsb->Trc->plA->Flp->Tag->Seq, "
                           f"{args.molecules} molecules per GPU, synthetic {3.1 * args.genome_scale:.2f} Gbp genome, "
-                          "nanopore2020 error+qscore models, identity 84,99,5.5, FASTQ with qscores",
+                          f"nanopore2020 error+qscore models, identity {args.identity}, FASTQ with qscores",
               "molecules_per_gpu": args.molecules, "sharding": f"independent molecule shards x{world}, no collective",
               "l2": "inputs+outputs (>3 GB per step) exceed the 126 MB L2; no explicit flush"}
 
@@ -120,7 +121,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from tksm_b200.sequence import BADREAD, FASTQ, PERFECT, Sequencer
 
-    s = Sequencer(seed=42, device=local)
+    s = Sequencer(identity=tuple(float(x) for x in args.identity.split(",")), seed=42, device=local)
     lengths = [max(1000, int(x * args.genome_scale)) for x in GRCH38]
     s.synth_reference(NAMES, lengths, n_frac=0.01, seed=42)
     have = os.path.exists(os.path.join(os.environ["TKSM_MODELS"], "badread", "nanopore2020.error.gz"))

@@ -112,7 +112,7 @@ struct Prepared {
     std::unique_ptr<char[]> blob;
     size_t blob_bytes = 0;
     size_t o_read_mol = 0, o_msb = 0, o_mrl = 0, o_mib = 0, o_src = 0, o_len = 0, o_smb = 0, o_mp = 0, o_mc = 0, o_lit = 0,
-           o_id = 0, o_so = 0, o_ro = 0, o_work[N_CLASSES] = {};
+           o_id = 0, o_so = 0, o_ro = 0;
 };
 
 // A device slot: the buffers of one chunk in flight.  The same object backs the device-resident
@@ -122,7 +122,7 @@ struct tksm_seq_batch {
     DBuf blob;
     DevBatch db{};
     uint32_t* d_work[N_CLASSES] = {};
-    DBuf scr_seq, scr_qual, scr_raw, per_read, out[2], rec_len[2], rec_off[2], sums, gws, counters;
+    DBuf scr_seq, scr_qual, scr_raw, per_read, out[2], rec_len[2], rec_off[2], sums, gws, counters, work_keys, work_sorted, work_bins;
     HBuf stage;           // pinned upload staging
     HBuf host_out[2];     // pinned download staging (streaming to files)
     HBuf h_tot;           // pinned: record bytes per output, read bases, status
@@ -140,7 +140,7 @@ struct tksm_seq_batch {
     }
     ~tksm_seq_batch() {
         for (DBuf* d : {&blob, &scr_seq, &scr_qual, &scr_raw, &per_read, &out[0], &out[1], &rec_len[0], &rec_len[1],
-                        &rec_off[0], &rec_off[1], &sums, &gws, &counters})
+                        &rec_off[0], &rec_off[1], &sums, &gws, &counters, &work_keys, &work_sorted, &work_bins})
             d->release();
         stage.release();
         host_out[0].release();
@@ -334,7 +334,6 @@ void prepare_host(const tksm_seq* h, const std::vector<const HostBatch*>& parts,
     p.o_id = add(ID);
     p.o_so = add((R + 1) * 8);
     p.o_ro = add((R + 1) * 8);
-    const size_t o_work_area = add(R * 4 + (size_t)N_CLASSES * 256);
     p.blob.reset(new char[total]);
     p.blob_bytes = total;
     char* B = p.blob.get();
@@ -352,10 +351,7 @@ void prepare_host(const tksm_seq* h, const std::vector<const HostBatch*>& parts,
     uint64_t* scr_off = (uint64_t*)(B + p.o_so);
     uint64_t* raw_off = (uint64_t*)(B + p.o_ro);
 
-    // (length, read) keys per class, sorted longest first: the tail of the dynamic schedule is then
-    // made of short reads, and neighbouring work items have near-equal lengths
-    std::vector<uint64_t> keys[N_CLASSES];
-    for (int c = 0; c < 2; c++) keys[c].reserve(R);
+    for (int c = 0; c < N_CLASSES; c++) p.n_work[c] = 0;
     uint64_t so = 0, ro = 0, per_read_segs = 0, per_read_mods = 0, idsum = 0;
     p.max_n_gws = 0;
     size_t r0 = 0, m0 = 0, s0 = 0, nm0 = 0, lit0 = 0, id0 = 0;
@@ -376,7 +372,7 @@ void prepare_host(const tksm_seq* h, const std::vector<const HostBatch*>& parts,
             const uint32_t n = L + 2 * k;
             int c = 0;
             while (c < GWS_CLASS && n > h->ncap[c]) c++;
-            keys[c].push_back(((uint64_t)(0xFFFFFFFFu - L) << 32) | (uint32_t)(r0 + r));
+            p.n_work[c]++;  // the device sorts the reads of each class (work_key / scan / scatter kernels)
             if (c == GWS_CLASS) p.max_n_gws = std::max(p.max_n_gws, n);
             per_read_segs += hb.mol_seg_begin[m + 1] - hb.mol_seg_begin[m];
             if (nm_n) per_read_mods += hb.seg_mod_begin[hb.mol_seg_begin[m + 1]] - hb.seg_mod_begin[hb.mol_seg_begin[m]];
@@ -416,29 +412,6 @@ void prepare_host(const tksm_seq* h, const std::vector<const HostBatch*>& parts,
     p.scr_total = so;
     p.raw_total = ro;
     p.idsum = idsum;
-    size_t wpos = o_work_area;
-    std::vector<uint64_t> tmp;
-    std::vector<uint32_t> cnt(65537);
-    for (int c = 0; c < N_CLASSES; c++) {
-        // keys are (~length, read): two 16-bit counting passes over the length half keep read order stable
-        std::vector<uint64_t>& kk = keys[c];
-        const size_t nk = kk.size();
-        p.n_work[c] = (uint32_t)nk;
-        p.o_work[c] = wpos;
-        wpos = align_up(wpos + nk * 4, 256);
-        if (nk == 0) continue;
-        tmp.resize(nk);
-        for (int pass = 0; pass < 2; pass++) {
-            const int sh = 32 + 16 * pass;
-            std::fill(cnt.begin(), cnt.end(), 0u);
-            for (size_t i = 0; i < nk; i++) cnt[((kk[i] >> sh) & 0xFFFFu) + 1]++;
-            for (size_t i = 0; i < 65536; i++) cnt[i + 1] += cnt[i];
-            for (size_t i = 0; i < nk; i++) tmp[cnt[(kk[i] >> sh) & 0xFFFFu]++] = kk[i];
-            kk.swap(tmp);
-        }
-        uint32_t* w = (uint32_t*)(B + p.o_work[c]);
-        for (size_t i = 0; i < nk; i++) w[i] = (uint32_t)kk[i];
-    }
     // ceil(L_genomic / 4) + L_literal + 24 per interval + 5 per mod
     p.alg_in_bytes = (gen + 3) / 4 + litb + 24 * per_read_segs + 5 * per_read_mods;
 }
@@ -474,7 +447,6 @@ void slot_bind(tksm_seq* h, tksm_seq_batch* b) {
     D.id_pool = (const uint8_t*)(base + p.o_id);
     D.scr_off = (const uint64_t*)(base + p.o_so);
     D.raw_off = (const uint64_t*)(base + p.o_ro);
-    for (int c = 0; c < N_CLASSES; c++) b->d_work[c] = (uint32_t*)(base + p.o_work[c]);
     b->per_read.ensure(std::max<size_t>(R, 1) * 16);
     D.read_len = b->per_read.as<uint32_t>();
     D.ident_num = D.read_len + R;
@@ -554,6 +526,42 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
 
     CK(cudaEventRecord(b->ev[0], h->stream));
     uint32_t launches = 0;
+    {
+        // device-side work order (kernels.cuh: class | identity bucket | length)
+        b->work_keys.ensure((size_t)R * 4);
+        b->work_sorted.ensure((size_t)R * 4);
+        b->work_bins.ensure((size_t)WORK_BINS * 4);
+        CK(cudaMemsetAsync(b->work_bins.p, 0, (size_t)WORK_BINS * 4, h->stream));
+        WorkSortParams WS{};
+        WS.n_reads = R;
+        WS.ordinal_base = p.ordinal_base;
+        WS.seed_lo = h->dt.seed_lo;
+        WS.seed_hi = h->dt.seed_hi;
+        WS.ident_const = h->dt.ident_const;
+        WS.k = (uint32_t)h->em.k;
+        WS.read_mol = D.read_mol;
+        WS.mol_raw_len = D.mol_raw_len;
+        for (int c = 0; c < 5; c++) WS.ncap[c] = ncap_c[c];
+        WS.gws_cap = ncap_c[GWS_CLASS];
+        for (int c = 0; c < N_CLASSES; c++) {
+            uint32_t sh = 0;
+            while ((ncap_c[c] >> sh) > 511u) sh++;
+            WS.len_shift[c] = sh;
+        }
+        WS.keys = b->work_keys.as<uint32_t>();
+        WS.bins = b->work_bins.as<uint32_t>();
+        WS.work = b->work_sorted.as<uint32_t>();
+        work_key_kernel<<<(R + 255) / 256, 256, 0, h->stream>>>(WS);
+        work_scan_kernel<<<1, 1024, 0, h->stream>>>(WS.bins);
+        work_scatter_kernel<<<(R + 255) / 256, 256, 0, h->stream>>>(WS);
+        CK(cudaGetLastError());
+        launches += 3;
+        uint32_t off = 0;
+        for (int c = 0; c < N_CLASSES; c++) {
+            b->d_work[c] = b->work_sorted.as<uint32_t>() + off;
+            off += p.n_work[c];
+        }
+    }
     for (int c = 0; c < N_CLASSES; c++) {
         if (p.n_work[c] == 0) continue;
         SimParams P;
@@ -568,7 +576,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         P.slab_bytes = slab_c[c];
         P.gws = b->gws.as<uint8_t>();
         {
-            static const int mode = getenv("TKSM_SIM_LOCKSTEP") ? atoi(getenv("TKSM_SIM_LOCKSTEP")) : 1;
+            static const int mode = getenv("TKSM_SIM_LOCKSTEP") ? atoi(getenv("TKSM_SIM_LOCKSTEP")) : 0;
             P.lockstep = (uint32_t)mode;
         }
         const int teams = c == GWS_CLASS ? 1 : SIM_WARPS / CLASS_W[c];

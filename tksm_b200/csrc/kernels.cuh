@@ -167,7 +167,7 @@ constexpr int SIM_WARPS = SIM_THREADS / 32;
 constexpr uint32_t MISC_WORDS = 64;  // per-team scratch words
 constexpr uint32_t MISC_WSUM = 8;    // W + 1 words of scan partials
 constexpr uint32_t MISC_LISTN = 40;  // touched-list length (teams of more than one warp)
-constexpr uint32_t QUEUE_BYTES = 64 * 4 + 64 * 2;  // per-warp compaction queue: 64 x (u32, u16)
+constexpr uint32_t QUEUE_BYTES = 64 * 4 + 64 * 4;  // per-warp compaction queue: 64 x (u32, u32)
 
 struct SimParams {
     DevTables T;
@@ -311,14 +311,14 @@ __device__ __forceinline__ uint32_t qscore_row(const DevTables& T, const uint8_t
 // shared memory and the warp drains 32 entries at a time with every lane busy.
 struct WarpQueue {
     uint32_t* a;
-    uint16_t* b;
+    uint32_t* b;
     uint32_t head, tail;  // warp-uniform
     __device__ __forceinline__ void push(bool pred, uint32_t va, uint32_t vb) {
         const uint32_t m = __ballot_sync(0xffffffffu, pred);
         if (pred) {
             const uint32_t slot = (tail + __popc(m & ((1u << (threadIdx.x & 31)) - 1))) & 63u;
             a[slot] = va;
-            b[slot] = (uint16_t)vb;
+            b[slot] = vb;
         }
         tail += __popc(m);
     }
@@ -355,7 +355,12 @@ __device__ __forceinline__ uint32_t nz4(uint32_t x, uint32_t mask) {
 // ------------------------------------------------------------ simulate one
 template <int W, bool GWS>
 __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams& P, uint32_t r, uint8_t* ws,
-                                              const uint8_t* qcls_s, const uint8_t* lut3) {
+                                              const uint8_t* qcls_s, const uint8_t* lut3, uint32_t phase_threads) {
+    // lockstep mode 2: the teams of the CTA also enter the error, expansion and qscore stages
+    // together (named barrier 15 over the threads of the teams that hold a read)
+    auto phase_sync = [&]() {
+        if (phase_threads) asm volatile("bar.sync 15, %0;" ::"r"(phase_threads) : "memory");
+    };
     using HistT = typename std::conditional<(GWS || W >= 8), uint64_t, uint32_t>::type;
     constexpr int SIZE = Team<W>::SIZE;
     const DevTables& T = P.T;
@@ -367,7 +372,7 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
     uint32_t* misc = (uint32_t*)(ws + LY.off_misc);
     uint32_t* wsum = misc + MISC_WSUM;
     uint32_t* wq_a = (uint32_t*)(ws + LY.off_queue + (uint32_t)(tm.rank >> 5) * QUEUE_BYTES);
-    uint16_t* wq_b = (uint16_t*)(wq_a + 64);
+    uint32_t* wq_b = wq_a + 64;
     uint32_t* list = (uint32_t*)(ws + LY.off_list);
     uint32_t* key = (uint32_t*)(ws + LY.off_key);
     uint8_t* keyb = (uint8_t*)key;
@@ -501,6 +506,7 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
     const uint16_t* thr_bin = T.thr + (size_t)bin * Q_CLASSES * THR_PER_CLASS;
     for (uint32_t c = tm.rank; c < Q_CLASSES; c += SIZE) T1[c] = thr_bin[c * THR_PER_CLASS];
     if (tm.rank == 0) misc[MISC_LISTN] = 0;
+    phase_sync();
 
     // ---- 3. error injection epochs
     uint32_t loss_c = 0, ins_c = 0, changed_c = 0;  // committed totals
@@ -737,6 +743,7 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
         }
     }
     tm.sync();
+    phase_sync();
 
     // ---- 4. slot contents are the low halves of the keys: content16, or 0xFFFF for an unchanged slot
     //         (dropped candidates were reset); the high halves are free for the cigar ops from here on
@@ -755,6 +762,35 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
     uint8_t* oseq = B.scr_seq + sbase;
     uint32_t carry = 0;
     const uint32_t opcap = 2 * n;
+    WarpQueue xq{wq_a, wq_b, 0, 0};
+    auto expand_changed = [&](uint32_t cnt) {
+        uint32_t pv = 0, o = 0;
+        if (!xq.take(cnt, pv, o)) return;
+        const uint32_t p = pv & 0x0FFFFFFFu, dc = pv >> 28;
+        const uint32_t c = key16[2 * p], b = frag[p];
+        const uint32_t len = content_len(c), kind = content_kind(c);
+        const bool body = p >= k && p < n - k;
+        uint32_t eqpos = 0xFFu;  // index inside the slot that aligns to the original base
+        bool first_x = false;
+        if (kind == 1u) eqpos = 0;
+        else if (kind == 2u) eqpos = 1;
+        else if (len >= 2 && b < 4 && content_base(c, 0) == b) eqpos = 0;
+        else if (len >= 2 && b < 4 && content_base(c, len - 1) == b) eqpos = len - 1;
+        else first_x = true;
+        for (uint32_t u = 0; u < len; u++) {
+            const uint32_t j = o + u;
+            uint32_t ch;
+            if (kind == 0u) ch = code_ascii(content_base(c, u));
+            else if (kind == 1u) ch = u == 0 ? code_ascii(b) : code_ascii(content_base(c, 0));
+            else ch = u == 0 ? code_ascii(content_base(c, 0)) : code_ascii(b);
+            if (body) {
+                const uint32_t d = j - start_trim;
+                if (d < scap) oseq[d] = (uint8_t)ch;
+            }
+            const uint32_t op = u == eqpos ? OP_EQ : (first_x && u == 0) ? OP_X : OP_I;
+            if (j < opcap) ops_put(keyb, j, op | ((u == 0 ? dc : 0u) << 2));
+        }
+    };
     for (uint32_t base = 0; base < n; base += 4 * SIZE) {
         const uint32_t p0 = base + 4 * tm.rank;
         uint32_t c[4], len[4], s = 0;
@@ -789,50 +825,36 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
 #pragma unroll
         for (int t = 0; t < 4; t++) {
             const uint32_t p = p0 + t;
+            bool changed = false;
+            uint32_t qv = 0, qo = 0;
             if (p < n) {
                 if (len[t] == 0) {
                     pend = pend < 15 ? pend + 1 : 15;
-                    continue;
-                }
-                const uint32_t b = (fb4 >> (8 * t)) & 0xFFu;
-                const uint32_t dc = pend;
-                pend = 0;
-                const bool body = p >= k && p < n - k;
-                if (c[t] == 0xFFFFu) {
-                    // unchanged slot: one '=' column
-                    if (body) {
-                        const uint32_t d = o - start_trim;
-                        if (d < scap) oseq[d] = code_ascii(b);
+                } else {
+                    const uint32_t dc = pend;
+                    pend = 0;
+                    if (c[t] == 0xFFFFu) {
+                        // unchanged slot: one '=' column
+                        if (p >= k && p < n - k) {
+                            const uint32_t d = o - start_trim;
+                            if (d < scap) oseq[d] = code_ascii((fb4 >> (8 * t)) & 0xFFu);
+                        }
+                        if (o < opcap) ops_put(keyb, o, OP_EQ | (dc << 2));
+                    } else {
+                        // changed slot (about one in six): queued, expanded 32 at a time with every lane busy
+                        changed = true;
+                        qv = p | (dc << 28);
+                        qo = o;
                     }
-                    if (o < opcap) ops_put(keyb, o, OP_EQ | (dc << 2));
-                    o += 1;
-                    continue;
+                    o += len[t];
                 }
-                const uint32_t kind = content_kind(c[t]);
-                uint32_t eqpos = 0xFFu;  // index inside the slot that aligns to the original base
-                bool first_x = false;
-                if (kind == 1u) eqpos = 0;
-                else if (kind == 2u) eqpos = 1;
-                else if (len[t] >= 2 && b < 4 && content_base(c[t], 0) == b) eqpos = 0;
-                else if (len[t] >= 2 && b < 4 && content_base(c[t], len[t] - 1) == b) eqpos = len[t] - 1;
-                else first_x = true;
-                for (uint32_t u = 0; u < len[t]; u++) {
-                    const uint32_t j = o + u;
-                    uint32_t ch;
-                    if (kind == 0u) ch = code_ascii(content_base(c[t], u));
-                    else if (kind == 1u) ch = u == 0 ? code_ascii(b) : code_ascii(content_base(c[t], 0));
-                    else ch = u == 0 ? code_ascii(content_base(c[t], 0)) : code_ascii(b);
-                    if (body) {
-                        uint32_t d = j - start_trim;
-                        if (d < scap) oseq[d] = (uint8_t)ch;
-                    }
-                    uint32_t op = u == eqpos ? OP_EQ : (first_x && u == 0) ? OP_X : OP_I;
-                    if (j < opcap) ops_put(keyb, j, op | ((u == 0 ? dc : 0u) << 2));
-                }
-                o += len[t];
             }
+            xq.push(changed, qv, qo);
+            const uint32_t cnt = xq.ready(false);
+            if (cnt) expand_changed(cnt);
         }
     }
+    for (uint32_t cnt; (cnt = xq.ready(true)) != 0;) expand_changed(cnt);
     const uint32_t Ttot = carry;
     const uint32_t Lp = Ttot - start_trim - end_trim;
     if (Ttot > opcap) status |= ST_OPS_OVERFLOW;
@@ -844,6 +866,7 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
         B.status[r] = status;
     }
     tm.sync();
+    phase_sync();
 
     // ---- 6. qscores for the read bases that survive trimming: 8 bases per Philox call
     if ((P.flags & RUN_QUAL) && !(status & (ST_OPS_OVERFLOW | ST_SCRATCH_OVERFLOW))) {
@@ -959,8 +982,11 @@ __global__ void __launch_bounds__(SIM_THREADS, 1) simulate_kernel(const SimParam
             __syncthreads();
             const uint32_t wi = *cta_ticket + (uint32_t)tm.id;
             __syncthreads();
-            if (wi - (uint32_t)tm.id >= P.n_work) break;
-            if (wi < P.n_work) simulate_read<W, GWS>(tm, P, P.work[wi], ws, qcls_s, lut3);
+            const uint32_t base = wi - (uint32_t)tm.id;
+            if (base >= P.n_work) break;
+            const uint32_t nact = min((uint32_t)TEAMS, P.n_work - base);
+            if (wi < P.n_work)
+                simulate_read<W, GWS>(tm, P, P.work[wi], ws, qcls_s, lut3, P.lockstep >= 2 ? nact * (uint32_t)(W * 32) : 0u);
         }
         return;
     }
@@ -970,8 +996,81 @@ __global__ void __launch_bounds__(SIM_THREADS, 1) simulate_kernel(const SimParam
         const uint32_t wi = *ticket;
         tm.sync();
         if (wi >= P.n_work) break;
-        simulate_read<W, GWS>(tm, P, P.work[wi], ws, qcls_s, lut3);
+        simulate_read<W, GWS>(tm, P, P.work[wi], ws, qcls_s, lut3, 0u);
     }
+}
+
+// -------------------------------------------------------------- work order
+// Reads are handed to the simulate kernels class by class, inside a class by ascending target
+// identity (32 buckets: the error level sets the number of trials) and then by descending length,
+// so that the teams of a CTA that start reads together (lockstep) finish them together.  One
+// counting sort over a 17-bit key: class(3) | identity bucket(5) | quantised length(9).
+constexpr uint32_t WORK_KEY_BITS = 17;
+constexpr uint32_t WORK_BINS = 1u << WORK_KEY_BITS;
+
+struct WorkSortParams {
+    uint32_t n_reads;
+    uint64_t ordinal_base;
+    uint32_t seed_lo, seed_hi;
+    int ident_const;
+    uint32_t k;
+    const uint32_t* read_mol;
+    const uint32_t* mol_raw_len;
+    uint32_t ncap[5];       // fragment capacity of the shared-memory classes
+    uint32_t len_shift[6];  // quantisation of (capacity - n) per class
+    uint32_t gws_cap;       // capacity used for the global-workspace class
+    uint32_t* keys;         // R
+    uint32_t* bins;         // WORK_BINS (zeroed), turned into cursors by work_scan_kernel
+    uint32_t* work;         // R: sorted read indices
+};
+
+__global__ void work_key_kernel(const WorkSortParams W) {
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= W.n_reads) return;
+    const uint32_t n = W.mol_raw_len[W.read_mol[r]] + 2 * W.k;
+    uint32_t c = 0;
+    while (c < 5 && n > W.ncap[c]) c++;
+    const uint32_t cap = c < 5 ? W.ncap[c] : W.gws_cap;
+    uint32_t lq = (cap - min(n, cap)) >> W.len_shift[c];
+    lq = min(lq, 511u);
+    uint32_t bucket = 0;
+    if (!W.ident_const) {
+        const uint64_t ordinal = W.ordinal_base + r;
+        bucket = philox4x32_10(0, TAG_READ, (uint32_t)ordinal, (uint32_t)(ordinal >> 32), W.seed_lo, W.seed_hi).x >> 27;
+    }
+    const uint32_t key = (c << 14) | (bucket << 9) | lq;
+    W.keys[r] = key;
+    atomicAdd(&W.bins[key], 1u);
+}
+
+// exclusive scan of the WORK_BINS counters, one block of 1024 threads
+__global__ void work_scan_kernel(uint32_t* bins) {
+    __shared__ uint32_t wsum[32];
+    constexpr uint32_t PER = WORK_BINS / 1024;
+    uint32_t* mine = bins + threadIdx.x * PER;
+    uint32_t s = 0;
+    for (uint32_t i = 0; i < PER; i++) s += mine[i];
+    const uint32_t inc = warp_incl_scan(s);
+    if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = inc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        const uint32_t v = wsum[threadIdx.x];
+        const uint32_t vi = warp_incl_scan(v);
+        wsum[threadIdx.x] = vi - v;
+    }
+    __syncthreads();
+    uint32_t run = wsum[threadIdx.x >> 5] + inc - s;
+    for (uint32_t i = 0; i < PER; i++) {
+        const uint32_t v = mine[i];
+        mine[i] = run;
+        run += v;
+    }
+}
+
+__global__ void work_scatter_kernel(const WorkSortParams W) {
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= W.n_reads) return;
+    W.work[atomicAdd(&W.bins[W.keys[r]], 1u)] = r;
 }
 
 // -------------------------------------------------------------- formatting

@@ -616,6 +616,10 @@ std::vector<float> make_delta_table(const ErrorModelHost& em) {
     // crossed its target at the end of an epoch simply runs another epoch.
     std::vector<float> tab(DELTA_TAB_BINS);
     const double rho = std::max(em.rate_slots, 1e-6);  // rate at which a given slot is hit
+    // head-room over the expected stopping time: larger => fewer reads need a second epoch (they
+    // hold up the warps that start reads together), more candidate trials per epoch
+    double head_room = 1.3;
+    if (const char* e = getenv("TKSM_DELTA_HEADROOM")) head_room = std::max(1.0, atof(e));
     const double f_loss = em.rate_loss / rho, f_ins = em.rate_ins / rho;
     for (int b = 0; b < DELTA_TAB_BINS; b++) {
         double target = 0.5 + b / 128.0;
@@ -623,7 +627,7 @@ std::vector<float> make_delta_table(const ErrorModelHost& em) {
         double c = (1.0 - target) / (f_loss + target * f_ins);
         c = std::min(c, 0.9);
         double t = -std::log1p(-c) / rho;
-        double d = 1.3 * t + 0.02;
+        double d = head_room * t + 0.02;
         tab[(size_t)b] = (float)std::min(d, 50.0);
     }
     return tab;
