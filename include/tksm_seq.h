@@ -129,6 +129,16 @@ void tksm_seq_batch_destroy(tksm_seq* h, tksm_seq_batch* b);
 int tksm_seq_synth_mdf(tksm_seq* h, int shape, uint64_t n_molecules, uint64_t seed, uint32_t min_len,
                        uint32_t max_len, char** out, size_t* out_len);
 
+/* Multi-GPU sharding (no reference counterpart: the reference forks --threads workers over
+ * one stream, py/sequence.py:358-366).  Cuts the MDF text at record boundaries into `world`
+ * contiguous shards of about equal simulated bases (sum over records of depth x interval lengths).
+ * byte_begin[i] .. byte_begin[i+1] is the text of shard i and ordinal_base[i] the global ordinal of
+ * its first read (after depth expansion), so that every rank keys Philox exactly as a single-GPU
+ * run would; both arrays have world + 1 entries (the last ones: text length, total reads).
+ * Host only: works on a host_only handle. */
+int tksm_seq_shard_plan(tksm_seq* h, const char* mdf, size_t mdf_len, int world, uint64_t* byte_begin,
+                        uint64_t* ordinal_base);
+
 /* the module entry point: argv[0] == "sequence" */
 int tksm_sequence_main(int argc, char** argv);
 

@@ -235,3 +235,17 @@ def test_streaming_pipeline_is_chunking_invariant(world, tmp_path, monkeypatch):
     with pytest.raises(Exception):
         s.simulate(mdf + b"chr1\t0\t5\n", BADREAD, True)
     assert s.simulate(mdf, BADREAD, True) == want
+
+
+def test_shard_plan_through_the_kernels(world):
+    """every rank simulates its shard with the global ordinal of its first read; the
+    rank outputs concatenate to the single-GPU bytes (here the ranks run one after the other)."""
+    from tksm_b200.sequence import BADREAD
+    s = world["Sequencer"](seed=31)
+    s.add_reference_text(world["fasta"])
+    s.load_models("random", "random")
+    mdf = b"+d3\t3\tx;\nchr1\t100\t400\t+\t\n" + s.synth_mdf(1, 700, seed=8) + handmade_mdf().encode()
+    whole = s.simulate(mdf, BADREAD, True)
+    for n_ranks in (2, 3, 8):
+        parts = [s.simulate(mdf[b0:b1], BADREAD, True, ordinal_base=ob) for b0, b1, ob, _ in s.shard_plan(mdf, n_ranks)]
+        assert b"".join(parts) == whole

@@ -1392,6 +1392,16 @@ int tksm_seq_simulate_text(tksm_seq* h, const char* mdf, size_t mdf_len, int whi
     API_END(h)
 }
 
+int tksm_seq_shard_plan(tksm_seq* h, const char* mdf, size_t mdf_len, int world, uint64_t* byte_begin,
+                        uint64_t* ordinal_base) {
+    API_BEGIN
+    std::vector<uint64_t> bb, ob;
+    plan_shards(mdf, mdf_len, world, bb, ob);
+    memcpy(byte_begin, bb.data(), bb.size() * 8);
+    memcpy(ordinal_base, ob.data(), ob.size() * 8);
+    API_END(h)
+}
+
 int tksm_seq_run_files(tksm_seq* h, const char* mdf_path, const char* badread_path, const char* perfect_path,
                        tksm_seq_stats* stats) {
     API_BEGIN

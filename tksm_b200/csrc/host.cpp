@@ -352,6 +352,68 @@ struct SvHash {
 
 }  // namespace
 
+void plan_shards(const char* text, size_t len, int world, std::vector<uint64_t>& byte_begin,
+                 std::vector<uint64_t>& ordinal_base) {
+    if (world < 1) throw std::runtime_error("shard plan: world size must be at least 1");
+    // one light pass: per record its byte offset, depth and depth x sum of (end - start)
+    struct Rec {
+        uint64_t off, reads, bases;
+    };
+    std::vector<Rec> recs;
+    LineScan ln;
+    size_t pos = 0;
+    long long depth = 0;
+    bool have = false;
+    while (scan_line(text, len, pos, ln)) {
+        const size_t line_start = pos;
+        pos = ln.next;
+        if (ln.b == ln.e) continue;  // the parser reports it
+        if (*ln.b == '+') {
+            depth = 0;
+            if (ln.ntab >= 1) {
+                try {
+                    depth = mdf_int(ln.tab[0] + 1, ln.ntab > 1 ? ln.tab[1] : ln.e);
+                } catch (const std::exception&) {
+                    depth = 0;
+                }
+            }
+            if (depth < 0) depth = 0;
+            recs.push_back({(uint64_t)line_start, (uint64_t)depth, 0});
+            have = true;
+        } else if (have && ln.ntab >= 2) {
+            try {
+                const long long a = mdf_int(ln.tab[0] + 1, ln.tab[1]);
+                const long long b = mdf_int(ln.tab[1] + 1, ln.ntab > 2 ? ln.tab[2] : ln.e);
+                if (b > a && a >= 0) recs.back().bases += (uint64_t)(b - a) * recs.back().reads;
+            } catch (const std::exception&) {
+            }
+        }
+    }
+    uint64_t total = 0;
+    for (auto& r : recs) total += r.bases + r.reads;  // + reads: records of empty molecules still cost a read
+    byte_begin.assign((size_t)world + 1, len);
+    ordinal_base.assign((size_t)world + 1, 0);
+    byte_begin[0] = 0;
+    uint64_t acc = 0, reads = 0;
+    int shard = 1;
+    for (size_t i = 0; i < recs.size(); i++) {
+        // record i starts shard `shard` once the records before it hold shard/world of the weight
+        while (shard < world && acc * (uint64_t)world >= total * (uint64_t)shard && i > 0) {
+            byte_begin[(size_t)shard] = recs[i].off;
+            ordinal_base[(size_t)shard] = reads;
+            shard++;
+        }
+        acc += recs[i].bases + recs[i].reads;
+        reads += recs[i].reads;
+    }
+    for (; shard < world; shard++) {  // fewer records than ranks: the rest are empty shards at the end
+        byte_begin[(size_t)shard] = len;
+        ordinal_base[(size_t)shard] = reads;
+    }
+    byte_begin[(size_t)world] = len;
+    ordinal_base[(size_t)world] = reads;
+}
+
 size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out, size_t max_reads,
                        uint64_t max_bases) {
     size_t pos = 0, consumed = 0;

@@ -78,6 +78,11 @@ struct MdfParser {
                 uint64_t max_bases = UINT64_MAX);
 };
 
+// Contiguous shards of about equal simulated bases, cut at record boundaries (multi-GPU runs).
+// byte_begin / ordinal_base get world + 1 entries.
+void plan_shards(const char* text, size_t len, int world, std::vector<uint64_t>& byte_begin,
+                 std::vector<uint64_t>& ordinal_base);
+
 // Fragment code of one byte: ACGT -> 0..3, anything else keeps its (ASCII) value.
 inline uint8_t frag_code(uint8_t c) {
     switch (c) {

@@ -1043,28 +1043,30 @@ __global__ void work_key_kernel(const WorkSortParams W) {
     atomicAdd(&W.bins[key], 1u);
 }
 
-// exclusive scan of the WORK_BINS counters, one block of 1024 threads
-__global__ void work_scan_kernel(uint32_t* bins) {
-    __shared__ uint32_t wsum[32];
-    constexpr uint32_t PER = WORK_BINS / 1024;
-    uint32_t* mine = bins + threadIdx.x * PER;
-    uint32_t s = 0;
-    for (uint32_t i = 0; i < PER; i++) s += mine[i];
-    const uint32_t inc = warp_incl_scan(s);
-    if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = inc;
+// exclusive scan of the WORK_BINS counters, one block of 1024 threads: every warp scans its own
+// contiguous 1/32 of the bins with coalesced row loads, then adds the total of the warps before it
+__global__ void __launch_bounds__(1024) work_scan_kernel(uint32_t* bins) {
+    __shared__ uint32_t wtot[32];
+    constexpr uint32_t PER_WARP = WORK_BINS / 32, ROWS = PER_WARP / 32;
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint32_t* mine = bins + warp * PER_WARP;
+    uint32_t carry = 0;
+    for (uint32_t i = 0; i < ROWS; i++) {
+        const uint32_t v = mine[i * 32 + lane];
+        const uint32_t inc = warp_incl_scan(v);
+        mine[i * 32 + lane] = carry + inc - v;
+        carry += __shfl_sync(0xffffffffu, inc, 31);
+    }
+    if (lane == 0) wtot[warp] = carry;
     __syncthreads();
     if (threadIdx.x < 32) {
-        const uint32_t v = wsum[threadIdx.x];
-        const uint32_t vi = warp_incl_scan(v);
-        wsum[threadIdx.x] = vi - v;
+        const uint32_t v = wtot[threadIdx.x];
+        wtot[threadIdx.x] = warp_incl_scan(v) - v;
     }
     __syncthreads();
-    uint32_t run = wsum[threadIdx.x >> 5] + inc - s;
-    for (uint32_t i = 0; i < PER; i++) {
-        const uint32_t v = mine[i];
-        mine[i] = run;
-        run += v;
-    }
+    const uint32_t base = wtot[warp];
+    if (base)
+        for (uint32_t i = 0; i < ROWS; i++) mine[i * 32 + lane] += base;
 }
 
 __global__ void work_scatter_kernel(const WorkSortParams W) {

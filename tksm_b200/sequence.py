@@ -146,6 +146,17 @@ class Sequencer:
         self.last_stats = st.as_dict()
         return self.last_stats
 
+    # ---- multi-GPU sharding (SURVEY.md 8e): contiguous shards of about equal simulated bases
+    def shard_plan(self, mdf_text, world):
+        """[(byte_begin, byte_end, ordinal_base, n_reads)] per rank; rank i simulates
+        mdf_text[byte_begin:byte_end] with ordinal_base and the rank outputs concatenate, in rank
+        order, to the bytes of a single-GPU run."""
+        b = mdf_text.encode() if isinstance(mdf_text, str) else mdf_text
+        bb = (C.c_uint64 * (world + 1))()
+        ob = (C.c_uint64 * (world + 1))()
+        self._ck(self._L.tksm_seq_shard_plan(self._h, b, len(b), world, bb, ob))
+        return [(bb[i], bb[i + 1], ob[i], ob[i + 1] - ob[i]) for i in range(world)]
+
     # ---- device-resident batches (bench)
     def batch(self, mdf_text, ordinal_base=0):
         return Batch(self, mdf_text, ordinal_base)
