@@ -271,37 +271,31 @@ __device__ __forceinline__ void hist_add(HistT* hist, uint32_t bin, uint32_t los
 __device__ __forceinline__ uint32_t ops_at(const uint8_t* keyb, uint32_t j) { return keyb[4 * (j >> 1) + 2 + (j & 1)]; }
 __device__ __forceinline__ void ops_put(uint8_t* keyb, uint32_t j, uint32_t v) { keyb[4 * (j >> 1) + 2 + (j & 1)] = (uint8_t)v; }
 
-__device__ __forceinline__ uint32_t qscore_row(const DevTables& T, const uint8_t* keyb, int start, int end) {
-    // py/tksm_badread.py:584-598 with the window given in read coordinates [start, end]
-    while (true) {
-        const int w = end - start + 1;
-        uint32_t code3 = 0, mul = 1, anyd = 0;
-        uint64_t key = 1;
-        uint32_t nsym = 0;
-        for (int c = start; c <= end; c++) {
-            uint32_t o = ops_at(keyb, (uint32_t)c);
-            uint32_t op = o & 3u, dc = c > start ? (o >> 2) : 0u;
-            anyd |= dc;
-            code3 += op * mul;
-            mul *= 3;
-            nsym += dc + 1;
-            if (nsym <= 31) {
-                key = (key << (2 * dc)) | ((1ull << (2 * dc)) - 1);  // dc times 'D' (3)
-                key = (key << 2) | op;
-            }
+// py/tksm_badread.py:584-598 for the 9-column window of one read base held in registers:
+//   ops18: op of column i at bits 2i; gaps: D count in front of column i (i >= 1) at bits 4(i-1);
+//   t0: first trim level (the window is already shrunk at the read ends).
+// Level t keeps columns t..8-t; a window without D goes to the direct table of its width, one with D
+// to the hash under the packed key of model.cpp: qkey_from_cigar; a miss trims one column per side
+// (leading/trailing D runs go with them, as cigar[1:-1].strip("D") does).
+__device__ __forceinline__ uint32_t qscore_row(const DevTables& T, const uint8_t* lut3, uint32_t ops18, uint32_t gaps,
+                                               uint32_t t0) {
+    for (uint32_t t = t0;; t++) {
+        const uint32_t w = 9u - 2u * t;
+        const uint32_t o = (ops18 >> (2u * t)) & ((1u << (2u * w)) - 1u);
+        const uint32_t gmask = w == 9u ? 0xFFFFFFFFu : ((1u << (4u * (w - 1u))) - 1u);
+        const uint32_t g = (uint32_t)(((uint64_t)gaps >> (4u * t)) & gmask);
+        if (g == 0u) {
+            const uint32_t code3 = lut3[o & 63u] + 27u * lut3[(o >> 6) & 63u] + 729u * lut3[o >> 12];
+            return T.q_direct[T.q_direct_off[w >> 1] + code3];
         }
-        if (!anyd) return T.q_direct[T.q_direct_off[w >> 1] + code3];
-        if (nsym <= 31) {
-            uint32_t h = (uint32_t)((key * 0x9E3779B97F4A7C15ull) >> T.q_hash_shift);
-            while (true) {
-                QHashEntry e = T.q_hash[h];
-                if (e.key == key) return e.row;
-                if (e.key == 0) break;
-                h = (h + 1) & T.q_hash_mask;
-            }
+        const uint64_t key = ((uint64_t)(0x10u | w) << 56) | ((uint64_t)o << 32) | g;
+        uint32_t h = (uint32_t)((key * 0x9E3779B97F4A7C15ull) >> T.q_hash_shift);
+        while (true) {
+            const QHashEntry e = T.q_hash[h];
+            if (e.key == key) return e.row;
+            if (e.key == 0) break;
+            h = (h + 1) & T.q_hash_mask;
         }
-        start++;
-        end--;
     }
 }
 
@@ -885,12 +879,16 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
         auto run_slow = [&](uint32_t cnt) {
             uint32_t j = 0, u = 0;
             if (!sq.take(cnt, j, u)) return;
-            int start = (int)j - margin, end = (int)j + margin;
-            while (start < 0 || end >= (int)Ttot) {
-                start++;
-                end--;
+            // columns j-4 .. j+4, shrunk symmetrically at the read ends (py/tksm_badread.py:632-639)
+            int t0 = 4 - margin;
+            t0 = max(t0, max(4 - (int)j, (int)j + 4 - (int)(Ttot - 1)));
+            uint32_t ops18 = 0, gaps = 0;
+            for (int i = t0; i <= 8 - t0; i++) {
+                const uint32_t o = ops_at(keyb, j + (uint32_t)i - 4u);
+                ops18 |= (o & 3u) << (2 * i);
+                if (i > t0) gaps |= (o >> 2) << (4 * (i - 1));
             }
-            const QRow rw = T.q_rows[qscore_row(T, keyb, start, end)];
+            const QRow rw = T.q_rows[qscore_row(T, lut3, ops18, gaps, (uint32_t)t0)];
             sample(rw.off, rw.lg, u, j);
         };
         const uint32_t g0 = jb >> 3, g1 = (je + 7) >> 3;  // groups of 8 read bases [g0, g1)

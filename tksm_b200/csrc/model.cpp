@@ -347,21 +347,33 @@ ErrorModelHost load_error_model(const std::string& name_or_path, const std::map<
     return em;
 }
 
+// Packed key of a D-bearing window cigar: ops o_0..o_{w-1} ('=' 0, 'X' 1, 'I' 2; w <= 9) and the
+// lengths d_1..d_{w-1} of the D runs in front of ops 1..w-1 (<= 15):
+//   key = (0x10 | w) << 56 | (sum o_i << 2 i) << 32 | sum d_i << 4 (i - 1)
+// 0 when the cigar cannot occur as a window (leading/trailing D, more than 9 ops, a run over 15).
 uint64_t qkey_from_cigar(const std::string& cigar) {
-    if (cigar.empty() || cigar.size() > 31) return 0;
-    uint64_t key = 1;
+    uint64_t ops = 0, gaps = 0;
+    uint32_t w = 0, run = 0;
     for (char c : cigar) {
-        uint64_t s;
+        uint64_t o;
         switch (c) {
-            case '=': s = OP_EQ; break;
-            case 'X': s = OP_X; break;
-            case 'I': s = OP_I; break;
-            case 'D': s = OP_D; break;
+            case '=': o = OP_EQ; break;
+            case 'X': o = OP_X; break;
+            case 'I': o = OP_I; break;
+            case 'D':
+                if (w == 0) return 0;
+                run++;
+                continue;
             default: return 0;
         }
-        key = (key << 2) | s;
+        if (w >= 9 || run > 15) return 0;
+        if (w > 0) gaps |= (uint64_t)run << (4 * (w - 1));
+        ops |= o << (2 * w);
+        w++;
+        run = 0;
     }
-    return key;
+    if (w == 0 || run) return 0;
+    return ((uint64_t)(0x10u | w) << 56) | (ops << 32) | gaps;
 }
 
 QScoreModelHost pack_qscore_model(
