@@ -98,6 +98,98 @@ inline uint32_t list_capacity(uint32_t ncap) { return ncap / 5 * 2 + 64; }
 
 }  // namespace
 
+// Page-locked upload buffers shared by the host threads that pack batches and the thread that
+// issues the uploads: a packer blocks in acquire() while all buffers are in flight.
+class StagePool {
+  public:
+    StagePool(int max_buffers, bool pinned) : max_(max_buffers), pinned_(pinned) {}
+    ~StagePool() {
+        for (auto& b : bufs_) {
+            if (pinned_) b.mem.release();
+            else free(b.mem.p);
+        }
+    }
+    // returns the index of a free buffer of at least `bytes`, or -1 when all buffers are in flight
+    // (never blocks: one packer may hold many batches before the issuing thread sees the first)
+    int acquire(size_t bytes, int device) {
+        std::unique_lock<std::mutex> g(mu_);
+        {
+            int idx = -1;
+            for (size_t i = 0; i < bufs_.size(); i++)
+                if (!bufs_[i].used && (idx < 0 || bufs_[i].mem.cap > bufs_[(size_t)idx].mem.cap)) idx = (int)i;
+            if (idx < 0 && (int)bufs_.size() < max_) {
+                bufs_.emplace_back();
+                idx = (int)bufs_.size() - 1;
+            }
+            if (idx >= 0) {
+                bufs_[(size_t)idx].used = true;
+                Buf& mine = bufs_[(size_t)idx];
+                g.unlock();
+                try {  // only this thread touches the buffer while it is `used`
+                    if (pinned_) {
+                        CK(cudaSetDevice(device));
+                        mine.mem.ensure(bytes);
+                    } else if (mine.mem.cap < bytes) {  // host_only handles: no CUDA call
+                        free(mine.mem.p);
+                        mine.mem.cap = bytes + bytes / 8 + 256;
+                        mine.mem.p = malloc(mine.mem.cap);
+                        if (!mine.mem.p) throw std::runtime_error("out of host memory");
+                    }
+                } catch (...) {
+                    release(idx);
+                    throw;
+                }
+                return idx;
+            }
+        }
+        return -1;
+    }
+    char* ptr(int idx) {
+        std::lock_guard<std::mutex> g(mu_);
+        return (char*)bufs_[(size_t)idx].mem.p;
+    }
+    void release(int idx) {
+        if (idx < 0) return;
+        std::lock_guard<std::mutex> g(mu_);
+        bufs_[(size_t)idx].used = false;
+    }
+
+  private:
+    struct Buf {
+        HBuf mem;
+        bool used = false;
+    };
+    std::mutex mu_;
+    std::deque<Buf> bufs_;   // deque: growing never moves the buffers other threads are filling
+    int max_;
+    bool pinned_;
+};
+
+// move-only ownership of one StagePool buffer
+struct StageLease {
+    StagePool* pool = nullptr;
+    int idx = -1;
+    StageLease() = default;
+    StageLease(StagePool* p, int i) : pool(p), idx(i) {}
+    StageLease(const StageLease&) = delete;
+    StageLease& operator=(const StageLease&) = delete;
+    StageLease(StageLease&& o) noexcept : pool(o.pool), idx(o.idx) { o.idx = -1; }
+    StageLease& operator=(StageLease&& o) noexcept {
+        if (this != &o) {
+            reset();
+            pool = o.pool;
+            idx = o.idx;
+            o.idx = -1;
+        }
+        return *this;
+    }
+    ~StageLease() { reset(); }
+    void reset() {
+        if (pool && idx >= 0) pool->release(idx);
+        idx = -1;
+    }
+};
+
 // One parsed MDF chunk with everything the device needs, built by host threads only
 // (no CUDA call): scratch layout, length-class work lists and the upload blob.
 struct Prepared {
@@ -109,7 +201,9 @@ struct Prepared {
     uint32_t max_n_gws = 0;
     uint64_t alg_in_bytes = 0, idsum = 0;
     bool mods = false;
-    std::unique_ptr<char[]> blob;
+    StageLease stage;         // page-locked buffer of the handle's StagePool holding the blob,
+    std::unique_ptr<char[]> heap_blob;  // or pageable memory when the pool is exhausted
+    char* blob = nullptr;
     size_t blob_bytes = 0;
     size_t o_read_mol = 0, o_msb = 0, o_mrl = 0, o_mib = 0, o_src = 0, o_len = 0, o_smb = 0, o_mp = 0, o_mc = 0, o_lit = 0,
            o_id = 0, o_so = 0, o_ro = 0;
@@ -127,6 +221,7 @@ struct tksm_seq_batch {
     HBuf host_out[2];     // pinned download staging (streaming to files)
     HBuf h_tot;           // pinned: record bytes per output, read bases, status
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // kernels begin, simulate end, kernels end, downloads end, totals on host
+    cudaEvent_t ev_sorted = nullptr, ev_class[4] = {nullptr, nullptr, nullptr, nullptr};  // work order ready; class stream done
     uint64_t out_bytes[2] = {0, 0};
     uint64_t out_cap[2] = {0, 0};
     uint32_t launches = 0;
@@ -137,6 +232,9 @@ struct tksm_seq_batch {
     void ensure_events() {
         for (auto& e : ev)
             if (!e) CK(cudaEventCreate(&e));
+        if (!ev_sorted) CK(cudaEventCreateWithFlags(&ev_sorted, cudaEventDisableTiming));
+        for (auto& e : ev_class)
+            if (!e) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     }
     ~tksm_seq_batch() {
         for (DBuf* d : {&blob, &scr_seq, &scr_qual, &scr_raw, &per_read, &out[0], &out[1], &rec_len[0], &rec_len[1],
@@ -147,6 +245,9 @@ struct tksm_seq_batch {
         host_out[1].release();
         h_tot.release();
         for (auto& e : ev)
+            if (e) cudaEventDestroy(e);
+        if (ev_sorted) cudaEventDestroy(ev_sorted);
+        for (auto& e : ev_class)
             if (e) cudaEventDestroy(e);
     }
 };
@@ -166,7 +267,9 @@ struct tksm_seq {
     // device
     cudaStream_t stream = nullptr;       // uploads + kernels
     cudaStream_t copy_stream = nullptr;  // record downloads, overlapped with the next chunk's kernels
+    cudaStream_t class_stream[4] = {nullptr, nullptr, nullptr, nullptr};  // simulate kernels of one batch, one stream per length class
     std::vector<std::unique_ptr<tksm_seq_batch>> slots;  // streaming pipeline (engine_stream)
+    std::unique_ptr<StagePool> stage_pool;
     int num_sms = 148;
     DBuf d_genome, d_exc_start, d_exc_len, d_exc_chr;
     DBuf d_qcls, d_thr, d_alias, d_alts, d_ident, d_delta, d_qdirect, d_qhash, d_qrows, d_qalias, d_t9, d_t9d1;
@@ -184,6 +287,8 @@ struct tksm_seq {
             d->release();
         slots.clear();
         if (copy_stream) cudaStreamDestroy(copy_stream);
+        for (auto& cs : class_stream)
+            if (cs) cudaStreamDestroy(cs);
         if (stream) cudaStreamDestroy(stream);
     }
 };
@@ -282,10 +387,10 @@ void upload_models(tksm_seq* h) {
 }
 
 template <int W, bool GWS>
-void launch_sim(tksm_seq* h, const SimParams& P, size_t smem, int grid) {
+void launch_sim(cudaStream_t stream, const SimParams& P, size_t smem, int grid) {
     auto kern = simulate_kernel<W, GWS>;
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<grid, SIM_THREADS, smem, h->stream>>>(P);
+    kern<<<grid, SIM_THREADS, smem, stream>>>(P);
     CK(cudaGetLastError());
 }
 
@@ -334,9 +439,15 @@ void prepare_host(const tksm_seq* h, const std::vector<const HostBatch*>& parts,
     p.o_id = add(ID);
     p.o_so = add((R + 1) * 8);
     p.o_ro = add((R + 1) * 8);
-    p.blob.reset(new char[total]);
+    p.stage = StageLease(h->stage_pool.get(), h->stage_pool->acquire(total, h->cfg.device));
+    if (p.stage.idx >= 0) {
+        p.blob = h->stage_pool->ptr(p.stage.idx);
+    } else {
+        p.heap_blob.reset(new char[total]);
+        p.blob = p.heap_blob.get();
+    }
     p.blob_bytes = total;
-    char* B = p.blob.get();
+    char* B = p.blob;
     uint32_t* read_mol = (uint32_t*)(B + p.o_read_mol);
     uint32_t* msb = (uint32_t*)(B + p.o_msb);
     uint32_t* mrl = (uint32_t*)(B + p.o_mrl);
@@ -424,11 +535,8 @@ void slot_bind(tksm_seq* h, tksm_seq_batch* b) {
     CK(cudaSetDevice(h->cfg.device));
     Prepared& p = b->prep;
     const size_t R = p.n_reads;
-    b->stage.ensure(p.blob_bytes);
-    memcpy(b->stage.p, p.blob.get(), p.blob_bytes);
-    p.blob.reset();
     b->blob.ensure(p.blob_bytes);
-    CK(cudaMemcpyAsync(b->blob.p, b->stage.p, p.blob_bytes, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(b->blob.p, p.blob, p.blob_bytes, cudaMemcpyHostToDevice, h->stream));
     b->h2d_bytes = p.blob_bytes;
     char* base = (char*)b->blob.p;
     DevBatch& D = b->db;
@@ -562,6 +670,10 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
             off += p.n_work[c];
         }
     }
+    // The classes are independent (own reads, own ticket counter): each gets its own stream so that
+    // the CTAs of the next class fill the SMs the tail of the previous one leaves idle.
+    CK(cudaEventRecord(b->ev_sorted, h->stream));
+    uint32_t used_streams = 0;
     for (int c = 0; c < N_CLASSES; c++) {
         if (p.n_work[c] == 0) continue;
         SimParams P;
@@ -581,15 +693,23 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         }
         const int teams = c == GWS_CLASS ? 1 : SIM_WARPS / CLASS_W[c];
         int grid = (int)std::min<size_t>((size_t)h->num_sms, (P.n_work + teams - 1) / teams);
+        const uint32_t si = used_streams % 4;
+        cudaStream_t st = h->class_stream[si];
+        if (used_streams < 4) CK(cudaStreamWaitEvent(st, b->ev_sorted, 0));
+        used_streams++;
         switch (c) {
-            case 0: launch_sim<1, false>(h, P, h->smem_bytes[c], grid); break;
-            case 1: launch_sim<2, false>(h, P, h->smem_bytes[c], grid); break;
-            case 2: launch_sim<4, false>(h, P, h->smem_bytes[c], grid); break;
-            case 3: launch_sim<8, false>(h, P, h->smem_bytes[c], grid); break;
-            case 4: launch_sim<24, false>(h, P, h->smem_bytes[c], grid); break;
-            default: launch_sim<24, true>(h, P, h->smem_bytes[c], grid); break;
+            case 0: launch_sim<1, false>(st, P, h->smem_bytes[c], grid); break;
+            case 1: launch_sim<2, false>(st, P, h->smem_bytes[c], grid); break;
+            case 2: launch_sim<4, false>(st, P, h->smem_bytes[c], grid); break;
+            case 3: launch_sim<8, false>(st, P, h->smem_bytes[c], grid); break;
+            case 4: launch_sim<24, false>(st, P, h->smem_bytes[c], grid); break;
+            default: launch_sim<24, true>(st, P, h->smem_bytes[c], grid); break;
         }
         launches++;
+    }
+    for (uint32_t i = 0; i < std::min<uint32_t>(used_streams, 4); i++) {
+        CK(cudaEventRecord(b->ev_class[i], h->class_stream[i]));
+        CK(cudaStreamWaitEvent(h->stream, b->ev_class[i], 0));
     }
     CK(cudaEventRecord(b->ev[1], h->stream));
     for (int o = 0; o < 2; o++) {
@@ -646,10 +766,16 @@ void slot_wait(tksm_seq* h, tksm_seq_batch* b, tksm_seq_stats* st) {
     s.h2d_bytes = b->h2d_bytes;
     if (s.reads == 0) {
         CK(cudaStreamSynchronize(h->stream));
+        p.stage.reset();
+        p.heap_blob.reset();
+        p.blob = nullptr;
         if (st) *st = s;
         return;
     }
     CK(cudaEventSynchronize(b->ev[4]));
+    p.stage.reset();  // the upload is long done
+    p.heap_blob.reset();
+    p.blob = nullptr;
     const bool want_bad = b->which & TKSM_SEQ_BADREAD, want_perf = b->which & TKSM_SEQ_PERFECT;
     const uint64_t* tot = (const uint64_t*)b->h_tot.p;
     float ms_all = 0, ms_sim = 0;
@@ -1128,6 +1254,7 @@ tksm_seq* tksm_seq_create(const tksm_seq_config* cfg) {
     try {
         if (cfg) h->cfg = *cfg; else tksm_seq_default_config(&h->cfg);
         h->idh = make_identities(h->cfg.identity_mean, h->cfg.identity_stdev, h->cfg.identity_max);
+        h->stage_pool.reset(new StagePool(10, !h->cfg.host_only));
         if (!h->cfg.host_only) {
             int ndev = 0;
             cudaError_t e = cudaGetDeviceCount(&ndev);
@@ -1143,6 +1270,7 @@ tksm_seq* tksm_seq_create(const tksm_seq_config* cfg) {
             h->num_sms = prop.multiProcessorCount;
             CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
             CK(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+            for (auto& cs : h->class_stream) CK(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
         }
     } catch (const std::exception& e) {
         g_create_error = e.what();
@@ -1351,6 +1479,9 @@ tksm_seq_batch* tksm_seq_batch_create(tksm_seq* h, const char* mdf, size_t mdf_l
             slot_bind(h, b.get());
             CK(cudaStreamSynchronize(h->stream));
         }
+        b->prep.stage.reset();  // uploaded (or never needed): the batch keeps no host buffer
+        b->prep.heap_blob.reset();
+        b->prep.blob = nullptr;
     } catch (const std::exception& e) {
         h->err = e.what();
         return nullptr;
