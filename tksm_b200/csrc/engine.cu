@@ -226,6 +226,7 @@ struct tksm_seq_batch {
     uint64_t out_cap[2] = {0, 0};
     uint32_t launches = 0;
     int which = 0;
+    int lane = 0;             // which pair of streams the batch runs on
     bool bound = false;
     bool d2h_pending = false;
     size_t h2d_bytes = 0;
@@ -267,7 +268,10 @@ struct tksm_seq {
     // device
     cudaStream_t stream = nullptr;       // uploads + kernels
     cudaStream_t copy_stream = nullptr;  // record downloads, overlapped with the next chunk's kernels
-    cudaStream_t class_stream[4] = {nullptr, nullptr, nullptr, nullptr};  // simulate kernels of one batch, one stream per length class
+    // Consecutive batches alternate between two lanes (own upload/kernel stream and class streams), so
+    // the kernels of the next batch fill the SMs while the previous one runs its tail and its format stage.
+    cudaStream_t lane_stream[2] = {nullptr, nullptr};   // lane 0 is `stream`
+    cudaStream_t class_stream[2][4] = {};  // simulate kernels of one batch, one stream per length class
     std::vector<std::unique_ptr<tksm_seq_batch>> slots;  // streaming pipeline (engine_stream)
     std::unique_ptr<StagePool> stage_pool;
     int num_sms = 148;
@@ -287,8 +291,10 @@ struct tksm_seq {
             d->release();
         slots.clear();
         if (copy_stream) cudaStreamDestroy(copy_stream);
-        for (auto& cs : class_stream)
-            if (cs) cudaStreamDestroy(cs);
+        for (auto& lane : class_stream)
+            for (auto& cs : lane)
+                if (cs) cudaStreamDestroy(cs);
+        if (lane_stream[1]) cudaStreamDestroy(lane_stream[1]);
         if (stream) cudaStreamDestroy(stream);
     }
 };
@@ -529,6 +535,7 @@ void prepare_host(const tksm_seq* h, const std::vector<const HostBatch*>& parts,
 
 // Uploads the prepared chunk of slot `b` (asynchronously on the compute stream).
 void slot_bind(tksm_seq* h, tksm_seq_batch* b) {
+    cudaStream_t S = h->lane_stream[b->lane];
     need_device(h);
     if (!h->models_loaded) throw std::runtime_error("models not loaded");
     commit_reference(h);
@@ -536,7 +543,7 @@ void slot_bind(tksm_seq* h, tksm_seq_batch* b) {
     Prepared& p = b->prep;
     const size_t R = p.n_reads;
     b->blob.ensure(p.blob_bytes);
-    CK(cudaMemcpyAsync(b->blob.p, p.blob, p.blob_bytes, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(b->blob.p, p.blob, p.blob_bytes, cudaMemcpyHostToDevice, S));
     b->h2d_bytes = p.blob_bytes;
     char* base = (char*)b->blob.p;
     DevBatch& D = b->db;
@@ -567,12 +574,13 @@ void slot_bind(tksm_seq* h, tksm_seq_batch* b) {
 }
 
 void run_scan(tksm_seq* h, tksm_seq_batch* b, int o, uint32_t R, uint64_t* d_total) {
+    cudaStream_t S = h->lane_stream[b->lane];
     const uint32_t per = SCAN_BLOCK * SCAN_ITEMS;
     const uint32_t nb = (R + per - 1) / per;
     b->sums.ensure((size_t)(nb + 2) * 8);
-    scan_block_sums<<<nb, SCAN_BLOCK, 0, h->stream>>>(b->rec_len[o].as<uint32_t>(), R, b->sums.as<uint64_t>());
-    scan_sums<<<1, 1024, 0, h->stream>>>(b->sums.as<uint64_t>(), nb, d_total);
-    scan_final<<<nb, SCAN_BLOCK, 0, h->stream>>>(b->rec_len[o].as<uint32_t>(), R, b->sums.as<uint64_t>(),
+    scan_block_sums<<<nb, SCAN_BLOCK, 0, S>>>(b->rec_len[o].as<uint32_t>(), R, b->sums.as<uint64_t>());
+    scan_sums<<<1, 1024, 0, S>>>(b->sums.as<uint64_t>(), nb, d_total);
+    scan_final<<<nb, SCAN_BLOCK, 0, S>>>(b->rec_len[o].as<uint32_t>(), R, b->sums.as<uint64_t>(),
                                                  b->rec_off[o].as<uint64_t>());
     CK(cudaGetLastError());
 }
@@ -582,6 +590,7 @@ constexpr size_t CNT_TOTALS = 32, CNT_READ_BASES = 48, CNT_STATUS = 56;
 
 // Enqueues the kernel sequence of the bound chunk on the compute stream; no host synchronisation.
 void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
+    cudaStream_t S = h->lane_stream[b->lane];
     if (!b->bound) throw std::runtime_error("batch not uploaded");
     CK(cudaSetDevice(h->cfg.device));
     Prepared& p = b->prep;
@@ -630,16 +639,16 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         b->gws.ensure((size_t)slab_c[GWS_CLASS] * h->num_sms);
     }
     uint64_t* d_totals = (uint64_t*)((char*)b->counters.p + CNT_TOTALS);
-    CK(cudaMemsetAsync(b->counters.p, 0, 64, h->stream));
+    CK(cudaMemsetAsync(b->counters.p, 0, 64, S));
 
-    CK(cudaEventRecord(b->ev[0], h->stream));
+    CK(cudaEventRecord(b->ev[0], S));
     uint32_t launches = 0;
     {
         // device-side work order (kernels.cuh: class | identity bucket | length)
         b->work_keys.ensure((size_t)R * 4);
         b->work_sorted.ensure((size_t)R * 4);
         b->work_bins.ensure((size_t)WORK_BINS * 4);
-        CK(cudaMemsetAsync(b->work_bins.p, 0, (size_t)WORK_BINS * 4, h->stream));
+        CK(cudaMemsetAsync(b->work_bins.p, 0, (size_t)WORK_BINS * 4, S));
         WorkSortParams WS{};
         WS.n_reads = R;
         WS.ordinal_base = p.ordinal_base;
@@ -659,9 +668,9 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         WS.keys = b->work_keys.as<uint32_t>();
         WS.bins = b->work_bins.as<uint32_t>();
         WS.work = b->work_sorted.as<uint32_t>();
-        work_key_kernel<<<(R + 255) / 256, 256, 0, h->stream>>>(WS);
-        work_scan_kernel<<<1, 1024, 0, h->stream>>>(WS.bins);
-        work_scatter_kernel<<<(R + 255) / 256, 256, 0, h->stream>>>(WS);
+        work_key_kernel<<<(R + 255) / 256, 256, 0, S>>>(WS);
+        work_scan_kernel<<<1, 1024, 0, S>>>(WS.bins);
+        work_scatter_kernel<<<(R + 255) / 256, 256, 0, S>>>(WS);
         CK(cudaGetLastError());
         launches += 3;
         uint32_t off = 0;
@@ -672,7 +681,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
     }
     // The classes are independent (own reads, own ticket counter): each gets its own stream so that
     // the CTAs of the next class fill the SMs the tail of the previous one leaves idle.
-    CK(cudaEventRecord(b->ev_sorted, h->stream));
+    CK(cudaEventRecord(b->ev_sorted, S));
     uint32_t used_streams = 0;
     for (int c = 0; c < N_CLASSES; c++) {
         if (p.n_work[c] == 0) continue;
@@ -694,7 +703,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         const int teams = c == GWS_CLASS ? 1 : SIM_WARPS / CLASS_W[c];
         int grid = (int)std::min<size_t>((size_t)h->num_sms, (P.n_work + teams - 1) / teams);
         const uint32_t si = used_streams % 4;
-        cudaStream_t st = h->class_stream[si];
+        cudaStream_t st = h->class_stream[b->lane][si];
         if (used_streams < 4) CK(cudaStreamWaitEvent(st, b->ev_sorted, 0));
         used_streams++;
         switch (c) {
@@ -708,10 +717,10 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         launches++;
     }
     for (uint32_t i = 0; i < std::min<uint32_t>(used_streams, 4); i++) {
-        CK(cudaEventRecord(b->ev_class[i], h->class_stream[i]));
-        CK(cudaStreamWaitEvent(h->stream, b->ev_class[i], 0));
+        CK(cudaEventRecord(b->ev_class[i], h->class_stream[b->lane][i]));
+        CK(cudaStreamWaitEvent(S, b->ev_class[i], 0));
     }
-    CK(cudaEventRecord(b->ev[1], h->stream));
+    CK(cudaEventRecord(b->ev[1], S));
     for (int o = 0; o < 2; o++) {
         if (!((o == 0 && want_bad) || (o == 1 && want_perf))) continue;
         FmtParams F{};
@@ -744,28 +753,29 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         F.rec_len = b->rec_len[o].as<uint32_t>();
         F.rec_off = b->rec_off[o].as<uint64_t>();
         F.out = b->out[o].as<uint8_t>();
-        reclen_kernel<<<(R + 255) / 256, 256, 0, h->stream>>>(F);
+        reclen_kernel<<<(R + 255) / 256, 256, 0, S>>>(F);
         run_scan(h, b, o, R, d_totals + o);
         int grid = (int)std::min<uint32_t>((R + 7) / 8, (uint32_t)h->num_sms * 8);
-        format_kernel<<<grid, 256, 0, h->stream>>>(F);
+        format_kernel<<<grid, 256, 0, S>>>(F);
         CK(cudaGetLastError());
         launches += 5;
     }
-    CK(cudaEventRecord(b->ev[2], h->stream));
-    CK(cudaMemcpyAsync(b->h_tot.p, d_totals, 32, cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaEventRecord(b->ev[4], h->stream));
+    CK(cudaEventRecord(b->ev[2], S));
+    CK(cudaMemcpyAsync(b->h_tot.p, d_totals, 32, cudaMemcpyDeviceToHost, S));
+    CK(cudaEventRecord(b->ev[4], S));
     b->launches = launches;
 }
 
 // Waits for the kernels of slot `b` and fills the statistics of the chunk.
 void slot_wait(tksm_seq* h, tksm_seq_batch* b, tksm_seq_stats* st) {
+    cudaStream_t S = h->lane_stream[b->lane];
     Prepared& p = b->prep;
     tksm_seq_stats s{};
     s.reads = p.n_reads;
     s.raw_bases = p.total_raw_bases;
     s.h2d_bytes = b->h2d_bytes;
     if (s.reads == 0) {
-        CK(cudaStreamSynchronize(h->stream));
+        CK(cudaStreamSynchronize(S));
         p.stage.reset();
         p.heap_blob.reset();
         p.blob = nullptr;
@@ -802,10 +812,11 @@ void slot_wait(tksm_seq* h, tksm_seq_batch* b, tksm_seq_stats* st) {
 }
 
 void batch_fetch(tksm_seq* h, tksm_seq_batch* b, int o, char* dst) {
+    cudaStream_t S = h->lane_stream[b->lane];
     if (b->out_bytes[o] == 0) return;
     CK(cudaSetDevice(h->cfg.device));
-    CK(cudaMemcpyAsync(dst, b->out[o].p, b->out_bytes[o], cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaMemcpyAsync(dst, b->out[o].p, b->out_bytes[o], cudaMemcpyDeviceToHost, S));
+    CK(cudaStreamSynchronize(S));
 }
 
 void add_stats(tksm_seq_stats& total, const tksm_seq_stats& s) {
@@ -1132,6 +1143,7 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
                 tksm_seq_batch* b = h->slots[issued % NS].get();
                 t0 = now_ms();
                 slot_reusable(b);
+                b->lane = (int)(issued & 1);
                 w_reuse += now_ms() - t0;
                 b->prep = std::move(*pp);
                 b->prep.ordinal_base = ordinal;
@@ -1172,8 +1184,7 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
                     now_ms(), g_ns_parse.load() / 1e6, g_ns_append.load() / 1e6, g_ns_prepare.load() / 1e6);
         (void)dev_ms;
     } catch (...) {
-        cudaStreamSynchronize(h->stream);
-        cudaStreamSynchronize(h->copy_stream);
+        cudaDeviceSynchronize();
         for (auto& sl : h->slots) sl->d2h_pending = false;
         release_arena();
         throw;
@@ -1270,7 +1281,10 @@ tksm_seq* tksm_seq_create(const tksm_seq_config* cfg) {
             h->num_sms = prop.multiProcessorCount;
             CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
             CK(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
-            for (auto& cs : h->class_stream) CK(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+            for (auto& lane : h->class_stream)
+                for (auto& cs : lane) CK(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+            h->lane_stream[0] = h->stream;
+            CK(cudaStreamCreateWithFlags(&h->lane_stream[1], cudaStreamNonBlocking));
         }
     } catch (const std::exception& e) {
         g_create_error = e.what();

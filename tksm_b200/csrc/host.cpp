@@ -440,11 +440,17 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
     TokEntry toks[NTOK];
     int tok_next = 0;
     size_t lit_epoch = 1;  // bumped when a rollback may have dropped pool bytes
+    TokEntry* last_tok = nullptr;  // exon lines of one molecule repeat the chromosome
     auto resolve = [&](std::string_view chrom) -> TokEntry& {
+        if (last_tok && last_tok->tok.size() == chrom.size() && !chrom.empty() &&
+            memcmp(last_tok->tok.data(), chrom.data(), chrom.size()) == 0)
+            return *last_tok;
         for (int i = 0; i < NTOK; i++)
             if (toks[i].tok.size() == chrom.size() && memcmp(toks[i].tok.data(), chrom.data(), chrom.size()) == 0 &&
-                (!chrom.empty() || toks[i].lit_epoch))
+                (!chrom.empty() || toks[i].lit_epoch)) {
+                last_tok = &toks[i];
                 return toks[i];
+            }
         TokEntry& t = toks[tok_next];
         tok_next = (tok_next + 1) % NTOK;
         t.tok.assign(chrom);
@@ -452,6 +458,7 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
         t.contig = it == genome->contigs.end() ? nullptr : &it->second;
         t.lit_s = t.lit_e = -1;
         t.lit_epoch = lit_epoch;
+        last_tok = &t;
         return t;
     };
 
