@@ -121,7 +121,10 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from tksm_b200.sequence import BADREAD, FASTQ, PERFECT, Sequencer
 
-    s = Sequencer(identity=tuple(float(x) for x in args.identity.split(",")), seed=42, device=local)
+    # host parser threads: the ranks of one box share its cores
+    local_world = int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))
+    host_threads = max(2, min(32, (os.cpu_count() or 1) // max(local_world, 1)))
+    s = Sequencer(identity=tuple(float(x) for x in args.identity.split(",")), seed=42, device=local, threads=host_threads)
     lengths = [max(1000, int(x * args.genome_scale)) for x in GRCH38]
     s.synth_reference(NAMES, lengths, n_frac=0.01, seed=42)
     have = os.path.exists(os.path.join(os.environ["TKSM_MODELS"], "badread", "nanopore2020.error.gz"))
@@ -205,7 +208,7 @@ def main():
                     "h2d_bytes_per_step": e2e_stats["h2d_bytes"] + len(mdf) * 0,
                     "d2h_bytes_per_step": e2e_stats["d2h_bytes"],
                     "ms_per_step": e2e_wall_max / args.e2e_steps * 1e3 if args.e2e_steps else None,
-                    "host_threads": min(os.cpu_count() or 1, 32),
+                    "host_threads": host_threads,
                     "note": "tksm_seq_simulate_text: MDF text in host memory -> parse (host threads) -> H2D -> kernels -> "
                             "D2H of the FASTQ bytes into a page-locked host buffer, chunks pipelined"},
             "gpu_launches": launches,

@@ -26,7 +26,7 @@ def output_is_fastq(path):
 
 class Sequencer:
     def __init__(self, identity=(84.0, 99.0, 5.5), seed=42, skip_qual_compute=False, device=0, host_only=False,
-                 corr=None, batch_reads=0, batch_bases=0):
+                 corr=None, batch_reads=0, batch_bases=0, threads=0):
         self._L = _lib.lib()
         cfg = Config()
         self._L.tksm_seq_default_config(C.byref(cfg))
@@ -37,6 +37,7 @@ class Sequencer:
         cfg.host_only = int(host_only)
         cfg.batch_reads = batch_reads
         cfg.batch_bases = batch_bases
+        cfg.threads = threads   # host MDF parser threads; 0 = all hardware threads (max 32)
         if corr is not None:
             cfg.calib_overshoot, cfg.calib_kappa = corr
         self._h = self._L.tksm_seq_create(C.byref(cfg))
