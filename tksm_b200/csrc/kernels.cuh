@@ -1237,9 +1237,34 @@ __global__ void scan_final(const uint32_t* in, uint32_t n, const uint64_t* sums,
 
 __device__ __forceinline__ char hexdig(uint32_t v) { return (char)(v < 10 ? '0' + v : 'a' + (v - 10)); }
 
+// Warp-wide byte copy with 16-byte stores: a few head bytes bring the destination to a 16-byte
+// boundary, then every lane moves 16 bytes per step (the source is read as aligned words and
+// funnel-shifted into place), then the tail.  May read up to 7 bytes past src + n inside the same
+// allocation (scratch arenas and the header buffer are padded).
+__device__ __forceinline__ void warp_copy(uint8_t* dst, const uint8_t* src, uint32_t n, uint32_t lane) {
+    uint32_t head = (uint32_t)((16u - (uint32_t)((uintptr_t)dst & 15u)) & 15u);
+    head = min(head, n);
+    if (lane < head) dst[lane] = src[lane];
+    dst += head;
+    src += head;
+    n -= head;
+    const uint32_t nv = n >> 4;
+    const uint32_t sh = (uint32_t)((uintptr_t)src & 3u) * 8u;
+    const uint32_t* sw = (const uint32_t*)((uintptr_t)src & ~(uintptr_t)3);
+    uint4* dv = (uint4*)dst;
+    for (uint32_t i = lane; i < nv; i += 32) {
+        const uint32_t* p = sw + 4 * i;
+        const uint32_t a = p[0], b = p[1], c = p[2], d = p[3], e = sh ? p[4] : 0u;
+        dv[i] = make_uint4(__funnelshift_r(a, b, sh), __funnelshift_r(b, c, sh), __funnelshift_r(c, d, sh),
+                           __funnelshift_r(d, e, sh));
+    }
+    const uint32_t done = nv << 4, tail = n - done;
+    if (lane < tail) dst[done + lane] = src[done + lane];
+}
+
 // one warp per read
 __global__ void __launch_bounds__(256) format_kernel(const FmtParams F) {
-    __shared__ uint8_t hdr_s[8][160];
+    __shared__ __align__(16) uint8_t hdr_s[8][160];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint8_t* hdr = hdr_s[warp];
     for (uint32_t r = blockIdx.x * 8 + warp; r < F.n_reads; r += gridDim.x * 8) {
@@ -1285,14 +1310,14 @@ __global__ void __launch_bounds__(256) format_kernel(const FmtParams F) {
         hl = __shfl_sync(0xffffffffu, hl, 0);
         __syncwarp();
         uint8_t* o = F.out + F.rec_off[r];
-        for (uint32_t x = lane; x < hl; x += 32) o[x] = hdr[x];
+        warp_copy(o, hdr, hl, (uint32_t)lane);
         o += hl;
         for (uint32_t x = lane; x < idl; x += 32) o[x] = F.id_pool[id0 + x];
         o += idl;
         if (lane == 0) o[0] = '\n';
         o += 1;
         const uint8_t* s = F.seq + F.seq_off[r];
-        for (uint32_t x = lane; x < Lp; x += 32) o[x] = s[x];
+        warp_copy(o, s, Lp, (uint32_t)lane);
         o += Lp;
         if (lane == 0) o[0] = '\n';
         o += 1;
@@ -1304,7 +1329,7 @@ __global__ void __launch_bounds__(256) format_kernel(const FmtParams F) {
             o += 2;
             if (F.qual) {
                 const uint8_t* q = F.qual + F.seq_off[r];
-                for (uint32_t x = lane; x < Lp; x += 32) o[x] = q[x];
+                warp_copy(o, q, Lp, (uint32_t)lane);
             } else {
                 for (uint32_t x = lane; x < Lp; x += 32) o[x] = 'K';
             }
