@@ -334,7 +334,7 @@ void commit_reference(tksm_seq* h) {
 void compute_classes(tksm_seq* h) {
     const size_t nq = h->em.has_table ? ((size_t)1 << (2 * h->em.k)) : 0;
     const size_t qcls_bytes = (nq + 15) & ~size_t(15);
-    const size_t pool = SMEM_TOTAL - qcls_bytes - 64 - 128;
+    const size_t pool = SMEM_TOTAL - qcls_bytes - SIM_FIXED_SMEM - 128;
     for (int c = 0; c < GWS_CLASS; c++) {
         const int W = CLASS_W[c], teams = SIM_WARPS / W;
         const uint32_t hist_elem = W >= 8 ? 8 : 4;
@@ -344,9 +344,9 @@ void compute_classes(tksm_seq* h) {
         h->ncap[c] = ncap;
         h->cap_list[c] = list_capacity(ncap);
         h->slab[c] = slab_layout(W, hist_elem, ncap, h->cap_list[c]).bytes;
-        h->smem_bytes[c] = qcls_bytes + 64 + (size_t)h->slab[c] * teams + 128;
+        h->smem_bytes[c] = qcls_bytes + SIM_FIXED_SMEM + (size_t)h->slab[c] * teams + 128;
     }
-    h->smem_bytes[GWS_CLASS] = qcls_bytes + 64 + 128;
+    h->smem_bytes[GWS_CLASS] = qcls_bytes + SIM_FIXED_SMEM + 128;
 }
 
 void upload_models(tksm_seq* h) {
@@ -1089,7 +1089,8 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
                 arena = bigger;
                 arena_cap = arena_pool().capacity(arena);
             }
-            if (nbytes)
+            static const bool dbg_no_d2h = getenv("TKSM_DBG_NO_D2H") != nullptr;
+            if (nbytes && !dbg_no_d2h)
                 CK(cudaMemcpyAsync(arena + arena_pos, b->out[o_arena].p, nbytes, cudaMemcpyDeviceToHost, h->copy_stream));
             arena_pos += nbytes;
             s.d2h_bytes += nbytes;
@@ -1106,7 +1107,8 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
     try {
         WorkerPool pool(nthreads);
         std::vector<std::shared_future<std::shared_ptr<HostBatchList>>> group;
-        size_t group_text = 0, group_target = 1, groups_made = 0;
+        size_t group_text = 0, group_target = 1, groups_made = 0, ramp = 1;
+        uint64_t text_submitted = 0;
         const size_t max_group = 32;  // text chunks per device batch in steady state (1 MiB each)
         auto close_group = [&]() {
             if (group.empty()) return;
@@ -1116,11 +1118,18 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
             group.clear();
             group_text = 0;
             groups_made++;
-            group_target = std::min(group_target * 2, max_group);  // small batches first: the device starts early
+            // small batches first (the device starts early) and, when the input size is known, small
+            // batches last (short last download and kernel tail): a batch takes at most half of what is left
+            ramp = std::min(ramp * 2, max_group);
+            group_target = ramp;
+            if (text_total > text_submitted) {
+                const size_t left = (size_t)((text_total - text_submitted) >> 20);  // 1 MiB chunks left, about
+                group_target = std::min(ramp, std::max<size_t>(2, left / 2));
+            }
         };
         while (true) {
             // keep the parser threads fed
-            while (!src_done && pending.size() < 4) {
+            while (!src_done && pending.size() < 8) {  // look-ahead: the host threads keep working while this thread waits on the device
                 TextChunk tc;
                 if (!src.next(tc)) {
                     src_done = true;
@@ -1131,6 +1140,7 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
                 const tksm_seq* hc = h;
                 group.push_back(pool.submit([hc, tc]() { return std::make_shared<HostBatchList>(parse_chunk(hc, tc)); }).share());
                 group_text += tc.n;
+                text_submitted += tc.n;
                 if (group.size() >= group_target) close_group();
             }
             if (pending.empty()) break;
@@ -1143,7 +1153,10 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
                 tksm_seq_batch* b = h->slots[issued % NS].get();
                 t0 = now_ms();
                 slot_reusable(b);
-                b->lane = (int)(issued & 1);
+                // measured: alternating the batches between the two lanes is 5 % slower end to end than one
+                // lane (the class streams already overlap the tails); TKSM_SEQ_LANES=2 turns it on
+                static const bool two_lanes = getenv("TKSM_SEQ_LANES") && atoi(getenv("TKSM_SEQ_LANES")) == 2;
+                b->lane = two_lanes ? (int)(issued & 1) : 0;
                 w_reuse += now_ms() - t0;
                 b->prep = std::move(*pp);
                 b->prep.ordinal_base = ordinal;
@@ -1265,7 +1278,7 @@ tksm_seq* tksm_seq_create(const tksm_seq_config* cfg) {
     try {
         if (cfg) h->cfg = *cfg; else tksm_seq_default_config(&h->cfg);
         h->idh = make_identities(h->cfg.identity_mean, h->cfg.identity_stdev, h->cfg.identity_max);
-        h->stage_pool.reset(new StagePool(10, !h->cfg.host_only));
+        h->stage_pool.reset(new StagePool(14, !h->cfg.host_only));
         if (!h->cfg.host_only) {
             int ndev = 0;
             cudaError_t e = cudaGetDeviceCount(&ndev);

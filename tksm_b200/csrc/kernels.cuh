@@ -164,6 +164,7 @@ __device__ __forceinline__ bool crossed(uint32_t n, uint32_t loss, uint32_t ins,
 
 constexpr int SIM_THREADS = 768;     // 24 warps per CTA, one CTA per SM
 constexpr int SIM_WARPS = SIM_THREADS / 32;
+constexpr uint32_t SIM_FIXED_SMEM = 64 + 512;  // CTA-wide: lut3[64] | alias row of the all-'=' window (128 cells)
 constexpr uint32_t MISC_WORDS = 64;  // per-team scratch words
 constexpr uint32_t MISC_WSUM = 8;    // W + 1 words of scan partials
 constexpr uint32_t MISC_LISTN = 40;  // touched-list length (teams of more than one warp)
@@ -868,6 +869,8 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
         const int margin = (T.kq - 1) >> 1;
         const uint32_t jb = start_trim, je = Ttot - end_trim;
         WarpQueue sq{wq_a, wq_b, 0, 0};
+        const uint32_t* q0row = (const uint32_t*)(lut3 + 64);
+        const uint32_t lg0 = T.q_t9 ? (__ldg(&T.q_t9[0]) & 7u) : 0u;
         auto sample = [&](uint32_t off, uint32_t lg, uint32_t u, uint32_t j) {
             const uint32_t col = lg ? (u >> (16 - lg)) : 0u;
             const uint32_t e = __ldg(&T.q_alias[off + col]);
@@ -918,13 +921,22 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
                 const bool want = live && j >= jb && j < je;
                 const uint32_t wsel = t < 4 ? (t < 2 ? ur.x : ur.y) : (t < 6 ? ur.z : ur.w);
                 const uint32_t u16 = (wsel >> (16 * (t & 1u))) & 0xFFFFu;
-                bool slow = want;
+                bool slow = want, want_sample = true;
                 if (want && fast) {
                     const uint32_t ops18 = (opsP >> (2 * t)) & 0x3FFFFu;
                     const uint32_t gm = (dmask >> (t + 1)) & 0xFFu;
                     const uint32_t code3 = lut3[ops18 & 63u] + 27u * lut3[(ops18 >> 6) & 63u] + 729u * lut3[ops18 >> 12];
                     uint32_t ent = 0;
-                    if (gm == 0) {
+                    if ((gm | ops18) == 0) {
+                        // nine matches, no deletion: alias row staged in shared memory by the kernel prologue
+                        const uint32_t col = lg0 ? (u16 >> (16 - lg0)) : 0u;
+                        const uint32_t e = q0row[col];
+                        const uint32_t fr = (u16 << lg0) & 0xFFFFu;
+                        const uint32_t q = fr < (e & 0xFFFFu) ? ((e >> 16) & 127u) : ((e >> 23) & 127u);
+                        oq[j - jb] = (uint8_t)(q + 33);
+                        want_sample = false;
+                        slow = false;
+                    } else if (gm == 0) {
                         ent = __ldg(&T.q_t9[code3]);
                         slow = false;
                     } else if ((gm & (gm - 1)) == 0) {
@@ -936,7 +948,7 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
                             slow = false;
                         }
                     }
-                    if (!slow) sample(ent >> 3, ent & 7u, u16, j);
+                    if (!slow && want_sample) sample(ent >> 3, ent & 7u, u16, j);
                 }
                 sq.push(slow, j, u16);
                 const uint32_t cnt = sq.ready(false);
@@ -963,13 +975,19 @@ __global__ void __launch_bounds__(SIM_THREADS, 1) simulate_kernel(const SimParam
     const uint32_t qcls_bytes = (nq + 15) & ~15u;
     uint8_t* lut3 = smem + qcls_bytes;
     if (threadIdx.x < 64) lut3[threadIdx.x] = (uint8_t)((threadIdx.x & 3) + 3 * ((threadIdx.x >> 2) & 3) + 9 * (threadIdx.x >> 4));
+    // the window of nine matches is by far the most frequent one: its alias row lives in shared memory
+    uint32_t* q0row = (uint32_t*)(lut3 + 64);
+    if (P.T.q_t9 && threadIdx.x < 128) {
+        const uint32_t e0 = P.T.q_t9[0];
+        if (threadIdx.x < (1u << (e0 & 7u))) q0row[threadIdx.x] = P.T.q_alias[(e0 >> 3) + threadIdx.x];
+    }
     __syncthreads();
     uint8_t* ws;
     if (GWS)
         ws = P.gws + (size_t)blockIdx.x * P.slab_bytes;
     else
-        ws = smem + qcls_bytes + 64 + (size_t)tm.id * P.slab_bytes;
-    uint32_t* ticket = (uint32_t*)(smem + qcls_bytes + 64 + (GWS ? 0 : (size_t)TEAMS * P.slab_bytes)) + tm.id;
+        ws = smem + qcls_bytes + SIM_FIXED_SMEM + (size_t)tm.id * P.slab_bytes;
+    uint32_t* ticket = (uint32_t*)(smem + qcls_bytes + SIM_FIXED_SMEM + (GWS ? 0 : (size_t)TEAMS * P.slab_bytes)) + tm.id;
     if (P.lockstep) {
         // The CTA takes TEAMS consecutive work items (near-equal lengths: the list is sorted) and its
         // teams start each of them together, so the warps of a scheduler walk the same code at about
