@@ -87,6 +87,7 @@ struct DevTables {
     // fast path for 9-wide windows (kq == 9), entries = alias offset << 3 | log2 columns; 0 pointers when kq != 9
     const uint32_t* q_t9;         // 3^9: D-free windows, base-3 code of the ops (first op lowest)
     const uint32_t* q_t9d1;       // 3^9 * 24: one D run of 1..3 at gap g: code + 19683 * (3 g + dc - 1)
+    const uint32_t* q_t9d2;       // 3^9 * 28: single D columns at gaps g1 < g2: code + 19683 * (g1 (15 - g1) / 2 + g2 - g1 - 1)
     const uint32_t* q_alias;      // thr16 | qa << 16 | qb << 23
     uint32_t seed_lo, seed_hi;
 };

@@ -276,7 +276,7 @@ struct tksm_seq {
     std::unique_ptr<StagePool> stage_pool;
     int num_sms = 148;
     DBuf d_genome, d_exc_start, d_exc_len, d_exc_chr;
-    DBuf d_qcls, d_thr, d_alias, d_alts, d_ident, d_delta, d_qdirect, d_qhash, d_qrows, d_qalias, d_t9, d_t9d1;
+    DBuf d_qcls, d_thr, d_alias, d_alts, d_ident, d_delta, d_qdirect, d_qhash, d_qrows, d_qalias, d_t9, d_t9d1, d_t9d2;
     DevTables dt{};
     uint32_t ncap[N_CLASSES] = {};
     uint32_t cap_list[N_CLASSES] = {};
@@ -287,7 +287,7 @@ struct tksm_seq {
 
     ~tksm_seq() {
         for (DBuf* d : {&d_genome, &d_exc_start, &d_exc_len, &d_exc_chr, &d_qcls, &d_thr, &d_alias, &d_alts, &d_ident, &d_delta,
-                        &d_qdirect, &d_qhash, &d_qrows, &d_qalias, &d_t9, &d_t9d1})
+                        &d_qdirect, &d_qhash, &d_qrows, &d_qalias, &d_t9, &d_t9d1, &d_t9d2})
             d->release();
         slots.clear();
         if (copy_stream) cudaStreamDestroy(copy_stream);
@@ -364,6 +364,7 @@ void upload_models(tksm_seq* h) {
     upload_vec(h->d_qalias, h->qm.alias, h->stream);
     upload_vec(h->d_t9, h->qm.t9, h->stream);
     upload_vec(h->d_t9d1, h->qm.t9d1, h->stream);
+    upload_vec(h->d_t9d2, h->qm.t9d2, h->stream);
     CK(cudaStreamSynchronize(h->stream));
     DevTables& T = h->dt;
     T.k = h->em.k;
@@ -388,6 +389,7 @@ void upload_models(tksm_seq* h) {
     T.q_alias = h->d_qalias.as<uint32_t>();
     T.q_t9 = h->qm.t9.empty() ? nullptr : h->d_t9.as<uint32_t>();
     T.q_t9d1 = h->qm.t9d1.empty() ? nullptr : h->d_t9d1.as<uint32_t>();
+    T.q_t9d2 = h->qm.t9d2.empty() ? nullptr : h->d_t9d2.as<uint32_t>();
     T.seed_lo = (uint32_t)h->cfg.seed;
     T.seed_hi = (uint32_t)(h->cfg.seed >> 32);
 }

@@ -939,13 +939,26 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
                     } else if (gm == 0) {
                         ent = __ldg(&T.q_t9[code3]);
                         slow = false;
-                    } else if ((gm & (gm - 1)) == 0) {
-                        const uint32_t gpos = __ffs(gm) - 1, bi = t + 1 + gpos;
-                        const uint32_t w = bi < 4 ? x0 : bi < 8 ? x1 : bi < 12 ? x2 : x3;
-                        const uint32_t dc = (w >> (8 * (bi & 3u) + 2)) & 15u;
-                        if (dc <= 3) {
-                            ent = __ldg(&T.q_t9d1[code3 + 19683u * (3 * gpos + dc - 1)]);
-                            slow = false;
+                    } else {
+                        // D count in front of column bi of the 16-column strip (bi = t + 1 + gap)
+                        auto dc_of = [&](uint32_t bi) {
+                            const uint32_t w = bi < 4 ? x0 : bi < 8 ? x1 : bi < 12 ? x2 : x3;
+                            return (w >> (8 * (bi & 3u) + 2)) & 15u;
+                        };
+                        const uint32_t g1 = __ffs(gm) - 1;
+                        const uint32_t rest = gm & (gm - 1);
+                        if (rest == 0) {
+                            const uint32_t dc = dc_of(t + 1 + g1);
+                            if (dc <= 3) {
+                                ent = __ldg(&T.q_t9d1[code3 + 19683u * (3 * g1 + dc - 1)]);
+                                slow = false;
+                            }
+                        } else if ((rest & (rest - 1)) == 0) {
+                            const uint32_t g2 = __ffs(rest) - 1;
+                            if (dc_of(t + 1 + g1) == 1 && dc_of(t + 1 + g2) == 1) {
+                                ent = __ldg(&T.q_t9d2[code3 + 19683u * (g1 * (15 - g1) / 2 + g2 - g1 - 1)]);
+                                slow = false;
+                            }
                         }
                     }
                     if (!slow && want_sample) sample(ent >> 3, ent & 7u, u16, j);

@@ -479,6 +479,22 @@ QScoreModelHost pack_qscore_model(
                     qm.t9d1[code + (size_t)19683 * (3 * g + dc - 1)] = ent(d);
                 }
         }
+        // two single-column deletions (the most frequent windows the one-run table misses)
+        qm.t9d2.assign((size_t)19683 * 28, 0);
+        for (uint32_t code = 0; code < 19683; code++) {
+            std::string s(9, '=');
+            uint32_t c = code;
+            for (int x = 0; x < 9; x++) {
+                s[(size_t)x] = sym[c % 3];
+                c /= 3;
+            }
+            for (int g1 = 0; g1 < 8; g1++)
+                for (int g2 = g1 + 1; g2 < 8; g2++) {
+                    std::string d = s.substr(0, (size_t)g1 + 1) + "D" + s.substr((size_t)g1 + 1, (size_t)(g2 - g1)) + "D" +
+                                    s.substr((size_t)g2 + 1);
+                    qm.t9d2[code + (size_t)19683 * (size_t)(g1 * (15 - g1) / 2 + g2 - g1 - 1)] = ent(d);
+                }
+        }
     }
     // hash of D-bearing cigars
     size_t nD = 0;

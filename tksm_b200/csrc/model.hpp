@@ -38,7 +38,7 @@ struct QScoreModelHost {
     uint32_t hash_shift = 63, hash_mask = 1;
     std::vector<uint32_t> rows;  // pairs (alias offset, log2 columns)
     std::vector<uint32_t> alias;
-    std::vector<uint32_t> t9, t9d1;  // closure tables of the 9-wide fast path (empty when kq != 9)
+    std::vector<uint32_t> t9, t9d1, t9d2;  // closure tables of the 9-wide fast path (empty when kq != 9)
     std::vector<std::string> row_cigar;  // debug / tests
 };
 
