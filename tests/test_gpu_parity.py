@@ -249,3 +249,47 @@ def test_shard_plan_through_the_kernels(world):
     for n_ranks in (2, 3, 8):
         parts = [s.simulate(mdf[b0:b1], BADREAD, True, ordinal_base=ob) for b0, b1, ob, _ in s.shard_plan(mdf, n_ranks)]
         assert b"".join(parts) == whole
+
+
+def test_cli_front_end_files_and_fifo(world, tmp_path):
+    """`tksm sequence` (src/tksm.cpp:164-166 -> Sequencer_module -> tksm_sequence_main): the command
+    rule `sequence` of the Snakefile runs (Snakefile:283-305), on files and on a FIFO input
+    (enable_piping, Snakefile:247-280), against the library call on the same text."""
+    import subprocess
+    import threading
+    from tksm_b200.sequence import BADREAD, PERFECT
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tksm_b200", "tksm")
+    s = world["Sequencer"](seed=7)
+    s.add_reference_text(world["fasta"])
+    s.load_models("random", "random")
+    mdf = s.synth_mdf(1, 400, seed=4) + handmade_mdf().encode()
+    want = s.simulate(mdf, BADREAD, True)
+    want_perf = s.simulate(mdf, PERFECT, False)
+    fa, src = tmp_path / "g.fa", tmp_path / "in.mdf"
+    fa.write_text(world["fasta"])
+    src.write_bytes(mdf)
+    common = ["-r", str(fa), "--badread-error-model", "random", "--badread-qscore-model", "random", "-s", "7", "-t", "3"]
+    out, perf = tmp_path / "o.fastq", tmp_path / "p.fasta"
+    p = subprocess.run([exe, "sequence", "-i", str(src), "-o", str(out), "--perfect", str(perf)] + common,
+                       capture_output=True, text=True, timeout=120)
+    assert p.returncode == 0, p.stderr
+    assert out.read_bytes() == want and perf.read_bytes() == want_perf
+    fifo = tmp_path / "in.fifo"
+    os.mkfifo(fifo)
+
+    def feed():
+        with open(fifo, "wb") as f:
+            for i in range(0, len(mdf), 7919):   # odd-sized writes: records straddle them
+                f.write(mdf[i:i + 7919])
+    th = threading.Thread(target=feed)
+    th.start()
+    out2 = tmp_path / "o2.fq"
+    p = subprocess.run([exe, "sequence", "-i", str(fifo), "-o", str(out2)] + common, capture_output=True, text=True, timeout=120)
+    th.join()
+    assert p.returncode == 0, p.stderr
+    assert out2.read_bytes() == want
+    # a broken record makes the module exit 1 like the reference's uncaught exception does
+    bad = tmp_path / "bad.mdf"
+    bad.write_bytes(mdf + b"chr1\t0\n")
+    p = subprocess.run([exe, "sequence", "-i", str(bad), "-o", str(tmp_path / "o3.fq")] + common, capture_output=True, text=True, timeout=120)
+    assert p.returncode == 1 and "not enough values" in p.stderr
