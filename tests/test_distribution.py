@@ -11,9 +11,10 @@ Known, documented deviations:
    qscore histograms of the read interior are compared by total variation and mean instead of a
    chi-square test, whose power at that sample size rejects any model.  The `ideal` qscore model
    makes the deviation maximally visible (every 'X'/'I' base of the reference gets Q1-3, every base
-   PB1 labels '=' gets Q4+): 14 % of the bases a re-alignment calls 'X' and 23 % of those it calls
-   'I' (an inserted base inside a homopolymer, which the aligner left-shifts) carry a generative '='
-   label, hence the wider TV limit for those two classes under `ideal`.
+   PB1 labels '=' gets Q4+): 13 % of the bases a re-alignment calls 'X' carry a generative '=' label
+   (a deletion next to an insertion ties with two substitutions), hence the wider TV limit for that
+   class under `ideal`.  Inserted bases are left-normalised inside homopolymers like an aligner
+   does (4 % mislabelled, was 23 % before), so 'I' is held to the common limit.
  * the `read_identity=` header token is PB1's *predicted* aligned identity; the reference prints the
    identity of its own flank-inclusive alignment, which runs 0.15 points above the identity of the
    read body.  The token is compared on mean and spread, the measured per-read identity by KS.
@@ -163,10 +164,10 @@ def compare(name, mine, ref, qdev=True):
                 continue
             tv = 0.5 * np.abs(a / a.sum() - b / b.sum()).sum()
             ma, mb = (a * np.arange(94)).sum() / a.sum(), (b * np.arange(94)).sum() / b.sum()
-            lim = (0.25 if ideal and oc else 0.10) + tv_noise(a, b)
+            lim = (0.16 if ideal and oc == 1 else 0.10) + tv_noise(a, b)
             va = (a * (np.arange(94) - ma) ** 2).sum() / a.sum()
             vb = (b * (np.arange(94) - mb) ** 2).sum() / b.sum()
-            mlim = (2.0 if ideal and oc else 1.0) + 3.0 * float(np.sqrt(va / a.sum() + vb / b.sum()))
+            mlim = 1.0 + 3.0 * float(np.sqrt(va / a.sum() + vb / b.sum()))
             if tv > lim or abs(ma - mb) > mlim:
                 fails.append(f"qscores of '{opname}' bases, position class {pc}: TV {tv:.3f} > {lim:.3f}, "
                              f"mean {ma:.2f} vs reference {mb:.2f}")

@@ -124,7 +124,7 @@ struct DevBatch {
     uint32_t* status;              // 0 ok, else error bits
 };
 
-enum : uint32_t { ST_OK = 0, ST_OPS_OVERFLOW = 1, ST_SCRATCH_OVERFLOW = 2, ST_EPOCH_CAP = 4 };
+enum : uint32_t { ST_OK = 0, ST_OPS_OVERFLOW = 1, ST_SCRATCH_OVERFLOW = 2, ST_EPOCH_CAP = 4, ST_FIXUP_OVERFLOW = 8 };
 
 // run flags
 enum : uint32_t {

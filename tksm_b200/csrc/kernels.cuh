@@ -168,6 +168,7 @@ constexpr uint32_t SIM_FIXED_SMEM = 64 + 512;  // CTA-wide: lut3[64] | alias row
 constexpr uint32_t MISC_WORDS = 64;  // per-team scratch words
 constexpr uint32_t MISC_WSUM = 8;    // W + 1 words of scan partials
 constexpr uint32_t MISC_LISTN = 40;  // touched-list length (teams of more than one warp)
+constexpr uint32_t MISC_FIXN = 41;   // number of insertion-label fix-ups queued by the expand stage
 constexpr uint32_t QUEUE_BYTES = 64 * 4 + 64 * 4;  // per-warp compaction queue: 64 x (u32, u32)
 
 struct SimParams {
@@ -500,7 +501,10 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
     const float delta = T.delta_tab[bin];
     const uint16_t* thr_bin = T.thr + (size_t)bin * Q_CLASSES * THR_PER_CLASS;
     for (uint32_t c = tm.rank; c < Q_CLASSES; c += SIZE) T1[c] = thr_bin[c * THR_PER_CLASS];
-    if (tm.rank == 0) misc[MISC_LISTN] = 0;
+    if (tm.rank == 0) {
+        misc[MISC_LISTN] = 0;
+        misc[MISC_FIXN] = 0;
+    }
     phase_sync();
 
     // ---- 3. error injection epochs
@@ -785,6 +789,30 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
             const uint32_t op = u == eqpos ? OP_EQ : (first_x && u == 0) ? OP_X : OP_I;
             if (j < opcap) ops_put(keyb, j, op | ((u == 0 ? dc : 0u) << 2));
         }
+        // Left-normalised insertion label: a single inserted base that repeats the
+        // base(s) on its left is labelled on the first base of that run, where an aligner that traces
+        // back from the end puts the gap.  Only unchanged slots are walked over, so the ranges of two
+        // fix-ups never overlap; they are applied after the whole read has its ops (the epoch's
+        // touched list is free by now and holds them).
+        if (len == 2 && !first_x) {
+            const uint32_t uI = 1u - eqpos;
+            const uint32_t cI = kind == 0u ? content_base(c, uI) : content_base(c, 0);
+            uint32_t m = 0;
+            bool go = true;
+            if (uI == 1u) {
+                const uint32_t c0 = kind == 0u ? content_base(c, 0) : b;
+                if (c0 == cI) m = 1; else go = false;
+            }
+            if (go)
+                for (uint32_t q = p; q > 0 && m < 255; q--) {
+                    if (frag[q - 1] != cI || key16[2 * (q - 1)] != 0xFFFFu) break;
+                    m++;
+                }
+            if (m) {
+                const uint32_t e = atomicAdd(&misc[MISC_FIXN], 1u);
+                if (e < P.cap_list) list[e] = (o + uI) | (m << 24);
+            }
+        }
     };
     for (uint32_t base = 0; base < n; base += 4 * SIZE) {
         const uint32_t p0 = base + 4 * tm.rank;
@@ -852,6 +880,19 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
     for (uint32_t cnt; (cnt = xq.ready(true)) != 0;) expand_changed(cnt);
     const uint32_t Ttot = carry;
     const uint32_t Lp = Ttot - start_trim - end_trim;
+    tm.sync();
+    {
+        const uint32_t nfix = misc[MISC_FIXN];
+        if (nfix > P.cap_list) {
+            status |= ST_FIXUP_OVERFLOW;  // never seen: would need 40 % of the slots to be such insertions
+        } else if (Ttot <= opcap) {
+            for (uint32_t e = tm.rank; e < nfix; e += SIZE) {
+                const uint32_t v = list[e], jI = v & 0xFFFFFFu, m = v >> 24;
+                ops_put(keyb, jI, OP_EQ);
+                ops_put(keyb, jI - m, OP_I | (ops_at(keyb, jI - m) & ~3u));
+            }
+        }
+    }
     if (Ttot > opcap) status |= ST_OPS_OVERFLOW;
     if (Lp > scap) status |= ST_SCRATCH_OVERFLOW;
     if (tm.rank == 0) {
