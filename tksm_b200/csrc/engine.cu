@@ -1111,7 +1111,8 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
         std::vector<std::shared_future<std::shared_ptr<HostBatchList>>> group;
         size_t group_text = 0, group_target = 1, groups_made = 0, ramp = 1;
         uint64_t text_submitted = 0;
-        const size_t max_group = 32;  // text chunks per device batch in steady state (1 MiB each)
+        // text chunks (1 MiB each) per device batch in steady state
+        const size_t max_group = getenv("TKSM_SEQ_MAX_GROUP") ? std::max(1, atoi(getenv("TKSM_SEQ_MAX_GROUP"))) : 32;
         auto close_group = [&]() {
             if (group.empty()) return;
             const tksm_seq* hc = h;
