@@ -293,3 +293,18 @@ def test_cli_front_end_files_and_fifo(world, tmp_path):
     bad.write_bytes(mdf + b"chr1\t0\n")
     p = subprocess.run([exe, "sequence", "-i", str(bad), "-o", str(tmp_path / "o3.fq")] + common, capture_output=True, text=True, timeout=120)
     assert p.returncode == 1 and "not enough values" in p.stderr
+
+
+def test_fused_and_split_kernels_agree(world, monkeypatch):
+    """The simulate stage runs as two kernels per length class by default (error injection | expansion +
+    qscores, state handed over through global memory); TKSM_SIM_SPLIT=0 runs the fused kernel."""
+    from tksm_b200.sequence import BADREAD, PERFECT
+    s = world["Sequencer"](seed=5)
+    s.add_reference_text(world["fasta"])
+    s.load_models("nanopore2020" if HAVE_MODELS else "random", "nanopore2020" if HAVE_MODELS else "random")
+    mdf = s.synth_mdf(1, 600, seed=12) + s.synth_mdf(2, 40, seed=13, min_len=300, max_len=60000) + handmade_mdf().encode()
+    out = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("TKSM_SIM_SPLIT", mode)
+        out[mode] = (s.simulate(mdf, BADREAD, True), s.simulate(mdf, PERFECT, False), s.simulate(mdf, BADREAD, False))
+    assert out["0"] == out["1"]

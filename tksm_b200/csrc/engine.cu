@@ -216,7 +216,7 @@ struct tksm_seq_batch {
     DBuf blob;
     DevBatch db{};
     uint32_t* d_work[N_CLASSES] = {};
-    DBuf scr_seq, scr_qual, scr_raw, per_read, out[2], rec_len[2], rec_off[2], sums, gws, counters, work_keys, work_sorted, work_bins;
+    DBuf scr_seq, scr_qual, scr_raw, per_read, out[2], rec_len[2], rec_off[2], sums, gws, counters, work_keys, work_sorted, work_bins, mid;
     HBuf stage;           // pinned upload staging
     HBuf host_out[2];     // pinned download staging (streaming to files)
     HBuf h_tot;           // pinned: record bytes per output, read bases, status
@@ -239,7 +239,7 @@ struct tksm_seq_batch {
     }
     ~tksm_seq_batch() {
         for (DBuf* d : {&blob, &scr_seq, &scr_qual, &scr_raw, &per_read, &out[0], &out[1], &rec_len[0], &rec_len[1],
-                        &rec_off[0], &rec_off[1], &sums, &gws, &counters, &work_keys, &work_sorted, &work_bins})
+                        &rec_off[0], &rec_off[1], &sums, &gws, &counters, &work_keys, &work_sorted, &work_bins, &mid})
             d->release();
         stage.release();
         host_out[0].release();
@@ -394,12 +394,27 @@ void upload_models(tksm_seq* h) {
     T.seed_hi = (uint32_t)(h->cfg.seed >> 32);
 }
 
-template <int W, bool GWS>
-void launch_sim(cudaStream_t stream, const SimParams& P, size_t smem, int grid) {
-    auto kern = simulate_kernel<W, GWS>;
+template <int W, bool GWS, int PHASE>
+void launch_sim_phase(cudaStream_t stream, const SimParams& P, size_t smem, int grid) {
+    auto kern = simulate_kernel<W, GWS, PHASE>;
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<grid, SIM_THREADS, smem, stream>>>(P);
     CK(cudaGetLastError());
+}
+
+// one kernel per class, or (split) error injection and expansion + qscores as two kernels with
+// their own ticket counters (P.counter, P.counter + 16)
+template <int W, bool GWS>
+void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, bool split) {
+    if (!split) {
+        launch_sim_phase<W, GWS, 0>(stream, P, smem, grid);
+        return;
+    }
+    launch_sim_phase<W, GWS, 1>(stream, P, smem, grid);
+    if (P.flags & RUN_ERRORS) {
+        P.counter += 16;
+        launch_sim_phase<W, GWS, 2>(stream, P, smem, grid);
+    }
 }
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -569,7 +584,7 @@ void slot_bind(tksm_seq* h, tksm_seq_batch* b) {
     D.ident_num = D.read_len + R;
     D.ident_den = D.ident_num + R;
     D.status = D.ident_den + R;
-    b->counters.ensure(64);
+    b->counters.ensure(128);
     b->h_tot.ensure(64);
     b->ensure_events();
     b->bound = true;
@@ -641,7 +656,11 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         b->gws.ensure((size_t)slab_c[GWS_CLASS] * h->num_sms);
     }
     uint64_t* d_totals = (uint64_t*)((char*)b->counters.p + CNT_TOTALS);
-    CK(cudaMemsetAsync(b->counters.p, 0, 64, S));
+    CK(cudaMemsetAsync(b->counters.p, 0, 128, S));
+    // error injection and expansion + qscores as two kernels per class (3 % faster than the fused kernel: less
+    // hot code per SM); TKSM_SIM_SPLIT=0 selects the fused kernel
+    const bool split = !(getenv("TKSM_SIM_SPLIT") && atoi(getenv("TKSM_SIM_SPLIT")) == 0);
+    if (split && want_bad) b->mid.ensure(3 * p.scr_total + 64 * (uint64_t)R + 64);
 
     CK(cudaEventRecord(b->ev[0], S));
     uint32_t launches = 0;
@@ -698,6 +717,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         P.cap_list = cap_list_c[c];
         P.slab_bytes = slab_c[c];
         P.gws = b->gws.as<uint8_t>();
+        P.mid = b->mid.as<uint8_t>();
         {
             static const int mode = getenv("TKSM_SIM_LOCKSTEP") ? atoi(getenv("TKSM_SIM_LOCKSTEP")) : 0;
             P.lockstep = (uint32_t)mode;
@@ -709,14 +729,14 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         if (used_streams < 4) CK(cudaStreamWaitEvent(st, b->ev_sorted, 0));
         used_streams++;
         switch (c) {
-            case 0: launch_sim<1, false>(st, P, h->smem_bytes[c], grid); break;
-            case 1: launch_sim<2, false>(st, P, h->smem_bytes[c], grid); break;
-            case 2: launch_sim<4, false>(st, P, h->smem_bytes[c], grid); break;
-            case 3: launch_sim<8, false>(st, P, h->smem_bytes[c], grid); break;
-            case 4: launch_sim<24, false>(st, P, h->smem_bytes[c], grid); break;
-            default: launch_sim<24, true>(st, P, h->smem_bytes[c], grid); break;
+            case 0: launch_sim<1, false>(st, P, h->smem_bytes[c], grid, split); break;
+            case 1: launch_sim<2, false>(st, P, h->smem_bytes[c], grid, split); break;
+            case 2: launch_sim<4, false>(st, P, h->smem_bytes[c], grid, split); break;
+            case 3: launch_sim<8, false>(st, P, h->smem_bytes[c], grid, split); break;
+            case 4: launch_sim<24, false>(st, P, h->smem_bytes[c], grid, split); break;
+            default: launch_sim<24, true>(st, P, h->smem_bytes[c], grid, split); break;
         }
-        launches++;
+        launches += (split && (flags & RUN_ERRORS)) ? 2 : 1;
     }
     for (uint32_t i = 0; i < std::min<uint32_t>(used_streams, 4); i++) {
         CK(cudaEventRecord(b->ev_class[i], h->class_stream[b->lane][i]));

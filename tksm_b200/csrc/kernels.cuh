@@ -183,6 +183,7 @@ struct SimParams {
     uint32_t slab_bytes;    // bytes of one team workspace
     uint8_t* gws;           // global workspaces (one per CTA) when GWS
     uint32_t lockstep;      // 1: CTA-wide tickets, teams start their reads together
+    uint8_t* mid;           // PHASE 1 -> 2 records (split kernels), 3 * scratch bytes + 64 per read
 };
 
 // Team workspace layout, shared by the host (sizing) and the kernel:
@@ -349,7 +350,10 @@ __device__ __forceinline__ uint32_t nz4(uint32_t x, uint32_t mask) {
 }
 
 // ------------------------------------------------------------ simulate one
-template <int W, bool GWS>
+// PHASE 0: the whole read in one kernel.  PHASE 1: materialise + error injection, then slot keys and
+// fragment go to the read's `mid` record in global memory.  PHASE 2: loads them back and does
+// expansion + qscores.  Two kernels halve the hot code an SM has to keep in its instruction caches.
+template <int W, bool GWS, int PHASE>
 __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams& P, uint32_t r, uint8_t* ws,
                                               const uint8_t* qcls_s, const uint8_t* lut3, uint32_t phase_threads) {
     // lockstep mode 2: the teams of the CTA also enter the error, expansion and qscore stages
@@ -384,6 +388,15 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
     const uint32_t olo = (uint32_t)ordinal, ohi = (uint32_t)(ordinal >> 32);
     const uint32_t k0 = T.seed_lo, k1 = T.seed_hi;
 
+    const uint64_t sbase = B.scr_off[r];
+    const uint32_t scap = (uint32_t)(B.scr_off[r + 1] - sbase);
+    uint32_t loss_c = 0, ins_c = 0;  // committed totals
+    uint32_t status = ST_OK;
+    // mid record of the read (PHASE 1 -> 2): keys (n rounded up to 4 slots) | fragment (n + 32 bytes);
+    // 3 * scratch bytes + 64 per read always holds it (scratch is 2 L + 32 per read, rounded up to 16)
+    uint4* mid4 = PHASE == 0 ? nullptr : (uint4*)(P.mid + 3 * sbase + 64 * (uint64_t)r);
+    const uint32_t key_q = (n + 3) >> 2, frag_q = (n + 32 + 15) >> 4;  // 16-byte units
+    if (PHASE != 2) {
     // ---- 1. materialise flank + molecule + flank as fragment codes
     {
         uint4 fl = philox4x32_10(2, TAG_READ, olo, ohi, k0, k1);
@@ -446,8 +459,6 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
     }
     tm.sync();
 
-    const uint64_t sbase = B.scr_off[r];
-    const uint32_t scap = (uint32_t)(B.scr_off[r + 1] - sbase);
     if ((P.flags & RUN_RAW) && B.scr_raw) {
         uint8_t* raw = B.scr_raw + B.raw_off[r];
         for (uint32_t x = tm.rank; x < L; x += SIZE) raw[x] = code_ascii(frag[k + x]);
@@ -508,8 +519,7 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
     phase_sync();
 
     // ---- 3. error injection epochs
-    uint32_t loss_c = 0, ins_c = 0, changed_c = 0;  // committed totals
-    uint32_t status = ST_OK;
+    uint32_t changed_c = 0;
     uint32_t list_n = 0;  // W == 1: the touched-list length lives in a (warp-uniform) register
     const uint32_t npos = n - k;
     const uint32_t vm0 = k >= 4 ? 0xFCFCFCFCu : (0xFCFCFCFCu >> (8 * (4 - k)));
@@ -743,6 +753,29 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
     }
     tm.sync();
     phase_sync();
+    }  // PHASE != 2
+    if (PHASE == 1) {
+        const uint4* k4 = (const uint4*)key;
+        const uint4* f4 = (const uint4*)frag;
+        for (uint32_t x = tm.rank; x < key_q; x += SIZE) mid4[x] = k4[x];
+        for (uint32_t x = tm.rank; x < frag_q; x += SIZE) mid4[key_q + x] = f4[x];
+        if (tm.rank == 0) {
+            B.ident_num[r] = n - loss_c;
+            B.ident_den[r] = n + ins_c;
+            B.status[r] = status;
+        }
+        tm.sync();
+        return;
+    }
+    if (PHASE == 2) {
+        uint4* k4 = (uint4*)key;
+        uint4* f4 = (uint4*)frag;
+        for (uint32_t x = tm.rank; x < key_q; x += SIZE) k4[x] = mid4[x];
+        for (uint32_t x = tm.rank; x < frag_q; x += SIZE) f4[x] = mid4[key_q + x];
+        status = B.status[r];
+        if (tm.rank == 0) misc[MISC_FIXN] = 0;
+        tm.sync();
+    }
 
     // ---- 4. slot contents are the low halves of the keys: content16, or 0xFFFF for an unchanged slot
     //         (dropped candidates were reset); the high halves are free for the cigar ops from here on
@@ -897,8 +930,10 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
     if (Lp > scap) status |= ST_SCRATCH_OVERFLOW;
     if (tm.rank == 0) {
         B.read_len[r] = Lp;
-        B.ident_num[r] = n - loss_c;
-        B.ident_den[r] = n + ins_c;
+        if (PHASE == 0) {
+            B.ident_num[r] = n - loss_c;
+            B.ident_den[r] = n + ins_c;
+        }
         B.status[r] = status;
     }
     tm.sync();
@@ -1014,7 +1049,7 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
     tm.sync();
 }
 
-template <int W, bool GWS>
+template <int W, bool GWS, int PHASE>
 __global__ void __launch_bounds__(SIM_THREADS, 1) simulate_kernel(const SimParams P) {
     extern __shared__ __align__(16) uint8_t smem[];
     constexpr int TEAMS = SIM_WARPS / W;
@@ -1056,7 +1091,7 @@ __global__ void __launch_bounds__(SIM_THREADS, 1) simulate_kernel(const SimParam
             if (base >= P.n_work) break;
             const uint32_t nact = min((uint32_t)TEAMS, P.n_work - base);
             if (wi < P.n_work)
-                simulate_read<W, GWS>(tm, P, P.work[wi], ws, qcls_s, lut3, P.lockstep >= 2 ? nact * (uint32_t)(W * 32) : 0u);
+                simulate_read<W, GWS, PHASE>(tm, P, P.work[wi], ws, qcls_s, lut3, P.lockstep >= 2 ? nact * (uint32_t)(W * 32) : 0u);
         }
         return;
     }
@@ -1066,7 +1101,7 @@ __global__ void __launch_bounds__(SIM_THREADS, 1) simulate_kernel(const SimParam
         const uint32_t wi = *ticket;
         tm.sync();
         if (wi >= P.n_work) break;
-        simulate_read<W, GWS>(tm, P, P.work[wi], ws, qcls_s, lut3, 0u);
+        simulate_read<W, GWS, PHASE>(tm, P, P.work[wi], ws, qcls_s, lut3, 0u);
     }
 }
 
