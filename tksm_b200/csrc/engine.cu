@@ -282,6 +282,9 @@ struct tksm_seq {
     uint32_t cap_list[N_CLASSES] = {};
     uint32_t slab[N_CLASSES] = {};
     size_t smem_bytes[N_CLASSES] = {};
+    // PHASE 2 kernels (split mode): lean team workspaces, 32 warps per CTA where they fit
+    uint32_t cap_list2[N_CLASSES] = {}, slab2[N_CLASSES] = {}, threads2[N_CLASSES] = {};
+    size_t smem_bytes2[N_CLASSES] = {};
     std::vector<uint16_t> thr;
     bool attrs_set = false;
 
@@ -345,8 +348,16 @@ void compute_classes(tksm_seq* h) {
         h->cap_list[c] = list_capacity(ncap);
         h->slab[c] = slab_layout(W, hist_elem, ncap, h->cap_list[c]).bytes;
         h->smem_bytes[c] = qcls_bytes + SIM_FIXED_SMEM + (size_t)h->slab[c] * teams + 128;
+        // PHASE 2: same fragment capacity, no k-mer classes, fix-up list only
+        h->cap_list2[c] = ncap / 8 + 64;
+        h->slab2[c] = slab_layout(W, hist_elem, ncap, h->cap_list2[c], true).bytes;
+        h->threads2[c] = SIM_THREADS;
+        if (32 % W == 0 && SIM_FIXED_SMEM + (size_t)h->slab2[c] * (32 / W) + 128 + 64 <= SMEM_TOTAL) h->threads2[c] = 1024;
+        h->smem_bytes2[c] = SIM_FIXED_SMEM + (size_t)h->slab2[c] * (h->threads2[c] / 32 / W) + 128 + 64;
     }
     h->smem_bytes[GWS_CLASS] = qcls_bytes + SIM_FIXED_SMEM + 128;
+    h->threads2[GWS_CLASS] = SIM_THREADS;
+    h->smem_bytes2[GWS_CLASS] = SIM_FIXED_SMEM + 128 + 64;
 }
 
 void upload_models(tksm_seq* h) {
@@ -395,17 +406,22 @@ void upload_models(tksm_seq* h) {
 }
 
 template <int W, bool GWS, int PHASE>
-void launch_sim_phase(cudaStream_t stream, const SimParams& P, size_t smem, int grid) {
+void launch_sim_phase(cudaStream_t stream, const SimParams& P, size_t smem, int grid, int threads = SIM_THREADS) {
     auto kern = simulate_kernel<W, GWS, PHASE>;
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<grid, SIM_THREADS, smem, stream>>>(P);
+    kern<<<grid, threads, smem, stream>>>(P);
     CK(cudaGetLastError());
 }
 
 // one kernel per class, or (split) error injection and expansion + qscores as two kernels with
 // their own ticket counters (P.counter, P.counter + 16)
+struct Phase2Launch {
+    size_t smem;
+    int grid, threads;
+    uint32_t slab_bytes, cap_list;
+};
 template <int W, bool GWS>
-void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, bool split) {
+void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, bool split, const Phase2Launch& p2) {
     if (!split) {
         launch_sim_phase<W, GWS, 0>(stream, P, smem, grid);
         return;
@@ -413,7 +429,9 @@ void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, bool sp
     launch_sim_phase<W, GWS, 1>(stream, P, smem, grid);
     if (P.flags & RUN_ERRORS) {
         P.counter += 16;
-        launch_sim_phase<W, GWS, 2>(stream, P, smem, grid);
+        P.slab_bytes = p2.slab_bytes;
+        P.cap_list = p2.cap_list;
+        launch_sim_phase<W, GWS, 2>(stream, P, p2.smem, p2.grid, p2.threads);
     }
 }
 
@@ -724,17 +742,26 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         }
         const int teams = c == GWS_CLASS ? 1 : SIM_WARPS / CLASS_W[c];
         int grid = (int)std::min<size_t>((size_t)h->num_sms, (P.n_work + teams - 1) / teams);
+        Phase2Launch p2;
+        {
+            const int teams2 = c == GWS_CLASS ? 1 : (int)h->threads2[c] / 32 / CLASS_W[c];
+            p2.smem = h->smem_bytes2[c];
+            p2.grid = (int)std::min<size_t>((size_t)h->num_sms, (P.n_work + teams2 - 1) / teams2);
+            p2.threads = (int)h->threads2[c];
+            p2.slab_bytes = c == GWS_CLASS ? slab_c[c] : h->slab2[c];   // the global workspaces keep their size
+            p2.cap_list = c == GWS_CLASS ? cap_list_c[c] : h->cap_list2[c];
+        }
         const uint32_t si = used_streams % 4;
         cudaStream_t st = h->class_stream[b->lane][si];
         if (used_streams < 4) CK(cudaStreamWaitEvent(st, b->ev_sorted, 0));
         used_streams++;
         switch (c) {
-            case 0: launch_sim<1, false>(st, P, h->smem_bytes[c], grid, split); break;
-            case 1: launch_sim<2, false>(st, P, h->smem_bytes[c], grid, split); break;
-            case 2: launch_sim<4, false>(st, P, h->smem_bytes[c], grid, split); break;
-            case 3: launch_sim<8, false>(st, P, h->smem_bytes[c], grid, split); break;
-            case 4: launch_sim<24, false>(st, P, h->smem_bytes[c], grid, split); break;
-            default: launch_sim<24, true>(st, P, h->smem_bytes[c], grid, split); break;
+            case 0: launch_sim<1, false>(st, P, h->smem_bytes[c], grid, split, p2); break;
+            case 1: launch_sim<2, false>(st, P, h->smem_bytes[c], grid, split, p2); break;
+            case 2: launch_sim<4, false>(st, P, h->smem_bytes[c], grid, split, p2); break;
+            case 3: launch_sim<8, false>(st, P, h->smem_bytes[c], grid, split, p2); break;
+            case 4: launch_sim<24, false>(st, P, h->smem_bytes[c], grid, split, p2); break;
+            default: launch_sim<24, true>(st, P, h->smem_bytes[c], grid, split, p2); break;
         }
         launches += (split && (flags & RUN_ERRORS)) ? 2 : 1;
     }

@@ -71,11 +71,12 @@ struct Team {
     static constexpr int SIZE = W * 32;
     int rank;  // thread rank inside the team
     int id;    // team index inside the CTA
+    int bar;   // named barrier of the team (W > 1): id + 1, or id when the CTA holds 16 teams
     __device__ __forceinline__ void sync() const {
         if (W == 1)
             __syncwarp();
         else
-            asm volatile("bar.sync %0, %1;" ::"r"(id + 1), "n"(W * 32) : "memory");
+            asm volatile("bar.sync %0, %1;" ::"r"(bar), "n"(W * 32) : "memory");
     }
 };
 
@@ -191,10 +192,12 @@ struct SimParams {
 struct SlabLayout {
     uint32_t off_hist, off_misc, off_queue, off_list, off_key, off_frag, bytes;
 };
-__host__ __device__ inline SlabLayout slab_layout(int W, uint32_t hist_elem_bytes, uint32_t ncap, uint32_t cap_list) {
+// `lean` (PHASE 2 kernels: expansion + qscores) drops the threshold row and the histogram.
+__host__ __device__ inline SlabLayout slab_layout(int W, uint32_t hist_elem_bytes, uint32_t ncap, uint32_t cap_list,
+                                                  bool lean = false) {
     SlabLayout L;
-    L.off_hist = 512;
-    L.off_misc = L.off_hist + 256 * hist_elem_bytes;
+    L.off_hist = lean ? 0u : 512u;
+    L.off_misc = L.off_hist + (lean ? 0u : 256 * hist_elem_bytes);
     L.off_queue = L.off_misc + MISC_WORDS * 4;
     L.off_list = L.off_queue + (uint32_t)W * QUEUE_BYTES;
     L.off_key = (L.off_list + 4 * cap_list + 15u) & ~15u;
@@ -365,7 +368,7 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
     constexpr int SIZE = Team<W>::SIZE;
     const DevTables& T = P.T;
     const DevBatch& B = P.B;
-    const SlabLayout LY = slab_layout(W, (uint32_t)sizeof(HistT), P.ncap, P.cap_list);
+    const SlabLayout LY = slab_layout(W, (uint32_t)sizeof(HistT), P.ncap, P.cap_list, PHASE == 2);
 
     uint16_t* T1 = (uint16_t*)ws;
     HistT* hist = (HistT*)(ws + LY.off_hist);
@@ -1050,15 +1053,18 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
 }
 
 template <int W, bool GWS, int PHASE>
-__global__ void __launch_bounds__(SIM_THREADS, 1) simulate_kernel(const SimParams P) {
+__global__ void __launch_bounds__(PHASE == 2 ? 1024 : SIM_THREADS, 1) simulate_kernel(const SimParams P) {
     extern __shared__ __align__(16) uint8_t smem[];
-    constexpr int TEAMS = SIM_WARPS / W;
+    // 24 warps per CTA; the PHASE 2 kernels need fewer registers and less shared memory per team and
+    // run 32 warps per CTA where the team workspaces fit (the host decides: blockDim.x)
+    const int TEAMS = (int)(blockDim.x >> 5) / W;
     Team<W> tm;
     tm.rank = threadIdx.x % (W * 32);
     tm.id = threadIdx.x / (W * 32);
+    tm.bar = TEAMS > 15 ? tm.id : tm.id + 1;
     // k-mer change-probability classes staged in shared memory for the whole CTA, then a 64-entry
     // table turning three packed cigar ops into their base-3 code
-    const uint32_t nq = P.T.has_err_table ? (1u << (2 * P.T.k)) : 0u;
+    const uint32_t nq = (P.T.has_err_table && PHASE != 2) ? (1u << (2 * P.T.k)) : 0u;  // arrivals only
     uint8_t* qcls_s = smem;
     for (uint32_t i = threadIdx.x; i < nq; i += blockDim.x) qcls_s[i] = P.T.qcls[i];
     const uint32_t qcls_bytes = (nq + 15) & ~15u;
