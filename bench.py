@@ -214,7 +214,9 @@ def main():
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": None, "peak_source": peak_src,
-                         "kernel": "simulate_kernel<1,false> + reclen/scan/format (whole kernel sequence of a step)",
+                         "kernel": "work order + simulate_kernel<W,phase> (error injection | expansion + qscores, per length class) + "
+                                   "reclen/scan/format: whole kernel sequence of a step",
+                         "traffic_note": "dram bytes of the four large simulate launches: profiles/r1g_simulate_summary.txt",
                          "simulate_share": sim_ms / dev_ms if dev_ms else None,
                          "algorithmic_bytes_per_step": st["algorithmic_bytes"]},
         }
