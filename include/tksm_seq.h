@@ -9,6 +9,7 @@
  *   tksm_seq_load_references    get_reference_seqs()                      py/sequence.py:189-194
  *   tksm_seq_load_models        ErrorModel(...), QScoreModel(...),
  *                               KDE_noise_generator.load(...)             py/sequence.py:337-345
+ *   tksm_seq_tail_draw          tail_model.noise_seq(len(fragment))       py/tksm_badread.py:335, 910-927
  *   tksm_seq_run_files          the __main__ loop                         py/sequence.py:347-376
  *   tksm_seq_simulate_text      mdf_generator + mdf_to_seq + formatter    py/sequence.py:197-320
  *
@@ -105,8 +106,14 @@ int tksm_seq_fetch_reference(tksm_seq* h, const char* contig, uint64_t start, ui
 int tksm_seq_commit_reference(tksm_seq* h);   /* upload; implicit on first run */
 
 /* names are looked up in $TKSM_MODELS (py/sequence.py:17-31) unless they are paths;
- * NULL selects the reference defaults (nanopore2020 if found else random; no_noise) */
+ * NULL selects the reference defaults (nanopore2020 if found else random; no_noise).
+ * tail_model: "no_noise", a *.tail.gz name found in $TKSM_MODELS, or the path of a JSON file (plain or .gz)
+ * as KDE_noise_generator.save writes it (py/tksm_badread.py:929-959) */
 int tksm_seq_load_models(tksm_seq* h, const char* error_model, const char* qscore_model, const char* tail_model);
+/* the tail-noise draw of one read (tail_model.noise_seq(len(fragment)), py/tksm_badread.py:335,910-927): the
+ * bases appended to a molecule of frag_len bases for the read with this global ordinal; *len = 0 without a
+ * tail; out is filled when *len <= cap.  Host only (tests, diagnostics). */
+int tksm_seq_tail_draw(tksm_seq* h, uint64_t ordinal, uint32_t frag_len, char* out, size_t cap, uint32_t* len);
 int tksm_seq_get_tables(tksm_seq* h, tksm_seq_tables* out);
 
 /* MDF file (or FIFO) -> output files; NULL path => that output is not produced */

@@ -217,6 +217,76 @@ def make_identity():
     print("identity:", rows[0])
 
 
+# ---------------------------------------------------------------- tail noise
+
+def tail_model_dict():
+    """A small synthetic tail model in the layout KDE_noise_generator.save writes (no model is shipped)."""
+    rng = np.random.default_rng(11)
+    lx = [0, 3, 6, 12, 25, 50, 100, 200]
+    ly = [200, 500, 1000, 2000]
+    grid = (rng.random((len(ly), len(lx))) + 0.05) * np.array([[3, 2, 2, 1.5, 1, 1, 0.5, 0.25]])
+    trans = rng.random((4, 4)) + 0.1
+    trans[0, 0] += 2.0   # homopolymer-rich, like poly(A) read-through
+    return {"lx": lx, "ly": ly, "grid": grid.tolist(), "bases": list("AGTC"), "ratio": 0.35,
+            "trans": trans.tolist(), "begin": [0.25, 0.25, 0.25, 0.25]}
+
+
+def make_tail():
+    import random
+    bad = import_reference_badread()
+    dc = tail_model_dict()
+    path = os.path.join(GOLD, "tail_model.json")
+    gen = bad.TAIL_NOISE_MODEL_PY.KDE_noise_generator(dc["lx"], dc["ly"], dc["grid"], (dc["begin"], dc["trans"]),
+                                                      dc["ratio"], dc["bases"])
+    with open(path, "w") as f:
+        gen.save(f)                                   # the reference's own writer
+    gen = bad.TAIL_NOISE_MODEL_PY.KDE_noise_generator.load(path)   # and its own reader
+    random.seed(20240611)
+    out = {"n": 40000, "frag_lens": {}}
+    for frag_len in (150, 340, 360, 500, 1400, 2000, 2001, 9000):
+        lens, pairs, first = {}, np.zeros((4, 4), np.int64), np.zeros(4, np.int64)
+        for _ in range(out["n"]):
+            t = gen.noise_seq(frag_len)
+            lens[len(t)] = lens.get(len(t), 0) + 1
+            if t:
+                idx = ["AGTC".index(c) for c in t]
+                first[idx[0]] += 1
+                for a, b in zip(idx, idx[1:]):
+                    pairs[a, b] += 1
+        out["frag_lens"][str(frag_len)] = {"lens": {str(k): v for k, v in sorted(lens.items())},
+                                           "pairs": pairs.tolist(), "first": first.tolist()}
+        print(f"tail/{frag_len}: empty {lens.get(0, 0) / out['n']:.3f}, lengths {sorted(lens)[:10]}")
+    # end to end through the unmodified sequence.py: the tail is part of the read, not of error_free_length,
+    # and the perfect file does not hold it (py/sequence.py:249-270)
+    with tempfile.TemporaryDirectory() as td:
+        rng = np.random.default_rng(3)
+        genome = "".join("ACGT"[i] for i in rng.integers(0, 4, 60000))
+        open(os.path.join(td, "g.fa"), "w").write(">c1\n" + genome + "\n")
+        with open(os.path.join(td, "in.mdf"), "w") as f:
+            for i in range(600):
+                st = int(rng.integers(0, 59000))
+                f.write(f"+m{i}\t1\t\n")
+                f.write(f"c1\t{st}\t{st + 500}\t+\t\n")
+        p = run_reference(["-i", "in.mdf", "-r", "g.fa", "-o", "out.fasta", "--badread-error-model", "random",
+                           "--badread-qscore-model", "random", "--badread-identity", "99.5,99.9,0.1",
+                           "--badread-tail-model", path], td)
+        assert p.returncode == 0, p.stderr
+        extra = []
+        for line in open(os.path.join(td, "out.fasta")):
+            if line.startswith(">"):
+                kv = dict(t.split("=") for t in line.split()[1:])
+                assert kv["error_free_length"] == "500"
+                extra.append(int(kv["length"]) - 500)
+        p = run_reference(["-i", "in.mdf", "-r", "g.fa", "--perfect", "perf.fasta", "--badread-tail-model", path], td)
+        assert p.returncode == 0, p.stderr
+        plen = {len(l.strip()) for i, l in enumerate(open(os.path.join(td, "perf.fasta"))) if i % 2 == 1}
+        assert plen == {500}, plen
+        out["e2e"] = {"frag_len": 500, "identity": "99.5,99.9,0.1", "extra": extra}
+        print(f"tail/e2e: mean extra length {np.mean(extra):.2f}, with tail {np.mean(np.array(extra) > 1):.3f}")
+    with gzip.open(os.path.join(GOLD, "ref_tail.json.gz"), "wt") as f:
+        json.dump(out, f, separators=(",", ":"))
+
+
 # ---------------------------------------------------------------- distributions
 
 def dist_inputs(seed=5, n_mol=1500, lo=250, hi=4000):
@@ -301,6 +371,8 @@ if __name__ == "__main__":
         make_qscore()
     if "identity" in what:
         make_identity()
+    if "tail" in what:
+        make_tail()
     if "dist" in what:
         sel = [w[5:] for w in what if w.startswith("dist:")]
         make_dist(sel or None)

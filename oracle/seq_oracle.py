@@ -126,6 +126,8 @@ def twin_lib():
         _twin.twin_simulate.restype = C.c_size_t
         _twin.twin_simulate.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                         C.c_uint64, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
+        _twin.twin_set_tail_lens.restype = None
+        _twin.twin_set_tail_lens.argtypes = [C.c_void_p]
         _twin.twin_expneg.restype = C.c_float
         _twin.twin_expneg.argtypes = [C.c_float]
     return _twin
@@ -139,11 +141,21 @@ def philox4x32_10(counter, key):
     return list(o)
 
 
-def twin_simulate(tables, seqs, ids, ordinal_base=0, badread=True, fastq=True, want_lengths=False):
+def twin_simulate(tables, seqs, ids, ordinal_base=0, badread=True, fastq=True, want_lengths=False, tails=None):
     """tables: ctypes struct with the layout of tksm_seq_tables (include/tksm_seq.h);
-    seqs: list of bytes (error-free molecules); ids: list of str/bytes."""
+    seqs: list of bytes (error-free molecules); ids: list of str/bytes;
+    tails: optional list of bytes, the tail-noise bases of each read (oracle/tail_oracle.py)."""
     lib = twin_lib()
     n = len(seqs)
+    if tails is not None:
+        assert len(tails) == n
+        tl = np.array([len(t) for t in tails] + [0], np.uint32)
+        lib.twin_set_tail_lens(tl.ctypes.data)
+        try:
+            return twin_simulate(tables, [s + t for s, t in zip(seqs, tails)], ids, ordinal_base, badread, fastq,
+                                 want_lengths)
+        finally:
+            lib.twin_set_tail_lens(None)
     seq_off = np.zeros(n + 1, np.uint64)
     seq_off[1:] = np.cumsum([len(s) for s in seqs], dtype=np.uint64)
     idb = [i.encode() if isinstance(i, str) else i for i in ids]

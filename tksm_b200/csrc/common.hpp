@@ -17,6 +17,7 @@ enum : uint32_t {
     TAG_ARRIVE = 1,  // | epoch << 8 ; c0 = start position >> 3 ; 16-bit lane (position & 7) of the 128 bits
     TAG_TRIAL = 2,   // | epoch << 8 | trial << 20 ; c0 = start position
     TAG_QUAL = 3,    // c0 = untrimmed read base index >> 3 ; 16-bit lane (index & 7) of the 128 bits
+    TAG_TAIL = 4,    // host only (tail.cpp): c0 = tail base index >> 2 ; word (index & 3). TAG_READ c0 = 3: tail yes/no, length, start state
 };
 
 constexpr int MAX_K = 7;             // error-model k-mer size supported (4^7 rows)

@@ -23,6 +23,7 @@
 #include "common.hpp"
 #include "engine.hpp"
 #include "host.hpp"
+#include "tail.hpp"
 #include "kernels.cuh"
 #include "model.hpp"
 
@@ -207,6 +208,11 @@ struct Prepared {
     size_t blob_bytes = 0;
     size_t o_read_mol = 0, o_msb = 0, o_mrl = 0, o_mib = 0, o_src = 0, o_len = 0, o_smb = 0, o_mp = 0, o_mc = 0, o_lit = 0,
            o_id = 0, o_so = 0, o_ro = 0;
+    size_t o_tail = SIZE_MAX;  // per-molecule tail lengths (tail-noise model loaded), else absent
+    // tail-noise model loaded: the tails depend on the global read ordinal, which is known when the batch is
+    // issued; the molecule batches are kept until then and the blob is built by finish_deferred()
+    std::vector<const HostBatch*> deferred_parts;
+    std::vector<std::shared_ptr<std::vector<std::unique_ptr<HostBatch>>>> deferred_keep;
 };
 
 // A device slot: the buffers of one chunk in flight.  The same object backs the device-resident
@@ -261,6 +267,7 @@ struct tksm_seq {
     bool genome_synthetic = false;
     ErrorModelHost em;
     QScoreModelHost qm;
+    TailModel tail;           // loaded == false: no_noise
     IdentityHost idh;
     std::vector<float> delta;
     float calib_overshoot = 0, calib_kappa = 0;
@@ -480,6 +487,9 @@ void prepare_host(const tksm_seq* h, const std::vector<const HostBatch*>& parts,
     p.o_id = add(ID);
     p.o_so = add((R + 1) * 8);
     p.o_ro = add((R + 1) * 8);
+    bool tails = false;
+    for (const HostBatch* hb : parts) tails = tails || !hb->mol_tail_len.empty();
+    p.o_tail = tails ? add(M * 4) : SIZE_MAX;
     p.stage = StageLease(h->stage_pool.get(), h->stage_pool->acquire(total, h->cfg.device));
     if (p.stage.idx >= 0) {
         p.blob = h->stage_pool->ptr(p.stage.idx);
@@ -535,6 +545,10 @@ void prepare_host(const tksm_seq* h, const std::vector<const HostBatch*>& parts,
             mib[m0 + m + 1] = (uint32_t)(id0 + hb.mol_id_begin[m + 1]);
         }
         if (m_n) memcpy(mrl + m0, hb.mol_raw_len.data(), m_n * 4);
+        if (tails) {
+            uint32_t* tl = (uint32_t*)(B + p.o_tail) + m0;
+            for (size_t m = 0; m < m_n; m++) tl[m] = m < hb.mol_tail_len.size() ? hb.mol_tail_len[m] : 0u;
+        }
         if (lit0 == 0) {
             if (s_n) memcpy(src + s0, hb.seg_src.data(), s_n * 8);
         } else {
@@ -779,6 +793,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         F.seed_hi = h->dt.seed_hi;
         F.read_mol = D.read_mol;
         F.mol_raw_len = D.mol_raw_len;
+        F.mol_tail_len = p.o_tail == SIZE_MAX ? nullptr : (const uint32_t*)((const char*)b->blob.p + p.o_tail);
         F.mol_id_begin = D.mol_id_begin;
         F.id_pool = D.id_pool;
         if (o == 0) {
@@ -1031,6 +1046,17 @@ HostBatchList parse_chunk(const tksm_seq* h, const tk::TextChunk& tc) {
     return out;
 }
 
+// Tail-noise model loaded: append the tails (keyed by the read ordinals, known now) and build the blob.
+void finish_deferred(const tksm_seq* h, Prepared& p, uint64_t ordinal) {
+    ScopedNs timer(g_ns_prepare);
+    const std::vector<const HostBatch*> parts = std::move(p.deferred_parts);
+    const auto keep = std::move(p.deferred_keep);
+    p.deferred_parts.clear();
+    p.deferred_keep.clear();
+    const HostBatch with_tails = apply_tails(h->tail, h->cfg.seed, ordinal, parts);
+    prepare_host(h, {&with_tails}, p);
+}
+
 // stage 2 (host threads): the batches of consecutive text chunks, concatenated up to the device
 // batch limits, with scratch layout, work lists and upload blob
 PreparedList assemble_group(const tksm_seq* h, std::vector<std::shared_future<std::shared_ptr<HostBatchList>>>& parts) {
@@ -1042,7 +1068,12 @@ PreparedList assemble_group(const tksm_seq* h, std::vector<std::shared_future<st
         if (!cur.empty()) {
             ScopedNs timer(g_ns_prepare);
             std::unique_ptr<Prepared> p(new Prepared());
-            prepare_host(h, cur, *p);
+            if (h->tail.loaded) {
+                p->deferred_parts = cur;
+                p->deferred_keep = lists;
+            } else {
+                prepare_host(h, cur, *p);
+            }
             out.push_back(std::move(p));
         }
         cur.clear();
@@ -1209,6 +1240,7 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
                 b->lane = two_lanes ? (int)(issued & 1) : 0;
                 w_reuse += now_ms() - t0;
                 b->prep = std::move(*pp);
+                if (!b->prep.deferred_parts.empty()) finish_deferred(h, b->prep, ordinal);
                 b->prep.ordinal_base = ordinal;
                 ordinal += b->prep.n_reads;
                 const uint64_t R = b->prep.n_reads;
@@ -1472,9 +1504,15 @@ int tksm_seq_load_models(tksm_seq* h, const char* error_model, const char* qscor
     ModelNames names = scan_model_dirs(env.empty() ? nullptr : env.c_str());
     std::string em = error_model ? error_model : (names.error.count("nanopore2020") ? "nanopore2020" : "random");
     std::string qm = qscore_model ? qscore_model : (names.qscore.count("nanopore2020") ? "nanopore2020" : "random");
+    // KDE_noise_generator.load (py/tksm_badread.py:937-959): "no_noise", a name found in $TKSM_MODELS, or a path
     std::string tail = tail_model ? tail_model : "no_noise";
-    if (tail != "no_noise")
-        throw std::runtime_error("tail-noise models are not implemented in this build (none is shipped with tksm); use no_noise");
+    h->tail = TailModel();
+    if (tail != "no_noise") {
+        auto it = names.tail.find(tail);
+        const std::string path = it != names.tail.end() ? it->second : tail;
+        fprintf(stderr, "Loading tail model %s\n", path.c_str());
+        h->tail.load_json(read_text_maybe_gz(path));
+    }
     fprintf(stderr, "\nLoading error model %s\n", em.c_str());
     h->em = load_error_model(em, names.error);
     fprintf(stderr, "Loading qscore model %s\n", qm.c_str());
@@ -1550,7 +1588,12 @@ tksm_seq_batch* tksm_seq_batch_create(tksm_seq* h, const char* mdf, size_t mdf_l
         MdfParser parser(&h->genome);
         HostBatch hb;
         parser.feed(mdf, mdf_len, true, hb);
-        prepare_host(h, {&hb}, b->prep);
+        if (h->tail.loaded) {
+            const HostBatch with_tails = apply_tails(h->tail, h->cfg.seed, ordinal_base, {&hb});
+            prepare_host(h, {&with_tails}, b->prep);
+        } else {
+            prepare_host(h, {&hb}, b->prep);
+        }
         b->prep.ordinal_base = ordinal_base;
         if (!h->cfg.host_only) {
             slot_bind(h, b.get());
@@ -1607,6 +1650,22 @@ int tksm_seq_shard_plan(tksm_seq* h, const char* mdf, size_t mdf_len, int world,
     plan_shards(mdf, mdf_len, world, bb, ob);
     memcpy(byte_begin, bb.data(), bb.size() * 8);
     memcpy(ordinal_base, ob.data(), ob.size() * 8);
+    API_END(h)
+}
+
+int tksm_seq_tail_draw(tksm_seq* h, uint64_t ordinal, uint32_t frag_len, char* out, size_t cap, uint32_t* len) {
+    API_BEGIN
+    *len = 0;
+    if (h->tail.loaded) {
+        uint32_t start = 0;
+        const uint32_t n = h->tail.draw_length(h->cfg.seed, ordinal, frag_len, &start);
+        *len = n;
+        if (n && n <= cap) {
+            std::vector<uint8_t> codes(n);
+            h->tail.draw_bases(h->cfg.seed, ordinal, start, n, codes.data());
+            for (uint32_t i = 0; i < n; i++) out[i] = codes[i] < 4 ? "ACGT"[codes[i]] : (char)codes[i];
+        }
+    }
     API_END(h)
 }
 

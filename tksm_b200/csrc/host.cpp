@@ -147,6 +147,7 @@ void HostBatch::clear() {
     mol_seg_begin.assign(1, 0);
     mol_raw_len.clear();
     mol_id_begin.assign(1, 0);
+    mol_tail_len.clear();
     seg_src.clear();
     seg_len.clear();
     seg_mod_begin.assign(1, 0);
@@ -172,6 +173,11 @@ void HostBatch::append(const HostBatch& o) {
     grow(seg_mod_begin, o.seg_mod_begin.size());
     for (uint32_t m : o.read_mol) read_mol.push_back(m + mol0);
     for (size_t i = 1; i < o.mol_seg_begin.size(); i++) mol_seg_begin.push_back(o.mol_seg_begin[i] + seg0);
+    if (!o.mol_tail_len.empty() || !mol_tail_len.empty()) {
+        mol_tail_len.resize(mol0, 0);
+        mol_tail_len.insert(mol_tail_len.end(), o.mol_tail_len.begin(), o.mol_tail_len.end());
+        mol_tail_len.resize(mol0 + o.n_mols(), 0);
+    }
     mol_raw_len.insert(mol_raw_len.end(), o.mol_raw_len.begin(), o.mol_raw_len.end());
     for (size_t i = 1; i < o.mol_id_begin.size(); i++) mol_id_begin.push_back(o.mol_id_begin[i] + id0);
     for (uint64_t s : o.seg_src) seg_src.push_back((s & SEG_LITERAL) ? s + lit0 : s);

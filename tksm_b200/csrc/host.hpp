@@ -49,6 +49,7 @@ struct HostBatch {
     std::vector<uint32_t> read_mol;
     std::vector<uint32_t> mol_seg_begin{0};
     std::vector<uint32_t> mol_raw_len;
+    std::vector<uint32_t> mol_tail_len;   // empty unless a tail-noise model appended tails (tail.cpp): bases of mol_raw_len that are tail
     std::vector<uint32_t> mol_id_begin{0};
     std::vector<uint64_t> seg_src;
     std::vector<uint32_t> seg_len;

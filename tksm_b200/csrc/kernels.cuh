@@ -1193,9 +1193,10 @@ struct FmtParams {
     uint32_t seed_lo, seed_hi;
     const uint32_t* read_mol;
     const uint32_t* mol_raw_len;
+    const uint32_t* mol_tail_len; // nullptr unless a tail-noise model is loaded: bases of the raw length that are tail
     const uint32_t* mol_id_begin;
     const uint8_t* id_pool;
-    const uint32_t* read_len;     // nullptr => perfect output (length = raw length)
+    const uint32_t* read_len;     // nullptr => perfect output (length = error-free length)
     const uint32_t* ident_num;
     const uint32_t* ident_den;
     const uint8_t* seq;           // scratch arena
@@ -1246,7 +1247,8 @@ __device__ __forceinline__ uint32_t pct_len(uint32_t h) { return h >= 10000 ? 6u
 
 __device__ __forceinline__ uint32_t record_len(const FmtParams& F, uint32_t r) {
     const uint32_t mol = F.read_mol[r];
-    const uint32_t L = F.mol_raw_len[mol];
+    // error_free_length = len(raw_seq), the molecule without its tail (py/sequence.py:253)
+    const uint32_t L = F.mol_raw_len[mol] - (F.mol_tail_len ? F.mol_tail_len[mol] : 0u);
     const uint32_t Lp = F.read_len ? F.read_len[r] : L;
     const uint32_t h = F.read_len ? pct_hundredths(F.ident_num[r], F.ident_den[r], F.kappa) : 10000u;
     const uint32_t idl = F.mol_id_begin[mol + 1] - F.mol_id_begin[mol];
@@ -1382,7 +1384,7 @@ __global__ void __launch_bounds__(256) format_kernel(const FmtParams F) {
     uint8_t* hdr = hdr_s[warp];
     for (uint32_t r = blockIdx.x * 8 + warp; r < F.n_reads; r += gridDim.x * 8) {
         const uint32_t mol = F.read_mol[r];
-        const uint32_t L = F.mol_raw_len[mol];
+        const uint32_t L = F.mol_raw_len[mol] - (F.mol_tail_len ? F.mol_tail_len[mol] : 0u);
         const uint32_t Lp = F.read_len ? F.read_len[r] : L;
         const uint32_t id0 = F.mol_id_begin[mol], idl = F.mol_id_begin[mol + 1] - id0;
         uint32_t hl = 0;

@@ -85,6 +85,16 @@ class Sequencer:
         enc = lambda s: None if s is None else s.encode()
         self._ck(self._L.tksm_seq_load_models(self._h, enc(error_model), enc(qscore_model), enc(tail_model)))
 
+    def tail_draw(self, ordinal, frag_len):
+        """tail_model.noise_seq(frag_len) for the read with this global ordinal (py/tksm_badread.py:910-927)."""
+        n = C.c_uint32()
+        buf = C.create_string_buffer(4096)
+        self._ck(self._L.tksm_seq_tail_draw(self._h, ordinal, frag_len, buf, 4096, C.byref(n)))
+        if n.value > 4096:
+            buf = C.create_string_buffer(n.value)
+            self._ck(self._L.tksm_seq_tail_draw(self._h, ordinal, frag_len, buf, n.value, C.byref(n)))
+        return buf.raw[:n.value]
+
     def tables(self):
         t = Tables()
         self._ck(self._L.tksm_seq_get_tables(self._h, C.byref(t)))
