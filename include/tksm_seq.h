@@ -146,6 +146,13 @@ int tksm_seq_synth_mdf(tksm_seq* h, int shape, uint64_t n_molecules, uint64_t se
 int tksm_seq_shard_plan(tksm_seq* h, const char* mdf, size_t mdf_len, int world, uint64_t* byte_begin,
                         uint64_t* ordinal_base);
 
+/* One process, several GPUs (`tksm sequence --gpus N`; no reference counterpart): handles[i] is
+ * a handle on device i with the same references, models, seed and identity settings loaded.  The MDF (file or
+ * FIFO, read to its end) is cut by the shard plan above, shard i runs on handles[i] in its own thread, and the
+ * records are written in shard order, so the files hold the bytes of a one-GPU run. */
+int tksm_seq_run_files_multi(tksm_seq* const* handles, int n_handles, const char* mdf_path, const char* badread_path,
+                             const char* perfect_path, tksm_seq_stats* stats);
+
 /* the module entry point: argv[0] == "sequence" */
 int tksm_sequence_main(int argc, char** argv);
 

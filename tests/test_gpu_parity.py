@@ -308,3 +308,51 @@ def test_fused_and_split_kernels_agree(world, monkeypatch):
         monkeypatch.setenv("TKSM_SIM_SPLIT", mode)
         out[mode] = (s.simulate(mdf, BADREAD, True), s.simulate(mdf, PERFECT, False), s.simulate(mdf, BADREAD, False))
     assert out["0"] == out["1"]
+
+
+@pytest.mark.gpu
+def test_cli_gpus_flag_shards_in_one_process(world, tmp_path):
+    """`tksm sequence --gpus N`: one process, one handle and one thread per shard of the plan,
+    files written in shard order hold the bytes of the one-GPU run.  On a one-GPU box $TKSM_GPU_LIST places every
+    shard on device 0; with more devices visible the default placement (device i for shard i) runs as well."""
+    import subprocess
+    import torch
+    from tksm_b200.sequence import BADREAD, PERFECT
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tksm_b200", "tksm")
+    s = world["Sequencer"](seed=11)
+    s.add_reference_text(world["fasta"])
+    s.load_models("random", "random")
+    mdf = s.synth_mdf(1, 900, seed=6) + handmade_mdf().encode()
+    want, want_perf = s.simulate(mdf, BADREAD, True), s.simulate(mdf, PERFECT, False)
+    fa, src = tmp_path / "g.fa", tmp_path / "in.mdf"
+    fa.write_text(world["fasta"])
+    src.write_bytes(mdf)
+    common = ["-r", str(fa), "--badread-error-model", "random", "--badread-qscore-model", "random", "-s", "11", "-t", "4"]
+    runs = [(3, {"TKSM_GPU_LIST": "0,0,0"}), (2, {"TKSM_GPU_LIST": "0"})]
+    if torch.cuda.device_count() >= 2:
+        runs.append((2, {}))
+    for n, env in runs:
+        out, perf = tmp_path / f"o{n}.fastq", tmp_path / f"p{n}.fasta"
+        p = subprocess.run([exe, "sequence", "-i", str(src), "-o", str(out), "--perfect", str(perf), "--gpus", str(n)] + common,
+                           capture_output=True, text=True, timeout=180, env={**os.environ, **env})
+        assert p.returncode == 0, p.stderr
+        assert out.read_bytes() == want and perf.read_bytes() == want_perf, (n, env)
+    # more shards than records, and an empty input
+    tiny = tmp_path / "tiny.mdf"
+    tiny.write_bytes(b"+a\t1\t\nchr1\t10\t300\t+\t\n")
+    out = tmp_path / "tiny.fastq"
+    p = subprocess.run([exe, "sequence", "-i", str(tiny), "-o", str(out), "--gpus", "4"] + common, capture_output=True,
+                       text=True, timeout=180, env={**os.environ, "TKSM_GPU_LIST": "0"})
+    assert p.returncode == 0, p.stderr
+    assert out.read_bytes() == s.simulate(tiny.read_bytes(), BADREAD, True)
+    empty = tmp_path / "empty.mdf"
+    empty.write_bytes(b"")
+    p = subprocess.run([exe, "sequence", "-i", str(empty), "-o", str(out), "--gpus", "2"] + common, capture_output=True,
+                       text=True, timeout=180, env={**os.environ, "TKSM_GPU_LIST": "0"})
+    assert p.returncode == 0 and out.read_bytes() == b""
+    # a broken record in the second shard fails the run like the one-GPU run does
+    bad = tmp_path / "bad.mdf"
+    bad.write_bytes(mdf + b"chr1\t0\n")
+    p = subprocess.run([exe, "sequence", "-i", str(bad), "-o", str(out), "--gpus", "2"] + common, capture_output=True,
+                       text=True, timeout=180, env={**os.environ, "TKSM_GPU_LIST": "0"})
+    assert p.returncode == 1 and "Error" in p.stderr

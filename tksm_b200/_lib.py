@@ -82,7 +82,7 @@ EXPORTS = [
     "tksm_seq_load_references", "tksm_seq_add_reference_text", "tksm_seq_synth_reference",
     "tksm_seq_fetch_reference", "tksm_seq_commit_reference", "tksm_seq_load_models", "tksm_seq_get_tables",
     "tksm_seq_run_files", "tksm_seq_simulate_text", "tksm_seq_batch_create", "tksm_seq_batch_run",
-    "tksm_seq_batch_fetch", "tksm_seq_batch_destroy", "tksm_seq_synth_mdf", "tksm_seq_shard_plan", "tksm_seq_tail_draw",
+    "tksm_seq_batch_fetch", "tksm_seq_batch_destroy", "tksm_seq_synth_mdf", "tksm_seq_shard_plan", "tksm_seq_tail_draw", "tksm_seq_run_files_multi",
     "tksm_sequence_main",
 ]
 
@@ -131,6 +131,7 @@ def lib():
     L.tksm_seq_batch_destroy.argtypes = [vp, vp]
     L.tksm_seq_batch_destroy.restype = None
     L.tksm_seq_shard_plan.argtypes = [vp, cp, sz, C.c_int, C.POINTER(u64), C.POINTER(u64)]
+    L.tksm_seq_run_files_multi.argtypes = [C.POINTER(vp), C.c_int, cp, cp, cp, C.POINTER(Stats)]
     L.tksm_seq_tail_draw.argtypes = [vp, u64, C.c_uint32, vp, sz, C.POINTER(C.c_uint32)]
     L.tksm_seq_synth_mdf.argtypes = [vp, C.c_int, u64, u64, C.c_uint32, C.c_uint32, C.POINTER(vp), C.POINTER(sz)]
     L.tksm_sequence_main.argtypes = [C.c_int, C.POINTER(cp)]

@@ -6,6 +6,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/tksm_seq.h"
@@ -47,7 +48,7 @@ void usage(FILE* f) {
             "                [--skip-qual-compute] [-O {fastq,fasta}] [-t THREADS]\n"
             "                [--badread-identity BADREAD_IDENTITY] [--badread-error-model BADREAD_ERROR_MODEL]\n"
             "                [--badread-qscore-model BADREAD_QSCORE_MODEL] [--badread-tail-model BADREAD_TAIL_MODEL]\n"
-            "                [--list] [-s SEED] [--device DEVICE]\n");
+            "                [--list] [-s SEED] [--gpus GPUS] [--device DEVICE]\n");
 }
 
 int usage_error(const std::string& msg) {
@@ -65,6 +66,7 @@ extern "C" int tksm_sequence_main(int argc, char** argv) {
     long threads = 1;
     long long seed = 42;
     int device = 0;
+    long gpus = getenv("TKSM_GPUS") ? atol(getenv("TKSM_GPUS")) : 1;   // extension: $TKSM_GPUS / --gpus
     for (int a = 1; a < argc; a++) {
         std::string arg = argv[a];
         const Opt* opt = nullptr;
@@ -166,7 +168,9 @@ extern "C" int tksm_sequence_main(int argc, char** argv) {
             seed = strtoll(vals[0].c_str(), &e, 10);
             if (*e) return usage_error("argument -s/--seed: invalid int value: '" + vals[0] + "'");
         } else if (d == "gpus") {
-            // accepted for forward compatibility; one process drives one device
+            char* e = nullptr;
+            gpus = strtol(vals[0].c_str(), &e, 10);
+            if (*e) return usage_error("argument --gpus: invalid int value: '" + vals[0] + "'");
         } else if (d == "device") {
             device = atoi(vals[0].c_str());
         }
@@ -218,37 +222,80 @@ extern "C" int tksm_sequence_main(int argc, char** argv) {
     if (badread.empty() && perfect.empty()) return usage_error("Must specify either --output or --perfect.");
     if (refs.empty()) return die("TypeError: 'NoneType' object is not iterable (no -r/--references given)");
 
-    tksm_seq_config cfg;
-    tksm_seq_default_config(&cfg);
-    cfg.device = device;
-    cfg.seed = (uint64_t)seed;
-    cfg.identity_mean = mean;
-    cfg.identity_max = mx;
-    cfg.identity_stdev = sd;
-    cfg.skip_qual_compute = skip_qual;
-    cfg.threads = threads > 0 ? (int)std::min<long>(threads, 256) : 1;  // -t: host parser threads (default 1)
-    tksm_seq* h = tksm_seq_create(&cfg);
-    if (!h) return die(std::string("Error: ") + tksm_seq_last_error(nullptr));
-    int rc = 0;
+    // --gpus N: devices device .. device + N - 1, or the comma list in $TKSM_GPU_LIST (one entry per shard;
+    // an ordinal may repeat, which runs several shards on one device)
+    std::vector<int> devices;
+    if (const char* lst = getenv("TKSM_GPU_LIST")) {
+        for (const char* p = lst; *p;) {
+            char* e = nullptr;
+            long v = strtol(p, &e, 10);
+            if (e == p) return die("Error: could not parse $TKSM_GPU_LIST");
+            devices.push_back((int)v);
+            p = *e == ',' ? e + 1 : e;
+        }
+    }
+    if (gpus < 1 || gpus > 64) return die("Error: --gpus must be between 1 and 64");
+    if (devices.empty())
+        for (long g = 0; g < gpus; g++) devices.push_back(device + (int)g);
+    else if (gpus > 1)
+        devices.resize((size_t)gpus, devices.back());
+    const int n = (int)devices.size();
+    const long host_threads = threads > 0 ? std::min<long>(threads, 256) : 1;  // -t: host parser threads (default 1)
+
     std::vector<const char*> paths;
     for (auto& r : refs) paths.push_back(r.c_str());
-    rc = tksm_seq_load_references(h, paths.data(), (int)paths.size());
-    if (!rc && !badread.empty())
-        rc = tksm_seq_load_models(h, have_err ? err_model.c_str() : nullptr, have_qs ? qs_model.c_str() : nullptr,
-                                  have_tail ? tail_model.c_str() : nullptr);
-    else if (!rc)
-        rc = tksm_seq_load_models(h, "random", "random", nullptr);  // perfect only: models are not consulted
-    tksm_seq_stats st;
-    if (!rc)
-        rc = tksm_seq_run_files(h, input.c_str(), badread.empty() ? nullptr : badread.c_str(),
-                                perfect.empty() ? nullptr : perfect.c_str(), &st);
-    if (rc) {
-        fprintf(stderr, "Error: %s\n", tksm_seq_last_error(h));
+    std::vector<tksm_seq*> handles((size_t)n, nullptr);
+    std::vector<std::string> errors((size_t)n);
+    auto set_up = [&](int i) {
+        tksm_seq_config cfg;
+        tksm_seq_default_config(&cfg);
+        cfg.device = devices[(size_t)i];
+        cfg.seed = (uint64_t)seed;
+        cfg.identity_mean = mean;
+        cfg.identity_max = mx;
+        cfg.identity_stdev = sd;
+        cfg.skip_qual_compute = skip_qual;
+        cfg.threads = (int)std::max<long>(host_threads / n, 1);
+        tksm_seq* h = tksm_seq_create(&cfg);
+        if (!h) {
+            errors[(size_t)i] = tksm_seq_last_error(nullptr);
+            return;
+        }
+        handles[(size_t)i] = h;
+        int rc = tksm_seq_load_references(h, paths.data(), (int)paths.size());
+        if (!rc && !badread.empty())
+            rc = tksm_seq_load_models(h, have_err ? err_model.c_str() : nullptr, have_qs ? qs_model.c_str() : nullptr,
+                                      have_tail ? tail_model.c_str() : nullptr);
+        else if (!rc)
+            rc = tksm_seq_load_models(h, "random", "random", nullptr);  // perfect only: models are not consulted
+        if (rc) errors[(size_t)i] = tksm_seq_last_error(h);
+    };
+    if (n == 1) {
+        set_up(0);
     } else {
-        fprintf(stderr, "Sequencing: %llu reads, %llu bases, %.1f ms on device\n", (unsigned long long)st.reads,
-                (unsigned long long)st.read_bases, st.kernel_ms);
+        std::vector<std::thread> th;
+        for (int i = 0; i < n; i++) th.emplace_back(set_up, i);
+        for (auto& t : th) t.join();
     }
-    tksm_seq_destroy(h);
+    int rc = 0;
+    for (int i = 0; i < n && !rc; i++)
+        if (!errors[(size_t)i].empty()) {
+            fprintf(stderr, "Error: %s\n", errors[(size_t)i].c_str());
+            rc = 1;
+        }
+    tksm_seq_stats st;
+    if (!rc) {
+        rc = tksm_seq_run_files_multi(handles.data(), n, input.c_str(), badread.empty() ? nullptr : badread.c_str(),
+                                      perfect.empty() ? nullptr : perfect.c_str(), &st);
+        if (rc) {
+            fprintf(stderr, "Error: %s\n", tksm_seq_last_error(handles[0]));
+        } else {
+            fprintf(stderr, "Sequencing: %llu reads, %llu bases, %.1f ms on device%s\n", (unsigned long long)st.reads,
+                    (unsigned long long)st.read_bases, st.kernel_ms, n > 1 ? " (slowest of the devices)" : "");
+        }
+    }
+    for (tksm_seq* h : handles)
+        if (h) tksm_seq_destroy(h);
     return rc ? 1 : 0;
 }
 

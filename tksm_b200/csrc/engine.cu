@@ -1677,11 +1677,25 @@ int tksm_seq_run_files(tksm_seq* h, const char* mdf_path, const char* badread_pa
     API_END(h)
 }
 
+int tksm_seq_run_files_multi(tksm_seq* const* handles, int n_handles, const char* mdf_path, const char* badread_path,
+                             const char* perfect_path, tksm_seq_stats* stats) {
+    tksm_seq* h = n_handles > 0 ? handles[0] : nullptr;
+    API_BEGIN
+    if (n_handles < 1) throw std::runtime_error("no handles");
+    if (!badread_path && !perfect_path) throw std::runtime_error("Must specify either --output or --perfect.");
+    if (n_handles == 1) tk::run_files(h, mdf_path, badread_path, perfect_path, stats);
+    else tk::run_files_multi(handles, n_handles, mdf_path, badread_path, perfect_path, stats);
+    API_END(h)
+}
+
 }  // extern "C"
 
 // ---------------------------------------------------------------- engine.hpp glue
 namespace tk {
 
+std::unique_ptr<ChunkSource> make_memory_source(const char* text, size_t len) {
+    return std::unique_ptr<ChunkSource>(new MemorySource(text, len));
+}
 const GenomeStore* engine_genome(const tksm_seq* h) { return &h->genome; }
 const tksm_seq_config* engine_config(const tksm_seq* h) { return &h->cfg; }
 

@@ -29,11 +29,17 @@ struct OutputSink {
 // engine.cu: the streaming pipeline (host parser threads -> upload -> kernels -> download)
 void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_t ordinal_base, OutputSink* sink,
                    char** arena_out, size_t* arena_len, tksm_seq_stats* stats);
+// chunker over MDF text in memory (the caller keeps the text alive)
+std::unique_ptr<ChunkSource> make_memory_source(const char* text, size_t len);
 const GenomeStore* engine_genome(const tksm_seq* h);
 const tksm_seq_config* engine_config(const tksm_seq* h);
 
 // runner.cpp: streaming MDF file -> output files (py/sequence.py:347-376)
 void run_files(tksm_seq* h, const char* mdf_path, const char* badread_path, const char* perfect_path,
                tksm_seq_stats* stats);
+// one process, several devices: contiguous shards of the MDF, one handle and one thread each,
+// outputs written in shard order == MDF order
+void run_files_multi(tksm_seq* const* handles, int n, const char* mdf_path, const char* badread_path,
+                     const char* perfect_path, tksm_seq_stats* stats);
 
 }  // namespace tk

@@ -10,6 +10,7 @@
 #include <memory>
 #include <stdexcept>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "engine.hpp"
@@ -143,6 +144,88 @@ void run_files(tksm_seq* h, const char* mdf_path, const char* badread_path, cons
     sinks.s[1] = perfect_path ? &perf : nullptr;
     tksm_seq_stats total{};
     engine_stream(h, src, which, format, 0, &sinks, nullptr, nullptr, &total);
+    bad.close();
+    perf.close();
+    if (stats) *stats = total;
+}
+
+namespace {
+
+// records of one shard held in memory until the shards before it are on disk
+struct MemorySinks : OutputSink {
+    std::vector<std::string> parts[2];
+    void write(int o, const char* p, size_t n) override { parts[o].emplace_back(p, n); }
+};
+
+}  // namespace
+
+void run_files_multi(tksm_seq* const* handles, int n, const char* mdf_path, const char* badread_path,
+                     const char* perfect_path, tksm_seq_stats* stats) {
+    Sink bad, perf;
+    if (badread_path) bad.open(badread_path);
+    if (perfect_path) perf.open(perfect_path);
+    const int which = (badread_path ? TKSM_SEQ_BADREAD : 0) | (perfect_path ? TKSM_SEQ_PERFECT : 0);
+    const int format = (bad.fastq ? TKSM_SEQ_FASTQ_BADREAD : 0) | (perf.fastq ? TKSM_SEQ_FASTQ_PERFECT : 0);
+
+    // the shard plan needs the whole text (a FIFO is read to its end first)
+    std::string text;
+    {
+        FILE* in = fopen(mdf_path, "rb");
+        if (!in) throw std::runtime_error(std::string("cannot open ") + mdf_path);
+        std::vector<char> buf((size_t)4 << 20);
+        size_t got;
+        while ((got = fread(buf.data(), 1, buf.size(), in)) > 0) text.append(buf.data(), got);
+        fclose(in);
+    }
+    std::vector<uint64_t> bb, ob;
+    plan_shards(text.data(), text.size(), n, bb, ob);
+
+    FileSinks direct;
+    direct.s[0] = badread_path ? &bad : nullptr;
+    direct.s[1] = perfect_path ? &perf : nullptr;
+    std::vector<MemorySinks> held((size_t)n);
+    std::vector<tksm_seq_stats> st((size_t)n);
+    std::vector<std::string> errors((size_t)n);
+    std::vector<std::thread> threads;
+    for (int i = 0; i < n; i++) {
+        threads.emplace_back([&, i]() {
+            try {
+                st[(size_t)i] = tksm_seq_stats{};
+                if (bb[(size_t)i + 1] == bb[(size_t)i]) return;
+                auto src = make_memory_source(text.data() + bb[(size_t)i], (size_t)(bb[(size_t)i + 1] - bb[(size_t)i]));
+                OutputSink* sink = i == 0 ? (OutputSink*)&direct : (OutputSink*)&held[(size_t)i];  // shard 0 streams to the files
+                engine_stream(handles[i], *src, which, format, ob[(size_t)i], sink, nullptr, nullptr, &st[(size_t)i]);
+            } catch (const std::exception& e) {
+                errors[(size_t)i] = e.what()[0] ? e.what() : "error";
+            }
+        });
+    }
+    tksm_seq_stats total{};
+    std::string first_error;
+    for (int i = 0; i < n; i++) {
+        threads[(size_t)i].join();
+        if (!errors[(size_t)i].empty() && first_error.empty()) first_error = errors[(size_t)i];
+        if (!first_error.empty()) continue;  // keep joining; nothing more is written
+        for (int o = 0; o < 2; o++) {
+            for (const std::string& part : held[(size_t)i].parts[o]) direct.write(o, part.data(), part.size());
+            held[(size_t)i].parts[o].clear();
+            held[(size_t)i].parts[o].shrink_to_fit();
+        }
+        const tksm_seq_stats& s = st[(size_t)i];
+        total.reads += s.reads;
+        total.raw_bases += s.raw_bases;
+        total.read_bases += s.read_bases;
+        total.out_bytes[0] += s.out_bytes[0];
+        total.out_bytes[1] += s.out_bytes[1];
+        total.algorithmic_bytes += s.algorithmic_bytes;
+        total.h2d_bytes += s.h2d_bytes;
+        total.d2h_bytes += s.d2h_bytes;
+        total.kernel_ms = std::max(total.kernel_ms, s.kernel_ms);      // the devices run side by side
+        total.simulate_ms = std::max(total.simulate_ms, s.simulate_ms);
+        total.kernel_launches += s.kernel_launches;
+        total.status_or |= s.status_or;
+    }
+    if (!first_error.empty()) throw std::runtime_error(first_error);
     bad.close();
     perf.close();
     if (stats) *stats = total;
