@@ -223,7 +223,7 @@ def main():
         # CPU baseline beside it, rank 0, N = 1 only, bounded sample
         if world == 1:
             line["cpu_baseline"] = cpu_baseline(s, mdf, args)
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=RESULT_OUT, flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -285,9 +285,16 @@ def reference_arm(args, config):
             "cpu_baseline": {"value": v, "unit": "bases/s", "cores": threads, "kind": "port", "what": kind,
                              "sample": f"{len(seqs)} molecules per step ({sum(map(len, seqs))} raw bases)"},
             "e2e": {"value": v, "unit": "bases/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=RESULT_OUT, flush=True)
     return 0
 
 
+# stdout carries the one JSON line and nothing else: whatever libraries print on fd 1 (NCCL's version banner when
+# the box sets NCCL_DEBUG) goes to stderr
+RESULT_OUT = sys.stdout
+
 if __name__ == "__main__":
+    sys.stdout.flush()
+    RESULT_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     sys.exit(main())

@@ -356,3 +356,35 @@ def test_cli_gpus_flag_shards_in_one_process(world, tmp_path):
     p = subprocess.run([exe, "sequence", "-i", str(bad), "-o", str(out), "--gpus", "2"] + common, capture_output=True,
                        text=True, timeout=180, env={**os.environ, "TKSM_GPU_LIST": "0"})
     assert p.returncode == 1 and "Error" in p.stderr
+
+
+@pytest.mark.gpu
+def test_gz_sink_blocks(world, tmp_path, monkeypatch):
+    """`.gz` outputs (get_output_file, py/sequence.py:291-296) are written as independently deflated blocks, one
+    gzip member each, by helper threads: Python's gzip and zcat read them back as the plain bytes, whatever the
+    block size; an empty MDF gives a valid empty .gz."""
+    import gzip
+    import subprocess
+    from tksm_b200.sequence import BADREAD, PERFECT
+    s = world["Sequencer"](seed=3)
+    s.add_reference_text(world["fasta"])
+    s.load_models("random", "random")
+    mdf = s.synth_mdf(1, 300, seed=8)
+    want, want_perf = s.simulate(mdf, BADREAD, True), s.simulate(mdf, PERFECT, False)
+    src = tmp_path / "in.mdf"
+    src.write_bytes(mdf)
+    for block in ("777", "65536", None):
+        if block:
+            monkeypatch.setenv("TKSM_GZ_BLOCK_BYTES", block)
+        else:
+            monkeypatch.delenv("TKSM_GZ_BLOCK_BYTES")
+        o, p = tmp_path / f"o{block}.fastq.gz", tmp_path / f"p{block}.fa.gz"
+        s.run_files(str(src), badread=str(o), perfect=str(p))
+        assert gzip.open(o).read() == want and gzip.open(p).read() == want_perf
+        assert subprocess.run(["zcat", str(o)], capture_output=True, timeout=60).stdout == want
+        if block == "777":
+            assert o.read_bytes().count(b"\x1f\x8b\x08") >= len(want) // 777   # one member per block
+    empty = tmp_path / "empty.mdf"
+    empty.write_bytes(b"")
+    s.run_files(str(empty), badread=str(tmp_path / "e.fq.gz"))
+    assert (tmp_path / "e.fq.gz").stat().st_size > 0 and gzip.open(tmp_path / "e.fq.gz").read() == b""

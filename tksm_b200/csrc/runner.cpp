@@ -7,6 +7,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <deque>
+#include <future>
 #include <memory>
 #include <stdexcept>
 #include <string>
@@ -24,15 +26,98 @@ bool ends_with(const std::string& s, const char* suf) {
     return s.size() >= n && s.compare(s.size() - n, n, suf) == 0;
 }
 
+// One gzip member per block, compressed by helper threads and written in order (a file of concatenated
+// members is a valid gzip file: `zcat`, Python's gzip and htslib read it as one stream).  Replaces the
+// gzip.open(path, "wt") sink of the reference (py/sequence.py:291-296), which deflates on one core.
+struct GzBlocks {
+    FILE* f = nullptr;
+    size_t block = (size_t)4 << 20;
+    size_t max_inflight = 4;
+    std::string pending;
+    std::deque<std::future<std::string>> inflight;
+    bool wrote_any = false;
+
+    static std::string compress(std::string raw) {
+        z_stream zs{};
+        if (deflateInit2(&zs, Z_DEFAULT_COMPRESSION, Z_DEFLATED, 15 + 16, 8, Z_DEFAULT_STRATEGY) != Z_OK)
+            throw std::runtime_error("gzip init failed");
+        std::string out(deflateBound(&zs, (uLong)raw.size()) + 64, 0);
+        zs.next_in = (Bytef*)raw.data();
+        zs.avail_in = (uInt)raw.size();
+        zs.next_out = (Bytef*)out.data();
+        zs.avail_out = (uInt)out.size();
+        const int rc = deflate(&zs, Z_FINISH);
+        const size_t n = out.size() - zs.avail_out;
+        deflateEnd(&zs);
+        if (rc != Z_STREAM_END) throw std::runtime_error("gzip write failed");
+        out.resize(n);
+        return out;
+    }
+    void open(const std::string& path) {
+        f = fopen(path.c_str(), "wb");
+        if (!f) throw std::runtime_error("cannot open " + path + " for writing");
+        if (const char* e = getenv("TKSM_GZ_BLOCK_BYTES")) block = std::max<size_t>((size_t)atoll(e), 1);
+        block = std::min<size_t>(block, (size_t)1 << 30);
+        max_inflight = std::max<size_t>(std::thread::hardware_concurrency(), 2);
+    }
+    void put(const std::string& member) {
+        if (!member.empty() && fwrite(member.data(), 1, member.size(), f) != member.size())
+            throw std::runtime_error("write failed");
+        wrote_any = true;
+    }
+    void submit(std::string raw) {
+        while (inflight.size() >= max_inflight) {
+            put(inflight.front().get());
+            inflight.pop_front();
+        }
+        inflight.push_back(std::async(std::launch::async, compress, std::move(raw)));
+    }
+    void write(const char* p, size_t n) {
+        while (n) {
+            const size_t take = std::min(n, block - pending.size());
+            pending.append(p, take);
+            p += take;
+            n -= take;
+            if (pending.size() >= block) {
+                std::string raw;
+                raw.swap(pending);
+                submit(std::move(raw));
+            }
+        }
+    }
+    void finish() {
+        if (!f) return;
+        if (!pending.empty()) {
+            std::string raw;
+            raw.swap(pending);
+            submit(std::move(raw));
+        }
+        while (!inflight.empty()) {
+            put(inflight.front().get());
+            inflight.pop_front();
+        }
+        if (!wrote_any) put(compress(std::string()));  // an empty input still gives a valid .gz
+        FILE* g = f;
+        f = nullptr;
+        if (fclose(g) != 0) throw std::runtime_error("write failed");
+    }
+    ~GzBlocks() {
+        for (auto& fu : inflight)
+            if (fu.valid()) fu.wait();
+        if (f) fclose(f);
+    }
+};
+
 struct Sink {
     FILE* f = nullptr;
-    gzFile gz = nullptr;
+    GzBlocks gz;
+    bool is_gz = false;
     bool fastq = false;
     void open(const std::string& path_in) {
         std::string path = path_in;
         if (ends_with(path, ".gz")) {
-            gz = gzopen(path_in.c_str(), "wb");
-            if (!gz) throw std::runtime_error("cannot open " + path_in + " for writing");
+            gz.open(path_in);
+            is_gz = true;
             path.resize(path.size() - 3);
         } else {
             f = fopen(path_in.c_str(), "wb");
@@ -41,24 +126,20 @@ struct Sink {
         fastq = ends_with(path, ".fastq") || ends_with(path, ".fq");
     }
     void write(const char* p, size_t n) {
-        if (gz) {
-            while (n) {
-                unsigned chunk = (unsigned)std::min<size_t>(n, 1u << 30);
-                if (gzwrite(gz, p, chunk) != (int)chunk) throw std::runtime_error("gzip write failed");
-                p += chunk;
-                n -= chunk;
-            }
+        if (is_gz) {
+            gz.write(p, n);
         } else if (f) {
             if (n && fwrite(p, 1, n, f) != n) throw std::runtime_error("write failed");
         }
     }
     void close() {
-        if (gz) gzclose(gz);
+        if (is_gz) gz.finish();
         if (f) fclose(f);
-        gz = nullptr;
         f = nullptr;
     }
-    ~Sink() { close(); }
+    ~Sink() {
+        if (f) fclose(f);
+    }
 };
 
 }  // namespace
