@@ -132,7 +132,8 @@ void tksm_seq_batch_destroy(tksm_seq* h, tksm_seq_batch* b);
 
 /* synthetic MDF text in the emitter format of src/interval.h:898-905 (bench / tests);
  * shape: 0 = Tsb only (depth >= 1), 1 = Tsb->Trc->plA->Flp->Tag (README bulk), 2 = single long
- * intervals with log-uniform lengths in [min_len, max_len] */
+ * intervals with log-uniform lengths in [min_len, max_len], 3 = scRNA Tsb->SCB->PCR (barcode, UMI and adapter
+ * literals, ".cycle" ids, base mods on every interval kind) */
 int tksm_seq_synth_mdf(tksm_seq* h, int shape, uint64_t n_molecules, uint64_t seed, uint32_t min_len,
                        uint32_t max_len, char** out, size_t* out_len);
 

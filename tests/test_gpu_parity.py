@@ -130,7 +130,7 @@ def test_perfect_handmade_matches_python_oracle(world):
                 so.perfect_record(uuid, mid, want, fastq)
 
 
-@pytest.mark.parametrize("shape,n", [(0, 400), (1, 1500), (2, 60)])
+@pytest.mark.parametrize("shape,n", [(0, 400), (1, 1500), (2, 60), (3, 600)])
 def test_perfect_synthetic_matches_python_oracle(world, shape, n):
     from tksm_b200.sequence import PERFECT
     s = world["Sequencer"](seed=9)
@@ -147,6 +147,7 @@ CASES = [
     # error model, qscore model, identity, skip_qual, shape, n
     ("random", "random", (84.0, 99.0, 5.5), False, 1, 300),
     ("random", "ideal", (90.0, 98.0, 3.0), False, 1, 200),
+    ("random", "random", (84.0, 99.0, 5.5), False, 3, 300),     # BASELINE configs[2] shape: scRNA Tsb->SCB->PCR
 ]
 if HAVE_MODELS:
     CASES += [
@@ -157,6 +158,8 @@ if HAVE_MODELS:
         ("nanopore2020", "nanopore2020", (95.0, 95.0, 0.0), False, 0, 200),
         ("nanopore2020", "nanopore2020", (60.0, 80.0, 8.0), False, 1, 200),
         ("nanopore2020", "nanopore2020", (84.0, 99.0, 5.5), False, 2, 80),
+        ("nanopore2020", "nanopore2020", (84.0, 99.0, 5.5), False, 3, 500),
+        ("pacbio2016", "pacbio2016", (99.0, 99.9, 0.5), False, 3, 300),   # configs[3]: high identity, qscore-dominated
     ]
 
 

@@ -214,3 +214,29 @@ def test_model_lookup_first_directory_wins(Sequencer, tmp_path):
         assert set(mo.decode_qrow(tn, mo.packed_row_for(tn, "="))) == {5}
     finally:
         os.environ["TKSM_MODELS"] = old
+
+
+@pytest.mark.parametrize("shape", [0, 1, 2, 3])
+def test_synthetic_mdf_shapes_parse_like_the_reference_reader(Sequencer, shape):
+    """tksm_seq_synth_mdf writes the emitter format of src/interval.h:898-905 for the BASELINE shapes (Tsb, README
+    bulk, length skew, scRNA with PCR mods): the oracle's restatement of mdf_generator / mdf_to_seq reads it (mods
+    in range, `.cycle` ids kept) and the shard plan counts the same reads."""
+    rng = np.random.default_rng(1)
+    g = rng.choice(np.frombuffer(b"ACGT", np.uint8), size=400000).tobytes().decode()
+    fasta = ">chr1\n" + g[:300000] + "\n>chr2\n" + g[300000:] + "\n"
+    s = Sequencer(host_only=True)
+    s.add_reference_text(fasta)
+    n = 300
+    mdf = s.synth_mdf(shape, n, seed=4, min_len=300, max_len=50000).decode()
+    mols = so.parse_mdf(mdf)
+    assert len(mols) == n                       # depth expanded
+    refs = so.load_fasta(fasta)
+    seqs = [so.molecule_sequence(refs, iv) for _, iv in mols]
+    assert all(len(q) > 0 for q in seqs)
+    plan = s.shard_plan(mdf, 3)
+    assert sum(p[3] for p in plan) == n
+    if shape == 3:
+        assert any("." in m for m, _ in mols)
+        with_mods = [l for l in mdf.split("\n") if l and l[0] != "+" and l.split("\t")[4]]
+        assert len(with_mods) > 50
+        assert any(l[0] in "ACGT" and l.split("\t")[0] not in ("chr1", "chr2") for l in with_mods)   # a literal with a mod

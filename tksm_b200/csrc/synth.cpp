@@ -1,8 +1,9 @@
 // Synthetic MDF generator for benchmarks and tests.  Emits the exact text the
 // upstream modules write (src/interval.h:898-905: header "+id\tdepth\tcomment", interval lines
 // "chr\tstart\tend\tstrand\tmods" with the trailing tab), shaped like the output of
-// Tsb (shape 0), Tsb->Trc->plA->Flp->Tag (shape 1, README bulk pipeline) or a length-skew
-// sweep of single-interval molecules (shape 2).
+// Tsb (shape 0), Tsb->Trc->plA->Flp->Tag (shape 1, README bulk pipeline), a length-skew
+// sweep of single-interval molecules (shape 2) or the scRNA pipeline Tsb->SCB->PCR (shape 3:
+// cell barcode + UMI + adapter literals, PCR copies with ".cycle" ids and base mods, src/pcr.cpp:40-64).
 #include <algorithm>
 #include <charconv>
 #include <cmath>
@@ -38,6 +39,7 @@ struct Seg {
     std::string lit;
     uint64_t start, end;
     bool plus;
+    std::string mods = {};   // "pos<char>,..." relative to the interval (src/interval.h:754)
 };
 
 void put_u64(std::string& o, uint64_t v) {
@@ -68,6 +70,7 @@ extern "C" int tksm_seq_synth_mdf(tksm_seq* h, int shape, uint64_t n_molecules, 
         const std::string tag3 = "GCAATACGTAACTGAACGAAGT";        // 22 nt
         uint64_t emitted = 0, rec = 0;
         std::vector<Seg> segs;
+        std::string pcr_suffix;
         while (emitted < n_molecules) {
             segs.clear();
             int ci = (int)(std::lower_bound(cum.begin(), cum.end(), rng.uni() * tot) - cum.begin());
@@ -102,7 +105,39 @@ extern "C" int tksm_seq_synth_mdf(tksm_seq* h, int shape, uint64_t n_molecules, 
                 const bool plus = rng.uni() < 0.5;
                 if (!plus) std::reverse(exons.begin(), exons.end());  // transcription order
                 for (auto& ex : exons) segs.push_back(Seg{ci, "", ex.first, ex.second, plus});
-                if (shape == 0) {
+                if (shape == 3) {
+                    // SCB: 16-nt cell barcode + 10-nt UMI literals and the 22-nt adapter in front, polyA behind
+                    auto random_lit = [&](int n) {
+                        std::string t((size_t)n, 'A');
+                        for (auto& c : t) c = "ACGT"[rng.next() & 3];
+                        return t;
+                    };
+                    const std::string cb = random_lit(16), umi = random_lit(10);
+                    int pa = (int)std::lround(15 + 7.5 * rng.normal());
+                    if (pa > 0) segs.push_back(Seg{-1, std::string((size_t)pa, 'A'), 0, (uint64_t)pa, true});
+                    segs.insert(segs.begin(), Seg{-1, umi, 0, umi.size(), true});
+                    segs.insert(segs.begin(), Seg{-1, cb, 0, cb.size(), true});
+                    segs.insert(segs.begin(), Seg{-1, tag3, 0, tag3.size(), true});
+                    // PCR: the copy of cycle path c1.c2...; every cycle mutates bases at rate 4/3 x 2.67e-4
+                    // (Taq-setting1, src/pcr.cpp:36) -- here x 5 so that small test inputs carry mods
+                    const int cycles = 1 + (int)(rng.next() % 4);
+                    for (auto& sg : segs) {
+                        const uint64_t len = sg.end - sg.start;
+                        const double expect = (double)cycles * 5.0 * (4.0 / 3.0) * 2.67e-4 * (double)len;
+                        int nm = (int)expect;
+                        nm += rng.uni() < expect - nm;
+                        for (int m = 0; m < nm && len > 0; m++) {
+                            if (!sg.mods.empty()) sg.mods.push_back(',');
+                            put_u64(sg.mods, (uint64_t)(rng.uni() * (double)len));
+                            sg.mods.push_back("ACGT"[rng.next() & 3]);
+                        }
+                    }
+                    pcr_suffix.clear();
+                    for (int c = 0; c < cycles; c++) {
+                        pcr_suffix.push_back('.');
+                        put_u64(pcr_suffix, (uint64_t)c + (rng.next() & 1));
+                    }
+                } else if (shape == 0) {
                     depth = 1;
                     while (depth < 50 && rng.uni() > 0.5) depth++;
                     depth = std::min<uint64_t>(depth, n_molecules - emitted);
@@ -139,6 +174,7 @@ extern "C" int tksm_seq_synth_mdf(tksm_seq* h, int shape, uint64_t n_molecules, 
             o.push_back('+');
             o.push_back('M');
             put_u64(o, rec);
+            o.append(pcr_suffix);
             o.push_back('\t');
             put_u64(o, depth);
             o.append("\ttid=T");
@@ -153,7 +189,9 @@ extern "C" int tksm_seq_synth_mdf(tksm_seq* h, int shape, uint64_t n_molecules, 
                 put_u64(o, s.start);
                 o.push_back('\t');
                 put_u64(o, s.end);
-                o.append(s.plus ? "\t+\t\n" : "\t-\t\n");
+                o.append(s.plus ? "\t+\t" : "\t-\t");
+                o.append(s.mods);
+                o.push_back('\n');
             }
             emitted += depth;
             rec++;
