@@ -32,6 +32,20 @@ GRCH38 = [248956422, 242193529, 198295559, 190214555, 181538259, 170805979, 1593
 NAMES = [f"chr{i}" for i in range(1, 23)] + ["chrX", "chrY", "chrM"]
 
 
+# --workload: the default is the configuration BASELINE.json's metric is quoted on (configs[1]); the others time the
+# shapes of the remaining configs on one GPU (extra data points for DESIGN.md, not the bench line the driver reads)
+WORKLOADS = {
+    "bulk": dict(shape=1, models="nanopore2020", identity=None,
+                 desc="BASELINE configs[1]: README bulk Tsb->Trc->plA->Flp->Tag->Seq"),
+    "scrna": dict(shape=3, models="nanopore2020", identity=None,
+                  desc="BASELINE configs[2] shape: scRNA Tsb->SCB->PCR->Seq (barcode, UMI, adapter literals, PCR base mods)"),
+    "pacbio": dict(shape=1, models="pacbio2016", identity="99,99.9,0.5",
+                   desc="BASELINE configs[3] shape: high-identity pacbio2016 tables on the bulk molecules"),
+    "skew": dict(shape=2, models="nanopore2020", identity=None,
+                 desc="BASELINE configs[4] shape: single-interval molecules, lengths log-uniform 500 bp-100 kbp"),
+}
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -98,20 +112,26 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--identity", default="84,99,5.5", help="--badread-identity mean,max,stdev (experiments)")
     ap.add_argument("--cpu-sample", type=int, default=0, help="molecules in the CPU baseline sample (0 = auto)")
+    ap.add_argument("--workload", default="bulk", choices=sorted(WORKLOADS))
     args = ap.parse_args()
+    wl = WORKLOADS[args.workload]
+    if wl["identity"] and args.identity == "84,99,5.5":
+        args.identity = wl["identity"]
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    config = {"workload": "BASELINE configs[1]: README bulk Tsb->Trc->plA->Flp->Tag->Seq, "
+    config = {"workload": f"{wl['desc']}, "
                           f"{args.molecules} molecules per GPU, synthetic {3.1 * args.genome_scale:.2f} Gbp genome, "
-                          f"nanopore2020 error+qscore models, identity {args.identity}, FASTQ with qscores",
+                          f"{wl['models']} error+qscore models, identity {args.identity}, FASTQ with qscores",
               "molecules_per_gpu": args.molecules, "sharding": f"independent molecule shards x{world}, no collective",
               "l2": "inputs+outputs (>3 GB per step) exceed the 126 MB L2; no explicit flush"}
 
     if args.impl == "reference":
         if rank != 0:
             return 0
+        if args.workload != "bulk":
+            raise SystemExit("--impl reference times the default workload only")
         return reference_arm(args, config)
 
     import torch
@@ -130,8 +150,8 @@ def main():
     have = os.path.exists(os.path.join(os.environ["TKSM_MODELS"], "badread", "nanopore2020.error.gz"))
     if not have:
         raise SystemExit("model files missing under tksm_b200/models/badread (run __graft_entry__.build())")
-    s.load_models("nanopore2020", "nanopore2020")
-    mdf = s.synth_mdf(1, args.molecules, seed=1000 + rank)
+    s.load_models(wl["models"], wl["models"])
+    mdf = s.synth_mdf(wl["shape"], args.molecules, seed=1000 + rank, min_len=500, max_len=100000)
     ordinal_base = rank * args.molecules
     batch = s.batch(mdf, ordinal_base)
 
@@ -221,7 +241,7 @@ def main():
                          "algorithmic_bytes_per_step": st["algorithmic_bytes"]},
         }
         # CPU baseline beside it, rank 0, N = 1 only, bounded sample
-        if world == 1:
+        if world == 1 and args.workload == "bulk":   # the CPU port is set up for the default models
             line["cpu_baseline"] = cpu_baseline(s, mdf, args)
         print(json.dumps(line), file=RESULT_OUT, flush=True)
     if world > 1:
