@@ -1431,6 +1431,7 @@ int tksm_seq_synth_reference(tksm_seq* h, const char* const* names, const uint64
         g.n_bases = (g.n_bases + 63) & ~uint64_t(63);
         uint64_t off = g.n_bases, len = lengths[i];
         g.contigs[names[i]] = Contig{off, len};
+        g.note_name(strlen(names[i]));
         // 'N' runs of 1..50 kbp until n_frac of the contig is covered
         uint64_t want = (uint64_t)(n_frac * (double)len), have = 0;
         std::vector<std::pair<uint64_t, uint32_t>> runs;

@@ -51,6 +51,7 @@ void GenomeStore::add_contig(const std::string& name, const char* seq, size_t le
     flush();
     n_bases = off + len;
     contigs[name] = Contig{off, (uint64_t)len};  // later files override earlier names (dict.update)
+    note_name(name.size());
 }
 
 void GenomeStore::load_fasta_text(const char* text, size_t len) {
@@ -447,6 +448,9 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
     int tok_next = 0;
     size_t lit_epoch = 1;  // bumped when a rollback may have dropped pool bytes
     TokEntry* last_tok = nullptr;  // exon lines of one molecule repeat the chromosome
+    TokEntry scratch_tok;
+    std::string lit;               // encoded literal of the current line (buffer reused)
+    constexpr size_t LIT_SLOTS = 4096;
     auto resolve = [&](std::string_view chrom) -> TokEntry& {
         if (last_tok && last_tok->tok.size() == chrom.size() && !chrom.empty() &&
             memcmp(last_tok->tok.data(), chrom.data(), chrom.size()) == 0)
@@ -457,6 +461,14 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
                 last_tok = &toks[i];
                 return toks[i];
             }
+        if (!genome->name_len_possible(chrom.size())) {
+            // no contig name has this length: a literal (barcode, UMI, adapter, poly(A) run); it stays out of the
+            // token cache, which the chromosome names keep
+            last_tok = nullptr;
+            scratch_tok.contig = nullptr;
+            scratch_tok.lit_s = scratch_tok.lit_e = -1;
+            return scratch_tok;
+        }
         TokEntry& t = toks[tok_next];
         tok_next = (tok_next + 1) % NTOK;
         t.tok.assign(chrom);
@@ -482,8 +494,8 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
         out.mod_chr.resize(m_mod);
         // literals appended by the rolled-back record may be indexed: drop the index entries lazily
         if (out.lit_pool.size() != m_lit) {
-            for (auto it = out.lit_index.begin(); it != out.lit_index.end();)
-                it = it->second >= m_lit ? out.lit_index.erase(it) : std::next(it);
+            for (auto& sl : out.lit_index)
+                if (sl.len && (size_t)sl.off + sl.len > m_lit) sl = HostBatch::LitSlot{};
             out.lit_pool.resize(m_lit);
             lit_epoch++;
         }
@@ -563,15 +575,23 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
             if (te.lit_s == s && te.lit_e == e && te.lit_epoch == lit_epoch) {
                 off = te.lit_off;
             } else {
-                std::string lit((size_t)slen, 0);
-                for (uint32_t i = 0; i < slen; i++) lit[i] = (char)frag_code(ascii_upper((uint8_t)chrom[(size_t)s + i]));
-                auto it = out.lit_index.find(lit);
-                if (it != out.lit_index.end()) {
-                    off = it->second;
+                lit.resize((size_t)slen);
+                uint64_t hsh = 0xCBF29CE484222325ull;
+                for (uint32_t i = 0; i < slen; i++) {
+                    const uint8_t c = frag_code(ascii_upper((uint8_t)chrom[(size_t)s + i]));
+                    lit[i] = (char)c;
+                    hsh = (hsh ^ c) * 0x100000001B3ull;
+                }
+                if (out.lit_index.empty()) out.lit_index.resize(LIT_SLOTS);
+                HostBatch::LitSlot& sl = out.lit_index[(size_t)((hsh ^ (hsh >> 29)) & (LIT_SLOTS - 1))];
+                if (sl.len == slen && sl.hash == hsh && slen && memcmp(out.lit_pool.data() + sl.off, lit.data(), slen) == 0) {
+                    off = sl.off;
                 } else {
                     off = (uint32_t)out.lit_pool.size();
                     out.lit_pool.insert(out.lit_pool.end(), lit.begin(), lit.end());
-                    if (out.lit_index.size() < (1u << 20)) out.lit_index.emplace(std::move(lit), off);
+                    sl.hash = hsh;
+                    sl.off = off;
+                    sl.len = slen;
                 }
                 te.lit_s = s;
                 te.lit_e = e;

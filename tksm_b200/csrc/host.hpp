@@ -24,6 +24,11 @@ struct Contig {
 // after upper-casing (N runs, IUPAC codes, anything else the FASTA holds).
 struct GenomeStore {
     std::unordered_map<std::string, Contig> contigs;
+    // bit min(len, 63) set for every contig-name length: most literal segment names (barcodes, UMIs, adapters)
+    // are ruled out as contigs without hashing them
+    uint64_t name_len_mask = 0;
+    void note_name(size_t len) { name_len_mask |= 1ull << (len < 63 ? len : 63); }
+    bool name_len_possible(size_t len) const { return (name_len_mask >> (len < 63 ? len : 63)) & 1ull; }
     std::vector<uint32_t> words;        // 16 bases per word
     uint64_t n_bases = 0;               // global coordinate space used so far
     std::vector<uint64_t> exc_start;
@@ -60,7 +65,13 @@ struct HostBatch {
     std::vector<uint8_t> id_pool;
     uint64_t total_raw_bases = 0;   // over reads (depth expanded)
     uint64_t genomic_bases = 0, literal_bases = 0;  // over reads, for the algorithmic-bytes figure
-    std::unordered_map<std::string, uint32_t> lit_index;
+    // literal de-duplication: direct-mapped on a hash of the encoded bytes (repeated tags and poly(A) runs share
+    // pool bytes; unique barcodes / UMIs overwrite a slot and cost no allocation)
+    struct LitSlot {
+        uint64_t hash = 0;
+        uint32_t off = 0, len = 0;   // len == 0: empty
+    };
+    std::vector<LitSlot> lit_index;
 
     size_t n_reads() const { return read_mol.size(); }
     size_t n_mols() const { return mol_raw_len.size(); }
