@@ -94,6 +94,7 @@ __global__ void synth_genome_kernel(uint32_t* words, uint64_t nwords, uint32_t s
 constexpr size_t SMEM_TOTAL = 232448;  // 227 KB opt-in maximum per CTA on sm_100 (smaller carve-outs for more L1 measured slower: 195 KB +5 %, 163 KB +19 %)
 constexpr int N_CLASSES = 6;           // teams of 1, 2, 4, 8, 24 warps in shared memory; 24 warps with a global workspace
 constexpr int GWS_CLASS = N_CLASSES - 1;
+constexpr int GWS_W2 = 32;   // warps per read of the expansion + qscore kernel of the global-workspace class
 const int CLASS_W[N_CLASSES] = {1, 2, 4, 8, 24, 24};
 inline uint32_t list_capacity(uint32_t ncap) { return ncap / 5 * 2 + 64; }
 
@@ -362,9 +363,9 @@ void compute_classes(tksm_seq* h) {
         if (32 % W == 0 && SIM_FIXED_SMEM + (size_t)h->slab2[c] * (32 / W) + 128 + 64 <= SMEM_TOTAL) h->threads2[c] = 1024;
         h->smem_bytes2[c] = SIM_FIXED_SMEM + (size_t)h->slab2[c] * (h->threads2[c] / 32 / W) + 128 + 64;
     }
-    h->smem_bytes[GWS_CLASS] = qcls_bytes + SIM_FIXED_SMEM + 128;
-    h->threads2[GWS_CLASS] = SIM_THREADS;
-    h->smem_bytes2[GWS_CLASS] = SIM_FIXED_SMEM + 128 + 64;
+    h->smem_bytes[GWS_CLASS] = qcls_bytes + SIM_FIXED_SMEM + gws_small_bytes(CLASS_W[GWS_CLASS], false) + 128;
+    h->threads2[GWS_CLASS] = GWS_W2 * 32;
+    h->smem_bytes2[GWS_CLASS] = SIM_FIXED_SMEM + gws_small_bytes(GWS_W2, true) + 128 + 64;
 }
 
 void upload_models(tksm_seq* h) {
@@ -427,7 +428,9 @@ struct Phase2Launch {
     int grid, threads;
     uint32_t slab_bytes, cap_list;
 };
-template <int W, bool GWS>
+// W2: warps per read of the PHASE 2 kernel (the global-workspace class is not bound by a shared-memory slab and
+// puts all 32 warps of a CTA on its read)
+template <int W, bool GWS, int W2 = W>
 void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, bool split, const Phase2Launch& p2) {
     if (!split) {
         launch_sim_phase<W, GWS, 0>(stream, P, smem, grid);
@@ -438,7 +441,7 @@ void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, bool sp
         P.counter += 16;
         P.slab_bytes = p2.slab_bytes;
         P.cap_list = p2.cap_list;
-        launch_sim_phase<W, GWS, 2>(stream, P, p2.smem, p2.grid, p2.threads);
+        launch_sim_phase<W2, GWS, 2>(stream, P, p2.smem, p2.grid, p2.threads);
     }
 }
 
@@ -684,7 +687,8 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         const uint32_t ncap = (uint32_t)align_up(p.max_n_gws + 16, 16);
         ncap_c[GWS_CLASS] = ncap;
         cap_list_c[GWS_CLASS] = ncap / 2 + 64;
-        slab_c[GWS_CLASS] = slab_layout(CLASS_W[GWS_CLASS], 8, ncap, cap_list_c[GWS_CLASS]).bytes;
+        slab_c[GWS_CLASS] = std::max(slab_layout(CLASS_W[GWS_CLASS], 8, ncap, cap_list_c[GWS_CLASS]).bytes,
+                                     slab_layout(GWS_W2, 8, ncap, cap_list_c[GWS_CLASS], true).bytes);
         b->gws.ensure((size_t)slab_c[GWS_CLASS] * h->num_sms);
     }
     uint64_t* d_totals = (uint64_t*)((char*)b->counters.p + CNT_TOTALS);
@@ -775,7 +779,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
             case 2: launch_sim<4, false>(st, P, h->smem_bytes[c], grid, split, p2); break;
             case 3: launch_sim<8, false>(st, P, h->smem_bytes[c], grid, split, p2); break;
             case 4: launch_sim<24, false>(st, P, h->smem_bytes[c], grid, split, p2); break;
-            default: launch_sim<24, true>(st, P, h->smem_bytes[c], grid, split, p2); break;
+            default: launch_sim<24, true, GWS_W2>(st, P, h->smem_bytes[c], grid, split, p2); break;
         }
         launches += (split && (flags & RUN_ERRORS)) ? 2 : 1;
     }

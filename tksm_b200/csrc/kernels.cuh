@@ -206,6 +206,11 @@ __host__ __device__ inline SlabLayout slab_layout(int W, uint32_t hist_elem_byte
     return L;
 }
 
+// shared-memory bytes of the GWS class for the part of the workspace in front of the candidate list
+__host__ __device__ inline uint32_t gws_small_bytes(int W, bool lean) {
+    return (slab_layout(W, 8, 16, 16, lean).off_list + 15u) & ~15u;
+}
+
 // Finds the first of 256 bins at which the cumulative (loss, ins) crosses the target.
 // Executed by the first warp of the team; results broadcast through misc[].
 //   misc[0] = bin (256 when no crossing), misc[1] = cum loss before bin, misc[2] = cum ins before bin,
@@ -357,8 +362,10 @@ __device__ __forceinline__ uint32_t nz4(uint32_t x, uint32_t mask) {
 // fragment go to the read's `mid` record in global memory.  PHASE 2: loads them back and does
 // expansion + qscores.  Two kernels halve the hot code an SM has to keep in its instruction caches.
 template <int W, bool GWS, int PHASE>
-__device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams& P, uint32_t r, uint8_t* ws,
+__device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams& P, uint32_t r, uint8_t* ws, uint8_t* wsl,
                                               const uint8_t* qcls_s, const uint8_t* lut3, uint32_t phase_threads) {
+    // ws: team workspace (shared memory; global memory for the GWS class).  wsl: where its small, hot part lives
+    // (threshold row, histogram, scratch words, compaction rings): == ws, or shared memory for the GWS class.
     // lockstep mode 2: the teams of the CTA also enter the error, expansion and qscore stages
     // together (named barrier 15 over the threads of the teams that hold a read)
     auto phase_sync = [&]() {
@@ -370,11 +377,11 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
     const DevBatch& B = P.B;
     const SlabLayout LY = slab_layout(W, (uint32_t)sizeof(HistT), P.ncap, P.cap_list, PHASE == 2);
 
-    uint16_t* T1 = (uint16_t*)ws;
-    HistT* hist = (HistT*)(ws + LY.off_hist);
-    uint32_t* misc = (uint32_t*)(ws + LY.off_misc);
+    uint16_t* T1 = (uint16_t*)wsl;
+    HistT* hist = (HistT*)(wsl + LY.off_hist);
+    uint32_t* misc = (uint32_t*)(wsl + LY.off_misc);
     uint32_t* wsum = misc + MISC_WSUM;
-    uint32_t* wq_a = (uint32_t*)(ws + LY.off_queue + (uint32_t)(tm.rank >> 5) * QUEUE_BYTES);
+    uint32_t* wq_a = (uint32_t*)(wsl + LY.off_queue + (uint32_t)(tm.rank >> 5) * QUEUE_BYTES);
     uint32_t* wq_b = wq_a + 64;
     uint32_t* list = (uint32_t*)(ws + LY.off_list);
     uint32_t* key = (uint32_t*)(ws + LY.off_key);
@@ -1077,12 +1084,17 @@ __global__ void __launch_bounds__(PHASE == 2 ? 1024 : SIM_THREADS, 1) simulate_k
         if (threadIdx.x < (1u << (e0 & 7u))) q0row[threadIdx.x] = P.T.q_alias[(e0 >> 3) + threadIdx.x];
     }
     __syncthreads();
-    uint8_t* ws;
-    if (GWS)
+    // GWS class: candidate list, slot keys and fragment of the (long) read in global memory, the small hot part
+    // of the workspace in shared memory
+    uint8_t *ws, *wsl;
+    const uint32_t small_bytes = GWS ? gws_small_bytes(W, PHASE == 2) : 0u;
+    if (GWS) {
         ws = P.gws + (size_t)blockIdx.x * P.slab_bytes;
-    else
-        ws = smem + qcls_bytes + SIM_FIXED_SMEM + (size_t)tm.id * P.slab_bytes;
-    uint32_t* ticket = (uint32_t*)(smem + qcls_bytes + SIM_FIXED_SMEM + (GWS ? 0 : (size_t)TEAMS * P.slab_bytes)) + tm.id;
+        wsl = smem + qcls_bytes + SIM_FIXED_SMEM;
+    } else {
+        ws = wsl = smem + qcls_bytes + SIM_FIXED_SMEM + (size_t)tm.id * P.slab_bytes;
+    }
+    uint32_t* ticket = (uint32_t*)(smem + qcls_bytes + SIM_FIXED_SMEM + (GWS ? (size_t)small_bytes : (size_t)TEAMS * P.slab_bytes)) + tm.id;
     if (P.lockstep) {
         // The CTA takes TEAMS consecutive work items (near-equal lengths: the list is sorted) and its
         // teams start each of them together, so the warps of a scheduler walk the same code at about
@@ -1097,7 +1109,7 @@ __global__ void __launch_bounds__(PHASE == 2 ? 1024 : SIM_THREADS, 1) simulate_k
             if (base >= P.n_work) break;
             const uint32_t nact = min((uint32_t)TEAMS, P.n_work - base);
             if (wi < P.n_work)
-                simulate_read<W, GWS, PHASE>(tm, P, P.work[wi], ws, qcls_s, lut3, P.lockstep >= 2 ? nact * (uint32_t)(W * 32) : 0u);
+                simulate_read<W, GWS, PHASE>(tm, P, P.work[wi], ws, wsl, qcls_s, lut3, P.lockstep >= 2 ? nact * (uint32_t)(W * 32) : 0u);
         }
         return;
     }
@@ -1107,7 +1119,7 @@ __global__ void __launch_bounds__(PHASE == 2 ? 1024 : SIM_THREADS, 1) simulate_k
         const uint32_t wi = *ticket;
         tm.sync();
         if (wi >= P.n_work) break;
-        simulate_read<W, GWS, PHASE>(tm, P, P.work[wi], ws, qcls_s, lut3, 0u);
+        simulate_read<W, GWS, PHASE>(tm, P, P.work[wi], ws, wsl, qcls_s, lut3, 0u);
     }
 }
 
