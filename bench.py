@@ -233,10 +233,13 @@ def main():
                             "D2H of the FASTQ bytes into a page-locked host buffer, chunks pipelined"},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src,
+                         # dram__bytes_read.sum + dram__bytes_write.sum over the 16 launches of one step of this
+                         # workload, one ncu capture (profiles/r1h_dram_per_launch.txt); other sizes: not captured
+                         "traffic": 15.16e9 if (args.workload == "bulk" and args.molecules == 1_000_000) else None,
+                         "traffic_unit": "bytes per step", "peak_source": peak_src,
                          "kernel": "work order + simulate_kernel<W,phase> (error injection | expansion + qscores, per length class) + "
                                    "reclen/scan/format: whole kernel sequence of a step",
-                         "traffic_note": "dram bytes of the four large simulate launches: profiles/r1g_simulate_summary.txt",
+                         "traffic_note": "7.5 x the algorithmic bytes: the slot keys and fragment handed from the error-injection to the expansion kernels through global memory (8.7 GB) and the per-read scratch the format kernel re-reads (3.3 GB); 2.3 ms of the step at HBM speed: profiles/r1h_dram_per_launch.txt",
                          "simulate_share": sim_ms / dev_ms if dev_ms else None,
                          "algorithmic_bytes_per_step": st["algorithmic_bytes"]},
         }
