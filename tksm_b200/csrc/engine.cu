@@ -1063,7 +1063,7 @@ void finish_deferred(const tksm_seq* h, Prepared& p, uint64_t ordinal) {
 
 // stage 2 (host threads): the batches of consecutive text chunks, concatenated up to the device
 // batch limits, with scratch layout, work lists and upload blob
-PreparedList assemble_group(const tksm_seq* h, std::vector<std::shared_future<std::shared_ptr<HostBatchList>>>& parts) {
+PreparedList assemble_group(const tksm_seq* h, const std::vector<std::shared_ptr<HostBatchList>>& parts) {
     PreparedList out;
     std::vector<std::shared_ptr<HostBatchList>> lists;
     std::vector<const HostBatch*> cur;
@@ -1084,7 +1084,7 @@ PreparedList assemble_group(const tksm_seq* h, std::vector<std::shared_future<st
         cur_reads = cur_bases = 0;
     };
     for (auto& f : parts) {
-        lists.push_back(f.get());
+        lists.push_back(f);
         for (auto& hb : *lists.back()) {
             if (!cur.empty() && (cur_reads + hb->n_reads() > limit_reads(h) || cur_bases + hb->total_raw_bases > limit_bases(h)))
                 flush();
@@ -1096,6 +1096,33 @@ PreparedList assemble_group(const tksm_seq* h, std::vector<std::shared_future<st
     flush();
     return out;
 }
+
+// The chunks of one device batch while the host threads parse them.  No thread waits for another: the
+// thread that finishes the last chunk of a closed group assembles the batch.
+struct GroupState {
+    std::atomic<int> remaining{1};   // chunks still being parsed, + 1 until the group is closed
+    std::mutex mu;
+    std::vector<std::shared_ptr<HostBatchList>> lists;   // by chunk index
+    std::exception_ptr error;
+    std::promise<PreparedList> done;
+    void store(size_t idx, std::shared_ptr<HostBatchList> r) {
+        std::lock_guard<std::mutex> g(mu);
+        if (lists.size() <= idx) lists.resize(idx + 1);
+        lists[idx] = std::move(r);
+    }
+    void fail(std::exception_ptr e) {
+        std::lock_guard<std::mutex> g(mu);
+        if (!error) error = e;
+    }
+    void complete(const tksm_seq* h) {
+        try {
+            if (error) std::rethrow_exception(error);
+            done.set_value(assemble_group(h, lists));
+        } catch (...) {
+            done.set_exception(std::current_exception());
+        }
+    }
+};
 
 }  // namespace
 
@@ -1190,17 +1217,21 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
     double w_parse = 0, w_bind = 0, w_launch = 0, w_finish = 0, w_reuse = 0, dev_ms = 0;
     try {
         WorkerPool pool(nthreads);
-        std::vector<std::shared_future<std::shared_ptr<HostBatchList>>> group;
+        std::shared_ptr<GroupState> group;
+        size_t group_chunks = 0;
         size_t group_text = 0, group_target = 1, groups_made = 0, ramp = 1;
         uint64_t text_submitted = 0;
         // text chunks (1 MiB each) per device batch in steady state
         const size_t max_group = getenv("TKSM_SEQ_MAX_GROUP") ? std::max(1, atoi(getenv("TKSM_SEQ_MAX_GROUP"))) : 32;
         auto close_group = [&]() {
-            if (group.empty()) return;
+            if (!group) return;
             const tksm_seq* hc = h;
-            auto parts = std::make_shared<std::vector<std::shared_future<std::shared_ptr<HostBatchList>>>>(std::move(group));
-            pending.push_back({pool.submit([hc, parts]() { return assemble_group(hc, *parts); }), group_text});
-            group.clear();
+            std::shared_ptr<GroupState> gs = std::move(group);
+            group.reset();
+            pending.push_back({gs->done.get_future(), group_text});
+            // every chunk already parsed: the batch is assembled by a host thread, never by this one
+            if (gs->remaining.fetch_sub(1) == 1) pool.submit([hc, gs]() { gs->complete(hc); });
+            group_chunks = 0;
             group_text = 0;
             groups_made++;
             // small batches first (the device starts early) and, when the input size is known, small
@@ -1223,10 +1254,23 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
                 }
                 text_total = std::max<uint64_t>(text_total, src.total_bytes_hint());
                 const tksm_seq* hc = h;
-                group.push_back(pool.submit([hc, tc]() { return std::make_shared<HostBatchList>(parse_chunk(hc, tc)); }).share());
+                if (!group) group = std::make_shared<GroupState>();
+                {
+                    std::shared_ptr<GroupState> gs = group;
+                    const size_t idx = group_chunks++;
+                    gs->remaining.fetch_add(1);
+                    pool.submit([hc, tc, gs, idx]() {
+                        try {
+                            gs->store(idx, std::make_shared<HostBatchList>(parse_chunk(hc, tc)));
+                        } catch (...) {
+                            gs->fail(std::current_exception());
+                        }
+                        if (gs->remaining.fetch_sub(1) == 1) gs->complete(hc);
+                    });
+                }
                 group_text += tc.n;
                 text_submitted += tc.n;
-                if (group.size() >= group_target) close_group();
+                if (group_chunks >= group_target) close_group();
             }
             if (pending.empty()) break;
             double t0 = now_ms();
