@@ -63,7 +63,29 @@ class ClockSampler(threading.Thread):
         super().__init__(daemon=True)
         self.gpu, self.rows, self.stop_ev = gpu, [], threading.Event()
 
+    def run_nvml(self):
+        """NVML directly (nvidia-ml-py): a query takes microseconds, so a 160 ms timed region gets tens of samples."""
+        import pynvml as nv
+        nv.nvmlInit()
+        h = nv.nvmlDeviceGetHandleByIndex(self.gpu)
+        mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+        get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        bits = [(0x8, 2), (0x40, 3), (0x20, 4), (0x4, 5)]   # hw_slowdown, hw_thermal, sw_thermal, sw_power_cap
+        while not self.stop_ev.is_set():
+            sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+            r = int(get_reasons(h))
+            row = [str(sm), str(mx), "", "", "", ""]
+            for bit, col in bits:
+                row[col] = "Active" if r & bit else "Not Active"
+            self.rows.append(row)
+            self.stop_ev.wait(0.005)
+
     def run(self):
+        try:
+            self.run_nvml()
+            return
+        except Exception:
+            pass
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
         while not self.stop_ev.is_set():
