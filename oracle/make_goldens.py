@@ -315,7 +315,8 @@ def make_dist(which=None):
         "random": dict(em="random", qm="random", ident="84.0,99.0,5.5"),
         "nanopore2020_const90": dict(em="nanopore2020", qm="ideal", ident="90.0,90.0,0.0"),
     }
-    fasta, mdf = dist_inputs()
+    n_mol = int(os.environ.get("DIST_N_MOL", "10000"))   # at least 10 k reads per model
+    fasta, mdf = dist_inputs(n_mol=n_mol)
     for name, c in configs.items():
         if which and name not in which:
             continue
@@ -339,12 +340,13 @@ def make_dist(which=None):
                 cmd = [sys.executable, os.path.join(REF, "py", "sequence.py"), "-i", f"in{w}.mdf", "-r", "g.fa",
                        "-o", f"out{w}.fastq", "-t", "1", "--badread-identity", c["ident"],
                        "--badread-error-model", c["em"], "--badread-qscore-model", c["qm"]]
-                procs.append((w, subprocess.Popen(cmd, cwd=td, env=ref_env(), stdout=subprocess.PIPE,
-                                                  stderr=subprocess.PIPE, text=True)))
+                # progress text goes to a file: a pipe nobody drains would block the worker
+                log = open(os.path.join(td, f"log{w}.txt"), "w")
+                procs.append((w, subprocess.Popen(cmd, cwd=td, env=ref_env(), stdout=log, stderr=log)))
             fq = b""
             for w, p in procs:
-                _, err = p.communicate()
-                if p.returncode != 0:
+                if p.wait() != 0:
+                    err = open(os.path.join(td, f"log{w}.txt")).read()
                     raise SystemExit(f"reference failed on dist/{name}: {err[-3000:]}")
                 fq += open(os.path.join(td, f"out{w}.fastq"), "rb").read()
             p2 = run_reference(["-i", "in.mdf", "-r", "g.fa", "--perfect", "perf.fasta"], td)
@@ -352,7 +354,10 @@ def make_dist(which=None):
             perf = open(os.path.join(td, "perf.fasta"), "rb").read()
         summary = st.summarise(fq, perf)
         summary["config"] = c
-        summary["inputs"] = {"seed": 5, "n_mol": 1500, "lo": 250, "hi": 4000}
+        summary["inputs"] = {"seed": 5, "n_mol": n_mol, "lo": 250, "hi": 4000}
+        for key in ("len_ratio", "identity", "hdr_identity", "sub_rate", "ins_rate", "del_rate", "mean_q", "hp_err",
+                    "hp_del", "mean_q_eq", "mean_q_x", "mean_q_i"):
+            summary[key] = [round(float(v), 5) for v in summary[key]]
         with gzip.open(os.path.join(GOLD, f"ref_dist_{name}.json.gz"), "wt") as f:
             json.dump(summary, f, separators=(",", ":"))
         print(f"dist/{name}: {summary['n_reads']} reads, rates {summary['rates']}, "

@@ -70,10 +70,11 @@ def summarise(fastq_bytes, perfect_bytes, max_reads=None):
     hp_err, hp_del, mq_cls = [], [], [[], [], []]   # per read: the unit the samples are independent in
     hp = np.zeros((HP_MAX + 1, HP_OBS), np.int64)
     qh = np.zeros((3, 3, 94), np.int64)           # [position class][op class =,X,I][q]
+    qh1 = np.zeros((3, 3, 94), np.int64)          # the same over ONE sampled base per read, position and op class
     ins_len = np.zeros(12, np.int64)
     del_len = np.zeros(12, np.int64)
     tot = np.zeros(4, np.int64)
-    for info, seq, qual in reads:
+    for ridx, (info, seq, qual) in enumerate(reads):
         raw = perf[info["molecule_id"]]
         ops = align_ops(seq, raw)
         ne, nx, ni, nd = (int((ops == c).sum()) for c in (E, X, I, D))
@@ -102,6 +103,14 @@ def summarise(fastq_bytes, perfect_bytes, max_reads=None):
         pos[:POS_EDGE] = 0
         pos[max(len(q) - POS_EDGE, 0):] = 2
         np.add.at(qh, (pos, cls, np.clip(q, 0, 93)), 1)
+        # independent units for a chi-square test: bases of one read share its identity, so one base per
+        # read is drawn (seeded by the read's index) for every (position class, op class) cell
+        srng = np.random.default_rng(977 * ridx + 13)
+        cell = pos * 3 + cls
+        for ce in range(9):
+            idx = np.flatnonzero(cell == ce)
+            if len(idx):
+                qh1[ce // 3, ce % 3, min(max(int(q[idx[srng.integers(len(idx))]]), 0), 93)] += 1
         for oc in range(3):
             sel = q[cls == oc]
             mq_cls[oc].append(float(sel.mean()) if len(sel) else -1.0)
@@ -144,5 +153,5 @@ def summarise(fastq_bytes, perfect_bytes, max_reads=None):
         "sub_rate": sub, "ins_rate": ins, "del_rate": dele, "mean_q": meanq,
         "hp_err": hp_err, "hp_del": hp_del, "mean_q_eq": mq_cls[0], "mean_q_x": mq_cls[1], "mean_q_i": mq_cls[2],
         "rates": {"X": tot[1] / n_raw, "I": tot[2] / n_raw, "D": tot[3] / n_raw, "identity": tot[0] / n_cols},
-        "hp": hp.tolist(), "qhist": qh.tolist(), "ins_len": ins_len.tolist(), "del_len": del_len.tolist(),
+        "hp": hp.tolist(), "qhist": qh.tolist(), "qhist1": qh1.tolist(), "ins_len": ins_len.tolist(), "del_len": del_len.tolist(),
     }

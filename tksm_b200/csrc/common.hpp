@@ -125,7 +125,16 @@ struct DevBatch {
     uint32_t* status;              // 0 ok, else error bits
 };
 
-enum : uint32_t { ST_OK = 0, ST_OPS_OVERFLOW = 1, ST_SCRATCH_OVERFLOW = 2, ST_EPOCH_CAP = 4, ST_FIXUP_OVERFLOW = 8 };
+enum : uint32_t {
+    ST_OK = 0,
+    ST_OPS_OVERFLOW = 1,      // the read outgrew twice its fragment
+    ST_SCRATCH_OVERFLOW = 2,  // the read outgrew its scratch slot
+    ST_EPOCH_CAP = 4,         // time cap of the error loop (py/tksm_badread.py:354)
+    ST_BAND = 8,              // the alignment left its widest band: qscores follow the edit script itself
+};
+// ident_den carries this flag when (num, den) are the matches / columns of the read's alignment (printed as they
+// are); without it they are the edit-script counts the calibration of DESIGN.md 3.5 maps to an aligned identity
+constexpr uint32_t IDENT_MEASURED = 0x80000000u;
 
 // run flags
 enum : uint32_t {

@@ -223,7 +223,7 @@ struct tksm_seq_batch {
     DBuf blob;
     DevBatch db{};
     uint32_t* d_work[N_CLASSES] = {};
-    DBuf scr_seq, scr_qual, scr_raw, per_read, out[2], rec_len[2], rec_off[2], sums, gws, counters, work_keys, work_sorted, work_bins, mid;
+    DBuf scr_seq, scr_qual, scr_raw, per_read, out[2], rec_len[2], rec_off[2], sums, gws, counters, work_keys, work_sorted, work_bins, mid, trace;
     HBuf stage;           // pinned upload staging
     HBuf host_out[2];     // pinned download staging (streaming to files)
     HBuf h_tot;           // pinned: record bytes per output, read bases, status
@@ -291,7 +291,7 @@ struct tksm_seq {
     uint32_t slab[N_CLASSES] = {};
     size_t smem_bytes[N_CLASSES] = {};
     // PHASE 2 kernels (split mode): lean team workspaces, 32 warps per CTA where they fit
-    uint32_t cap_list2[N_CLASSES] = {}, slab2[N_CLASSES] = {}, threads2[N_CLASSES] = {};
+    uint32_t slab2[N_CLASSES] = {}, threads2[N_CLASSES] = {};
     size_t smem_bytes2[N_CLASSES] = {};
     std::vector<uint16_t> thr;
     bool attrs_set = false;
@@ -356,16 +356,16 @@ void compute_classes(tksm_seq* h) {
         h->cap_list[c] = list_capacity(ncap);
         h->slab[c] = slab_layout(W, hist_elem, ncap, h->cap_list[c]).bytes;
         h->smem_bytes[c] = qcls_bytes + SIM_FIXED_SMEM + (size_t)h->slab[c] * teams + 128;
-        // PHASE 2: same fragment capacity, no k-mer classes, fix-up list only
-        h->cap_list2[c] = ncap / 8 + 64;
-        h->slab2[c] = slab_layout(W, hist_elem, ncap, h->cap_list2[c], true).bytes;
+        // PHASE 2 (expansion, alignment, qscores): fragment, slot lengths and read in shared memory; no k-mer
+        // classes, threshold row or histogram, so 32 warps per CTA where the workspaces fit
+        h->slab2[c] = slab2_small_bytes(W) + slab2_big_bytes(ncap);
         h->threads2[c] = SIM_THREADS;
         if (32 % W == 0 && SIM_FIXED_SMEM + (size_t)h->slab2[c] * (32 / W) + 128 + 64 <= SMEM_TOTAL) h->threads2[c] = 1024;
         h->smem_bytes2[c] = SIM_FIXED_SMEM + (size_t)h->slab2[c] * (h->threads2[c] / 32 / W) + 128 + 64;
     }
-    h->smem_bytes[GWS_CLASS] = qcls_bytes + SIM_FIXED_SMEM + gws_small_bytes(CLASS_W[GWS_CLASS], false) + 128;
+    h->smem_bytes[GWS_CLASS] = qcls_bytes + SIM_FIXED_SMEM + gws_small_bytes(CLASS_W[GWS_CLASS]) + 128;
     h->threads2[GWS_CLASS] = GWS_W2 * 32;
-    h->smem_bytes2[GWS_CLASS] = SIM_FIXED_SMEM + gws_small_bytes(GWS_W2, true) + 128 + 64;
+    h->smem_bytes2[GWS_CLASS] = SIM_FIXED_SMEM + slab2_small_bytes(GWS_W2) + 128 + 64;
 }
 
 void upload_models(tksm_seq* h) {
@@ -421,26 +421,21 @@ void launch_sim_phase(cudaStream_t stream, const SimParams& P, size_t smem, int 
     CK(cudaGetLastError());
 }
 
-// one kernel per class, or (split) error injection and expansion + qscores as two kernels with
-// their own ticket counters (P.counter, P.counter + 16)
+// error injection and expansion + alignment + qscores as two kernels per class with their own ticket
+// counters (P.counter, P.counter + 16)
 struct Phase2Launch {
     size_t smem;
     int grid, threads;
-    uint32_t slab_bytes, cap_list;
+    uint32_t slab_bytes;
 };
 // W2: warps per read of the PHASE 2 kernel (the global-workspace class is not bound by a shared-memory slab and
 // puts all 32 warps of a CTA on its read)
 template <int W, bool GWS, int W2 = W>
-void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, bool split, const Phase2Launch& p2) {
-    if (!split) {
-        launch_sim_phase<W, GWS, 0>(stream, P, smem, grid);
-        return;
-    }
+void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, const Phase2Launch& p2) {
     launch_sim_phase<W, GWS, 1>(stream, P, smem, grid);
     if (P.flags & RUN_ERRORS) {
         P.counter += 16;
         P.slab_bytes = p2.slab_bytes;
-        P.cap_list = p2.cap_list;
         launch_sim_phase<W2, GWS, 2>(stream, P, p2.smem, p2.grid, p2.threads);
     }
 }
@@ -688,15 +683,25 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         ncap_c[GWS_CLASS] = ncap;
         cap_list_c[GWS_CLASS] = ncap / 2 + 64;
         slab_c[GWS_CLASS] = std::max(slab_layout(CLASS_W[GWS_CLASS], 8, ncap, cap_list_c[GWS_CLASS]).bytes,
-                                     slab_layout(GWS_W2, 8, ncap, cap_list_c[GWS_CLASS], true).bytes);
+                                     slab2_big_bytes(ncap));
         b->gws.ensure((size_t)slab_c[GWS_CLASS] * h->num_sms);
     }
     uint64_t* d_totals = (uint64_t*)((char*)b->counters.p + CNT_TOTALS);
     CK(cudaMemsetAsync(b->counters.p, 0, 128, S));
-    // error injection and expansion + qscores as two kernels per class (3 % faster than the fused kernel: less
-    // hot code per SM); TKSM_SIM_SPLIT=0 selects the fused kernel
-    const bool split = !(getenv("TKSM_SIM_SPLIT") && atoi(getenv("TKSM_SIM_SPLIT")) == 0);
-    if (split && want_bad) b->mid.ensure(3 * p.scr_total + 64 * (uint64_t)R + 64);
+    if (want_bad) b->mid.ensure(3 * p.scr_total + 64 * (uint64_t)R + 64);
+    // alignment trace words: one region per team of every PHASE 2 grid (the classes run concurrently)
+    uint64_t trace_off[N_CLASSES] = {}, trace_team[N_CLASSES] = {}, trace_total = 0;
+    if (flags & RUN_QUAL)
+        for (int c = 0; c < N_CLASSES; c++) {
+            if (p.n_work[c] == 0) continue;
+            const int W2 = c == GWS_CLASS ? GWS_W2 : CLASS_W[c];
+            const int teams2 = c == GWS_CLASS ? 1 : (int)h->threads2[c] / 32 / CLASS_W[c];
+            const size_t grid2 = std::min<size_t>((size_t)h->num_sms, (p.n_work[c] + teams2 - 1) / teams2);
+            trace_team[c] = trace_team_bytes(W2, ncap_c[c]);
+            trace_off[c] = trace_total;
+            trace_total += trace_team[c] * teams2 * grid2;
+        }
+    b->trace.ensure(std::max<uint64_t>(trace_total, 16));
 
     CK(cudaEventRecord(b->ev[0], S));
     uint32_t launches = 0;
@@ -754,10 +759,8 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         P.slab_bytes = slab_c[c];
         P.gws = b->gws.as<uint8_t>();
         P.mid = b->mid.as<uint8_t>();
-        {
-            static const int mode = getenv("TKSM_SIM_LOCKSTEP") ? atoi(getenv("TKSM_SIM_LOCKSTEP")) : 0;
-            P.lockstep = (uint32_t)mode;
-        }
+        P.trace = b->trace.as<uint8_t>() + trace_off[c];
+        P.trace_bytes = trace_team[c];
         const int teams = c == GWS_CLASS ? 1 : SIM_WARPS / CLASS_W[c];
         int grid = (int)std::min<size_t>((size_t)h->num_sms, (P.n_work + teams - 1) / teams);
         Phase2Launch p2;
@@ -767,21 +770,20 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
             p2.grid = (int)std::min<size_t>((size_t)h->num_sms, (P.n_work + teams2 - 1) / teams2);
             p2.threads = (int)h->threads2[c];
             p2.slab_bytes = c == GWS_CLASS ? slab_c[c] : h->slab2[c];   // the global workspaces keep their size
-            p2.cap_list = c == GWS_CLASS ? cap_list_c[c] : h->cap_list2[c];
         }
         const uint32_t si = used_streams % 4;
         cudaStream_t st = h->class_stream[b->lane][si];
         if (used_streams < 4) CK(cudaStreamWaitEvent(st, b->ev_sorted, 0));
         used_streams++;
         switch (c) {
-            case 0: launch_sim<1, false>(st, P, h->smem_bytes[c], grid, split, p2); break;
-            case 1: launch_sim<2, false>(st, P, h->smem_bytes[c], grid, split, p2); break;
-            case 2: launch_sim<4, false>(st, P, h->smem_bytes[c], grid, split, p2); break;
-            case 3: launch_sim<8, false>(st, P, h->smem_bytes[c], grid, split, p2); break;
-            case 4: launch_sim<24, false>(st, P, h->smem_bytes[c], grid, split, p2); break;
-            default: launch_sim<24, true, GWS_W2>(st, P, h->smem_bytes[c], grid, split, p2); break;
+            case 0: launch_sim<1, false>(st, P, h->smem_bytes[c], grid, p2); break;
+            case 1: launch_sim<2, false>(st, P, h->smem_bytes[c], grid, p2); break;
+            case 2: launch_sim<4, false>(st, P, h->smem_bytes[c], grid, p2); break;
+            case 3: launch_sim<8, false>(st, P, h->smem_bytes[c], grid, p2); break;
+            case 4: launch_sim<24, false>(st, P, h->smem_bytes[c], grid, p2); break;
+            default: launch_sim<24, true, GWS_W2>(st, P, h->smem_bytes[c], grid, p2); break;
         }
-        launches += (split && (flags & RUN_ERRORS)) ? 2 : 1;
+        launches += (flags & RUN_ERRORS) ? 2 : 1;
     }
     for (uint32_t i = 0; i < std::min<uint32_t>(used_streams, 4); i++) {
         CK(cudaEventRecord(b->ev_class[i], h->class_stream[b->lane][i]));

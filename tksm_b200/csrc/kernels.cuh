@@ -18,6 +18,7 @@
 #include <cstdint>
 #include <type_traits>
 
+#include "align.cuh"
 #include "common.hpp"
 
 namespace tk {
@@ -169,7 +170,7 @@ constexpr uint32_t SIM_FIXED_SMEM = 64 + 512;  // CTA-wide: lut3[64] | alias row
 constexpr uint32_t MISC_WORDS = 64;  // per-team scratch words
 constexpr uint32_t MISC_WSUM = 8;    // W + 1 words of scan partials
 constexpr uint32_t MISC_LISTN = 40;  // touched-list length (teams of more than one warp)
-constexpr uint32_t MISC_FIXN = 41;   // number of insertion-label fix-ups queued by the expand stage
+constexpr uint32_t MISC_ALIGN_FLAG = 42;  // two words: "some thread's chunk-edge assumption was wrong" of the alignment rounds
 constexpr uint32_t QUEUE_BYTES = 64 * 4 + 64 * 4;  // per-warp compaction queue: 64 x (u32, u32)
 
 struct SimParams {
@@ -183,8 +184,9 @@ struct SimParams {
     uint32_t cap_list;      // touched-list capacity
     uint32_t slab_bytes;    // bytes of one team workspace
     uint8_t* gws;           // global workspaces (one per CTA) when GWS
-    uint32_t lockstep;      // 1: CTA-wide tickets, teams start their reads together
-    uint8_t* mid;           // PHASE 1 -> 2 records (split kernels), 3 * scratch bytes + 64 per read
+    uint8_t* mid;           // PHASE 1 -> 2 records, 3 * scratch bytes + 64 per read
+    uint8_t* trace;         // PHASE 2: alignment trace words, trace_bytes per team (global, L2-resident)
+    uint64_t trace_bytes;
 };
 
 // Team workspace layout, shared by the host (sizing) and the kernel:
@@ -192,12 +194,10 @@ struct SimParams {
 struct SlabLayout {
     uint32_t off_hist, off_misc, off_queue, off_list, off_key, off_frag, bytes;
 };
-// `lean` (PHASE 2 kernels: expansion + qscores) drops the threshold row and the histogram.
-__host__ __device__ inline SlabLayout slab_layout(int W, uint32_t hist_elem_bytes, uint32_t ncap, uint32_t cap_list,
-                                                  bool lean = false) {
+__host__ __device__ inline SlabLayout slab_layout(int W, uint32_t hist_elem_bytes, uint32_t ncap, uint32_t cap_list) {
     SlabLayout L;
-    L.off_hist = lean ? 0u : 512u;
-    L.off_misc = L.off_hist + (lean ? 0u : 256 * hist_elem_bytes);
+    L.off_hist = 512u;
+    L.off_misc = L.off_hist + 256 * hist_elem_bytes;
     L.off_queue = L.off_misc + MISC_WORDS * 4;
     L.off_list = L.off_queue + (uint32_t)W * QUEUE_BYTES;
     L.off_key = (L.off_list + 4 * cap_list + 15u) & ~15u;
@@ -206,9 +206,21 @@ __host__ __device__ inline SlabLayout slab_layout(int W, uint32_t hist_elem_byte
     return L;
 }
 
+// PHASE 2 (expansion, alignment, qscores) team workspace:
+//   small part: misc[64] u32 | W x 512 bytes (warp compaction queues; the chunk-edge exchange of the alignment)
+//   big part:   frag[ncap + 32] u8 | slen[ncap] u8 (slot lengths) | rb[2 ncap + 32] u8 (read codes, then cigar ops)
+// The big part follows the small one in shared memory, or lives in global memory for the GWS class.
+__host__ __device__ inline uint32_t slab2_small_bytes(int W) { return MISC_WORDS * 4 + (uint32_t)W * QUEUE_BYTES; }
+__host__ __device__ inline uint32_t slab2_big_bytes(uint32_t ncap) { return (4 * ncap + 64 + 15u) & ~15u; }
+// columns of alignment trace one team needs room for (a chunk per thread, at least ALIGN_MIN_CHUNK columns each)
+__host__ __device__ inline uint64_t trace_team_bytes(int W, uint32_t ncap) {
+    const uint64_t cols = (uint64_t)(ncap / (32u * W) + 1 > ALIGN_MIN_CHUNK ? ncap / (32u * W) + 1 : ALIGN_MIN_CHUNK) * 32u * W;
+    return cols * 16;   // (Dg, Pv) as 64-bit words
+}
+
 // shared-memory bytes of the GWS class for the part of the workspace in front of the candidate list
-__host__ __device__ inline uint32_t gws_small_bytes(int W, bool lean) {
-    return (slab_layout(W, 8, 16, 16, lean).off_list + 15u) & ~15u;
+__host__ __device__ inline uint32_t gws_small_bytes(int W) {
+    return (slab_layout(W, 8, 16, 16).off_list + 15u) & ~15u;
 }
 
 // Finds the first of 256 bins at which the cumulative (loss, ins) crosses the target.
@@ -358,24 +370,20 @@ __device__ __forceinline__ uint32_t nz4(uint32_t x, uint32_t mask) {
 }
 
 // ------------------------------------------------------------ simulate one
-// PHASE 0: the whole read in one kernel.  PHASE 1: materialise + error injection, then slot keys and
-// fragment go to the read's `mid` record in global memory.  PHASE 2: loads them back and does
-// expansion + qscores.  Two kernels halve the hot code an SM has to keep in its instruction caches.
-template <int W, bool GWS, int PHASE>
-__device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams& P, uint32_t r, uint8_t* ws, uint8_t* wsl,
-                                              const uint8_t* qcls_s, const uint8_t* lut3, uint32_t phase_threads) {
+// PHASE 1 (inject_read): materialise + error injection, then slot keys and fragment go to the read's
+// `mid` record in global memory.  PHASE 2 (finish_read): expansion, alignment, qscores.  Two kernels
+// halve the hot code an SM has to keep in its instruction caches.
+template <int W, bool GWS>
+__device__ __forceinline__ void inject_read(const Team<W>& tm, const SimParams& P, uint32_t r, uint8_t* ws, uint8_t* wsl,
+                                            const uint8_t* qcls_s) {
     // ws: team workspace (shared memory; global memory for the GWS class).  wsl: where its small, hot part lives
     // (threshold row, histogram, scratch words, compaction rings): == ws, or shared memory for the GWS class.
-    // lockstep mode 2: the teams of the CTA also enter the error, expansion and qscore stages
-    // together (named barrier 15 over the threads of the teams that hold a read)
-    auto phase_sync = [&]() {
-        if (phase_threads) asm volatile("bar.sync 15, %0;" ::"r"(phase_threads) : "memory");
-    };
+    constexpr int PHASE = 1;
     using HistT = typename std::conditional<(GWS || W >= 8), uint64_t, uint32_t>::type;
     constexpr int SIZE = Team<W>::SIZE;
     const DevTables& T = P.T;
     const DevBatch& B = P.B;
-    const SlabLayout LY = slab_layout(W, (uint32_t)sizeof(HistT), P.ncap, P.cap_list, PHASE == 2);
+    const SlabLayout LY = slab_layout(W, (uint32_t)sizeof(HistT), P.ncap, P.cap_list);
 
     uint16_t* T1 = (uint16_t*)wsl;
     HistT* hist = (HistT*)(wsl + LY.off_hist);
@@ -404,7 +412,7 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
     uint32_t status = ST_OK;
     // mid record of the read (PHASE 1 -> 2): keys (n rounded up to 4 slots) | fragment (n + 32 bytes);
     // 3 * scratch bytes + 64 per read always holds it (scratch is 2 L + 32 per read, rounded up to 16)
-    uint4* mid4 = PHASE == 0 ? nullptr : (uint4*)(P.mid + 3 * sbase + 64 * (uint64_t)r);
+    uint4* mid4 = (uint4*)(P.mid + 3 * sbase + 64 * (uint64_t)r);
     const uint32_t key_q = (n + 3) >> 2, frag_q = (n + 32 + 15) >> 4;  // 16-byte units
     if (PHASE != 2) {
     // ---- 1. materialise flank + molecule + flank as fragment codes
@@ -524,9 +532,7 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
     for (uint32_t c = tm.rank; c < Q_CLASSES; c += SIZE) T1[c] = thr_bin[c * THR_PER_CLASS];
     if (tm.rank == 0) {
         misc[MISC_LISTN] = 0;
-        misc[MISC_FIXN] = 0;
     }
-    phase_sync();
 
     // ---- 3. error injection epochs
     uint32_t changed_c = 0;
@@ -762,7 +768,6 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
         }
     }
     tm.sync();
-    phase_sync();
     }  // PHASE != 2
     if (PHASE == 1) {
         const uint4* k4 = (const uint4*)key;
@@ -777,180 +782,341 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
         tm.sync();
         return;
     }
-    if (PHASE == 2) {
-        uint4* k4 = (uint4*)key;
-        uint4* f4 = (uint4*)frag;
-        for (uint32_t x = tm.rank; x < key_q; x += SIZE) k4[x] = mid4[x];
-        for (uint32_t x = tm.rank; x < frag_q; x += SIZE) f4[x] = mid4[key_q + x];
-        status = B.status[r];
-        if (tm.rank == 0) misc[MISC_FIXN] = 0;
+}
+
+// ---- team-parallel alignment (align.cuh has the per-thread pieces and the definition)
+// One chunk of columns per thread; chunk-edge states (forward) and entry cells (traceback) are
+// assumed, compared with what the neighbour produced and redone until they agree.  xch: one 16-byte
+// cell per thread.  Returns false when the traceback left the band (rb is then untouched).
+template <int W, typename BV>
+__device__ __forceinline__ bool align_team_impl(const Team<W>& tm, AlignCtx<BV>& A, uint4* xch, uint32_t* misc, uint32_t* wsum,
+                                                uint32_t& eq_out, uint32_t& cols_out) {
+    uint32_t lanes;
+    align_chunking(A.n, (uint32_t)Team<W>::SIZE, A.chunk, lanes, A.magic);
+    A.stride = (uint32_t)Team<W>::SIZE;
+    const uint32_t l = (uint32_t)tm.rank;
+    const bool active = l < lanes;
+    const uint32_t c0 = 1 + l * A.chunk;
+    const uint32_t c1 = min(A.n + 1, c0 + A.chunk);
+    uint32_t mine = 0;
+    if (active)
+        for (uint32_t j = c0; j < c1; j++) mine += A.slen[j - 1];
+    uint32_t tot;
+    const uint32_t ob = team_excl_scan<W>(tm, mine, wsum, tot);   // read bases in front of the chunk
+    // agreement flags of the rounds (teams of more than one warp): two words, used alternately
+    uint32_t* flag = misc + MISC_ALIGN_FLAG;
+    if (W > 1) {
+        if (tm.rank == 0) flag[0] = flag[1] = 0;
         tm.sync();
     }
+    uint32_t round = 0;
+    auto team_any = [&](bool pred) -> bool {
+        bool any;
+        if (W == 1) {
+            any = __any_sync(0xffffffffu, pred);
+        } else {
+            if (pred) flag[round & 1u] = 1;
+            tm.sync();
+            any = flag[round & 1u] != 0;
+            if (tm.rank == 0) flag[(round + 1) & 1u] = 0;
+        }
+        round++;
+        return any;
+    };
+    // ---- forward
+    {
+        BV P, M, oP = 0, oM = 0;
+        if (l == 0) {
+            P = ~BV(0);
+            M = 0;
+        } else {
+            align_ideal_state<BV>(ob, P, M);
+        }
+        bool need = active;
+        while (true) {
+            if (need) {
+                oP = P;
+                oM = M;
+                align_forward_chunk<BV, true>(A, c0, c1, ob, oP, oM);
+            }
+            xch[l] = make_uint4((uint32_t)oP, (uint32_t)((uint64_t)oP >> 32), (uint32_t)oM, (uint32_t)((uint64_t)oM >> 32));
+            tm.sync();
+            bool ch = false;
+            if (active && l > 0) {
+                const uint4 v = xch[l - 1];
+                const BV nP = (BV)(((uint64_t)v.y << 32) | v.x), nM = (BV)(((uint64_t)v.w << 32) | v.z);
+                ch = nP != P || nM != M;
+                P = nP;
+                M = nM;
+            }
+            need = ch;
+            if (!team_any(ch)) break;
+        }
+    }
+    __threadfence_block();
+    tm.sync();
+    // ---- traceback: exit cells until they agree, then the writing pass
+    uint32_t ei, ej, eo;
+    const bool top = l + 1 == lanes;
+    if (top) {
+        ei = A.m;
+        ej = A.n;
+        eo = A.m;
+    } else {
+        ei = ob + mine;
+        ej = c1 - 1;
+        eo = ob + mine;
+    }
+    bool ok = true;
+    {
+        bool need = active;
+        uint32_t xi = 0, xj = 0, xo = 0;
+        while (true) {
+            if (need) {
+                xi = ei;
+                xj = ej;
+                xo = eo;
+                uint32_t e = 0, c = 0;
+                ok = align_trace_chunk<BV, false>(A, c0, l == 0, top, xi, xj, xo, e, c);
+            }
+            xch[l] = make_uint4(xi, xj, xo, 0u);
+            tm.sync();
+            bool ch = false;
+            if (active && !top) {
+                const uint4 v = xch[l + 1];
+                ch = v.x != ei || v.y != ej || v.z != eo;
+                ei = v.x;
+                ej = v.y;
+                eo = v.z;
+            }
+            need = ch;
+            if (!team_any(ch)) break;
+        }
+    }
+    if (team_any(active && !ok)) return false;
+    uint32_t eq = 0, cols = 0;
+    if (active) align_trace_chunk<BV, true>(A, c0, l == 0, top, ei, ej, eo, eq, cols);
+    eq_out = team_sum<W>(tm, eq, wsum);
+    cols_out = team_sum<W>(tm, cols, wsum);
+    return true;
+}
 
-    // ---- 4. slot contents are the low halves of the keys: content16, or 0xFFFF for an unchanged slot
-    //         (dropped candidates were reset); the high halves are free for the cigar ops from here on
-    const uint16_t* key16 = (const uint16_t*)key;
-    auto slot_len = [&](uint32_t p) -> uint32_t {
-        uint32_t c = key16[2 * p];
+template <int W>
+__device__ __noinline__ bool align_team_wide(const Team<W>& tm, AlignCtx<uint64_t>& A, uint4* xch, uint32_t* misc, uint32_t* wsum,
+                                             uint32_t& eq_out, uint32_t& cols_out) {
+    return align_team_impl<W, uint64_t>(tm, A, xch, misc, wsum, eq_out, cols_out);
+}
+
+// ------------------------------------------------------------- PHASE 2
+// Expansion of the slot contents into the read, alignment of the read back to the fragment
+// (py/tksm_badread.py:613), qscores from the alignment's window cigars (:584-655).
+//   wsl: misc | compaction queues (shared memory);  ws: frag | slen | rb (shared, or global for the GWS class)
+template <int W, bool GWS>
+__device__ __forceinline__ void finish_read(const Team<W>& tm, const SimParams& P, uint32_t r, uint8_t* ws, uint8_t* wsl,
+                                            const uint8_t* lut3, uint8_t* trace) {
+    constexpr int SIZE = Team<W>::SIZE;
+    const DevTables& T = P.T;
+    const DevBatch& B = P.B;
+    uint32_t* misc = (uint32_t*)wsl;
+    uint32_t* wsum = misc + MISC_WSUM;
+    uint8_t* qbase = wsl + MISC_WORDS * 4;
+    uint32_t* wq_a = (uint32_t*)(qbase + (uint32_t)(tm.rank >> 5) * QUEUE_BYTES);
+    uint32_t* wq_b = wq_a + 64;
+    uint8_t* frag = ws;
+    uint8_t* slen = ws + P.ncap + 32;
+    uint8_t* rb = slen + P.ncap;
+    const uint32_t* fragw = (const uint32_t*)frag;
+
+    const uint32_t mol = B.read_mol[r];
+    const uint32_t L = B.mol_raw_len[mol];
+    const uint32_t k = (uint32_t)T.k;
+    const uint32_t n = L + 2 * k;
+    const uint64_t ordinal = B.ordinal_base + r;
+    const uint32_t olo = (uint32_t)ordinal, ohi = (uint32_t)(ordinal >> 32);
+    const uint32_t k0 = T.seed_lo, k1 = T.seed_hi;
+    const uint64_t sbase = B.scr_off[r];
+    const uint32_t scap = (uint32_t)(B.scr_off[r + 1] - sbase);
+    const uint4* mid4 = (const uint4*)(P.mid + 3 * sbase + 64 * (uint64_t)r);
+    const uint32_t key_q = (n + 3) >> 2, frag_q = (n + 32 + 15) >> 4;  // 16-byte units
+    const uint32_t* gkey = (const uint32_t*)mid4;   // slot keys stay in global memory (each is read once or twice)
+    {
+        uint4* f4 = (uint4*)frag;
+        for (uint32_t x = tm.rank; x < frag_q; x += SIZE) f4[x] = mid4[key_q + x];
+    }
+    uint32_t status = B.status[r];
+    auto key_len = [&](uint32_t p) -> uint32_t {
+        const uint32_t c = __ldg(gkey + p) & 0xFFFFu;
         return c == 0xFFFFu ? 1u : content_len(c);
     };
     uint32_t start_trim = 0, end_trim = 0;
     for (uint32_t j = 0; j < k; j++) {
-        start_trim += slot_len(j);
-        end_trim += slot_len(n - k + j);
+        start_trim += key_len(j);
+        end_trim += key_len(n - k + j);
     }
-
-    // ---- 5. slot lengths -> read offsets; write read bases and per-base cigar ops
-    uint8_t* oseq = B.scr_seq + sbase;
-    uint32_t carry = 0;
-    const uint32_t opcap = 2 * n;
-    WarpQueue xq{wq_a, wq_b, 0, 0};
-    auto expand_changed = [&](uint32_t cnt) {
-        uint32_t pv = 0, o = 0;
-        if (!xq.take(cnt, pv, o)) return;
-        const uint32_t p = pv & 0x0FFFFFFFu, dc = pv >> 28;
-        const uint32_t c = key16[2 * p], b = frag[p];
-        const uint32_t len = content_len(c), kind = content_kind(c);
-        const bool body = p >= k && p < n - k;
-        uint32_t eqpos = 0xFFu;  // index inside the slot that aligns to the original base
-        bool first_x = false;
-        if (kind == 1u) eqpos = 0;
-        else if (kind == 2u) eqpos = 1;
-        else if (len >= 2 && b < 4 && content_base(c, 0) == b) eqpos = 0;
-        else if (len >= 2 && b < 4 && content_base(c, len - 1) == b) eqpos = len - 1;
-        else first_x = true;
-        for (uint32_t u = 0; u < len; u++) {
-            const uint32_t j = o + u;
-            uint32_t ch;
-            if (kind == 0u) ch = code_ascii(content_base(c, u));
-            else if (kind == 1u) ch = u == 0 ? code_ascii(b) : code_ascii(content_base(c, 0));
-            else ch = u == 0 ? code_ascii(content_base(c, 0)) : code_ascii(b);
-            if (body) {
-                const uint32_t d = j - start_trim;
-                if (d < scap) oseq[d] = (uint8_t)ch;
-            }
-            const uint32_t op = u == eqpos ? OP_EQ : (first_x && u == 0) ? OP_X : OP_I;
-            if (j < opcap) ops_put(keyb, j, op | ((u == 0 ? dc : 0u) << 2));
-        }
-        // Left-normalised insertion label: a single inserted base that repeats the
-        // base(s) on its left is labelled on the first base of that run, where an aligner that traces
-        // back from the end puts the gap.  Only unchanged slots are walked over, so the ranges of two
-        // fix-ups never overlap; they are applied after the whole read has its ops (the epoch's
-        // touched list is free by now and holds them).
-        if (len == 2 && !first_x) {
-            const uint32_t uI = 1u - eqpos;
-            const uint32_t cI = kind == 0u ? content_base(c, uI) : content_base(c, 0);
-            uint32_t m = 0;
-            bool go = true;
-            if (uI == 1u) {
-                const uint32_t c0 = kind == 0u ? content_base(c, 0) : b;
-                if (c0 == cI) m = 1; else go = false;
-            }
-            if (go)
-                for (uint32_t q = p; q > 0 && m < 255; q--) {
-                    if (frag[q - 1] != cI || key16[2 * (q - 1)] != 0xFFFFu) break;
-                    m++;
-                }
-            if (m) {
-                const uint32_t e = atomicAdd(&misc[MISC_FIXN], 1u);
-                if (e < P.cap_list) list[e] = (o + uI) | (m << 24);
-            }
-        }
-    };
-    for (uint32_t base = 0; base < n; base += 4 * SIZE) {
-        const uint32_t p0 = base + 4 * tm.rank;
-        uint32_t c[4], len[4], s = 0;
-        uint32_t fb4 = 0;
-        if (p0 < n) {
-            const uint4 kq4 = *(const uint4*)(key + p0);  // the key array is padded to a multiple of 4 slots
-            c[0] = kq4.x & 0xFFFFu;
-            c[1] = kq4.y & 0xFFFFu;
-            c[2] = kq4.z & 0xFFFFu;
-            c[3] = kq4.w & 0xFFFFu;
-            fb4 = fragw[p0 >> 2];
-        } else {
-            c[0] = c[1] = c[2] = c[3] = 0;
-        }
-#pragma unroll
-        for (int t = 0; t < 4; t++) {
-            const uint32_t p = p0 + t;
-            len[t] = p < n ? (c[t] == 0xFFFFu ? 1u : content_len(c[t])) : 0u;
-            s += len[t];
-        }
-        uint32_t tot;
-        uint32_t o = carry + team_excl_scan<W>(tm, s, wsum, tot);
-        carry += tot;
-        // deleted slots right before this lane's first slot
-        uint32_t pend = 0;
-        if (p0 < n) {
-            for (uint32_t q = p0; q > 0 && pend < 15; q--) {
-                if (key16[2 * (q - 1)] >> CONTENT_LEN_SHIFT != 0) break;  // 0xFFFF and len >= 1 both stop
-                pend++;
-            }
-        }
-#pragma unroll
-        for (int t = 0; t < 4; t++) {
-            const uint32_t p = p0 + t;
-            bool changed = false;
-            uint32_t qv = 0, qo = 0;
-            if (p < n) {
-                if (len[t] == 0) {
-                    pend = pend < 15 ? pend + 1 : 15;
-                } else {
-                    const uint32_t dc = pend;
-                    pend = 0;
-                    if (c[t] == 0xFFFFu) {
-                        // unchanged slot: one '=' column
-                        if (p >= k && p < n - k) {
-                            const uint32_t d = o - start_trim;
-                            if (d < scap) oseq[d] = code_ascii((fb4 >> (8 * t)) & 0xFFu);
-                        }
-                        if (o < opcap) ops_put(keyb, o, OP_EQ | (dc << 2));
-                    } else {
-                        // changed slot (about one in six): queued, expanded 32 at a time with every lane busy
-                        changed = true;
-                        qv = p | (dc << 28);
-                        qo = o;
-                    }
-                    o += len[t];
-                }
-            }
-            xq.push(changed, qv, qo);
-            const uint32_t cnt = xq.ready(false);
-            if (cnt) expand_changed(cnt);
-        }
-    }
-    for (uint32_t cnt; (cnt = xq.ready(true)) != 0;) expand_changed(cnt);
-    const uint32_t Ttot = carry;
-    const uint32_t Lp = Ttot - start_trim - end_trim;
     tm.sync();
-    {
-        const uint32_t nfix = misc[MISC_FIXN];
-        if (nfix > P.cap_list) {
-            status |= ST_FIXUP_OVERFLOW;  // never seen: would need 40 % of the slots to be such insertions
-        } else if (Ttot <= opcap) {
-            for (uint32_t e = tm.rank; e < nfix; e += SIZE) {
-                const uint32_t v = list[e], jI = v & 0xFFFFFFu, m = v >> 24;
-                ops_put(keyb, jI, OP_EQ);
-                ops_put(keyb, jI - m, OP_I | (ops_at(keyb, jI - m) & ~3u));
+
+    // ---- slot lengths -> read offsets; read bases into rb (codes) and the scratch arena (text);
+    //      `ops_mode`: instead, the cigar ops of the edit script itself (used when the alignment fails)
+    uint8_t* oseq = B.scr_seq + sbase;
+    const uint32_t rbcap = 2 * n;
+    uint32_t Ttot = 0;
+    auto expand_pass = [&](const bool ops_mode) {
+        uint32_t carry = 0;
+        WarpQueue xq{wq_a, wq_b, 0, 0};
+        auto expand_changed = [&](uint32_t cnt) {
+            uint32_t pv = 0, o = 0;
+            if (!xq.take(cnt, pv, o)) return;
+            const uint32_t p = pv & 0x0FFFFFFFu, dc = pv >> 28;
+            const uint32_t c = __ldg(gkey + p) & 0xFFFFu, b = frag[p];
+            const uint32_t len = content_len(c), kind = content_kind(c);
+            const bool body = p >= k && p < n - k;
+            uint32_t eqpos = 0xFFu;  // index inside the slot that aligns to the original base
+            bool first_x = false;
+            if (kind == 1u) eqpos = 0;
+            else if (kind == 2u) eqpos = 1;
+            else if (len >= 2 && b < 4 && content_base(c, 0) == b) eqpos = 0;
+            else if (len >= 2 && b < 4 && content_base(c, len - 1) == b) eqpos = len - 1;
+            else first_x = true;
+            for (uint32_t u = 0; u < len; u++) {
+                const uint32_t j = o + u;
+                uint32_t code;
+                if (kind == 0u) code = content_base(c, u);
+                else if (kind == 1u) code = u == 0 ? b : content_base(c, 0);
+                else code = u == 0 ? content_base(c, 0) : b;
+                if (ops_mode) {
+                    const uint32_t op = u == eqpos ? OP_EQ : (first_x && u == 0) ? OP_X : OP_I;
+                    if (j < rbcap) rb[j] = (uint8_t)(op | ((u == 0 ? dc : 0u) << 2));
+                } else {
+                    if (j < rbcap) rb[j] = (uint8_t)code;
+                    if (body) {
+                        const uint32_t d = j - start_trim;
+                        if (d < scap) oseq[d] = code_ascii(code);
+                    }
+                }
+            }
+        };
+        for (uint32_t base = 0; base < n; base += 4 * SIZE) {
+            const uint32_t p0 = base + 4 * tm.rank;
+            uint32_t c[4], len[4], s = 0;
+            uint32_t fb4 = 0;
+            if (p0 < n) {
+                const uint4 kq4 = __ldg((const uint4*)(gkey + p0));  // the key array is padded to a multiple of 4 slots
+                c[0] = kq4.x & 0xFFFFu;
+                c[1] = kq4.y & 0xFFFFu;
+                c[2] = kq4.z & 0xFFFFu;
+                c[3] = kq4.w & 0xFFFFu;
+                fb4 = fragw[p0 >> 2];
+            } else {
+                c[0] = c[1] = c[2] = c[3] = 0;
+            }
+#pragma unroll
+            for (int t = 0; t < 4; t++) {
+                const uint32_t p = p0 + t;
+                len[t] = p < n ? (c[t] == 0xFFFFu ? 1u : content_len(c[t])) : 0u;
+                s += len[t];
+            }
+            if (!ops_mode && p0 < n) *(uint32_t*)(slen + p0) = len[0] | (len[1] << 8) | (len[2] << 16) | (len[3] << 24);
+            uint32_t tot;
+            uint32_t o = carry + team_excl_scan<W>(tm, s, wsum, tot);
+            carry += tot;
+            // deleted slots right before this lane's first slot (only the edit-script cigar needs them)
+            uint32_t pend = 0;
+            if (ops_mode && p0 < n) {
+                for (uint32_t q = p0; q > 0 && pend < 15; q--) {
+                    if ((__ldg(gkey + q - 1) & 0xFFFFu) >> CONTENT_LEN_SHIFT != 0) break;  // 0xFFFF and len >= 1 both stop
+                    pend++;
+                }
+            }
+#pragma unroll
+            for (int t = 0; t < 4; t++) {
+                const uint32_t p = p0 + t;
+                bool changed = false;
+                uint32_t qv = 0, qo = 0;
+                if (p < n) {
+                    if (len[t] == 0) {
+                        pend = pend < 15 ? pend + 1 : 15;
+                    } else {
+                        const uint32_t dc = pend;
+                        pend = 0;
+                        if (c[t] == 0xFFFFu) {
+                            // unchanged slot: one '=' column
+                            const uint32_t code = (fb4 >> (8 * t)) & 0xFFu;
+                            if (ops_mode) {
+                                if (o < rbcap) rb[o] = (uint8_t)(OP_EQ | (dc << 2));
+                            } else {
+                                if (o < rbcap) rb[o] = (uint8_t)code;
+                                if (p >= k && p < n - k) {
+                                    const uint32_t d = o - start_trim;
+                                    if (d < scap) oseq[d] = code_ascii(code);
+                                }
+                            }
+                        } else {
+                            // changed slot (about one in six): queued, expanded 32 at a time with every lane busy
+                            changed = true;
+                            qv = p | (dc << 28);
+                            qo = o;
+                        }
+                        o += len[t];
+                    }
+                }
+                xq.push(changed, qv, qo);
+                const uint32_t cnt = xq.ready(false);
+                if (cnt) expand_changed(cnt);
             }
         }
-    }
-    if (Ttot > opcap) status |= ST_OPS_OVERFLOW;
+        for (uint32_t cnt; (cnt = xq.ready(true)) != 0;) expand_changed(cnt);
+        Ttot = carry;
+        tm.sync();
+    };
+    expand_pass(false);
+    const uint32_t Lp = Ttot - start_trim - end_trim;
+    if (Ttot > rbcap) status |= ST_OPS_OVERFLOW;
     if (Lp > scap) status |= ST_SCRATCH_OVERFLOW;
     if (tm.rank == 0) {
         B.read_len[r] = Lp;
-        if (PHASE == 0) {
-            B.ident_num[r] = n - loss_c;
-            B.ident_den[r] = n + ins_c;
-        }
         B.status[r] = status;
     }
-    tm.sync();
-    phase_sync();
 
-    // ---- 6. qscores for the read bases that survive trimming: 8 bases per Philox call
+    // ---- qscores for the read bases that survive trimming
     if ((P.flags & RUN_QUAL) && !(status & (ST_OPS_OVERFLOW | ST_SCRATCH_OVERFLOW))) {
+        // the read is aligned back to the fragment; the ops of the alignment replace the read codes in rb
+        {
+            uint32_t eq = 0, cols = 0;
+            bool ok;
+            {
+                AlignCtx<uint32_t> A;
+                A.frag = frag;
+                A.slen = slen;
+                A.rb = rb;
+                A.trace = (uint32_t*)trace;
+                A.n = n;
+                A.m = Ttot;
+                ok = align_team_impl<W, uint32_t>(tm, A, (uint4*)qbase, misc, wsum, eq, cols);
+            }
+            if (!ok) {
+                AlignCtx<uint64_t> A;
+                A.frag = frag;
+                A.slen = slen;
+                A.rb = rb;
+                A.trace = (uint64_t*)trace;
+                A.n = n;
+                A.m = Ttot;
+                tm.sync();
+                ok = align_team_wide<W>(tm, A, (uint4*)qbase, misc, wsum, eq, cols);
+            }
+            tm.sync();
+            if (ok) {
+                if (tm.rank == 0) {
+                    B.ident_num[r] = eq;
+                    B.ident_den[r] = cols | IDENT_MEASURED;
+                }
+            } else {
+                // never seen at the shipped models' usual identities: the edit script itself is the cigar then
+                status |= ST_BAND;
+                if (tm.rank == 0) B.status[r] = status;
+                expand_pass(true);
+            }
+        }
         uint8_t* oq = B.scr_qual + sbase;
         const int margin = (T.kq - 1) >> 1;
         const uint32_t jb = start_trim, je = Ttot - end_trim;
@@ -973,7 +1139,7 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
             t0 = max(t0, max(4 - (int)j, (int)j + 4 - (int)(Ttot - 1)));
             uint32_t ops18 = 0, gaps = 0;
             for (int i = t0; i <= 8 - t0; i++) {
-                const uint32_t o = ops_at(keyb, j + (uint32_t)i - 4u);
+                const uint32_t o = rb[j + (uint32_t)i - 4u];
                 ops18 |= (o & 3u) << (2 * i);
                 if (i > t0) gaps |= (o >> 2) << (4 * (i - 1));
             }
@@ -991,12 +1157,11 @@ __device__ __forceinline__ void simulate_read(const Team<W>& tm, const SimParams
             uint32_t x0 = 0, x1 = 0, x2 = 0, x3 = 0, opsP = 0, dmask = 0;
             if (live) ur = philox4x32_10(g, TAG_QUAL, olo, ohi, k0, k1);
             if (fast) {
-                const uint2* kp = (const uint2*)(key + ((j0 - 4) >> 1));
-                const uint2 a = kp[0], b = kp[1], c = kp[2], d = kp[3];
-                x0 = __byte_perm(a.x, a.y, 0x7632);
-                x1 = __byte_perm(b.x, b.y, 0x7632);
-                x2 = __byte_perm(c.x, c.y, 0x7632);
-                x3 = __byte_perm(d.x, d.y, 0x7632);
+                const uint32_t* kp = (const uint32_t*)(rb + (j0 - 4));   // j0 is a multiple of 8
+                x0 = kp[0];
+                x1 = kp[1];
+                x2 = kp[2];
+                x3 = kp[3];
                 opsP = pack4(x0) | (pack4(x1) << 8) | (pack4(x2) << 16) | (pack4(x3) << 24);
                 dmask = nz4(x0, 0x3C3C3C3Cu) | (nz4(x1, 0x3C3C3C3Cu) << 4) | (nz4(x2, 0x3C3C3C3Cu) << 8) |
                         (nz4(x3, 0x3C3C3C3Cu) << 12);
@@ -1079,47 +1244,49 @@ __global__ void __launch_bounds__(PHASE == 2 ? 1024 : SIM_THREADS, 1) simulate_k
     if (threadIdx.x < 64) lut3[threadIdx.x] = (uint8_t)((threadIdx.x & 3) + 3 * ((threadIdx.x >> 2) & 3) + 9 * (threadIdx.x >> 4));
     // the window of nine matches is by far the most frequent one: its alias row lives in shared memory
     uint32_t* q0row = (uint32_t*)(lut3 + 64);
-    if (P.T.q_t9 && threadIdx.x < 128) {
+    if (PHASE == 2 && P.T.q_t9 && threadIdx.x < 128) {
         const uint32_t e0 = P.T.q_t9[0];
         if (threadIdx.x < (1u << (e0 & 7u))) q0row[threadIdx.x] = P.T.q_alias[(e0 >> 3) + threadIdx.x];
     }
     __syncthreads();
-    // GWS class: candidate list, slot keys and fragment of the (long) read in global memory, the small hot part
-    // of the workspace in shared memory
+    // GWS class: the large arrays of the (long) read in global memory, the small hot part of the workspace in
+    // shared memory.  P.slab_bytes: bytes of one team workspace (shared classes) / of one global workspace (GWS).
+    uint8_t* pool = smem + qcls_bytes + SIM_FIXED_SMEM;
     uint8_t *ws, *wsl;
-    const uint32_t small_bytes = GWS ? gws_small_bytes(W, PHASE == 2) : 0u;
-    if (GWS) {
-        ws = P.gws + (size_t)blockIdx.x * P.slab_bytes;
-        wsl = smem + qcls_bytes + SIM_FIXED_SMEM;
-    } else {
-        ws = wsl = smem + qcls_bytes + SIM_FIXED_SMEM + (size_t)tm.id * P.slab_bytes;
-    }
-    uint32_t* ticket = (uint32_t*)(smem + qcls_bytes + SIM_FIXED_SMEM + (GWS ? (size_t)small_bytes : (size_t)TEAMS * P.slab_bytes)) + tm.id;
-    if (P.lockstep) {
-        // The CTA takes TEAMS consecutive work items (near-equal lengths: the list is sorted) and its
-        // teams start each of them together, so the warps of a scheduler walk the same code at about
-        // the same time and share the instruction cache lines.
-        uint32_t* cta_ticket = ticket - tm.id;
-        while (true) {
-            if (threadIdx.x == 0) *cta_ticket = atomicAdd(P.counter, (uint32_t)TEAMS);
-            __syncthreads();
-            const uint32_t wi = *cta_ticket + (uint32_t)tm.id;
-            __syncthreads();
-            const uint32_t base = wi - (uint32_t)tm.id;
-            if (base >= P.n_work) break;
-            const uint32_t nact = min((uint32_t)TEAMS, P.n_work - base);
-            if (wi < P.n_work)
-                simulate_read<W, GWS, PHASE>(tm, P, P.work[wi], ws, wsl, qcls_s, lut3, P.lockstep >= 2 ? nact * (uint32_t)(W * 32) : 0u);
+    size_t pool_used;
+    if (PHASE == 2) {
+        const uint32_t small = slab2_small_bytes(W);
+        if (GWS) {
+            wsl = pool;
+            ws = P.gws + (size_t)blockIdx.x * P.slab_bytes;
+            pool_used = small;
+        } else {
+            wsl = pool + (size_t)tm.id * P.slab_bytes;
+            ws = wsl + small;
+            pool_used = (size_t)TEAMS * P.slab_bytes;
         }
-        return;
+    } else {
+        if (GWS) {
+            wsl = pool;
+            ws = P.gws + (size_t)blockIdx.x * P.slab_bytes;
+            pool_used = gws_small_bytes(W);
+        } else {
+            ws = wsl = pool + (size_t)tm.id * P.slab_bytes;
+            pool_used = (size_t)TEAMS * P.slab_bytes;
+        }
     }
+    uint32_t* ticket = (uint32_t*)(pool + pool_used) + tm.id;
+    uint8_t* trace = PHASE == 2 ? P.trace + ((size_t)blockIdx.x * TEAMS + tm.id) * P.trace_bytes : nullptr;
     while (true) {
         if (tm.rank == 0) *ticket = atomicAdd(P.counter, 1u);
         tm.sync();
         const uint32_t wi = *ticket;
         tm.sync();
         if (wi >= P.n_work) break;
-        simulate_read<W, GWS, PHASE>(tm, P, P.work[wi], ws, wsl, qcls_s, lut3, 0u);
+        if (PHASE == 2)
+            finish_read<W, GWS>(tm, P, P.work[wi], ws, wsl, lut3, trace);
+        else
+            inject_read<W, GWS>(tm, P, P.work[wi], ws, wsl, qcls_s);
     }
 }
 
@@ -1257,12 +1424,20 @@ __device__ __forceinline__ uint32_t pct_hundredths(uint32_t num, uint32_t den, d
 
 __device__ __forceinline__ uint32_t pct_len(uint32_t h) { return h >= 10000 ? 6u : h >= 1000 ? 5u : 4u; }
 
+// read_identity of read r in hundredths of a percent: the identity of its alignment when it was aligned
+// (py/tksm_badread.py:613-614), else the calibrated edit-script estimate (:443-444)
+template <typename FP>
+__device__ __forceinline__ uint32_t read_pct(const FP& F, uint32_t r) {
+    const uint32_t den = F.ident_den[r];
+    return pct_hundredths(F.ident_num[r], den & ~IDENT_MEASURED, (den & IDENT_MEASURED) ? 0.0 : F.kappa);
+}
+
 __device__ __forceinline__ uint32_t record_len(const FmtParams& F, uint32_t r) {
     const uint32_t mol = F.read_mol[r];
     // error_free_length = len(raw_seq), the molecule without its tail (py/sequence.py:253)
     const uint32_t L = F.mol_raw_len[mol] - (F.mol_tail_len ? F.mol_tail_len[mol] : 0u);
     const uint32_t Lp = F.read_len ? F.read_len[r] : L;
-    const uint32_t h = F.read_len ? pct_hundredths(F.ident_num[r], F.ident_den[r], F.kappa) : 10000u;
+    const uint32_t h = F.read_len ? read_pct(F, r) : 10000u;
     const uint32_t idl = F.mol_id_begin[mol + 1] - F.mol_id_begin[mol];
     // "@" uuid " length=" Lp " error_free_length=" L " read_identity=" pct "% molecule_id=" id "\n" seq "\n"
     uint32_t len = 1 + 36 + 8 + dec_digits(Lp) + 19 + dec_digits(L) + 15 + pct_len(h) + 14 + idl + 1 + Lp + 1;
@@ -1426,7 +1601,7 @@ __global__ void __launch_bounds__(256) format_kernel(const FmtParams F) {
             puts_(" error_free_length=");
             putu(L);
             puts_(" read_identity=");
-            uint32_t h = F.read_len ? pct_hundredths(F.ident_num[r], F.ident_den[r], F.kappa) : 10000u;
+            uint32_t h = F.read_len ? read_pct(F, r) : 10000u;
             putu(h / 100);
             hdr[p++] = '.';
             hdr[p++] = (uint8_t)('0' + (h / 10) % 10);
