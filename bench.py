@@ -254,6 +254,7 @@ def main():
                     "note": "tksm_seq_simulate_text: MDF text in host memory -> parse (host threads) -> H2D -> kernels -> "
                             "D2H of the FASTQ bytes into a page-locked host buffer, chunks pipelined"},
             "gpu_launches": launches,
+            "status_or": int(st.get("status_or", 0)),   # OR of the per-read status words of the last step (8 = some read's qscores follow the edit script: alignment band left)
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          # dram__bytes_read.sum + dram__bytes_write.sum over the 16 launches of one step of this
                          # workload, one ncu capture (profiles/r1h_dram_per_launch.txt); other sizes: not captured

@@ -17,55 +17,49 @@ using namespace tk;
 template <typename BV>
 static int run(const uint8_t* frag, const uint8_t* slen, uint8_t* rb, uint32_t n, uint32_t m, uint32_t threads,
                uint32_t* eq_out, uint32_t* cols_out, uint32_t* rounds) {
-    const uint32_t warm = getenv("ALIGN_WARM") ? (uint32_t)atoi(getenv("ALIGN_WARM")) : ALIGN_WARMUP;
     AlignCtx<BV> A;
     uint32_t lanes;
-    align_chunking(n, threads, A.chunk, lanes, A.magic);
+    align_chunking(n, threads, A.chunk, lanes);
     A.frag = frag;
     A.slen = slen;
     A.rb = rb;
     A.n = n;
     A.m = m;
     A.stride = threads;
-    std::vector<BV> trace((size_t)A.chunk * threads * 2 + 2, 0);
+    // the trace array is reused from read to read on the device: start from garbage
+    std::vector<AlignCell<BV>> trace((size_t)A.chunk * threads + 1);
+    memset((void*)trace.data(), 0x5A, trace.size() * sizeof(AlignCell<BV>));
     A.trace = trace.data();
-    std::vector<uint32_t> c0(lanes), c1(lanes), ob(lanes + 1);
+    A.cells = (uint32_t)trace.size();
+    uint32_t oob = 0;
+    A.oob = &oob;
+    std::vector<AlignLane<BV>> ln(lanes);
     uint32_t o = 0;
     for (uint32_t l = 0; l < lanes; l++) {
-        c0[l] = 1 + l * A.chunk;
-        c1[l] = c0[l] + A.chunk < n + 1 ? c0[l] + A.chunk : n + 1;
-        ob[l] = o;
-        for (uint32_t j = c0[l]; j < c1[l]; j++) o += slen[j - 1];
+        ln[l].c0 = 1 + l * A.chunk;
+        ln[l].c1 = ln[l].c0 + A.chunk < n + 1 ? ln[l].c0 + A.chunk : n + 1;
+        ln[l].ob = o;
+        for (uint32_t j = ln[l].c0; j < ln[l].c1; j++) o += slen[j - 1];
     }
-    ob[lanes] = o;
     if (o != m) return -1;
+    for (uint32_t l = 0; l < lanes; l++) align_lane_init(A, ln[l]);
     // forward fixpoint
     std::vector<BV> inP(lanes), inM(lanes), outP(lanes), outM(lanes);
     std::vector<char> need(lanes, 1);
     for (uint32_t l = 0; l < lanes; l++) {
         if (l == 0) { inP[l] = ~BV(0); inM[l] = 0; }
-        else {
-            // warm-up: the state at the chunk edge is guessed by running a few columns up to it from an
-            // undisturbed diagonal
-            const uint32_t wu = c0[l] - 1 < warm ? c0[l] - 1 : warm;
-            uint32_t ow = ob[l];
-            for (uint32_t j = c0[l] - wu; j < c0[l]; j++) ow -= slen[j - 1];
-            BV P, M;
-            if (c0[l] - wu == 1) { P = ~BV(0); M = 0; }
-            else align_ideal_state<BV>(ow, P, M);
-            if (wu) align_forward_chunk<BV, false>(A, c0[l] - wu, c0[l], ow, P, M);
-            inP[l] = P; inM[l] = M;
-        }
+        else align_ideal_state<BV>(ln[l].ob, inP[l], inM[l]);
     }
     rounds[0] = 0;
     for (;;) {
-        rounds[0]++;
         for (uint32_t l = 0; l < lanes; l++)
             if (need[l]) {
                 BV P = inP[l], M = inM[l];
-                align_forward_chunk(A, c0[l], c1[l], ob[l], P, M);
-                outP[l] = P; outM[l] = M;
+                const bool conv = rounds[0] == 0 ? align_forward_chunk<BV, false>(A, ln[l], P, M)
+                                                 : align_forward_chunk<BV, true>(A, ln[l], P, M);
+                if (!conv) { outP[l] = P; outM[l] = M; }
             }
+        rounds[0]++;
         bool any = false;
         for (uint32_t l = lanes; l-- > 1;) {
             need[l] = outP[l - 1] != inP[l] || outM[l - 1] != inM[l];
@@ -78,21 +72,30 @@ static int run(const uint8_t* frag, const uint8_t* slen, uint8_t* rb, uint32_t n
     struct Cell { uint32_t i, j, o; };
     std::vector<Cell> ent(lanes), ext(lanes);
     std::vector<char> ok(lanes, 1);
+    std::vector<uint32_t> tag(lanes, 1), emin(lanes, 1);
     for (uint32_t l = 0; l < lanes; l++) {
         if (l == lanes - 1) ent[l] = {m, n, m};
-        else ent[l] = {ob[l + 1], c1[l] - 1, ob[l + 1]};
+        else ent[l] = {ln[l + 1].ob, ln[l].c1 - 1, ln[l + 1].ob};
         need[l] = 1;
     }
     rounds[1] = 0;
     for (;;) {
-        rounds[1]++;
         for (uint32_t l = 0; l < lanes; l++)
             if (need[l]) {
                 Cell c = ent[l];
                 uint32_t e = 0, k = 0;
-                ok[l] = align_trace_chunk<BV, false>(A, c0[l], l == 0, l == lanes - 1, c.i, c.j, c.o, e, k);
-                ext[l] = c;
+                bool merged = false;
+                if (rounds[1] == 0) {
+                    ok[l] = align_trace_chunk<BV, TRACE_FIRST>(A, ln[l].c0, l == 0, l == lanes - 1, c.i, c.j, c.o, e, k, merged, 1, 1);
+                    ext[l] = c;
+                } else {
+                    tag[l]++;
+                    const bool r = align_trace_chunk<BV, TRACE_REDO>(A, ln[l].c0, l == 0, l == lanes - 1, c.i, c.j, c.o, e, k, merged,
+                                                                     tag[l], emin[l]);
+                    if (!merged) { ok[l] = r; ext[l] = c; emin[l] = tag[l]; }
+                }
             }
+        rounds[1]++;
         bool any = false;
         for (uint32_t l = 0; l + 1 < lanes; l++) {
             const Cell& x = ext[l + 1];
@@ -107,11 +110,12 @@ static int run(const uint8_t* frag, const uint8_t* slen, uint8_t* rb, uint32_t n
     uint32_t eq = 0, cols = 0;
     for (uint32_t l = 0; l < lanes; l++) {
         Cell c = ent[l];
-        if (!align_trace_chunk<BV, true>(A, c0[l], l == 0, l == lanes - 1, c.i, c.j, c.o, eq, cols)) return 1;
+        bool merged;
+        if (!align_trace_chunk<BV, TRACE_WRITE>(A, ln[l].c0, l == 0, l == lanes - 1, c.i, c.j, c.o, eq, cols, merged)) return 1;
     }
     *eq_out = eq;
     *cols_out = cols;
-    return 0;
+    return oob ? -2 : 0;
 }
 
 // wide: 0 = 32-bit band, 1 = 64-bit band.  Returns 0 ok, 1 band left, -1 inconsistent input.

@@ -15,22 +15,25 @@
 //   inside the band, otherwise the alignment fails and the caller retries with 64-bit words.
 //
 // Columns are computed with Myers' bit-vector recurrence (vertical deltas Pv / Mv of the band in
-// one machine word, horizontal input +1 at the band top); per column the word pair
-// (Dg, Pv) is kept: Dg = "the diagonal move is optimal", Pv = "the move from above is optimal",
-// which is all the traceback needs.  oracle/twin.c: twin_bnw is the plain integer form of the
-// same definition; tests compare them cell path by cell path.
+// one machine word, horizontal input +1 at the band top).  Per column a cell {Dg, Pv, Mv, arr} is
+// kept: Dg = "the diagonal move is optimal", Pv = "the move from above is optimal" (all the
+// traceback needs), Mv to recognise a recomputed column that has come back to the known state,
+// arr = row at which the last traceback first started a read base in this column.
+// oracle/twin.c: twin_bnw is the plain integer form of the same definition; tests compare them.
 //
 // Parallelism: the columns of a read are cut into one chunk per thread of the team.  A chunk
 // needs the band state at its left edge, which only the chunk before it can tell, so every thread
-// first assumes the state of an undisturbed diagonal, and chunks whose assumption turns out wrong
-// (it is compared with what the neighbour actually produced) are redone until nothing changes:
-// lane 0 starts from the true boundary, so after r rounds the first r chunks are exact and the
-// fixpoint is the sequential result.  The traceback is parallelised the same way from the other
-// end (entry cell assumed on the script path, corrected by the neighbour's exit cell).
+// first assumes the state of an undisturbed diagonal; chunks whose assumption turns out wrong (it
+// is compared with what the neighbour actually produced) are redone, only as far as their state
+// differs from what they had computed before, until nothing changes.  Lane 0 starts from the true
+// boundary, so after r rounds the first r chunks are exact and the fixpoint is the sequential
+// result.  The traceback is parallelised the same way from the other end (entry cell assumed on
+// the script path, corrected by the neighbour's exit cell, redone until it meets its old path).
 //
 // The per-thread functions are plain C++ (no intrinsics) so that tests/ can compile them for the
 // host and run the same chunking sequentially against the twin.
 #pragma once
+#include <cstddef>
 #include <cstdint>
 
 #ifndef TK_HD
@@ -46,34 +49,43 @@ namespace tk {
 constexpr uint32_t ALIGN_MARGIN = 4;      // cells the traceback keeps away from the band edges
 constexpr uint32_t ALIGN_MIN_CHUNK = 16;  // columns per thread at least
 constexpr uint32_t ALIGN_DC_CAP = 15;     // D columns recorded in front of one read base
-constexpr uint32_t ALIGN_WARMUP = 12;     // columns a thread runs ahead of its chunk to guess the state at its edge
+constexpr uint32_t ALIGN_CELL_BYTES = 32; // trace bytes per column the caller provides (a cell of 64-bit words)
+constexpr uint32_t ALIGN_WIDE_FROM = 8192; // fragments with more slots start with the 64-bit band
+constexpr uint32_t ALIGN_ROW_BITS = 18;   // arr = walk tag << 18 | row; rows stay below 2^18 - 1 (reads of up to 2 x 131 070 bases)
 
 enum : uint32_t { MV_DIAG = 0, MV_UP = 1, MV_LEFT = 2, MV_OUT = 3 };
+
+template <typename BV>
+struct alignas(4 * sizeof(BV)) AlignCell {
+    BV dg, pv, mv, arr;
+};
 
 template <typename BV>
 struct AlignCtx {
     const uint8_t* frag;   // n fragment codes (0..3, or the raw byte)
     const uint8_t* slen;   // n slot lengths of the edit script
     uint8_t* rb;           // m read codes; the traceback replaces them by op | dcount << 2
-    BV* trace;             // 2 words per column: [(within * stride + owner) * 2 + {0: Dg, 1: Pv}]
+    AlignCell<BV>* trace;  // cell of column j at [within * stride + owner], (owner, within) = divmod(j - 1, chunk)
     uint32_t n, m;
     uint32_t chunk;        // columns per thread
     uint32_t stride;       // threads of the team
-    uint32_t magic;        // floor(2^32 / chunk) + 1: (x * magic) >> 32 == x / chunk for x * chunk < 2^32
+    uint32_t cells;        // capacity of the trace array (cells)
+    uint32_t* oob;         // set when an access would have left the trace array (never expected; the access is skipped)
 };
+
+// TK_ALIGN_PARANOID: every index is checked; the first violation is recorded in A.oob[1..4] (site, index, limit, j)
+// and the access is redirected to element 0.
+#ifdef TK_ALIGN_PARANOID
+#define TK_AIDX(A, site, idx, lim, jj) \
+    (((uint32_t)(idx) < (uint32_t)(lim)) ? (uint32_t)(idx) : ((A).oob[0] ? 0u : ((A).oob[0] = 1, (A).oob[1] = (site), (A).oob[2] = (uint32_t)(idx), (A).oob[3] = (uint32_t)(lim), (A).oob[4] = (uint32_t)(jj), 0u)))
+#else
+#define TK_AIDX(A, site, idx, lim, jj) (idx)
+#endif
 
 template <typename BV>
 TK_HD uint32_t align_lo(uint32_t o) {
     constexpr uint32_t H = 4 * sizeof(BV);
     return o > H + 1 ? o - H : 1u;
-}
-
-template <typename BV>
-TK_HD size_t align_trace_index(const AlignCtx<BV>& A, uint32_t j) {
-    const uint32_t jj = j - 1;
-    const uint32_t owner = (uint32_t)(((uint64_t)jj * A.magic) >> 32);
-    const uint32_t within = jj - owner * A.chunk;
-    return ((size_t)within * A.stride + owner) * 2;
 }
 
 // State of an undisturbed diagonal through (o, .): values grow by one per row away from it.
@@ -86,64 +98,92 @@ TK_HD void align_ideal_state(uint32_t o, BV& Pv, BV& Mv) {
     Pv = ~Mv;
 }
 
-// Columns [c0, c1) of the band.  In: (Pv, Mv) of column c0 - 1 (o_prev read bases in front of it);
-// out: the state of column c1 - 1.  STORE: writes the (Dg, Pv) words of its columns.
-template <typename BV, bool STORE = true>
-TK_HD void align_forward_chunk(const AlignCtx<BV>& A, uint32_t c0, uint32_t c1, uint32_t o_prev, BV& Pv, BV& Mv) {
-    constexpr uint32_t BW = 8 * sizeof(BV);
-    uint32_t lo_prev = align_lo<BV>(o_prev);
-    // match masks of the band rows for the four bases: bit b <-> row lo + b <-> read base lo + b - 1
-    BV M0 = 0, M1 = 0, M2 = 0, M3 = 0;
-    for (uint32_t b = 0; b < BW; b++) {
-        const uint32_t row = lo_prev + b;
-        if (row > A.m) break;
-        const uint32_t c = A.rb[row - 1];
-        const BV bit = BV(1) << b;
-        M0 |= c == 0 ? bit : BV(0);
-        M1 |= c == 1 ? bit : BV(0);
-        M2 |= c == 2 ? bit : BV(0);
-        M3 |= c == 3 ? bit : BV(0);
+// The read bases of the band rows as bit planes: bit b <-> row lo + b <-> read base lo + b - 1.
+template <typename BV>
+struct AlignPlanes {
+    BV b0, b1, v, np;   // code bit 0, code bit 1, "is A/C/G/T", "is N"
+    TK_HD void put(uint32_t c, uint32_t pos) {
+        b0 |= BV(c & 1u) << pos;
+        b1 |= BV((c >> 1) & 1u) << pos;
+        v |= BV(c < 4u) << pos;
+        np |= BV(c == 78u) << pos;
     }
-    size_t ti = align_trace_index(A, c0);
-    for (uint32_t j = c0; j < c1; j++) {
-        const uint32_t o = o_prev + A.slen[j - 1];
+};
+
+// One thread's share of the forward pass: columns [c0, c1), ob read bases in front of column c0 - 1's slot.
+template <typename BV>
+struct AlignLane {
+    uint32_t c0, c1, ob;
+    AlignPlanes<BV> pl;   // planes of the band of column c0 - 1 (they depend on the read only, not on the round)
+};
+
+template <typename BV>
+TK_HD void align_lane_init(const AlignCtx<BV>& A, AlignLane<BV>& Ln) {
+    constexpr uint32_t BW = 8 * sizeof(BV);
+    const uint32_t lo = align_lo<BV>(Ln.ob);
+    Ln.pl.b0 = Ln.pl.b1 = Ln.pl.v = Ln.pl.np = 0;
+    for (uint32_t b = 0; b < BW; b++) {
+        const uint32_t row = lo + b;
+        if (row > A.m) break;
+        Ln.pl.put(A.rb[TK_AIDX(A, 1, row - 1, A.m, Ln.c0)], b);
+    }
+}
+
+// Columns [c0, c1) of the band.  In: (Pv, Mv) of column c0 - 1; out: the state of column c1 - 1.
+// RECHECK: the columns have been computed before from another input state; returns true (and leaves
+// Pv / Mv alone) as soon as a column ends in the state stored for it, since everything after it is
+// then what it was.
+template <typename BV, bool RECHECK>
+TK_HD bool align_forward_chunk(const AlignCtx<BV>& A, const AlignLane<BV>& Ln, BV& Pv_io, BV& Mv_io) {
+    constexpr uint32_t BW = 8 * sizeof(BV);
+    BV Pv = Pv_io, Mv = Mv_io;
+    AlignPlanes<BV> pl = Ln.pl;
+    uint32_t o_prev = Ln.ob;
+    uint32_t lo_prev = align_lo<BV>(o_prev);
+    AlignCell<BV>* cell = A.trace + (Ln.c0 - 1) / A.chunk;   // first column of the chunk: within = 0, owner = the thread
+    for (uint32_t j = Ln.c0; j < Ln.c1; j++, cell += A.stride) {
+        if ((size_t)(cell - A.trace) >= A.cells) {
+            *A.oob = 1;
+            break;
+        }
+        BV old_pv = 0, old_mv = 0;
+        if (RECHECK) {
+            old_pv = cell->pv;
+            old_mv = cell->mv;
+        }
+        const uint32_t o = o_prev + A.slen[TK_AIDX(A, 2, j - 1, A.n, j)];
         const uint32_t lo = align_lo<BV>(o);
         const uint32_t s = lo - lo_prev;
         if (s) {
             // the band moves down s rows: rows that enter at the bottom were outside the previous column
-            const BV fill = ~BV(0) << (BW - s);
-            Pv = (Pv >> s) | fill;
+            Pv = (Pv >> s) | (~BV(0) << (BW - s));
             Mv >>= s;
-            M0 >>= s;
-            M1 >>= s;
-            M2 >>= s;
-            M3 >>= s;
+            pl.b0 >>= s;
+            pl.b1 >>= s;
+            pl.v >>= s;
+            pl.np >>= s;
             for (uint32_t t = 0; t < s; t++) {
                 const uint32_t row = lo_prev + BW + t;
-                if (row <= A.m) {
-                    const uint32_t c = A.rb[row - 1];
-                    const BV bit = BV(1) << (BW - s + t);
-                    M0 |= c == 0 ? bit : BV(0);
-                    M1 |= c == 1 ? bit : BV(0);
-                    M2 |= c == 2 ? bit : BV(0);
-                    M3 |= c == 3 ? bit : BV(0);
-                }
+                if (row <= A.m) pl.put(A.rb[TK_AIDX(A, 3, row - 1, A.m, j)], BW - s + t);
             }
         } else if (lo > 1) {
             // same top row as the previous column: the cell above it was outside that column's band
             Pv &= ~BV(1);
             Mv |= BV(1);
         }
-        const uint32_t f = A.frag[j - 1];
+        const uint32_t f = A.frag[TK_AIDX(A, 4, j - 1, A.n, j)];
         BV Eq;
         if (f < 4) {
-            Eq = f == 0 ? M0 : f == 1 ? M1 : f == 2 ? M2 : M3;
+            const BV f0 = BV(0) - BV(f & 1u), f1 = BV(0) - BV(f >> 1);
+            Eq = pl.v & ~((pl.b0 ^ f0) | (pl.b1 ^ f1));
+        } else if (f == 78u) {
+            Eq = pl.np;
         } else {
             Eq = 0;
             for (uint32_t b = 0; b < BW; b++) {
                 const uint32_t row = lo + b;
                 if (row > A.m) break;
-                if (A.rb[row - 1] == f) Eq |= BV(1) << b;
+                if (A.rb[TK_AIDX(A, 5, row - 1, A.m, j)] == f) Eq |= BV(1) << b;
             }
         }
         // Myers' column step with horizontal input +1 at the band top
@@ -156,88 +196,169 @@ TK_HD void align_forward_chunk(const AlignCtx<BV>& A, uint32_t c0, uint32_t c1, 
         Mh <<= 1;
         Pv = Mh | ~(Xv | Ph);
         Mv = Ph & Xv;
-        if (STORE) {
-            A.trace[ti] = Eq | ~D0;
-            A.trace[ti + 1] = Pv;
-            ti += (size_t)A.stride * 2;
+        if (RECHECK) {
+            cell->dg = Eq | ~D0;
+            cell->pv = Pv;
+            cell->mv = Mv;
+            if (Pv == old_pv && Mv == old_mv) return true;
+        } else {
+            AlignCell<BV> c;
+            c.dg = Eq | ~D0;
+            c.pv = Pv;
+            c.mv = Mv;
+            c.arr = ~BV(0);   // no walk has been here (the trace array is reused from read to read)
+            *cell = c;
         }
         o_prev = o;
         lo_prev = lo;
     }
+    Pv_io = Pv;
+    Mv_io = Mv;
+    return false;
 }
 
+// Position of the traceback inside the trace array: column j, its cell index and (owner, within).
 template <typename BV>
-TK_HD uint32_t align_decide(const AlignCtx<BV>& A, uint32_t i, uint32_t j, uint32_t oj) {
-    constexpr uint32_t BW = 8 * sizeof(BV);
-    if (i == 0) return MV_LEFT;
-    if (j == 0) return MV_UP;
-    const uint32_t lo = align_lo<BV>(oj);
-    if (i < lo + (lo > 1 ? ALIGN_MARGIN : 0u) || i + ALIGN_MARGIN >= lo + BW) return MV_OUT;
-    const uint32_t b = i - lo;
-    const size_t ti = align_trace_index(A, j);
-    if ((A.trace[ti] >> b) & 1) return MV_DIAG;
-    if ((A.trace[ti + 1] >> b) & 1) return MV_UP;
-    return MV_LEFT;
-}
-
-// Walks the path back from cell (i, j) (oj = o_j) while it is in columns >= cmin (to the origin when
-// `bottom`).  `top`: (i, j) is the end cell (m, n), whose trailing D run is walked first.  A step
-// consumes one read base and then the D run in front of it, so the cell handed to the next thread
-// always continues with a read base.  WRITE: store op | dcount << 2 over the read codes and count
-// matches; without it only the exit cell is computed.  Returns false when the band was left.
-template <typename BV, bool WRITE>
-TK_HD bool align_trace_chunk(const AlignCtx<BV>& A, uint32_t cmin, bool bottom, bool top, uint32_t& i, uint32_t& j,
-                             uint32_t& oj, uint32_t& eq, uint32_t& cols) {
-    if (top) {
-        while (j > 0) {
-            const uint32_t d = align_decide(A, i, j, oj);
-            if (d == MV_OUT) return false;
-            if (d != MV_LEFT) break;
-            oj -= A.slen[j - 1];
-            j--;
-            cols++;
+struct AlignCursor {
+    uint32_t owner = 0, within = 0;
+    size_t idx = 0;
+    TK_HD void seek(const AlignCtx<BV>& A, uint32_t j) {
+        const uint32_t jj = j - 1;
+        owner = jj / A.chunk;
+        within = jj - owner * A.chunk;
+        idx = (size_t)within * A.stride + owner;
+    }
+    TK_HD void left(const AlignCtx<BV>& A) {
+        if (within) {
+            within--;
+            idx -= A.stride;
+        } else {
+            owner--;
+            within = A.chunk - 1;
+            idx = (size_t)within * A.stride + owner;
         }
     }
-    while (i > 0 && (j >= cmin || bottom)) {
-        const uint32_t d = align_decide(A, i, j, oj);
-        if (d == MV_OUT) return false;
-        if (d == MV_LEFT) {   // only from a mistaken entry cell of a round that will be redone
-            oj -= A.slen[j - 1];
+};
+
+enum : int { TRACE_FIRST = 0, TRACE_REDO = 1, TRACE_WRITE = 2 };
+
+// Walks the path back from cell (i, j) (oj = o_j), which must be one the path leaves by consuming a read
+// base (or the end cell (m, n) when `top`), while it is in columns >= cmin (to the origin when `bottom`),
+// and returns the cell it hands to the thread below in (i, j, oj).
+//   TRACE_FIRST  records in every column the row at which a read base was first started, tagged `tag`;
+//   TRACE_REDO   the same from a corrected entry cell; stops with `merged` as soon as it starts a base where
+//                a walk tagged >= emin did (the caller keeps emin = the oldest walk that ended in the exit
+//                cell it holds): from there on it is that walk, and (i, j, oj) are left alone;
+//   TRACE_WRITE  stores op | dcount << 2 over the read codes and counts matches and columns.
+// Returns false when the band was left.
+template <typename BV, int MODE>
+TK_HD bool align_trace_chunk(const AlignCtx<BV>& A, uint32_t cmin, bool bottom, bool top, uint32_t& i_io, uint32_t& j_io,
+                             uint32_t& oj_io, uint32_t& eq, uint32_t& cols, bool& merged, uint32_t tag = 0,
+                             uint32_t emin = 0) {
+    constexpr uint32_t BW = 8 * sizeof(BV);
+    uint32_t i = i_io, j = j_io, oj = oj_io;
+    merged = false;
+    (void)top;   // the end cell needs no special case: its D run is walked before the first read base starts
+    AlignCursor<BV> cur;
+    BV dg = 0, pv = 0;
+    uint32_t lo = 1, arr_old = 0;
+    bool newcol = true;
+    auto enter = [&]() {   // (j, oj) changed: fetch the column's cell
+        if (j > 0 && cur.idx >= A.cells) {
+            *A.oob = 1;
+            j = 0;
+            i = 0;
+        }
+        if (j > 0) {
+            const AlignCell<BV>& c = A.trace[cur.idx];
+            dg = c.dg;
+            pv = c.pv;
+            if (MODE == TRACE_REDO) arr_old = (uint32_t)c.arr;
+            lo = align_lo<BV>(oj);
+        }
+        newcol = true;
+    };
+    if (j > 0) cur.seek(A, j);
+    enter();
+    bool have = false;
+    uint32_t bi = 0, op = 0, run = 0;
+    while (true) {
+        uint32_t d;
+        if (i == 0) {
+            if (j == 0) break;
+            d = MV_LEFT;
+        } else if (j == 0) {
+            d = MV_UP;
+        } else {
+            if (i < lo + (lo > 1 ? ALIGN_MARGIN : 0u) || i + ALIGN_MARGIN >= lo + BW) return false;
+            const uint32_t b = i - lo;
+            d = ((dg >> b) & 1) ? MV_DIAG : ((pv >> b) & 1) ? MV_UP : MV_LEFT;
+        }
+        if (d == MV_LEFT) {
+            run++;
+            oj -= A.slen[TK_AIDX(A, 6, j - 1, A.n, i)];
             j--;
+            if (j > 0) cur.left(A);
+            enter();
             continue;
         }
-        const uint32_t bi = i - 1;
-        uint32_t op = 2u;   // OP_I
-        if (d == MV_DIAG) {
-            if (WRITE) op = A.rb[bi] == A.frag[j - 1] ? 0u : 1u;   // OP_EQ : OP_X
-            oj -= A.slen[j - 1];
-            j--;
+        // a read base starts here: the one before it is complete (its D run is known now)
+        if (have) {
+            if (MODE == TRACE_WRITE) {
+                A.rb[TK_AIDX(A, 7, bi, A.m, j)] = (uint8_t)(op | ((run > ALIGN_DC_CAP ? ALIGN_DC_CAP : run) << 2));
+                eq += op == 0u;
+            }
+            cols += 1 + run;
+        } else {
+            cols += run;   // D run after the last read base (top), nothing otherwise
         }
+        if (!(j >= cmin || bottom)) {
+            i_io = i;
+            j_io = j;
+            oj_io = oj;
+            return true;
+        }
+        if (MODE != TRACE_WRITE && newcol && j > 0) {
+            if (MODE == TRACE_REDO && (arr_old & ((1u << ALIGN_ROW_BITS) - 1)) == i && (arr_old >> ALIGN_ROW_BITS) >= emin) {
+                merged = true;
+                return true;
+            }
+            A.trace[cur.idx].arr = (BV)((tag << ALIGN_ROW_BITS) | i);
+            newcol = false;
+        }
+        bi = i - 1;
+        have = true;
+        run = 0;
+        op = 2u;   // OP_I
         i--;
-        uint32_t run = 0;
-        while (j > 0) {
-            const uint32_t d2 = align_decide(A, i, j, oj);
-            if (d2 == MV_OUT) return false;
-            if (d2 != MV_LEFT) break;
-            oj -= A.slen[j - 1];
+        if (d == MV_DIAG) {
+            if (MODE == TRACE_WRITE) op = A.rb[TK_AIDX(A, 8, bi, A.m, j)] == A.frag[TK_AIDX(A, 9, j - 1, A.n, i)] ? 0u : 1u;   // OP_EQ : OP_X
+            oj -= A.slen[TK_AIDX(A, 10, j - 1, A.n, i)];
             j--;
-            run++;
+            if (j > 0) cur.left(A);
+            enter();
         }
-        if (WRITE) {
+    }
+    if (have) {
+        if (MODE == TRACE_WRITE) {
             A.rb[bi] = (uint8_t)(op | ((run > ALIGN_DC_CAP ? ALIGN_DC_CAP : run) << 2));
             eq += op == 0u;
         }
         cols += 1 + run;
+    } else {
+        cols += run;
     }
+    i_io = 0;
+    j_io = 0;
+    oj_io = 0;
     return true;
 }
 
 // chunking of n columns over `threads` threads
-TK_HD void align_chunking(uint32_t n, uint32_t threads, uint32_t& chunk, uint32_t& lanes, uint32_t& magic) {
+TK_HD void align_chunking(uint32_t n, uint32_t threads, uint32_t& chunk, uint32_t& lanes) {
     chunk = (n + threads - 1) / threads;
     if (chunk < ALIGN_MIN_CHUNK) chunk = ALIGN_MIN_CHUNK;
     lanes = (n + chunk - 1) / chunk;
-    magic = (uint32_t)(0x100000000ull / chunk) + 1u;
 }
 
 }  // namespace tk

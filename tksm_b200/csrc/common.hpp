@@ -130,6 +130,7 @@ enum : uint32_t {
     ST_OPS_OVERFLOW = 1,      // the read outgrew twice its fragment
     ST_SCRATCH_OVERFLOW = 2,  // the read outgrew its scratch slot
     ST_EPOCH_CAP = 4,         // time cap of the error loop (py/tksm_badread.py:354)
+    ST_ALIGN_OOB = 16,        // internal error: the alignment would have left its trace array
     ST_BAND = 8,              // the alignment left its widest band: qscores follow the edit script itself
 };
 // ident_den carries this flag when (num, den) are the matches / columns of the read's alignment (printed as they
@@ -141,6 +142,8 @@ enum : uint32_t {
     RUN_ERRORS = 1,     // inject errors (badread output requested)
     RUN_QUAL = 2,       // compute qscores
     RUN_RAW = 4,        // also store the error-free sequence
+    RUN_NO_ALIGN = 8,   // experiments ($TKSM_SEQ_DEBUG bit 0): qscores from the edit script's own cigar, no alignment
+    RUN_NO_WIDE = 16,   // experiments ($TKSM_SEQ_DEBUG bit 1): no retry with the 64-bit band
 };
 
 }  // namespace tk

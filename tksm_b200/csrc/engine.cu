@@ -223,7 +223,7 @@ struct tksm_seq_batch {
     DBuf blob;
     DevBatch db{};
     uint32_t* d_work[N_CLASSES] = {};
-    DBuf scr_seq, scr_qual, scr_raw, per_read, out[2], rec_len[2], rec_off[2], sums, gws, counters, work_keys, work_sorted, work_bins, mid, trace;
+    DBuf scr_seq, scr_qual, scr_raw, per_read, out[2], rec_len[2], rec_off[2], sums, gws, counters, work_keys, work_sorted, work_bins, mid, trace, redo;
     HBuf stage;           // pinned upload staging
     HBuf host_out[2];     // pinned download staging (streaming to files)
     HBuf h_tot;           // pinned: record bytes per output, read bases, status
@@ -363,6 +363,9 @@ void compute_classes(tksm_seq* h) {
         if (32 % W == 0 && SIM_FIXED_SMEM + (size_t)h->slab2[c] * (32 / W) + 128 + 64 <= SMEM_TOTAL) h->threads2[c] = 1024;
         h->smem_bytes2[c] = SIM_FIXED_SMEM + (size_t)h->slab2[c] * (h->threads2[c] / 32 / W) + 128 + 64;
     }
+    // the classes of 24 warps take the 64-bit alignment band at once, which is the rule for fragments above
+    // ALIGN_WIDE_FROM slots: the class below them must reach that far
+    if (h->ncap[3] < ALIGN_WIDE_FROM) throw std::runtime_error("length class of 8 warps ends below ALIGN_WIDE_FROM");
     h->smem_bytes[GWS_CLASS] = qcls_bytes + SIM_FIXED_SMEM + gws_small_bytes(CLASS_W[GWS_CLASS]) + 128;
     h->threads2[GWS_CLASS] = GWS_W2 * 32;
     h->smem_bytes2[GWS_CLASS] = SIM_FIXED_SMEM + slab2_small_bytes(GWS_W2) + 128 + 64;
@@ -433,10 +436,24 @@ struct Phase2Launch {
 template <int W, bool GWS, int W2 = W>
 void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, const Phase2Launch& p2) {
     launch_sim_phase<W, GWS, 1>(stream, P, smem, grid);
-    if (P.flags & RUN_ERRORS) {
-        P.counter += 16;
-        P.slab_bytes = p2.slab_bytes;
-        launch_sim_phase<W2, GWS, 2>(stream, P, p2.smem, p2.grid, p2.threads);
+    if (!(P.flags & RUN_ERRORS)) return;
+    uint32_t* const counters = P.counter;
+    P.slab_bytes = p2.slab_bytes;
+    if (W >= 24) {
+        // every read of these classes is above ALIGN_WIDE_FROM slots: 64-bit band at once
+        P.counter = counters + 16;
+        P.n_work_dev = nullptr;
+        launch_sim_phase<W2, GWS, 3>(stream, P, p2.smem, p2.grid, p2.threads);
+        return;
+    }
+    P.counter = counters + 16;
+    launch_sim_phase<W2, GWS, 2>(stream, P, p2.smem, p2.grid, p2.threads);
+    if (P.flags & RUN_QUAL) {
+        // reads whose alignment left the 32-bit band (about one in a thousand) or that are above ALIGN_WIDE_FROM slots
+        P.counter = counters + 24;
+        P.work = P.redo;
+        P.n_work_dev = P.redo_count;
+        launch_sim_phase<W2, GWS, 3>(stream, P, p2.smem, std::min(p2.grid, 32), p2.threads);
     }
 }
 
@@ -614,8 +631,8 @@ void slot_bind(tksm_seq* h, tksm_seq_batch* b) {
     D.ident_num = D.read_len + R;
     D.ident_den = D.ident_num + R;
     D.status = D.ident_den + R;
-    b->counters.ensure(128);
-    b->h_tot.ensure(64);
+    b->counters.ensure(256);
+    b->h_tot.ensure(256);
     b->ensure_events();
     b->bound = true;
 }
@@ -654,6 +671,11 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
     if (want_bad) flags |= RUN_ERRORS;
     if (want_bad && fastq && !h->cfg.skip_qual_compute) flags |= RUN_QUAL;  // py/sequence.py:349-353
     if (want_perf) flags |= RUN_RAW;
+    {
+        static const int dbg = getenv("TKSM_SEQ_DEBUG") ? atoi(getenv("TKSM_SEQ_DEBUG")) : 0;
+        if (dbg & 1) flags |= RUN_NO_ALIGN;
+        if (dbg & 2) flags |= RUN_NO_WIDE;
+    }
     if (want_bad) {
         b->scr_seq.ensure(p.scr_total);
         if (flags & RUN_QUAL) b->scr_qual.ensure(p.scr_total);
@@ -687,7 +709,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         b->gws.ensure((size_t)slab_c[GWS_CLASS] * h->num_sms);
     }
     uint64_t* d_totals = (uint64_t*)((char*)b->counters.p + CNT_TOTALS);
-    CK(cudaMemsetAsync(b->counters.p, 0, 128, S));
+    CK(cudaMemsetAsync(b->counters.p, 0, 256, S));
     if (want_bad) b->mid.ensure(3 * p.scr_total + 64 * (uint64_t)R + 64);
     // alignment trace words: one region per team of every PHASE 2 grid (the classes run concurrently)
     uint64_t trace_off[N_CLASSES] = {}, trace_team[N_CLASSES] = {}, trace_total = 0;
@@ -709,6 +731,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         // device-side work order (kernels.cuh: class | identity bucket | length)
         b->work_keys.ensure((size_t)R * 4);
         b->work_sorted.ensure((size_t)R * 4);
+        b->redo.ensure((size_t)R * 4);
         b->work_bins.ensure((size_t)WORK_BINS * 4);
         CK(cudaMemsetAsync(b->work_bins.p, 0, (size_t)WORK_BINS * 4, S));
         WorkSortParams WS{};
@@ -761,6 +784,10 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         P.mid = b->mid.as<uint8_t>();
         P.trace = b->trace.as<uint8_t>() + trace_off[c];
         P.trace_bytes = trace_team[c];
+        P.dbg = (uint32_t*)((char*)b->counters.p + 128);
+        P.redo = b->redo.as<uint32_t>() + (b->d_work[c] - b->work_sorted.as<uint32_t>());
+        P.redo_count = b->counters.as<uint32_t>() + 48 + c;
+        P.n_work_dev = nullptr;
         const int teams = c == GWS_CLASS ? 1 : SIM_WARPS / CLASS_W[c];
         int grid = (int)std::min<size_t>((size_t)h->num_sms, (P.n_work + teams - 1) / teams);
         Phase2Launch p2;
@@ -783,7 +810,11 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
             case 4: launch_sim<24, false>(st, P, h->smem_bytes[c], grid, p2); break;
             default: launch_sim<24, true, GWS_W2>(st, P, h->smem_bytes[c], grid, p2); break;
         }
-        launches += (flags & RUN_ERRORS) ? 2 : 1;
+        launches += (flags & RUN_ERRORS) ? ((flags & RUN_QUAL) && CLASS_W[c] < 24 ? 3 : 2) : 1;
+        if (getenv("TKSM_SEQ_DEBUG") && (atoi(getenv("TKSM_SEQ_DEBUG")) & 8)) {
+            const cudaError_t e = cudaStreamSynchronize(st);
+            fprintf(stderr, "[debug] class %d (W=%d, %u reads, ncap %u): %s\n", c, CLASS_W[c], P.n_work, P.ncap, cudaGetErrorString(e));
+        }
     }
     for (uint32_t i = 0; i < std::min<uint32_t>(used_streams, 4); i++) {
         CK(cudaEventRecord(b->ev_class[i], h->class_stream[b->lane][i]));
@@ -831,7 +862,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         launches += 5;
     }
     CK(cudaEventRecord(b->ev[2], S));
-    CK(cudaMemcpyAsync(b->h_tot.p, d_totals, 32, cudaMemcpyDeviceToHost, S));
+    CK(cudaMemcpyAsync(b->h_tot.p, d_totals, 224, cudaMemcpyDeviceToHost, S));
     CK(cudaEventRecord(b->ev[4], S));
     b->launches = launches;
 }
@@ -858,6 +889,9 @@ void slot_wait(tksm_seq* h, tksm_seq_batch* b, tksm_seq_stats* st) {
     p.blob = nullptr;
     const bool want_bad = b->which & TKSM_SEQ_BADREAD, want_perf = b->which & TKSM_SEQ_PERFECT;
     const uint64_t* tot = (const uint64_t*)b->h_tot.p;
+    if (const uint32_t* dbg = (const uint32_t*)((const char*)b->h_tot.p + 96); dbg[0])
+        fprintf(stderr, "[align paranoid] %u violations; first: read %u site %u index %u limit %u j %u (n %u, m %u)\n", dbg[0], dbg[1],
+                dbg[3], dbg[4], dbg[5], dbg[6], dbg[7], dbg[8]);
     float ms_all = 0, ms_sim = 0;
     CK(cudaEventElapsedTime(&ms_all, b->ev[0], b->ev[2]));
     CK(cudaEventElapsedTime(&ms_sim, b->ev[0], b->ev[1]));

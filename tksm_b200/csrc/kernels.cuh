@@ -170,6 +170,8 @@ constexpr uint32_t SIM_FIXED_SMEM = 64 + 512;  // CTA-wide: lut3[64] | alias row
 constexpr uint32_t MISC_WORDS = 64;  // per-team scratch words
 constexpr uint32_t MISC_WSUM = 8;    // W + 1 words of scan partials
 constexpr uint32_t MISC_LISTN = 40;  // touched-list length (teams of more than one warp)
+constexpr uint32_t MISC_ALIGN_OOB = 44;   // (+ 4 words of detail in TK_ALIGN_PARANOID builds)
+// dummy to keep the numbering visible:   // set when the alignment would have left its trace array
 constexpr uint32_t MISC_ALIGN_FLAG = 42;  // two words: "some thread's chunk-edge assumption was wrong" of the alignment rounds
 constexpr uint32_t QUEUE_BYTES = 64 * 4 + 64 * 4;  // per-warp compaction queue: 64 x (u32, u32)
 
@@ -187,6 +189,10 @@ struct SimParams {
     uint8_t* mid;           // PHASE 1 -> 2 records, 3 * scratch bytes + 64 per read
     uint8_t* trace;         // PHASE 2: alignment trace words, trace_bytes per team (global, L2-resident)
     uint64_t trace_bytes;
+    uint32_t* dbg;          // TK_ALIGN_PARANOID builds: first recorded violation
+    uint32_t* redo;         // PHASE 2: reads to be finished by the PHASE 3 kernel of the class (64-bit band)
+    uint32_t* redo_count;
+    const uint32_t* n_work_dev;  // PHASE 3 on a redo list: number of entries (device memory); nullptr: n_work
 };
 
 // Team workspace layout, shared by the host (sizing) and the kernel:
@@ -215,7 +221,7 @@ __host__ __device__ inline uint32_t slab2_big_bytes(uint32_t ncap) { return (4 *
 // columns of alignment trace one team needs room for (a chunk per thread, at least ALIGN_MIN_CHUNK columns each)
 __host__ __device__ inline uint64_t trace_team_bytes(int W, uint32_t ncap) {
     const uint64_t cols = (uint64_t)(ncap / (32u * W) + 1 > ALIGN_MIN_CHUNK ? ncap / (32u * W) + 1 : ALIGN_MIN_CHUNK) * 32u * W;
-    return cols * 16;   // (Dg, Pv) as 64-bit words
+    return cols * ALIGN_CELL_BYTES;
 }
 
 // shared-memory bytes of the GWS class for the part of the workspace in front of the candidate list
@@ -792,17 +798,19 @@ template <int W, typename BV>
 __device__ __forceinline__ bool align_team_impl(const Team<W>& tm, AlignCtx<BV>& A, uint4* xch, uint32_t* misc, uint32_t* wsum,
                                                 uint32_t& eq_out, uint32_t& cols_out) {
     uint32_t lanes;
-    align_chunking(A.n, (uint32_t)Team<W>::SIZE, A.chunk, lanes, A.magic);
+    align_chunking(A.n, (uint32_t)Team<W>::SIZE, A.chunk, lanes);
     A.stride = (uint32_t)Team<W>::SIZE;
     const uint32_t l = (uint32_t)tm.rank;
     const bool active = l < lanes;
-    const uint32_t c0 = 1 + l * A.chunk;
-    const uint32_t c1 = min(A.n + 1, c0 + A.chunk);
+    AlignLane<BV> Ln;
+    Ln.c0 = 1 + l * A.chunk;
+    Ln.c1 = min(A.n + 1, Ln.c0 + A.chunk);
     uint32_t mine = 0;
     if (active)
-        for (uint32_t j = c0; j < c1; j++) mine += A.slen[j - 1];
+        for (uint32_t j = Ln.c0; j < Ln.c1; j++) mine += A.slen[j - 1];
     uint32_t tot;
-    const uint32_t ob = team_excl_scan<W>(tm, mine, wsum, tot);   // read bases in front of the chunk
+    Ln.ob = team_excl_scan<W>(tm, mine, wsum, tot);   // read bases in front of the chunk
+    if (active) align_lane_init(A, Ln);
     // agreement flags of the rounds (teams of more than one warp): two words, used alternately
     uint32_t* flag = misc + MISC_ALIGN_FLAG;
     if (W > 1) {
@@ -830,15 +838,14 @@ __device__ __forceinline__ bool align_team_impl(const Team<W>& tm, AlignCtx<BV>&
             P = ~BV(0);
             M = 0;
         } else {
-            align_ideal_state<BV>(ob, P, M);
+            align_ideal_state<BV>(Ln.ob, P, M);
         }
-        bool need = active;
+        if (active) {
+            oP = P;
+            oM = M;
+            align_forward_chunk<BV, false>(A, Ln, oP, oM);
+        }
         while (true) {
-            if (need) {
-                oP = P;
-                oM = M;
-                align_forward_chunk<BV, true>(A, c0, c1, ob, oP, oM);
-            }
             xch[l] = make_uint4((uint32_t)oP, (uint32_t)((uint64_t)oP >> 32), (uint32_t)oM, (uint32_t)((uint64_t)oM >> 32));
             tm.sync();
             bool ch = false;
@@ -849,8 +856,14 @@ __device__ __forceinline__ bool align_team_impl(const Team<W>& tm, AlignCtx<BV>&
                 P = nP;
                 M = nM;
             }
-            need = ch;
             if (!team_any(ch)) break;
+            if (ch) {
+                BV tP = P, tM = M;
+                if (!align_forward_chunk<BV, true>(A, Ln, tP, tM)) {
+                    oP = tP;
+                    oM = tM;
+                }
+            }
         }
     }
     __threadfence_block();
@@ -863,22 +876,19 @@ __device__ __forceinline__ bool align_team_impl(const Team<W>& tm, AlignCtx<BV>&
         ej = A.n;
         eo = A.m;
     } else {
-        ei = ob + mine;
-        ej = c1 - 1;
-        eo = ob + mine;
+        ei = Ln.ob + mine;
+        ej = Ln.c1 - 1;
+        eo = Ln.ob + mine;
     }
     bool ok = true;
     {
-        bool need = active;
-        uint32_t xi = 0, xj = 0, xo = 0;
+        uint32_t xi = ei, xj = ej, xo = eo, tag = 1, emin = 1;
+        if (active) {
+            uint32_t e = 0, c = 0;
+            bool merged;
+            ok = align_trace_chunk<BV, TRACE_FIRST>(A, Ln.c0, l == 0, top, xi, xj, xo, e, c, merged, 1u, 1u);
+        }
         while (true) {
-            if (need) {
-                xi = ei;
-                xj = ej;
-                xo = eo;
-                uint32_t e = 0, c = 0;
-                ok = align_trace_chunk<BV, false>(A, c0, l == 0, top, xi, xj, xo, e, c);
-            }
             xch[l] = make_uint4(xi, xj, xo, 0u);
             tm.sync();
             bool ch = false;
@@ -889,29 +899,40 @@ __device__ __forceinline__ bool align_team_impl(const Team<W>& tm, AlignCtx<BV>&
                 ej = v.y;
                 eo = v.z;
             }
-            need = ch;
             if (!team_any(ch)) break;
+            if (ch) {
+                uint32_t ti = ei, tj = ej, to = eo, e = 0, c = 0;
+                bool merged;
+                tag++;
+                const bool r = align_trace_chunk<BV, TRACE_REDO>(A, Ln.c0, l == 0, top, ti, tj, to, e, c, merged, tag, emin);
+                if (!merged) {
+                    ok = r;
+                    xi = ti;
+                    xj = tj;
+                    xo = to;
+                    emin = tag;
+                }
+            }
         }
     }
     if (team_any(active && !ok)) return false;
     uint32_t eq = 0, cols = 0;
-    if (active) align_trace_chunk<BV, true>(A, c0, l == 0, top, ei, ej, eo, eq, cols);
+    if (active) {
+        bool merged;
+        align_trace_chunk<BV, TRACE_WRITE>(A, Ln.c0, l == 0, top, ei, ej, eo, eq, cols, merged);
+    }
     eq_out = team_sum<W>(tm, eq, wsum);
     cols_out = team_sum<W>(tm, cols, wsum);
     return true;
-}
-
-template <int W>
-__device__ __noinline__ bool align_team_wide(const Team<W>& tm, AlignCtx<uint64_t>& A, uint4* xch, uint32_t* misc, uint32_t* wsum,
-                                             uint32_t& eq_out, uint32_t& cols_out) {
-    return align_team_impl<W, uint64_t>(tm, A, xch, misc, wsum, eq_out, cols_out);
 }
 
 // ------------------------------------------------------------- PHASE 2
 // Expansion of the slot contents into the read, alignment of the read back to the fragment
 // (py/tksm_badread.py:613), qscores from the alignment's window cigars (:584-655).
 //   wsl: misc | compaction queues (shared memory);  ws: frag | slen | rb (shared, or global for the GWS class)
-template <int W, bool GWS>
+// WIDE: 64-bit alignment band (PHASE 3 kernels: reads above ALIGN_WIDE_FROM slots and the redo lists); otherwise
+// 32-bit, and a read whose traceback leaves that band is put on the redo list of its class instead of finished.
+template <int W, bool GWS, bool WIDE>
 __device__ __forceinline__ void finish_read(const Team<W>& tm, const SimParams& P, uint32_t r, uint8_t* ws, uint8_t* wsl,
                                             const uint8_t* lut3, uint8_t* trace) {
     constexpr int SIZE = Team<W>::SIZE;
@@ -944,6 +965,7 @@ __device__ __forceinline__ void finish_read(const Team<W>& tm, const SimParams& 
         for (uint32_t x = tm.rank; x < frag_q; x += SIZE) f4[x] = mid4[key_q + x];
     }
     uint32_t status = B.status[r];
+    if (tm.rank == 0) misc[MISC_ALIGN_OOB] = 0;
     auto key_len = [&](uint32_t p) -> uint32_t {
         const uint32_t c = __ldg(gkey + p) & 0xFFFFu;
         return c == 0xFFFFu ? 1u : content_len(c);
@@ -1082,29 +1104,44 @@ __device__ __forceinline__ void finish_read(const Team<W>& tm, const SimParams& 
         // the read is aligned back to the fragment; the ops of the alignment replace the read codes in rb
         {
             uint32_t eq = 0, cols = 0;
-            bool ok;
-            {
-                AlignCtx<uint32_t> A;
-                A.frag = frag;
-                A.slen = slen;
-                A.rb = rb;
-                A.trace = (uint32_t*)trace;
-                A.n = n;
-                A.m = Ttot;
-                ok = align_team_impl<W, uint32_t>(tm, A, (uint4*)qbase, misc, wsum, eq, cols);
-            }
-            if (!ok) {
-                AlignCtx<uint64_t> A;
-                A.frag = frag;
-                A.slen = slen;
-                A.rb = rb;
-                A.trace = (uint64_t*)trace;
-                A.n = n;
-                A.m = Ttot;
+            bool ok = false;
+            if (!WIDE && n > ALIGN_WIDE_FROM) {
+                // long reads start with the 64-bit band (the 32-bit one is left somewhere along most of them)
+                if (tm.rank == 0) P.redo[atomicAdd(P.redo_count, 1u)] = r;
                 tm.sync();
-                ok = align_team_wide<W>(tm, A, (uint4*)qbase, misc, wsum, eq, cols);
+                return;
+            }
+            if (!(P.flags & RUN_NO_ALIGN)) {
+                using BV = typename std::conditional<WIDE, uint64_t, uint32_t>::type;
+                AlignCtx<BV> A;
+                A.frag = frag;
+                A.slen = slen;
+                A.rb = rb;
+                A.trace = (AlignCell<BV>*)trace;
+                A.cells = (uint32_t)(P.trace_bytes / sizeof(AlignCell<BV>));
+                A.oob = misc + MISC_ALIGN_OOB;
+                A.n = n;
+                A.m = Ttot;
+                ok = align_team_impl<W, BV>(tm, A, (uint4*)qbase, misc, wsum, eq, cols);
+                if (!WIDE && !ok && !(P.flags & RUN_NO_WIDE) && !misc[MISC_ALIGN_OOB]) {
+                    if (tm.rank == 0) P.redo[atomicAdd(P.redo_count, 1u)] = r;
+                    tm.sync();
+                    return;
+                }
             }
             tm.sync();
+            if (misc[MISC_ALIGN_OOB]) {
+                ok = false;
+                status |= ST_ALIGN_OOB;
+#ifdef TK_ALIGN_PARANOID
+                if (tm.rank == 0 && P.dbg && atomicAdd(P.dbg, 1u) == 0) {
+                    P.dbg[1] = r;
+                    for (int q = 0; q < 5; q++) P.dbg[2 + q] = misc[MISC_ALIGN_OOB + q];
+                    P.dbg[7] = n;
+                    P.dbg[8] = Ttot;
+                }
+#endif
+            }
             if (ok) {
                 if (tm.rank == 0) {
                     B.ident_num[r] = eq;
@@ -1225,7 +1262,7 @@ __device__ __forceinline__ void finish_read(const Team<W>& tm, const SimParams& 
 }
 
 template <int W, bool GWS, int PHASE>
-__global__ void __launch_bounds__(PHASE == 2 ? 1024 : SIM_THREADS, 1) simulate_kernel(const SimParams P) {
+__global__ void __launch_bounds__(PHASE >= 2 ? 1024 : SIM_THREADS, 1) simulate_kernel(const SimParams P) {
     extern __shared__ __align__(16) uint8_t smem[];
     // 24 warps per CTA; the PHASE 2 kernels need fewer registers and less shared memory per team and
     // run 32 warps per CTA where the team workspaces fit (the host decides: blockDim.x)
@@ -1236,7 +1273,7 @@ __global__ void __launch_bounds__(PHASE == 2 ? 1024 : SIM_THREADS, 1) simulate_k
     tm.bar = TEAMS > 15 ? tm.id : tm.id + 1;
     // k-mer change-probability classes staged in shared memory for the whole CTA, then a 64-entry
     // table turning three packed cigar ops into their base-3 code
-    const uint32_t nq = (P.T.has_err_table && PHASE != 2) ? (1u << (2 * P.T.k)) : 0u;  // arrivals only
+    const uint32_t nq = (P.T.has_err_table && PHASE == 1) ? (1u << (2 * P.T.k)) : 0u;  // arrivals only
     uint8_t* qcls_s = smem;
     for (uint32_t i = threadIdx.x; i < nq; i += blockDim.x) qcls_s[i] = P.T.qcls[i];
     const uint32_t qcls_bytes = (nq + 15) & ~15u;
@@ -1244,7 +1281,7 @@ __global__ void __launch_bounds__(PHASE == 2 ? 1024 : SIM_THREADS, 1) simulate_k
     if (threadIdx.x < 64) lut3[threadIdx.x] = (uint8_t)((threadIdx.x & 3) + 3 * ((threadIdx.x >> 2) & 3) + 9 * (threadIdx.x >> 4));
     // the window of nine matches is by far the most frequent one: its alias row lives in shared memory
     uint32_t* q0row = (uint32_t*)(lut3 + 64);
-    if (PHASE == 2 && P.T.q_t9 && threadIdx.x < 128) {
+    if (PHASE >= 2 && P.T.q_t9 && threadIdx.x < 128) {
         const uint32_t e0 = P.T.q_t9[0];
         if (threadIdx.x < (1u << (e0 & 7u))) q0row[threadIdx.x] = P.T.q_alias[(e0 >> 3) + threadIdx.x];
     }
@@ -1254,7 +1291,7 @@ __global__ void __launch_bounds__(PHASE == 2 ? 1024 : SIM_THREADS, 1) simulate_k
     uint8_t* pool = smem + qcls_bytes + SIM_FIXED_SMEM;
     uint8_t *ws, *wsl;
     size_t pool_used;
-    if (PHASE == 2) {
+    if (PHASE >= 2) {
         const uint32_t small = slab2_small_bytes(W);
         if (GWS) {
             wsl = pool;
@@ -1276,15 +1313,16 @@ __global__ void __launch_bounds__(PHASE == 2 ? 1024 : SIM_THREADS, 1) simulate_k
         }
     }
     uint32_t* ticket = (uint32_t*)(pool + pool_used) + tm.id;
-    uint8_t* trace = PHASE == 2 ? P.trace + ((size_t)blockIdx.x * TEAMS + tm.id) * P.trace_bytes : nullptr;
+    uint8_t* trace = PHASE >= 2 ? P.trace + ((size_t)blockIdx.x * TEAMS + tm.id) * P.trace_bytes : nullptr;
+    const uint32_t n_work = (PHASE == 3 && P.n_work_dev) ? *P.n_work_dev : P.n_work;
     while (true) {
         if (tm.rank == 0) *ticket = atomicAdd(P.counter, 1u);
         tm.sync();
         const uint32_t wi = *ticket;
         tm.sync();
-        if (wi >= P.n_work) break;
-        if (PHASE == 2)
-            finish_read<W, GWS>(tm, P, P.work[wi], ws, wsl, lut3, trace);
+        if (wi >= n_work) break;
+        if (PHASE >= 2)
+            finish_read<W, GWS, PHASE == 3>(tm, P, P.work[wi], ws, wsl, lut3, trace);
         else
             inject_read<W, GWS>(tm, P, P.work[wi], ws, wsl, qcls_s);
     }
