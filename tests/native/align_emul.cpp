@@ -19,10 +19,11 @@ static int run(const uint8_t* frag, const uint8_t* slen, uint8_t* rb, uint32_t n
                uint32_t* eq_out, uint32_t* cols_out, uint32_t* rounds) {
     AlignCtx<BV> A;
     uint32_t lanes;
-    align_chunking(n, threads, A.chunk, lanes);
+    align_chunking(n, threads, 8 * (uint32_t)sizeof(BV), A.chunk, lanes);
     A.frag = frag;
     A.slen = slen;
     A.rb = rb;
+    A.out = rb;
     A.n = n;
     A.m = m;
     A.stride = threads;

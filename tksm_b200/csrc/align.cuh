@@ -60,12 +60,19 @@ struct alignas(4 * sizeof(BV)) AlignCell {
     BV dg, pv, mv, arr;
 };
 
+// the cell of a pass that needs neither rounds nor redone walks (align_kernel: one thread per read)
 template <typename BV>
+struct alignas(2 * sizeof(BV)) AlignCell2 {
+    BV dg, pv;
+};
+
+template <typename BV, typename CELL = AlignCell<BV>>
 struct AlignCtx {
     const uint8_t* frag;   // n fragment codes (0..3, or the raw byte)
     const uint8_t* slen;   // n slot lengths of the edit script
-    uint8_t* rb;           // m read codes; the traceback replaces them by op | dcount << 2
-    AlignCell<BV>* trace;  // cell of column j at [within * stride + owner], (owner, within) = divmod(j - 1, chunk)
+    const uint8_t* rb;     // m read codes
+    uint8_t* out;          // op | dcount << 2 per read base (may be the array of the read codes)
+    CELL* trace;           // cell of column j at [within * stride + owner], (owner, within) = divmod(j - 1, chunk)
     uint32_t n, m;
     uint32_t chunk;        // columns per thread
     uint32_t stride;       // threads of the team
@@ -117,8 +124,8 @@ struct AlignLane {
     AlignPlanes<BV> pl;   // planes of the band of column c0 - 1 (they depend on the read only, not on the round)
 };
 
-template <typename BV>
-TK_HD void align_lane_init(const AlignCtx<BV>& A, AlignLane<BV>& Ln) {
+template <typename BV, typename CTX>
+TK_HD void align_lane_init(const CTX& A, AlignLane<BV>& Ln) {
     constexpr uint32_t BW = 8 * sizeof(BV);
     const uint32_t lo = align_lo<BV>(Ln.ob);
     Ln.pl.b0 = Ln.pl.b1 = Ln.pl.v = Ln.pl.np = 0;
@@ -133,14 +140,14 @@ TK_HD void align_lane_init(const AlignCtx<BV>& A, AlignLane<BV>& Ln) {
 // RECHECK: the columns have been computed before from another input state; returns true (and leaves
 // Pv / Mv alone) as soon as a column ends in the state stored for it, since everything after it is
 // then what it was.
-template <typename BV, bool RECHECK>
-TK_HD bool align_forward_chunk(const AlignCtx<BV>& A, const AlignLane<BV>& Ln, BV& Pv_io, BV& Mv_io) {
+template <typename BV, bool RECHECK, typename CTX>
+TK_HD bool align_forward_chunk(const CTX& A, const AlignLane<BV>& Ln, BV& Pv_io, BV& Mv_io) {
     constexpr uint32_t BW = 8 * sizeof(BV);
     BV Pv = Pv_io, Mv = Mv_io;
     AlignPlanes<BV> pl = Ln.pl;
     uint32_t o_prev = Ln.ob;
     uint32_t lo_prev = align_lo<BV>(o_prev);
-    AlignCell<BV>* cell = A.trace + (Ln.c0 - 1) / A.chunk;   // first column of the chunk: within = 0, owner = the thread
+    auto* cell = A.trace + (Ln.c0 - 1) / A.chunk;   // first column of the chunk: within = 0, owner = the thread
     for (uint32_t j = Ln.c0; j < Ln.c1; j++, cell += A.stride) {
         if ((size_t)(cell - A.trace) >= A.cells) {
             *A.oob = 1;
@@ -218,17 +225,18 @@ TK_HD bool align_forward_chunk(const AlignCtx<BV>& A, const AlignLane<BV>& Ln, B
 }
 
 // Position of the traceback inside the trace array: column j, its cell index and (owner, within).
-template <typename BV>
 struct AlignCursor {
     uint32_t owner = 0, within = 0;
     size_t idx = 0;
-    TK_HD void seek(const AlignCtx<BV>& A, uint32_t j) {
+    template <typename CTX>
+    TK_HD void seek(const CTX& A, uint32_t j) {
         const uint32_t jj = j - 1;
         owner = jj / A.chunk;
         within = jj - owner * A.chunk;
         idx = (size_t)within * A.stride + owner;
     }
-    TK_HD void left(const AlignCtx<BV>& A) {
+    template <typename CTX>
+    TK_HD void left(const CTX& A) {
         if (within) {
             within--;
             idx -= A.stride;
@@ -251,15 +259,15 @@ enum : int { TRACE_FIRST = 0, TRACE_REDO = 1, TRACE_WRITE = 2 };
 //                cell it holds): from there on it is that walk, and (i, j, oj) are left alone;
 //   TRACE_WRITE  stores op | dcount << 2 over the read codes and counts matches and columns.
 // Returns false when the band was left.
-template <typename BV, int MODE>
-TK_HD bool align_trace_chunk(const AlignCtx<BV>& A, uint32_t cmin, bool bottom, bool top, uint32_t& i_io, uint32_t& j_io,
+template <typename BV, int MODE, typename CTX>
+TK_HD bool align_trace_chunk(const CTX& A, uint32_t cmin, bool bottom, bool top, uint32_t& i_io, uint32_t& j_io,
                              uint32_t& oj_io, uint32_t& eq, uint32_t& cols, bool& merged, uint32_t tag = 0,
                              uint32_t emin = 0) {
     constexpr uint32_t BW = 8 * sizeof(BV);
     uint32_t i = i_io, j = j_io, oj = oj_io;
     merged = false;
     (void)top;   // the end cell needs no special case: its D run is walked before the first read base starts
-    AlignCursor<BV> cur;
+    AlignCursor cur;
     BV dg = 0, pv = 0;
     uint32_t lo = 1, arr_old = 0;
     bool newcol = true;
@@ -270,10 +278,10 @@ TK_HD bool align_trace_chunk(const AlignCtx<BV>& A, uint32_t cmin, bool bottom, 
             i = 0;
         }
         if (j > 0) {
-            const AlignCell<BV>& c = A.trace[cur.idx];
+            const auto& c = A.trace[cur.idx];
             dg = c.dg;
             pv = c.pv;
-            if (MODE == TRACE_REDO) arr_old = (uint32_t)c.arr;
+            if constexpr (MODE == TRACE_REDO) arr_old = (uint32_t)c.arr;
             lo = align_lo<BV>(oj);
         }
         newcol = true;
@@ -305,7 +313,7 @@ TK_HD bool align_trace_chunk(const AlignCtx<BV>& A, uint32_t cmin, bool bottom, 
         // a read base starts here: the one before it is complete (its D run is known now)
         if (have) {
             if (MODE == TRACE_WRITE) {
-                A.rb[TK_AIDX(A, 7, bi, A.m, j)] = (uint8_t)(op | ((run > ALIGN_DC_CAP ? ALIGN_DC_CAP : run) << 2));
+                A.out[TK_AIDX(A, 7, bi, A.m, j)] = (uint8_t)(op | ((run > ALIGN_DC_CAP ? ALIGN_DC_CAP : run) << 2));
                 eq += op == 0u;
             }
             cols += 1 + run;
@@ -318,7 +326,7 @@ TK_HD bool align_trace_chunk(const AlignCtx<BV>& A, uint32_t cmin, bool bottom, 
             oj_io = oj;
             return true;
         }
-        if (MODE != TRACE_WRITE && newcol && j > 0) {
+        if constexpr (MODE != TRACE_WRITE) if (newcol && j > 0) {
             if (MODE == TRACE_REDO && (arr_old & ((1u << ALIGN_ROW_BITS) - 1)) == i && (arr_old >> ALIGN_ROW_BITS) >= emin) {
                 merged = true;
                 return true;
@@ -341,7 +349,7 @@ TK_HD bool align_trace_chunk(const AlignCtx<BV>& A, uint32_t cmin, bool bottom, 
     }
     if (have) {
         if (MODE == TRACE_WRITE) {
-            A.rb[bi] = (uint8_t)(op | ((run > ALIGN_DC_CAP ? ALIGN_DC_CAP : run) << 2));
+            A.out[bi] = (uint8_t)(op | ((run > ALIGN_DC_CAP ? ALIGN_DC_CAP : run) << 2));
             eq += op == 0u;
         }
         cols += 1 + run;
@@ -354,10 +362,13 @@ TK_HD bool align_trace_chunk(const AlignCtx<BV>& A, uint32_t cmin, bool bottom, 
     return true;
 }
 
-// chunking of n columns over `threads` threads
-TK_HD void align_chunking(uint32_t n, uint32_t threads, uint32_t& chunk, uint32_t& lanes) {
+// chunking of n columns over `threads` threads.  The state of a band of BW rows remembers about BW columns, and a chunk
+// shorter than that rarely ends in a state that does not depend on the one it started from (every such chunk costs
+// a round): chunks are at least 4 BW columns long.
+TK_HD void align_chunking(uint32_t n, uint32_t threads, uint32_t band_bits, uint32_t& chunk, uint32_t& lanes) {
     chunk = (n + threads - 1) / threads;
-    if (chunk < ALIGN_MIN_CHUNK) chunk = ALIGN_MIN_CHUNK;
+    const uint32_t min_chunk = band_bits >= 64 ? 4 * band_bits : ALIGN_MIN_CHUNK;
+    if (chunk < min_chunk) chunk = min_chunk;
     lanes = (n + chunk - 1) / chunk;
 }
 

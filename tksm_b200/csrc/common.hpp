@@ -99,6 +99,13 @@ constexpr uint64_t SEG_MINUS = 1ull << 62;
 constexpr uint64_t SEG_HAS_EXC = 1ull << 61;
 constexpr uint64_t SEG_OFF_MASK = (1ull << 56) - 1;
 
+// what the expansion of a read tells the alignment and qscore kernels
+struct alignas(16) RInfo {
+    uint32_t m;            // read length with flanks
+    uint32_t start_trim, end_trim;
+    uint32_t flags;        // RINFO_*
+};
+
 struct DevBatch {
     uint32_t n_reads;
     uint64_t ordinal_base;
@@ -117,6 +124,9 @@ struct DevBatch {
     const uint64_t* scr_off;       // R + 1; read r owns [scr_off[r], scr_off[r+1]) in each arena
     uint8_t* scr_seq;
     uint8_t* scr_qual;
+    uint8_t* scr_ops;              // read codes with flanks (expansion kernels); nullptr without qscores
+    uint8_t* scr_cig;              // op | dcount << 2 per read base (align_kernel); nullptr without qscores
+    RInfo* rinfo;                  // per read, written by the expansion kernels; nullptr without qscores
     uint8_t* scr_raw;              // error-free sequence (perfect output) or nullptr
     const uint64_t* raw_off;       // R + 1 when scr_raw != nullptr
     uint32_t* read_len;            // L'

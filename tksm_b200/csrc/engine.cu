@@ -223,7 +223,7 @@ struct tksm_seq_batch {
     DBuf blob;
     DevBatch db{};
     uint32_t* d_work[N_CLASSES] = {};
-    DBuf scr_seq, scr_qual, scr_raw, per_read, out[2], rec_len[2], rec_off[2], sums, gws, counters, work_keys, work_sorted, work_bins, mid, trace, redo;
+    DBuf scr_seq, scr_qual, scr_raw, per_read, out[2], rec_len[2], rec_off[2], sums, gws, counters, work_keys, work_sorted, work_bins, mid, trace, redo, redo64, scr_ops, scr_cig, rinfo, atrace;
     HBuf stage;           // pinned upload staging
     HBuf host_out[2];     // pinned download staging (streaming to files)
     HBuf h_tot;           // pinned: record bytes per output, read bases, status
@@ -356,8 +356,9 @@ void compute_classes(tksm_seq* h) {
         h->cap_list[c] = list_capacity(ncap);
         h->slab[c] = slab_layout(W, hist_elem, ncap, h->cap_list[c]).bytes;
         h->smem_bytes[c] = qcls_bytes + SIM_FIXED_SMEM + (size_t)h->slab[c] * teams + 128;
-        // PHASE 2 (expansion, alignment, qscores): fragment, slot lengths and read in shared memory; no k-mer
-        // classes, threshold row or histogram, so 32 warps per CTA where the workspaces fit
+        // FIN_FULL kernels (expansion, team-parallel alignment, qscores: long reads and the redo lists): fragment, slot
+        // lengths and read in shared memory; no k-mer classes, threshold row or histogram, so 32 warps per CTA where the
+        // workspaces fit.  FIN_EXPAND / FIN_QUAL kernels: only the small workspace part.
         h->slab2[c] = slab2_small_bytes(W) + slab2_big_bytes(ncap);
         h->threads2[c] = SIM_THREADS;
         if (32 % W == 0 && SIM_FIXED_SMEM + (size_t)h->slab2[c] * (32 / W) + 128 + 64 <= SMEM_TOTAL) h->threads2[c] = 1024;
@@ -433,28 +434,53 @@ struct Phase2Launch {
 };
 // W2: warps per read of the PHASE 2 kernel (the global-workspace class is not bound by a shared-memory slab and
 // puts all 32 warps of a CTA on its read)
+struct AlignLaunch {
+    AlignKParams K;   // 32-bit instance: its give-up list is (redo64, redo64_count)
+    int grid;
+    uint32_t* redo64;         // give-up list of the 32-bit instance = work list of the 64-bit one
+    uint32_t* redo64_count;
+};
 template <int W, bool GWS, int W2 = W>
-void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, const Phase2Launch& p2) {
+void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, const Phase2Launch& p2, const AlignLaunch& al) {
     launch_sim_phase<W, GWS, 1>(stream, P, smem, grid);
     if (!(P.flags & RUN_ERRORS)) return;
     uint32_t* const counters = P.counter;
-    P.slab_bytes = p2.slab_bytes;
     if (W >= 24) {
-        // every read of these classes is above ALIGN_WIDE_FROM slots: 64-bit band at once
+        // every read of these classes is above ALIGN_WIDE_FROM slots: team-parallel alignment with the 64-bit band
+        P.slab_bytes = p2.slab_bytes;
         P.counter = counters + 16;
         P.n_work_dev = nullptr;
-        launch_sim_phase<W2, GWS, 3>(stream, P, p2.smem, p2.grid, p2.threads);
+        launch_sim_phase<W2, GWS, FIN_FULL>(stream, P, p2.smem, p2.grid, p2.threads);
         return;
     }
-    P.counter = counters + 16;
-    launch_sim_phase<W2, GWS, 2>(stream, P, p2.smem, p2.grid, p2.threads);
-    if (P.flags & RUN_QUAL) {
-        // reads whose alignment left the 32-bit band (about one in a thousand) or that are above ALIGN_WIDE_FROM slots
-        P.counter = counters + 24;
-        P.work = P.redo;
-        P.n_work_dev = P.redo_count;
-        launch_sim_phase<W2, GWS, 3>(stream, P, p2.smem, std::min(p2.grid, 32), p2.threads);
+    // expansion | one thread per read: alignment | qscores; then the redo list of the class
+    constexpr int TEAMS = 32 / W;
+    const size_t smem_small = SIM_FIXED_SMEM + (size_t)slab2_small_bytes(W) * TEAMS + 128 + 64;
+    const int grid_small = (int)std::min<size_t>((size_t)grid * 2, (P.n_work + TEAMS - 1) / TEAMS);
+    SimParams Q = P;
+    Q.slab_bytes = slab2_small_bytes(W);
+    Q.counter = counters + 16;
+    launch_sim_phase<W, GWS, FIN_EXPAND>(stream, Q, smem_small, grid_small, 1024);
+    if (!(P.flags & RUN_QUAL)) return;
+    align_kernel<uint32_t><<<al.grid, 256, 0, stream>>>(al.K);
+    {
+        // the few reads that left the 32-bit band (about one in a thousand)
+        AlignKParams K2 = al.K;
+        K2.work = al.redo64;
+        K2.n_work_dev = al.redo64_count;
+        K2.counter = al.K.counter + 8;
+        K2.redo = P.redo;
+        K2.redo_count = P.redo_count;
+        align_kernel<uint64_t><<<std::min(al.grid, 16), 256, 0, stream>>>(K2);
     }
+    CK(cudaGetLastError());
+    Q.counter = counters + 24;
+    launch_sim_phase<W, GWS, FIN_QUAL>(stream, Q, smem_small, grid_small, 1024);
+    P.slab_bytes = p2.slab_bytes;
+    P.counter = counters + 56;
+    P.work = P.redo;
+    P.n_work_dev = P.redo_count;
+    launch_sim_phase<W2, GWS, FIN_FULL>(stream, P, p2.smem, std::min(p2.grid, 32), p2.threads);
 }
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -631,7 +657,7 @@ void slot_bind(tksm_seq* h, tksm_seq_batch* b) {
     D.ident_num = D.read_len + R;
     D.ident_den = D.ident_num + R;
     D.status = D.ident_den + R;
-    b->counters.ensure(256);
+    b->counters.ensure(512);
     b->h_tot.ensure(256);
     b->ensure_events();
     b->bound = true;
@@ -678,11 +704,19 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
     }
     if (want_bad) {
         b->scr_seq.ensure(p.scr_total);
-        if (flags & RUN_QUAL) b->scr_qual.ensure(p.scr_total);
+        if (flags & RUN_QUAL) {
+            b->scr_qual.ensure(p.scr_total);
+            b->scr_ops.ensure(p.scr_total + 64);
+            b->scr_cig.ensure(p.scr_total + 64);
+            b->rinfo.ensure((size_t)R * sizeof(RInfo));
+        }
     }
     if (want_perf) b->scr_raw.ensure(std::max<uint64_t>(p.raw_total, 16));
     D.scr_seq = b->scr_seq.as<uint8_t>();
     D.scr_qual = b->scr_qual.as<uint8_t>();
+    D.scr_ops = (flags & RUN_QUAL) ? b->scr_ops.as<uint8_t>() : nullptr;
+    D.scr_cig = (flags & RUN_QUAL) ? b->scr_cig.as<uint8_t>() : nullptr;
+    D.rinfo = (flags & RUN_QUAL) ? b->rinfo.as<RInfo>() : nullptr;
     D.scr_raw = want_perf ? b->scr_raw.as<uint8_t>() : nullptr;
     // output upper bounds
     b->out_cap[0] = want_bad ? (uint64_t)R * 128 + p.idsum + p.scr_total * (fastq ? 2 : 1) : 0;
@@ -709,22 +743,39 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         b->gws.ensure((size_t)slab_c[GWS_CLASS] * h->num_sms);
     }
     uint64_t* d_totals = (uint64_t*)((char*)b->counters.p + CNT_TOTALS);
-    CK(cudaMemsetAsync(b->counters.p, 0, 256, S));
+    // u32 words: [0..5] error-injection tickets | [8..15] totals (u64 x 4) | [16..21] expansion tickets | [24..29] qscore
+    // tickets | [32..40] debug | [48..53] redo counts | [56..61] redo tickets | [64..69] alignment tickets | [72..77] tickets of its 64-bit instance | [80..85] its work counts
+    CK(cudaMemsetAsync(b->counters.p, 0, 512, S));
     if (want_bad) b->mid.ensure(3 * p.scr_total + 64 * (uint64_t)R + 64);
-    // alignment trace words: one region per team of every PHASE 2 grid (the classes run concurrently)
+    // alignment trace cells.  FIN_FULL kernels: one region per team of the grid (the classes run concurrently; the redo
+    // launch of a class uses the regions of its first CTAs).  align_kernel: one region per warp, (Dg, Pv) of column j of
+    // the warp's 32 reads side by side.
     uint64_t trace_off[N_CLASSES] = {}, trace_team[N_CLASSES] = {}, trace_total = 0;
+    uint64_t atrace_off[N_CLASSES] = {}, atrace_warp[N_CLASSES] = {}, atrace_total = 0;
+    int agrid[N_CLASSES] = {};
     if (flags & RUN_QUAL)
         for (int c = 0; c < N_CLASSES; c++) {
             if (p.n_work[c] == 0) continue;
             const int W2 = c == GWS_CLASS ? GWS_W2 : CLASS_W[c];
             const int teams2 = c == GWS_CLASS ? 1 : (int)h->threads2[c] / 32 / CLASS_W[c];
-            const size_t grid2 = std::min<size_t>((size_t)h->num_sms, (p.n_work[c] + teams2 - 1) / teams2);
+            size_t grid2 = std::min<size_t>((size_t)h->num_sms, (p.n_work[c] + teams2 - 1) / teams2);
+            if (CLASS_W[c] < 24) grid2 = std::min<size_t>(grid2, 32);   // redo lists only
             trace_team[c] = trace_team_bytes(W2, ncap_c[c]);
             trace_off[c] = trace_total;
             trace_total += trace_team[c] * teams2 * grid2;
+            if (CLASS_W[c] < 24) {
+                const uint32_t cols = std::min<uint32_t>(ncap_c[c], ALIGN_WIDE_FROM) + 2;
+                atrace_warp[c] = (uint64_t)cols * 32 * sizeof(AlignCell2<uint64_t>);
+                // 8 warps per CTA; enough warps to fill the SMs, bounded by the reads there are and by 1.5 GB of cells
+                const uint64_t warps_mem = std::max<uint64_t>((1536ull << 20) / atrace_warp[c], 64);
+                const uint64_t warps = std::min<uint64_t>({(uint64_t)h->num_sms * 48, (p.n_work[c] + 31) / 32, warps_mem});
+                agrid[c] = (int)((warps + 7) / 8);
+                atrace_off[c] = atrace_total;
+                atrace_total += atrace_warp[c] * 8 * agrid[c];
+            }
         }
     b->trace.ensure(std::max<uint64_t>(trace_total, 16));
-
+    b->atrace.ensure(std::max<uint64_t>(atrace_total, 16));
     CK(cudaEventRecord(b->ev[0], S));
     uint32_t launches = 0;
     {
@@ -732,6 +783,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         b->work_keys.ensure((size_t)R * 4);
         b->work_sorted.ensure((size_t)R * 4);
         b->redo.ensure((size_t)R * 4);
+        b->redo64.ensure((size_t)R * 4);
         b->work_bins.ensure((size_t)WORK_BINS * 4);
         CK(cudaMemsetAsync(b->work_bins.p, 0, (size_t)WORK_BINS * 4, S));
         WorkSortParams WS{};
@@ -788,6 +840,23 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         P.redo = b->redo.as<uint32_t>() + (b->d_work[c] - b->work_sorted.as<uint32_t>());
         P.redo_count = b->counters.as<uint32_t>() + 48 + c;
         P.n_work_dev = nullptr;
+        AlignLaunch al{};
+        al.grid = agrid[c];
+        al.K.B = D;
+        al.K.work = P.work;
+        al.K.n_work = P.n_work;
+        al.K.counter = b->counters.as<uint32_t>() + 64 + c;
+        al.K.mid = P.mid;
+        al.K.trace = b->atrace.as<uint8_t>() + atrace_off[c];
+        al.K.trace_warp_bytes = atrace_warp[c];
+        al.K.k = (uint32_t)h->em.k;
+        al.K.flags = flags;
+        // the 32-bit instance hands its failures to the 64-bit one, which hands its own to the FIN_FULL redo list
+        al.redo64 = b->redo64.as<uint32_t>() + (b->d_work[c] - b->work_sorted.as<uint32_t>());
+        al.redo64_count = b->counters.as<uint32_t>() + 80 + c;
+        al.K.n_work_dev = nullptr;
+        al.K.redo = al.redo64;
+        al.K.redo_count = al.redo64_count;
         const int teams = c == GWS_CLASS ? 1 : SIM_WARPS / CLASS_W[c];
         int grid = (int)std::min<size_t>((size_t)h->num_sms, (P.n_work + teams - 1) / teams);
         Phase2Launch p2;
@@ -803,14 +872,14 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         if (used_streams < 4) CK(cudaStreamWaitEvent(st, b->ev_sorted, 0));
         used_streams++;
         switch (c) {
-            case 0: launch_sim<1, false>(st, P, h->smem_bytes[c], grid, p2); break;
-            case 1: launch_sim<2, false>(st, P, h->smem_bytes[c], grid, p2); break;
-            case 2: launch_sim<4, false>(st, P, h->smem_bytes[c], grid, p2); break;
-            case 3: launch_sim<8, false>(st, P, h->smem_bytes[c], grid, p2); break;
-            case 4: launch_sim<24, false>(st, P, h->smem_bytes[c], grid, p2); break;
-            default: launch_sim<24, true, GWS_W2>(st, P, h->smem_bytes[c], grid, p2); break;
+            case 0: launch_sim<1, false>(st, P, h->smem_bytes[c], grid, p2, al); break;
+            case 1: launch_sim<2, false>(st, P, h->smem_bytes[c], grid, p2, al); break;
+            case 2: launch_sim<4, false>(st, P, h->smem_bytes[c], grid, p2, al); break;
+            case 3: launch_sim<8, false>(st, P, h->smem_bytes[c], grid, p2, al); break;
+            case 4: launch_sim<24, false>(st, P, h->smem_bytes[c], grid, p2, al); break;
+            default: launch_sim<24, true, GWS_W2>(st, P, h->smem_bytes[c], grid, p2, al); break;
         }
-        launches += (flags & RUN_ERRORS) ? ((flags & RUN_QUAL) && CLASS_W[c] < 24 ? 3 : 2) : 1;
+        launches += !(flags & RUN_ERRORS) ? 1 : CLASS_W[c] >= 24 ? 2 : (flags & RUN_QUAL) ? 5 : 2;
         if (getenv("TKSM_SEQ_DEBUG") && (atoi(getenv("TKSM_SEQ_DEBUG")) & 8)) {
             const cudaError_t e = cudaStreamSynchronize(st);
             fprintf(stderr, "[debug] class %d (W=%d, %u reads, ncap %u): %s\n", c, CLASS_W[c], P.n_work, P.ncap, cudaGetErrorString(e));

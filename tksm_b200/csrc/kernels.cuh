@@ -220,7 +220,7 @@ __host__ __device__ inline uint32_t slab2_small_bytes(int W) { return MISC_WORDS
 __host__ __device__ inline uint32_t slab2_big_bytes(uint32_t ncap) { return (4 * ncap + 64 + 15u) & ~15u; }
 // columns of alignment trace one team needs room for (a chunk per thread, at least ALIGN_MIN_CHUNK columns each)
 __host__ __device__ inline uint64_t trace_team_bytes(int W, uint32_t ncap) {
-    const uint64_t cols = (uint64_t)(ncap / (32u * W) + 1 > ALIGN_MIN_CHUNK ? ncap / (32u * W) + 1 : ALIGN_MIN_CHUNK) * 32u * W;
+    const uint64_t cols = (uint64_t)(ncap / (32u * W) + 1 > 256u ? ncap / (32u * W) + 1 : 256u) * 32u * W;   // align_chunking, 64-bit band
     return cols * ALIGN_CELL_BYTES;
 }
 
@@ -798,7 +798,7 @@ template <int W, typename BV>
 __device__ __forceinline__ bool align_team_impl(const Team<W>& tm, AlignCtx<BV>& A, uint4* xch, uint32_t* misc, uint32_t* wsum,
                                                 uint32_t& eq_out, uint32_t& cols_out) {
     uint32_t lanes;
-    align_chunking(A.n, (uint32_t)Team<W>::SIZE, A.chunk, lanes);
+    align_chunking(A.n, (uint32_t)Team<W>::SIZE, 8u * (uint32_t)sizeof(BV), A.chunk, lanes);
     A.stride = (uint32_t)Team<W>::SIZE;
     const uint32_t l = (uint32_t)tm.rank;
     const bool active = l < lanes;
@@ -930,9 +930,16 @@ __device__ __forceinline__ bool align_team_impl(const Team<W>& tm, AlignCtx<BV>&
 // Expansion of the slot contents into the read, alignment of the read back to the fragment
 // (py/tksm_badread.py:613), qscores from the alignment's window cigars (:584-655).
 //   wsl: misc | compaction queues (shared memory);  ws: frag | slen | rb (shared, or global for the GWS class)
-// WIDE: 64-bit alignment band (PHASE 3 kernels: reads above ALIGN_WIDE_FROM slots and the redo lists); otherwise
-// 32-bit, and a read whose traceback leaves that band is put on the redo list of its class instead of finished.
-template <int W, bool GWS, bool WIDE>
+// MODE (one kernel each; reads of up to ALIGN_WIDE_FROM slots go EXPAND -> align_kernel -> QUAL, the others FULL):
+//   FIN_EXPAND  expansion only: read codes to the scr_ops arena, slot lengths behind the fragment in the `mid` record,
+//               (read length with flanks, trims) to rinfo; nothing but the small workspace part in shared memory;
+//   FIN_QUAL    qscores from the ops align_kernel left in scr_ops;
+//   FIN_FULL    expansion, team-parallel alignment with the 64-bit band, qscores, all on the workspace arrays:
+//               long reads and the redo lists (reads align_kernel gave up on).
+enum : int { FIN_EXPAND = 2, FIN_FULL = 3, FIN_QUAL = 4 };
+constexpr uint32_t RINFO_SKIP = 1;   // rinfo.w: the read is finished by the FIN_FULL kernel of its class
+
+template <int W, bool GWS, int MODE>
 __device__ __forceinline__ void finish_read(const Team<W>& tm, const SimParams& P, uint32_t r, uint8_t* ws, uint8_t* wsl,
                                             const uint8_t* lut3, uint8_t* trace) {
     constexpr int SIZE = Team<W>::SIZE;
@@ -943,11 +950,6 @@ __device__ __forceinline__ void finish_read(const Team<W>& tm, const SimParams& 
     uint8_t* qbase = wsl + MISC_WORDS * 4;
     uint32_t* wq_a = (uint32_t*)(qbase + (uint32_t)(tm.rank >> 5) * QUEUE_BYTES);
     uint32_t* wq_b = wq_a + 64;
-    uint8_t* frag = ws;
-    uint8_t* slen = ws + P.ncap + 32;
-    uint8_t* rb = slen + P.ncap;
-    const uint32_t* fragw = (const uint32_t*)frag;
-
     const uint32_t mol = B.read_mol[r];
     const uint32_t L = B.mol_raw_len[mol];
     const uint32_t k = (uint32_t)T.k;
@@ -960,7 +962,12 @@ __device__ __forceinline__ void finish_read(const Team<W>& tm, const SimParams& 
     const uint4* mid4 = (const uint4*)(P.mid + 3 * sbase + 64 * (uint64_t)r);
     const uint32_t key_q = (n + 3) >> 2, frag_q = (n + 32 + 15) >> 4;  // 16-byte units
     const uint32_t* gkey = (const uint32_t*)mid4;   // slot keys stay in global memory (each is read once or twice)
-    {
+    // fragment, slot lengths, read codes: workspace arrays (FIN_FULL), else the `mid` record and the scr_ops arena
+    uint8_t* frag = MODE == FIN_FULL ? ws : (uint8_t*)(mid4 + key_q);
+    uint8_t* slen = MODE == FIN_FULL ? ws + P.ncap + 32 : (uint8_t*)(mid4 + key_q + frag_q);
+    uint8_t* rb = MODE == FIN_FULL ? slen + P.ncap : (MODE == FIN_QUAL ? B.scr_cig : B.scr_ops) + sbase;
+    const uint32_t* fragw = (const uint32_t*)frag;
+    if (MODE == FIN_FULL) {
         uint4* f4 = (uint4*)frag;
         for (uint32_t x = tm.rank; x < frag_q; x += SIZE) f4[x] = mid4[key_q + x];
     }
@@ -971,16 +978,18 @@ __device__ __forceinline__ void finish_read(const Team<W>& tm, const SimParams& 
         return c == 0xFFFFu ? 1u : content_len(c);
     };
     uint32_t start_trim = 0, end_trim = 0;
-    for (uint32_t j = 0; j < k; j++) {
-        start_trim += key_len(j);
-        end_trim += key_len(n - k + j);
+    if (MODE != FIN_QUAL) {
+        for (uint32_t j = 0; j < k; j++) {
+            start_trim += key_len(j);
+            end_trim += key_len(n - k + j);
+        }
     }
     tm.sync();
 
     // ---- slot lengths -> read offsets; read bases into rb (codes) and the scratch arena (text);
     //      `ops_mode`: instead, the cigar ops of the edit script itself (used when the alignment fails)
     uint8_t* oseq = B.scr_seq + sbase;
-    const uint32_t rbcap = 2 * n;
+    const uint32_t rbcap = (MODE == FIN_FULL || B.scr_ops) ? 2 * n : 0u;   // no read codes without qscores
     uint32_t Ttot = 0;
     auto expand_pass = [&](const bool ops_mode) {
         uint32_t carry = 0;
@@ -1090,44 +1099,53 @@ __device__ __forceinline__ void finish_read(const Team<W>& tm, const SimParams& 
         Ttot = carry;
         tm.sync();
     };
-    expand_pass(false);
-    const uint32_t Lp = Ttot - start_trim - end_trim;
-    if (Ttot > rbcap) status |= ST_OPS_OVERFLOW;
-    if (Lp > scap) status |= ST_SCRATCH_OVERFLOW;
-    if (tm.rank == 0) {
-        B.read_len[r] = Lp;
-        B.status[r] = status;
+    if (MODE != FIN_QUAL) {
+        expand_pass(false);
+        const uint32_t Lp = Ttot - start_trim - end_trim;
+        if (Ttot > 2 * n) status |= ST_OPS_OVERFLOW;
+        if (Lp > scap) status |= ST_SCRATCH_OVERFLOW;
+        if (tm.rank == 0) {
+            B.read_len[r] = Lp;
+            B.status[r] = status;
+        }
+    }
+    if (MODE == FIN_EXPAND) {
+        // reads above ALIGN_WIDE_FROM slots take the 64-bit band at once: the FIN_FULL kernel of the class does them
+        const bool full = (P.flags & RUN_QUAL) && n > ALIGN_WIDE_FROM && !(status & (ST_OPS_OVERFLOW | ST_SCRATCH_OVERFLOW));
+        if (tm.rank == 0) {
+            if (B.rinfo) B.rinfo[r] = RInfo{Ttot, start_trim, end_trim, full ? RINFO_SKIP : 0u};
+            if (full) P.redo[atomicAdd(P.redo_count, 1u)] = r;
+        }
+        tm.sync();
+        return;
+    }
+    if (MODE == FIN_QUAL) {
+        const RInfo ri = B.rinfo[r];
+        if (ri.flags & RINFO_SKIP) return;
+        Ttot = ri.m;
+        start_trim = ri.start_trim;
+        end_trim = ri.end_trim;
     }
 
     // ---- qscores for the read bases that survive trimming
     if ((P.flags & RUN_QUAL) && !(status & (ST_OPS_OVERFLOW | ST_SCRATCH_OVERFLOW))) {
         // the read is aligned back to the fragment; the ops of the alignment replace the read codes in rb
-        {
+        if (MODE == FIN_FULL) {
             uint32_t eq = 0, cols = 0;
             bool ok = false;
-            if (!WIDE && n > ALIGN_WIDE_FROM) {
-                // long reads start with the 64-bit band (the 32-bit one is left somewhere along most of them)
-                if (tm.rank == 0) P.redo[atomicAdd(P.redo_count, 1u)] = r;
-                tm.sync();
-                return;
-            }
             if (!(P.flags & RUN_NO_ALIGN)) {
-                using BV = typename std::conditional<WIDE, uint64_t, uint32_t>::type;
+                using BV = uint64_t;
                 AlignCtx<BV> A;
                 A.frag = frag;
                 A.slen = slen;
                 A.rb = rb;
+                A.out = rb;
                 A.trace = (AlignCell<BV>*)trace;
                 A.cells = (uint32_t)(P.trace_bytes / sizeof(AlignCell<BV>));
                 A.oob = misc + MISC_ALIGN_OOB;
                 A.n = n;
                 A.m = Ttot;
                 ok = align_team_impl<W, BV>(tm, A, (uint4*)qbase, misc, wsum, eq, cols);
-                if (!WIDE && !ok && !(P.flags & RUN_NO_WIDE) && !misc[MISC_ALIGN_OOB]) {
-                    if (tm.rank == 0) P.redo[atomicAdd(P.redo_count, 1u)] = r;
-                    tm.sync();
-                    return;
-                }
             }
             tm.sync();
             if (misc[MISC_ALIGN_OOB]) {
@@ -1281,7 +1299,7 @@ __global__ void __launch_bounds__(PHASE >= 2 ? 1024 : SIM_THREADS, 1) simulate_k
     if (threadIdx.x < 64) lut3[threadIdx.x] = (uint8_t)((threadIdx.x & 3) + 3 * ((threadIdx.x >> 2) & 3) + 9 * (threadIdx.x >> 4));
     // the window of nine matches is by far the most frequent one: its alias row lives in shared memory
     uint32_t* q0row = (uint32_t*)(lut3 + 64);
-    if (PHASE >= 2 && P.T.q_t9 && threadIdx.x < 128) {
+    if ((PHASE == FIN_FULL || PHASE == FIN_QUAL) && P.T.q_t9 && threadIdx.x < 128) {
         const uint32_t e0 = P.T.q_t9[0];
         if (threadIdx.x < (1u << (e0 & 7u))) q0row[threadIdx.x] = P.T.q_alias[(e0 >> 3) + threadIdx.x];
     }
@@ -1291,7 +1309,12 @@ __global__ void __launch_bounds__(PHASE >= 2 ? 1024 : SIM_THREADS, 1) simulate_k
     uint8_t* pool = smem + qcls_bytes + SIM_FIXED_SMEM;
     uint8_t *ws, *wsl;
     size_t pool_used;
-    if (PHASE >= 2) {
+    if (PHASE == FIN_EXPAND || PHASE == FIN_QUAL) {
+        // no large arrays: P.slab_bytes is the small part
+        wsl = pool + (size_t)tm.id * P.slab_bytes;
+        ws = nullptr;
+        pool_used = (size_t)TEAMS * P.slab_bytes;
+    } else if (PHASE == FIN_FULL) {
         const uint32_t small = slab2_small_bytes(W);
         if (GWS) {
             wsl = pool;
@@ -1313,7 +1336,7 @@ __global__ void __launch_bounds__(PHASE >= 2 ? 1024 : SIM_THREADS, 1) simulate_k
         }
     }
     uint32_t* ticket = (uint32_t*)(pool + pool_used) + tm.id;
-    uint8_t* trace = PHASE >= 2 ? P.trace + ((size_t)blockIdx.x * TEAMS + tm.id) * P.trace_bytes : nullptr;
+    uint8_t* trace = PHASE == FIN_FULL ? P.trace + ((size_t)blockIdx.x * TEAMS + tm.id) * P.trace_bytes : nullptr;
     const uint32_t n_work = (PHASE == 3 && P.n_work_dev) ? *P.n_work_dev : P.n_work;
     while (true) {
         if (tm.rank == 0) *ticket = atomicAdd(P.counter, 1u);
@@ -1322,9 +1345,267 @@ __global__ void __launch_bounds__(PHASE >= 2 ? 1024 : SIM_THREADS, 1) simulate_k
         tm.sync();
         if (wi >= n_work) break;
         if (PHASE >= 2)
-            finish_read<W, GWS, PHASE == 3>(tm, P, P.work[wi], ws, wsl, lut3, trace);
+            finish_read<W, GWS, PHASE>(tm, P, P.work[wi], ws, wsl, lut3, trace);
         else
             inject_read<W, GWS>(tm, P, P.work[wi], ws, wsl, qcls_s);
+    }
+}
+
+// ------------------------------------------------------- align_kernel
+// Alignment of reads of up to ALIGN_WIDE_FROM slots: ONE THREAD PER READ, a warp takes 32 consecutive reads of the
+// sorted work list (near-equal lengths).  The forward pass is align.cuh's column step run over the whole read
+// (one chunk, true initial state: no assumptions, no rounds); fragment codes, slot lengths and read codes stream
+// through 8-byte windows fetched one window ahead; the (Dg, Pv) cells of column j of the 32 reads of a warp are
+// neighbours in the trace array ([(j - 1) * 32 + lane]: one coalesced store per column).  The traceback is the walk
+// of align_trace_chunk<TRACE_WRITE> over the whole read with the same windows running backwards and the next
+// column's cell fetched ahead; it writes op | dcount << 2 per read base to the scr_cig arena (the read codes stay
+// intact).  A read whose walk leaves the 32-bit band goes to a list the 64-bit instance of the kernel works off; one
+// that leaves that band too goes to the redo list of its class, where the FIN_FULL kernel gives it the edit script's
+// own cigar.
+struct AlignKParams {
+    DevBatch B;
+    const uint32_t* work;
+    uint32_t n_work;
+    uint32_t* counter;      // work ticket
+    const uint8_t* mid;
+    uint8_t* trace;         // trace_warp_bytes per warp of the grid
+    uint64_t trace_warp_bytes;
+    uint32_t k;
+    uint32_t flags;
+    uint32_t* redo;         // reads this kernel gives up on: for its 64-bit instance (32-bit instance) / the FIN_FULL kernel
+    uint32_t* redo_count;
+    const uint32_t* n_work_dev;   // 64-bit instance: number of entries of `work` (device memory)
+};
+
+// sequential bytes of a global array through 8-byte windows, the next window in flight (base 8-byte aligned; reads up
+// to 15 bytes past the last byte asked for)
+struct ByteStream {
+    const uint2* p;
+    uint64_t win, nxt;
+    uint32_t left;
+    __device__ __forceinline__ static uint64_t ld(const uint2* q) {
+        const uint2 v = __ldg(q);
+        return ((uint64_t)v.y << 32) | v.x;
+    }
+    __device__ __forceinline__ void open(const uint8_t* base) {
+        p = (const uint2*)base;
+        win = ld(p++);
+        nxt = ld(p++);
+        left = 8;
+    }
+    __device__ __forceinline__ uint32_t next() {
+        if (left == 0) {
+            win = nxt;
+            nxt = ld(p++);
+            left = 8;
+        }
+        const uint32_t c = (uint32_t)win & 0xFFu;
+        win >>= 8;
+        left--;
+        return c;
+    }
+};
+// the same running backwards: byte(idx) for non-increasing idx
+struct ByteStreamBack {
+    const uint2* base;
+    uint64_t win, nxt;
+    uint32_t q;   // window holds bytes [8 q, 8 q + 8)
+    __device__ __forceinline__ void open(const uint8_t* b, uint32_t idx) {
+        base = (const uint2*)b;
+        q = idx >> 3;
+        win = ByteStream::ld(base + q);
+        nxt = q ? ByteStream::ld(base + q - 1) : 0ull;
+    }
+    __device__ __forceinline__ uint32_t at(uint32_t idx) {
+        while ((idx >> 3) != q) {   // one window down as a rule; more after a long run of D or I moves
+            q--;
+            win = nxt;
+            if (q) nxt = ByteStream::ld(base + q - 1);
+        }
+        return (uint32_t)(win >> (8u * (idx & 7u))) & 0xFFu;
+    }
+};
+
+template <typename BV>
+__device__ __forceinline__ bool align_one(const uint8_t* frag, const uint8_t* slen, const uint8_t* rb, uint8_t* out, uint32_t n,
+                                          uint32_t m, AlignCell2<BV>* cells, uint32_t& eq_out, uint32_t& cols_out) {
+    constexpr uint32_t BW = 8 * sizeof(BV);
+    // ---- forward: the column step of align_forward_chunk over columns 1 .. n from the true boundary
+    {
+        ByteStream fs, ls, rs;
+        fs.open(frag);
+        ls.open(slen);
+        rs.open(rb);
+        AlignPlanes<BV> pl;
+        pl.b0 = pl.b1 = pl.v = pl.np = 0;
+        for (uint32_t b = 0; b < BW && b < m; b++) pl.put(rs.next(), b);
+        BV Pv = ~BV(0), Mv = 0;
+        uint32_t o_prev = 0, lo_prev = 1;
+        AlignCell2<BV>* cell = cells;
+        for (uint32_t j = 1; j <= n; j++, cell += 32) {
+            const uint32_t o = o_prev + ls.next();
+            const uint32_t lo = align_lo<BV>(o);
+            const uint32_t s = lo - lo_prev;
+            if (s) {
+                Pv = (Pv >> s) | (~BV(0) << (BW - s));
+                Mv >>= s;
+                pl.b0 >>= s;
+                pl.b1 >>= s;
+                pl.v >>= s;
+                pl.np >>= s;
+                for (uint32_t t = 0; t < s; t++)
+                    if (lo_prev + BW + t <= m) pl.put(rs.next(), BW - s + t);
+            } else if (lo > 1) {
+                Pv &= ~BV(1);
+                Mv |= BV(1);
+            }
+            const uint32_t f = fs.next();
+            BV Eq;
+            if (f < 4) {
+                const BV f0 = BV(0) - BV(f & 1u), f1 = BV(0) - BV(f >> 1);
+                Eq = pl.v & ~((pl.b0 ^ f0) | (pl.b1 ^ f1));
+            } else if (f == 78u) {
+                Eq = pl.np;
+            } else {
+                Eq = 0;
+                for (uint32_t b = 0; b < BW; b++) {
+                    const uint32_t row = lo + b;
+                    if (row > m) break;
+                    if (rb[row - 1] == f) Eq |= BV(1) << b;
+                }
+            }
+            const BV Xv = Eq | Mv;
+            const BV Xh = (((Eq & Pv) + Pv) ^ Pv) | Eq;
+            BV Ph = Mv | ~(Xh | Pv);
+            BV Mh = Pv & Xh;
+            const BV D0 = Xh | Mv;
+            Ph = (Ph << 1) | BV(1);
+            Mh <<= 1;
+            Pv = Mh | ~(Xv | Ph);
+            Mv = Ph & Xv;
+            AlignCell2<BV> c;
+            c.dg = Eq | ~D0;
+            c.pv = Pv;
+            *cell = c;
+            o_prev = o;
+            lo_prev = lo;
+        }
+    }
+    // ---- traceback over the whole read (align_trace_chunk<TRACE_WRITE> with cmin = 1, bottom, top)
+    uint32_t i = m, j = n, oj = m, lo = align_lo<BV>(oj);
+    ByteStreamBack lb, fb, rbk;
+    if (n) {
+        lb.open(slen, n - 1);
+        fb.open(frag, n - 1);
+    }
+    if (m) rbk.open(rb, m - 1);
+    // cells of columns j, j - 1, j - 2, j - 3: the trace array is in DRAM by now, the loads run four columns ahead
+    AlignCell2<BV> cur{}, nx1{}, nx2{}, nx3{};
+    if (j > 0) cur = cells[(size_t)(j - 1) * 32];
+    if (j > 1) nx1 = cells[(size_t)(j - 2) * 32];
+    if (j > 2) nx2 = cells[(size_t)(j - 3) * 32];
+    if (j > 3) nx3 = cells[(size_t)(j - 4) * 32];
+    auto step_left = [&]() {   // to column j - 1
+        oj -= lb.at(j - 1);
+        j--;
+        lo = align_lo<BV>(oj);
+        cur = nx1;
+        nx1 = nx2;
+        nx2 = nx3;
+        if (j > 3) nx3 = cells[(size_t)(j - 4) * 32];
+    };
+    bool have = false;
+    uint32_t bi = 0, op = 0, run = 0, eq = 0, cols = 0, acc = 0;
+    auto flush = [&]() {
+        if (have) {
+            acc |= (op | ((run > ALIGN_DC_CAP ? ALIGN_DC_CAP : run) << 2)) << (8u * (bi & 3u));
+            if ((bi & 3u) == 0) {   // four ops per store (the array is 16-byte aligned and padded)
+                *(uint32_t*)(out + bi) = acc;
+                acc = 0;
+            }
+            eq += op == 0u;
+            cols += 1 + run;
+        } else {
+            cols += run;   // D run after the last read base
+        }
+    };
+    while (true) {
+        uint32_t d;
+        if (i == 0) {
+            if (j == 0) break;
+            d = MV_LEFT;
+        } else if (j == 0) {
+            d = MV_UP;
+        } else {
+            if (i < lo + (lo > 1 ? ALIGN_MARGIN : 0u) || i + ALIGN_MARGIN >= lo + BW) return false;
+            const uint32_t b = i - lo;
+            d = ((cur.dg >> b) & 1) ? MV_DIAG : ((cur.pv >> b) & 1) ? MV_UP : MV_LEFT;
+        }
+        if (d == MV_LEFT) {
+            run++;
+            step_left();
+            continue;
+        }
+        flush();
+        bi = i - 1;
+        have = true;
+        run = 0;
+        op = 2u;   // OP_I
+        i--;
+        if (d == MV_DIAG) {
+            op = rbk.at(bi) == fb.at(j - 1) ? 0u : 1u;   // OP_EQ : OP_X
+            step_left();
+        }
+    }
+    flush();
+    eq_out = eq;
+    cols_out = cols;
+    return true;
+}
+
+template <typename BV>
+__global__ void __launch_bounds__(256) align_kernel(const AlignKParams K) {
+    const uint32_t n_work = K.n_work_dev ? *K.n_work_dev : K.n_work;
+    const DevBatch& B = K.B;
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    uint8_t* region = K.trace + (size_t)warp * K.trace_warp_bytes;
+    while (true) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(K.counter, 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n_work) break;
+        const uint32_t wi = base + lane;
+        if (wi < n_work) {
+            const uint32_t r = K.work[wi];
+            const RInfo ri = B.rinfo[r];
+            const uint32_t st = B.status[r];
+            if ((!(ri.flags & RINFO_SKIP) || sizeof(BV) == 8) && !(st & (ST_OPS_OVERFLOW | ST_SCRATCH_OVERFLOW))) {
+                const uint32_t n = B.mol_raw_len[B.read_mol[r]] + 2 * K.k;
+                const uint64_t sbase = B.scr_off[r];
+                const uint4* mid4 = (const uint4*)(K.mid + 3 * sbase + 64 * (uint64_t)r);
+                const uint32_t key_q = (n + 3) >> 2, frag_q = (n + 32 + 15) >> 4;
+                const uint8_t* frag = (const uint8_t*)(mid4 + key_q);
+                const uint8_t* slen = (const uint8_t*)(mid4 + key_q + frag_q);
+                const uint8_t* rb = B.scr_ops + sbase;
+                uint8_t* out = B.scr_cig + sbase;
+                uint32_t eq = 0, cols = 0;
+                bool ok = false;
+                if (!(K.flags & RUN_NO_ALIGN) && !(sizeof(BV) == 8 && (K.flags & RUN_NO_WIDE)))
+                    ok = align_one<BV>(frag, slen, rb, out, n, ri.m, (AlignCell2<BV>*)region + lane, eq, cols);
+                if (ok) {
+                    B.ident_num[r] = eq;
+                    B.ident_den[r] = cols | IDENT_MEASURED;
+                    if (sizeof(BV) == 8) B.rinfo[r].flags = ri.flags & ~RINFO_SKIP;
+                } else {
+                    // the band was left: the read goes on to the 64-bit instance, from there to the FIN_FULL kernel of the
+                    // class (which gives it the edit script's own cigar); the qscore kernel leaves it alone meanwhile
+                    B.rinfo[r].flags = ri.flags | RINFO_SKIP;
+                    K.redo[atomicAdd(K.redo_count, 1u)] = r;
+                }
+            }
+        }
+        __syncwarp();
     }
 }
 
