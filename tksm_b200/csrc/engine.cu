@@ -462,7 +462,14 @@ void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, const P
     Q.counter = counters + 16;
     launch_sim_phase<W, GWS, FIN_EXPAND>(stream, Q, smem_small, grid_small, 1024);
     if (!(P.flags & RUN_QUAL)) return;
-    align_kernel<uint32_t><<<al.grid, 256, 0, stream>>>(al.K);
+    constexpr int AW = ALIGN_K_THREADS / 32;
+    static bool attr_set = false;
+    if (!attr_set) {
+        CK(cudaFuncSetAttribute(align_kernel<uint32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(AW * align_warp_smem<uint32_t>())));
+        CK(cudaFuncSetAttribute(align_kernel<uint64_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(AW * align_warp_smem<uint64_t>())));
+        attr_set = true;
+    }
+    align_kernel<uint32_t><<<al.grid, ALIGN_K_THREADS, AW * align_warp_smem<uint32_t>(), stream>>>(al.K);
     {
         // the few reads that left the 32-bit band (about one in a thousand)
         AlignKParams K2 = al.K;
@@ -471,7 +478,7 @@ void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, const P
         K2.counter = al.K.counter + 8;
         K2.redo = P.redo;
         K2.redo_count = P.redo_count;
-        align_kernel<uint64_t><<<std::min(al.grid, 16), 256, 0, stream>>>(K2);
+        align_kernel<uint64_t><<<std::min(al.grid, 32), ALIGN_K_THREADS, AW * align_warp_smem<uint64_t>(), stream>>>(K2);
     }
     CK(cudaGetLastError());
     Q.counter = counters + 24;
@@ -766,12 +773,13 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
             if (CLASS_W[c] < 24) {
                 const uint32_t cols = std::min<uint32_t>(ncap_c[c], ALIGN_WIDE_FROM) + 2;
                 atrace_warp[c] = (uint64_t)cols * 32 * sizeof(AlignCell2<uint64_t>);
-                // 8 warps per CTA; enough warps to fill the SMs, bounded by the reads there are and by 1.5 GB of cells
+                // enough warps to fill the SMs, bounded by the reads there are and by 1.5 GB of cells
                 const uint64_t warps_mem = std::max<uint64_t>((1536ull << 20) / atrace_warp[c], 64);
                 const uint64_t warps = std::min<uint64_t>({(uint64_t)h->num_sms * 48, (p.n_work[c] + 31) / 32, warps_mem});
-                agrid[c] = (int)((warps + 7) / 8);
+                constexpr int AW = ALIGN_K_THREADS / 32;
+                agrid[c] = (int)((warps + AW - 1) / AW);
                 atrace_off[c] = atrace_total;
-                atrace_total += atrace_warp[c] * 8 * agrid[c];
+                atrace_total += atrace_warp[c] * AW * agrid[c];
             }
         }
     b->trace.ensure(std::max<uint64_t>(trace_total, 16));

@@ -1428,7 +1428,7 @@ struct ByteStreamBack {
 
 template <typename BV>
 __device__ __forceinline__ bool align_one(const uint8_t* frag, const uint8_t* slen, const uint8_t* rb, uint8_t* out, uint32_t n,
-                                          uint32_t m, AlignCell2<BV>* cells, uint32_t& eq_out, uint32_t& cols_out) {
+                                          uint32_t m, AlignCell2<BV>* cells, uint8_t* sm, uint32_t& eq_out, uint32_t& cols_out) {
     constexpr uint32_t BW = 8 * sizeof(BV);
     // ---- forward: the column step of align_forward_chunk over columns 1 .. n from the true boundary
     {
@@ -1491,28 +1491,45 @@ __device__ __forceinline__ bool align_one(const uint8_t* frag, const uint8_t* sl
             lo_prev = lo;
         }
     }
-    // ---- traceback over the whole read (align_trace_chunk<TRACE_WRITE> with cmin = 1, bottom, top)
+    // ---- traceback over the whole read (align_trace_chunk<TRACE_WRITE> with cmin = 1, bottom, top).  The trace array
+    // is in DRAM by now and every step depends on the one before it, so the thread stages what the walk reads in
+    // shared memory 32 columns at a time (32 cells, 32 slot lengths, 32 fragment codes: all loads of a block in flight
+    // together) and the read codes 32 rows at a time.
+    const uint32_t lane = threadIdx.x & 31;
+    AlignCell2<BV>* sc = (AlignCell2<BV>*)sm + lane;                               // [column & 31][lane]
+    uint32_t* sl = (uint32_t*)(sm + 32 * 32 * sizeof(AlignCell2<BV>)) + lane;      // [word][lane]: slot lengths
+    uint32_t* sf = sl + 8 * 32;                                                    // fragment codes
+    uint32_t* sr = sf + 8 * 32;                                                    // read codes
+    uint32_t jb = 0xFFFFFFFFu, ib = 0xFFFFFFFFu;
+    auto col_block = [&](uint32_t nb) {   // columns with (j - 1) >> 5 == nb
+        jb = nb;
+        const uint32_t c0 = nb << 5;
+#pragma unroll 8
+        for (uint32_t c = 0; c < 32; c++)
+            if (c0 + c < n) sc[c * 32] = cells[(size_t)(c0 + c) * 32];
+        const uint4 a0 = __ldg((const uint4*)(slen + c0)), a1 = __ldg((const uint4*)(slen + c0) + 1);
+        const uint4 f0 = __ldg((const uint4*)(frag + c0)), f1 = __ldg((const uint4*)(frag + c0) + 1);
+        sl[0] = a0.x; sl[32] = a0.y; sl[64] = a0.z; sl[96] = a0.w; sl[128] = a1.x; sl[160] = a1.y; sl[192] = a1.z; sl[224] = a1.w;
+        sf[0] = f0.x; sf[32] = f0.y; sf[64] = f0.z; sf[96] = f0.w; sf[128] = f1.x; sf[160] = f1.y; sf[192] = f1.z; sf[224] = f1.w;
+    };
+    auto row_block = [&](uint32_t nb) {   // read bases with index >> 5 == nb
+        ib = nb;
+        const uint4 r0 = __ldg((const uint4*)(rb + (nb << 5))), r1 = __ldg((const uint4*)(rb + (nb << 5)) + 1);
+        sr[0] = r0.x; sr[32] = r0.y; sr[64] = r0.z; sr[96] = r0.w; sr[128] = r1.x; sr[160] = r1.y; sr[192] = r1.z; sr[224] = r1.w;
+    };
+    auto byte_of = [](const uint32_t* w, uint32_t idx) { return (w[((idx & 31u) >> 2) * 32] >> (8u * (idx & 3u))) & 0xFFu; };
     uint32_t i = m, j = n, oj = m, lo = align_lo<BV>(oj);
-    ByteStreamBack lb, fb, rbk;
-    if (n) {
-        lb.open(slen, n - 1);
-        fb.open(frag, n - 1);
-    }
-    if (m) rbk.open(rb, m - 1);
-    // cells of columns j, j - 1, j - 2, j - 3: the trace array is in DRAM by now, the loads run four columns ahead
-    AlignCell2<BV> cur{}, nx1{}, nx2{}, nx3{};
-    if (j > 0) cur = cells[(size_t)(j - 1) * 32];
-    if (j > 1) nx1 = cells[(size_t)(j - 2) * 32];
-    if (j > 2) nx2 = cells[(size_t)(j - 3) * 32];
-    if (j > 3) nx3 = cells[(size_t)(j - 4) * 32];
-    auto step_left = [&]() {   // to column j - 1
-        oj -= lb.at(j - 1);
-        j--;
+    AlignCell2<BV> cur{};
+    auto enter = [&]() {   // column j (> 0) becomes the current one
+        if (((j - 1) >> 5) != jb) col_block((j - 1) >> 5);
+        cur = sc[((j - 1) & 31u) * 32];
         lo = align_lo<BV>(oj);
-        cur = nx1;
-        nx1 = nx2;
-        nx2 = nx3;
-        if (j > 3) nx3 = cells[(size_t)(j - 4) * 32];
+    };
+    if (j > 0) enter();
+    auto step_left = [&]() {   // to column j - 1
+        oj -= byte_of(sl, j - 1);
+        j--;
+        if (j > 0) enter();
     };
     bool have = false;
     uint32_t bi = 0, op = 0, run = 0, eq = 0, cols = 0, acc = 0;
@@ -1553,7 +1570,8 @@ __device__ __forceinline__ bool align_one(const uint8_t* frag, const uint8_t* sl
         op = 2u;   // OP_I
         i--;
         if (d == MV_DIAG) {
-            op = rbk.at(bi) == fb.at(j - 1) ? 0u : 1u;   // OP_EQ : OP_X
+            if ((bi >> 5) != ib) row_block(bi >> 5);
+            op = byte_of(sr, bi) == byte_of(sf, j - 1) ? 0u : 1u;   // OP_EQ : OP_X
             step_left();
         }
     }
@@ -1563,8 +1581,15 @@ __device__ __forceinline__ bool align_one(const uint8_t* frag, const uint8_t* sl
     return true;
 }
 
+// shared memory of one warp of align_kernel<BV>: 32 cells + 3 x 32 bytes per thread
 template <typename BV>
-__global__ void __launch_bounds__(256) align_kernel(const AlignKParams K) {
+constexpr uint32_t align_warp_smem() { return 32u * (32u * (uint32_t)sizeof(AlignCell2<BV>) + 96u); }
+
+constexpr int ALIGN_K_THREADS = 128;
+template <typename BV>
+__global__ void __launch_bounds__(ALIGN_K_THREADS) align_kernel(const AlignKParams K) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint8_t* sm = smem + (threadIdx.x >> 5) * align_warp_smem<BV>();
     const uint32_t n_work = K.n_work_dev ? *K.n_work_dev : K.n_work;
     const DevBatch& B = K.B;
     const uint32_t lane = threadIdx.x & 31;
@@ -1592,7 +1617,7 @@ __global__ void __launch_bounds__(256) align_kernel(const AlignKParams K) {
                 uint32_t eq = 0, cols = 0;
                 bool ok = false;
                 if (!(K.flags & RUN_NO_ALIGN) && !(sizeof(BV) == 8 && (K.flags & RUN_NO_WIDE)))
-                    ok = align_one<BV>(frag, slen, rb, out, n, ri.m, (AlignCell2<BV>*)region + lane, eq, cols);
+                    ok = align_one<BV>(frag, slen, rb, out, n, ri.m, (AlignCell2<BV>*)region + lane, sm, eq, cols);
                 if (ok) {
                     B.ident_num[r] = eq;
                     B.ident_den[r] = cols | IDENT_MEASURED;
