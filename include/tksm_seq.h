@@ -40,7 +40,7 @@ typedef struct tksm_seq_config {
     double identity_stdev;
     int skip_qual_compute;    /* --skip-qual-compute */
     double calib_overshoot;  /* identity calibration: reference overshoot in errors per read, */
-    double calib_kappa;      /* alignment explain-away coefficient; NaN => built-in default for the model */
+    double calib_kappa;      /* alignment explain-away coefficient; NaN => measured on the device when the models are loaded */
     uint64_t batch_reads;     /* streaming batch limits, 0 => defaults */
     uint64_t batch_bases;
     int host_only;            /* 1 => no device (table packing / parsing only; run calls fail) */
@@ -87,6 +87,8 @@ typedef struct tksm_seq_tables {
     const uint8_t* qcls; size_t n_qcls;           /* 4^k change-probability classes (0 entries without a table) */
     const double* qrep; size_t n_qrep;            /* 256 class representatives */
     const uint16_t* thr; size_t n_thr;            /* [64 delta bins][256 classes][8]: P(N >= m) * 65536 */
+    float calib_kappa_measured;                   /* explain-away coefficient measured on the device when the models were
+                                                     loaded (NaN: host-only handle, or calib_kappa given in the config) */
 } tksm_seq_tables;
 
 void tksm_seq_default_config(tksm_seq_config* cfg);

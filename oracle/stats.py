@@ -69,6 +69,7 @@ def summarise(fastq_bytes, perfect_bytes, max_reads=None):
     len_ratio, identity, hdr_identity, sub, ins, dele, meanq, rawlen = [], [], [], [], [], [], [], []
     hp_err, hp_del, mq_cls = [], [], [[], [], []]   # per read: the unit the samples are independent in
     hp = np.zeros((HP_MAX + 1, HP_OBS), np.int64)
+    hp1 = np.zeros((HP_MAX + 1, HP_OBS), np.int64)  # the same over ONE run per read and run length (independent units)
     qh = np.zeros((3, 3, 94), np.int64)           # [position class][op class =,X,I][q]
     qh1 = np.zeros((3, 3, 94), np.int64)          # the same over ONE sampled base per read, position and op class
     ins_len = np.zeros(12, np.int64)
@@ -124,10 +125,20 @@ def summarise(fastq_bytes, perfect_bytes, max_reads=None):
         ends = np.concatenate((bnd, [L]))
         colbase = np.where(ops != D, seqa[np.clip(qidx, 0, len(seqa) - 1)], 0)
         n_hp = n_hp_err = n_hp_del = 0
-        for a, b in zip(starts, ends):
+        # the run of each length class that goes into hp1: drawn with the read's own generator
+        rls = np.minimum(ends - starts, HP_MAX)
+        pick = {}
+        for rl in range(1, HP_MAX + 1):
+            idx = np.flatnonzero(rls == rl)
+            if len(idx):
+                pick[int(idx[srng.integers(len(idx))])] = rl
+        for ri, (a, b) in enumerate(zip(starts, ends)):
             rl = b - a
             if rl < 3:
-                hp[min(rl, HP_MAX), min(int((colbase[tcol[a]:tcol[b - 1] + 1] == rawa[a]).sum()), HP_OBS - 1)] += 1
+                obs = min(int((colbase[tcol[a]:tcol[b - 1] + 1] == rawa[a]).sum()), HP_OBS - 1)
+                hp[min(rl, HP_MAX), obs] += 1
+                if ri in pick:
+                    hp1[min(rl, HP_MAX), obs] += 1
                 continue
             c0, c1 = tcol[a], tcol[b - 1]
             # extend over insertion columns adjacent to the run
@@ -137,6 +148,8 @@ def summarise(fastq_bytes, perfect_bytes, max_reads=None):
                 c1 += 1
             obs = int((colbase[c0:c1 + 1] == rawa[a]).sum())
             hp[min(rl, HP_MAX), min(obs, HP_OBS - 1)] += 1
+            if ri in pick:
+                hp1[min(rl, HP_MAX), min(obs, HP_OBS - 1)] += 1
             n_hp += 1
             n_hp_err += obs != rl
             n_hp_del += obs < rl
@@ -153,5 +166,5 @@ def summarise(fastq_bytes, perfect_bytes, max_reads=None):
         "sub_rate": sub, "ins_rate": ins, "del_rate": dele, "mean_q": meanq,
         "hp_err": hp_err, "hp_del": hp_del, "mean_q_eq": mq_cls[0], "mean_q_x": mq_cls[1], "mean_q_i": mq_cls[2],
         "rates": {"X": tot[1] / n_raw, "I": tot[2] / n_raw, "D": tot[3] / n_raw, "identity": tot[0] / n_cols},
-        "hp": hp.tolist(), "qhist": qh.tolist(), "qhist1": qh1.tolist(), "ins_len": ins_len.tolist(), "del_len": del_len.tolist(),
+        "hp": hp.tolist(), "hp1": hp1.tolist(), "qhist": qh.tolist(), "qhist1": qh1.tolist(), "ins_len": ins_len.tolist(), "del_len": del_len.tolist(),
     }

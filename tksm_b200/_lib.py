@@ -69,6 +69,7 @@ class Tables(C.Structure):
         ("qcls", C.POINTER(C.c_uint8)), ("n_qcls", C.c_size_t),
         ("qrep", C.POINTER(C.c_double)), ("n_qrep", C.c_size_t),
         ("thr", C.POINTER(C.c_uint16)), ("n_thr", C.c_size_t),
+        ("calib_kappa_measured", C.c_float),
     ]
 
 

@@ -271,7 +271,7 @@ struct tksm_seq {
     TailModel tail;           // loaded == false: no_noise
     IdentityHost idh;
     std::vector<float> delta;
-    float calib_overshoot = 0, calib_kappa = 0;
+    float calib_overshoot = 0, calib_kappa = 0, calib_kappa_measured = NAN;
     bool models_loaded = false;
     // device
     cudaStream_t stream = nullptr;       // uploads + kernels
@@ -1488,6 +1488,91 @@ struct MemorySource : tk::ChunkSource {
 
 // ============================================================== C ABI ====
 
+namespace {
+
+// PB1 stops a read on the identity of its own edit script (error g); what the reference stops on and
+// what the header prints is the identity of an optimal alignment (error a), which explains part of the edits away:
+// a = g - kappa g^2.  kappa depends on the error model's mix of substitutions, insertions and deletions, so it is
+// MEASURED when a model is loaded: 512 random fragments of 1000 bases (fixed seed) are simulated at four constant
+// target identities, once without and once with the alignment stage, and kappa is the least-squares coefficient of
+// g - a on g^2.  (oracle/fit_calibration.py measures the same with the CPU twin; the GPU suite compares the two.)
+constexpr int CALIB_MOLS = 512, CALIB_LEN = 1000;
+constexpr float CALIB_ALPHA = 0.161f, CALIB_BETA = 0.62f;   // oracle/fit_calibration.py
+constexpr float CALIB_KAPPA_UNMEASURED = 0.48f;            // host-only handles without calib_kappa in the config
+constexpr uint64_t CALIB_SEED = 0x5EEDCA11Bull;
+
+double self_calibrate(tksm_seq* h) {
+    std::string mdf;
+    mdf.reserve((size_t)CALIB_MOLS * (CALIB_LEN + 40));
+    uint64_t state = 12345;
+    for (int m = 0; m < CALIB_MOLS; m++) {
+        mdf += "+c" + std::to_string(m) + "\t1\t\n";
+        for (int i = 0; i < CALIB_LEN; i += 32) {
+            state += 0x9E3779B97F4A7C15ull;   // splitmix64
+            uint64_t z = state;
+            z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+            z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+            z ^= z >> 31;
+            for (int t = 0; t < 32 && i + t < CALIB_LEN; t++) mdf += "ACGT"[(z >> (2 * t)) & 3];
+        }
+        mdf += "\t0\t" + std::to_string(CALIB_LEN) + "\t+\t\n";   // unknown contig name: the name is the sequence (py/sequence.py:307)
+    }
+    // the settings of the run are put aside: constant targets, no calibration, no tails, the calibration seed
+    const DevTables saved = h->dt;
+    const TailModel saved_tail = h->tail;
+    const auto saved_skip = h->cfg.skip_qual_compute;
+    h->tail = TailModel();
+    double sx = 0, sy = 0;
+    {
+        tksm_seq_batch b;
+        GenomeStore no_genome;
+        MdfParser parser(&no_genome);
+        HostBatch hb;
+        parser.feed(mdf.data(), mdf.size(), true, hb);
+        prepare_host(h, {&hb}, b.prep);
+        b.prep.ordinal_base = 0;
+        slot_bind(h, &b);
+        const size_t R = b.prep.n_reads;
+        std::vector<uint32_t> gen(4 * R), ali(4 * R);
+        const double levels[4] = {0.78, 0.84, 0.90, 0.95};
+        for (double level : levels) {
+            h->dt.ident_const = 1;
+            h->dt.ident_mean = (float)level;
+            h->dt.calib_kappa = 0.0f;
+            h->dt.calib_overshoot = 0.0f;
+            h->dt.seed_lo = (uint32_t)CALIB_SEED;
+            h->dt.seed_hi = (uint32_t)(CALIB_SEED >> 32);
+            for (int pass = 0; pass < 2; pass++) {
+                h->cfg.skip_qual_compute = pass == 0;
+                slot_launch(h, &b, TKSM_SEQ_BADREAD, TKSM_SEQ_FASTQ_BADREAD);
+                tksm_seq_stats st;
+                slot_wait(h, &b, &st);
+                CK(cudaMemcpy((pass ? ali : gen).data(), b.per_read.p, 16 * R, cudaMemcpyDeviceToHost));
+            }
+            for (size_t r = 0; r < R; r++) {
+                if (!(ali[2 * R + r] & IDENT_MEASURED)) continue;   // not aligned (never expected here)
+                const double g = 1.0 - (double)gen[R + r] / (double)gen[2 * R + r];
+                const double a = 1.0 - (double)ali[R + r] / (double)(ali[2 * R + r] & ~IDENT_MEASURED);
+                sx += g * g * (g - a);
+                sy += g * g * g * g;
+            }
+        }
+    }
+    // (slot_bind may have committed the reference meanwhile: only the fields touched here are put back)
+    h->dt.ident_const = saved.ident_const;
+    h->dt.ident_mean = saved.ident_mean;
+    h->dt.calib_kappa = saved.calib_kappa;
+    h->dt.calib_overshoot = saved.calib_overshoot;
+    h->dt.seed_lo = saved.seed_lo;
+    h->dt.seed_hi = saved.seed_hi;
+    h->tail = saved_tail;
+    h->cfg.skip_qual_compute = saved_skip;
+    if (!(sy > 0)) throw std::runtime_error("identity calibration: no read was aligned");
+    return sx / sy;
+}
+
+}  // namespace
+
 extern "C" {
 
 void tksm_seq_default_config(tksm_seq_config* c) {
@@ -1681,23 +1766,23 @@ int tksm_seq_load_models(tksm_seq* h, const char* error_model, const char* qscor
     h->qm = load_qscore_model(qm, names.qscore);
     h->delta = make_delta_table(h->em);
     h->thr = make_threshold_table(h->em, h->delta);
-    // alignment explain-away coefficient of the PB1 edit statistics per error model
-    // (oracle/fit_calibration.py measures it with the CPU twin) and the reference's mean overshoot
-    // in errors for fragments it re-aligns whole (py/tksm_badread.py:408-413)
-    {
-        std::string base = em.substr(em.find_last_of('/') == std::string::npos ? 0 : em.find_last_of('/') + 1);
-        base = base.substr(0, base.find('.'));
-        double kappa = 0.45;
-        if (base == "nanopore2020") kappa = 0.43;
-        else if (base == "nanopore2018") kappa = 0.40;
-        else if (base == "pacbio2016") kappa = 0.58;
-        else if (base == "random") kappa = 0.44;
-        h->calib_overshoot = std::isnan(h->cfg.calib_overshoot) ? 0.8f : (float)h->cfg.calib_overshoot;
-        h->calib_kappa = std::isnan(h->cfg.calib_kappa) ? (float)kappa : (float)h->cfg.calib_kappa;
-    }
+    // the reference's mean overshoot in errors for fragments it re-aligns whole
+    // (py/tksm_badread.py:408-413); the explain-away coefficient of the error model is measured below
+    h->calib_overshoot = std::isnan(h->cfg.calib_overshoot) ? 0.8f : (float)h->cfg.calib_overshoot;
+    h->calib_kappa = std::isnan(h->cfg.calib_kappa) ? CALIB_KAPPA_UNMEASURED : (float)h->cfg.calib_kappa;
+    h->calib_kappa_measured = NAN;
     compute_classes(h);
     upload_models(h);
     h->models_loaded = true;
+    if (std::isnan(h->cfg.calib_kappa) && !h->cfg.host_only) {
+        // kappa of THIS error model, measured by simulating random fragments with and without the alignment stage; the
+        // effective target uses CALIB_ALPHA + CALIB_BETA kappa: real sequence explains less away than random sequence
+        // and the reference overshoots its target a little (constants fitted by oracle/fit_calibration.py on reference
+        // runs the distribution tests do not use)
+        h->calib_kappa_measured = (float)self_calibrate(h);
+        h->calib_kappa = CALIB_ALPHA + CALIB_BETA * h->calib_kappa_measured;
+        h->dt.calib_kappa = h->calib_kappa;
+    }
     API_END(h)
 }
 
@@ -1721,6 +1806,7 @@ int tksm_seq_get_tables(tksm_seq* h, tksm_seq_tables* t) {
     t->n_delta_tab = h->delta.size();
     t->calib_overshoot = h->calib_overshoot;
     t->calib_kappa = h->calib_kappa;
+    t->calib_kappa_measured = h->calib_kappa_measured;
     t->kq = h->qm.kq;
     t->q_direct = h->qm.direct.data();
     t->n_q_direct = h->qm.direct.size();

@@ -1428,13 +1428,14 @@ struct ByteStreamBack {
 
 template <typename BV>
 __device__ __forceinline__ bool align_one(const uint8_t* frag, const uint8_t* slen, const uint8_t* rb, uint8_t* out, uint32_t n,
-                                          uint32_t m, AlignCell2<BV>* cells, uint8_t* sm, uint32_t& eq_out, uint32_t& cols_out) {
+                                          uint32_t m, AlignCell2<BV>* cells, uint8_t* sm, bool valid, uint32_t& eq_out,
+                                          uint32_t& cols_out) {
+    // every thread of the warp comes here (`valid`: it has a read); n = m = 0 otherwise
     constexpr uint32_t BW = 8 * sizeof(BV);
-    // ---- forward: the column step of align_forward_chunk over columns 1 .. n from the true boundary
-    {
-        ByteStream fs, ls, rs;
-        fs.open(frag);
-        ls.open(slen);
+    // ---- forward: the column step of align_forward_chunk over columns 1 .. n from the true boundary, eight columns
+    //      per group (their slot lengths and fragment codes are two 8-byte words, fetched one group ahead)
+    if (valid) {
+        ByteStream rs;
         rs.open(rb);
         AlignPlanes<BV> pl;
         pl.b0 = pl.b1 = pl.v = pl.np = 0;
@@ -1442,53 +1443,64 @@ __device__ __forceinline__ bool align_one(const uint8_t* frag, const uint8_t* sl
         BV Pv = ~BV(0), Mv = 0;
         uint32_t o_prev = 0, lo_prev = 1;
         AlignCell2<BV>* cell = cells;
-        for (uint32_t j = 1; j <= n; j++, cell += 32) {
-            const uint32_t o = o_prev + ls.next();
-            const uint32_t lo = align_lo<BV>(o);
-            const uint32_t s = lo - lo_prev;
-            if (s) {
-                Pv = (Pv >> s) | (~BV(0) << (BW - s));
-                Mv >>= s;
-                pl.b0 >>= s;
-                pl.b1 >>= s;
-                pl.v >>= s;
-                pl.np >>= s;
-                for (uint32_t t = 0; t < s; t++)
-                    if (lo_prev + BW + t <= m) pl.put(rs.next(), BW - s + t);
-            } else if (lo > 1) {
-                Pv &= ~BV(1);
-                Mv |= BV(1);
-            }
-            const uint32_t f = fs.next();
-            BV Eq;
-            if (f < 4) {
-                const BV f0 = BV(0) - BV(f & 1u), f1 = BV(0) - BV(f >> 1);
-                Eq = pl.v & ~((pl.b0 ^ f0) | (pl.b1 ^ f1));
-            } else if (f == 78u) {
-                Eq = pl.np;
-            } else {
-                Eq = 0;
-                for (uint32_t b = 0; b < BW; b++) {
-                    const uint32_t row = lo + b;
-                    if (row > m) break;
-                    if (rb[row - 1] == f) Eq |= BV(1) << b;
+        const uint2* lp = (const uint2*)slen;
+        const uint2* fp = (const uint2*)frag;
+        uint64_t lw_n = ByteStream::ld(lp++), fw_n = ByteStream::ld(fp++);
+        for (uint32_t j0 = 1; j0 <= n; j0 += 8) {
+            const uint64_t lw = lw_n, fw = fw_n;
+            lw_n = ByteStream::ld(lp++);   // (reads up to 15 bytes past the arrays: inside the padded record)
+            fw_n = ByteStream::ld(fp++);
+#pragma unroll
+            for (uint32_t t8 = 0; t8 < 8; t8++) {
+                if (j0 + t8 > n) break;
+                const uint32_t o = o_prev + ((uint32_t)(lw >> (8 * t8)) & 0xFFu);
+                const uint32_t lo = align_lo<BV>(o);
+                const uint32_t s = lo - lo_prev;
+                if (s) {
+                    Pv = (Pv >> s) | (~BV(0) << (BW - s));
+                    Mv >>= s;
+                    pl.b0 >>= s;
+                    pl.b1 >>= s;
+                    pl.v >>= s;
+                    pl.np >>= s;
+                    for (uint32_t t = 0; t < s; t++)
+                        if (lo_prev + BW + t <= m) pl.put(rs.next(), BW - s + t);
+                } else if (lo > 1) {
+                    Pv &= ~BV(1);
+                    Mv |= BV(1);
                 }
+                const uint32_t f = (uint32_t)(fw >> (8 * t8)) & 0xFFu;
+                BV Eq;
+                if (f < 4) {
+                    const BV f0 = BV(0) - BV(f & 1u), f1 = BV(0) - BV(f >> 1);
+                    Eq = pl.v & ~((pl.b0 ^ f0) | (pl.b1 ^ f1));
+                } else if (f == 78u) {
+                    Eq = pl.np;
+                } else {
+                    Eq = 0;
+                    for (uint32_t b = 0; b < BW; b++) {
+                        const uint32_t row = lo + b;
+                        if (row > m) break;
+                        if (rb[row - 1] == f) Eq |= BV(1) << b;
+                    }
+                }
+                const BV Xv = Eq | Mv;
+                const BV Xh = (((Eq & Pv) + Pv) ^ Pv) | Eq;
+                BV Ph = Mv | ~(Xh | Pv);
+                BV Mh = Pv & Xh;
+                const BV D0 = Xh | Mv;
+                Ph = (Ph << 1) | BV(1);
+                Mh <<= 1;
+                Pv = Mh | ~(Xv | Ph);
+                Mv = Ph & Xv;
+                AlignCell2<BV> c;
+                c.dg = Eq | ~D0;
+                c.pv = Pv;
+                cell[(size_t)t8 * 32] = c;
+                o_prev = o;
+                lo_prev = lo;
             }
-            const BV Xv = Eq | Mv;
-            const BV Xh = (((Eq & Pv) + Pv) ^ Pv) | Eq;
-            BV Ph = Mv | ~(Xh | Pv);
-            BV Mh = Pv & Xh;
-            const BV D0 = Xh | Mv;
-            Ph = (Ph << 1) | BV(1);
-            Mh <<= 1;
-            Pv = Mh | ~(Xv | Ph);
-            Mv = Ph & Xv;
-            AlignCell2<BV> c;
-            c.dg = Eq | ~D0;
-            c.pv = Pv;
-            *cell = c;
-            o_prev = o;
-            lo_prev = lo;
+            cell += 8 * 32;
         }
     }
     // ---- traceback over the whole read (align_trace_chunk<TRACE_WRITE> with cmin = 1, bottom, top).  The trace array
@@ -1500,9 +1512,10 @@ __device__ __forceinline__ bool align_one(const uint8_t* frag, const uint8_t* sl
     uint32_t* sl = (uint32_t*)(sm + 32 * 32 * sizeof(AlignCell2<BV>)) + lane;      // [word][lane]: slot lengths
     uint32_t* sf = sl + 8 * 32;                                                    // fragment codes
     uint32_t* sr = sf + 8 * 32;                                                    // read codes
-    uint32_t jb = 0xFFFFFFFFu, ib = 0xFFFFFFFFu;
+    // The 32 threads of the warp stage their blocks TOGETHER: a thread walks until it needs a block it does not have,
+    // then waits for the others (a block is 32 columns, about 64 steps, for every thread), so the loads of a block are
+    // issued once for the warp instead of once per thread.
     auto col_block = [&](uint32_t nb) {   // columns with (j - 1) >> 5 == nb
-        jb = nb;
         const uint32_t c0 = nb << 5;
 #pragma unroll 8
         for (uint32_t c = 0; c < 32; c++)
@@ -1513,25 +1526,14 @@ __device__ __forceinline__ bool align_one(const uint8_t* frag, const uint8_t* sl
         sf[0] = f0.x; sf[32] = f0.y; sf[64] = f0.z; sf[96] = f0.w; sf[128] = f1.x; sf[160] = f1.y; sf[192] = f1.z; sf[224] = f1.w;
     };
     auto row_block = [&](uint32_t nb) {   // read bases with index >> 5 == nb
-        ib = nb;
         const uint4 r0 = __ldg((const uint4*)(rb + (nb << 5))), r1 = __ldg((const uint4*)(rb + (nb << 5)) + 1);
         sr[0] = r0.x; sr[32] = r0.y; sr[64] = r0.z; sr[96] = r0.w; sr[128] = r1.x; sr[160] = r1.y; sr[192] = r1.z; sr[224] = r1.w;
     };
     auto byte_of = [](const uint32_t* w, uint32_t idx) { return (w[((idx & 31u) >> 2) * 32] >> (8u * (idx & 3u))) & 0xFFu; };
-    uint32_t i = m, j = n, oj = m, lo = align_lo<BV>(oj);
+    uint32_t i = m, j = n, oj = m, lo = 1;
+    uint32_t jb = 0xFFFFFFFFu, ib = 0xFFFFFFFFu;
     AlignCell2<BV> cur{};
-    auto enter = [&]() {   // column j (> 0) becomes the current one
-        if (((j - 1) >> 5) != jb) col_block((j - 1) >> 5);
-        cur = sc[((j - 1) & 31u) * 32];
-        lo = align_lo<BV>(oj);
-    };
-    if (j > 0) enter();
-    auto step_left = [&]() {   // to column j - 1
-        oj -= byte_of(sl, j - 1);
-        j--;
-        if (j > 0) enter();
-    };
-    bool have = false;
+    bool have = false, failed = false;
     uint32_t bi = 0, op = 0, run = 0, eq = 0, cols = 0, acc = 0;
     auto flush = [&]() {
         if (have) {
@@ -1546,35 +1548,67 @@ __device__ __forceinline__ bool align_one(const uint8_t* frag, const uint8_t* sl
             cols += run;   // D run after the last read base
         }
     };
-    while (true) {
-        uint32_t d;
-        if (i == 0) {
-            if (j == 0) break;
-            d = MV_LEFT;
-        } else if (j == 0) {
-            d = MV_UP;
-        } else {
-            if (i < lo + (lo > 1 ? ALIGN_MARGIN : 0u) || i + ALIGN_MARGIN >= lo + BW) return false;
-            const uint32_t b = i - lo;
-            d = ((cur.dg >> b) & 1) ? MV_DIAG : ((cur.pv >> b) & 1) ? MV_UP : MV_LEFT;
+    bool done = !valid || (i | j) == 0;
+    while (!__all_sync(0xffffffffu, done)) {
+        if (!done) {
+            // the blocks of column j and of read base i - 1 (the one a move from here may consume)
+            if (j > 0 && ((j - 1) >> 5) != jb) {
+                jb = (j - 1) >> 5;
+                col_block(jb);
+            }
+            if (i > 0 && ((i - 1) >> 5) != ib) {
+                ib = (i - 1) >> 5;
+                row_block(ib);
+            }
+            if (j > 0) {
+                cur = sc[((j - 1) & 31u) * 32];
+                lo = align_lo<BV>(oj);
+            }
         }
-        if (d == MV_LEFT) {
-            run++;
-            step_left();
-            continue;
-        }
-        flush();
-        bi = i - 1;
-        have = true;
-        run = 0;
-        op = 2u;   // OP_I
-        i--;
-        if (d == MV_DIAG) {
-            if ((bi >> 5) != ib) row_block(bi >> 5);
-            op = byte_of(sr, bi) == byte_of(sf, j - 1) ? 0u : 1u;   // OP_EQ : OP_X
-            step_left();
+        while (!done) {
+            uint32_t d;
+            if (i == 0) {
+                d = MV_LEFT;
+            } else if (j == 0) {
+                d = MV_UP;
+            } else {
+                if (i < lo + (lo > 1 ? ALIGN_MARGIN : 0u) || i + ALIGN_MARGIN >= lo + BW) {
+                    failed = true;
+                    done = true;
+                    break;
+                }
+                const uint32_t b = i - lo;
+                d = ((cur.dg >> b) & 1) ? MV_DIAG : ((cur.pv >> b) & 1) ? MV_UP : MV_LEFT;
+            }
+            if (d == MV_LEFT) {
+                run++;
+            } else {
+                // a read base starts here: the one before it is complete (its D run is known now)
+                flush();
+                bi = i - 1;
+                have = true;
+                run = 0;
+                op = 2u;   // OP_I
+                i--;
+                if (d == MV_DIAG) op = byte_of(sr, bi) == byte_of(sf, j - 1) ? 0u : 1u;   // OP_EQ : OP_X
+            }
+            if (d != MV_UP) {   // to column j - 1
+                oj -= byte_of(sl, j - 1);
+                j--;
+            }
+            if ((i | j) == 0) {
+                done = true;
+                break;
+            }
+            // next cell: are its blocks here?
+            if ((j > 0 && ((j - 1) >> 5) != jb) || (i > 0 && ((i - 1) >> 5) != ib)) break;
+            if (d != MV_UP && j > 0) {
+                cur = sc[((j - 1) & 31u) * 32];
+                lo = align_lo<BV>(oj);
+            }
         }
     }
+    if (failed || !valid) return false;
     flush();
     eq_out = eq;
     cols_out = cols;
@@ -1601,33 +1635,42 @@ __global__ void __launch_bounds__(ALIGN_K_THREADS) align_kernel(const AlignKPara
         base = __shfl_sync(0xffffffffu, base, 0);
         if (base >= n_work) break;
         const uint32_t wi = base + lane;
+        bool valid = false;
+        uint32_t r = 0, n = 0, m = 0, rflags = 0;
+        const uint8_t *frag = nullptr, *slen = nullptr, *rb = nullptr;
+        uint8_t* out = nullptr;
         if (wi < n_work) {
-            const uint32_t r = K.work[wi];
+            r = K.work[wi];
             const RInfo ri = B.rinfo[r];
             const uint32_t st = B.status[r];
+            rflags = ri.flags;
             if ((!(ri.flags & RINFO_SKIP) || sizeof(BV) == 8) && !(st & (ST_OPS_OVERFLOW | ST_SCRATCH_OVERFLOW))) {
-                const uint32_t n = B.mol_raw_len[B.read_mol[r]] + 2 * K.k;
+                valid = true;
+                n = B.mol_raw_len[B.read_mol[r]] + 2 * K.k;
+                m = ri.m;
                 const uint64_t sbase = B.scr_off[r];
                 const uint4* mid4 = (const uint4*)(K.mid + 3 * sbase + 64 * (uint64_t)r);
                 const uint32_t key_q = (n + 3) >> 2, frag_q = (n + 32 + 15) >> 4;
-                const uint8_t* frag = (const uint8_t*)(mid4 + key_q);
-                const uint8_t* slen = (const uint8_t*)(mid4 + key_q + frag_q);
-                const uint8_t* rb = B.scr_ops + sbase;
-                uint8_t* out = B.scr_cig + sbase;
-                uint32_t eq = 0, cols = 0;
-                bool ok = false;
-                if (!(K.flags & RUN_NO_ALIGN) && !(sizeof(BV) == 8 && (K.flags & RUN_NO_WIDE)))
-                    ok = align_one<BV>(frag, slen, rb, out, n, ri.m, (AlignCell2<BV>*)region + lane, sm, eq, cols);
-                if (ok) {
-                    B.ident_num[r] = eq;
-                    B.ident_den[r] = cols | IDENT_MEASURED;
-                    if (sizeof(BV) == 8) B.rinfo[r].flags = ri.flags & ~RINFO_SKIP;
-                } else {
-                    // the band was left: the read goes on to the 64-bit instance, from there to the FIN_FULL kernel of the
-                    // class (which gives it the edit script's own cigar); the qscore kernel leaves it alone meanwhile
-                    B.rinfo[r].flags = ri.flags | RINFO_SKIP;
-                    K.redo[atomicAdd(K.redo_count, 1u)] = r;
-                }
+                frag = (const uint8_t*)(mid4 + key_q);
+                slen = (const uint8_t*)(mid4 + key_q + frag_q);
+                rb = B.scr_ops + sbase;
+                out = B.scr_cig + sbase;
+            }
+        }
+        uint32_t eq = 0, cols = 0;
+        const bool run_it = valid && !(K.flags & RUN_NO_ALIGN) && !(sizeof(BV) == 8 && (K.flags & RUN_NO_WIDE));
+        const bool ok = align_one<BV>(frag, slen, rb, out, run_it ? n : 0u, run_it ? m : 0u, (AlignCell2<BV>*)region + lane, sm,
+                                      run_it, eq, cols);
+        if (valid) {
+            if (ok) {
+                B.ident_num[r] = eq;
+                B.ident_den[r] = cols | IDENT_MEASURED;
+                if (sizeof(BV) == 8) B.rinfo[r].flags = rflags & ~RINFO_SKIP;
+            } else {
+                // the band was left: the read goes on to the 64-bit instance, from there to the FIN_FULL kernel of the
+                // class (which gives it the edit script's own cigar); the qscore kernel leaves it alone meanwhile
+                B.rinfo[r].flags = rflags | RINFO_SKIP;
+                K.redo[atomicAdd(K.redo_count, 1u)] = r;
             }
         }
         __syncwarp();
