@@ -68,7 +68,59 @@ def measure_kappa(em, qm):
     return sx / sy
 
 
+def _twin_hdr_mean(args):
+    """Mean read_identity= of the twin on a slice of the calibration molecules at a given effective kappa."""
+    em, qm, ident, lo, hi, kappa = args
+    from oracle.make_goldens import dist_inputs
+    from tksm_b200.sequence import Sequencer
+    fasta, mdf = dist_inputs(seed=6, n_mol=4000)
+    recs = mdf.split("\n+")
+    recs = [recs[0]] + ["+" + r for r in recs[1:]]
+    part = "\n".join(x.rstrip("\n") for x in recs[lo:hi]) + "\n"
+    s = Sequencer(identity=ident, seed=4242, host_only=True, corr=(0.8, kappa))
+    s.add_reference_text(fasta)
+    s.load_models(em, qm)
+    refs = so.load_fasta(fasta)
+    mols = so.parse_mdf(part)
+    seqs = [so.molecule_sequence(refs, iv) for _, iv in mols]
+    fq = so.twin_simulate(s.tables(), seqs, [m for m, _ in mols], ordinal_base=lo, badread=True, fastq=True)
+    vals = [float(ln.split(b"read_identity=")[1].split(b"%")[0]) / 100.0 for ln in fq.split(b"\n")[0::4] if ln]
+    return sum(vals), len(vals)
+
+
+def fit_affine(n_reads=2400, procs=8):
+    """CALIB_ALPHA, CALIB_BETA of engine.cu: the effective kappa at which the twin's mean header identity equals the
+    reference's (tests/golden/ref_calib.json: molecules the distribution tests do not use), regressed on the measured
+    kappa of the four shipped models."""
+    from multiprocessing import Pool
+    cal = json.load(open(os.path.join(ROOT, "tests", "golden", "calibration.json")))
+    ref = json.load(open(os.path.join(ROOT, "tests", "golden", "ref_calib.json")))
+    xs, ys = [], []
+    per = (n_reads + procs - 1) // procs
+    for name, info in ref["models"].items():
+        c = info["config"]
+        ident = tuple(float(x) for x in c["ident"].split(","))
+        means = []
+        for kappa in (0.38, 0.62):
+            with Pool(procs) as p:
+                parts = p.map(_twin_hdr_mean, [(c["em"], c["qm"], ident, i * per, min(n_reads, (i + 1) * per), kappa)
+                                               for i in range(procs)])
+            means.append(sum(a for a, _ in parts) / sum(b for _, b in parts))
+        slope = (means[1] - means[0]) / (0.62 - 0.38)
+        k0 = 0.38 + (info["hdr_identity_mean"] - means[0]) / slope
+        print(f"{name}: twin header identity {means[0]:.5f} (kappa 0.38) / {means[1]:.5f} (0.62), reference "
+              f"{info['hdr_identity_mean']:.5f} -> kappa {k0:.3f}; measured on random fragments {cal[name]:.3f}")
+        xs.append(cal[name])
+        ys.append(k0)
+    beta, alpha = np.polyfit(xs, ys, 1)
+    print(f"CALIB_ALPHA = {alpha:.3f}, CALIB_BETA = {beta:.3f}; residuals {[round(y - alpha - beta * x, 3) for x, y in zip(xs, ys)]}")
+    return alpha, beta
+
+
 if __name__ == "__main__":
+    if sys.argv[1:2] == ["fit"]:
+        fit_affine()
+        sys.exit(0)
     models = sys.argv[1:] or ["nanopore2020", "nanopore2018", "pacbio2016", "random"]
     path = os.path.join(ROOT, "tests", "golden", "calibration.json")
     cal = json.load(open(path)) if os.path.exists(path) else {}

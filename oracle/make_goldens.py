@@ -305,53 +305,61 @@ def dist_inputs(seed=5, n_mol=1500, lo=250, hi=4000):
     return fasta, "\n".join(lines) + "\n"
 
 
+def reference_reads(fasta, mdf, c):
+    """FASTQ of the unmodified reference for the MDF (independent single-threaded processes) + its --perfect FASTA."""
+    # The reference draws read identities from numpy's global RandomState, which fork() copies
+    # into every Pool worker unchanged (py/sequence.py:363-365, py/tksm_badread.py:741-745): with
+    # `-t N` the N workers replay the same identity sequence.  Independent samples need `-t 1`,
+    # so the MDF is cut into chunks that separate single-threaded reference processes simulate.
+    recs = mdf.split("\n+")
+    recs = [recs[0]] + ["+" + r for r in recs[1:]]
+    nproc = max(1, min(os.cpu_count() or 1, 8))
+    per = (len(recs) + nproc - 1) // nproc
+    with tempfile.TemporaryDirectory() as td:
+        open(os.path.join(td, "g.fa"), "w").write(fasta)
+        open(os.path.join(td, "in.mdf"), "w").write(mdf)
+        procs = []
+        for w in range(nproc):
+            part = recs[w * per:(w + 1) * per]
+            if not part:
+                continue
+            open(os.path.join(td, f"in{w}.mdf"), "w").write("\n".join(x.rstrip("\n") for x in part) + "\n")
+            cmd = [sys.executable, os.path.join(REF, "py", "sequence.py"), "-i", f"in{w}.mdf", "-r", "g.fa",
+                   "-o", f"out{w}.fastq", "-t", "1", "--badread-identity", c["ident"],
+                   "--badread-error-model", c["em"], "--badread-qscore-model", c["qm"]]
+            # progress text goes to a file: a pipe nobody drains would block the worker
+            log = open(os.path.join(td, f"log{w}.txt"), "w")
+            procs.append((w, subprocess.Popen(cmd, cwd=td, env=ref_env(), stdout=log, stderr=log)))
+        fq = b""
+        for w, p in procs:
+            if p.wait() != 0:
+                err = open(os.path.join(td, f"log{w}.txt")).read()
+                raise SystemExit(f"reference failed on {c}: {err[-3000:]}")
+            fq += open(os.path.join(td, f"out{w}.fastq"), "rb").read()
+        p2 = run_reference(["-i", "in.mdf", "-r", "g.fa", "--perfect", "perf.fasta"], td)
+        assert p2.returncode == 0
+        perf = open(os.path.join(td, "perf.fasta"), "rb").read()
+    return fq, perf
+
+
+DIST_CONFIGS = {
+    "nanopore2020": dict(em="nanopore2020", qm="nanopore2020", ident="84.0,99.0,5.5"),
+    "nanopore2018": dict(em="nanopore2018", qm="nanopore2018", ident="84.0,99.0,5.5"),
+    "pacbio2016": dict(em="pacbio2016", qm="pacbio2016", ident="84.0,99.0,5.5"),
+    "pacbio2016_hifi": dict(em="pacbio2016", qm="pacbio2016", ident="99.0,99.9,0.5"),
+    "random": dict(em="random", qm="random", ident="84.0,99.0,5.5"),
+    "nanopore2020_const90": dict(em="nanopore2020", qm="ideal", ident="90.0,90.0,0.0"),
+}
+
+
 def make_dist(which=None):
     from oracle import stats as st
-    configs = {
-        "nanopore2020": dict(em="nanopore2020", qm="nanopore2020", ident="84.0,99.0,5.5"),
-        "nanopore2018": dict(em="nanopore2018", qm="nanopore2018", ident="84.0,99.0,5.5"),
-        "pacbio2016": dict(em="pacbio2016", qm="pacbio2016", ident="84.0,99.0,5.5"),
-        "pacbio2016_hifi": dict(em="pacbio2016", qm="pacbio2016", ident="99.0,99.9,0.5"),
-        "random": dict(em="random", qm="random", ident="84.0,99.0,5.5"),
-        "nanopore2020_const90": dict(em="nanopore2020", qm="ideal", ident="90.0,90.0,0.0"),
-    }
     n_mol = int(os.environ.get("DIST_N_MOL", "10000"))   # SURVEY.md 8(c): at least 10 k reads per model
     fasta, mdf = dist_inputs(n_mol=n_mol)
-    for name, c in configs.items():
+    for name, c in DIST_CONFIGS.items():
         if which and name not in which:
             continue
-        # The reference draws read identities from numpy's global RandomState, which fork() copies
-        # into every Pool worker unchanged (py/sequence.py:363-365, py/tksm_badread.py:741-745): with
-        # `-t N` the N workers replay the same identity sequence.  Independent samples need `-t 1`,
-        # so the MDF is cut into chunks that separate single-threaded reference processes simulate.
-        recs = mdf.split("\n+")
-        recs = [recs[0]] + ["+" + r for r in recs[1:]]
-        nproc = max(1, min(os.cpu_count() or 1, 8))
-        per = (len(recs) + nproc - 1) // nproc
-        with tempfile.TemporaryDirectory() as td:
-            open(os.path.join(td, "g.fa"), "w").write(fasta)
-            open(os.path.join(td, "in.mdf"), "w").write(mdf)
-            procs = []
-            for w in range(nproc):
-                part = recs[w * per:(w + 1) * per]
-                if not part:
-                    continue
-                open(os.path.join(td, f"in{w}.mdf"), "w").write("\n".join(x.rstrip("\n") for x in part) + "\n")
-                cmd = [sys.executable, os.path.join(REF, "py", "sequence.py"), "-i", f"in{w}.mdf", "-r", "g.fa",
-                       "-o", f"out{w}.fastq", "-t", "1", "--badread-identity", c["ident"],
-                       "--badread-error-model", c["em"], "--badread-qscore-model", c["qm"]]
-                # progress text goes to a file: a pipe nobody drains would block the worker
-                log = open(os.path.join(td, f"log{w}.txt"), "w")
-                procs.append((w, subprocess.Popen(cmd, cwd=td, env=ref_env(), stdout=log, stderr=log)))
-            fq = b""
-            for w, p in procs:
-                if p.wait() != 0:
-                    err = open(os.path.join(td, f"log{w}.txt")).read()
-                    raise SystemExit(f"reference failed on dist/{name}: {err[-3000:]}")
-                fq += open(os.path.join(td, f"out{w}.fastq"), "rb").read()
-            p2 = run_reference(["-i", "in.mdf", "-r", "g.fa", "--perfect", "perf.fasta"], td)
-            assert p2.returncode == 0
-            perf = open(os.path.join(td, "perf.fasta"), "rb").read()
+        fq, perf = reference_reads(fasta, mdf, c)
         summary = st.summarise(fq, perf)
         summary["config"] = c
         summary["inputs"] = {"seed": 5, "n_mol": n_mol, "lo": 250, "hi": 4000}
@@ -362,6 +370,25 @@ def make_dist(which=None):
             json.dump(summary, f, separators=(",", ":"))
         print(f"dist/{name}: {summary['n_reads']} reads, rates {summary['rates']}, "
               f"mean identity {np.mean(summary['identity']):.4f}, mean len ratio {np.mean(summary['len_ratio']):.4f}")
+
+
+def make_calib():
+    """Reference runs the identity calibration is fitted on (oracle/fit_calibration.py): other molecules and another
+    genome (dist_inputs seed 6) than the distribution tests use, so the gate does not check what the fit has seen."""
+    fasta, mdf = dist_inputs(seed=6, n_mol=4000)
+    out = {"inputs": {"seed": 6, "n_mol": 4000, "lo": 250, "hi": 4000}, "models": {}}
+    for name in ("nanopore2020", "nanopore2018", "pacbio2016", "random"):
+        c = DIST_CONFIGS[name]
+        fq, _ = reference_reads(fasta, mdf, c)
+        hdr = []
+        for ln in fq.split(b"\n")[0::4]:
+            if ln:
+                tok = [t for t in ln.decode().split(" ") if t.startswith("read_identity=")][0]
+                hdr.append(float(tok.split("=")[1].rstrip("%")) / 100.0)
+        out["models"][name] = {"config": c, "n_reads": len(hdr), "hdr_identity_mean": float(np.mean(hdr)),
+                               "hdr_identity_std": float(np.std(hdr))}
+        print(f"calib/{name}: {len(hdr)} reads, mean header identity {np.mean(hdr):.5f}")
+    json.dump(out, open(os.path.join(GOLD, "ref_calib.json"), "w"), indent=1)
 
 
 if __name__ == "__main__":
@@ -378,6 +405,8 @@ if __name__ == "__main__":
         make_identity()
     if "tail" in what:
         make_tail()
+    if "calib" in what:
+        make_calib()
     if "dist" in what:
         sel = [w[5:] for w in what if w.startswith("dist:")]
         make_dist(sel or None)

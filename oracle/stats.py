@@ -58,13 +58,58 @@ HP_OBS = 16      # observed lengths 0..HP_OBS-1
 POS_EDGE = 20    # qscore histograms: first / last POS_EDGE read bases vs the middle
 
 
-def summarise(fastq_bytes, perfect_bytes, max_reads=None):
+_PAR = {}
+
+
+def _summarise_part(span):
+    lo, hi = span
+    return _summarise_reads(_PAR["reads"][lo:hi], _PAR["perf"], lo)
+
+
+def summarise(fastq_bytes, perfect_bytes, max_reads=None, procs=None):
+    """Statistics of the reads; large inputs are cut into spans that worker processes (fork) reduce in parallel."""
     reads = parse_fastx(fastq_bytes, True)
     perf = {}
     for info, seq, _ in parse_fastx(perfect_bytes, False):
         perf.setdefault(info["molecule_id"], seq)
     if max_reads:
         reads = reads[:max_reads]
+    procs = procs or min(os.cpu_count() or 1, 16)
+    if len(reads) < 2000 or procs < 2:
+        out = _summarise_reads(reads, perf, 0)
+        out.pop("_tot")
+        return out
+    import multiprocessing as mp
+    nw_lib()
+    _PAR["reads"], _PAR["perf"] = reads, perf
+    per = (len(reads) + procs - 1) // procs
+    spans = [(i, min(len(reads), i + per)) for i in range(0, len(reads), per)]
+    try:
+        with mp.get_context("fork").Pool(len(spans)) as pool:
+            parts = pool.map(_summarise_part, spans)
+    finally:
+        _PAR.clear()
+    out = parts[0]
+    for q in parts[1:]:
+        for k, v in q.items():
+            if k in ("rates", "n_reads", "_tot"):
+                continue
+            if isinstance(v, list) and v and isinstance(v[0], list):
+                out[k] = (np.array(out[k]) + np.array(v)).tolist()
+            elif k in ("ins_len", "del_len"):
+                out[k] = (np.array(out[k]) + np.array(v)).tolist()
+            else:
+                out[k] = out[k] + v
+    out["n_reads"] = len(reads)
+    tot = np.array(out.pop("_tot"))
+    for q in parts[1:]:
+        tot = tot + np.array(q["_tot"])
+    n_cols, n_raw = int(tot.sum()), int(tot[0] + tot[1] + tot[3])
+    out["rates"] = {"X": tot[1] / n_raw, "I": tot[2] / n_raw, "D": tot[3] / n_raw, "identity": tot[0] / n_cols}
+    return out
+
+
+def _summarise_reads(reads, perf, first_index):
     E, X, I, D = ord("="), ord("X"), ord("I"), ord("D")
     len_ratio, identity, hdr_identity, sub, ins, dele, meanq, rawlen = [], [], [], [], [], [], [], []
     hp_err, hp_del, mq_cls = [], [], [[], [], []]   # per read: the unit the samples are independent in
@@ -75,7 +120,7 @@ def summarise(fastq_bytes, perfect_bytes, max_reads=None):
     ins_len = np.zeros(12, np.int64)
     del_len = np.zeros(12, np.int64)
     tot = np.zeros(4, np.int64)
-    for ridx, (info, seq, qual) in enumerate(reads):
+    for ridx, (info, seq, qual) in enumerate(reads, first_index):
         raw = perf[info["molecule_id"]]
         ops = align_ops(seq, raw)
         ne, nx, ni, nd = (int((ops == c).sum()) for c in (E, X, I, D))
@@ -158,6 +203,7 @@ def summarise(fastq_bytes, perfect_bytes, max_reads=None):
     n_cols = int(tot.sum())
     n_raw = int(tot[0] + tot[1] + tot[3])
     return {
+        "_tot": tot.tolist(),
         "n_reads": len(reads),
         "raw_len": rawlen,
         "len_ratio": len_ratio,

@@ -1,23 +1,26 @@
 """Distributional parity with the unmodified reference (north_star: KS / chi-square p > 0.01).
 
-tests/golden/ref_dist_<config>.json.gz hold statistics of 1500 reads per configuration simulated by
+tests/golden/ref_dist_<config>.json.gz hold statistics of 10 000 reads per configuration simulated by
 the reference's py/sequence.py + py/tksm_badread.py (oracle/make_goldens.py dist; independent
 single-threaded runs).  Here the same molecules go through the PB1 model -- its CPU twin in the CPU
 suite, the CUDA path through the C ABI in the GPU suite (both are bit-identical, test_gpu_parity) --
-and the same statistics (oracle/stats.py: reads aligned back to their molecules) are compared.
+and the same statistics (oracle/stats.py: reads aligned back to their molecules) are compared:
 
-Known, documented deviations:
- * qscores follow the generative edit script instead of a re-alignment, so the pooled 1.7 M-base
-   qscore histograms of the read interior are compared by total variation and mean instead of a
-   chi-square test, whose power at that sample size rejects any model.  The `ideal` qscore model
-   makes the deviation maximally visible (every 'X'/'I' base of the reference gets Q1-3, every base
-   PB1 labels '=' gets Q4+): 13 % of the bases a re-alignment calls 'X' carry a generative '=' label
-   (a deletion next to an insertion ties with two substitutions), hence the wider TV limit for that
-   class under `ideal`.  Inserted bases are left-normalised inside homopolymers like an aligner
-   does (4 % mislabelled, was 23 % before), so 'I' is held to the common limit.
- * the `read_identity=` header token is PB1's *predicted* aligned identity; the reference prints the
-   identity of its own flank-inclusive alignment, which runs 0.15 points above the identity of the
-   read body.  The token is compared on mean and spread, the measured per-read identity by KS.
+  read length, per-read identity (measured and header), sub / ins / del rates, per-read homopolymer
+  error rates, per-read mean qscores (all, and of '=' / 'X' / 'I' bases)      two-sample KS
+  indel length spectra, homopolymer spectrum (observed length by run length),
+  qscore histograms by position class and cigar class                          chi-square homogeneity
+
+The chi-square tables are built from ONE run (one base) per read and cell (stats.py: hp1, qhist1), so that
+their units are independent (bases of one read share the read's identity).  Every test is held to
+p > 0.01; a family of k tables of one kind (10 run lengths, 9 qscore cells) to p > 0.01 / k.
+
+Since the read is aligned back to its fragment on the device (align.cuh) the way the reference does it
+(py/tksm_badread.py:613), qscores and the header identity need no tolerance of their own any more.
+One configuration keeps a documented deviation: with a CONSTANT target identity (nanopore2020_const90)
+the spread of the per-read identity is nothing but the noise of the reference's stopping rule, which has
+two regimes (whole-fragment alignment up to 1000 bases, sampled windows above; py/tksm_badread.py:408-432)
+that PB1 does not imitate; means and spread are compared there instead of the distribution's shape.
 """
 import gzip
 import json
@@ -62,13 +65,19 @@ def chi2_p(a, b, min_exp=5):
     return float(sps.chi2_contingency(np.array([A, B])).pvalue)
 
 
-def tv_noise(a, b):
-    """Total variation two samples of one multinomial show by chance: E|p1 - p2| summed over the
-    occupied cells is about 0.4 sqrt(k (1/n1 + 1/n2)); 1.5 times that is allowed on top of the model
-    tolerance, so the limit tightens to the model tolerance as the counts grow."""
-    a, b = np.asarray(a, float), np.asarray(b, float)
-    k = int(((a + b) > 0).sum())
-    return 1.5 * 0.4 * float(np.sqrt(k * (1.0 / a.sum() + 1.0 / b.sum())))
+SEED = 7   # the calibration constants were fitted on other molecules and other seeds (oracle/fit_calibration.py)
+
+
+def effective_kappa(em):
+    """What a device handle derives when it loads the model (engine.cu: CALIB_ALPHA + CALIB_BETA * measured kappa),
+    from the twin's measurement of the same coefficient (tests/golden/calibration.json); host-only handles cannot
+    measure."""
+    cal = json.load(open(os.path.join(GOLD, "calibration.json")))
+    base = os.path.basename(em).split(".")[0]
+    return CALIB_ALPHA + CALIB_BETA * cal[base]
+
+
+CALIB_ALPHA, CALIB_BETA = 0.095, 0.725   # engine.cu
 
 
 def setup(name, n_reads, host_only):
@@ -79,7 +88,7 @@ def setup(name, n_reads, host_only):
     fasta, mdf = dist_inputs(**ref["inputs"])
     recs = mdf.split("\n+")
     mdf = "\n+".join(recs[:n_reads]).rstrip("\n") + "\n"
-    s = Sequencer(identity=ident, seed=42, host_only=host_only)
+    s = Sequencer(identity=ident, seed=SEED, host_only=host_only, corr=(0.8, effective_kappa(c["em"])) if host_only else None)
     s.add_reference_text(fasta)
     s.load_models(c["em"], c["qm"])
     return ref, s, fasta, mdf
@@ -94,89 +103,61 @@ def twin_outputs(s, fasta, mdf):
             so.twin_simulate(s.tables(), seqs, ids, badread=False, fastq=False))
 
 
-def compare(name, mine, ref, qdev=True):
-    """qdev: the reads' qscores follow the generative edit script (PB1), not a re-alignment."""
+def compare(name, mine, ref):
     fails = []
     const = "const" in name
-    ideal = ref["config"]["qm"] == "ideal"
-    for k in ("len_ratio", "identity", "hdr_identity", "sub_rate", "ins_rate", "del_rate", "mean_q"):
-        a, b = np.array(mine[k]), np.array(ref[k])
-        if const and k in ("identity", "hdr_identity", "sub_rate", "del_rate", "ins_rate", "len_ratio"):
-            # constant target: the spread is the reference's estimation noise, which has two
-            # regimes (whole-fragment alignment up to 1000 bases, sampled windows above;
-            # py/tksm_badread.py:408-432) that PB1 does not imitate.  Means must agree.
-            tol = {"identity": 0.0015, "hdr_identity": 0.0025, "len_ratio": 0.003}.get(k, 0.0015)
-            if abs(a.mean() - b.mean()) > tol:
-                fails.append(f"{k}: mean {a.mean():.4f} vs reference {b.mean():.4f}")
-            if k == "identity" and not (0.6 < a.std() / b.std() < 1.6):
-                fails.append(f"{k}: std {a.std():.4f} vs reference {b.std():.4f}")
-            continue
-        p = sps.ks_2samp(a, b).pvalue
-        if k == "hdr_identity":
-            if abs(a.mean() - b.mean()) > 0.006 or not (0.8 < a.std() / b.std() < 1.25):
-                fails.append(f"{k}: mean {a.mean():.4f} / std {a.std():.4f} vs reference {b.mean():.4f} / {b.std():.4f}")
-            continue
-        if k == "mean_q" and qdev:
-            # DESIGN.md 3.7: tolerance on the per-read mean instead of KS for the one quantity the
-            # generative-cigar deviation shifts
-            if abs(a.mean() - b.mean()) > 0.6:
-                fails.append(f"{k}: mean {a.mean():.3f} vs reference {b.mean():.3f}")
-            continue
-        if p < P_MIN:
-            fails.append(f"{k}: KS p={p:.3g} (mean {a.mean():.4f} vs reference {b.mean():.4f})")
-    for k in ("ins_len", "del_len"):
-        p = chi2_p(mine[k], ref[k])
-        if p < P_MIN:
-            fails.append(f"{k}: chi2 p={p:.3g}")
-    # Homopolymer error spectrum and qscores per alignment class.  Bases of one read share the read's
-    # identity, so the independent unit is the read: per-read statistics are compared with KS; the
-    # pooled per-base tables are compared by chi-square only where they are small enough for the
-    # within-read clustering not to matter, and by total variation otherwise.
-    for k in ("hp_err", "hp_del", "mean_q_eq", "mean_q_x", "mean_q_i"):
-        a, b = np.array(mine[k]), np.array(ref[k])
+
+    def ks(key, k_family=1):
+        a, b = np.array(mine[key]), np.array(ref[key])
         a, b = a[a >= 0], b[b >= 0]
-        if const or len(a) < 50 or len(b) < 50:
-            continue
-        if k.startswith("mean_q") and qdev:
-            if abs(a.mean() - b.mean()) > 1.0:
-                fails.append(f"{k}: mean {a.mean():.2f} vs reference {b.mean():.2f}")
-            continue
+        if len(a) < 50 or len(b) < 50:
+            return
         p = sps.ks_2samp(a, b).pvalue
-        if p < P_MIN:
-            fails.append(f"{k}: KS p={p:.3g} (mean {a.mean():.4f} vs reference {b.mean():.4f})")
-    hm, hr = np.array(mine["hp"], float), np.array(ref["hp"], float)
-    for rl in range(1, hm.shape[0]):
-        if hm[rl].sum() < 100 or hr[rl].sum() < 100:
-            continue
-        tv = 0.5 * np.abs(hm[rl] / hm[rl].sum() - hr[rl] / hr[rl].sum()).sum()
-        if max(hm[rl].sum(), hr[rl].sum()) <= 20000 and not const:
-            p = chi2_p(hm[rl], hr[rl])
-            if p < P_MIN / 10:   # Bonferroni over the run lengths
-                fails.append(f"homopolymer run {rl}: chi2 p={p:.3g}")
-        lim = (0.03 if not const else 0.05) + tv_noise(hm[rl], hr[rl])
-        if tv > lim:
-            fails.append(f"homopolymer run {rl}: total variation {tv:.3f} > {lim:.3f}")
-    qm, qr = np.array(mine["qhist"], float), np.array(ref["qhist"], float)
-    for pc in range(3):
-        for oc, opname in enumerate("=XI"):
-            a, b = qm[pc, oc], qr[pc, oc]
-            if a.sum() < 200 or b.sum() < 200:
-                continue
-            tv = 0.5 * np.abs(a / a.sum() - b / b.sum()).sum()
-            ma, mb = (a * np.arange(94)).sum() / a.sum(), (b * np.arange(94)).sum() / b.sum()
-            lim = (0.16 if ideal and oc == 1 else 0.10) + tv_noise(a, b)
-            va = (a * (np.arange(94) - ma) ** 2).sum() / a.sum()
-            vb = (b * (np.arange(94) - mb) ** 2).sum() / b.sum()
-            mlim = 1.0 + 3.0 * float(np.sqrt(va / a.sum() + vb / b.sum()))
-            if tv > lim or abs(ma - mb) > mlim:
-                fails.append(f"qscores of '{opname}' bases, position class {pc}: TV {tv:.3f} > {lim:.3f}, "
-                             f"mean {ma:.2f} vs reference {mb:.2f}")
+        if p < P_MIN / k_family:
+            fails.append(f"{key}: KS p={p:.3g} (mean {a.mean():.4f} vs reference {b.mean():.4f})")
+
+    if const:
+        # constant target: the spread is the reference's estimation noise (module docstring): means and spread
+        for key, tol in (("identity", 0.0015), ("hdr_identity", 0.0015), ("len_ratio", 0.002), ("sub_rate", 0.001),
+                         ("ins_rate", 0.001), ("del_rate", 0.001)):
+            a, b = np.array(mine[key]), np.array(ref[key])
+            if abs(a.mean() - b.mean()) > tol:
+                fails.append(f"{key}: mean {a.mean():.4f} vs reference {b.mean():.4f}")
+            if key in ("identity", "hdr_identity") and not (0.75 < a.std() / b.std() < 1.33):
+                fails.append(f"{key}: std {a.std():.4f} vs reference {b.std():.4f}")
+    else:
+        for key in ("len_ratio", "identity", "hdr_identity", "sub_rate", "ins_rate", "del_rate"):
+            ks(key)
+        for key in ("hp_err", "hp_del"):
+            ks(key, 2)
+    for key in ("mean_q", "mean_q_eq", "mean_q_x", "mean_q_i"):
+        if not const:      # the per-read mean qscore follows the read's identity
+            ks(key, 4)
+    for key in ("ins_len", "del_len"):
+        p = chi2_p(mine[key], ref[key])
+        if p < P_MIN / 2:
+            fails.append(f"{key}: chi2 p={p:.3g}")
+    # homopolymer spectrum: observed length by run length, one run per read and run length
+    hm, hr = np.array(mine["hp1"], float), np.array(ref["hp1"], float)
+    rows = [rl for rl in range(1, hm.shape[0]) if hm[rl].sum() >= 100 and hr[rl].sum() >= 100]
+    for rl in rows:
+        p = chi2_p(hm[rl], hr[rl])
+        if p < P_MIN / len(rows):
+            fails.append(f"homopolymer run {rl}: chi2 p={p:.3g}")
+    # qscore histograms by position class (first 20 / middle / last 20 read bases) and cigar class, one base per read
+    qm, qr = np.array(mine["qhist1"], float), np.array(ref["qhist1"], float)
+    cells = [(pc, oc) for pc in range(3) for oc in range(3) if qm[pc, oc].sum() >= 100 and qr[pc, oc].sum() >= 100]
+    for pc, oc in cells:
+        p = chi2_p(qm[pc, oc], qr[pc, oc])
+        if p < P_MIN / len(cells):
+            fails.append(f"qscores of '{'=XI'[oc]}' bases, position class {pc}: chi2 p={p:.3g}")
     assert not fails, f"{name}: " + "; ".join(fails)
 
 
-CPU_CASES = [("nanopore2020", 500), ("pacbio2016_hifi", 500)]
-GPU_CASES = [("nanopore2020", 1500), ("nanopore2018", 700), ("pacbio2016", 700), ("pacbio2016_hifi", 700),
-             ("random", 700), ("nanopore2020_const90", 700)]
+CPU_CASES = [("nanopore2020", 600), ("pacbio2016_hifi", 600)]
+# 10 000 reads per model through the CUDA path
+GPU_CASES = [("nanopore2020", 10000), ("nanopore2018", 10000), ("pacbio2016", 10000), ("pacbio2016_hifi", 10000),
+             ("random", 10000), ("nanopore2020_const90", 10000)]
 
 
 @needs_models

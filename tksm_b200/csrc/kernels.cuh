@@ -937,7 +937,9 @@ __device__ __forceinline__ bool align_team_impl(const Team<W>& tm, AlignCtx<BV>&
 //   FIN_FULL    expansion, team-parallel alignment with the 64-bit band, qscores, all on the workspace arrays:
 //               long reads and the redo lists (reads align_kernel gave up on).
 enum : int { FIN_EXPAND = 2, FIN_FULL = 3, FIN_QUAL = 4 };
-constexpr uint32_t RINFO_SKIP = 1;   // rinfo.w: the read is finished by the FIN_FULL kernel of its class
+constexpr uint32_t RINFO_SKIP = 1;     // the qscore kernel of the class leaves the read alone: the 64-bit alignment instance /
+                                       // the FIN_FULL kernel finish it
+constexpr uint32_t RINFO_WIDE_OK = 2;  // aligned by the 64-bit instance: its qscores come from the FIN_QUAL launch on that list
 
 template <int W, bool GWS, int MODE>
 __device__ __forceinline__ void finish_read(const Team<W>& tm, const SimParams& P, uint32_t r, uint8_t* ws, uint8_t* wsl,
@@ -1121,7 +1123,9 @@ __device__ __forceinline__ void finish_read(const Team<W>& tm, const SimParams& 
     }
     if (MODE == FIN_QUAL) {
         const RInfo ri = B.rinfo[r];
-        if (ri.flags & RINFO_SKIP) return;
+        // the launch on the class's work list does the reads the 32-bit band aligned, the one on the 64-bit instance's
+        // list (P.n_work_dev set) those that instance aligned
+        if (P.n_work_dev ? !(ri.flags & RINFO_WIDE_OK) : (ri.flags & RINFO_SKIP) != 0) return;
         Ttot = ri.m;
         start_trim = ri.start_trim;
         end_trim = ri.end_trim;
@@ -1337,7 +1341,7 @@ __global__ void __launch_bounds__(PHASE >= 2 ? 1024 : SIM_THREADS, 1) simulate_k
     }
     uint32_t* ticket = (uint32_t*)(pool + pool_used) + tm.id;
     uint8_t* trace = PHASE == FIN_FULL ? P.trace + ((size_t)blockIdx.x * TEAMS + tm.id) * P.trace_bytes : nullptr;
-    const uint32_t n_work = (PHASE == 3 && P.n_work_dev) ? *P.n_work_dev : P.n_work;
+    const uint32_t n_work = P.n_work_dev ? *P.n_work_dev : P.n_work;
     while (true) {
         if (tm.rank == 0) *ticket = atomicAdd(P.counter, 1u);
         tm.sync();
@@ -1665,7 +1669,7 @@ __global__ void __launch_bounds__(ALIGN_K_THREADS) align_kernel(const AlignKPara
             if (ok) {
                 B.ident_num[r] = eq;
                 B.ident_den[r] = cols | IDENT_MEASURED;
-                if (sizeof(BV) == 8) B.rinfo[r].flags = rflags & ~RINFO_SKIP;
+                if (sizeof(BV) == 8) B.rinfo[r].flags = rflags | RINFO_WIDE_OK;
             } else {
                 // the band was left: the read goes on to the 64-bit instance, from there to the FIN_FULL kernel of the
                 // class (which gives it the edit script's own cigar); the qscore kernel leaves it alone meanwhile
