@@ -89,9 +89,9 @@ def _twin_hdr_mean(args):
 
 
 def fit_affine(n_reads=2400, procs=8):
-    """CALIB_ALPHA, CALIB_BETA of engine.cu: the effective kappa at which the twin's mean header identity equals the
-    reference's (tests/golden/ref_calib.json: molecules the distribution tests do not use), regressed on the measured
-    kappa of the four shipped models."""
+    """CALIB_OFFSET_TABLE / _RANDOM of engine.cu: the effective kappa at which the twin's mean header identity equals
+    the reference's (tests/golden/ref_calib.json: molecules the distribution tests do not use) minus the kappa
+    measured on random fragments, averaged over the shipped models of each family."""
     from multiprocessing import Pool
     cal = json.load(open(os.path.join(ROOT, "tests", "golden", "calibration.json")))
     ref = json.load(open(os.path.join(ROOT, "tests", "golden", "ref_calib.json")))
@@ -112,9 +112,13 @@ def fit_affine(n_reads=2400, procs=8):
               f"{info['hdr_identity_mean']:.5f} -> kappa {k0:.3f}; measured on random fragments {cal[name]:.3f}")
         xs.append(cal[name])
         ys.append(k0)
-    beta, alpha = np.polyfit(xs, ys, 1)
-    print(f"CALIB_ALPHA = {alpha:.3f}, CALIB_BETA = {beta:.3f}; residuals {[round(y - alpha - beta * x, 3) for x, y in zip(xs, ys)]}")
-    return alpha, beta
+    # one offset for the models with a k-mer table, one for the table-less `random` model (three points carry no slope)
+    names = list(ref["models"])
+    tab = [y - x for nm, x, y in zip(names, xs, ys) if nm != "random"]
+    rnd = [y - x for nm, x, y in zip(names, xs, ys) if nm == "random"]
+    print(f"CALIB_OFFSET_TABLE = {np.mean(tab):.3f} (per model {[round(v, 3) for v in tab]}), "
+          f"CALIB_OFFSET_RANDOM = {np.mean(rnd):.3f}")
+    return float(np.mean(tab)), float(np.mean(rnd))
 
 
 if __name__ == "__main__":

@@ -1541,7 +1541,11 @@ namespace {
 // target identities, once without and once with the alignment stage, and kappa is the least-squares coefficient of
 // g - a on g^2.  (oracle/fit_calibration.py measures the same with the CPU twin; the GPU suite compares the two.)
 constexpr int CALIB_MOLS = 512, CALIB_LEN = 1000;
-constexpr float CALIB_ALPHA = 0.095f, CALIB_BETA = 0.725f;   // oracle/fit_calibration.py fit (tests/golden/ref_calib.json)
+// effective kappa = measured kappa + offset: real sequence explains less away than the random fragments of the
+// measurement and the reference overshoots its target a little.  One constant for error models with a k-mer table, one
+// for the table-less `random` model; oracle/fit_calibration.py fit (reference runs of tests/golden/ref_calib.json, which
+// the distribution tests do not use)
+constexpr float CALIB_OFFSET_TABLE = -0.072f, CALIB_OFFSET_RANDOM = 0.026f;
 constexpr float CALIB_KAPPA_UNMEASURED = 0.48f;            // host-only handles without calib_kappa in the config
 constexpr uint64_t CALIB_SEED = 0x5EEDCA11Bull;
 
@@ -1821,12 +1825,9 @@ int tksm_seq_load_models(tksm_seq* h, const char* error_model, const char* qscor
     upload_models(h);
     h->models_loaded = true;
     if (std::isnan(h->cfg.calib_kappa) && !h->cfg.host_only) {
-        // kappa of THIS error model, measured by simulating random fragments with and without the alignment stage; the
-        // effective target uses CALIB_ALPHA + CALIB_BETA kappa: real sequence explains less away than random sequence
-        // and the reference overshoots its target a little (constants fitted by oracle/fit_calibration.py on reference
-        // runs the distribution tests do not use)
+        // kappa of THIS error model, measured by simulating random fragments with and without the alignment stage
         h->calib_kappa_measured = (float)self_calibrate(h);
-        h->calib_kappa = CALIB_ALPHA + CALIB_BETA * h->calib_kappa_measured;
+        h->calib_kappa = h->calib_kappa_measured + (h->em.has_table ? CALIB_OFFSET_TABLE : CALIB_OFFSET_RANDOM);
         h->dt.calib_kappa = h->calib_kappa;
     }
     API_END(h)
