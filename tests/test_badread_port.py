@@ -40,4 +40,4 @@ def test_port_matches_reference_distributions(built, name, n_reads):
     r1, _, _ = bp.simulate(model, seqs[:20], seed=3, threads=1)
     assert r1 == reads[:20]
     fq, pf = bp.to_fastq(seqs, ids, reads, quals, idn)
-    compare(name, st.summarise(fq, pf), ref, qdev=False)
+    compare(name, st.summarise(fq, pf), ref)

@@ -391,3 +391,78 @@ def test_gz_sink_blocks(world, tmp_path, monkeypatch):
     empty.write_bytes(b"")
     s.run_files(str(empty), badread=str(tmp_path / "e.fq.gz"))
     assert (tmp_path / "e.fq.gz").stat().st_size > 0 and gzip.open(tmp_path / "e.fq.gz").read() == b""
+
+
+# ---------------------------------------------------------------- BASELINE configs[0] at its size
+def _twin_span(args):
+    """One span of the molecules through the CPU twin (worker process)."""
+    tables_kw, fasta, mdf_part, lo, fastq = args
+    from tksm_b200.sequence import Sequencer
+    s = Sequencer(host_only=True, **tables_kw)
+    s.add_reference_text(fasta)
+    s.load_models("nanopore2020", "nanopore2020")
+    refs = so.load_fasta(fasta)
+    mols = so.parse_mdf(mdf_part)
+    seqs = [so.molecule_sequence(refs, iv) for _, iv in mols]
+    return so.twin_simulate(s.tables(), seqs, [m for m, _ in mols], ordinal_base=lo, badread=True, fastq=fastq)
+
+
+@pytest.mark.skipif(not HAVE_MODELS, reason="Badread model files not present")
+def test_c1_sized_run_matches_cpu_twin(built):
+    """BASELINE configs[0]: 10 k Tsb-shape molecules (multi-exon, both strands, depth > 1) from a 1 Mbp genome,
+    nanopore2020 models, FASTQ with qscores: the CUDA path against the CPU twin, byte for byte.  The twin runs in
+    worker processes over spans of the molecules (results depend on the global read ordinal only)."""
+    import multiprocessing as mp
+    from tksm_b200.sequence import BADREAD, Sequencer
+    rng = np.random.default_rng(31)
+    fasta = make_fasta(rng, [("chr1", 600000), ("chr2", 400000)])
+    s = Sequencer(seed=4321)
+    s.add_reference_text(fasta)
+    s.load_models("nanopore2020", "nanopore2020")
+    mdf = s.synth_mdf(0, 10000, seed=3, min_len=300, max_len=20000)
+    got = s.simulate(mdf, BADREAD, fastq=True)
+    assert s.last_stats["reads"] >= 10000 and s.last_stats["status_or"] & 3 == 0
+    # the twin needs the effective kappa the device measured
+    kw = dict(seed=4321, corr=(float(s.tables().calib_overshoot), float(s.tables().calib_kappa)))
+    text = mdf.decode()
+    recs = text.split("\n+")
+    recs = [recs[0]] + ["+" + r for r in recs[1:]]
+    depth = [int(r.split("\n", 1)[0].split("\t")[1]) for r in recs]
+    procs = min(os.cpu_count() or 1, 16)
+    per = (len(recs) + procs - 1) // procs
+    jobs, lo = [], 0
+    for i in range(0, len(recs), per):
+        part = "\n".join(x.rstrip("\n") for x in recs[i:i + per]) + "\n"
+        jobs.append((kw, fasta, part, lo, True))
+        lo += sum(depth[i:i + per])
+    with mp.get_context("fork").Pool(len(jobs)) as pool:
+        want = b"".join(pool.map(_twin_span, jobs))
+    d = first_diff(got, want, True)
+    assert d is None, d
+
+
+@pytest.mark.skipif(not HAVE_MODELS, reason="Badread model files not present")
+def test_model_given_by_path_under_another_name(built, tmp_path):
+    """--badread-error-model / --badread-qscore-model take a name or a path (py/tksm_badread.py:84-89).  Nothing may
+    hang on the file name: a copy under another name gives the same measured calibration and the same reads."""
+    import shutil
+    from tksm_b200.sequence import BADREAD, Sequencer
+    src = os.path.join(os.environ["TKSM_MODELS"], "badread")
+    em, qm = str(tmp_path / "my_flowcell.error.gz"), str(tmp_path / "my_flowcell.qscore.gz")
+    shutil.copy(os.path.join(src, "nanopore2018.error.gz"), em)
+    shutil.copy(os.path.join(src, "nanopore2018.qscore.gz"), qm)
+    rng = np.random.default_rng(5)
+    fasta = make_fasta(rng, [("chr1", 80000)])
+    outs, kappas = [], []
+    for e, q in (("nanopore2018", "nanopore2018"), (em, qm)):
+        s = Sequencer(seed=99)
+        s.add_reference_text(fasta)
+        s.load_models(e, q)
+        kappas.append((float(s.tables().calib_kappa_measured), float(s.tables().calib_kappa)))
+        outs.append(s.simulate(s.synth_mdf(1, 300, seed=8), BADREAD, fastq=True))
+    assert kappas[0] == kappas[1] and 0.2 < kappas[0][0] < 0.9
+    assert outs[0] == outs[1]
+    # and the device's measurement is the twin's (oracle/fit_calibration.py -> tests/golden/calibration.json)
+    import json
+    cal = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "calibration.json")))
+    assert kappas[0][0] == pytest.approx(cal["nanopore2018"], abs=2e-3)

@@ -64,6 +64,7 @@ extern "C" int tksm_sequence_main(int argc, char** argv) {
     std::vector<std::string> refs;
     bool have_err = false, have_qs = false, have_tail = false, skip_qual = false, have_input = false;
     long threads = 1;
+    bool threads_given = false;
     long long seed = 42;
     int device = 0;
     long gpus = getenv("TKSM_GPUS") ? atol(getenv("TKSM_GPUS")) : 1;   // extension: $TKSM_GPUS / --gpus
@@ -151,6 +152,7 @@ extern "C" int tksm_sequence_main(int argc, char** argv) {
         } else if (d == "threads") {
             char* e = nullptr;
             threads = strtol(vals[0].c_str(), &e, 10);
+            threads_given = true;
             if (*e) return usage_error("argument -t/--threads: invalid int value: '" + vals[0] + "'");
         } else if (d == "badread_identity") {
             identity = vals[0];
@@ -240,7 +242,9 @@ extern "C" int tksm_sequence_main(int argc, char** argv) {
     else if (gpus > 1)
         devices.resize((size_t)gpus, devices.back());
     const int n = (int)devices.size();
-    const long host_threads = threads > 0 ? std::min<long>(threads, 256) : 1;  // -t: host parser threads (default 1)
+    // -t sizes the host parser pool here (the reference forks that many workers, default 1): without -t every hardware
+    // thread is used (0), split between the GPUs
+    const long host_threads = !threads_given ? 0 : threads > 0 ? std::min<long>(threads, 256) : 1;
 
     std::vector<const char*> paths;
     for (auto& r : refs) paths.push_back(r.c_str());
@@ -255,7 +259,8 @@ extern "C" int tksm_sequence_main(int argc, char** argv) {
         cfg.identity_max = mx;
         cfg.identity_stdev = sd;
         cfg.skip_qual_compute = skip_qual;
-        cfg.threads = (int)std::max<long>(host_threads / n, 1);
+        const long hw = std::min<long>(std::max<long>((long)std::thread::hardware_concurrency(), 1), 32L * n);
+        cfg.threads = (int)std::max<long>((host_threads == 0 ? hw : host_threads) / n, 1);
         tksm_seq* h = tksm_seq_create(&cfg);
         if (!h) {
             errors[(size_t)i] = tksm_seq_last_error(nullptr);

@@ -157,10 +157,11 @@ std::vector<AliasCol> build_alias(const std::vector<double>& p_in, int ncols, in
 
 }  // namespace
 
-// Groups the 4^k change probabilities into Q_CLASSES - 1 classes (1-D Lloyd iteration from a
-// quantile start; representative = class mean, so the total trial rate is preserved) so that the
-// arrival test of the kernels is two shared-memory look-ups: class of the k-mer, threshold of the
-// class.  Class 255 is reserved for k-mers that are not in the table (q = 1).
+// Groups the 4^k change probabilities into Q_CLASSES - 1 classes of equal width between the smallest and the largest
+// one (representative = class mean, so the total trial rate is preserved and a k-mer's arrival rate is its own to
+// within half a class width, about 0.1 % of a trial) so that the arrival test of the kernels is two shared-memory
+// look-ups: class of the k-mer, threshold of the class.  Class 255 is reserved for k-mers that are not in the table
+// (q = 1).
 static void build_q_classes(ErrorModelHost& em) {
     em.qrep.assign(Q_CLASSES, 1.0);
     if (!em.has_table) return;
@@ -169,25 +170,9 @@ static void build_q_classes(ErrorModelHost& em) {
     for (size_t c = 0; c < rows; c++) order[c] = {em.q16[c], (uint32_t)c};
     std::sort(order.begin(), order.end());
     const int K = Q_CLASSES - 1;
-    std::vector<double> cent((size_t)K);
-    for (int c = 0; c < K; c++) cent[(size_t)c] = order[std::min(rows - 1, (size_t)((c + 0.5) * rows / K))].first;
+    const double vmin = order.front().first, span = (double)order.back().first - vmin + 1.0;
     std::vector<int> assign(rows, 0);
-    for (int it = 0; it < 40; it++) {
-        // sorted values: boundaries are the mid-points between consecutive centroids
-        std::sort(cent.begin(), cent.end());
-        int c = 0;
-        std::vector<double> sum((size_t)K, 0.0);
-        std::vector<size_t> cnt((size_t)K, 0);
-        for (size_t i = 0; i < rows; i++) {
-            double v = order[i].first;
-            while (c + 1 < K && std::fabs(cent[(size_t)c + 1] - v) <= std::fabs(cent[(size_t)c] - v)) c++;
-            assign[i] = c;
-            sum[(size_t)c] += v;
-            cnt[(size_t)c]++;
-        }
-        for (int j = 0; j < K; j++)
-            if (cnt[(size_t)j]) cent[(size_t)j] = sum[(size_t)j] / (double)cnt[(size_t)j];
-    }
+    for (size_t i = 0; i < rows; i++) assign[i] = std::min(K - 1, (int)(((double)order[i].first - vmin) / span * K));
     em.qcls.assign(rows, 0);
     std::vector<double> sum((size_t)K, 0.0);
     std::vector<size_t> cnt((size_t)K, 0);

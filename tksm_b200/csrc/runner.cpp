@@ -134,8 +134,9 @@ struct Sink {
     }
     void close() {
         if (is_gz) gz.finish();
-        if (f) fclose(f);
+        FILE* g = f;
         f = nullptr;
+        if (g && fclose(g) != 0) throw std::runtime_error("write failed");   // e.g. ENOSPC at the final flush
     }
     ~Sink() {
         if (f) fclose(f);
