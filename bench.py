@@ -12,7 +12,12 @@ Philox-keyed by global read ordinal; no collective on the data path).
 value  : whole-job simulated bases/s with the molecule batch resident in HBM (CUDA events around
          the kernel sequence, max over ranks).
 e2e    : same metric through tksm_seq_simulate_text(): MDF text in host memory -> parse -> H2D ->
-         kernels -> FASTQ bytes back in host memory.
+         kernels -> FASTQ bytes back in host memory.  At N > 1 the product's sharding is what is timed: ONE
+         MDF of N x M molecules, cut by tksm_seq_shard_plan into N contiguous shards of equal simulated bases,
+         rank r streams shard r with the global ordinal of its first read (the rank outputs in rank order are the
+         bytes of the one-GPU run; tests/test_sharding.py).
+gates  : before the timed region, untimed: the error-free stage byte for byte against oracle/seq_oracle.py and the
+         CUDA FASTQ byte for byte against the CPU twin on the first reads of the workload.
 """
 import argparse
 import json
@@ -44,6 +49,12 @@ WORKLOADS = {
     "skew": dict(shape=2, models="nanopore2020", identity=None,
                  desc="BASELINE configs[4] shape: single-interval molecules, lengths log-uniform 500 bp-100 kbp"),
 }
+
+
+# dram__bytes_read.sum + dram__bytes_write.sum over all launches of one step of the default workload (one ncu pass,
+# profiles/r2_dram_per_launch.txt)
+TRAFFIC_BYTES = 15.16e9
+TRAFFIC_NOTE = "see profiles/r2_dram_per_launch.txt"
 
 
 def peaks():
@@ -109,18 +120,28 @@ class ClockSampler(threading.Thread):
                 "reasons": reasons, "samples": len(self.rows)}
 
 
-def cpu_port_run(tables, seqs, ids, threads):
-    """Times the CPU oracle on a bounded sample.  Returns (bases, seconds, kind description)."""
-    from oracle import seq_oracle as so
+def cpu_port_run(seqs, ids, threads):
+    """Times the reference's algorithm (oracle/badread_port.c: sequence_fragment + get_qscores, statement by statement
+    in C) on the given molecules: error injection, alignment, qscores and FASTQ formatting.  (bases, seconds)."""
+    from oracle import badread_port as bp
+    model = bp.get_model("nanopore2020", "nanopore2020", (84.0, 99.0, 5.5))   # model load is not timed
+    t0 = time.perf_counter()
+    reads, quals, idn = bp.simulate(model, seqs, seed=1, threads=threads)
+    fq, _ = bp.to_fastq(seqs, ids, reads, quals, idn)
+    secs = time.perf_counter() - t0
+    assert fq[:1] == b"@"
+    return sum(len(r) for r in reads), secs
+
+
+CPU_KIND = ("port: oracle/badread_port.c (the reference's sequence_fragment + get_qscores in C, banded NW for edlib) + "
+            "FASTQ formatting; inputs from oracle/bulk_inputs.py (numpy), nothing of the library under test")
+
+
+def cpu_model():
     try:
-        from oracle import badread_port as bp
-        t0 = time.perf_counter()
-        bases = bp.simulate_count(seqs, threads=threads)
-        return bases, time.perf_counter() - t0, "port: oracle/badread_port.c (sequential Badread algorithm of the reference, C)"
-    except ImportError:
-        t0 = time.perf_counter()
-        _, lens, _ = so.twin_simulate(tables, seqs, ids, want_lengths=True)
-        return int(lens.sum()), time.perf_counter() - t0, "port: oracle/twin.c (CPU twin of the PB1 model, 1 thread)"
+        return open("/proc/cpuinfo").read().split("model name")[1].split(":")[1].splitlines()[0].strip()
+    except Exception:
+        return "unknown"
 
 
 def main():
@@ -135,6 +156,8 @@ def main():
     ap.add_argument("--identity", default="84,99,5.5", help="--badread-identity mean,max,stdev (experiments)")
     ap.add_argument("--cpu-sample", type=int, default=0, help="molecules in the CPU baseline sample (0 = auto)")
     ap.add_argument("--workload", default="bulk", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-gates", action="store_true", help="skip the untimed correctness gates")
+    ap.add_argument("--gate-reads", type=int, default=10000, help="reads of the workload the CPU twin is run on")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     if wl["identity"] and args.identity == "84,99,5.5":
@@ -173,9 +196,21 @@ def main():
     if not have:
         raise SystemExit("model files missing under tksm_b200/models/badread (run __graft_entry__.build())")
     s.load_models(wl["models"], wl["models"])
-    mdf = s.synth_mdf(wl["shape"], args.molecules, seed=1000 + rank, min_len=500, max_len=100000)
-    ordinal_base = rank * args.molecules
+    if world == 1:
+        mdf = s.synth_mdf(wl["shape"], args.molecules, seed=1000, min_len=500, max_len=100000)
+        ordinal_base = 0
+    else:
+        # ONE stream of N x M molecules (every rank generates the same text), cut by the product's shard plan:
+        # contiguous shards of about equal simulated bases, global ordinals
+        full = s.synth_mdf(wl["shape"], args.molecules * world, seed=1000, min_len=500, max_len=100000)
+        plan = s.shard_plan(full, world)
+        lo, hi, ordinal_base = plan[rank]
+        mdf = full[lo:hi]
+        del full
+        config["sharding"] = (f"tksm_seq_shard_plan: one MDF of {args.molecules * world} molecules cut into {world} contiguous "
+                              f"shards of equal simulated bases, rank r streams shard r, no collective")
     batch = s.batch(mdf, ordinal_base)
+    gates = run_gates(s, mdf, ordinal_base, wl, args) if (rank == 0 and not args.no_gates) else "skipped"
 
     def barrier():
         torch.cuda.synchronize()
@@ -247,22 +282,25 @@ def main():
             "reads_per_s": total_reads_step * args.steps / (dev_ms_max / 1e3),
             "clocks": clocks,
             "e2e": {"value": total_e2e_bases / e2e_wall_max if args.e2e_steps else None, "unit": "bases/s",
-                    "h2d_bytes_per_step": e2e_stats["h2d_bytes"] + len(mdf) * 0,
+                    "h2d_bytes_per_step": e2e_stats["h2d_bytes"],
+                    "mdf_text_bytes_per_step": len(mdf),   # host memory -> library (parsed on the host), not a device copy
                     "d2h_bytes_per_step": e2e_stats["d2h_bytes"],
                     "ms_per_step": e2e_wall_max / args.e2e_steps * 1e3 if args.e2e_steps else None,
                     "host_threads": host_threads,
                     "note": "tksm_seq_simulate_text: MDF text in host memory -> parse (host threads) -> H2D -> kernels -> "
                             "D2H of the FASTQ bytes into a page-locked host buffer, chunks pipelined"},
             "gpu_launches": launches,
+            "gates": gates,
             "status_or": int(st.get("status_or", 0)),   # OR of the per-read status words of the last step (8 = some read's qscores follow the edit script: alignment band left)
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          # dram__bytes_read.sum + dram__bytes_write.sum over the 16 launches of one step of this
                          # workload, one ncu capture (profiles/r1h_dram_per_launch.txt); other sizes: not captured
-                         "traffic": 15.16e9 if (args.workload == "bulk" and args.molecules == 1_000_000) else None,
+                         "traffic": TRAFFIC_BYTES if (args.workload == "bulk" and args.molecules == 1_000_000) else None,
                          "traffic_unit": "bytes per step", "peak_source": peak_src,
-                         "kernel": "work order + simulate_kernel<W,phase> (error injection | expansion + qscores, per length class) + "
+                         "kernel": "work order + per length class: simulate_kernel<W,1> (error injection) | <W,2> (expansion) | "
+                                   "align_kernel (read-to-fragment alignment, one thread per read) | <W,4> (qscores) + "
                                    "reclen/scan/format: whole kernel sequence of a step",
-                         "traffic_note": "7.5 x the algorithmic bytes: the slot keys and fragment handed from the error-injection to the expansion kernels through global memory (8.7 GB) and the per-read scratch the format kernel re-reads (3.3 GB); 2.3 ms of the step at HBM speed: profiles/r1h_dram_per_launch.txt",
+                         "traffic_note": TRAFFIC_NOTE,
                          "simulate_share": sim_ms / dev_ms if dev_ms else None,
                          "algorithmic_bytes_per_step": st["algorithmic_bytes"]},
         }
@@ -276,12 +314,34 @@ def main():
     return 0
 
 
-def sample_inputs(s, mdf, n_mol):
-    """First n_mol records of the workload as (error-free sequences, ids) for the CPU oracle."""
+def cpu_baseline(s, mdf, args):
+    from oracle import bulk_inputs as bi
+    n = args.cpu_sample or 2000
+    seqs, ids = bi.molecules(n, seed=1000)
+    bases, secs = cpu_port_run(seqs, ids, 1)
+    return {"value": bases / secs, "unit": "bases/s", "cores": 1, "kind": "port", "what": CPU_KIND, "cpu": cpu_model(),
+            "sample": f"{len(seqs)} bulk-shape molecules ({sum(map(len, seqs))} raw bases), {secs:.1f} s"}
+
+
+def _twin_chunk(kw, models, seqs, ids, lo):
+    """One span of the gate's reads through the CPU twin (worker process)."""
     from oracle import seq_oracle as so
-    from tksm_b200.sequence import PERFECT
+    from tksm_b200.sequence import Sequencer
+    s = Sequencer(host_only=True, **kw)
+    s.load_models(models, models)
+    return so.twin_simulate(s.tables(), seqs, ids, ordinal_base=lo, badread=True, fastq=True)
+
+
+def run_gates(s, mdf, ordinal_base, wl, args):
+    """SURVEY.md 8(d), untimed: (1) error-free stage of the first reads byte for byte against oracle/seq_oracle.py;
+    (2) CUDA FASTQ of the first --gate-reads reads byte for byte against the CPU twin.  The oracle needs reference
+    text: the genomic intervals of those reads are fetched back from the device-generated genome one by one."""
+    import multiprocessing as mp
+    from oracle import seq_oracle as so
+    from tksm_b200.sequence import BADREAD, PERFECT
+    n = min(args.gate_reads, args.molecules)
     pos, cnt = 0, 0
-    while cnt <= n_mol:
+    while cnt < n:
         nxt = mdf.find(b"\n+", pos + 1)
         if nxt < 0:
             pos = len(mdf)
@@ -289,47 +349,61 @@ def sample_inputs(s, mdf, n_mol):
         pos = nxt + 1
         cnt += 1
     sub = mdf[:pos]
-    recs = so.parse_records(s.simulate(sub, PERFECT, fastq=False), fastq=False)
-    seqs = [r[1] for r in recs]
-    ids = [r[0].split("molecule_id=")[1] for r in recs]
-    return seqs, ids
-
-
-def cpu_baseline(s, mdf, args):
-    n = args.cpu_sample or 2000
-    seqs, ids = sample_inputs(s, mdf, n)
-    threads = 1
-    bases, secs, kind = cpu_port_run(s.tables(), seqs, ids, threads)
-    return {"value": bases / secs, "unit": "bases/s", "cores": threads, "kind": "port", "what": kind,
-            "sample": f"first {len(seqs)} molecules of the workload ({sum(map(len, seqs))} raw bases), {secs:.1f} s"}
+    mols = so.parse_mdf(sub)
+    contigs = set(NAMES)
+    refs, seqs = {}, []
+    for _, ivs in mols:
+        rebased = []
+        for chrom, a, b, strand, mods in ivs:
+            if chrom in contigs:
+                key = f"{chrom}:{a}-{b}"
+                if key not in refs:
+                    refs[key] = s.fetch_reference(chrom, a, b - a).decode("latin-1")
+                rebased.append((key, 0, b - a, strand, mods))
+            else:
+                rebased.append((chrom, a, b, strand, mods))
+        seqs.append(so.molecule_sequence(refs, rebased))
+    ids = [m for m, _ in mols]
+    tables = s.tables()
+    got_p = s.simulate(sub, PERFECT, fastq=False, ordinal_base=ordinal_base)
+    want_p = so.twin_simulate(tables, seqs, ids, ordinal_base=ordinal_base, badread=False, fastq=False)
+    if got_p != want_p:
+        return "FAILED: error-free stage differs from oracle/seq_oracle.py"
+    got = s.simulate(sub, BADREAD, fastq=True, ordinal_base=ordinal_base)
+    kw = dict(identity=tuple(float(x) for x in args.identity.split(",")), seed=42,
+              corr=(float(tables.calib_overshoot), float(tables.calib_kappa)))
+    procs = min(os.cpu_count() or 1, 16)
+    per = (len(seqs) + procs - 1) // procs
+    jobs = [(kw, wl["models"], seqs[i:i + per], ids[i:i + per], ordinal_base + i) for i in range(0, len(seqs), per)]
+    with mp.get_context("fork").Pool(len(jobs)) as pool:
+        parts = pool.starmap(_twin_chunk, jobs)
+    if got != b"".join(parts):
+        return "FAILED: CUDA FASTQ differs from the CPU twin"
+    return f"ok: error-free stage == oracle/seq_oracle.py and CUDA FASTQ == CPU twin, byte for byte, on the first {len(seqs)} reads"
 
 
 def reference_arm(args, config):
-    """The reference's CPU algorithm for this path on the host cores (the oracle port: the Python
-    reference itself needs /root/reference and python-edlib, neither of which is on the GPU box)."""
-    from tksm_b200.sequence import Sequencer
-    import torch  # noqa: F401  (device needed only to materialise the sample's sequences)
-    s = Sequencer(seed=42, device=0)
-    lengths = [max(1000, int(x * args.genome_scale)) for x in GRCH38]
-    s.synth_reference(NAMES, lengths, n_frac=0.01, seed=42)
-    s.load_models("nanopore2020", "nanopore2020")
+    """The reference's CPU algorithm for this path on the host cores: oracle/badread_port.c with all threads, inputs
+    from oracle/bulk_inputs.py (the Python reference itself needs /root/reference and python-edlib, neither of which
+    is on the GPU box; BASELINE.md has its timing in the build container).  Nothing of tksm_b200/ is loaded here."""
+    from oracle import bulk_inputs as bi
     n = args.cpu_sample or 4000
-    mdf = s.synth_mdf(1, n, seed=1000)
-    seqs, ids = sample_inputs(s, mdf, n)
+    seqs, ids = bi.molecules(n, seed=1000)
     threads = os.cpu_count() or 1
     vals = []
     for i in range(args.warmup + args.steps):
-        bases, secs, kind = cpu_port_run(s.tables(), seqs, ids, threads)
+        bases, secs = cpu_port_run(seqs, ids, threads)
         if i >= args.warmup:
             vals.append((bases, secs))
     tb, ts = sum(b for b, _ in vals), sum(t for _, t in vals)
     v = tb / ts
+    config = dict(config, sharding="host threads", molecules_per_step=len(seqs))
     line = {"impl": "reference", "metric": "Seq simulated bases/s (errors+quals, FASTQ)", "value": v, "unit": "bases/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ts / args.steps * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": config,
-            "cpu_baseline": {"value": v, "unit": "bases/s", "cores": threads, "kind": "port", "what": kind,
-                             "sample": f"{len(seqs)} molecules per step ({sum(map(len, seqs))} raw bases)"},
+            "cpu_baseline": {"value": v, "unit": "bases/s", "cores": threads, "kind": "port", "what": CPU_KIND, "cpu": cpu_model(),
+                             "sample": f"{len(seqs)} bulk-shape molecules per step ({sum(map(len, seqs))} raw bases)"},
             "e2e": {"value": v, "unit": "bases/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), file=RESULT_OUT, flush=True)
     return 0

@@ -1768,17 +1768,27 @@ int tksm_seq_fetch_reference(tksm_seq* h, const char* contig, uint64_t start, ui
     if (start + len > it->second.length) throw std::runtime_error("fetch beyond contig end");
     uint64_t g0 = it->second.offset + start;
     if (h->genome_synthetic) {
+        // device-generated genome: only the words of the range come back (the exception runs are on the host)
         need_device(h);
         CK(cudaSetDevice(h->cfg.device));
-        uint64_t w0 = g0 >> 4, w1 = (g0 + len + 15) >> 4;
-        h->genome.words.assign((size_t)(w1 + 1), 0);
-        if (w1 > w0)
-            CK(cudaMemcpy(h->genome.words.data() + w0, h->d_genome.as<uint32_t>() + w0, (w1 - w0) * 4,
-                          cudaMemcpyDeviceToHost));
+        const uint64_t w0 = g0 >> 4, w1 = (g0 + len + 15) >> 4;
+        std::vector<uint32_t> w((size_t)(w1 - w0 + 1), 0);
+        if (w1 > w0) CK(cudaMemcpy(w.data(), h->d_genome.as<uint32_t>() + w0, (w1 - w0) * 4, cudaMemcpyDeviceToHost));
+        for (uint64_t i = 0; i < len; i++) {
+            const uint64_t g = g0 + i;
+            out[i] = "ACGT"[(w[(size_t)((g >> 4) - w0)] >> (2 * (g & 15))) & 3];
+        }
+        const auto& G = h->genome;
+        size_t r = (size_t)(std::lower_bound(G.exc_start.begin(), G.exc_start.end(), g0) - G.exc_start.begin());
+        if (r > 0) r--;
+        for (; r < G.exc_start.size() && G.exc_start[r] < g0 + len; r++) {
+            const uint64_t a = std::max(G.exc_start[r], g0), b = std::min(G.exc_start[r] + G.exc_len[r], g0 + len);
+            for (uint64_t g = a; g < b; g++) out[g - g0] = (char)G.exc_chr[r];
+        }
+    } else {
+        std::string s = h->genome.fetch(g0, len);
+        memcpy(out, s.data(), len);
     }
-    std::string s = h->genome.fetch(g0, len);
-    memcpy(out, s.data(), len);
-    if (h->genome_synthetic) std::vector<uint32_t>().swap(h->genome.words);
     API_END(h)
 }
 
