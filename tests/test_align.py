@@ -130,3 +130,59 @@ def test_band_around_the_edit_script_finds_the_full_matrix_alignment(built):
 
     twin_alignments("nanopore2020", "nanopore2020", (84.0, 99.0, 5.5), 400, cb)
     assert seen["n"] == 400 and seen["fail"] == 0 and seen["diff"] == 0, seen
+
+
+@pytest.fixture(scope="module")
+def emul_one():
+    """Host build of align_kernel's per-thread routine: the lines of kernels.cuh from `struct ByteStream` to the end
+    of align_one, with the few CUDA names stubbed (tests/native/align_one_emul.cpp)."""
+    src = os.path.join(HERE, "native", "align_one_emul.cpp")
+    kern = os.path.join(HERE, "..", "tksm_b200", "csrc", "kernels.cuh")
+    bdir = os.path.join(HERE, "native", "_build")
+    os.makedirs(bdir, exist_ok=True)
+    lines = open(kern).read().split("\n")
+    a = next(i for i, l in enumerate(lines) if l.startswith("struct ByteStream {"))
+    b = next(i for i, l in enumerate(lines) if l.startswith("// shared memory of one warp of align_kernel<BV>"))
+    open(os.path.join(bdir, "align_one_body.inc"), "w").write("\n".join(lines[a:b]) + "\n")
+    out = os.path.join(bdir, "libalign_one_emul.so")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", out, src])
+    lib = C.CDLL(out)
+    lib.align_one_emul.argtypes = [C.c_void_p] * 4 + [C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]
+    return lib
+
+
+@needs_models
+@pytest.mark.parametrize("em,ident,n_reads", [("nanopore2020", (84.0, 99.0, 5.5), 250), ("nanopore2018", (70.0, 85.0, 6.0), 100)])
+def test_thread_per_read_alignment_equals_the_integer_band(built, emul_one, em, ident, n_reads):
+    """align_kernel (one thread per read: streamed forward pass, traceback on staged blocks) against twin_bnw, with
+    the kernel's band rule: 32-bit band up to ALIGN_WIDE64_FROM slots, retried with 64 bits; 64 bits at once above."""
+    seen = {"n": 0, "wide": 0, "bad": []}
+
+    def cb(fa, n, sq, m, ops, dc, status, soff):
+        seen["n"] += 1
+        frag = CODE[np.frombuffer(C.string_at(fa, n), np.uint8)]
+        read = CODE[np.frombuffer(C.string_at(sq, m), np.uint8)]
+        slen = np.diff(np.ctypeslib.as_array(soff, (n + 1,)).astype(np.int64)).astype(np.uint8)
+        out = np.zeros(m, np.uint8)
+        eq, cols = C.c_uint32(), C.c_uint32()
+        wide = 1 if n > 2048 else 0
+        r = emul_one.align_one_emul(frag.ctypes.data, slen.ctypes.data, read.ctypes.data, out.ctypes.data, n, m, wide,
+                                    C.byref(eq), C.byref(cols))
+        if r == 1 and not wide:
+            wide = 1
+            r = emul_one.align_one_emul(frag.ctypes.data, slen.ctypes.data, read.ctypes.data, out.ctypes.data, n, m, 1,
+                                        C.byref(eq), C.byref(cols))
+        seen["wide"] += wide
+        if status:
+            if r != 1:
+                seen["bad"].append(("twin failed, kernel routine did not", n, m))
+            return
+        want = np.frombuffer(C.string_at(ops, m), np.uint8)
+        wdc = np.frombuffer(C.string_at(dc, m), np.uint8)
+        wop = (np.where(want == ord("="), 0, np.where(want == ord("X"), 1, 2)) | (wdc.astype(np.int64) << 2)).astype(np.uint8)
+        if r != 0 or not np.array_equal(out, wop) or eq.value != int((want == ord("=")).sum()):
+            seen["bad"].append((r, wide, n, m))
+
+    twin_alignments(em, em, ident, n_reads, cb)
+    assert seen["n"] == n_reads and seen["wide"] > 0
+    assert not seen["bad"], seen["bad"][:5]

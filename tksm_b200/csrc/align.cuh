@@ -50,7 +50,8 @@ constexpr uint32_t ALIGN_MARGIN = 4;      // cells the traceback keeps away from
 constexpr uint32_t ALIGN_MIN_CHUNK = 16;  // columns per thread at least
 constexpr uint32_t ALIGN_DC_CAP = 15;     // D columns recorded in front of one read base
 constexpr uint32_t ALIGN_CELL_BYTES = 32; // trace bytes per column the caller provides (a cell of 64-bit words)
-constexpr uint32_t ALIGN_WIDE_FROM = 8192; // fragments with more slots start with the 64-bit band
+constexpr uint32_t ALIGN_WIDE64_FROM = 2048; // fragments with more slots start with the 64-bit band (no 32-bit attempt)
+constexpr uint32_t ALIGN_WIDE_FROM = 8192; // ... and above this the team-parallel form of it (FIN_FULL kernels) does them
 constexpr uint32_t ALIGN_ROW_BITS = 18;   // arr = walk tag << 18 | row; rows stay below 2^18 - 1 (reads of up to 2 x 131 070 bases)
 
 enum : uint32_t { MV_DIAG = 0, MV_UP = 1, MV_LEFT = 2, MV_OUT = 3 };

@@ -286,11 +286,12 @@ struct tksm_seq {
     // device
     cudaStream_t stream = nullptr;       // uploads + kernels
     cudaStream_t copy_stream = nullptr;  // record downloads, overlapped with the next chunk's kernels
-    // Consecutive batches alternate between two lanes (own upload/kernel stream and class streams), so
-    // the kernels of the next batch fill the SMs while the previous one runs its tail and its format stage.
-    cudaStream_t lane_stream[2] = {nullptr, nullptr};   // lane 0 is `stream`
-    cudaStream_t class_stream[2][4] = {};  // simulate kernels of one batch, one stream per length class
-    cudaStream_t side_stream[2][4] = {};   // the few reads of a class that need the 64-bit alignment band or a redo
+    // Every device slot of the streaming pipeline has its own lane (upload/kernel stream, class streams, side
+    // streams): the kernel sequence of a batch has long single-warp chains (one thread per read in the alignment
+    // kernels), which the kernels of the neighbouring batches fill.
+    cudaStream_t lane_stream[3] = {nullptr, nullptr, nullptr};   // lane 0 is `stream`
+    cudaStream_t class_stream[3][4] = {};  // simulate kernels of one batch, one stream per length class
+    cudaStream_t side_stream[3][4] = {};   // the few reads of a class that need the 64-bit alignment band or a redo
     std::vector<std::unique_ptr<tksm_seq_batch>> slots;  // streaming pipeline (engine_stream)
     std::unique_ptr<StagePool> stage_pool;
     int num_sms = 148;
@@ -320,6 +321,7 @@ struct tksm_seq {
             for (auto& cs : lane)
                 if (cs) cudaStreamDestroy(cs);
         if (lane_stream[1]) cudaStreamDestroy(lane_stream[1]);
+        if (lane_stream[2]) cudaStreamDestroy(lane_stream[2]);
         if (stream) cudaStreamDestroy(stream);
     }
 };
@@ -455,6 +457,8 @@ struct AlignLaunch {
     uint32_t* redo64_count;
     uint8_t* trace64;         // trace cells of the 64-bit instance
     uint64_t trace64_warp_bytes;
+    bool wide_class;          // every read of the class is above ALIGN_WIDE64_FROM slots: 64-bit instance on all of them
+    int grid64;
     cudaStream_t side;        // stream of the 64-bit instance and the redo list
     cudaEvent_t ev_fork, ev_side;
 };
@@ -481,24 +485,34 @@ void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, const P
     launch_sim_phase<W, GWS, FIN_EXPAND>(stream, Q, smem_small, grid_small, 1024);
     if (!(P.flags & RUN_QUAL)) return;
     constexpr int AW = ALIGN_K_THREADS / 32;
-    static bool attr_set = false;
-    if (!attr_set) {
-        CK(cudaFuncSetAttribute(align_kernel<uint32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(AW * align_warp_smem<uint32_t>())));
-        CK(cudaFuncSetAttribute(align_kernel<uint64_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(AW * align_warp_smem<uint64_t>())));
-        attr_set = true;
-    }
-    align_kernel<uint32_t><<<al.grid, ALIGN_K_THREADS, AW * align_warp_smem<uint32_t>(), stream>>>(al.K);
-    CK(cudaGetLastError());
-    CK(cudaEventRecord(al.ev_fork, stream));
-    // main stream: qscores of the reads the 32-bit band did
-    Q.counter = counters + 24;
-    launch_sim_phase<W, GWS, FIN_QUAL>(stream, Q, smem_small, grid_small, 1024);
-    // side stream: the few reads that left the 32-bit band (about one in a thousand) take the 64-bit instance and
-    // their qscores; what leaves that band too, and the reads above ALIGN_WIDE_FROM slots, the FIN_FULL kernel.  These
-    // launches are long chains on a handful of reads: beside the main stream they cost nothing.
+    // (per device: a process may drive several GPUs)
+    CK(cudaFuncSetAttribute(align_kernel<uint32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(AW * align_warp_smem<uint32_t>())));
+    CK(cudaFuncSetAttribute(align_kernel<uint64_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(AW * align_warp_smem<uint64_t>())));
     cudaStream_t side = al.side;
-    CK(cudaStreamWaitEvent(side, al.ev_fork, 0));
-    {
+    if (al.wide_class) {
+        // 64-bit band at once, on every read of the class; what leaves it goes to the FIN_FULL redo list
+        AlignKParams K2 = al.K;
+        K2.trace = al.trace64;
+        K2.trace_warp_bytes = al.trace64_warp_bytes;
+        K2.redo = P.redo;
+        K2.redo_count = P.redo_count;
+        align_kernel<uint64_t><<<al.grid64, ALIGN_K_THREADS, AW * align_warp_smem<uint64_t>(), stream>>>(K2);
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(al.ev_fork, stream));
+        Q.counter = counters + 24;
+        launch_sim_phase<W, GWS, FIN_QUAL>(stream, Q, smem_small, grid_small, 1024);
+        CK(cudaStreamWaitEvent(side, al.ev_fork, 0));
+    } else {
+        align_kernel<uint32_t><<<al.grid, ALIGN_K_THREADS, AW * align_warp_smem<uint32_t>(), stream>>>(al.K);
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(al.ev_fork, stream));
+        // main stream: qscores of the reads the 32-bit band did
+        Q.counter = counters + 24;
+        launch_sim_phase<W, GWS, FIN_QUAL>(stream, Q, smem_small, grid_small, 1024);
+        // side stream: the reads that left the 32-bit band (about one in a thousand) and those above ALIGN_WIDE64_FROM
+        // slots take the 64-bit instance and their qscores.  Long chains on few reads: beside the main stream they
+        // cost nothing.
+        CK(cudaStreamWaitEvent(side, al.ev_fork, 0));
         AlignKParams K2 = al.K;
         K2.work = al.redo64;
         K2.n_work_dev = al.redo64_count;
@@ -507,14 +521,15 @@ void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, const P
         K2.trace_warp_bytes = al.trace64_warp_bytes;
         K2.redo = P.redo;
         K2.redo_count = P.redo_count;
-        align_kernel<uint64_t><<<std::min(al.grid, 16), ALIGN_K_THREADS, AW * align_warp_smem<uint64_t>(), side>>>(K2);
+        align_kernel<uint64_t><<<al.grid64, ALIGN_K_THREADS, AW * align_warp_smem<uint64_t>(), side>>>(K2);
         CK(cudaGetLastError());
         SimParams Q2 = Q;
         Q2.counter = counters + 88;
         Q2.work = al.redo64;
         Q2.n_work_dev = al.redo64_count;
-        launch_sim_phase<W, GWS, FIN_QUAL>(side, Q2, smem_small, std::min(grid_small, 16), 1024);
+        launch_sim_phase<W, GWS, FIN_QUAL>(side, Q2, smem_small, std::min(grid_small, 32), 1024);
     }
+    // what left the 64-bit band too, and the reads above ALIGN_WIDE_FROM slots: the FIN_FULL kernel
     P.slab_bytes = p2.slab_bytes;
     P.counter = counters + 56;
     P.work = P.redo;
@@ -794,6 +809,8 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
     uint64_t trace_off[N_CLASSES] = {}, trace_team[N_CLASSES] = {}, trace_total = 0;
     uint64_t atrace_off[N_CLASSES] = {}, atrace_warp[N_CLASSES] = {}, atrace_total = 0;
     uint64_t atrace64_off[N_CLASSES] = {}, atrace64_warp[N_CLASSES] = {};
+    bool wide_class[N_CLASSES] = {};
+    int agrid64[N_CLASSES] = {};
     int agrid[N_CLASSES] = {};
     if (flags & RUN_QUAL)
         for (int c = 0; c < N_CLASSES; c++) {
@@ -814,11 +831,19 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
                 const uint64_t warps_mem = std::max<uint64_t>((3072ull << 20) / atrace_warp[c], 64);
                 const uint64_t warps = std::min<uint64_t>({(uint64_t)h->num_sms * 20, (p.n_work[c] + 31) / 32, warps_mem});
                 agrid[c] = (int)((warps + AW - 1) / AW);
+                wide_class[c] = c > 0 && ncap_c[c - 1] >= ALIGN_WIDE64_FROM;
                 atrace_off[c] = atrace_total;
-                atrace_total += atrace_warp[c] * AW * agrid[c];
+                if (!wide_class[c]) atrace_total += atrace_warp[c] * AW * agrid[c];
                 atrace64_warp[c] = (uint64_t)cols * 32 * sizeof(AlignCell2<uint64_t>);
+                if (wide_class[c]) {
+                    const uint64_t wm = std::max<uint64_t>((3072ull << 20) / atrace64_warp[c], 64);
+                    const uint64_t w64 = std::min<uint64_t>({(uint64_t)h->num_sms * 8, (p.n_work[c] + 31) / 32, wm});
+                    agrid64[c] = (int)((w64 + AW - 1) / AW);
+                } else {
+                    agrid64[c] = std::min(agrid[c], 16);
+                }
                 atrace64_off[c] = atrace_total;
-                atrace_total += atrace64_warp[c] * AW * std::min(agrid[c], 16);
+                atrace_total += atrace64_warp[c] * AW * agrid64[c];
             }
         }
     b->trace.ensure(std::max<uint64_t>(trace_total, 16));
@@ -907,6 +932,10 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         al.redo64 = b->redo64.as<uint32_t>() + (b->d_work[c] - b->work_sorted.as<uint32_t>());
         al.redo64_count = b->counters.as<uint32_t>() + 80 + c;
         al.K.n_work_dev = nullptr;
+        al.wide_class = wide_class[c];
+        al.grid64 = agrid64[c];
+        P.redo64 = wide_class[c] ? nullptr : al.redo64;
+        P.redo64_count = al.redo64_count;
         al.K.redo = al.redo64;
         al.K.redo_count = al.redo64_count;
         const int teams = c == GWS_CLASS ? 1 : SIM_WARPS / CLASS_W[c];
@@ -1376,10 +1405,13 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
         WorkerPool pool(nthreads);
         std::shared_ptr<GroupState> group;
         size_t group_chunks = 0;
-        size_t group_text = 0, group_target = 1, groups_made = 0, ramp = 1;
+        // every batch pays the latency of its kernel chain (single-warp stretches in the alignment kernels), so batches
+        // start at min_group chunks rather than one
+        const size_t min_group = getenv("TKSM_SEQ_MIN_GROUP") ? std::max(1, atoi(getenv("TKSM_SEQ_MIN_GROUP"))) : 8;
+        size_t group_text = 0, group_target = min_group, groups_made = 0, ramp = min_group;
         uint64_t text_submitted = 0;
         // text chunks (1 MiB each) per device batch in steady state
-        const size_t max_group = getenv("TKSM_SEQ_MAX_GROUP") ? std::max(1, atoi(getenv("TKSM_SEQ_MAX_GROUP"))) : 32;
+        const size_t max_group = getenv("TKSM_SEQ_MAX_GROUP") ? std::max(1, atoi(getenv("TKSM_SEQ_MAX_GROUP"))) : 64;
         auto close_group = [&]() {
             if (!group) return;
             const tksm_seq* hc = h;
@@ -1397,7 +1429,7 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
             group_target = ramp;
             if (text_total > text_submitted) {
                 const size_t left = (size_t)((text_total - text_submitted) >> 20);  // 1 MiB chunks left, about
-                group_target = std::min(ramp, std::max<size_t>(2, left / 2));
+                group_target = std::min(ramp, std::max<size_t>(min_group, left / 2));
             }
         };
         while (true) {
@@ -1439,10 +1471,9 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
                 tksm_seq_batch* b = h->slots[issued % NS].get();
                 t0 = now_ms();
                 slot_reusable(b);
-                // measured: alternating the batches between the two lanes is 5 % slower end to end than one
-                // lane (the class streams already overlap the tails); TKSM_SEQ_LANES=2 turns it on
-                static const bool two_lanes = getenv("TKSM_SEQ_LANES") && atoi(getenv("TKSM_SEQ_LANES")) == 2;
-                b->lane = two_lanes ? (int)(issued & 1) : 0;
+                // one lane per slot ($TKSM_SEQ_LANES=1: everything on one lane, as before the alignment kernels)
+                static const int lanes = getenv("TKSM_SEQ_LANES") ? std::min(std::max(atoi(getenv("TKSM_SEQ_LANES")), 1), 3) : 3;
+                b->lane = (int)(issued % (size_t)lanes);
                 w_reuse += now_ms() - t0;
                 b->prep = std::move(*pp);
                 if (!b->prep.deferred_parts.empty()) finish_deferred(h, b->prep, ordinal);
@@ -1676,6 +1707,7 @@ tksm_seq* tksm_seq_create(const tksm_seq_config* cfg) {
                 for (auto& cs : lane) CK(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
             h->lane_stream[0] = h->stream;
             CK(cudaStreamCreateWithFlags(&h->lane_stream[1], cudaStreamNonBlocking));
+            CK(cudaStreamCreateWithFlags(&h->lane_stream[2], cudaStreamNonBlocking));
         }
     } catch (const std::exception& e) {
         g_create_error = e.what();

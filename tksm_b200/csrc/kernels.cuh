@@ -192,7 +192,9 @@ struct SimParams {
     uint32_t* dbg;          // TK_ALIGN_PARANOID builds: first recorded violation
     uint32_t* redo;         // PHASE 2: reads to be finished by the PHASE 3 kernel of the class (64-bit band)
     uint32_t* redo_count;
-    const uint32_t* n_work_dev;  // PHASE 3 on a redo list: number of entries (device memory); nullptr: n_work
+    const uint32_t* n_work_dev;  // launches on a device-side list: number of entries (device memory); nullptr: n_work
+    uint32_t* redo64;       // FIN_EXPAND: list of the 64-bit alignment instance (nullptr: that instance runs on all reads)
+    uint32_t* redo64_count;
 };
 
 // Team workspace layout, shared by the host (sizing) and the kernel:
@@ -1113,10 +1115,15 @@ __device__ __forceinline__ void finish_read(const Team<W>& tm, const SimParams& 
     }
     if (MODE == FIN_EXPAND) {
         // reads above ALIGN_WIDE_FROM slots take the 64-bit band at once: the FIN_FULL kernel of the class does them
-        const bool full = (P.flags & RUN_QUAL) && n > ALIGN_WIDE_FROM && !(status & (ST_OPS_OVERFLOW | ST_SCRATCH_OVERFLOW));
+        const bool aligned = (P.flags & RUN_QUAL) && !(status & (ST_OPS_OVERFLOW | ST_SCRATCH_OVERFLOW));
+        const bool full = aligned && n > ALIGN_WIDE_FROM;
+        // above ALIGN_WIDE64_FROM slots the 64-bit band at once: in a class that also holds shorter reads, through the
+        // list of the 64-bit alignment instance (P.redo64; the other classes run that instance on all their reads)
+        const bool wide64 = aligned && !full && n > ALIGN_WIDE64_FROM && P.redo64;
         if (tm.rank == 0) {
-            if (B.rinfo) B.rinfo[r] = RInfo{Ttot, start_trim, end_trim, full ? RINFO_SKIP : 0u};
+            if (B.rinfo) B.rinfo[r] = RInfo{Ttot, start_trim, end_trim, (full || wide64) ? RINFO_SKIP : 0u};
             if (full) P.redo[atomicAdd(P.redo_count, 1u)] = r;
+            if (wide64) P.redo64[atomicAdd(P.redo64_count, 1u)] = r;
         }
         tm.sync();
         return;
@@ -1648,7 +1655,9 @@ __global__ void __launch_bounds__(ALIGN_K_THREADS) align_kernel(const AlignKPara
             const RInfo ri = B.rinfo[r];
             const uint32_t st = B.status[r];
             rflags = ri.flags;
-            if ((!(ri.flags & RINFO_SKIP) || sizeof(BV) == 8) && !(st & (ST_OPS_OVERFLOW | ST_SCRATCH_OVERFLOW))) {
+            // on its list the 64-bit instance takes what the 32-bit one (or the expansion) left for it: RINFO_SKIP is set
+            // there; on a class's own work list it leaves the reads above ALIGN_WIDE_FROM slots to the FIN_FULL kernel
+            if ((!(ri.flags & RINFO_SKIP) || K.n_work_dev) && !(st & (ST_OPS_OVERFLOW | ST_SCRATCH_OVERFLOW))) {
                 valid = true;
                 n = B.mol_raw_len[B.read_mol[r]] + 2 * K.k;
                 m = ri.m;
