@@ -204,7 +204,7 @@ def main():
         # contiguous shards of about equal simulated bases, global ordinals
         full = s.synth_mdf(wl["shape"], args.molecules * world, seed=1000, min_len=500, max_len=100000)
         plan = s.shard_plan(full, world)
-        lo, hi, ordinal_base = plan[rank]
+        lo, hi, ordinal_base, _ = plan[rank]
         mdf = full[lo:hi]
         del full
         config["sharding"] = (f"tksm_seq_shard_plan: one MDF of {args.molecules * world} molecules cut into {world} contiguous "

@@ -941,6 +941,7 @@ __device__ __forceinline__ bool align_team_impl(const Team<W>& tm, AlignCtx<BV>&
 enum : int { FIN_EXPAND = 2, FIN_FULL = 3, FIN_QUAL = 4 };
 constexpr uint32_t RINFO_SKIP = 1;     // the qscore kernel of the class leaves the read alone: the 64-bit alignment instance /
                                        // the FIN_FULL kernel finish it
+constexpr uint32_t RINFO_BAND_LEFT = 4; // the 64-bit instance gave up on the read: the FIN_FULL kernel need not try that band again
 constexpr uint32_t RINFO_WIDE_OK = 2;  // aligned by the 64-bit instance: its qscores come from the FIN_QUAL launch on that list
 
 template <int W, bool GWS, int MODE>
@@ -1144,7 +1145,9 @@ __device__ __forceinline__ void finish_read(const Team<W>& tm, const SimParams& 
         if (MODE == FIN_FULL) {
             uint32_t eq = 0, cols = 0;
             bool ok = false;
-            if (!(P.flags & RUN_NO_ALIGN)) {
+            // (a read the thread-per-read 64-bit instance gave up on would leave the same band here: same definition)
+            const bool band_left = P.n_work_dev && B.rinfo && (B.rinfo[r].flags & RINFO_BAND_LEFT);
+            if (!(P.flags & RUN_NO_ALIGN) && !band_left) {
                 using BV = uint64_t;
                 AlignCtx<BV> A;
                 A.frag = frag;
@@ -1682,7 +1685,7 @@ __global__ void __launch_bounds__(ALIGN_K_THREADS) align_kernel(const AlignKPara
             } else {
                 // the band was left: the read goes on to the 64-bit instance, from there to the FIN_FULL kernel of the
                 // class (which gives it the edit script's own cigar); the qscore kernel leaves it alone meanwhile
-                B.rinfo[r].flags = rflags | RINFO_SKIP;
+                B.rinfo[r].flags = rflags | RINFO_SKIP | ((sizeof(BV) == 8 && run_it) ? RINFO_BAND_LEFT : 0u);
                 K.redo[atomicAdd(K.redo_count, 1u)] = r;
             }
         }
@@ -1836,7 +1839,8 @@ __device__ __forceinline__ uint32_t record_len(const FmtParams& F, uint32_t r) {
     const uint32_t mol = F.read_mol[r];
     // error_free_length = len(raw_seq), the molecule without its tail (py/sequence.py:253)
     const uint32_t L = F.mol_raw_len[mol] - (F.mol_tail_len ? F.mol_tail_len[mol] : 0u);
-    const uint32_t Lp = F.read_len ? F.read_len[r] : L;
+    // (a read that outgrew its scratch slot is flagged and reported by the host; its record is cut to the slot)
+    const uint32_t Lp = F.read_len ? min(F.read_len[r], (uint32_t)(F.seq_off[r + 1] - F.seq_off[r])) : L;
     const uint32_t h = F.read_len ? read_pct(F, r) : 10000u;
     const uint32_t idl = F.mol_id_begin[mol + 1] - F.mol_id_begin[mol];
     // "@" uuid " length=" Lp " error_free_length=" L " read_identity=" pct "% molecule_id=" id "\n" seq "\n"
@@ -1972,7 +1976,7 @@ __global__ void __launch_bounds__(256) format_kernel(const FmtParams F) {
     for (uint32_t r = blockIdx.x * 8 + warp; r < F.n_reads; r += gridDim.x * 8) {
         const uint32_t mol = F.read_mol[r];
         const uint32_t L = F.mol_raw_len[mol] - (F.mol_tail_len ? F.mol_tail_len[mol] : 0u);
-        const uint32_t Lp = F.read_len ? F.read_len[r] : L;
+        const uint32_t Lp = F.read_len ? min(F.read_len[r], (uint32_t)(F.seq_off[r + 1] - F.seq_off[r])) : L;
         const uint32_t id0 = F.mol_id_begin[mol], idl = F.mol_id_begin[mol + 1] - id0;
         uint32_t hl = 0;
         if (lane == 0) {
