@@ -466,3 +466,39 @@ def test_model_given_by_path_under_another_name(built, tmp_path):
     import json
     cal = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "calibration.json")))
     assert kappas[0][0] == pytest.approx(cal["nanopore2018"], abs=2e-3)
+
+
+def test_insertion_heavy_reads_rerun_in_larger_slots(built, tmp_path):
+    """A read that outgrows twice its fragment does not fit the slot of the first pass (ST_OPS_OVERFLOW /
+    ST_SCRATCH_OVERFLOW): the chunk runs again in slots no edit script can outgrow (engine.cu: slot_launch(grow))
+    and comes out as the CPU twin, which knows no slots, writes it.  The model here turns every 3-mer into a 6-mer."""
+    import itertools
+    from tksm_b200.sequence import BADREAD, Sequencer
+    em = tmp_path / "insertions.error"
+    with open(em, "w") as f:
+        for km in itertools.product("ACGT", repeat=3):
+            km = "".join(km)
+            ins = "".join("ACGT"[("ACGT".index(km[1]) + 1 + i) % 4] for i in range(3))
+            f.write(f"{km},0.02;{km[0]}{km[1]}{ins}{km[2]},0.9;\n")
+    rng = np.random.default_rng(11)
+    fasta = make_fasta(rng, [("chr1", 120000)], n_rate=0.0, lower=False)
+    s = Sequencer(identity=(40.0, 40.0, 0.0), seed=5)
+    s.add_reference_text(fasta)
+    s.load_models(str(em), "random")
+    mdf = s.synth_mdf(1, 60, seed=3, min_len=40, max_len=12000)
+    refs = so.load_fasta(fasta)
+    mols = so.parse_mdf(mdf)
+    seqs = [so.molecule_sequence(refs, iv) for _, iv in mols]
+    ids = [m for m, _ in mols]
+    for fastq in (True, False):
+        got = s.simulate(mdf, BADREAD, fastq=fastq)
+        assert s.last_stats["status_or"] & 3 == 0
+        assert s.last_stats["read_bases"] > 2.2 * s.last_stats["raw_bases"]     # the first pass cannot have held them
+        want = so.twin_simulate(s.tables(), seqs, ids, badread=True, fastq=fastq)
+        d = first_diff(got, want, fastq)
+        assert d is None, d
+    # a device-resident batch takes the same second pass
+    from tksm_b200.sequence import FASTQ
+    b = s.batch(mdf)
+    st = b.run(BADREAD, FASTQ)
+    assert st["status_or"] & 3 == 0 and b.fetch(BADREAD) == s.simulate(mdf, BADREAD, fastq=True)

@@ -201,6 +201,10 @@ struct Prepared {
     uint64_t scr_total = 0, raw_total = 0;   // bytes of the per-read scratch arenas
     uint32_t n_work[N_CLASSES] = {};
     uint32_t max_n_gws = 0;
+    // the same for the second pass of a batch in which a read outgrew its slot (slot_launch: grow): classes chosen
+    // by grow_len(n), so that a read may reach MAX_SLOT_LEN bases per slot
+    uint32_t n_work_grow[N_CLASSES] = {};
+    uint32_t max_n_gws_grow = 0;
     uint64_t alg_in_bytes = 0, idsum = 0;
     bool mods = false;
     StageLease stage;         // page-locked buffer of the handle's StagePool holding the blob,
@@ -223,7 +227,7 @@ struct tksm_seq_batch {
     DBuf blob;
     DevBatch db{};
     uint32_t* d_work[N_CLASSES] = {};
-    DBuf scr_seq, scr_qual, scr_raw, per_read, out[2], rec_len[2], rec_off[2], sums, gws, counters, work_keys, work_sorted, work_bins, mid, trace, redo, redo64, scr_ops, scr_cig, rinfo, atrace;
+    DBuf scr_seq, scr_qual, scr_raw, per_read, out[2], rec_len[2], rec_off[2], sums, gws, counters, work_keys, work_sorted, work_bins, mid, trace, redo, redo64, scr_ops, scr_cig, rinfo, atrace, scr_off_grow;
     HBuf stage;           // pinned upload staging
     HBuf host_out[2];     // pinned download staging (streaming to files)
     HBuf h_tot;           // pinned: record bytes per output, read bases, status
@@ -233,7 +237,8 @@ struct tksm_seq_batch {
     uint64_t out_bytes[2] = {0, 0};
     uint64_t out_cap[2] = {0, 0};
     uint32_t launches = 0;
-    int which = 0;
+    int which = 0, format = 0;
+    bool grown = false;       // the kernels ran in the larger slots of slot_launch(grow)
     int lane = 0;             // which pair of streams the batch runs on
     bool bound = false;
     bool d2h_pending = false;
@@ -252,7 +257,7 @@ struct tksm_seq_batch {
     ~tksm_seq_batch() {
         for (DBuf* d : {&blob, &scr_seq, &scr_qual, &scr_raw, &per_read, &out[0], &out[1], &rec_len[0], &rec_len[1],
                         &rec_off[0], &rec_off[1], &sums, &gws, &counters, &work_keys, &work_sorted, &work_bins, &mid, &trace, &redo,
-                        &redo64, &scr_ops, &scr_cig, &rinfo, &atrace})
+                        &redo64, &scr_ops, &scr_cig, &rinfo, &atrace, &scr_off_grow})
             d->release();
         stage.release();
         host_out[0].release();
@@ -610,9 +615,9 @@ void prepare_host(const tksm_seq* h, const std::vector<const HostBatch*>& parts,
     uint64_t* scr_off = (uint64_t*)(B + p.o_so);
     uint64_t* raw_off = (uint64_t*)(B + p.o_ro);
 
-    for (int c = 0; c < N_CLASSES; c++) p.n_work[c] = 0;
+    for (int c = 0; c < N_CLASSES; c++) p.n_work[c] = p.n_work_grow[c] = 0;
     uint64_t so = 0, ro = 0, per_read_segs = 0, per_read_mods = 0, idsum = 0;
-    p.max_n_gws = 0;
+    p.max_n_gws = p.max_n_gws_grow = 0;
     size_t r0 = 0, m0 = 0, s0 = 0, nm0 = 0, lit0 = 0, id0 = 0;
     msb[0] = 0;
     mib[0] = 0;
@@ -633,6 +638,10 @@ void prepare_host(const tksm_seq* h, const std::vector<const HostBatch*>& parts,
             while (c < GWS_CLASS && n > h->ncap[c]) c++;
             p.n_work[c]++;  // the device sorts the reads of each class (work_key / scan / scatter kernels)
             if (c == GWS_CLASS) p.max_n_gws = std::max(p.max_n_gws, n);
+            const uint32_t ng = grow_len(n);
+            while (c < GWS_CLASS && ng > h->ncap[c]) c++;
+            p.n_work_grow[c]++;
+            if (c == GWS_CLASS) p.max_n_gws_grow = std::max(p.max_n_gws_grow, ng);
             per_read_segs += hb.mol_seg_begin[m + 1] - hb.mol_seg_begin[m];
             if (nm_n) per_read_mods += hb.seg_mod_begin[hb.mol_seg_begin[m + 1]] - hb.seg_mod_begin[hb.mol_seg_begin[m]];
             idsum += hb.mol_id_begin[m + 1] - hb.mol_id_begin[m];
@@ -735,13 +744,22 @@ void run_scan(tksm_seq* h, tksm_seq_batch* b, int o, uint32_t R, uint64_t* d_tot
 constexpr size_t CNT_TOTALS = 32, CNT_READ_BASES = 48, CNT_STATUS = 56;
 
 // Enqueues the kernel sequence of the bound chunk on the compute stream; no host synchronisation.
-void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
+// grow: second pass of a chunk in which a read outgrew its slot (slot_wait).  Every read gets GROW_SLOT_MUL times
+// its scratch slot and room for MAX_SLOT_LEN bases per fragment slot, which no edit script can exceed; the length
+// classes are chosen by grow_len(n) so that the workspaces of a class hold such a read.  Results depend on the read
+// ordinal only, so the reads that had fitted come out as before.
+void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format, bool grow = false) {
     cudaStream_t S = h->lane_stream[b->lane];
     if (!b->bound) throw std::runtime_error("batch not uploaded");
     CK(cudaSetDevice(h->cfg.device));
     Prepared& p = b->prep;
     const uint32_t R = (uint32_t)p.n_reads;
     b->which = which;
+    b->format = format;
+    b->grown = grow;
+    const uint64_t scr_total = grow ? p.scr_total * GROW_SLOT_MUL : p.scr_total;
+    const uint32_t* n_work = grow ? p.n_work_grow : p.n_work;
+    const uint32_t max_n_gws = grow ? p.max_n_gws_grow : p.max_n_gws;
     b->out_bytes[0] = b->out_bytes[1] = 0;
     b->launches = 0;
     if (R == 0) return;
@@ -749,6 +767,13 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
     const bool fastq_o[2] = {(format & TKSM_SEQ_FASTQ_BADREAD) != 0, (format & TKSM_SEQ_FASTQ_PERFECT) != 0};
     const bool fastq = fastq_o[0];
     DevBatch& D = b->db;
+    D.scr_off = (const uint64_t*)((const char*)b->blob.p + p.o_so);
+    if (grow) {
+        b->scr_off_grow.ensure(((size_t)R + 1) * 8);
+        scale_offsets_kernel<<<(R + 256) / 256, 256, 0, S>>>(D.scr_off, R + 1, GROW_SLOT_MUL, b->scr_off_grow.as<uint64_t>());
+        CK(cudaGetLastError());
+        D.scr_off = b->scr_off_grow.as<uint64_t>();
+    }
     uint32_t flags = 0;
     if (want_bad) flags |= RUN_ERRORS;
     if (want_bad && fastq && !h->cfg.skip_qual_compute) flags |= RUN_QUAL;  // py/sequence.py:349-353
@@ -759,11 +784,11 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         if (dbg & 2) flags |= RUN_NO_WIDE;
     }
     if (want_bad) {
-        b->scr_seq.ensure(p.scr_total);
+        b->scr_seq.ensure(scr_total);
         if (flags & RUN_QUAL) {
-            b->scr_qual.ensure(p.scr_total);
-            b->scr_ops.ensure(p.scr_total + 64);
-            b->scr_cig.ensure(p.scr_total + 64);
+            b->scr_qual.ensure(scr_total);
+            b->scr_ops.ensure(scr_total + 64);
+            b->scr_cig.ensure(scr_total + 64);
             b->rinfo.ensure((size_t)R * sizeof(RInfo));
         }
     }
@@ -775,7 +800,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
     D.rinfo = (flags & RUN_QUAL) ? b->rinfo.as<RInfo>() : nullptr;
     D.scr_raw = want_perf ? b->scr_raw.as<uint8_t>() : nullptr;
     // output upper bounds
-    b->out_cap[0] = want_bad ? (uint64_t)R * 128 + p.idsum + p.scr_total * (fastq ? 2 : 1) : 0;
+    b->out_cap[0] = want_bad ? (uint64_t)R * 128 + p.idsum + scr_total * (fastq ? 2 : 1) : 0;
     b->out_cap[1] = want_perf ? (uint64_t)R * 128 + p.idsum + p.total_raw_bases * (fastq_o[1] ? 2 : 1) : 0;
     if (want_bad) b->out[0].ensure(b->out_cap[0]);
     if (want_perf) b->out[1].ensure(b->out_cap[1]);
@@ -790,8 +815,8 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         cap_list_c[c] = h->cap_list[c];
         slab_c[c] = h->slab[c];
     }
-    if (p.max_n_gws) {
-        const uint32_t ncap = (uint32_t)align_up(p.max_n_gws + 16, 16);
+    if (max_n_gws) {
+        const uint32_t ncap = (uint32_t)align_up(max_n_gws + 16, 16);
         ncap_c[GWS_CLASS] = ncap;
         cap_list_c[GWS_CLASS] = ncap / 2 + 64;
         slab_c[GWS_CLASS] = std::max(slab_layout(CLASS_W[GWS_CLASS], 8, ncap, cap_list_c[GWS_CLASS]).bytes,
@@ -802,7 +827,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
     // u32 words: [0..5] error-injection tickets | [8..15] totals (u64 x 4) | [16..21] expansion tickets | [24..29] qscore
     // tickets | [32..40] debug | [48..53] redo counts | [56..61] redo tickets | [64..69] alignment tickets | [72..77] tickets of its 64-bit instance | [80..85] its work counts | [88..93] qscore tickets of those reads
     CK(cudaMemsetAsync(b->counters.p, 0, 512, S));
-    if (want_bad) b->mid.ensure(3 * p.scr_total + 64 * (uint64_t)R + 64);
+    if (want_bad) b->mid.ensure(3 * scr_total + 64 * (uint64_t)R + 64);
     // alignment trace cells.  FIN_FULL kernels: one region per team of the grid (the classes run concurrently; the redo
     // launch of a class uses the regions of its first CTAs).  align_kernel: one region per warp, (Dg, Pv) of column j of
     // the warp's 32 reads side by side.
@@ -814,10 +839,10 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
     int agrid[N_CLASSES] = {};
     if (flags & RUN_QUAL)
         for (int c = 0; c < N_CLASSES; c++) {
-            if (p.n_work[c] == 0) continue;
+            if (n_work[c] == 0) continue;
             const int W2 = c == GWS_CLASS ? GWS_W2 : CLASS_W[c];
             const int teams2 = c == GWS_CLASS ? 1 : (int)h->threads2[c] / 32 / CLASS_W[c];
-            size_t grid2 = std::min<size_t>((size_t)h->num_sms, (p.n_work[c] + teams2 - 1) / teams2);
+            size_t grid2 = std::min<size_t>((size_t)h->num_sms, (n_work[c] + teams2 - 1) / teams2);
             if (CLASS_W[c] < 24) grid2 = std::min<size_t>(grid2, 32);   // redo lists only
             trace_team[c] = trace_team_bytes(W2, ncap_c[c]);
             trace_off[c] = trace_total;
@@ -829,15 +854,16 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
                 // there are and by 3 GB of cells; the 64-bit instance (about one read in a thousand) gets 16 CTAs
                 atrace_warp[c] = (uint64_t)cols * 32 * sizeof(AlignCell2<uint32_t>);
                 const uint64_t warps_mem = std::max<uint64_t>((3072ull << 20) / atrace_warp[c], 64);
-                const uint64_t warps = std::min<uint64_t>({(uint64_t)h->num_sms * 20, (p.n_work[c] + 31) / 32, warps_mem});
+                const uint64_t warps = std::min<uint64_t>({(uint64_t)h->num_sms * 20, (n_work[c] + 31) / 32, warps_mem});
                 agrid[c] = (int)((warps + AW - 1) / AW);
-                wide_class[c] = c > 0 && ncap_c[c - 1] >= ALIGN_WIDE64_FROM;
+                // (grow: a class also holds reads well below the capacity of the class before it)
+                wide_class[c] = !grow && c > 0 && ncap_c[c - 1] >= ALIGN_WIDE64_FROM;
                 atrace_off[c] = atrace_total;
                 if (!wide_class[c]) atrace_total += atrace_warp[c] * AW * agrid[c];
                 atrace64_warp[c] = (uint64_t)cols * 32 * sizeof(AlignCell2<uint64_t>);
                 if (wide_class[c]) {
                     const uint64_t wm = std::max<uint64_t>((3072ull << 20) / atrace64_warp[c], 64);
-                    const uint64_t w64 = std::min<uint64_t>({(uint64_t)h->num_sms * 8, (p.n_work[c] + 31) / 32, wm});
+                    const uint64_t w64 = std::min<uint64_t>({(uint64_t)h->num_sms * 8, (n_work[c] + 31) / 32, wm});
                     agrid64[c] = (int)((w64 + AW - 1) / AW);
                 } else {
                     agrid64[c] = std::min(agrid[c], 16);
@@ -865,6 +891,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         WS.seed_hi = h->dt.seed_hi;
         WS.ident_const = h->dt.ident_const;
         WS.k = (uint32_t)h->em.k;
+        WS.grow = grow ? 1u : 0u;
         WS.read_mol = D.read_mol;
         WS.mol_raw_len = D.mol_raw_len;
         for (int c = 0; c < 5; c++) WS.ncap[c] = ncap_c[c];
@@ -885,7 +912,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         uint32_t off = 0;
         for (int c = 0; c < N_CLASSES; c++) {
             b->d_work[c] = b->work_sorted.as<uint32_t>() + off;
-            off += p.n_work[c];
+            off += n_work[c];
         }
     }
     // The classes are independent (own reads, own ticket counter): each gets its own stream so that
@@ -893,12 +920,12 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
     CK(cudaEventRecord(b->ev_sorted, S));
     uint32_t used_streams = 0;
     for (int c = 0; c < N_CLASSES; c++) {
-        if (p.n_work[c] == 0) continue;
+        if (n_work[c] == 0) continue;
         SimParams P;
         P.T = h->dt;
         P.B = D;
         P.work = b->d_work[c];
-        P.n_work = p.n_work[c];
+        P.n_work = n_work[c];
         P.counter = b->counters.as<uint32_t>() + c;
         P.flags = flags;
         P.ncap = ncap_c[c];
@@ -912,6 +939,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format) {
         P.redo = b->redo.as<uint32_t>() + (b->d_work[c] - b->work_sorted.as<uint32_t>());
         P.redo_count = b->counters.as<uint32_t>() + 48 + c;
         P.n_work_dev = nullptr;
+        P.rb_mul = grow ? GROW_RB_MUL : 2u;
         AlignLaunch al{};
         al.grid = agrid[c];
         al.K.B = D;
@@ -1057,8 +1085,12 @@ void slot_wait(tksm_seq* h, tksm_seq_batch* b, tksm_seq_stats* st) {
     if (want_bad) {
         s.read_bases = tot[2];
         s.status_or = (uint32_t)tot[3];
-        if (s.status_or & (ST_OPS_OVERFLOW | ST_SCRATCH_OVERFLOW))
-            throw std::runtime_error("a read outgrew its scratch slot (insertion-heavy read); rerun unsupported");
+        if ((s.status_or & (ST_OPS_OVERFLOW | ST_SCRATCH_OVERFLOW)) && !b->grown) {
+            // a read outgrew its slot (more than twice its fragment): the chunk runs again in slots no read can outgrow
+            slot_launch(h, b, b->which, b->format, true);
+            slot_wait(h, b, st);
+            return;
+        }
     } else {
         s.read_bases = p.total_raw_bases;
     }

@@ -193,6 +193,7 @@ struct SimParams {
     uint32_t* redo;         // PHASE 2: reads to be finished by the PHASE 3 kernel of the class (64-bit band)
     uint32_t* redo_count;
     const uint32_t* n_work_dev;  // launches on a device-side list: number of entries (device memory); nullptr: n_work
+    uint32_t rb_mul;        // read codes a read may produce per fragment slot: 2, or GROW_RB_MUL in the larger slots of a second pass
     uint32_t* redo64;       // FIN_EXPAND: list of the 64-bit alignment instance (nullptr: that instance runs on all reads)
     uint32_t* redo64_count;
 };
@@ -994,7 +995,7 @@ __device__ __forceinline__ void finish_read(const Team<W>& tm, const SimParams& 
     // ---- slot lengths -> read offsets; read bases into rb (codes) and the scratch arena (text);
     //      `ops_mode`: instead, the cigar ops of the edit script itself (used when the alignment fails)
     uint8_t* oseq = B.scr_seq + sbase;
-    const uint32_t rbcap = (MODE == FIN_FULL || B.scr_ops) ? 2 * n : 0u;   // no read codes without qscores
+    const uint32_t rbcap = (MODE == FIN_FULL || B.scr_ops) ? P.rb_mul * n : 0u;   // no read codes without qscores
     uint32_t Ttot = 0;
     auto expand_pass = [&](const bool ops_mode) {
         uint32_t carry = 0;
@@ -1107,7 +1108,7 @@ __device__ __forceinline__ void finish_read(const Team<W>& tm, const SimParams& 
     if (MODE != FIN_QUAL) {
         expand_pass(false);
         const uint32_t Lp = Ttot - start_trim - end_trim;
-        if (Ttot > 2 * n) status |= ST_OPS_OVERFLOW;
+        if (Ttot > P.rb_mul * n) status |= ST_OPS_OVERFLOW;
         if (Lp > scap) status |= ST_SCRATCH_OVERFLOW;
         if (tm.rank == 0) {
             B.read_len[r] = Lp;
@@ -1693,6 +1694,19 @@ __global__ void __launch_bounds__(ALIGN_K_THREADS) align_kernel(const AlignKPara
     }
 }
 
+// -------------------------------------------------------------- larger slots
+// A read may not outgrow twice its fragment in the first pass of a chunk (scratch slot of 2 L + 32 bytes, 2 n read
+// codes).  A chunk in which one did (ST_OPS_OVERFLOW / ST_SCRATCH_OVERFLOW) runs again with slots GROW_SLOT_MUL times
+// as large and GROW_RB_MUL n read codes (MAX_SLOT_LEN bases per slot: the most an edit script can produce), in the
+// length class that holds grow_len(n) slots, since the workspaces of a class hold twice its capacity in read codes.
+constexpr uint32_t GROW_SLOT_MUL = 3, GROW_RB_MUL = MAX_SLOT_LEN;
+__host__ __device__ inline uint32_t grow_len(uint32_t n) { return (GROW_RB_MUL * n + 1) / 2; }
+
+__global__ void scale_offsets_kernel(const uint64_t* in, uint32_t count, uint32_t mul, uint64_t* out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) out[i] = in[i] * mul;
+}
+
 // -------------------------------------------------------------- work order
 // Reads are handed to the simulate kernels class by class, inside a class by ascending target
 // identity (32 buckets: the error level sets the number of trials) and then by descending length,
@@ -1712,6 +1726,7 @@ struct WorkSortParams {
     uint32_t ncap[5];       // fragment capacity of the shared-memory classes
     uint32_t len_shift[6];  // quantisation of (capacity - n) per class
     uint32_t gws_cap;       // capacity used for the global-workspace class
+    uint32_t grow;          // classes by grow_len(n): second pass of a chunk with an outgrown slot (engine.cu: slot_launch)
     uint32_t* keys;         // R
     uint32_t* bins;         // WORK_BINS (zeroed), turned into cursors by work_scan_kernel
     uint32_t* work;         // R: sorted read indices
@@ -1720,7 +1735,8 @@ struct WorkSortParams {
 __global__ void work_key_kernel(const WorkSortParams W) {
     const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= W.n_reads) return;
-    const uint32_t n = W.mol_raw_len[W.read_mol[r]] + 2 * W.k;
+    uint32_t n = W.mol_raw_len[W.read_mol[r]] + 2 * W.k;
+    if (W.grow) n = grow_len(n);
     uint32_t c = 0;
     while (c < 5 && n > W.ncap[c]) c++;
     const uint32_t cap = c < 5 ? W.ncap[c] : W.gws_cap;
