@@ -156,6 +156,24 @@ int tksm_seq_shard_plan(tksm_seq* h, const char* mdf, size_t mdf_len, int world,
 int tksm_seq_run_files_multi(tksm_seq* const* handles, int n_handles, const char* mdf_path, const char* badread_path,
                              const char* perfect_path, tksm_seq_stats* stats);
 
+/* Record offsets without allocation.  This entry point has no counterpart in the reference; it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  It is the record-offset scan of the formatting stage on its own:
+ * d_rec_off[i] = d_rec_len[0] + ... + d_rec_len[i-1] (byte offset of record i in the output file) and
+ * *d_total = the sum of all lengths.  d_rec_len (n_records x u32), d_rec_off (n_records x u64) and d_total (one u64)
+ * are DEVICE pointers on `device`, owned by the caller; cuda_stream is a cudaStream_t (NULL: the default stream) and
+ * the kernels are only enqueued on it: synchronise the stream before reading the results.  The call allocates
+ * nothing (no cudaMalloc / cudaFree, no allocating library routine): the per-block sums it needs live in a
+ * file-scope device array of 32 784 bytes that every GPU loading the library holds until the process exits, which
+ * limits a call to TKSM_SEQ_STATIC_SCAN_MAX_RECORDS records (more: return code 2, tksm_seq_last_error(NULL) says
+ * so).  All calls on a device share that array: calls that may overlap on the GPU (different streams, different
+ * threads) race and must be serialised by the caller; calls in stream order are safe and nothing has to be cleared
+ * between them.  The first call on a device looks up the array's address (cudaGetSymbolAddress); a call with
+ * n_records = 0 does only that and writes *d_total = 0, so it can serve as set-up before a graph capture. */
+#define TKSM_SEQ_STATIC_SCAN_MAX_RECORDS (1u << 24)
+int tksm_seq_record_offsets_static(int device, const uint32_t* d_rec_len, uint32_t n_records, uint64_t* d_rec_off,
+                                   uint64_t* d_total, void* cuda_stream);
+
 /* the module entry point: argv[0] == "sequence" */
 int tksm_sequence_main(int argc, char** argv);
 

@@ -136,5 +136,6 @@ def lib():
     L.tksm_seq_tail_draw.argtypes = [vp, u64, C.c_uint32, vp, sz, C.POINTER(C.c_uint32)]
     L.tksm_seq_synth_mdf.argtypes = [vp, C.c_int, u64, u64, C.c_uint32, C.c_uint32, C.POINTER(vp), C.POINTER(sz)]
     L.tksm_sequence_main.argtypes = [C.c_int, C.POINTER(cp)]
+    L.tksm_seq_record_offsets_static.argtypes = [C.c_int, vp, C.c_uint32, vp, vp, vp]
     _lib = L
     return L

@@ -2069,3 +2069,66 @@ const GenomeStore* engine_genome(const tksm_seq* h) { return &h->genome; }
 const tksm_seq_config* engine_config(const tksm_seq* h) { return &h->cfg; }
 
 }  // namespace tk
+
+// ---------------------------------------------------------------- record offsets without allocation
+// tksm_seq_record_offsets_static (include/tksm_seq.h): the record-offset scan of the formatting stage (run_scan
+// above: scan_block_sums -> scan_sums -> scan_final) for callers that may not allocate.  Its scratch, the per-block
+// sums, lives in a file-scope device array instead of a DBuf; every device that loads the library holds the
+// STATIC_SCAN_SCRATCH_BYTES of it until the process exits.
+namespace {
+
+constexpr uint32_t STATIC_SCAN_MAX_RECORDS = TKSM_SEQ_STATIC_SCAN_MAX_RECORDS;
+constexpr uint32_t STATIC_SCAN_PER_BLOCK = tk::SCAN_BLOCK * tk::SCAN_ITEMS;
+constexpr uint32_t STATIC_SCAN_MAX_BLOCKS = (STATIC_SCAN_MAX_RECORDS + STATIC_SCAN_PER_BLOCK - 1) / STATIC_SCAN_PER_BLOCK;
+constexpr size_t STATIC_SCAN_SCRATCH_BYTES = (size_t)(STATIC_SCAN_MAX_BLOCKS + 2) * 8;   // 32 784 bytes
+static_assert(STATIC_SCAN_SCRATCH_BYTES <= 64 * 1024, "the static scan scratch is meant to stay small");
+
+// In host code this name is only a handle for cudaGetSymbolAddress, never a device address.
+static __device__ __align__(256) uint64_t g_static_scan_sums[STATIC_SCAN_MAX_BLOCKS + 2];
+
+constexpr int STATIC_SCAN_MAX_DEVICES = 64;
+std::mutex g_static_scan_mu;
+uint64_t* g_static_scan_ptr[STATIC_SCAN_MAX_DEVICES] = {};   // device address of the array on each device (set once)
+
+// device address of the scratch on `device` (which must be current); looked up once per device
+cudaError_t static_scan_scratch(int device, uint64_t** out) {
+    std::lock_guard<std::mutex> g(g_static_scan_mu);
+    if (!g_static_scan_ptr[device]) {
+        uint64_t* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_static_scan_sums);
+        if (e != cudaSuccess) return e;
+        g_static_scan_ptr[device] = p;
+    }
+    *out = g_static_scan_ptr[device];
+    return cudaSuccess;
+}
+
+}  // namespace
+
+extern "C" int tksm_seq_record_offsets_static(int device, const uint32_t* d_rec_len, uint32_t n_records, uint64_t* d_rec_off,
+                                              uint64_t* d_total, void* cuda_stream) {
+    auto fail = [](int code, const std::string& msg) {
+        g_create_error = "tksm_seq_record_offsets_static: " + msg;
+        return code;
+    };
+    if (n_records > STATIC_SCAN_MAX_RECORDS)
+        return fail(2, std::to_string(n_records) + " records exceed the static scratch (at most " +
+                           std::to_string(STATIC_SCAN_MAX_RECORDS) + " per call); split the call or use a batch");
+    if (device < 0 || device >= STATIC_SCAN_MAX_DEVICES) return fail(2, "invalid device ordinal");
+    if (!d_total || (n_records && (!d_rec_len || !d_rec_off))) return fail(2, "null pointer");
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return fail(1, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
+    uint64_t* sums = nullptr;
+    e = static_scan_scratch(device, &sums);
+    if (e != cudaSuccess) return fail(1, std::string("cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+    cudaStream_t S = (cudaStream_t)cuda_stream;
+    // Nothing in the scratch has to start at zero: the first kernel overwrites sums[0 .. nb) and the second one reads
+    // exactly those entries (n_records == 0: none), whatever an earlier call left behind.
+    const uint32_t nb = (n_records + STATIC_SCAN_PER_BLOCK - 1) / STATIC_SCAN_PER_BLOCK;
+    if (nb) tk::scan_block_sums<<<nb, tk::SCAN_BLOCK, 0, S>>>(d_rec_len, n_records, sums);
+    tk::scan_sums<<<1, 1024, 0, S>>>(sums, nb, d_total);
+    if (nb) tk::scan_final<<<nb, tk::SCAN_BLOCK, 0, S>>>(d_rec_len, n_records, sums, d_rec_off);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(1, std::string("kernel launch: ") + cudaGetErrorString(e));
+    return 0;
+}
