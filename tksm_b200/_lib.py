@@ -84,7 +84,7 @@ EXPORTS = [
     "tksm_seq_fetch_reference", "tksm_seq_commit_reference", "tksm_seq_load_models", "tksm_seq_get_tables",
     "tksm_seq_run_files", "tksm_seq_simulate_text", "tksm_seq_batch_create", "tksm_seq_batch_run",
     "tksm_seq_batch_fetch", "tksm_seq_batch_destroy", "tksm_seq_synth_mdf", "tksm_seq_shard_plan", "tksm_seq_tail_draw", "tksm_seq_run_files_multi",
-    "tksm_sequence_main",
+    "tksm_sequence_main", "tksm_seq_record_offsets_static",
 ]
 
 
