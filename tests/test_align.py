@@ -142,7 +142,7 @@ def emul_one():
     os.makedirs(bdir, exist_ok=True)
     lines = open(kern).read().split("\n")
     a = next(i for i, l in enumerate(lines) if l.startswith("struct ByteStream {"))
-    b = next(i for i, l in enumerate(lines) if l.startswith("// shared memory of one warp of align_kernel<BV>"))
+    b = next(i for i, l in enumerate(lines) if l.startswith("// -------------------------------------------------------------- align_kernel"))
     open(os.path.join(bdir, "align_one_body.inc"), "w").write("\n".join(lines[a:b]) + "\n")
     out = os.path.join(bdir, "libalign_one_emul.so")
     subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", out, src])
@@ -154,7 +154,7 @@ def emul_one():
 @needs_models
 @pytest.mark.parametrize("em,ident,n_reads", [("nanopore2020", (84.0, 99.0, 5.5), 250), ("nanopore2018", (70.0, 85.0, 6.0), 100)])
 def test_thread_per_read_alignment_equals_the_integer_band(built, emul_one, em, ident, n_reads):
-    """align_kernel (one thread per read: streamed forward pass, traceback on staged blocks) against twin_bnw, with
+    """align_kernel (one thread per read: streamed forward pass, traceback through register windows) against twin_bnw, with
     the kernel's band rule: 32-bit band up to ALIGN_WIDE64_FROM slots, retried with 64 bits; 64 bits at once above."""
     seen = {"n": 0, "wide": 0, "bad": []}
 

@@ -234,6 +234,7 @@ struct tksm_seq_batch {
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // kernels begin, simulate end, kernels end, downloads end, totals on host
     cudaEvent_t ev_sorted = nullptr, ev_class[4] = {nullptr, nullptr, nullptr, nullptr};  // work order ready; class stream done
     cudaEvent_t ev_fork[4] = {nullptr, nullptr, nullptr, nullptr}, ev_side[4] = {nullptr, nullptr, nullptr, nullptr};  // side streams
+    cudaEvent_t ev_early[4] = {nullptr, nullptr, nullptr, nullptr};   // expansion of a class done (its side stream starts on the long reads)
     uint64_t out_bytes[2] = {0, 0};
     uint64_t out_cap[2] = {0, 0};
     uint32_t launches = 0;
@@ -250,6 +251,8 @@ struct tksm_seq_batch {
         for (auto& e : ev_class)
             if (!e) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         for (auto& e : ev_fork)
+            if (!e) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        for (auto& e : ev_early)
             if (!e) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         for (auto& e : ev_side)
             if (!e) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -269,6 +272,8 @@ struct tksm_seq_batch {
         for (auto& e : ev_class)
             if (e) cudaEventDestroy(e);
         for (auto& e : ev_fork)
+            if (e) cudaEventDestroy(e);
+        for (auto& e : ev_early)
             if (e) cudaEventDestroy(e);
         for (auto& e : ev_side)
             if (e) cudaEventDestroy(e);
@@ -465,7 +470,8 @@ struct AlignLaunch {
     bool wide_class;          // every read of the class is above ALIGN_WIDE64_FROM slots: 64-bit instance on all of them
     int grid64;
     cudaStream_t side;        // stream of the 64-bit instance and the redo list
-    cudaEvent_t ev_fork, ev_side;
+    cudaEvent_t ev_fork, ev_side, ev_early;
+    bool early64;             // the class holds reads above ALIGN_WIDE64_FROM slots: the 64-bit instance starts on them beside the 32-bit one
 };
 template <int W, bool GWS, int W2 = W>
 void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, const Phase2Launch& p2, const AlignLaunch& al) {
@@ -491,8 +497,6 @@ void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, const P
     if (!(P.flags & RUN_QUAL)) return;
     constexpr int AW = ALIGN_K_THREADS / 32;
     // (per device: a process may drive several GPUs)
-    CK(cudaFuncSetAttribute(align_kernel<uint32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(AW * align_warp_smem<uint32_t>())));
-    CK(cudaFuncSetAttribute(align_kernel<uint64_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(AW * align_warp_smem<uint64_t>())));
     cudaStream_t side = al.side;
     if (al.wide_class) {
         // 64-bit band at once, on every read of the class; what leaves it goes to the FIN_FULL redo list
@@ -501,14 +505,31 @@ void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, const P
         K2.trace_warp_bytes = al.trace64_warp_bytes;
         K2.redo = P.redo;
         K2.redo_count = P.redo_count;
-        align_kernel<uint64_t><<<al.grid64, ALIGN_K_THREADS, AW * align_warp_smem<uint64_t>(), stream>>>(K2);
+        align_kernel<uint64_t><<<al.grid64, ALIGN_K_THREADS, 0, stream>>>(K2);
         CK(cudaGetLastError());
         CK(cudaEventRecord(al.ev_fork, stream));
         Q.counter = counters + 24;
         launch_sim_phase<W, GWS, FIN_QUAL>(stream, Q, smem_small, grid_small, 1024);
         CK(cudaStreamWaitEvent(side, al.ev_fork, 0));
     } else {
-        align_kernel<uint32_t><<<al.grid, ALIGN_K_THREADS, AW * align_warp_smem<uint32_t>(), stream>>>(al.K);
+        // side stream, at once: the reads above ALIGN_WIDE64_FROM slots (the expansion listed them; `split` = how many)
+        uint32_t* const split = counters + 104;
+        if (al.early64) {
+            CK(cudaMemcpyAsync(split, al.redo64_count, 4, cudaMemcpyDeviceToDevice, stream));
+            CK(cudaEventRecord(al.ev_early, stream));
+            CK(cudaStreamWaitEvent(side, al.ev_early, 0));
+            AlignKParams K1 = al.K;
+            K1.work = al.redo64;
+            K1.n_work_dev = split;
+            K1.counter = counters + 96;
+            K1.trace = al.trace64;
+            K1.trace_warp_bytes = al.trace64_warp_bytes;
+            K1.redo = P.redo;
+            K1.redo_count = P.redo_count;
+            align_kernel<uint64_t><<<al.grid64, ALIGN_K_THREADS, 0, side>>>(K1);
+            CK(cudaGetLastError());
+        }
+        align_kernel<uint32_t><<<al.grid, ALIGN_K_THREADS, 0, stream>>>(al.K);
         CK(cudaGetLastError());
         CK(cudaEventRecord(al.ev_fork, stream));
         // main stream: qscores of the reads the 32-bit band did
@@ -521,12 +542,13 @@ void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, const P
         AlignKParams K2 = al.K;
         K2.work = al.redo64;
         K2.n_work_dev = al.redo64_count;
+        K2.work_begin_dev = al.early64 ? split : nullptr;   // (zero without the early launch: the counters are cleared per batch)
         K2.counter = al.K.counter + 8;
         K2.trace = al.trace64;
         K2.trace_warp_bytes = al.trace64_warp_bytes;
         K2.redo = P.redo;
         K2.redo_count = P.redo_count;
-        align_kernel<uint64_t><<<al.grid64, ALIGN_K_THREADS, AW * align_warp_smem<uint64_t>(), side>>>(K2);
+        align_kernel<uint64_t><<<al.grid64, ALIGN_K_THREADS, 0, side>>>(K2);
         CK(cudaGetLastError());
         SimParams Q2 = Q;
         Q2.counter = counters + 88;
@@ -853,8 +875,10 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format, bool gro
                 // 32-bit instance: enough warps to fill the SMs (20 resident per SM: shared memory), bounded by the reads
                 // there are and by 3 GB of cells; the 64-bit instance (about one read in a thousand) gets 16 CTAs
                 atrace_warp[c] = (uint64_t)cols * 32 * sizeof(AlignCell2<uint32_t>);
-                const uint64_t warps_mem = std::max<uint64_t>((3072ull << 20) / atrace_warp[c], 64);
-                const uint64_t warps = std::min<uint64_t>({(uint64_t)h->num_sms * 20, (n_work[c] + 31) / 32, warps_mem});
+                static const int aw32 = getenv("TKSM_SEQ_AW32") ? atoi(getenv("TKSM_SEQ_AW32")) : 36;   // warps per SM (56 registers)
+                static const int aw64 = getenv("TKSM_SEQ_AW64") ? atoi(getenv("TKSM_SEQ_AW64")) : 16;
+                const uint64_t warps_mem = std::max<uint64_t>((6144ull << 20) / atrace_warp[c], 64);
+                const uint64_t warps = std::min<uint64_t>({(uint64_t)h->num_sms * aw32, (n_work[c] + 31) / 32, warps_mem});
                 agrid[c] = (int)((warps + AW - 1) / AW);
                 // (grow: a class also holds reads well below the capacity of the class before it)
                 wide_class[c] = !grow && c > 0 && ncap_c[c - 1] >= ALIGN_WIDE64_FROM;
@@ -862,11 +886,12 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format, bool gro
                 if (!wide_class[c]) atrace_total += atrace_warp[c] * AW * agrid[c];
                 atrace64_warp[c] = (uint64_t)cols * 32 * sizeof(AlignCell2<uint64_t>);
                 if (wide_class[c]) {
-                    const uint64_t wm = std::max<uint64_t>((3072ull << 20) / atrace64_warp[c], 64);
-                    const uint64_t w64 = std::min<uint64_t>({(uint64_t)h->num_sms * 8, (n_work[c] + 31) / 32, wm});
+                    const uint64_t wm = std::max<uint64_t>((6144ull << 20) / atrace64_warp[c], 64);
+                    const uint64_t w64 = std::min<uint64_t>({(uint64_t)h->num_sms * aw64, (n_work[c] + 31) / 32, wm});
                     agrid64[c] = (int)((w64 + AW - 1) / AW);
                 } else {
-                    agrid64[c] = std::min(agrid[c], 16);
+                    // (a class that also holds reads above ALIGN_WIDE64_FROM slots gives this instance real work)
+                    agrid64[c] = std::min(agrid[c], ncap_c[c] > ALIGN_WIDE64_FROM ? h->num_sms : 16);
                 }
                 atrace64_off[c] = atrace_total;
                 atrace_total += atrace64_warp[c] * AW * agrid64[c];
@@ -952,6 +977,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format, bool gro
         al.side = h->side_stream[b->lane][used_streams % 4];
         al.ev_fork = b->ev_fork[used_streams % 4];
         al.ev_side = b->ev_side[used_streams % 4];
+        al.ev_early = b->ev_early[used_streams % 4];
         al.trace64 = b->atrace.as<uint8_t>() + atrace64_off[c];
         al.trace64_warp_bytes = atrace64_warp[c];
         al.K.k = (uint32_t)h->em.k;
@@ -963,6 +989,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format, bool gro
         al.wide_class = wide_class[c];
         al.grid64 = agrid64[c];
         P.redo64 = wide_class[c] ? nullptr : al.redo64;
+        al.early64 = !wide_class[c] && ncap_c[c] > ALIGN_WIDE64_FROM;
         P.redo64_count = al.redo64_count;
         al.K.redo = al.redo64;
         al.K.redo_count = al.redo64_count;

@@ -1390,6 +1390,7 @@ struct AlignKParams {
     uint32_t* redo;         // reads this kernel gives up on: for its 64-bit instance (32-bit instance) / the FIN_FULL kernel
     uint32_t* redo_count;
     const uint32_t* n_work_dev;   // 64-bit instance: number of entries of `work` (device memory)
+    const uint32_t* work_begin_dev;   // ... and the entry it starts at (an earlier launch did those before it); nullptr: 0
 };
 
 // sequential bytes of a global array through 8-byte windows, the next window in flight (base 8-byte aligned; reads up
@@ -1441,113 +1442,182 @@ struct ByteStreamBack {
     }
 };
 
+// 2 BW rows of one bit plane of the read, bit 0 of `cur` = row lo of the band: the band itself and the rows the next
+// columns will shift into it
+template <typename BV>
+struct AlignAhead {
+    BV cur, nxt;
+    __device__ __forceinline__ void shift(uint32_t s) {   // 1 <= s < BW
+        constexpr uint32_t BW = 8 * sizeof(BV);
+        cur = (cur >> s) | (nxt << (BW - s));
+        nxt >>= s;
+    }
+    __device__ __forceinline__ void insert(uint32_t bits8, uint32_t p) {   // eight rows at p <= 2 BW - 8
+        constexpr uint32_t BW = 8 * sizeof(BV);
+        if (p < BW) {
+            cur |= BV(bits8) << p;
+            if (p + 8 > BW) nxt |= BV(bits8) >> (BW - p);
+        } else {
+            nxt |= BV(bits8) << (p - BW);
+        }
+    }
+};
+// bits 0, 8, 16, 24 of x -> bits 0..3
+__device__ __forceinline__ uint32_t gather4(uint32_t x) { return (x * 0x10204080u) >> 28; }
+
+// Eq of a column whose fragment byte is not A/C/G/T (an N as a rule): the rows of the band that hold the same byte
+template <typename BV>
+__device__ inline BV align_eq_rare(const uint8_t* rb, uint32_t lo, uint32_t m, uint32_t f) {
+    constexpr uint32_t BW = 8 * sizeof(BV);
+    BV Eq = 0;
+#pragma unroll 1
+    for (uint32_t b = 0; b < BW; b++) {
+        const uint32_t row = lo + b;
+        if (row > m) break;
+        if (rb[row - 1] == f) Eq |= BV(1) << b;
+    }
+    return Eq;
+}
+
 template <typename BV>
 __device__ __forceinline__ bool align_one(const uint8_t* frag, const uint8_t* slen, const uint8_t* rb, uint8_t* out, uint32_t n,
-                                          uint32_t m, AlignCell2<BV>* cells, uint8_t* sm, bool valid, uint32_t& eq_out,
-                                          uint32_t& cols_out) {
-    // every thread of the warp comes here (`valid`: it has a read); n = m = 0 otherwise
+                                          uint32_t m, AlignCell2<BV>* cells, uint32_t off, uint32_t nmax, bool valid,
+                                          uint32_t& eq_out, uint32_t& cols_out) {
+    // every thread of the warp comes here (`valid`: it has a read); n = m = 0 otherwise; nmax = largest n of the warp
     constexpr uint32_t BW = 8 * sizeof(BV);
-    // ---- forward: the column step of align_forward_chunk over columns 1 .. n from the true boundary, eight columns
-    //      per group (their slot lengths and fragment codes are two 8-byte words, fetched one group ahead)
-    if (valid) {
-        ByteStream rs;
-        rs.open(rb);
-        AlignPlanes<BV> pl;
-        pl.b0 = pl.b1 = pl.v = pl.np = 0;
-        for (uint32_t b = 0; b < BW && b < m; b++) pl.put(rs.next(), b);
+    const uint2* l8 = (const uint2*)slen;
+    const uint2* f8 = (const uint2*)frag;
+    const uint2* r8 = (const uint2*)rb;
+    // ---- forward: the column step of align_forward_chunk over columns 1 .. n from the true boundary, the 32 threads
+    //      of the warp in step (same instructions for every thread: the per-thread branches of the chunked form cost
+    //      a warp the sum of their paths).  The read enters as bit planes of 2 BW rows, refilled eight rows at a time
+    //      for the whole warp at once when one of its threads runs low.
+    {
+        AlignAhead<BV> a0{0, 0}, a1{0, 0}, ax{0, 0}, an{0, 0};   // code bit 0, code bit 1, "not A/C/G/T, or beyond the read", "N"
+        uint32_t avail = 0, gnext = 0;   // rows the planes hold from row lo on; next eight-byte group of the read
+        auto refill = [&]() {
+            uint64_t w = 0;
+            if (8 * gnext < m) w = ByteStream::ld(r8 + gnext);
+            const uint32_t x0 = (uint32_t)w, x1 = (uint32_t)(w >> 32);
+            const uint32_t t0 = x0 & 0xFCFCFCFCu, t1 = x1 & 0xFCFCFCFCu;
+            uint32_t inv = 0;
+            if (t0 | t1) {   // (rare: an N of the fragment that came through, or another IUPAC letter)
+                inv = gather4((((t0 & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | t0) >> 7 & 0x01010101u) |
+                      gather4((((t1 & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | t1) >> 7 & 0x01010101u) << 4;
+                const uint32_t y0 = x0 ^ 0x4E4E4E4Eu, y1 = x1 ^ 0x4E4E4E4Eu;   // zero bytes: N (78)
+                const uint32_t z0 = ~(((y0 & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | y0) >> 7 & 0x01010101u;
+                const uint32_t z1 = ~(((y1 & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | y1) >> 7 & 0x01010101u;
+                uint32_t isn = gather4(z0) | gather4(z1) << 4;
+                const uint32_t have_n = m > 8 * gnext ? m - 8 * gnext : 0u;
+                if (have_n < 8) isn &= (1u << have_n) - 1u;
+                an.insert(isn, avail);
+            }
+            const uint32_t have = m > 8 * gnext ? m - 8 * gnext : 0u;   // read bases of this group
+            if (have < 8) inv |= 0xFFu << have;
+            a0.insert(gather4(x0 & 0x01010101u) | gather4(x1 & 0x01010101u) << 4, avail);
+            a1.insert(gather4((x0 >> 1) & 0x01010101u) | gather4((x1 >> 1) & 0x01010101u) << 4, avail);
+            ax.insert(inv & 0xFFu, avail);
+            avail += 8;
+            gnext++;
+        };
+#pragma unroll 1
+        for (uint32_t t = 0; t < 2 * BW / 8; t++) refill();
         BV Pv = ~BV(0), Mv = 0;
         uint32_t o_prev = 0, lo_prev = 1;
-        AlignCell2<BV>* cell = cells;
-        const uint2* lp = (const uint2*)slen;
-        const uint2* fp = (const uint2*)frag;
-        uint64_t lw_n = ByteStream::ld(lp++), fw_n = ByteStream::ld(fp++);
-        for (uint32_t j0 = 1; j0 <= n; j0 += 8) {
+        AlignCell2<BV>* cell = cells + (size_t)off * 32;
+        uint64_t lw_n = 0, fw_n = 0;
+        if (n) {
+            lw_n = ByteStream::ld(l8);
+            fw_n = ByteStream::ld(f8);
+        }
+#pragma unroll 1
+        for (uint32_t j0 = 1; j0 <= nmax; j0 += 8) {
             const uint64_t lw = lw_n, fw = fw_n;
-            lw_n = ByteStream::ld(lp++);   // (reads up to 15 bytes past the arrays: inside the padded record)
-            fw_n = ByteStream::ld(fp++);
+            if (j0 + 8 <= n) {   // (the group after the last one is never fetched)
+                lw_n = ByteStream::ld(l8 + (j0 >> 3) + 1);
+                fw_n = ByteStream::ld(f8 + (j0 >> 3) + 1);
+            }
 #pragma unroll
             for (uint32_t t8 = 0; t8 < 8; t8++) {
-                if (j0 + t8 > n) break;
-                const uint32_t o = o_prev + ((uint32_t)(lw >> (8 * t8)) & 0xFFu);
-                const uint32_t lo = align_lo<BV>(o);
-                const uint32_t s = lo - lo_prev;
-                if (s) {
-                    Pv = (Pv >> s) | (~BV(0) << (BW - s));
-                    Mv >>= s;
-                    pl.b0 >>= s;
-                    pl.b1 >>= s;
-                    pl.v >>= s;
-                    pl.np >>= s;
-                    for (uint32_t t = 0; t < s; t++)
-                        if (lo_prev + BW + t <= m) pl.put(rs.next(), BW - s + t);
-                } else if (lo > 1) {
-                    Pv &= ~BV(1);
-                    Mv |= BV(1);
+                const bool live = j0 + t8 <= n;
+                if (__any_sync(0xffffffffu, live && avail < BW + 13)) {
+                    if (avail + 8 <= 2 * BW) refill();
                 }
-                const uint32_t f = (uint32_t)(fw >> (8 * t8)) & 0xFFu;
-                BV Eq;
-                if (f < 4) {
-                    const BV f0 = BV(0) - BV(f & 1u), f1 = BV(0) - BV(f >> 1);
-                    Eq = pl.v & ~((pl.b0 ^ f0) | (pl.b1 ^ f1));
-                } else if (f == 78u) {
-                    Eq = pl.np;
-                } else {
-                    Eq = 0;
-                    for (uint32_t b = 0; b < BW; b++) {
-                        const uint32_t row = lo + b;
-                        if (row > m) break;
-                        if (rb[row - 1] == f) Eq |= BV(1) << b;
+                if (live) {
+                    const uint32_t o = o_prev + ((uint32_t)(lw >> (8 * t8)) & 0xFFu);
+                    const uint32_t lo = align_lo<BV>(o);
+                    const uint32_t s = lo - lo_prev;
+                    if (s) {
+                        Pv = (Pv >> s) | (~BV(0) << (BW - s));
+                        Mv >>= s;
+                        a0.shift(s);
+                        a1.shift(s);
+                        ax.shift(s);
+                        an.shift(s);
+                        avail -= s;
+                    } else if (lo > 1) {
+                        Pv &= ~BV(1);
+                        Mv |= BV(1);
                     }
+                    const uint32_t f = (uint32_t)(fw >> (8 * t8)) & 0xFFu;
+                    BV Eq;
+                    if (f < 4) {
+                        const BV f0 = BV(0) - BV(f & 1u), f1 = BV(0) - BV(f >> 1);
+                        Eq = ~(ax.cur | (a0.cur ^ f0) | (a1.cur ^ f1));
+                    } else if (f == 78u) {
+                        Eq = an.cur;
+                    } else {
+                        Eq = align_eq_rare<BV>(rb, lo, m, f);
+                    }
+                    const BV Xv = Eq | Mv;
+                    const BV Xh = (((Eq & Pv) + Pv) ^ Pv) | Eq;
+                    BV Ph = Mv | ~(Xh | Pv);
+                    BV Mh = Pv & Xh;
+                    const BV D0 = Xh | Mv;
+                    Ph = (Ph << 1) | BV(1);
+                    Mh <<= 1;
+                    Pv = Mh | ~(Xv | Ph);
+                    Mv = Ph & Xv;
+                    AlignCell2<BV> c;
+                    c.dg = Eq | ~D0;
+                    c.pv = Pv;
+                    cell[(size_t)t8 * 32] = c;
+                    o_prev = o;
+                    lo_prev = lo;
                 }
-                const BV Xv = Eq | Mv;
-                const BV Xh = (((Eq & Pv) + Pv) ^ Pv) | Eq;
-                BV Ph = Mv | ~(Xh | Pv);
-                BV Mh = Pv & Xh;
-                const BV D0 = Xh | Mv;
-                Ph = (Ph << 1) | BV(1);
-                Mh <<= 1;
-                Pv = Mh | ~(Xv | Ph);
-                Mv = Ph & Xv;
-                AlignCell2<BV> c;
-                c.dg = Eq | ~D0;
-                c.pv = Pv;
-                cell[(size_t)t8 * 32] = c;
-                o_prev = o;
-                lo_prev = lo;
             }
             cell += 8 * 32;
         }
     }
-    // ---- traceback over the whole read (align_trace_chunk<TRACE_WRITE> with cmin = 1, bottom, top).  The trace array
-    // is in DRAM by now and every step depends on the one before it, so the thread stages what the walk reads in
-    // shared memory 32 columns at a time (32 cells, 32 slot lengths, 32 fragment codes: all loads of a block in flight
-    // together) and the read codes 32 rows at a time.
-    const uint32_t lane = threadIdx.x & 31;
-    AlignCell2<BV>* sc = (AlignCell2<BV>*)sm + lane;                               // [column & 31][lane]
-    uint32_t* sl = (uint32_t*)(sm + 32 * 32 * sizeof(AlignCell2<BV>)) + lane;      // [word][lane]: slot lengths
-    uint32_t* sf = sl + 8 * 32;                                                    // fragment codes
-    uint32_t* sr = sf + 8 * 32;                                                    // read codes
-    // The 32 threads of the warp stage their blocks TOGETHER: a thread walks until it needs a block it does not have,
-    // then waits for the others (a block is 32 columns, about 64 steps, for every thread), so the loads of a block are
-    // issued once for the warp instead of once per thread.
-    auto col_block = [&](uint32_t nb) {   // columns with (j - 1) >> 5 == nb
-        const uint32_t c0 = nb << 5;
-#pragma unroll 8
-        for (uint32_t c = 0; c < 32; c++)
-            if (c0 + c < n) sc[c * 32] = cells[(size_t)(c0 + c) * 32];
-        const uint4 a0 = __ldg((const uint4*)(slen + c0)), a1 = __ldg((const uint4*)(slen + c0) + 1);
-        const uint4 f0 = __ldg((const uint4*)(frag + c0)), f1 = __ldg((const uint4*)(frag + c0) + 1);
-        sl[0] = a0.x; sl[32] = a0.y; sl[64] = a0.z; sl[96] = a0.w; sl[128] = a1.x; sl[160] = a1.y; sl[192] = a1.z; sl[224] = a1.w;
-        sf[0] = f0.x; sf[32] = f0.y; sf[64] = f0.z; sf[96] = f0.w; sf[128] = f1.x; sf[160] = f1.y; sf[192] = f1.z; sf[224] = f1.w;
-    };
-    auto row_block = [&](uint32_t nb) {   // read bases with index >> 5 == nb
-        const uint4 r0 = __ldg((const uint4*)(rb + (nb << 5))), r1 = __ldg((const uint4*)(rb + (nb << 5)) + 1);
-        sr[0] = r0.x; sr[32] = r0.y; sr[64] = r0.z; sr[96] = r0.w; sr[128] = r1.x; sr[160] = r1.y; sr[192] = r1.z; sr[224] = r1.w;
-    };
-    auto byte_of = [](const uint32_t* w, uint32_t idx) { return (w[((idx & 31u) >> 2) * 32] >> (8u * (idx & 3u))) & 0xFFu; };
-    uint32_t i = m, j = n, oj = m, lo = 1;
-    uint32_t jb = 0xFFFFFFFFu, ib = 0xFFFFFFFFu;
-    AlignCell2<BV> cur{};
+    // ---- traceback over the whole read (align_trace_chunk<TRACE_WRITE> with cmin = 1, bottom, top), the 32 threads of
+    // the warp one move at a time.  Every move depends on the one before it, so what the walk reads is fetched ahead
+    // into registers: the cells of the next two columns, and slot lengths, fragment codes and read codes eight at a time
+    // with the group after them in flight.  The rows of the trace array are shifted per thread (`off`) so that the
+    // walks of a warp start in the same row and, moving at about the same pace, keep reading the same 256-byte rows
+    // (measured against cells contiguous per thread: 7.3 ms instead of 9.8 ms for the largest class of the bulk shape).
+    const AlignCell2<BV>* crow = cells + (size_t)off * 32;   // cell of column x at crow[(x - 1) * 32]
+    uint32_t i = m, j = n, oj = m;
+    uint64_t lwin = 0, lnx = 0, fwin = 0, fnx = 0, rwin = 0, rnx = 0;
+    uint32_t gj = 0, gi = 0;   // eight-byte groups the windows hold: (j - 1) >> 3, (i - 1) >> 3
+    AlignCell2<BV> c0{}, c1{}, c2{};   // cells of columns j, j - 1, j - 2
+    if (valid && n) {
+        gj = (n - 1) >> 3;
+        lwin = ByteStream::ld(l8 + gj);
+        fwin = ByteStream::ld(f8 + gj);
+        if (gj) {
+            lnx = ByteStream::ld(l8 + gj - 1);
+            fnx = ByteStream::ld(f8 + gj - 1);
+        }
+        c0 = crow[(size_t)(n - 1) * 32];
+        if (n >= 2) c1 = crow[(size_t)(n - 2) * 32];
+        if (n >= 3) c2 = crow[(size_t)(n - 3) * 32];
+    }
+    if (valid && m) {
+        gi = (m - 1) >> 3;
+        rwin = ByteStream::ld(r8 + gi);
+        if (gi) rnx = ByteStream::ld(r8 + gi - 1);
+    }
+    auto byte_of = [](uint64_t w, uint32_t idx) { return (uint32_t)(w >> (8u * (idx & 7u))) & 0xFFu; };
     bool have = false, failed = false;
     uint32_t bi = 0, op = 0, run = 0, eq = 0, cols = 0, acc = 0;
     auto flush = [&]() {
@@ -1564,64 +1634,63 @@ __device__ __forceinline__ bool align_one(const uint8_t* frag, const uint8_t* sl
         }
     };
     bool done = !valid || (i | j) == 0;
-    while (!__all_sync(0xffffffffu, done)) {
+    while (__any_sync(0xffffffffu, !done)) {
+        // the move of every thread first, then the threads that start a read base together, then those that change
+        // column together (left to itself the compiler gives each kind of move its own copy of the shared parts and
+        // the warp runs them one after the other)
+        uint32_t d = MV_OUT;   // MV_OUT: no move (done)
         if (!done) {
-            // the blocks of column j and of read base i - 1 (the one a move from here may consume)
-            if (j > 0 && ((j - 1) >> 5) != jb) {
-                jb = (j - 1) >> 5;
-                col_block(jb);
-            }
-            if (i > 0 && ((i - 1) >> 5) != ib) {
-                ib = (i - 1) >> 5;
-                row_block(ib);
-            }
-            if (j > 0) {
-                cur = sc[((j - 1) & 31u) * 32];
-                lo = align_lo<BV>(oj);
-            }
-        }
-        while (!done) {
-            uint32_t d;
-            if (i == 0) {
-                d = MV_LEFT;
-            } else if (j == 0) {
+            d = MV_LEFT;
+            if (i != 0) {
                 d = MV_UP;
-            } else {
-                if (i < lo + (lo > 1 ? ALIGN_MARGIN : 0u) || i + ALIGN_MARGIN >= lo + BW) {
-                    failed = true;
-                    done = true;
-                    break;
+                if (j != 0) {
+                    const uint32_t lo = align_lo<BV>(oj);
+                    const uint32_t b = (i - lo) & (BW - 1);
+                    d = ((c0.dg >> b) & 1) ? MV_DIAG : ((c0.pv >> b) & 1) ? MV_UP : MV_LEFT;
+                    if (i < lo + (lo > 1 ? ALIGN_MARGIN : 0u) || i + ALIGN_MARGIN >= lo + BW) {
+                        failed = true;
+                        done = true;
+                        d = MV_OUT;
+                    }
                 }
-                const uint32_t b = i - lo;
-                d = ((cur.dg >> b) & 1) ? MV_DIAG : ((cur.pv >> b) & 1) ? MV_UP : MV_LEFT;
-            }
-            if (d == MV_LEFT) {
-                run++;
-            } else {
-                // a read base starts here: the one before it is complete (its D run is known now)
-                flush();
-                bi = i - 1;
-                have = true;
-                run = 0;
-                op = 2u;   // OP_I
-                i--;
-                if (d == MV_DIAG) op = byte_of(sr, bi) == byte_of(sf, j - 1) ? 0u : 1u;   // OP_EQ : OP_X
-            }
-            if (d != MV_UP) {   // to column j - 1
-                oj -= byte_of(sl, j - 1);
-                j--;
-            }
-            if ((i | j) == 0) {
-                done = true;
-                break;
-            }
-            // next cell: are its blocks here?
-            if ((j > 0 && ((j - 1) >> 5) != jb) || (i > 0 && ((i - 1) >> 5) != ib)) break;
-            if (d != MV_UP && j > 0) {
-                cur = sc[((j - 1) & 31u) * 32];
-                lo = align_lo<BV>(oj);
             }
         }
+        __syncwarp();
+        run += d == MV_LEFT;
+        if (d == MV_DIAG || d == MV_UP) {
+            // a read base starts here: the one before it is complete (its D run is known now)
+            flush();
+            bi = i - 1;
+            have = true;
+            run = 0;
+            op = 2u;   // OP_I
+            if (d == MV_DIAG) op = byte_of(rwin, bi) == byte_of(fwin, j - 1) ? 0u : 1u;   // OP_EQ : OP_X
+            i--;
+            if (i != 0 && ((i - 1) & 7u) == 7u) {   // the next base is the last of the group below
+                rwin = rnx;
+                gi--;
+                if (gi) rnx = ByteStream::ld(r8 + gi - 1);
+            }
+        }
+        __syncwarp();
+        if (d == MV_DIAG || d == MV_LEFT) {   // to column j - 1
+            oj -= byte_of(lwin, j - 1);
+            j--;
+            c0 = c1;
+            c1 = c2;
+            if (j >= 3) c2 = crow[(size_t)(j - 3) * 32];
+            if (j != 0 && ((j - 1) & 7u) == 7u) {
+                lwin = lnx;
+                fwin = fnx;
+                gj--;
+                if (gj) {
+                    lnx = ByteStream::ld(l8 + gj - 1);
+                    fnx = ByteStream::ld(f8 + gj - 1);
+                }
+            }
+        }
+        __syncwarp();
+        if (d != MV_OUT) done = (i | j) == 0;
     }
     if (failed || !valid) return false;
     flush();
@@ -1630,23 +1699,20 @@ __device__ __forceinline__ bool align_one(const uint8_t* frag, const uint8_t* sl
     return true;
 }
 
-// shared memory of one warp of align_kernel<BV>: 32 cells + 3 x 32 bytes per thread
-template <typename BV>
-constexpr uint32_t align_warp_smem() { return 32u * (32u * (uint32_t)sizeof(AlignCell2<BV>) + 96u); }
-
+// -------------------------------------------------------------- align_kernel
+// One thread per read, a warp takes 32 consecutive reads of the work list (similar lengths: the list is sorted).
 constexpr int ALIGN_K_THREADS = 128;
 template <typename BV>
 __global__ void __launch_bounds__(ALIGN_K_THREADS) align_kernel(const AlignKParams K) {
-    extern __shared__ __align__(16) uint8_t smem[];
-    uint8_t* sm = smem + (threadIdx.x >> 5) * align_warp_smem<BV>();
     const uint32_t n_work = K.n_work_dev ? *K.n_work_dev : K.n_work;
+    const uint32_t begin = K.work_begin_dev ? *K.work_begin_dev : 0u;
     const DevBatch& B = K.B;
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     uint8_t* region = K.trace + (size_t)warp * K.trace_warp_bytes;
     while (true) {
         uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(K.counter, 32u);
+        if (lane == 0) base = begin + atomicAdd(K.counter, 32u);
         base = __shfl_sync(0xffffffffu, base, 0);
         if (base >= n_work) break;
         const uint32_t wi = base + lane;
@@ -1676,8 +1742,12 @@ __global__ void __launch_bounds__(ALIGN_K_THREADS) align_kernel(const AlignKPara
         }
         uint32_t eq = 0, cols = 0;
         const bool run_it = valid && !(K.flags & RUN_NO_ALIGN) && !(sizeof(BV) == 8 && (K.flags & RUN_NO_WIDE));
-        const bool ok = align_one<BV>(frag, slen, rb, out, run_it ? n : 0u, run_it ? m : 0u, (AlignCell2<BV>*)region + lane, sm,
-                                      run_it, eq, cols);
+        // the longest fragment of the warp: the forward pass runs the warp in step up to it, and it sets the row in
+        // which every walk of the warp starts
+        uint32_t nmax = run_it ? n : 0u;
+        for (int dd = 16; dd; dd >>= 1) nmax = max(nmax, __shfl_xor_sync(0xffffffffu, nmax, dd));
+        const bool ok = align_one<BV>(frag, slen, rb, out, run_it ? n : 0u, run_it ? m : 0u, (AlignCell2<BV>*)region + lane,
+                                      run_it ? nmax - n : 0u, nmax, run_it, eq, cols);
         if (valid) {
             if (ok) {
                 B.ident_num[r] = eq;
