@@ -1485,6 +1485,9 @@ __device__ __forceinline__ bool align_one(const uint8_t* frag, const uint8_t* sl
                                           uint32_t& eq_out, uint32_t& cols_out) {
     // every thread of the warp comes here (`valid`: it has a read); n = m = 0 otherwise; nmax = largest n of the warp
     constexpr uint32_t BW = 8 * sizeof(BV);
+    static_assert(ALIGN_MARGIN == 4, "the cells carry four bits of column data where the margin rows would be");
+    constexpr uint32_t CELL_SH = BW - ALIGN_MARGIN;
+    constexpr BV CELL_LOW = (BV(1) << CELL_SH) - 1;
     const uint2* l8 = (const uint2*)slen;
     const uint2* f8 = (const uint2*)frag;
     const uint2* r8 = (const uint2*)rb;
@@ -1544,7 +1547,8 @@ __device__ __forceinline__ bool align_one(const uint8_t* frag, const uint8_t* sl
                     if (avail + 8 <= 2 * BW) refill();
                 }
                 if (live) {
-                    const uint32_t o = o_prev + ((uint32_t)(lw >> (8 * t8)) & 0xFFu);
+                    const uint32_t len = (uint32_t)(lw >> (8 * t8)) & 0xFFu;
+                    const uint32_t o = o_prev + len;
                     const uint32_t lo = align_lo<BV>(o);
                     const uint32_t s = lo - lo_prev;
                     if (s) {
@@ -1578,9 +1582,11 @@ __device__ __forceinline__ bool align_one(const uint8_t* frag, const uint8_t* sl
                     Mh <<= 1;
                     Pv = Mh | ~(Xv | Ph);
                     Mv = Ph & Xv;
+                    // the walk never looks at the top ALIGN_MARGIN rows of a band: their bits carry the slot length and the
+                    // fragment code of the column, so that it needs neither array again
                     AlignCell2<BV> c;
-                    c.dg = Eq | ~D0;
-                    c.pv = Pv;
+                    c.dg = ((Eq | ~D0) & CELL_LOW) | (BV(len | (f < 4 ? 0u : 8u)) << CELL_SH);
+                    c.pv = (Pv & CELL_LOW) | (BV(f & 3u) << CELL_SH);
                     cell[(size_t)t8 * 32] = c;
                     o_prev = o;
                     lo_prev = lo;
@@ -1591,23 +1597,16 @@ __device__ __forceinline__ bool align_one(const uint8_t* frag, const uint8_t* sl
     }
     // ---- traceback over the whole read (align_trace_chunk<TRACE_WRITE> with cmin = 1, bottom, top), the 32 threads of
     // the warp one move at a time.  Every move depends on the one before it, so what the walk reads is fetched ahead
-    // into registers: the cells of the next two columns, and slot lengths, fragment codes and read codes eight at a time
-    // with the group after them in flight.  The rows of the trace array are shifted per thread (`off`) so that the
+    // into registers: the cells of the next two columns (they carry the slot length and the fragment code of their
+    // column) and the read codes eight at a time with the group after them in flight.  The rows of the trace array are shifted per thread (`off`) so that the
     // walks of a warp start in the same row and, moving at about the same pace, keep reading the same 256-byte rows
     // (measured against cells contiguous per thread: 7.3 ms instead of 9.8 ms for the largest class of the bulk shape).
     const AlignCell2<BV>* crow = cells + (size_t)off * 32;   // cell of column x at crow[(x - 1) * 32]
     uint32_t i = m, j = n, oj = m;
-    uint64_t lwin = 0, lnx = 0, fwin = 0, fnx = 0, rwin = 0, rnx = 0;
-    uint32_t gj = 0, gi = 0;   // eight-byte groups the windows hold: (j - 1) >> 3, (i - 1) >> 3
+    uint64_t rwin = 0, rnx = 0;
+    uint32_t gi = 0;   // eight-byte group of the read the window holds: (i - 1) >> 3
     AlignCell2<BV> c0{}, c1{}, c2{};   // cells of columns j, j - 1, j - 2
     if (valid && n) {
-        gj = (n - 1) >> 3;
-        lwin = ByteStream::ld(l8 + gj);
-        fwin = ByteStream::ld(f8 + gj);
-        if (gj) {
-            lnx = ByteStream::ld(l8 + gj - 1);
-            fnx = ByteStream::ld(f8 + gj - 1);
-        }
         c0 = crow[(size_t)(n - 1) * 32];
         if (n >= 2) c1 = crow[(size_t)(n - 2) * 32];
         if (n >= 3) c2 = crow[(size_t)(n - 3) * 32];
@@ -1664,7 +1663,10 @@ __device__ __forceinline__ bool align_one(const uint8_t* frag, const uint8_t* sl
             have = true;
             run = 0;
             op = 2u;   // OP_I
-            if (d == MV_DIAG) op = byte_of(rwin, bi) == byte_of(fwin, j - 1) ? 0u : 1u;   // OP_EQ : OP_X
+            if (d == MV_DIAG) {   // OP_EQ : OP_X
+                const uint32_t fc = ((uint32_t)(c0.dg >> (CELL_SH + 3)) & 1u) ? (uint32_t)frag[j - 1] : (uint32_t)(c0.pv >> CELL_SH) & 3u;
+                op = byte_of(rwin, bi) == fc ? 0u : 1u;
+            }
             i--;
             if (i != 0 && ((i - 1) & 7u) == 7u) {   // the next base is the last of the group below
                 rwin = rnx;
@@ -1674,20 +1676,11 @@ __device__ __forceinline__ bool align_one(const uint8_t* frag, const uint8_t* sl
         }
         __syncwarp();
         if (d == MV_DIAG || d == MV_LEFT) {   // to column j - 1
-            oj -= byte_of(lwin, j - 1);
+            oj -= (uint32_t)(c0.dg >> CELL_SH) & 7u;
             j--;
             c0 = c1;
             c1 = c2;
             if (j >= 3) c2 = crow[(size_t)(j - 3) * 32];
-            if (j != 0 && ((j - 1) & 7u) == 7u) {
-                lwin = lnx;
-                fwin = fnx;
-                gj--;
-                if (gj) {
-                    lnx = ByteStream::ld(l8 + gj - 1);
-                    fnx = ByteStream::ld(f8 + gj - 1);
-                }
-            }
         }
         __syncwarp();
         if (d != MV_OUT) done = (i | j) == 0;
