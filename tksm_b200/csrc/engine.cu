@@ -567,6 +567,8 @@ void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, const P
 }
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+std::atomic<uint64_t> g_ns_prep_alloc{0}, g_ns_prep_reads{0}, g_ns_prep_copy{0};
+inline uint64_t now_ns() { return (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
 // Host-only preparation of one device batch from the molecule batches of consecutive text chunks:
 // per-read scratch layout, length classes and the upload blob, written in one pass (the parts are
@@ -614,6 +616,7 @@ void prepare_host(const tksm_seq* h, const std::vector<const HostBatch*>& parts,
     bool tails = false;
     for (const HostBatch* hb : parts) tails = tails || !hb->mol_tail_len.empty();
     p.o_tail = tails ? add(M * 4) : SIZE_MAX;
+    const uint64_t t_a0 = now_ns();
     p.stage = StageLease(h->stage_pool.get(), h->stage_pool->acquire(total, h->cfg.device));
     if (p.stage.idx >= 0) {
         p.blob = h->stage_pool->ptr(p.stage.idx);
@@ -622,6 +625,7 @@ void prepare_host(const tksm_seq* h, const std::vector<const HostBatch*>& parts,
         p.blob = p.heap_blob.get();
     }
     p.blob_bytes = total;
+    g_ns_prep_alloc += now_ns() - t_a0;
     char* B = p.blob;
     uint32_t* read_mol = (uint32_t*)(B + p.o_read_mol);
     uint32_t* msb = (uint32_t*)(B + p.o_msb);
@@ -647,6 +651,7 @@ void prepare_host(const tksm_seq* h, const std::vector<const HostBatch*>& parts,
     for (const HostBatch* hbp : parts) {
         const HostBatch& hb = *hbp;
         const size_t r_n = hb.n_reads(), m_n = hb.n_mols(), s_n = hb.seg_src.size(), nm_n = hb.mod_pos.size();
+        const uint64_t t_r0 = now_ns();
         for (size_t r = 0; r < r_n; r++) {
             const uint32_t m = hb.read_mol[r];
             const uint32_t L = hb.mol_raw_len[m];
@@ -668,6 +673,8 @@ void prepare_host(const tksm_seq* h, const std::vector<const HostBatch*>& parts,
             if (nm_n) per_read_mods += hb.seg_mod_begin[hb.mol_seg_begin[m + 1]] - hb.seg_mod_begin[hb.mol_seg_begin[m]];
             idsum += hb.mol_id_begin[m + 1] - hb.mol_id_begin[m];
         }
+        const uint64_t t_r1 = now_ns();
+        g_ns_prep_reads += t_r1 - t_r0;
         for (size_t m = 0; m < m_n; m++) {
             msb[m0 + m + 1] = (uint32_t)(s0 + hb.mol_seg_begin[m + 1]);
             mib[m0 + m + 1] = (uint32_t)(id0 + hb.mol_id_begin[m + 1]);
@@ -694,6 +701,7 @@ void prepare_host(const tksm_seq* h, const std::vector<const HostBatch*>& parts,
         }
         if (!hb.lit_pool.empty()) memcpy(lit + lit0, hb.lit_pool.data(), hb.lit_pool.size());
         if (!hb.id_pool.empty()) memcpy(idp + id0, hb.id_pool.data(), hb.id_pool.size());
+        g_ns_prep_copy += now_ns() - t_r1;
         r0 += r_n;
         m0 += m_n;
         s0 += s_n;
@@ -865,6 +873,8 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format, bool gro
             const int W2 = c == GWS_CLASS ? GWS_W2 : CLASS_W[c];
             const int teams2 = c == GWS_CLASS ? 1 : (int)h->threads2[c] / 32 / CLASS_W[c];
             size_t grid2 = std::min<size_t>((size_t)h->num_sms, (n_work[c] + teams2 - 1) / teams2);
+            // (a class of long fragments with few reads is a few long chains for align_kernel, 7 ms at 8192 slots whatever
+            // the batch; measured: the team-parallel FIN_FULL kernel on such a class is no faster)
             if (CLASS_W[c] < 24) grid2 = std::min<size_t>(grid2, 32);   // redo lists only
             trace_team[c] = trace_team_bytes(W2, ncap_c[c]);
             trace_off[c] = trace_total;
@@ -999,7 +1009,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format, bool gro
         {
             const int teams2 = c == GWS_CLASS ? 1 : (int)h->threads2[c] / 32 / CLASS_W[c];
             p2.smem = h->smem_bytes2[c];
-            p2.grid = (int)std::min<size_t>((size_t)h->num_sms, (P.n_work + teams2 - 1) / teams2);
+            p2.grid = (int)std::min<size_t>((size_t)h->num_sms, (P.n_work + teams2 - 1) / teams2);   // (as the trace regions above)
             p2.threads = (int)h->threads2[c];
             p2.slab_bytes = c == GWS_CLASS ? slab_c[c] : h->slab2[c];   // the global workspaces keep their size
         }
@@ -1265,7 +1275,10 @@ struct ScopedNs {
 using PreparedList = std::vector<std::unique_ptr<Prepared>>;
 using HostBatchList = std::vector<std::unique_ptr<HostBatch>>;
 
-inline size_t limit_reads(const tksm_seq* h) { return h->cfg.batch_reads ? (size_t)h->cfg.batch_reads : ((size_t)1 << 18); }
+inline size_t limit_reads(const tksm_seq* h) {
+    static const size_t env = getenv("TKSM_SEQ_BATCH_READS") ? (size_t)atoll(getenv("TKSM_SEQ_BATCH_READS")) : 0;
+    return h->cfg.batch_reads ? (size_t)h->cfg.batch_reads : env ? env : ((size_t)1 << 18);
+}
 inline uint64_t limit_bases(const tksm_seq* h) { return h->cfg.batch_bases ? h->cfg.batch_bases : (1ull << 28); }
 
 // stage 1 (host threads): one text chunk of complete records -> molecule batches
@@ -1384,7 +1397,9 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
     if (!h->models_loaded) throw std::runtime_error("models not loaded");
     commit_reference(h);
     CK(cudaSetDevice(h->cfg.device));
-    const int NS = 3;
+    // device batches in flight (their kernels queued or running) and one more slot being filled
+    static const int max_inflight = getenv("TKSM_SEQ_INFLIGHT") ? std::min(std::max(atoi(getenv("TKSM_SEQ_INFLIGHT")), 1), 6) : 2;
+    const int NS = max_inflight + 1;
     while ((int)h->slots.size() < NS) h->slots.emplace_back(new tksm_seq_batch());
     const int nthreads = host_threads(h);
     tksm_seq_stats total{};
@@ -1551,7 +1566,7 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
                 w_launch += t2 - t1;
                 issued++;
                 inflight.push_back({b});
-                if (inflight.size() >= 2) {
+                if (inflight.size() >= (size_t)max_inflight) {
                     finish(inflight.front().b);
                     inflight.pop_front();
                 }
@@ -1572,6 +1587,9 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
         if (trace)
             fprintf(stderr, "[trace] done at %.2f ms; host thread time: parse %.1f ms, append %.1f ms, prepare %.1f ms (cumulative)\n",
                     now_ms(), g_ns_parse.load() / 1e6, g_ns_append.load() / 1e6, g_ns_prepare.load() / 1e6);
+        if (trace)
+            fprintf(stderr, "[trace] prepare: stage buffer %.1f ms, per-read loop %.1f ms, copies %.1f ms (cumulative)\n",
+                    g_ns_prep_alloc.load() / 1e6, g_ns_prep_reads.load() / 1e6, g_ns_prep_copy.load() / 1e6);
         (void)dev_ms;
     } catch (...) {
         cudaDeviceSynchronize();
