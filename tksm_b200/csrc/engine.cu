@@ -1025,7 +1025,9 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format, bool gro
             case 4: launch_sim<24, false>(st, P, h->smem_bytes[c], grid, p2, al); break;
             default: launch_sim<24, true, GWS_W2>(st, P, h->smem_bytes[c], grid, p2, al); break;
         }
-        launches += !(flags & RUN_ERRORS) ? 1 : CLASS_W[c] >= 24 ? 2 : (flags & RUN_QUAL) ? 5 : 2;
+        // inject | FIN_FULL, or inject | expand, or inject | expand | align | qscores | [64-bit align early] | 64-bit align | its
+        // qscores | FIN_FULL on the redo list (a class of the 64-bit band only: inject | expand | align | qscores | FIN_FULL)
+        launches += !(flags & RUN_ERRORS) ? 1 : CLASS_W[c] >= 24 ? 2 : !(flags & RUN_QUAL) ? 2 : wide_class[c] ? 5 : al.early64 ? 8 : 7;
         if (getenv("TKSM_SEQ_DEBUG") && (atoi(getenv("TKSM_SEQ_DEBUG")) & 8)) {
             const cudaError_t e = cudaStreamSynchronize(st);
             fprintf(stderr, "[debug] class %d (W=%d, %u reads, ncap %u): %s\n", c, CLASS_W[c], P.n_work, P.ncap, cudaGetErrorString(e));

@@ -1462,6 +1462,14 @@ struct AlignAhead {
         }
     }
 };
+constexpr uint32_t ALIGN_PREFETCH_COLS = 12;
+__device__ __forceinline__ void prefetch_l2(const void* p) {
+#ifdef __CUDA_ARCH__
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+#else
+    (void)p;
+#endif
+}
 // bits 0, 8, 16, 24 of x -> bits 0..3
 __device__ __forceinline__ uint32_t gather4(uint32_t x) { return (x * 0x10204080u) >> 28; }
 
@@ -1498,9 +1506,10 @@ __device__ __forceinline__ bool align_one(const uint8_t* frag, const uint8_t* sl
     {
         AlignAhead<BV> a0{0, 0}, a1{0, 0}, ax{0, 0}, an{0, 0};   // code bit 0, code bit 1, "not A/C/G/T, or beyond the read", "N"
         uint32_t avail = 0, gnext = 0;   // rows the planes hold from row lo on; next eight-byte group of the read
+        uint64_t w_ahead = m ? ByteStream::ld(r8) : 0ull;   // that group, fetched one refill ahead
         auto refill = [&]() {
-            uint64_t w = 0;
-            if (8 * gnext < m) w = ByteStream::ld(r8 + gnext);
+            const uint64_t w = w_ahead;
+            w_ahead = 8 * (gnext + 1) < m ? ByteStream::ld(r8 + gnext + 1) : 0ull;
             const uint32_t x0 = (uint32_t)w, x1 = (uint32_t)(w >> 32);
             const uint32_t t0 = x0 & 0xFCFCFCFCu, t1 = x1 & 0xFCFCFCFCu;
             uint32_t inv = 0;
@@ -1681,6 +1690,9 @@ __device__ __forceinline__ bool align_one(const uint8_t* frag, const uint8_t* sl
             c0 = c1;
             c1 = c2;
             if (j >= 3) c2 = crow[(size_t)(j - 3) * 32];
+            // (the cells were written a forward pass ago: they come from DRAM, so the row the walk reaches in
+            // ALIGN_PREFETCH_COLS moves is asked for now)
+            if (j >= 3 + ALIGN_PREFETCH_COLS) prefetch_l2(crow + (size_t)(j - 3 - ALIGN_PREFETCH_COLS) * 32);
         }
         __syncwarp();
         if (d != MV_OUT) done = (i | j) == 0;
