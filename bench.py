@@ -238,7 +238,7 @@ def main():
 
     # end to end through the public host-buffer call (MDF text in host memory -> FASTQ bytes in host
     # memory): tksm_seq_simulate_text parses on the host threads, uploads, runs the kernels and
-    # downloads the records, chunk by chunk.  Two untimed calls first (the page-locked staging and record buffers
+    # downloads the records, chunk by chunk.  Three untimed calls first (the page-locked staging and record buffers
     # are allocated on first use and the record buffer is sized from the first call's output; on a fresh box the
     # first large page-locked allocation alone can take a second), then e2e_steps timed calls.
     e2e_bases = 0
@@ -246,7 +246,7 @@ def main():
     e2e_wall = 0.0
     e2e_each = []
     if args.e2e_steps:
-        for _ in range(2):
+        for _ in range(3):
             with s.simulate_view(mdf, BADREAD, fastq=True, ordinal_base=ordinal_base) as rb:
                 assert rb.nbytes > 0 and rb.array()[0] == ord("@")
         barrier()
