@@ -54,7 +54,7 @@ WORKLOADS = {
 # dram__bytes_read.sum + dram__bytes_write.sum over all launches of one step of the default workload (one ncu pass,
 # profiles/r2_dram_per_launch.txt)
 TRAFFIC_BYTES = 40.16e9
-TRAFFIC_NOTE = "profiles/r2v_dram_per_launch.txt: every launch of one step, ncu (serialised, cold caches); 7.6 GB of it are the alignment trace cells written and read back by the two largest align_kernel launches, 8.7 GB the hand-off records between the error-injection and expansion kernels"
+TRAFFIC_NOTE = "profiles/r2v_dram_per_launch.txt: every launch of one step, ncu (serialised, cold caches); 19.2 GB of it are the two largest align_kernel launches (7.6 GB of trace cells written and read back, plus the per-read byte streams), 8.7 GB the hand-off records between the error-injection and expansion kernels"
 
 
 def peaks():

@@ -449,6 +449,28 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
     size_t lit_epoch = 1;  // bumped when a rollback may have dropped pool bytes
     TokEntry* last_tok = nullptr;  // exon lines of one molecule repeat the chromosome
     TokEntry scratch_tok;
+    // Literal lines that repeat from molecule to molecule (tags, adapters, poly(A) runs of common lengths): the raw
+    // field text and the slice taken from it, direct-mapped on its length and first / last bytes, so that a repeat
+    // costs one memcmp instead of encoding and hashing the bases again.
+    struct LitText {
+        std::string text;
+        long long s = 0, e = 0;
+        size_t epoch = 0;   // 0: no text stored
+        uint32_t off = 0;
+        uint64_t seen = 0;  // fingerprint of the last text that fell here: the text is stored when it comes a second time
+    };
+    constexpr size_t LIT_TEXTS = 256;
+    std::vector<LitText> lit_texts(LIT_TEXTS);
+    uint64_t lit_fp = 0;   // fingerprint of the text lit_text_slot() was last asked about
+    auto lit_text_slot = [&](std::string_view t) -> LitText& {
+        uint64_t a = 0, b = 0;
+        const size_t k = t.size() < 8 ? t.size() : 8;
+        memcpy(&a, t.data(), k);
+        memcpy(&b, t.data() + t.size() - k, k);
+        const uint64_t h = (a * 0x9E3779B97F4A7C15ull) ^ (b * 0xC2B2AE3D27D4EB4Full) ^ (t.size() * 0x165667B19E3779F9ull);
+        lit_fp = h | 1;
+        return lit_texts[(size_t)(h >> 56) & (LIT_TEXTS - 1)];
+    };
     std::string lit;               // encoded literal of the current line (buffer reused)
     constexpr size_t LIT_SLOTS = 4096;
     auto resolve = [&](std::string_view chrom) -> TokEntry& {
@@ -572,8 +594,12 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
             py_slice(start, end, (long long)chrom.size(), s, e);
             slen = (uint32_t)(e - s);
             uint32_t off;
+            LitText* lt = nullptr;
             if (te.lit_s == s && te.lit_e == e && te.lit_epoch == lit_epoch) {
                 off = te.lit_off;
+            } else if (!chrom.empty() && (lt = &lit_text_slot(chrom))->epoch == lit_epoch && lt->s == s && lt->e == e &&
+                       lt->text.size() == chrom.size() && memcmp(lt->text.data(), chrom.data(), chrom.size()) == 0) {
+                off = lt->off;
             } else {
                 lit.resize((size_t)slen);
                 uint64_t hsh = 0xCBF29CE484222325ull;
@@ -597,6 +623,17 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
                 te.lit_e = e;
                 te.lit_off = off;
                 te.lit_epoch = lit_epoch;
+                if (lt) {
+                    if (lt->seen == lit_fp) {   // (unique barcodes and UMIs never get here)
+                        lt->text.assign(chrom);
+                        lt->s = s;
+                        lt->e = e;
+                        lt->off = off;
+                        lt->epoch = lit_epoch;
+                    } else {
+                        lt->seen = lit_fp;
+                    }
+                }
             }
             src = SEG_LITERAL | off;
             lit_b += slen;
