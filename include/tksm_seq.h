@@ -118,6 +118,22 @@ int tksm_seq_load_models(tksm_seq* h, const char* error_model, const char* qscor
 int tksm_seq_tail_draw(tksm_seq* h, uint64_t ordinal, uint32_t frag_len, char* out, size_t cap, uint32_t* len);
 int tksm_seq_get_tables(tksm_seq* h, tksm_seq_tables* out);
 
+/* Badread extras (north_star names them; the reference does not have them -- only the two unused constants of
+ * py/tksm_badread.py:61-63 -- so there is no reference interface to cite and parity is unpinned; semantics after
+ * `badread simulate`, defined in DESIGN.md 3.10).  All off by default and after tksm_seq_set_extras(h, NULL); with
+ * every rate at zero the output is byte-identical to a run without the call.  Percentages are 0..100. */
+typedef struct tksm_seq_extras {
+    double junk_reads;             /* --junk_reads: percent of reads that are low-complexity junk of the molecule's length */
+    double random_reads;           /* --random_reads: percent of reads that are random sequence of the molecule's length */
+    double chimeras;               /* --chimeras: percent of reads that run on into the molecule of the read before them */
+    double start_adapter_rate, start_adapter_amount;   /* --start_adapter rate,amount: percent of reads with the adapter; mean percent of it present */
+    double end_adapter_rate, end_adapter_amount;       /* --end_adapter rate,amount */
+    double glitch_rate, glitch_size, glitch_skip;      /* --glitches rate,size,skip: mean distance between glitches in bases (0: none), mean random bases inserted, mean bases lost */
+    const char* start_adapter_seq; /* NULL: AATGTACTTCGTTCAGTTACGTATTGCT */
+    const char* end_adapter_seq;   /* NULL: GCAATACGTAACTGAACGAAGT */
+} tksm_seq_extras;
+int tksm_seq_set_extras(tksm_seq* h, const tksm_seq_extras* x);
+
 /* MDF file (or FIFO) -> output files; NULL path => that output is not produced */
 int tksm_seq_run_files(tksm_seq* h, const char* mdf_path, const char* badread_path, const char* perfect_path,
                        tksm_seq_stats* stats);

@@ -25,6 +25,17 @@ class Config(C.Structure):
     ]
 
 
+class Extras(C.Structure):
+    """tksm_seq_extras (include/tksm_seq.h): Badread extras, percentages 0..100, all off by default."""
+    _fields_ = [
+        ("junk_reads", C.c_double), ("random_reads", C.c_double), ("chimeras", C.c_double),
+        ("start_adapter_rate", C.c_double), ("start_adapter_amount", C.c_double),
+        ("end_adapter_rate", C.c_double), ("end_adapter_amount", C.c_double),
+        ("glitch_rate", C.c_double), ("glitch_size", C.c_double), ("glitch_skip", C.c_double),
+        ("start_adapter_seq", C.c_char_p), ("end_adapter_seq", C.c_char_p),
+    ]
+
+
 class Stats(C.Structure):
     _fields_ = [
         ("reads", C.c_uint64),
@@ -84,7 +95,7 @@ EXPORTS = [
     "tksm_seq_fetch_reference", "tksm_seq_commit_reference", "tksm_seq_load_models", "tksm_seq_get_tables",
     "tksm_seq_run_files", "tksm_seq_simulate_text", "tksm_seq_batch_create", "tksm_seq_batch_run",
     "tksm_seq_batch_fetch", "tksm_seq_batch_destroy", "tksm_seq_synth_mdf", "tksm_seq_shard_plan", "tksm_seq_tail_draw", "tksm_seq_run_files_multi",
-    "tksm_sequence_main", "tksm_seq_record_offsets_static",
+    "tksm_sequence_main", "tksm_seq_record_offsets_static", "tksm_seq_set_extras",
 ]
 
 
@@ -136,6 +147,7 @@ def lib():
     L.tksm_seq_tail_draw.argtypes = [vp, u64, C.c_uint32, vp, sz, C.POINTER(C.c_uint32)]
     L.tksm_seq_synth_mdf.argtypes = [vp, C.c_int, u64, u64, C.c_uint32, C.c_uint32, C.POINTER(vp), C.POINTER(sz)]
     L.tksm_sequence_main.argtypes = [C.c_int, C.POINTER(cp)]
+    L.tksm_seq_set_extras.argtypes = [vp, C.POINTER(Extras)]
     L.tksm_seq_record_offsets_static.argtypes = [C.c_int, vp, C.c_uint32, vp, vp, vp]
     _lib = L
     return L

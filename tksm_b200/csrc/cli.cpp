@@ -39,6 +39,15 @@ const Opt OPTS[] = {
     {"seed", "seed", 's', 1},
     {"gpus", "gpus", 0, 1},
     {"device", "device", 0, 1},
+    // Badread extras (include/tksm_seq.h: tksm_seq_extras), all off unless given
+    {"badread_junk_reads", "badread-junk-reads", 0, 1},
+    {"badread_random_reads", "badread-random-reads", 0, 1},
+    {"badread_chimeras", "badread-chimeras", 0, 1},
+    {"badread_start_adapter", "badread-start-adapter", 0, 1},
+    {"badread_end_adapter", "badread-end-adapter", 0, 1},
+    {"badread_start_adapter_seq", "badread-start-adapter-seq", 0, 1},
+    {"badread_end_adapter_seq", "badread-end-adapter-seq", 0, 1},
+    {"badread_glitches", "badread-glitches", 0, 1},
 };
 const int N_OPTS = sizeof(OPTS) / sizeof(OPTS[0]);
 
@@ -48,7 +57,41 @@ void usage(FILE* f) {
             "                [--skip-qual-compute] [-O {fastq,fasta}] [-t THREADS]\n"
             "                [--badread-identity BADREAD_IDENTITY] [--badread-error-model BADREAD_ERROR_MODEL]\n"
             "                [--badread-qscore-model BADREAD_QSCORE_MODEL] [--badread-tail-model BADREAD_TAIL_MODEL]\n"
-            "                [--list] [-s SEED] [--gpus GPUS] [--device DEVICE]\n");
+            "                [--list] [-s SEED] [--gpus GPUS] [--device DEVICE]\n"
+            "                [--badread-junk-reads PCT] [--badread-random-reads PCT] [--badread-chimeras PCT]\n"
+            "                [--badread-start-adapter RATE,AMOUNT] [--badread-end-adapter RATE,AMOUNT]\n"
+            "                [--badread-start-adapter-seq SEQ] [--badread-end-adapter-seq SEQ]\n"
+            "                [--badread-glitches RATE,SIZE,SKIP]\n");
+}
+
+// comma-separated numbers of one extras flag into the fields they set; false: not such a flag or not numbers
+bool extras_arg(const std::string& d, const std::string& val, tksm_seq_extras& x, std::string& start_seq, std::string& end_seq,
+                bool& have) {
+    auto numbers = [&](size_t count, double* out) {
+        size_t pos = 0;
+        for (size_t i = 0; i < count; i++) {
+            size_t comma = val.find(',', pos);
+            if ((i + 1 < count) != (comma != std::string::npos)) return false;
+            const std::string tok = val.substr(pos, comma == std::string::npos ? std::string::npos : comma - pos);
+            char* e = nullptr;
+            out[i] = strtod(tok.c_str(), &e);
+            if (tok.empty() || *e) return false;
+            pos = comma + 1;
+        }
+        return true;
+    };
+    double v[3];
+    bool ok = false;
+    if (d == "badread_junk_reads") { if ((ok = numbers(1, v))) x.junk_reads = v[0]; }
+    else if (d == "badread_random_reads") { if ((ok = numbers(1, v))) x.random_reads = v[0]; }
+    else if (d == "badread_chimeras") { if ((ok = numbers(1, v))) x.chimeras = v[0]; }
+    else if (d == "badread_start_adapter") { if ((ok = numbers(2, v))) { x.start_adapter_rate = v[0]; x.start_adapter_amount = v[1]; } }
+    else if (d == "badread_end_adapter") { if ((ok = numbers(2, v))) { x.end_adapter_rate = v[0]; x.end_adapter_amount = v[1]; } }
+    else if (d == "badread_glitches") { if ((ok = numbers(3, v))) { x.glitch_rate = v[0]; x.glitch_size = v[1]; x.glitch_skip = v[2]; } }
+    else if (d == "badread_start_adapter_seq") { start_seq = val; ok = true; }
+    else if (d == "badread_end_adapter_seq") { end_seq = val; ok = true; }
+    have = have || ok;
+    return ok;
 }
 
 int usage_error(const std::string& msg) {
@@ -61,6 +104,9 @@ int usage_error(const std::string& msg) {
 
 extern "C" int tksm_sequence_main(int argc, char** argv) {
     std::string input, badread, perfect, identity = "84.0,99.0,5.5", err_model, qs_model, tail_model, out_fmt;
+    tksm_seq_extras extras{};
+    std::string start_seq, end_seq;
+    bool have_extras = false;
     std::vector<std::string> refs;
     bool have_err = false, have_qs = false, have_tail = false, skip_qual = false, have_input = false;
     long threads = 1;
@@ -165,6 +211,11 @@ extern "C" int tksm_sequence_main(int argc, char** argv) {
         } else if (d == "badread_tail_model") {
             tail_model = vals[0];
             have_tail = true;
+        } else if (d.rfind("badread_", 0) == 0 && extras_arg(d, vals[0], extras, start_seq, end_seq, have_extras)) {
+            // (parsed by extras_arg)
+        } else if (d.rfind("badread_", 0) == 0 && (d == "badread_junk_reads" || d == "badread_random_reads" || d == "badread_chimeras" ||
+                                                   d == "badread_start_adapter" || d == "badread_end_adapter" || d == "badread_glitches")) {
+            return usage_error("argument --" + std::string(d).replace(0, 8, "badread-") + ": invalid value: '" + vals[0] + "'");
         } else if (d == "seed") {
             char* e = nullptr;
             seed = strtoll(vals[0].c_str(), &e, 10);
@@ -273,6 +324,12 @@ extern "C" int tksm_sequence_main(int argc, char** argv) {
                                       have_tail ? tail_model.c_str() : nullptr);
         else if (!rc)
             rc = tksm_seq_load_models(h, "random", "random", nullptr);  // perfect only: models are not consulted
+        if (!rc && have_extras) {
+            tksm_seq_extras x = extras;
+            x.start_adapter_seq = start_seq.empty() ? nullptr : start_seq.c_str();
+            x.end_adapter_seq = end_seq.empty() ? nullptr : end_seq.c_str();
+            rc = tksm_seq_set_extras(h, &x);
+        }
         if (rc) errors[(size_t)i] = tksm_seq_last_error(h);
     };
     if (n == 1) {

@@ -24,6 +24,7 @@
 #include "engine.hpp"
 #include "host.hpp"
 #include "tail.hpp"
+#include "extras.hpp"
 #include "kernels.cuh"
 #include "model.hpp"
 
@@ -289,6 +290,8 @@ struct tksm_seq {
     ErrorModelHost em;
     QScoreModelHost qm;
     TailModel tail;           // loaded == false: no_noise
+    ExtrasConfig extras;      // Badread extras (all off by default)
+    bool per_read_molecules() const { return tail.loaded || extras.any(); }   // the blob is built at issue time, one molecule per read
     IdentityHost idh;
     std::vector<float> delta;
     float calib_overshoot = 0, calib_kappa = 0, calib_kappa_measured = NAN;
@@ -1311,14 +1314,14 @@ HostBatchList parse_chunk(const tksm_seq* h, const tk::TextChunk& tc) {
 }
 
 // Tail-noise model loaded: append the tails (keyed by the read ordinals, known now) and build the blob.
-void finish_deferred(const tksm_seq* h, Prepared& p, uint64_t ordinal) {
+void finish_deferred(const tksm_seq* h, Prepared& p, uint64_t ordinal, ChimeraCarry* carry) {
     ScopedNs timer(g_ns_prepare);
     const std::vector<const HostBatch*> parts = std::move(p.deferred_parts);
     const auto keep = std::move(p.deferred_keep);
     p.deferred_parts.clear();
     p.deferred_keep.clear();
-    const HostBatch with_tails = apply_tails(h->tail, h->cfg.seed, ordinal, parts);
-    prepare_host(h, {&with_tails}, p);
+    const HostBatch per_read = apply_read_transforms(h->tail, h->extras, h->cfg.seed, ordinal, parts, carry);
+    prepare_host(h, {&per_read}, p);
 }
 
 // stage 2 (host threads): the batches of consecutive text chunks, concatenated up to the device
@@ -1332,7 +1335,7 @@ PreparedList assemble_group(const tksm_seq* h, const std::vector<std::shared_ptr
         if (!cur.empty()) {
             ScopedNs timer(g_ns_prepare);
             std::unique_ptr<Prepared> p(new Prepared());
-            if (h->tail.loaded) {
+            if (h->per_read_molecules()) {
                 p->deferred_parts = cur;
                 p->deferred_keep = lists;
             } else {
@@ -1411,6 +1414,7 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
     size_t arena_cap = 0, arena_pos = 0;
     uint64_t text_total = 0, text_done = 0, cap_done = 0;  // for the arena size estimate
 
+    ChimeraCarry chimera_carry;   // the molecule of the last read of the batch before (Badread extras: chimeras)
     struct Pending {
         std::future<PreparedList> fut;
         size_t text_bytes;
@@ -1552,7 +1556,7 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
                 b->lane = (int)(issued % (size_t)lanes);
                 w_reuse += now_ms() - t0;
                 b->prep = std::move(*pp);
-                if (!b->prep.deferred_parts.empty()) finish_deferred(h, b->prep, ordinal);
+                if (!b->prep.deferred_parts.empty()) finish_deferred(h, b->prep, ordinal, &chimera_carry);
                 b->prep.ordinal_base = ordinal;
                 ordinal += b->prep.n_reads;
                 const uint64_t R = b->prep.n_reads;
@@ -2004,9 +2008,9 @@ tksm_seq_batch* tksm_seq_batch_create(tksm_seq* h, const char* mdf, size_t mdf_l
         MdfParser parser(&h->genome);
         HostBatch hb;
         parser.feed(mdf, mdf_len, true, hb);
-        if (h->tail.loaded) {
-            const HostBatch with_tails = apply_tails(h->tail, h->cfg.seed, ordinal_base, {&hb});
-            prepare_host(h, {&with_tails}, b->prep);
+        if (h->per_read_molecules()) {
+            const HostBatch per_read = apply_read_transforms(h->tail, h->extras, h->cfg.seed, ordinal_base, {&hb}, nullptr);
+            prepare_host(h, {&per_read}, b->prep);
         } else {
             prepare_host(h, {&hb}, b->prep);
         }
@@ -2066,6 +2070,39 @@ int tksm_seq_shard_plan(tksm_seq* h, const char* mdf, size_t mdf_len, int world,
     plan_shards(mdf, mdf_len, world, bb, ob);
     memcpy(byte_begin, bb.data(), bb.size() * 8);
     memcpy(ordinal_base, ob.data(), ob.size() * 8);
+    API_END(h)
+}
+
+int tksm_seq_set_extras(tksm_seq* h, const tksm_seq_extras* x) {
+    API_BEGIN
+    ExtrasConfig e;
+    if (x) {
+        auto pct = [](double v, const char* what) {
+            if (!(v >= 0.0 && v <= 100.0)) throw std::runtime_error(std::string("Error: ") + what + " must be between 0 and 100");
+            return v / 100.0;
+        };
+        e.junk = pct(x->junk_reads, "--badread-junk-reads");
+        e.random = pct(x->random_reads, "--badread-random-reads");
+        e.chimera = pct(x->chimeras, "--badread-chimeras");
+        if (e.junk + e.random > 1.0) throw std::runtime_error("Error: junk and random reads together exceed 100 percent");
+        e.start_rate = pct(x->start_adapter_rate, "--badread-start-adapter rate");
+        e.start_amount = pct(x->start_adapter_amount, "--badread-start-adapter amount");
+        e.end_rate = pct(x->end_adapter_rate, "--badread-end-adapter rate");
+        e.end_amount = pct(x->end_adapter_amount, "--badread-end-adapter amount");
+        if (x->glitch_rate < 0 || x->glitch_size < 0 || x->glitch_skip < 0)
+            throw std::runtime_error("Error: --badread-glitches values must not be negative");
+        e.glitch_rate = x->glitch_rate;
+        e.glitch_size = x->glitch_size;
+        e.glitch_skip = x->glitch_skip;
+        auto codes = [](const char* seq, const char* dflt) {
+            std::vector<uint8_t> v;
+            for (const char* p = seq ? seq : dflt; *p; p++) v.push_back(frag_code(ascii_upper((uint8_t)*p)));
+            return v;
+        };
+        e.start_seq = codes(x->start_adapter_seq, "AATGTACTTCGTTCAGTTACGTATTGCT");
+        e.end_seq = codes(x->end_adapter_seq, "GCAATACGTAACTGAACGAAGT");
+    }
+    h->extras = std::move(e);
     API_END(h)
 }
 

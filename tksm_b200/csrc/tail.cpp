@@ -283,62 +283,4 @@ void TailModel::draw_bases(uint64_t seed, uint64_t ordinal, uint32_t start, uint
     }
 }
 
-HostBatch apply_tails(const TailModel& T, uint64_t seed, uint64_t ordinal_base, const std::vector<const HostBatch*>& parts) {
-    HostBatch out;
-    out.ordinal_base = ordinal_base;
-    size_t R = 0;
-    for (const HostBatch* hb : parts) R += hb->n_reads();
-    out.read_mol.reserve(R);
-    out.mol_raw_len.reserve(R);
-    out.mol_tail_len.reserve(R);
-    out.mol_seg_begin.reserve(R + 1);
-    out.mol_id_begin.reserve(R + 1);
-    uint64_t ord = ordinal_base;
-    for (const HostBatch* hbp : parts) {
-        const HostBatch& hb = *hbp;
-        const uint64_t lit0 = out.lit_pool.size();
-        out.lit_pool.insert(out.lit_pool.end(), hb.lit_pool.begin(), hb.lit_pool.end());
-        const bool has_mods = !hb.mod_pos.empty();
-        for (size_t r = 0; r < hb.n_reads(); r++, ord++) {
-            const uint32_t m = hb.read_mol[r];
-            const uint32_t L = hb.mol_raw_len[m];
-            uint32_t start = 0;
-            uint32_t tl = T.draw_length(seed, ord, L, &start);
-            if ((uint64_t)L + tl > 0xFFFFFF00ull) tl = 0;
-            out.read_mol.push_back((uint32_t)out.mol_raw_len.size());
-            for (uint32_t s = hb.mol_seg_begin[m]; s < hb.mol_seg_begin[m + 1]; s++) {
-                const uint64_t v = hb.seg_src[s];
-                out.seg_src.push_back((v & SEG_LITERAL) ? v + lit0 : v);
-                out.seg_len.push_back(hb.seg_len[s]);
-                if (has_mods) {
-                    for (uint32_t x = hb.seg_mod_begin[s]; x < hb.seg_mod_begin[s + 1]; x++) {
-                        out.mod_pos.push_back(hb.mod_pos[x]);
-                        out.mod_chr.push_back(hb.mod_chr[x]);
-                    }
-                }
-                out.seg_mod_begin.push_back((uint32_t)out.mod_pos.size());
-                if (v & SEG_LITERAL) out.literal_bases += hb.seg_len[s];
-                else out.genomic_bases += hb.seg_len[s];
-            }
-            if (tl) {
-                const uint64_t off = out.lit_pool.size();
-                if (off + tl > SEG_OFF_MASK) throw std::runtime_error("literal pool too large");
-                out.lit_pool.resize(off + tl);
-                T.draw_bases(seed, ord, start, tl, out.lit_pool.data() + off);
-                out.seg_src.push_back(SEG_LITERAL | off);
-                out.seg_len.push_back(tl);
-                out.seg_mod_begin.push_back((uint32_t)out.mod_pos.size());
-                out.literal_bases += tl;
-            }
-            out.mol_seg_begin.push_back((uint32_t)out.seg_src.size());
-            out.mol_raw_len.push_back(L + tl);
-            out.mol_tail_len.push_back(tl);
-            out.id_pool.insert(out.id_pool.end(), hb.id_pool.begin() + hb.mol_id_begin[m], hb.id_pool.begin() + hb.mol_id_begin[m + 1]);
-            out.mol_id_begin.push_back((uint32_t)out.id_pool.size());
-            out.total_raw_bases += (uint64_t)L + tl;
-        }
-    }
-    return out;
-}
-
 }  // namespace tk

@@ -37,8 +37,6 @@ struct TailModel {
 
 void philox4x32_10_host(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t out[4]);
 
-// One molecule per read, each followed by its tail segment; mol_tail_len filled.  `ordinal_base` is the
-// global ordinal of the first read of the first part.
-HostBatch apply_tails(const TailModel& T, uint64_t seed, uint64_t ordinal_base, const std::vector<const HostBatch*>& parts);
+// (the tail joins the molecule of its read in extras.cpp: apply_read_transforms)
 
 }  // namespace tk

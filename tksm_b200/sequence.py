@@ -60,6 +60,27 @@ class Sequencer:
         if rc:
             raise SeqError(self._L.tksm_seq_last_error(self._h).decode())
 
+    # ---- Badread extras (include/tksm_seq.h: tksm_seq_extras); no reference counterpart
+    def set_extras(self, **kw):
+        """junk_reads, random_reads, chimeras (percent); start_adapter=(rate, amount), end_adapter=(rate, amount);
+        glitches=(rate, size, skip); start_adapter_seq, end_adapter_seq.  No arguments: all off."""
+        if not kw:
+            self._ck(self._L.tksm_seq_set_extras(self._h, None))
+            return
+        x = _lib.Extras()
+        x.junk_reads = kw.pop("junk_reads", 0.0)
+        x.random_reads = kw.pop("random_reads", 0.0)
+        x.chimeras = kw.pop("chimeras", 0.0)
+        x.start_adapter_rate, x.start_adapter_amount = kw.pop("start_adapter", (0.0, 0.0))
+        x.end_adapter_rate, x.end_adapter_amount = kw.pop("end_adapter", (0.0, 0.0))
+        x.glitch_rate, x.glitch_size, x.glitch_skip = kw.pop("glitches", (0.0, 0.0, 0.0))
+        for name in ("start_adapter_seq", "end_adapter_seq"):
+            v = kw.pop(name, None)
+            setattr(x, name, v.encode() if isinstance(v, str) else v)
+        if kw:
+            raise TypeError(f"unknown extras: {sorted(kw)}")
+        self._ck(self._L.tksm_seq_set_extras(self._h, C.byref(x)))
+
     # ---- get_reference_seqs (py/sequence.py:189-194)
     def load_references(self, paths):
         arr = (C.c_char_p * len(paths))(*[p.encode() for p in paths])
