@@ -134,6 +134,17 @@ typedef struct tksm_seq_extras {
 } tksm_seq_extras;
 int tksm_seq_set_extras(tksm_seq* h, const tksm_seq_extras* x);
 
+/* Fused front-end steps: the modules that usually run between the transcript sampler and Seq as
+ * in-process edits of every MDF record, in the order given, before the record is sequenced:
+ *   "plA:normal=15,7.5"  src/polyA.cpp:133-148 (normal | poisson | gamma | weibull = parameters[,min,max])
+ *   "Flp:0.5"            src/strand_man.cpp:47-53, src/interval.h:908-920
+ *   "Tag:FMT5,FMT3"      src/tag.cpp:84-114, src/util.h:53-92 (IUPAC formats, a number n = n times N, either may be empty)
+ *   "SCB"                src/scb.cpp:73-81 (appends the first value of the record's CB= comment unless it is ".")
+ * joined by ';', e.g. the README bulk pipeline "plA:normal=15,7.5;Flp:0.5;Tag:AATGTACTTCGTTCAGTTACGTATTGCT,GCAATACGTAACTGAACGAAGT".
+ * The modules draw from std::mt19937; the fused steps draw from Philox keyed by (seed, ordinal of the record's first
+ * read), so a fused run matches the module pipeline in distribution, not byte for byte.  NULL or "": none (default). */
+int tksm_seq_set_front_end(tksm_seq* h, const char* spec);
+
 /* MDF file (or FIFO) -> output files; NULL path => that output is not produced */
 int tksm_seq_run_files(tksm_seq* h, const char* mdf_path, const char* badread_path, const char* perfect_path,
                        tksm_seq_stats* stats);

@@ -116,3 +116,129 @@ def apply(seqs, seed, ordinal_base=0, junk_reads=0.0, random_reads=0.0, chimeras
             frag = add_glitches(frag, seed, o, glitches[0], glitches[1], glitches[2])
         out.append(frag)
     return out
+
+
+# ---------------------------------------------------------------- fused front-end steps (SURVEY.md 8 f2)
+# Restated on interval lists, following the modules of the reference (draws: Philox as in csrc/extras.hpp, since the
+# modules' std::mt19937 streams are not reproduced):
+#   plA  /root/reference/src/polyA.cpp:133-148      Flp  src/strand_man.cpp:47-53, src/interval.h:908-920
+#   Tag  src/tag.cpp:84-114, src/util.h:53-92       SCB  src/scb.cpp:73-81
+TAG_FUSE = 6
+IUPAC = {"A": "A", "G": "G", "T": "T", "C": "C", "U": "U", "R": "GA", "Y": "TC", "K": "GT", "M": "AC", "S": "GC", "W": "AT",
+         "B": "GTC", "D": "GAT", "H": "ACT", "V": "GCA", "N": "AGCT"}          # src/util.h:61-76
+
+
+def fuse_words(seed, ordinal, step, index):
+    return philox4x32_10((index, TAG_FUSE | (step << 8), ordinal & 0xFFFFFFFF, ordinal >> 32), (seed & 0xFFFFFFFF, seed >> 32))
+
+
+def parse_records(text):
+    """[(id, depth, comment, [(chrom, start, end, strand, mods), ...])] of the records with depth > 0."""
+    if isinstance(text, (bytes, bytearray)):
+        text = text.decode()
+    out, cur = [], None
+    for ln in text.split("\n"):
+        if not ln:
+            continue
+        f = ln.split("\t")
+        if f[0][0] == "+":
+            cur = (f[0][1:], int(f[1]), f[2] if len(f) > 2 else "", [])
+            if cur[1] > 0:
+                out.append(cur)
+        elif cur is not None:
+            f = f + [""] if len(f) == 4 else f
+            cur[3].append((f[0], int(f[1]), int(f[2]), f[3], f[4]))
+    return out
+
+
+def polya_length(dist, params, lo, hi, seed, ordinal, step):
+    w = fuse_words(seed, ordinal, step, 0)
+    two_pi = 6.283185307179586
+    if dist == "normal":
+        x = params[0] + params[1] * (math.sqrt(-2.0 * math.log(unit(w[0]))) * math.cos(two_pi * unit(w[1])))
+    elif dist == "weibull":
+        x = params[1] * math.pow(-math.log(1.0 - unit(w[0])), 1.0 / params[0])
+    elif dist == "poisson":
+        u, pk, k = unit(w[0]), math.exp(-params[0]), 0
+        c = pk
+        while u > c and k < 100000:
+            k += 1
+            pk *= params[0] / k
+            c += pk
+        x = float(k)
+    else:   # gamma: shape, scale (Marsaglia-Tsang)
+        a = params[0] + 1.0 if params[0] < 1.0 else params[0]
+        d = a - 1.0 / 3.0
+        c = 1.0 / math.sqrt(9.0 * d)
+        x = 0.0
+        for it in range(1, 1000):
+            v = fuse_words(seed, ordinal, step, it)
+            z = math.sqrt(-2.0 * math.log(unit(v[0]))) * math.cos(two_pi * unit(v[1]))
+            t = 1.0 + c * z
+            if t <= 0.0:
+                continue
+            t3 = t * t * t
+            if math.log(unit(v[2])) < 0.5 * z * z + d - d * t3 + d * math.log(t3):
+                x = d * t3
+                break
+        if params[0] < 1.0:
+            x *= math.pow(unit(w[3]), 1.0 / params[0])
+        x *= params[1]
+    return max(lo, min(hi, int(x)))       # int(): toward zero, like the module's `int poly_a_len = dist(rand_gen)`
+
+
+def tag_sequence(fmt, seed, ordinal, step, base):
+    if fmt and fmt[0].isdigit():
+        fmt = "N" * int(fmt)
+    out, w = [], None
+    for j, ch in enumerate(fmt):
+        if j & 3 == 0:
+            w = fuse_words(seed, ordinal, step, base + (j >> 2))
+        s = IUPAC.get(ch, "")
+        if s:
+            out.append(s[(w[j & 3] * len(s)) >> 32])
+    return "".join(out)
+
+
+def front_end(records, seed, ordinal_base, spec):
+    """records: parse_records(); spec as tksm_seq_set_front_end takes it.  Returns (id, intervals) per READ (depth
+    expanded), i.e. what oracle/seq_oracle.parse_mdf would give for the MDF the module pipeline would have written."""
+    steps = [s for s in spec.split(";") if s]
+    out, ordinal = [], ordinal_base
+    for rid, depth, comment, ivs in records:
+        ivs = list(ivs)
+        for k, st in enumerate(steps):
+            name, _, arg = st.partition(":")
+            if name == "plA":
+                dist, _, nums = arg.partition("=")
+                v = [float(x) for x in nums.split(",")]
+                npar = 1 if dist == "poisson" else 2
+                lo, hi = (int(v[npar]), int(v[npar + 1])) if len(v) == npar + 2 else (0, 5000)
+                n = polya_length(dist, v[:npar], lo, hi, seed, ordinal, k)
+                if n > 0:
+                    ivs.append(("A" * n, 0, n, "+", ""))
+            elif name == "Flp":
+                if unit(fuse_words(seed, ordinal, k, 0)[0]) < float(arg):
+                    ivs = [(c, s, e, "-" if sd == "+" else "+", m) for c, s, e, sd, m in reversed(ivs)]
+            elif name == "Tag":
+                f5, _, f3 = arg.partition(",")
+                t5, t3 = tag_sequence(f5, seed, ordinal, k, 0), tag_sequence(f3, seed, ordinal, k, 1 << 16)
+                if t5:
+                    ivs.insert(0, (t5, 0, len(t5), "+", ""))
+                if t3:
+                    ivs.append((t3, 0, len(t3), "+", ""))
+            elif name == "SCB":
+                cb = None
+                for item in comment.split(";"):
+                    if item.startswith("CB="):
+                        cb = item[3:].split(",")[0]
+                        break
+                if not cb:
+                    raise KeyError("CB")
+                if cb != ".":
+                    ivs.append((cb, 0, len(cb), "+", ""))
+            else:
+                raise ValueError(name)
+        out.extend((rid, ivs) for _ in range(depth))
+        ordinal += depth
+    return out

@@ -1,6 +1,6 @@
 // TEST CODE: host materialisation of the per-read molecules csrc/extras.cpp builds (apply_read_transforms), so that the
 // segment-level Badread extras can be compared with oracle/extras_oracle.py without a GPU (tests/test_extras_host.py).
-// usage: extras_emul FASTA MDF SEED ORDINAL_BASE JUNK RANDOM CHIMERAS S_RATE S_AMOUNT E_RATE E_AMOUNT G_RATE G_SIZE G_SKIP S_SEQ E_SEQ
+// usage: extras_emul FASTA MDF SEED ORDINAL_BASE JUNK RANDOM CHIMERAS S_RATE S_AMOUNT E_RATE E_AMOUNT G_RATE G_SIZE G_SKIP S_SEQ E_SEQ [FUSE_SPEC]
 // prints the fragment of every read, one per line (what the error-free output of the product shows).
 #include <cstdio>
 #include <cstring>
@@ -23,11 +23,14 @@ int main(int argc, char** argv) {
     X.glitch_rate = atof(argv[12]); X.glitch_size = atof(argv[13]); X.glitch_skip = atof(argv[14]);
     for (const char* p = argv[15]; *p; p++) X.start_seq.push_back(frag_code(ascii_upper(*p)));
     for (const char* p = argv[16]; *p; p++) X.end_seq.push_back(frag_code(ascii_upper(*p)));
+    FrontEnd F;
+    if (argc > 17) F = parse_front_end(argv[17]);
     MdfParser p(&g);
+    p.capture_cb = F.needs_cb();
     HostBatch hb;
     p.feed(mdf.data(), mdf.size(), true, hb);
     TailModel T;
-    HostBatch out = apply_read_transforms(T, X, seed, ob, {&hb}, nullptr);
+    HostBatch out = apply_read_transforms(T, X, F, seed, ob, {&hb}, nullptr);
     const bool mods = !out.mod_pos.empty();
     for (size_t r = 0; r < out.n_reads(); r++) {
         uint32_t m = out.read_mol[r];

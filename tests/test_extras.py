@@ -7,6 +7,8 @@ errored FASTQ equals the CPU twin run on those fragments; (3) on 10 000 reads th
 the flags ask for; (4) the streaming pipeline gives the bytes of a single device batch (chimeras reach across
 device batches).
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -37,7 +39,7 @@ def world(built):
     s = Sequencer(seed=SEED)
     s.add_reference_text(fasta)
     s.load_models("random", "random")
-    return {"s": s, "refs": so.load_fasta(fasta)}
+    return {"s": s, "refs": so.load_fasta(fasta), "fasta": fasta}
 
 
 def molecules(world, mdf):
@@ -163,3 +165,45 @@ def test_rates_and_lengths_on_ten_thousand_reads(world):
     fr = fragments(chimeras=12.0)
     chim = sum(1 for i in range(1, n) if fr[i] != seqs[i] and fr[i].startswith(seqs[i]) and fr[i].endswith(seqs[i - 1]))
     assert near(chim, 0.12) and sum(f != m for f, m in zip(fr, seqs)) == chim
+
+
+# ---------------------------------------------------------------- fused front-end steps
+@pytest.mark.parametrize("spec", [
+    "plA:normal=15,7.5;Flp:0.5;Tag:AATGTACTTCGTTCAGTTACGTATTGCT,GCAATACGTAACTGAACGAAGT",
+    "plA:poisson=20;Tag:,10;SCB;Tag:,AGATCGGAAGAGCGTCGTGTAG",
+])
+def test_fused_front_end_through_the_kernels(world, spec, tmp_path):
+    """tksm_seq_set_front_end / --fuse: the molecules the steps make (oracle/extras_oracle.front_end on interval lists)
+    are what the error-free output shows and what the CPU twin must be given to reproduce the errored reads; the
+    command line flag gives the same bytes."""
+    import subprocess
+    from test_extras_host import with_cb
+    from tksm_b200 import _lib
+    from tksm_b200.sequence import BADREAD, PERFECT
+    s = world["s"]
+    mdf = with_cb(s.synth_mdf(0, 300, seed=4, min_len=200, max_len=6000) + handmade_mdf().encode() + s.synth_mdf(3, 100, seed=5), 3)
+    reads = xo.front_end(xo.parse_records(mdf), SEED, 0, spec)
+    want = [so.molecule_sequence(world["refs"], iv).decode() for _, iv in reads]
+    ids = [i for i, _ in reads]
+    try:
+        s.set_front_end(spec)
+        perfect = s.simulate(mdf, PERFECT, False)
+        assert [r[1] for r in records(perfect, False)] == want
+        fq = s.simulate(mdf, BADREAD, True)
+        d = first_diff(fq, so.twin_simulate(s.tables(), [w.encode() for w in want], ids, badread=True, fastq=True), True)
+        assert d is None, d
+        # with the per-read extras on top
+        cfg = dict(chimeras=20.0, end_adapter=(60.0, 40.0), glitches=(600.0, 8.0, 8.0))
+        s.set_extras(**cfg)
+        assert [r[1] for r in records(s.simulate(mdf, PERFECT, False), False)] == xo.apply(want, SEED, 0, **cfg)
+    finally:
+        s.set_extras()
+        s.set_front_end(None)
+    assert s.simulate(mdf, PERFECT, False) != perfect
+    # the front-end binary
+    (tmp_path / "g.fa").write_text(world["fasta"])
+    (tmp_path / "in.mdf").write_bytes(mdf)
+    exe = os.path.join(os.path.dirname(_lib.LIB_PATH), "tksm")
+    subprocess.check_call([exe, "sequence", "-i", str(tmp_path / "in.mdf"), "-r", str(tmp_path / "g.fa"), "--perfect",
+                           str(tmp_path / "p.fasta"), "-s", str(SEED), "--fuse", spec], stderr=subprocess.DEVNULL)
+    assert (tmp_path / "p.fasta").read_bytes() == perfect

@@ -95,7 +95,7 @@ EXPORTS = [
     "tksm_seq_fetch_reference", "tksm_seq_commit_reference", "tksm_seq_load_models", "tksm_seq_get_tables",
     "tksm_seq_run_files", "tksm_seq_simulate_text", "tksm_seq_batch_create", "tksm_seq_batch_run",
     "tksm_seq_batch_fetch", "tksm_seq_batch_destroy", "tksm_seq_synth_mdf", "tksm_seq_shard_plan", "tksm_seq_tail_draw", "tksm_seq_run_files_multi",
-    "tksm_sequence_main", "tksm_seq_record_offsets_static", "tksm_seq_set_extras",
+    "tksm_sequence_main", "tksm_seq_record_offsets_static", "tksm_seq_set_extras", "tksm_seq_set_front_end",
 ]
 
 
@@ -148,6 +148,7 @@ def lib():
     L.tksm_seq_synth_mdf.argtypes = [vp, C.c_int, u64, u64, C.c_uint32, C.c_uint32, C.POINTER(vp), C.POINTER(sz)]
     L.tksm_sequence_main.argtypes = [C.c_int, C.POINTER(cp)]
     L.tksm_seq_set_extras.argtypes = [vp, C.POINTER(Extras)]
+    L.tksm_seq_set_front_end.argtypes = [vp, cp]
     L.tksm_seq_record_offsets_static.argtypes = [C.c_int, vp, C.c_uint32, vp, vp, vp]
     _lib = L
     return L

@@ -48,6 +48,8 @@ const Opt OPTS[] = {
     {"badread_start_adapter_seq", "badread-start-adapter-seq", 0, 1},
     {"badread_end_adapter_seq", "badread-end-adapter-seq", 0, 1},
     {"badread_glitches", "badread-glitches", 0, 1},
+    // fused front-end steps (include/tksm_seq.h: tksm_seq_set_front_end)
+    {"fuse", "fuse", 0, 1},
 };
 const int N_OPTS = sizeof(OPTS) / sizeof(OPTS[0]);
 
@@ -61,7 +63,7 @@ void usage(FILE* f) {
             "                [--badread-junk-reads PCT] [--badread-random-reads PCT] [--badread-chimeras PCT]\n"
             "                [--badread-start-adapter RATE,AMOUNT] [--badread-end-adapter RATE,AMOUNT]\n"
             "                [--badread-start-adapter-seq SEQ] [--badread-end-adapter-seq SEQ]\n"
-            "                [--badread-glitches RATE,SIZE,SKIP]\n");
+            "                [--badread-glitches RATE,SIZE,SKIP] [--fuse 'plA:normal=15,7.5;Flp:0.5;Tag:FMT5,FMT3;SCB']\n");
 }
 
 // comma-separated numbers of one extras flag into the fields they set; false: not such a flag or not numbers
@@ -107,6 +109,7 @@ extern "C" int tksm_sequence_main(int argc, char** argv) {
     tksm_seq_extras extras{};
     std::string start_seq, end_seq;
     bool have_extras = false;
+    std::string fuse_spec;
     std::vector<std::string> refs;
     bool have_err = false, have_qs = false, have_tail = false, skip_qual = false, have_input = false;
     long threads = 1;
@@ -211,6 +214,8 @@ extern "C" int tksm_sequence_main(int argc, char** argv) {
         } else if (d == "badread_tail_model") {
             tail_model = vals[0];
             have_tail = true;
+        } else if (d == "fuse") {
+            fuse_spec = vals[0];
         } else if (d.rfind("badread_", 0) == 0 && extras_arg(d, vals[0], extras, start_seq, end_seq, have_extras)) {
             // (parsed by extras_arg)
         } else if (d.rfind("badread_", 0) == 0 && (d == "badread_junk_reads" || d == "badread_random_reads" || d == "badread_chimeras" ||
@@ -330,6 +335,7 @@ extern "C" int tksm_sequence_main(int argc, char** argv) {
             x.end_adapter_seq = end_seq.empty() ? nullptr : end_seq.c_str();
             rc = tksm_seq_set_extras(h, &x);
         }
+        if (!rc && !fuse_spec.empty()) rc = tksm_seq_set_front_end(h, fuse_spec.c_str());
         if (rc) errors[(size_t)i] = tksm_seq_last_error(h);
     };
     if (n == 1) {

@@ -291,7 +291,8 @@ struct tksm_seq {
     QScoreModelHost qm;
     TailModel tail;           // loaded == false: no_noise
     ExtrasConfig extras;      // Badread extras (all off by default)
-    bool per_read_molecules() const { return tail.loaded || extras.any(); }   // the blob is built at issue time, one molecule per read
+    FrontEnd front;           // fused polyA / flip / tag / scb steps (none by default)
+    bool per_read_molecules() const { return tail.loaded || extras.any() || front.any(); }   // the blob is built at issue time, one molecule per read
     IdentityHost idh;
     std::vector<float> delta;
     float calib_overshoot = 0, calib_kappa = 0, calib_kappa_measured = NAN;
@@ -1291,6 +1292,7 @@ HostBatchList parse_chunk(const tksm_seq* h, const tk::TextChunk& tc) {
     ScopedNs timer(g_ns_parse);
     HostBatchList out;
     MdfParser parser(&h->genome);
+    parser.capture_cb = h->front.needs_cb();
     size_t pos = 0;
     while (true) {
         std::unique_ptr<HostBatch> hb(new HostBatch());
@@ -1320,7 +1322,7 @@ void finish_deferred(const tksm_seq* h, Prepared& p, uint64_t ordinal, ChimeraCa
     const auto keep = std::move(p.deferred_keep);
     p.deferred_parts.clear();
     p.deferred_keep.clear();
-    const HostBatch per_read = apply_read_transforms(h->tail, h->extras, h->cfg.seed, ordinal, parts, carry);
+    const HostBatch per_read = apply_read_transforms(h->tail, h->extras, h->front, h->cfg.seed, ordinal, parts, carry);
     prepare_host(h, {&per_read}, p);
 }
 
@@ -2006,10 +2008,11 @@ tksm_seq_batch* tksm_seq_batch_create(tksm_seq* h, const char* mdf, size_t mdf_l
     std::unique_ptr<tksm_seq_batch> b(new tksm_seq_batch());
     try {
         MdfParser parser(&h->genome);
+        parser.capture_cb = h->front.needs_cb();
         HostBatch hb;
         parser.feed(mdf, mdf_len, true, hb);
         if (h->per_read_molecules()) {
-            const HostBatch per_read = apply_read_transforms(h->tail, h->extras, h->cfg.seed, ordinal_base, {&hb}, nullptr);
+            const HostBatch per_read = apply_read_transforms(h->tail, h->extras, h->front, h->cfg.seed, ordinal_base, {&hb}, nullptr);
             prepare_host(h, {&per_read}, b->prep);
         } else {
             prepare_host(h, {&hb}, b->prep);
@@ -2103,6 +2106,12 @@ int tksm_seq_set_extras(tksm_seq* h, const tksm_seq_extras* x) {
         e.end_seq = codes(x->end_adapter_seq, "GCAATACGTAACTGAACGAAGT");
     }
     h->extras = std::move(e);
+    API_END(h)
+}
+
+int tksm_seq_set_front_end(tksm_seq* h, const char* spec) {
+    API_BEGIN
+    h->front = spec && *spec ? parse_front_end(spec) : FrontEnd();
     API_END(h)
 }
 

@@ -1,7 +1,10 @@
 // Badread extras and tail noise applied to the molecules of a batch, one molecule per read (see extras.hpp).
 #include "extras.hpp"
 
+#include <algorithm>
 #include <cmath>
+#include <cstdlib>
+#include <cstring>
 #include <stdexcept>
 
 namespace tk {
@@ -153,10 +156,216 @@ void add_glitches(const Builder& in, Builder& out, std::vector<uint8_t>& pool, c
     }
 }
 
+// ---- fused front-end steps: one record's molecule `in` -> `out`
+struct FuseDraw {
+    uint64_t seed, ordinal;
+    uint32_t step;
+    void words(uint32_t index, uint32_t out[4]) const {
+        philox4x32_10_host(index, TAG_FUSE | (step << 8), (uint32_t)ordinal, (uint32_t)(ordinal >> 32), (uint32_t)seed,
+                           (uint32_t)(seed >> 32), out);
+    }
+};
+
+// the length the polyA module's `int poly_a_len = dist(rand_gen)` would hold, by inversion / Box-Muller /
+// Marsaglia-Tsang on Philox uniforms (the truncation toward zero is the module's)
+double polya_draw(const FrontStep& S, const FuseDraw& D) {
+    uint32_t w[4];
+    D.words(0, w);
+    const double TWO_PI = 6.283185307179586;
+    switch (S.dist) {
+        case FrontStep::NORMAL:
+            return S.p1 + S.p2 * (std::sqrt(-2.0 * std::log(unit(w[0]))) * std::cos(TWO_PI * unit(w[1])));
+        case FrontStep::WEIBULL:
+            return S.p2 * std::pow(-std::log(1.0 - unit(w[0])), 1.0 / S.p1);
+        case FrontStep::POISSON: {
+            const double u = unit(w[0]);
+            double pk = std::exp(-S.p1), c = pk;
+            int k = 0;
+            while (u > c && k < 100000) {
+                k++;
+                pk *= S.p1 / k;
+                c += pk;
+            }
+            return (double)k;
+        }
+        case FrontStep::GAMMA: {   // shape p1, scale p2
+            const double a = S.p1 < 1.0 ? S.p1 + 1.0 : S.p1;
+            const double d = a - 1.0 / 3.0, c = 1.0 / std::sqrt(9.0 * d);
+            double x = 0;
+            for (uint32_t it = 1; it < 1000; it++) {
+                uint32_t v[4];
+                D.words(it, v);
+                const double z = std::sqrt(-2.0 * std::log(unit(v[0]))) * std::cos(TWO_PI * unit(v[1]));
+                const double t = 1.0 + c * z;
+                if (t <= 0.0) continue;
+                const double t3 = t * t * t;
+                if (std::log(unit(v[2])) < 0.5 * z * z + d - d * t3 + d * std::log(t3)) {
+                    x = d * t3;
+                    break;
+                }
+            }
+            if (S.p1 < 1.0) x *= std::pow(unit(w[3]), 1.0 / S.p1);
+            return x * S.p2;
+        }
+    }
+    return 0;
+}
+
+// src/util.h:53-92: the bases an IUPAC letter of a tag format stands for
+const char* iupac_set(char c) {
+    switch (c) {
+        case 'A': return "A"; case 'G': return "G"; case 'T': return "T"; case 'C': return "C"; case 'U': return "U";
+        case 'R': return "GA"; case 'Y': return "TC"; case 'K': return "GT"; case 'M': return "AC"; case 'S': return "GC";
+        case 'W': return "AT"; case 'B': return "GTC"; case 'D': return "GAT"; case 'H': return "ACT"; case 'V': return "GCA";
+        case 'N': return "AGCT";
+        default: return "";
+    }
+}
+// one sequence of a tag format: letter j takes word j & 3 of counter (base + (j >> 2))
+void tag_draw(const std::string& fmt, const FuseDraw& D, uint32_t base, std::vector<uint8_t>& out) {
+    out.clear();
+    uint32_t w[4] = {0, 0, 0, 0};
+    for (size_t j = 0; j < fmt.size(); j++) {
+        if ((j & 3u) == 0) D.words(base + (uint32_t)(j >> 2), w);
+        const char* set = iupac_set(fmt[j]);
+        const size_t k = strlen(set);
+        if (!k) continue;   // a letter fmt2seq has no entry for yields nothing
+        out.push_back(frag_code((uint8_t)set[((uint64_t)w[j & 3u] * k) >> 32]));
+    }
+}
+
+void apply_front_end(const FrontEnd& F, uint64_t seed, uint64_t ordinal, const MolView& self, const uint8_t* cb, uint32_t cb_len,
+                     bool have_cb, std::vector<uint8_t>& pool, Builder& cur, Builder& tmp, std::vector<uint8_t>& scratch) {
+    cur.clear();
+    add_molecule(cur, self);
+    for (size_t k = 0; k < F.steps.size(); k++) {
+        const FrontStep& S = F.steps[k];
+        const FuseDraw D{seed, ordinal, (uint32_t)k};
+        if (S.kind == FrontStep::POLYA) {
+            const double x = polya_draw(S, D);
+            long len = x >= 2.0e9 ? 2000000000L : x <= -2.0e9 ? -2000000000L : (long)x;   // (int) conversion: toward zero
+            if (len < S.min_len) len = S.min_len;
+            if (len > S.max_len) len = S.max_len;
+            if (len > 0) {
+                scratch.assign((size_t)len, frag_code('A'));
+                cur.add_literal(pool, scratch.data(), (uint32_t)len);
+            }
+        } else if (S.kind == FrontStep::FLIP) {
+            uint32_t w[4];
+            D.words(0, w);
+            if (unit(w[0]) < S.p1) {
+                tmp.clear();
+                for (size_t s = cur.src.size(); s-- > 0;) {
+                    const uint32_t m0 = cur.mod_begin[s], m1 = cur.mod_begin[s + 1];
+                    for (uint32_t x = m0; x < m1; x++) {
+                        tmp.mod_pos.push_back(cur.mod_pos[x]);
+                        tmp.mod_chr.push_back(cur.mod_chr[x]);
+                    }
+                    tmp.end_seg(cur.src[s] ^ SEG_MINUS, cur.len[s]);
+                }
+                std::swap(cur, tmp);
+            }
+        } else if (S.kind == FrontStep::TAG) {
+            tag_draw(S.fmt5, D, 0, scratch);
+            if (!scratch.empty()) {
+                tmp.clear();
+                tmp.add_literal(pool, scratch.data(), (uint32_t)scratch.size());
+                const MolView rest{cur.src.data(), cur.len.data(), cur.mod_begin.data(), cur.mod_pos.data(), cur.mod_chr.data(),
+                                   (uint32_t)cur.src.size(), 0};
+                add_molecule(tmp, rest);
+                std::swap(cur, tmp);
+            }
+            tag_draw(S.fmt3, D, 1u << 16, scratch);
+            if (!scratch.empty()) cur.add_literal(pool, scratch.data(), (uint32_t)scratch.size());
+        } else {   // SCB
+            if (!have_cb) throw std::runtime_error("SCB step: the MDF record has no CB comment");
+            if (!(cb_len == 1 && cb[0] == '.') && cb_len) {
+                scratch.resize(cb_len);
+                for (uint32_t i = 0; i < cb_len; i++) scratch[i] = frag_code(ascii_upper(cb[i]));
+                cur.add_literal(pool, scratch.data(), cb_len);
+            }
+        }
+    }
+}
+
 }  // namespace
 
-HostBatch apply_read_transforms(const TailModel& T, const ExtrasConfig& X, uint64_t seed, uint64_t ordinal_base,
-                                const std::vector<const HostBatch*>& parts, ChimeraCarry* carry) {
+FrontEnd parse_front_end(const std::string& spec) {
+    FrontEnd F;
+    auto bad = [&](const std::string& why) { throw std::runtime_error("Error: --fuse: " + why + " in '" + spec + "'"); };
+    auto numbers = [&](const std::string& t) {
+        std::vector<double> v;
+        size_t pos = 0;
+        while (pos <= t.size()) {
+            size_t c = t.find(',', pos);
+            const std::string tok = t.substr(pos, c == std::string::npos ? std::string::npos : c - pos);
+            char* e = nullptr;
+            const double x = strtod(tok.c_str(), &e);
+            if (tok.empty() || *e) bad("not a number: '" + tok + "'");
+            v.push_back(x);
+            if (c == std::string::npos) break;
+            pos = c + 1;
+        }
+        return v;
+    };
+    auto expand = [](std::string f) {   // src/tag.cpp:84-91: a format that starts with a digit is that many N
+        if (!f.empty() && isdigit((unsigned char)f[0])) f = std::string((size_t)std::stoi(f), 'N');
+        return f;
+    };
+    size_t pos = 0;
+    while (pos < spec.size()) {
+        size_t semi = spec.find(';', pos);
+        const std::string item = spec.substr(pos, semi == std::string::npos ? std::string::npos : semi - pos);
+        pos = semi == std::string::npos ? spec.size() : semi + 1;
+        if (item.empty()) continue;
+        const size_t colon = item.find(':');
+        const std::string name = item.substr(0, colon), arg = colon == std::string::npos ? "" : item.substr(colon + 1);
+        FrontStep S;
+        if (name == "plA") {
+            const size_t eq = arg.find('=');
+            if (eq == std::string::npos) bad("plA needs DIST=PARAMS");
+            const std::string dn = arg.substr(0, eq);
+            const std::vector<double> v = numbers(arg.substr(eq + 1));
+            S.kind = FrontStep::POLYA;
+            size_t np = 2;
+            if (dn == "normal") S.dist = FrontStep::NORMAL;
+            else if (dn == "gamma") S.dist = FrontStep::GAMMA;
+            else if (dn == "weibull") S.dist = FrontStep::WEIBULL;
+            else if (dn == "poisson") { S.dist = FrontStep::POISSON; np = 1; }
+            else bad("unknown polyA distribution '" + dn + "'");
+            if (v.size() != np && v.size() != np + 2) bad("plA:" + dn + " takes " + std::to_string(np) + " parameters (and optionally min,max)");
+            S.p1 = v[0];
+            if (np == 2) S.p2 = v[1];
+            if (v.size() == np + 2) {
+                S.min_len = (int)v[np];
+                S.max_len = (int)v[np + 1];
+            }
+            if (S.min_len < 0 || S.max_len < 0 || S.min_len > S.max_len) bad("polyA length limits");   // src/polyA.cpp:106-117
+            if ((S.dist == FrontStep::GAMMA || S.dist == FrontStep::WEIBULL) && !(S.p1 > 0 && S.p2 > 0)) bad("distribution parameters");
+            if (S.dist == FrontStep::POISSON && !(S.p1 > 0 && S.p1 < 700)) bad("poisson mean");
+        } else if (name == "Flp") {
+            const std::vector<double> v = numbers(arg);
+            if (v.size() != 1 || v[0] < 0.0 || v[0] > 1.0) bad("Flp takes a probability");   // src/strand_man.cpp:78
+            S.kind = FrontStep::FLIP;
+            S.p1 = v[0];
+        } else if (name == "Tag") {
+            const size_t comma = arg.find(',');
+            S.kind = FrontStep::TAG;
+            S.fmt5 = expand(arg.substr(0, comma));
+            S.fmt3 = expand(comma == std::string::npos ? "" : arg.substr(comma + 1));
+        } else if (name == "SCB") {
+            S.kind = FrontStep::SCB;
+        } else {
+            bad("unknown step '" + name + "'");
+        }
+        if (F.steps.size() >= 200) bad("too many steps");
+        F.steps.push_back(S);
+    }
+    return F;
+}
+
+HostBatch apply_read_transforms(const TailModel& T, const ExtrasConfig& X, const FrontEnd& F, uint64_t seed,
+                                uint64_t ordinal_base, const std::vector<const HostBatch*>& parts, ChimeraCarry* carry) {
     HostBatch out;
     out.ordinal_base = ordinal_base;
     size_t R = 0;
@@ -167,7 +376,11 @@ HostBatch apply_read_transforms(const TailModel& T, const ExtrasConfig& X, uint6
     out.mol_seg_begin.reserve(R + 1);
     out.mol_id_begin.reserve(R + 1);
     const bool extras = X.any();
-    Builder A, G;
+    Builder A, G, Rec, RecPrev, Tmp;   // Rec: the molecule of the current MDF record after the fused front-end steps
+    auto view = [](const Builder& b) {
+        return MolView{b.src.data(), b.len.data(), b.mod_begin.data(), b.mod_pos.data(), b.mod_chr.data(), (uint32_t)b.src.size(), 0};
+    };
+    bool have_rec = false;
     std::vector<uint8_t> scratch;
     uint64_t ord = ordinal_base;
     // the molecule of the read before the current one (chimera partner)
@@ -182,19 +395,37 @@ HostBatch apply_read_transforms(const TailModel& T, const ExtrasConfig& X, uint6
     } else {
         have_prev = false;
     }
-    const HostBatch* last_hb = nullptr;
-    uint32_t last_m = 0;
     for (const HostBatch* hbp : parts) {
         const HostBatch& hb = *hbp;
         const uint64_t lit0 = out.lit_pool.size();
         out.lit_pool.insert(out.lit_pool.end(), hb.lit_pool.begin(), hb.lit_pool.end());
         const bool has_mods = !hb.mod_pos.empty();
+        const bool has_cb = hb.mol_cb_begin.size() == hb.n_mols() + 1;
+        uint32_t cur_m = 0xFFFFFFFFu;
         for (size_t r = 0; r < hb.n_reads(); r++, ord++) {
             const uint32_t m = hb.read_mol[r];
-            const uint32_t L = hb.mol_raw_len[m];
-            const uint32_t s0 = hb.mol_seg_begin[m], s1 = hb.mol_seg_begin[m + 1];
-            const MolView self{hb.seg_src.data() + s0, hb.seg_len.data() + s0, has_mods ? hb.seg_mod_begin.data() + s0 : nullptr,
-                               hb.mod_pos.data(), hb.mod_chr.data(), s1 - s0, lit0};
+            if (m != cur_m) {
+                // first read of an MDF record: its molecule, through the fused front-end steps (keyed by this ordinal)
+                cur_m = m;
+                if (have_rec && X.chimera > 0) {
+                    std::swap(RecPrev, Rec);
+                    prev = view(RecPrev);
+                    have_prev = true;
+                }
+                const uint32_t s0 = hb.mol_seg_begin[m], s1 = hb.mol_seg_begin[m + 1];
+                const MolView self{hb.seg_src.data() + s0, hb.seg_len.data() + s0, has_mods ? hb.seg_mod_begin.data() + s0 : nullptr,
+                                   hb.mod_pos.data(), hb.mod_chr.data(), s1 - s0, lit0};
+                const uint8_t* cb = has_cb ? hb.cb_pool.data() + hb.mol_cb_begin[m] : nullptr;
+                const uint32_t cb_len = has_cb ? hb.mol_cb_begin[m + 1] - hb.mol_cb_begin[m] : 0;
+                apply_front_end(F, seed, ord, self, cb, cb_len, has_cb && cb_len > 0, out.lit_pool, Rec, Tmp, scratch);
+                if (Rec.total > 0xFFFFFF00ull) throw std::runtime_error("molecule too long after the fused front-end steps");
+                have_rec = true;
+            } else if (X.chimera > 0) {
+                prev = view(Rec);   // the read before this one comes from the same record
+                have_prev = true;
+            }
+            const uint32_t L = (uint32_t)Rec.total;
+            const MolView self = view(Rec);
             const Draw D{seed, ord};
             A.clear();
             uint32_t w[4] = {0, 0, 0, 0}, wa[4] = {0, 0, 0, 0};
@@ -272,36 +503,26 @@ HostBatch apply_read_transforms(const TailModel& T, const ExtrasConfig& X, uint6
             out.id_pool.insert(out.id_pool.end(), hb.id_pool.begin() + hb.mol_id_begin[m], hb.id_pool.begin() + hb.mol_id_begin[m + 1]);
             out.mol_id_begin.push_back((uint32_t)out.id_pool.size());
             out.total_raw_bases += F->total;
-            if (X.chimera > 0) {
-                prev = self;
-                have_prev = true;
-            }
-            last_hb = &hb;
-            last_m = m;
         }
     }
-    if (carry && X.chimera > 0 && last_hb) {
-        // keep the plain molecule of the last read for the first read of the next batch
-        const HostBatch& hb = *last_hb;
+    if (carry && X.chimera > 0 && have_rec) {
+        // keep the molecule of the last read for the first read of the next batch
         ChimeraCarry c;
         c.have = true;
-        const uint32_t s0 = hb.mol_seg_begin[last_m], s1 = hb.mol_seg_begin[last_m + 1];
-        const bool has_mods = !hb.mod_pos.empty();
-        for (uint32_t s = s0; s < s1; s++) {
-            uint64_t v = hb.seg_src[s];
+        for (size_t s = 0; s < Rec.src.size(); s++) {
+            uint64_t v = Rec.src[s];
             if (v & SEG_LITERAL) {
                 const uint64_t o = v & SEG_OFF_MASK;
                 const uint64_t no = c.lit.size();
-                c.lit.insert(c.lit.end(), hb.lit_pool.begin() + (long)o, hb.lit_pool.begin() + (long)(o + hb.seg_len[s]));
+                c.lit.insert(c.lit.end(), out.lit_pool.begin() + (long)o, out.lit_pool.begin() + (long)(o + Rec.len[s]));
                 v = (v & ~SEG_OFF_MASK) | no;
             }
             c.seg_src.push_back(v);
-            c.seg_len.push_back(hb.seg_len[s]);
-            if (has_mods)
-                for (uint32_t x = hb.seg_mod_begin[s]; x < hb.seg_mod_begin[s + 1]; x++) {
-                    c.mod_pos.push_back(hb.mod_pos[x]);
-                    c.mod_chr.push_back(hb.mod_chr[x]);
-                }
+            c.seg_len.push_back(Rec.len[s]);
+            for (uint32_t x = Rec.mod_begin[s]; x < Rec.mod_begin[s + 1]; x++) {
+                c.mod_pos.push_back(Rec.mod_pos[x]);
+                c.mod_chr.push_back(Rec.mod_chr[x]);
+            }
             c.seg_mod_begin.push_back((uint32_t)c.mod_pos.size());
         }
         *carry = std::move(c);

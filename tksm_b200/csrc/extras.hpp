@@ -44,7 +44,42 @@ struct ExtrasConfig {
     }
 };
 
-// the molecule a chimeric read continues into: the molecule of the read before it (in global read order)
+// ---------------------------------------------------------------- fused front-end steps
+// The modules that usually sit between the transcript sampler and Seq only edit the segment list of a molecule
+// record; as optional in-process steps they save the MDF round trips of a pipeline.  Each follows its module:
+//   plA  src/polyA.cpp:133-148   a literal 'A' run of dist() bases, clamped to [min, max], appended (plus strand)
+//   Flp  src/strand_man.cpp:47-53, src/interval.h:908-920   with probability p the segments are reversed and every
+//        strand is toggled
+//   Tag  src/tag.cpp:84-114, src/util.h:53-92 (fmt2seq)   a sequence drawn from the 5' format (IUPAC letters: one of
+//        the letter's bases each; a number n: n times N) prepended, one from the 3' format appended
+//   SCB  src/scb.cpp:73-81   the first value of the record's CB= comment appended, unless it is "."
+// Steps run in the order given, once per MDF record (the `depth` copies of a record share the result), before the
+// per-read extras.  The modules draw from std::mt19937 streams; here the draws of a record come from Philox keyed
+// by the ordinal of the record's first read: counter (i, TAG_FUSE | step << 8, ordinal), so a fused run matches a
+// pipeline of the standalone modules in distribution, not byte for byte.
+constexpr uint32_t TAG_FUSE = 6;
+
+struct FrontStep {
+    enum Kind { POLYA, FLIP, TAG, SCB } kind = POLYA;
+    enum Dist { NORMAL, POISSON, GAMMA, WEIBULL } dist = NORMAL;
+    double p1 = 0, p2 = 0;             // distribution parameters (plA); p1 = flip probability (Flp)
+    int min_len = 0, max_len = 5000;   // src/polyA.cpp defaults
+    std::string fmt5, fmt3;            // Tag formats (numbers already expanded to N runs)
+};
+struct FrontEnd {
+    std::vector<FrontStep> steps;
+    bool any() const { return !steps.empty(); }
+    bool needs_cb() const {
+        for (const FrontStep& s : steps)
+            if (s.kind == FrontStep::SCB) return true;
+        return false;
+    }
+};
+// "plA:normal=15,7.5[,min,max];Flp:0.5;Tag:FMT5,FMT3;SCB" (an empty format is allowed: "Tag:,10"); throws on a bad spec
+FrontEnd parse_front_end(const std::string& spec);
+
+// the molecule a chimeric read continues into: the molecule of the read before it (in global read order), after the
+// fused front-end steps
 struct ChimeraCarry {
     bool have = false;
     std::vector<uint64_t> seg_src;      // literal offsets relative to `lit`
@@ -58,7 +93,7 @@ struct ChimeraCarry {
 // One molecule per read with the extras and the tail of that read applied; mol_tail_len filled when a tail model
 // is loaded.  `ordinal_base` is the global ordinal of the first read of the first part.  `carry` (may be null: no
 // chimeras across calls) holds the molecule of the read before the first one and is left holding the last one.
-HostBatch apply_read_transforms(const TailModel& T, const ExtrasConfig& X, uint64_t seed, uint64_t ordinal_base,
-                                const std::vector<const HostBatch*>& parts, ChimeraCarry* carry);
+HostBatch apply_read_transforms(const TailModel& T, const ExtrasConfig& X, const FrontEnd& F, uint64_t seed,
+                                uint64_t ordinal_base, const std::vector<const HostBatch*>& parts, ChimeraCarry* carry);
 
 }  // namespace tk

@@ -156,6 +156,8 @@ void HostBatch::clear() {
     mod_chr.clear();
     lit_pool.clear();
     id_pool.clear();
+    mol_cb_begin.assign(1, 0);
+    cb_pool.clear();
     lit_index.clear();
     total_raw_bases = genomic_bases = literal_bases = 0;
 }
@@ -430,7 +432,7 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
     uint32_t raw_len = 0;
     uint64_t gen_b = 0, lit_b = 0;
     // roll-back marks
-    size_t m_seg = 0, m_mod = 0, m_lit = 0, m_id = 0;
+    size_t m_seg = 0, m_mod = 0, m_lit = 0, m_id = 0, m_cb = 0;
 
     // The first field of recent interval lines, resolved once: contig (or "the name is the sequence",
     // py/sequence.py:307) and, for literals, the pool offset of the last slice taken from it.  Tags,
@@ -507,6 +509,7 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
         m_mod = out.mod_pos.size();
         m_lit = out.lit_pool.size();
         m_id = out.id_pool.size();
+        m_cb = out.cb_pool.size();
     };
     auto rollback = [&]() {
         out.seg_src.resize(m_seg);
@@ -522,6 +525,7 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
             lit_epoch++;
         }
         out.id_pool.resize(m_id);
+        out.cb_pool.resize(m_cb);
     };
     auto commit = [&]() {
         // py/sequence.py:208-210: the record is yielded `depth` times
@@ -530,6 +534,7 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
             out.mol_raw_len.push_back(raw_len);
             out.mol_seg_begin.push_back((uint32_t)out.seg_src.size());
             out.mol_id_begin.push_back((uint32_t)out.id_pool.size());
+            if (capture_cb) out.mol_cb_begin.push_back((uint32_t)out.cb_pool.size());
             for (long long d = 0; d < depth; d++) out.read_mol.push_back(mol);
             out.total_raw_bases += (uint64_t)raw_len * (uint64_t)depth;
             out.genomic_bases += gen_b * (uint64_t)depth;
@@ -560,6 +565,22 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
             depth = mdf_int(t1 + 1, ln.ntab > 1 ? ln.tab[1] : ln.e);
             mark();
             out.id_pool.insert(out.id_pool.end(), (const uint8_t*)ln.b + 1, (const uint8_t*)t1);
+            if (capture_cb && ln.ntab > 1) {
+                // comment field "key=v1,v2;key=...;" (src/interval.h: dump_comment): first value of CB
+                const char* c = ln.tab[1] + 1;
+                const char* ce = ln.ntab > 2 ? ln.tab[2] : ln.e;
+                while (c < ce) {
+                    const char* semi = (const char*)memchr(c, ';', (size_t)(ce - c));
+                    const char* ie = semi ? semi : ce;
+                    if (ie - c >= 3 && c[0] == 'C' && c[1] == 'B' && c[2] == '=') {
+                        const char* v = c + 3;
+                        const char* comma = (const char*)memchr(v, ',', (size_t)(ie - v));
+                        out.cb_pool.insert(out.cb_pool.end(), (const uint8_t*)v, (const uint8_t*)(comma ? comma : ie));
+                        break;
+                    }
+                    c = ie + 1;
+                }
+            }
             have = true;
             raw_len = 0;
             gen_b = lit_b = 0;

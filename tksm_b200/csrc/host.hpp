@@ -63,6 +63,9 @@ struct HostBatch {
     std::vector<uint8_t> mod_chr;
     std::vector<uint8_t> lit_pool;
     std::vector<uint8_t> id_pool;
+    // first value of the CB= comment of every molecule (MdfParser::capture_cb; the fused SCB step appends it)
+    std::vector<uint32_t> mol_cb_begin{0};
+    std::vector<uint8_t> cb_pool;
     uint64_t total_raw_bases = 0;   // over reads (depth expanded)
     uint64_t genomic_bases = 0, literal_bases = 0;  // over reads, for the algorithmic-bytes figure
     // literal de-duplication: direct-mapped on a hash of the encoded bytes (repeated tags and poly(A) runs share
@@ -85,6 +88,7 @@ struct HostBatch {
 // Throws std::runtime_error where the reference would raise (py/sequence.py:205-218, 229-239).
 struct MdfParser {
     const GenomeStore* genome;
+    bool capture_cb = false;   // keep the first value of the header's CB= comment per molecule (fused SCB step)
     explicit MdfParser(const GenomeStore* g) : genome(g) {}
     size_t feed(const char* text, size_t len, bool final, HostBatch& out, size_t max_reads = SIZE_MAX,
                 uint64_t max_bases = UINT64_MAX);

@@ -81,6 +81,10 @@ class Sequencer:
             raise TypeError(f"unknown extras: {sorted(kw)}")
         self._ck(self._L.tksm_seq_set_extras(self._h, C.byref(x)))
 
+    def set_front_end(self, spec=None):
+        """Fused front-end steps, e.g. "plA:normal=15,7.5;Flp:0.5;Tag:FMT5,FMT3;SCB" (include/tksm_seq.h); None: none."""
+        self._ck(self._L.tksm_seq_set_front_end(self._h, spec.encode() if spec else None))
+
     # ---- get_reference_seqs (py/sequence.py:189-194)
     def load_references(self, paths):
         arr = (C.c_char_p * len(paths))(*[p.encode() for p in paths])
