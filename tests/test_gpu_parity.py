@@ -502,3 +502,49 @@ def test_insertion_heavy_reads_rerun_in_larger_slots(built, tmp_path):
     b = s.batch(mdf)
     st = b.run(BADREAD, FASTQ)
     assert st["status_or"] & 3 == 0 and b.fetch(BADREAD) == s.simulate(mdf, BADREAD, fastq=True)
+
+
+@pytest.mark.parametrize("models", [("random", "random")] + ([("nanopore2020", "nanopore2020")] if HAVE_MODELS else []))
+def test_device_mdf_tokeniser_matches_the_host_parser(world, monkeypatch, models):
+    """with TKSM_SEQ_DEVICE_PARSE=1 the streaming pipeline uploads the MDF text and builds the molecule
+    batch on the device (csrc/mdf_device.cuh).  The records must be the bytes the host parser's batch gives, for every
+    MDF shape, whatever the chunking; text outside the emitter's format (negative indices, CR line ends) and every
+    input error go through the host parser and behave as before."""
+    from tksm_b200.sequence import BADREAD, FASTQ, PERFECT
+    s = world["Sequencer"](seed=31)
+    s.add_reference_text(world["fasta"])
+    s.load_models(*models)
+    clean = b"".join(s.synth_mdf(shape, n, seed=40 + shape, min_len=300, max_len=30000)
+                     for shape, n in ((0, 400), (1, 1500), (2, 60), (3, 700)))
+    clean += b"+zero_depth\t0\t\nchr1\t0\t10\t+\t\n+lit\t2\tx=1;\nTTacgN\t1\t5\t-\t2g\nchr2\t119990\t999999\t+\t\n+four\t1\t\nchr2\t5\t45\t-\n"
+    monkeypatch.delenv("TKSM_SEQ_DEVICE_PARSE", raising=False)
+    b = s.batch(clean)
+    b.run(BADREAD | PERFECT, FASTQ)
+    want, want_perf = b.fetch(BADREAD), b.fetch(PERFECT)
+    host_h2d = None
+    for chunk_bytes in (0, 30000):
+        if chunk_bytes:
+            monkeypatch.setenv("TKSM_SEQ_CHUNK_BYTES", str(chunk_bytes))
+        monkeypatch.delenv("TKSM_SEQ_DEVICE_PARSE", raising=False)
+        assert s.simulate(clean, BADREAD, True) == want
+        host_h2d = s.last_stats["h2d_bytes"]
+        monkeypatch.setenv("TKSM_SEQ_DEVICE_PARSE", "1")
+        assert s.simulate(clean, BADREAD, True) == want
+        assert s.last_stats["h2d_bytes"] == len(clean) != host_h2d          # the text went up, not a host-built blob
+        assert s.last_stats["reads"] == len(so.parse_mdf(clean))
+        assert s.simulate(clean, PERFECT, True) == want_perf
+    monkeypatch.delenv("TKSM_SEQ_CHUNK_BYTES")
+    # the handmade records hold negative indices and modification positions: that batch takes the host parser
+    odd = s.synth_mdf(1, 200, seed=3) + handmade_mdf().encode()
+    monkeypatch.delenv("TKSM_SEQ_DEVICE_PARSE")
+    want_odd = s.simulate(odd, BADREAD, True)
+    monkeypatch.setenv("TKSM_SEQ_DEVICE_PARSE", "1")
+    assert s.simulate(odd, BADREAD, True) == want_odd
+    assert s.last_stats["h2d_bytes"] != len(odd)
+    crlf = clean.replace(b"\n", b"\r\n")
+    assert s.simulate(crlf, BADREAD, True) == want
+    # errors surface as they do from the host parser, and the handle keeps working
+    for bad in (b"chr1\t0\t5\n", b"chr1\t0\tx\t+\t\n", b"chr1\t0\t5\t+\t9A\n", b"\n"):
+        with pytest.raises(Exception):
+            s.simulate(clean + bad, BADREAD, True)
+    assert s.simulate(clean, BADREAD, True) == want

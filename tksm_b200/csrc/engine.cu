@@ -26,6 +26,7 @@
 #include "tail.hpp"
 #include "extras.hpp"
 #include "kernels.cuh"
+#include "mdf_device.cuh"
 #include "model.hpp"
 
 using namespace tk;
@@ -215,6 +216,10 @@ struct Prepared {
     size_t o_read_mol = 0, o_msb = 0, o_mrl = 0, o_mib = 0, o_src = 0, o_len = 0, o_smb = 0, o_mp = 0, o_mc = 0, o_lit = 0,
            o_id = 0, o_so = 0, o_ro = 0;
     size_t o_tail = SIZE_MAX;  // per-molecule tail lengths (tail-noise model loaded), else absent
+    // device MDF tokeniser (mdf_device.cuh): `blob` is the TEXT of the batch (complete records, newline at the end);
+    // the arrays are built on the device and the counts above are filled in by slot_bind_text
+    bool dev_text = false;
+    uint32_t text_lines = 0, text_records = 0;
     // tail-noise model loaded: the tails depend on the global read ordinal, which is known when the batch is
     // issued; the molecule batches are kept until then and the blob is built by finish_deferred()
     std::vector<const HostBatch*> deferred_parts;
@@ -228,6 +233,8 @@ struct tksm_seq_batch {
     DBuf blob;
     DevBatch db{};
     uint32_t* d_work[N_CLASSES] = {};
+    DBuf text, mdf_ws;    // device MDF tokeniser: the text of the batch and its per-line / per-record work arrays
+    HBuf h_mdf;           // pinned: MdfTotals
     DBuf scr_seq, scr_qual, scr_raw, per_read, out[2], rec_len[2], rec_off[2], sums, gws, counters, work_keys, work_sorted, work_bins, mid, trace, redo, redo64, scr_ops, scr_cig, rinfo, atrace, scr_off_grow;
     HBuf stage;           // pinned upload staging
     HBuf host_out[2];     // pinned download staging (streaming to files)
@@ -261,9 +268,10 @@ struct tksm_seq_batch {
     ~tksm_seq_batch() {
         for (DBuf* d : {&blob, &scr_seq, &scr_qual, &scr_raw, &per_read, &out[0], &out[1], &rec_len[0], &rec_len[1],
                         &rec_off[0], &rec_off[1], &sums, &gws, &counters, &work_keys, &work_sorted, &work_bins, &mid, &trace, &redo,
-                        &redo64, &scr_ops, &scr_cig, &rinfo, &atrace, &scr_off_grow})
+                        &redo64, &scr_ops, &scr_cig, &rinfo, &atrace, &scr_off_grow, &text, &mdf_ws})
             d->release();
         stage.release();
+        h_mdf.release();
         host_out[0].release();
         host_out[1].release();
         h_tot.release();
@@ -310,6 +318,8 @@ struct tksm_seq {
     std::unique_ptr<StagePool> stage_pool;
     int num_sms = 148;
     DBuf d_genome, d_exc_start, d_exc_len, d_exc_chr;
+    DBuf d_ct_hash, d_ct_contig, d_ct_nameoff, d_ct_names, d_ct_offset, d_ct_length;   // contig names for the device MDF tokeniser
+    ContigTable ct{};
     DBuf d_qcls, d_thr, d_alias, d_alts, d_ident, d_delta, d_qdirect, d_qhash, d_qrows, d_qalias, d_t9, d_t9d1, d_t9d2;
     DevTables dt{};
     uint32_t ncap[N_CLASSES] = {};
@@ -323,6 +333,7 @@ struct tksm_seq {
     bool attrs_set = false;
 
     ~tksm_seq() {
+        for (DBuf* d : {&d_ct_hash, &d_ct_contig, &d_ct_nameoff, &d_ct_names, &d_ct_offset, &d_ct_length}) d->release();
         for (DBuf* d : {&d_genome, &d_exc_start, &d_exc_len, &d_exc_chr, &d_qcls, &d_thr, &d_alias, &d_alts, &d_ident, &d_delta,
                         &d_qdirect, &d_qhash, &d_qrows, &d_qalias, &d_t9, &d_t9d1, &d_t9d2})
             d->release();
@@ -369,6 +380,39 @@ void commit_reference(tksm_seq* h) {
     h->dt.exc_len = h->d_exc_len.as<uint32_t>();
     h->dt.exc_chr = h->d_exc_chr.as<uint8_t>();
     h->dt.n_exc = (uint32_t)h->genome.exc_start.size();
+    // the reference's names for the device MDF tokeniser (mdf_device.cuh): open addressing on a hash of the name
+    {
+        const auto& C = h->genome.contigs;
+        uint32_t slots = 16;
+        while (slots < 2 * C.size() + 2) slots <<= 1;
+        std::vector<uint64_t> sh(slots, 0), off, len;
+        std::vector<uint32_t> sc(slots, 0), noff{0};
+        std::vector<uint8_t> names;
+        for (const auto& kv : C) {
+            const uint32_t c = (uint32_t)off.size();
+            names.insert(names.end(), kv.first.begin(), kv.first.end());
+            noff.push_back((uint32_t)names.size());
+            off.push_back(kv.second.offset);
+            len.push_back(kv.second.length);
+            const uint64_t hh = mdf_name_hash((const uint8_t*)kv.first.data(), (uint32_t)kv.first.size());
+            uint32_t x = (uint32_t)(hh >> 17) & (slots - 1);
+            while (sh[x]) x = (x + 1) & (slots - 1);
+            sh[x] = hh;
+            sc[x] = c;
+        }
+        if (names.empty()) names.push_back(0);
+        if (off.empty()) { off.push_back(0); len.push_back(0); }
+        upload_vec(h->d_ct_hash, sh, h->stream);
+        upload_vec(h->d_ct_contig, sc, h->stream);
+        upload_vec(h->d_ct_nameoff, noff, h->stream);
+        upload_vec(h->d_ct_names, names, h->stream);
+        upload_vec(h->d_ct_offset, off, h->stream);
+        upload_vec(h->d_ct_length, len, h->stream);
+        CK(cudaStreamSynchronize(h->stream));
+        h->ct = ContigTable{h->d_ct_hash.as<uint64_t>(), h->d_ct_contig.as<uint32_t>(), slots - 1, h->d_ct_nameoff.as<uint32_t>(),
+                            h->d_ct_names.as<uint8_t>(), h->d_ct_offset.as<uint64_t>(), h->d_ct_length.as<uint64_t>(),
+                            h->genome.name_len_mask};
+    }
     h->genome_dirty = false;
 }
 
@@ -760,6 +804,200 @@ void slot_bind(tksm_seq* h, tksm_seq_batch* b) {
     b->h_tot.ensure(256);
     b->ensure_events();
     b->bound = true;
+}
+
+// exclusive prefix sums of n u32 values into out[0 .. n], out[n] = the total (scan kernels of the formatting stage)
+void dev_scan(tksm_seq_batch* b, cudaStream_t S, const uint32_t* in, uint32_t n, uint64_t* out) {
+    const uint32_t per = SCAN_BLOCK * SCAN_ITEMS;
+    const uint32_t nb = (n + per - 1) / per;
+    if (nb) scan_block_sums<<<nb, SCAN_BLOCK, 0, S>>>(in, n, b->sums.as<uint64_t>());
+    scan_sums<<<1, 1024, 0, S>>>(b->sums.as<uint64_t>(), nb, out + n);
+    if (nb) scan_final<<<nb, SCAN_BLOCK, 0, S>>>(in, n, b->sums.as<uint64_t>(), out);
+}
+
+// Device MDF tokeniser (mdf_device.cuh): uploads the text of the batch and builds the molecule batch from it on the
+// device.  One synchronisation, for the counts the launch configuration needs.  Returns false when the text holds
+// something the device passes do not interpret: the caller parses it on the host instead.
+bool slot_bind_text(tksm_seq* h, tksm_seq_batch* b) {
+    cudaStream_t S = h->lane_stream[b->lane];
+    need_device(h);
+    if (!h->models_loaded) throw std::runtime_error("models not loaded");
+    commit_reference(h);
+    CK(cudaSetDevice(h->cfg.device));
+    Prepared& p = b->prep;
+    const uint64_t nbytes = p.blob_bytes;
+    const uint32_t NL = p.text_lines, NR = p.text_records;
+    if (NL == 0 || nbytes == 0) return false;
+    const uint32_t read_cap = 2 * NR + 4096;
+    b->text.ensure(nbytes + 64);
+    CK(cudaMemcpyAsync(b->text.p, p.blob, nbytes, cudaMemcpyHostToDevice, S));
+    b->h2d_bytes = nbytes;
+    // work arrays
+    size_t total = 0;
+    auto add = [&](size_t bytes) {
+        const size_t off = total;
+        total = align_up(total + std::max<size_t>(bytes, 8), 256);
+        return off;
+    };
+    const uint32_t tiles = (uint32_t)((nbytes + MDF_TILE - 1) / MDF_TILE);
+    const size_t L1 = (size_t)NL + 1, R1 = (size_t)NR + 1;
+    const size_t w_tot = add(sizeof(MdfTotals)), w_tc = add((size_t)tiles * 4), w_to = add(((size_t)tiles + 1) * 8), w_ls = add(L1 * 8),
+                 w_kind = add(NL), w_a = add((size_t)NL * 4), w_b = add((size_t)NL * 4), w_c = add((size_t)NL * 4), w_src = add((size_t)NL * 8),
+                 w_ih = add((size_t)NL * 4), w_he = add(L1 * 8), w_ks = add((size_t)NL * 4), w_nm = add((size_t)NL * 4),
+                 w_lk = add((size_t)NL * 4), w_ln = add((size_t)NL * 4), w_si = add(L1 * 8), w_mo = add(L1 * 8), w_lo = add(L1 * 8),
+                 w_lp = add(L1 * 8), w_rl = add(R1 * 4), w_rk = add(R1 * 4), w_rd = add(R1 * 4), w_ri = add(R1 * 4), w_rs = add(R1 * 4),
+                 w_rr = add(R1 * 4), w_mr = add(R1 * 8), w_rr8 = add(R1 * 8), w_ir = add(R1 * 8), w_so = add(R1 * 8), w_ro = add(R1 * 8);
+    b->mdf_ws.ensure(total);
+    char* W = (char*)b->mdf_ws.p;
+    // outputs: the blob of the batch at bounds every input satisfies
+    const size_t S_cap = NL - std::min(NL, NR), NM_cap = nbytes / 2 + 1;
+    total = 0;
+    p.o_read_mol = add((size_t)read_cap * 4);
+    p.o_msb = add(R1 * 4);
+    p.o_mrl = add(R1 * 4);
+    p.o_mib = add(R1 * 4);
+    p.o_src = add(S_cap * 8);
+    p.o_len = add(S_cap * 4);
+    p.o_smb = add((S_cap + 1) * 4);
+    p.o_mp = add(NM_cap * 4);
+    p.o_mc = add(NM_cap);
+    p.o_lit = add(nbytes);
+    p.o_id = add(nbytes);
+    p.o_so = add(((size_t)read_cap + 1) * 8);
+    p.o_ro = add(((size_t)read_cap + 1) * 8);
+    p.o_tail = SIZE_MAX;
+    b->blob.ensure(total);
+    char* base = (char*)b->blob.p;
+    b->sums.ensure(((size_t)std::max(tiles, NL) / (SCAN_BLOCK * SCAN_ITEMS) + 4) * 8);
+    b->h_mdf.ensure(sizeof(MdfTotals));
+    MdfParams P{};
+    P.text = b->text.as<uint8_t>();
+    P.n_bytes = nbytes;
+    P.n_lines = NL;
+    P.n_records = NR;
+    P.read_cap = read_cap;
+    P.ct = h->ct;
+    P.exc_start = h->dt.exc_start;
+    P.exc_len = h->dt.exc_len;
+    P.n_exc = h->dt.n_exc;
+    P.k = (uint32_t)h->em.k;
+    for (int c = 0; c < 5; c++) P.ncap[c] = h->ncap[c];
+    P.totals = (MdfTotals*)(W + w_tot);
+    P.line_start = (uint64_t*)(W + w_ls);
+    P.kind = (uint8_t*)(W + w_kind);
+    P.a32 = (uint32_t*)(W + w_a);
+    P.b32 = (uint32_t*)(W + w_b);
+    P.c32 = (uint32_t*)(W + w_c);
+    P.src = (uint64_t*)(W + w_src);
+    P.is_hdr = (uint32_t*)(W + w_ih);
+    P.hdr_excl = (uint64_t*)(W + w_he);
+    P.keep_seg = (uint32_t*)(W + w_ks);
+    P.nm_k = (uint32_t*)(W + w_nm);
+    P.lit_k = (uint32_t*)(W + w_lk);
+    P.len_k = (uint32_t*)(W + w_ln);
+    P.seg_idx = (uint64_t*)(W + w_si);
+    P.mod_off = (uint64_t*)(W + w_mo);
+    P.lit_off = (uint64_t*)(W + w_lo);
+    P.len_prefix = (uint64_t*)(W + w_lp);
+    P.rec_line = (uint32_t*)(W + w_rl);
+    P.rec_keep = (uint32_t*)(W + w_rk);
+    P.rec_depth = (uint32_t*)(W + w_rd);
+    P.rec_idlen = (uint32_t*)(W + w_ri);
+    P.rec_slot = (uint32_t*)(W + w_rs);
+    P.rec_rawslot = (uint32_t*)(W + w_rr);
+    P.mol_of_rec = (uint64_t*)(W + w_mr);
+    P.read_of_rec = (uint64_t*)(W + w_rr8);
+    P.id_of_rec = (uint64_t*)(W + w_ir);
+    P.so_of_rec = (uint64_t*)(W + w_so);
+    P.ro_of_rec = (uint64_t*)(W + w_ro);
+    P.read_mol = (uint32_t*)(base + p.o_read_mol);
+    P.mol_seg_begin = (uint32_t*)(base + p.o_msb);
+    P.mol_raw_len = (uint32_t*)(base + p.o_mrl);
+    P.mol_id_begin = (uint32_t*)(base + p.o_mib);
+    P.seg_src = (uint64_t*)(base + p.o_src);
+    P.seg_len = (uint32_t*)(base + p.o_len);
+    P.seg_mod_begin = (uint32_t*)(base + p.o_smb);
+    P.mod_pos = (uint32_t*)(base + p.o_mp);
+    P.mod_chr = (uint8_t*)(base + p.o_mc);
+    P.lit_pool = (uint8_t*)(base + p.o_lit);
+    P.id_pool = (uint8_t*)(base + p.o_id);
+    P.scr_off = (uint64_t*)(base + p.o_so);
+    P.raw_off = (uint64_t*)(base + p.o_ro);
+    uint32_t* tile_count = (uint32_t*)(W + w_tc);
+    uint64_t* tile_off = (uint64_t*)(W + w_to);
+    CK(cudaMemsetAsync(P.totals, 0, sizeof(MdfTotals), S));
+    const uint32_t gl = (NL + 255) / 256, gr = (NR + 255) / 256, gt = (tiles + 255) / 256;
+    mdf_mark_lines<<<gt, 256, 0, S>>>(P.text, nbytes, tile_count);
+    dev_scan(b, S, tile_count, tiles, tile_off);
+    mdf_line_starts<<<gt, 256, 0, S>>>(P.text, nbytes, tile_off, P.line_start, NL);
+    mdf_parse_lines<<<gl, 256, 0, S>>>(P);
+    dev_scan(b, S, P.is_hdr, NL, P.hdr_excl);
+    if (NR) mdf_header_records<<<gl, 256, 0, S>>>(P);
+    dev_scan(b, S, P.rec_keep, NR, P.mol_of_rec);
+    dev_scan(b, S, P.rec_depth, NR, P.read_of_rec);   // (records of depth 0 add nothing)
+    dev_scan(b, S, P.rec_idlen, NR, P.id_of_rec);
+    mdf_keep_lines<<<gl, 256, 0, S>>>(P);
+    dev_scan(b, S, P.keep_seg, NL, P.seg_idx);
+    dev_scan(b, S, P.nm_k, NL, P.mod_off);
+    dev_scan(b, S, P.lit_k, NL, P.lit_off);
+    dev_scan(b, S, P.len_k, NL, P.len_prefix);
+    mdf_fill_segments<<<gl, 256, 0, S>>>(P);
+    if (NR) mdf_record_slots<<<gr, 256, 0, S>>>(P);
+    dev_scan(b, S, P.rec_slot, NR, P.so_of_rec);
+    dev_scan(b, S, P.rec_rawslot, NR, P.ro_of_rec);
+    if (NR) mdf_fill_records<<<gr, 256, 0, S>>>(P);
+    mdf_finalize<<<1, 32, 0, S>>>(P);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(b->h_mdf.p, P.totals, sizeof(MdfTotals), cudaMemcpyDeviceToHost, S));
+    CK(cudaStreamSynchronize(S));
+    const MdfTotals T = *(const MdfTotals*)b->h_mdf.p;
+    // the header lines the host counted must be the ones the device saw (a '+' after a CR-only line end is not)
+    if (T.bad) {
+        if (getenv("TKSM_SEQ_TRACE")) fprintf(stderr, "[trace] device MDF tokeniser hands a batch of %u lines to the host parser (reason %u)\n", NL, T.bad);
+        return false;
+    }
+    p.n_reads = T.reads;
+    p.n_mols = T.mols;
+    p.total_raw_bases = T.total_raw_bases;
+    p.scr_total = T.scr_total;
+    p.raw_total = T.raw_total;
+    p.idsum = T.idsum;
+    p.mods = T.mods > 0;
+    p.alg_in_bytes = (T.gen_bases + 3) / 4 + T.lit_bases + 24 * T.per_read_segs + 5 * T.per_read_mods;
+    for (int c = 0; c < N_CLASSES; c++) {
+        p.n_work[c] = T.n_work[c];
+        p.n_work_grow[c] = T.n_work_grow[c];
+    }
+    p.max_n_gws = T.max_n_gws;
+    p.max_n_gws_grow = T.max_n_gws_grow;
+    if (T.reads > 0xFFFFFFF0ull || T.segs > 0xFFFFFFF0ull || T.id_bytes > 0xFFFFFFF0ull) return false;
+    const size_t R = p.n_reads;
+    DevBatch& D = b->db;
+    D.n_reads = (uint32_t)R;
+    D.ordinal_base = p.ordinal_base;
+    D.read_mol = P.read_mol;
+    D.mol_seg_begin = P.mol_seg_begin;
+    D.mol_raw_len = P.mol_raw_len;
+    D.mol_id_begin = P.mol_id_begin;
+    D.seg_src = P.seg_src;
+    D.seg_len = P.seg_len;
+    D.seg_mod_begin = p.mods ? P.seg_mod_begin : nullptr;
+    D.mod_pos = P.mod_pos;
+    D.mod_chr = P.mod_chr;
+    D.lit_pool = P.lit_pool;
+    D.id_pool = P.id_pool;
+    D.scr_off = P.scr_off;
+    D.raw_off = P.raw_off;
+    b->per_read.ensure(std::max<size_t>(R, 1) * 16);
+    D.read_len = b->per_read.as<uint32_t>();
+    D.ident_num = D.read_len + R;
+    D.ident_den = D.ident_num + R;
+    D.status = D.ident_den + R;
+    b->counters.ensure(512);
+    b->h_tot.ensure(256);
+    b->ensure_events();
+    b->bound = true;
+    return true;
 }
 
 void run_scan(tksm_seq* h, tksm_seq_batch* b, int o, uint32_t R, uint64_t* d_total) {
@@ -1364,9 +1602,73 @@ PreparedList assemble_group(const tksm_seq* h, const std::vector<std::shared_ptr
 
 // The chunks of one device batch while the host threads parse them.  No thread waits for another: the
 // thread that finishes the last chunk of a closed group assembles the batch.
+// device MDF tokeniser: what a host thread notes about a text chunk (the text itself is copied when the group closes)
+struct TextNote {
+    tk::TextChunk tc;
+    uint32_t lines = 0, records = 0;
+};
+TextNote note_chunk(const tk::TextChunk& tc) {
+    ScopedNs timer(g_ns_parse);
+    TextNote t;
+    t.tc = tc;
+    const char* p = tc.p;
+    const char* const e = tc.p + tc.n;
+    if (tc.n && *p == '+') t.records++;
+    while (p < e) {
+        const char* nl = (const char*)memchr(p, '\n', (size_t)(e - p));
+        if (!nl) break;
+        t.lines++;
+        if (nl + 1 < e && nl[1] == '+') t.records++;
+        p = nl + 1;
+    }
+    if (tc.n && e[-1] != '\n') t.lines++;   // the copy gets the missing newline
+    return t;
+}
+// the chunks of a group as one text in a page-locked buffer, to be tokenised on the device
+PreparedList assemble_text_group(const tksm_seq* h, const std::vector<TextNote>& notes) {
+    ScopedNs timer(g_ns_prepare);
+    PreparedList out;
+    size_t total = 0;
+    uint64_t lines = 0, records = 0;
+    for (const TextNote& t : notes) {
+        total += t.tc.n + 1;
+        lines += t.lines;
+        records += t.records;
+    }
+    if (lines == 0) return out;
+    if (lines > 0x7FFFFFF0ull) throw std::runtime_error("device batch too large");
+    std::unique_ptr<Prepared> p(new Prepared());
+    p->stage = StageLease(h->stage_pool.get(), h->stage_pool->acquire(total + 64, h->cfg.device));
+    if (p->stage.idx >= 0) {
+        p->blob = h->stage_pool->ptr(p->stage.idx);
+    } else {
+        p->heap_blob.reset(new char[total + 64]);
+        p->blob = p->heap_blob.get();
+    }
+    size_t pos = 0;
+    for (const TextNote& t : notes) {
+        if (!t.tc.n) continue;
+        memcpy(p->blob + pos, t.tc.p, t.tc.n);
+        pos += t.tc.n;
+        if (p->blob[pos - 1] != '\n') p->blob[pos++] = '\n';
+    }
+    p->blob_bytes = pos;
+    p->dev_text = true;
+    p->text_lines = (uint32_t)lines;
+    p->text_records = (uint32_t)records;
+    out.push_back(std::move(p));
+    return out;
+}
+
 struct GroupState {
     std::atomic<int> remaining{1};   // chunks still being parsed, + 1 until the group is closed
     std::mutex mu;
+    std::vector<TextNote> notes;     // device tokeniser: by chunk index
+    void store_note(size_t idx, TextNote t) {
+        std::lock_guard<std::mutex> g(mu);
+        if (notes.size() <= idx) notes.resize(idx + 1);
+        notes[idx] = std::move(t);
+    }
     std::vector<std::shared_ptr<HostBatchList>> lists;   // by chunk index
     std::exception_ptr error;
     std::promise<PreparedList> done;
@@ -1382,7 +1684,7 @@ struct GroupState {
     void complete(const tksm_seq* h) {
         try {
             if (error) std::rethrow_exception(error);
-            done.set_value(assemble_group(h, lists));
+            done.set_value(notes.empty() ? assemble_group(h, lists) : assemble_text_group(h, notes));
         } catch (...) {
             done.set_exception(std::current_exception());
         }
@@ -1416,6 +1718,9 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
     size_t arena_cap = 0, arena_pos = 0;
     uint64_t text_total = 0, text_done = 0, cap_done = 0;  // for the arena size estimate
 
+    // MDF tokenisation on the device (mdf_device.cuh) unless the molecules are rebuilt per read on the host anyway
+    const int dev_parse_env = getenv("TKSM_SEQ_DEVICE_PARSE") ? atoi(getenv("TKSM_SEQ_DEVICE_PARSE")) : 0;
+    const bool dev_parse = dev_parse_env != 0 && !h->per_read_molecules();
     ChimeraCarry chimera_carry;   // the molecule of the last read of the batch before (Badread extras: chimeras)
     struct Pending {
         std::future<PreparedList> fut;
@@ -1530,9 +1835,10 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
                     std::shared_ptr<GroupState> gs = group;
                     const size_t idx = group_chunks++;
                     gs->remaining.fetch_add(1);
-                    pool.submit([hc, tc, gs, idx]() {
+                    pool.submit([hc, tc, gs, idx, dev_parse]() {
                         try {
-                            gs->store(idx, std::make_shared<HostBatchList>(parse_chunk(hc, tc)));
+                            if (dev_parse) gs->store_note(idx, note_chunk(tc));
+                            else gs->store(idx, std::make_shared<HostBatchList>(parse_chunk(hc, tc)));
                         } catch (...) {
                             gs->fail(std::current_exception());
                         }
@@ -1560,13 +1866,28 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
                 b->prep = std::move(*pp);
                 if (!b->prep.deferred_parts.empty()) finish_deferred(h, b->prep, ordinal, &chimera_carry);
                 b->prep.ordinal_base = ordinal;
+                t0 = now_ms();
+                if (b->prep.dev_text) {
+                    // the molecule batch is built from the text on the device; text it does not interpret (and every
+                    // error the reference would raise) goes through the host parser
+                    if (!slot_bind_text(h, b)) {
+                        Prepared text = std::move(b->prep);
+                        HostBatch hb;
+                        MdfParser parser(&h->genome);
+                        parser.feed(text.blob, text.blob_bytes, true, hb);
+                        b->prep = Prepared();
+                        prepare_host(h, {&hb}, b->prep);
+                        b->prep.ordinal_base = ordinal;
+                        slot_bind(h, b);
+                    }
+                } else {
+                    slot_bind(h, b);
+                }
                 ordinal += b->prep.n_reads;
                 const uint64_t R = b->prep.n_reads;
                 cap_done += R * 128 + b->prep.idsum +
                             (o_arena == 0 ? b->prep.scr_total * ((format & TKSM_SEQ_FASTQ_BADREAD) ? 2 : 1)
                                           : b->prep.total_raw_bases * ((format & TKSM_SEQ_FASTQ_PERFECT) ? 2 : 1));
-                t0 = now_ms();
-                slot_bind(h, b);
                 double t1 = now_ms();
                 slot_launch(h, b, which, format);
                 double t2 = now_ms();
