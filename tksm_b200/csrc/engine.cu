@@ -1412,11 +1412,15 @@ struct ArenaPool {
     };
     std::mutex mu;
     std::vector<Block> blocks;
-    void* acquire(size_t bytes) {
+    // a block of at least `need` bytes: the largest free one there is (the estimate `bytes` of a call's output moves a
+    // little from call to call with the grouping of its batches; page-locking a new 1.6 GB block for that costs most of
+    // a second), else a new one of `bytes`
+    void* acquire(size_t bytes, size_t need = 0) {
         std::lock_guard<std::mutex> g(mu);
+        if (need == 0 || need > bytes) need = bytes;
         int best = -1;
         for (size_t i = 0; i < blocks.size(); i++)
-            if (!blocks[i].used && blocks[i].cap >= bytes && (best < 0 || blocks[i].cap < blocks[(size_t)best].cap)) best = (int)i;
+            if (!blocks[i].used && blocks[i].cap >= need && (best < 0 || blocks[i].cap > blocks[(size_t)best].cap)) best = (int)i;
         if (best >= 0) {
             blocks[(size_t)best].used = true;
             return blocks[(size_t)best].p;
@@ -1764,7 +1768,7 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
                 size_t want = arena_pos + nbytes;
                 if (text_done && text_total > text_done)
                     want = std::max<size_t>(want, (size_t)((double)cap_done / (double)text_done * (double)text_total * 1.05));
-                char* bigger = (char*)arena_pool().acquire(want);
+                char* bigger = (char*)arena_pool().acquire(want, arena_pos + nbytes);
                 if (arena) {
                     CK(cudaStreamSynchronize(h->copy_stream));
                     memcpy(bigger, arena, arena_pos);
@@ -1814,9 +1818,13 @@ void engine_stream(tksm_seq* h, ChunkSource& src, int which, int format, uint64_
             // batches last (short last download and kernel tail): a batch takes at most half of what is left
             ramp = std::min(ramp * 2, max_group);
             group_target = ramp;
+            // (halving the batches towards the end of the input shortened the last download when a batch took a
+            // millisecond; with the alignment chains every batch has a floor of 6 ms and full batches to the end are
+            // 5 % faster: TKSM_SEQ_TAIL_DIV=2 brings the halving back)
+            static const int tail_div = getenv("TKSM_SEQ_TAIL_DIV") ? std::max(1, atoi(getenv("TKSM_SEQ_TAIL_DIV"))) : 1;
             if (text_total > text_submitted) {
                 const size_t left = (size_t)((text_total - text_submitted) >> 20);  // 1 MiB chunks left, about
-                group_target = std::min(ramp, std::max<size_t>(min_group, left / 2));
+                group_target = std::min(ramp, std::max<size_t>(min_group, left / (size_t)tail_div));
             }
         };
         while (true) {
