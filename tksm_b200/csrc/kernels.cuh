@@ -1192,7 +1192,7 @@ __device__ __forceinline__ void finish_read(const Team<W>& tm, const SimParams& 
         const uint32_t jb = start_trim, je = Ttot - end_trim;
         WarpQueue sq{wq_a, wq_b, 0, 0};
         const uint32_t* q0row = (const uint32_t*)(lut3 + 64);
-        const uint32_t lg0 = T.q_t9 ? (__ldg(&T.q_t9[0]) & 7u) : 0u;
+        const uint32_t ent0 = T.q_t9 ? __ldg(&T.q_t9[0]) : 0u;   // the all-match window (its alias row is q0row)
         auto sample = [&](uint32_t off, uint32_t lg, uint32_t u, uint32_t j) {
             const uint32_t col = lg ? (u >> (16 - lg)) : 0u;
             const uint32_t e = __ldg(&T.q_alias[off + col]);
@@ -1242,47 +1242,38 @@ __device__ __forceinline__ void finish_read(const Team<W>& tm, const SimParams& 
                 const bool want = live && j >= jb && j < je;
                 const uint32_t wsel = t < 4 ? (t < 2 ? ur.x : ur.y) : (t < 6 ? ur.z : ur.w);
                 const uint32_t u16 = (wsel >> (16 * (t & 1u))) & 0xFFFFu;
-                bool slow = want, want_sample = true;
+                bool slow = want;
                 if (want && fast) {
+                    // One path for every window the closure tables cover (no deletion; one D run of up to 3; two single
+                    // D columns): which table and which entry is worked out with selects, so that the lanes of a warp
+                    // stay together (each kind used to be a branch of its own: 14 of 32 lanes active on average).
                     const uint32_t ops18 = (opsP >> (2 * t)) & 0x3FFFFu;
                     const uint32_t gm = (dmask >> (t + 1)) & 0xFFu;
                     const uint32_t code3 = lut3[ops18 & 63u] + 27u * lut3[(ops18 >> 6) & 63u] + 729u * lut3[ops18 >> 12];
-                    uint32_t ent = 0;
-                    if ((gm | ops18) == 0) {
-                        // nine matches, no deletion: alias row staged in shared memory by the kernel prologue
-                        const uint32_t col = lg0 ? (u16 >> (16 - lg0)) : 0u;
-                        const uint32_t e = q0row[col];
-                        const uint32_t fr = (u16 << lg0) & 0xFFFFu;
+                    // D count in front of column bi of the 16-column strip (bi = t + 1 + gap)
+                    auto dc_of = [&](uint32_t bi) {
+                        const uint32_t w = bi < 4 ? x0 : bi < 8 ? x1 : bi < 12 ? x2 : x3;
+                        return (w >> (8 * (bi & 3u) + 2)) & 15u;
+                    };
+                    const uint32_t rest = gm & (gm - 1);
+                    const uint32_t g1 = gm ? __ffs(gm) - 1 : 0u, g2 = rest ? __ffs(rest) - 1 : 0u;
+                    const uint32_t d1 = dc_of(t + 1 + g1), d2 = dc_of(t + 1 + g2);
+                    const bool none = gm == 0;
+                    const bool one = gm != 0 && rest == 0 && d1 <= 3;
+                    const bool two = rest != 0 && (rest & (rest - 1)) == 0 && d1 == 1 && d2 == 1;
+                    const bool allmatch = (gm | ops18) == 0;   // nine matches: entry and alias row are at hand
+                    const uint32_t* tbl = one ? T.q_t9d1 : two ? T.q_t9d2 : T.q_t9;
+                    const uint32_t idx = code3 + 19683u * (one ? 3 * g1 + d1 - 1 : two ? g1 * (15 - g1) / 2 + g2 - g1 - 1 : 0u);
+                    if (none || one || two) {
+                        slow = false;
+                        const uint32_t ent = allmatch ? ent0 : __ldg(tbl + idx);
+                        const uint32_t off = ent >> 3, lg = ent & 7u;
+                        const uint32_t col = lg ? (u16 >> (16 - lg)) : 0u;
+                        const uint32_t e = allmatch ? q0row[col] : __ldg(&T.q_alias[off + col]);
+                        const uint32_t fr = (u16 << lg) & 0xFFFFu;
                         const uint32_t q = fr < (e & 0xFFFFu) ? ((e >> 16) & 127u) : ((e >> 23) & 127u);
                         oq[j - jb] = (uint8_t)(q + 33);
-                        want_sample = false;
-                        slow = false;
-                    } else if (gm == 0) {
-                        ent = __ldg(&T.q_t9[code3]);
-                        slow = false;
-                    } else {
-                        // D count in front of column bi of the 16-column strip (bi = t + 1 + gap)
-                        auto dc_of = [&](uint32_t bi) {
-                            const uint32_t w = bi < 4 ? x0 : bi < 8 ? x1 : bi < 12 ? x2 : x3;
-                            return (w >> (8 * (bi & 3u) + 2)) & 15u;
-                        };
-                        const uint32_t g1 = __ffs(gm) - 1;
-                        const uint32_t rest = gm & (gm - 1);
-                        if (rest == 0) {
-                            const uint32_t dc = dc_of(t + 1 + g1);
-                            if (dc <= 3) {
-                                ent = __ldg(&T.q_t9d1[code3 + 19683u * (3 * g1 + dc - 1)]);
-                                slow = false;
-                            }
-                        } else if ((rest & (rest - 1)) == 0) {
-                            const uint32_t g2 = __ffs(rest) - 1;
-                            if (dc_of(t + 1 + g1) == 1 && dc_of(t + 1 + g2) == 1) {
-                                ent = __ldg(&T.q_t9d2[code3 + 19683u * (g1 * (15 - g1) / 2 + g2 - g1 - 1)]);
-                                slow = false;
-                            }
-                        }
                     }
-                    if (!slow && want_sample) sample(ent >> 3, ent & 7u, u16, j);
                 }
                 sq.push(slow, j, u16);
                 const uint32_t cnt = sq.ready(false);
