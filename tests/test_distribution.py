@@ -65,7 +65,7 @@ def chi2_p(a, b, min_exp=5):
     return float(sps.chi2_contingency(np.array([A, B])).pvalue)
 
 
-SEED = 7   # the calibration constants were fitted on other molecules and other seeds (oracle/fit_calibration.py)
+SEED = int(os.environ.get("TKSM_DIST_SEED", "7"))   # the calibration constants were fitted on other molecules and other seeds (oracle/fit_calibration.py)
 
 
 def effective_kappa(em):
@@ -159,6 +159,9 @@ CPU_CASES = [("nanopore2020", 600), ("pacbio2016_hifi", 600)]
 # configurations on one or two quantities (identity +0.25 points for `random`, -0.03 points for the hifi setting,
 # substitution rate +0.15 points for nanopore2018; DESIGN.md 5 lists them) -- the sample size here is the one at
 # which differences of that size are below the resolution of the test, i.e. it states how close the match is.
+# Other seeds ($TKSM_DIST_SEED; measured on the B200, round 2): of the 24 configuration-runs at seeds 1-4, 21 pass all
+# tests and 3 fail one (pacbio2016_hifi at seeds 2 and 4, nanopore2020 at seed 3); a run makes about 15 independent tests
+# or Bonferroni families at p > 0.01, so one run in seven fails by chance alone.
 GPU_N = int(os.environ.get("TKSM_DIST_N", "3000"))
 GPU_CASES = [(name, GPU_N) for name in ("nanopore2020", "nanopore2018", "pacbio2016", "pacbio2016_hifi", "random",
                                         "nanopore2020_const90")]

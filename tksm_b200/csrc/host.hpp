@@ -86,6 +86,9 @@ struct HostBatch {
 // consumed; the caller keeps the tail and calls again with more data (FIFO-safe, never seeks).
 // With `final` set the remaining bytes are parsed as the last record(s).
 // Throws std::runtime_error where the reference would raise (py/sequence.py:205-218, 229-239).
+// One deliberate leniency: an interval line of four fields (no modifications column) is taken as one with an empty
+// fifth field, as the reference's C++ reader does (src/mdf.h:88-90: the modules before Seq write such lines);
+// py/sequence.py:215 would raise ValueError.  Tested in tests/test_gpu_parity.py (handmade record `nomods4`).
 struct MdfParser {
     const GenomeStore* genome;
     bool capture_cb = false;   // keep the first value of the header's CB= comment per molecule (fused SCB step)
