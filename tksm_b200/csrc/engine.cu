@@ -52,7 +52,15 @@ struct DBuf {
         p = nullptr;
         cap = 0;
         size_t want = bytes + bytes / 8 + 256;
-        CK(cudaMalloc(&p, want));
+        if (want > ((size_t)1 << 30) && getenv("TKSM_SEQ_TRACE")) fprintf(stderr, "[trace] device buffer of %zu MiB\n", want >> 20);
+        const cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) {
+            p = nullptr;
+            size_t fr = 0, tot = 0;
+            cudaMemGetInfo(&fr, &tot);
+            throw std::runtime_error(std::string("CUDA error: ") + cudaGetErrorString(e) + " allocating " + std::to_string(want >> 20) +
+                                     " MiB of device memory (" + std::to_string(fr >> 20) + " of " + std::to_string(tot >> 20) + " MiB free)");
+        }
         cap = want;
     }
     void release() {
@@ -96,7 +104,9 @@ __global__ void synth_genome_kernel(uint32_t* words, uint64_t nwords, uint32_t s
 constexpr size_t SMEM_TOTAL = 232448;  // 227 KB opt-in maximum per CTA on sm_100 (smaller carve-outs for more L1 measured slower: 195 KB +5 %, 163 KB +19 %)
 constexpr int N_CLASSES = 6;           // teams of 1, 2, 4, 8, 24 warps in shared memory; 24 warps with a global workspace
 constexpr int GWS_CLASS = N_CLASSES - 1;
-constexpr int GWS_W2 = 32;   // warps per read of the expansion + qscore kernel of the global-workspace class
+constexpr int GWS_W2 = 8;    // warps per read of the FIN_FULL kernel of the global-workspace class: the chunks of its alignment keep
+                             // a few hundred threads busy at most, so several small CTAs per SM (GWS_FULL_CTAS) beat one of 32 warps
+constexpr int GWS_FULL_CTAS = 4;
 const int CLASS_W[N_CLASSES] = {1, 2, 4, 8, 24, 24};
 inline uint32_t list_capacity(uint32_t ncap) { return ncap / 5 * 2 + 64; }
 
@@ -233,6 +243,7 @@ struct tksm_seq_batch {
     DBuf blob;
     DevBatch db{};
     uint32_t* d_work[N_CLASSES] = {};
+    DBuf gws4;            // global workspaces of the FIN_FULL kernel of the class of 24 warps
     DBuf text, mdf_ws;    // device MDF tokeniser: the text of the batch and its per-line / per-record work arrays
     HBuf h_mdf;           // pinned: MdfTotals
     DBuf scr_seq, scr_qual, scr_raw, per_read, out[2], rec_len[2], rec_off[2], sums, gws, counters, work_keys, work_sorted, work_bins, mid, trace, redo, redo64, scr_ops, scr_cig, rinfo, atrace, scr_off_grow;
@@ -268,7 +279,7 @@ struct tksm_seq_batch {
     ~tksm_seq_batch() {
         for (DBuf* d : {&blob, &scr_seq, &scr_qual, &scr_raw, &per_read, &out[0], &out[1], &rec_len[0], &rec_len[1],
                         &rec_off[0], &rec_off[1], &sums, &gws, &counters, &work_keys, &work_sorted, &work_bins, &mid, &trace, &redo,
-                        &redo64, &scr_ops, &scr_cig, &rinfo, &atrace, &scr_off_grow, &text, &mdf_ws})
+                        &redo64, &scr_ops, &scr_cig, &rinfo, &atrace, &scr_off_grow, &text, &mdf_ws, &gws4})
             d->release();
         stage.release();
         h_mdf.release();
@@ -505,6 +516,7 @@ struct Phase2Launch {
     size_t smem;
     int grid, threads;
     uint32_t slab_bytes;
+    uint8_t* gws = nullptr;   // workspace region of the FIN_FULL kernel when it is a global-workspace instance of its own
 };
 // W2: warps per read of the PHASE 2 kernel (the global-workspace class is not bound by a shared-memory slab and
 // puts all 32 warps of a CTA on its read)
@@ -521,7 +533,9 @@ struct AlignLaunch {
     cudaEvent_t ev_fork, ev_side, ev_early;
     bool early64;             // the class holds reads above ALIGN_WIDE64_FROM slots: the 64-bit instance starts on them beside the 32-bit one
 };
-template <int W, bool GWS, int W2 = W>
+// GWS2: the FIN_FULL kernel works on a workspace in global memory (the class of 24 warps does, with teams of GWS_W2
+// warps, although its error-injection kernel has its read in shared memory)
+template <int W, bool GWS, int W2 = W, bool GWS2 = GWS>
 void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, const Phase2Launch& p2, const AlignLaunch& al) {
     launch_sim_phase<W, GWS, 1>(stream, P, smem, grid);
     if (!(P.flags & RUN_ERRORS)) return;
@@ -531,7 +545,8 @@ void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, const P
         P.slab_bytes = p2.slab_bytes;
         P.counter = counters + 16;
         P.n_work_dev = nullptr;
-        launch_sim_phase<W2, GWS, FIN_FULL>(stream, P, p2.smem, p2.grid, p2.threads);
+        if (p2.gws) P.gws = p2.gws;
+        launch_sim_phase<W2, GWS2, FIN_FULL>(stream, P, p2.smem, p2.grid, p2.threads);
         return;
     }
     // expansion | one thread per read: alignment | qscores; then the redo list of the class
@@ -609,7 +624,8 @@ void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, const P
     P.counter = counters + 56;
     P.work = P.redo;
     P.n_work_dev = P.redo_count;
-    launch_sim_phase<W2, GWS, FIN_FULL>(side, P, p2.smem, std::min(p2.grid, 32), p2.threads);
+    if (p2.gws) P.gws = p2.gws;
+    launch_sim_phase<W2, GWS2, FIN_FULL>(side, P, p2.smem, std::min(p2.grid, 32), p2.threads);
     CK(cudaEventRecord(al.ev_side, side));
     CK(cudaStreamWaitEvent(stream, al.ev_side, 0));
 }
@@ -1093,8 +1109,11 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format, bool gro
         cap_list_c[GWS_CLASS] = ncap / 2 + 64;
         slab_c[GWS_CLASS] = std::max(slab_layout(CLASS_W[GWS_CLASS], 8, ncap, cap_list_c[GWS_CLASS]).bytes,
                                      slab2_big_bytes(ncap));
-        b->gws.ensure((size_t)slab_c[GWS_CLASS] * h->num_sms);
+        b->gws.ensure((size_t)slab_c[GWS_CLASS] * h->num_sms * GWS_FULL_CTAS);
     }
+    // the class of 24 warps: its FIN_FULL kernel runs as a global-workspace instance too (fragment, slot lengths, read)
+    const size_t gws4_slab = align_up((size_t)slab2_big_bytes(ncap_c[4]) + 256, 256);
+    if (n_work[4] && (flags & RUN_ERRORS)) b->gws4.ensure(gws4_slab * h->num_sms * GWS_FULL_CTAS);
     uint64_t* d_totals = (uint64_t*)((char*)b->counters.p + CNT_TOTALS);
     // u32 words: [0..5] error-injection tickets | [8..15] totals (u64 x 4) | [16..21] expansion tickets | [24..29] qscore
     // tickets | [32..40] debug | [48..53] redo counts | [56..61] redo tickets | [64..69] alignment tickets | [72..77] tickets of its 64-bit instance | [80..85] its work counts | [88..93] qscore tickets of those reads
@@ -1112,9 +1131,10 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format, bool gro
     if (flags & RUN_QUAL)
         for (int c = 0; c < N_CLASSES; c++) {
             if (n_work[c] == 0) continue;
-            const int W2 = c == GWS_CLASS ? GWS_W2 : CLASS_W[c];
-            const int teams2 = c == GWS_CLASS ? 1 : (int)h->threads2[c] / 32 / CLASS_W[c];
-            size_t grid2 = std::min<size_t>((size_t)h->num_sms, (n_work[c] + teams2 - 1) / teams2);
+            const bool gws_full = c == GWS_CLASS || c == 4;   // FIN_FULL as a global-workspace instance: one team per CTA
+            const int W2 = gws_full ? GWS_W2 : CLASS_W[c];
+            const int teams2 = gws_full ? 1 : (int)h->threads2[c] / 32 / CLASS_W[c];
+            size_t grid2 = std::min<size_t>((size_t)h->num_sms * (gws_full ? GWS_FULL_CTAS : 1), (n_work[c] + teams2 - 1) / teams2);
             // (a class of long fragments with few reads is a few long chains for align_kernel, 7 ms at 8192 slots whatever
             // the batch; measured: the team-parallel FIN_FULL kernel on such a class is no faster)
             if (CLASS_W[c] < 24) grid2 = std::min<size_t>(grid2, 32);   // redo lists only
@@ -1249,11 +1269,13 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format, bool gro
         int grid = (int)std::min<size_t>((size_t)h->num_sms, (P.n_work + teams - 1) / teams);
         Phase2Launch p2;
         {
-            const int teams2 = c == GWS_CLASS ? 1 : (int)h->threads2[c] / 32 / CLASS_W[c];
-            p2.smem = h->smem_bytes2[c];
-            p2.grid = (int)std::min<size_t>((size_t)h->num_sms, (P.n_work + teams2 - 1) / teams2);   // (as the trace regions above)
-            p2.threads = (int)h->threads2[c];
-            p2.slab_bytes = c == GWS_CLASS ? slab_c[c] : h->slab2[c];   // the global workspaces keep their size
+            const bool gws_full = c == GWS_CLASS || c == 4;
+            const int teams2 = gws_full ? 1 : (int)h->threads2[c] / 32 / CLASS_W[c];
+            p2.smem = h->smem_bytes2[gws_full ? GWS_CLASS : c];
+            p2.grid = (int)std::min<size_t>((size_t)h->num_sms * (gws_full ? GWS_FULL_CTAS : 1), (P.n_work + teams2 - 1) / teams2);   // (as the trace regions above)
+            p2.threads = (int)h->threads2[gws_full ? GWS_CLASS : c];
+            p2.slab_bytes = c == GWS_CLASS ? slab_c[c] : c == 4 ? (uint32_t)gws4_slab : h->slab2[c];   // the global workspaces keep their size
+            if (c == 4) p2.gws = b->gws4.as<uint8_t>();
         }
         const uint32_t si = used_streams % 4;
         cudaStream_t st = h->class_stream[b->lane][si];
@@ -1264,7 +1286,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format, bool gro
             case 1: launch_sim<2, false>(st, P, h->smem_bytes[c], grid, p2, al); break;
             case 2: launch_sim<4, false>(st, P, h->smem_bytes[c], grid, p2, al); break;
             case 3: launch_sim<8, false>(st, P, h->smem_bytes[c], grid, p2, al); break;
-            case 4: launch_sim<24, false>(st, P, h->smem_bytes[c], grid, p2, al); break;
+            case 4: launch_sim<24, false, GWS_W2, true>(st, P, h->smem_bytes[c], grid, p2, al); break;
             default: launch_sim<24, true, GWS_W2>(st, P, h->smem_bytes[c], grid, p2, al); break;
         }
         // inject | FIN_FULL, or inject | expand, or inject | expand | align | qscores | [64-bit align early] | 64-bit align | its
