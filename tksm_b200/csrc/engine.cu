@@ -106,7 +106,10 @@ constexpr int N_CLASSES = 6;           // teams of 1, 2, 4, 8, 24 warps in share
 constexpr int GWS_CLASS = N_CLASSES - 1;
 constexpr int GWS_W2 = 8;    // warps per read of the FIN_FULL kernel of the global-workspace class: the chunks of its alignment keep
                              // a few hundred threads busy at most, so several small CTAs per SM (GWS_FULL_CTAS) beat one of 32 warps
-constexpr int GWS_FULL_CTAS = 4;
+constexpr int GWS_FULL_CTAS = 4;   // (length-skew shape: 8 warps x 4 CTAs 171 ms, 4 x 8 189 ms, 16 x 2 205 ms, 32 x 1 236 ms)
+// CTAs of the FIN_FULL launch on a class's redo list: a few reads as a rule, but in the class of 8 warps every read above
+// ALIGN_WIDE_FROM slots
+inline int redo_grid_cap(int c, int num_sms) { return c >= 3 ? num_sms : 32; }
 const int CLASS_W[N_CLASSES] = {1, 2, 4, 8, 24, 24};
 inline uint32_t list_capacity(uint32_t ncap) { return ncap / 5 * 2 + 64; }
 
@@ -531,6 +534,7 @@ struct AlignLaunch {
     int grid64;
     cudaStream_t side;        // stream of the 64-bit instance and the redo list
     cudaEvent_t ev_fork, ev_side, ev_early;
+    int redo_grid;            // CTAs of the FIN_FULL launch on the redo list
     bool early64;             // the class holds reads above ALIGN_WIDE64_FROM slots: the 64-bit instance starts on them beside the 32-bit one
 };
 // GWS2: the FIN_FULL kernel works on a workspace in global memory (the class of 24 warps does, with teams of GWS_W2
@@ -625,7 +629,7 @@ void launch_sim(cudaStream_t stream, SimParams P, size_t smem, int grid, const P
     P.work = P.redo;
     P.n_work_dev = P.redo_count;
     if (p2.gws) P.gws = p2.gws;
-    launch_sim_phase<W2, GWS2, FIN_FULL>(side, P, p2.smem, std::min(p2.grid, 32), p2.threads);
+    launch_sim_phase<W2, GWS2, FIN_FULL>(side, P, p2.smem, std::min(p2.grid, al.redo_grid), p2.threads);
     CK(cudaEventRecord(al.ev_side, side));
     CK(cudaStreamWaitEvent(stream, al.ev_side, 0));
 }
@@ -1137,7 +1141,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format, bool gro
             size_t grid2 = std::min<size_t>((size_t)h->num_sms * (gws_full ? GWS_FULL_CTAS : 1), (n_work[c] + teams2 - 1) / teams2);
             // (a class of long fragments with few reads is a few long chains for align_kernel, 7 ms at 8192 slots whatever
             // the batch; measured: the team-parallel FIN_FULL kernel on such a class is no faster)
-            if (CLASS_W[c] < 24) grid2 = std::min<size_t>(grid2, 32);   // redo lists only
+            if (CLASS_W[c] < 24) grid2 = std::min<size_t>(grid2, (size_t)redo_grid_cap(c, h->num_sms));   // redo lists only
             trace_team[c] = trace_team_bytes(W2, ncap_c[c]);
             trace_off[c] = trace_total;
             trace_total += trace_team[c] * teams2 * grid2;
@@ -1259,6 +1263,7 @@ void slot_launch(tksm_seq* h, tksm_seq_batch* b, int which, int format, bool gro
         al.redo64_count = b->counters.as<uint32_t>() + 80 + c;
         al.K.n_work_dev = nullptr;
         al.wide_class = wide_class[c];
+        al.redo_grid = redo_grid_cap(c, h->num_sms);
         al.grid64 = agrid64[c];
         P.redo64 = wide_class[c] ? nullptr : al.redo64;
         al.early64 = !wide_class[c] && ncap_c[c] > ALIGN_WIDE64_FROM;
