@@ -53,8 +53,8 @@ WORKLOADS = {
 
 # dram__bytes_read.sum + dram__bytes_write.sum over all launches of one step of the default workload (one ncu pass,
 # profiles/r2_dram_per_launch.txt)
-TRAFFIC_BYTES = 40.16e9
-TRAFFIC_NOTE = "profiles/r2v_dram_per_launch.txt: every launch of one step, ncu (serialised, cold caches); 19.2 GB of it are the two largest align_kernel launches (7.6 GB of trace cells written and read back, plus the per-read byte streams), 8.7 GB the hand-off records between the error-injection and expansion kernels"
+TRAFFIC_BYTES = 41.94e9
+TRAFFIC_NOTE = "profiles/r2zz_dram_per_launch.txt: every launch of one step, ncu (serialised, cold caches); about 21 GB of it are the two largest align_kernel launches (7.6 GB of trace cells written and read back, plus the per-read byte streams), 8.7 GB the hand-off records between the error-injection and expansion kernels"
 
 
 def peaks():
@@ -299,7 +299,7 @@ def main():
             "status_or": int(st.get("status_or", 0)),   # OR of the per-read status words of the last step (8 = some read's qscores follow the edit script: alignment band left)
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          # dram__bytes_read.sum + dram__bytes_write.sum over the 33 launches of one step of this
-                         # workload, one ncu capture (profiles/r2v_dram_per_launch.txt); other sizes: not captured
+                         # workload, one ncu capture (profiles/r2zz_dram_per_launch.txt); other sizes: not captured
                          "traffic": TRAFFIC_BYTES if (args.workload == "bulk" and args.molecules == 1_000_000) else None,
                          "traffic_unit": "bytes per step", "peak_source": peak_src,
                          "kernel": "work order + per length class: simulate_kernel<W,1> (error injection) | <W,2> (expansion) | "
