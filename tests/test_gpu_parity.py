@@ -359,6 +359,23 @@ def test_cli_gpus_flag_shards_in_one_process(world, tmp_path):
     p = subprocess.run([exe, "sequence", "-i", str(bad), "-o", str(out), "--gpus", "2"] + common, capture_output=True,
                        text=True, timeout=180, env={**os.environ, "TKSM_GPU_LIST": "0"})
     assert p.returncode == 1 and "Error" in p.stderr
+    # a stream that cannot be read twice is dealt to the devices piece by piece, not slurped: same bytes
+    import threading
+    for deal_bytes in ("7000", "100000000"):
+        fifo = tmp_path / f"in{deal_bytes}.fifo"
+        os.mkfifo(fifo)
+        feeder = threading.Thread(target=lambda: open(fifo, "wb").write(mdf))
+        feeder.start()
+        out, perf = tmp_path / "of.fastq", tmp_path / "pf.fasta"
+        p = subprocess.run([exe, "sequence", "-i", str(fifo), "-o", str(out), "--perfect", str(perf), "--gpus", "3"] + common,
+                           capture_output=True, text=True, timeout=180,
+                           env={**os.environ, "TKSM_GPU_LIST": "0,0,0", "TKSM_SEQ_DEAL_BYTES": deal_bytes})
+        feeder.join()
+        assert p.returncode == 0, p.stderr
+        assert out.read_bytes() == want and perf.read_bytes() == want_perf, deal_bytes
+    p = subprocess.run([exe, "sequence", "-i", str(bad), "-o", str(out), "--gpus", "2"] + common, capture_output=True, text=True,
+                       timeout=180, env={**os.environ, "TKSM_GPU_LIST": "0", "TKSM_SEQ_DEAL": "1", "TKSM_SEQ_DEAL_BYTES": "9000"})
+    assert p.returncode == 1 and "Error" in p.stderr
 
 
 @pytest.mark.gpu

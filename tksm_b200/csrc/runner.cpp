@@ -9,13 +9,19 @@
 #include <cstring>
 #include <deque>
 #include <future>
+#include <condition_variable>
+#include <map>
 #include <memory>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 #include <thread>
 #include <vector>
 
+#include <sys/stat.h>
+
 #include "engine.hpp"
+#include "host.hpp"
 
 namespace tk {
 
@@ -241,6 +247,160 @@ struct MemorySinks : OutputSink {
 
 }  // namespace
 
+namespace {
+
+// --gpus N on a stream: pieces of the MDF (complete records, TKSM_SEQ_DEAL_BYTES each, 64 MiB by default) go to the
+// devices round-robin; piece k carries the global ordinal of its first read (a light pass over its header lines
+// counts the reads), so the records are those of a one-GPU run, and they are written in piece order.
+void deal_stream(tksm_seq* const* handles, int n, const char* mdf_path, int which, int format, OutputSink& out, tksm_seq_stats* stats) {
+    struct Piece {
+        std::string text;
+        uint64_t ordinal = 0;
+        MemorySinks sink;
+        tksm_seq_stats st{};
+        std::string error;
+        bool done = false;
+    };
+    const size_t piece_bytes = getenv("TKSM_SEQ_DEAL_BYTES") ? std::max<size_t>((size_t)atoll(getenv("TKSM_SEQ_DEAL_BYTES")), 1) : ((size_t)64 << 20);
+    std::mutex mu;
+    std::condition_variable cv;
+    std::vector<std::deque<std::shared_ptr<Piece>>> queue((size_t)n);   // per device: pieces waiting or running
+    std::map<size_t, std::shared_ptr<Piece>> finished;                  // by piece index
+    std::vector<int> pending((size_t)n, 0);
+    bool closed = false, failed = false;
+    std::string first_error;
+
+    std::vector<std::thread> workers;
+    for (int i = 0; i < n; i++)
+        workers.emplace_back([&, i]() {
+            while (true) {
+                std::shared_ptr<Piece> p;
+                {
+                    std::unique_lock<std::mutex> g(mu);
+                    cv.wait(g, [&] { return !queue[(size_t)i].empty() || closed; });
+                    if (queue[(size_t)i].empty()) return;
+                    p = queue[(size_t)i].front();
+                    queue[(size_t)i].pop_front();
+                }
+                try {
+                    if (!failed) {
+                        auto src = make_memory_source(p->text.data(), p->text.size());
+                        engine_stream(handles[i], *src, which, format, p->ordinal, &p->sink, nullptr, nullptr, &p->st);
+                    }
+                } catch (const std::exception& e) {
+                    p->error = e.what()[0] ? e.what() : "error";
+                }
+                p->text.clear();
+                p->text.shrink_to_fit();
+                {
+                    std::lock_guard<std::mutex> g(mu);
+                    p->done = true;
+                    pending[(size_t)i]--;
+                    if (!p->error.empty()) failed = true;
+                }
+                cv.notify_all();
+            }
+        });
+
+    tksm_seq_stats total{};
+    size_t dealt = 0, written = 0;
+    std::map<size_t, std::shared_ptr<Piece>> inflight;
+    auto drain = [&](bool all) {   // write finished pieces in order; with `all`, wait for every piece
+        while (written < dealt) {
+            std::shared_ptr<Piece> p = inflight[written];
+            {
+                std::unique_lock<std::mutex> g(mu);
+                if (!all && !p->done) return;
+                cv.wait(g, [&] { return p->done; });
+            }
+            if (!p->error.empty() && first_error.empty()) first_error = p->error;
+            if (first_error.empty()) {
+                for (int o = 0; o < 2; o++)
+                    for (const std::string& part : p->sink.parts[o]) out.write(o, part.data(), part.size());
+                const tksm_seq_stats& s = p->st;
+                total.reads += s.reads;
+                total.raw_bases += s.raw_bases;
+                total.read_bases += s.read_bases;
+                total.out_bytes[0] += s.out_bytes[0];
+                total.out_bytes[1] += s.out_bytes[1];
+                total.algorithmic_bytes += s.algorithmic_bytes;
+                total.h2d_bytes += s.h2d_bytes;
+                total.d2h_bytes += s.d2h_bytes;
+                total.kernel_ms += s.kernel_ms;
+                total.simulate_ms += s.simulate_ms;
+                total.kernel_launches += s.kernel_launches;
+                total.status_or |= s.status_or;
+            }
+            inflight.erase(written);
+            written++;
+        }
+    };
+
+    FILE* in = strcmp(mdf_path, "-") == 0 ? stdin : fopen(mdf_path, "rb");
+    if (!in) {
+        {
+            std::lock_guard<std::mutex> g(mu);
+            closed = true;
+        }
+        cv.notify_all();
+        for (auto& t : workers) t.join();
+        throw std::runtime_error(std::string("cannot open ") + mdf_path);
+    }
+    std::string carry;
+    std::vector<char> buf((size_t)4 << 20);
+    uint64_t ordinal = 0;
+    bool eof = false;
+    while (!eof && !failed) {
+        // fill up to a piece, cut at the last record boundary
+        while (carry.size() < piece_bytes) {
+            const size_t got = fread(buf.data(), 1, buf.size(), in);
+            if (got == 0) {
+                eof = true;
+                break;
+            }
+            carry.append(buf.data(), got);
+        }
+        std::string piece;
+        if (eof) {
+            piece.swap(carry);
+        } else {
+            size_t cut = carry.rfind("\n+");
+            if (cut == std::string::npos || cut == 0) continue;   // one record larger than a piece: keep reading
+            piece.assign(carry, 0, cut + 1);
+            carry.erase(0, cut + 1);
+        }
+        if (piece.empty()) continue;
+        std::vector<uint64_t> bb, ob;
+        plan_shards(piece.data(), piece.size(), 1, bb, ob);
+        auto p = std::make_shared<Piece>();
+        p->text.swap(piece);
+        p->ordinal = ordinal;
+        ordinal += ob[1];
+        const size_t dev = dealt % (size_t)n;
+        {
+            std::unique_lock<std::mutex> g(mu);
+            cv.wait(g, [&] { return pending[dev] < 2 || failed; });
+            queue[dev].push_back(p);
+            pending[dev]++;
+        }
+        inflight[dealt++] = p;
+        cv.notify_all();
+        drain(false);
+    }
+    if (in != stdin) fclose(in);
+    {
+        std::lock_guard<std::mutex> g(mu);
+        closed = true;
+    }
+    cv.notify_all();
+    drain(true);
+    for (auto& t : workers) t.join();
+    if (!first_error.empty()) throw std::runtime_error(first_error);
+    if (stats) *stats = total;
+}
+
+}  // namespace
+
 void run_files_multi(tksm_seq* const* handles, int n, const char* mdf_path, const char* badread_path,
                      const char* perfect_path, tksm_seq_stats* stats) {
     Sink bad, perf;
@@ -249,7 +409,24 @@ void run_files_multi(tksm_seq* const* handles, int n, const char* mdf_path, cons
     const int which = (badread_path ? TKSM_SEQ_BADREAD : 0) | (perfect_path ? TKSM_SEQ_PERFECT : 0);
     const int format = (bad.fastq ? TKSM_SEQ_FASTQ_BADREAD : 0) | (perf.fastq ? TKSM_SEQ_FASTQ_PERFECT : 0);
 
-    // the shard plan needs the whole text (a FIFO is read to its end first)
+    // A stream that cannot be read twice (FIFO, stdin; $TKSM_SEQ_DEAL=1 forces it for files) is not slurped: pieces
+    // of complete records are dealt to the devices round-robin as they arrive, each with the global ordinal of its
+    // first read, and written back in order (at most two pieces per device in flight).
+    {
+        struct stat sb{};
+        const char* deal_env = getenv("TKSM_SEQ_DEAL");
+        const bool fifo = stat(mdf_path, &sb) == 0 && !S_ISREG(sb.st_mode);
+        if ((fifo && !(deal_env && atoi(deal_env) == 0)) || (deal_env && atoi(deal_env) == 1)) {
+            FileSinks direct;
+            direct.s[0] = badread_path ? &bad : nullptr;
+            direct.s[1] = perfect_path ? &perf : nullptr;
+            deal_stream(handles, n, mdf_path, which, format, direct, stats);
+            bad.close();
+            perf.close();
+            return;
+        }
+    }
+    // the shard plan needs the whole text
     std::string text;
     {
         FILE* in = fopen(mdf_path, "rb");
