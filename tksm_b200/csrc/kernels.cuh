@@ -570,8 +570,13 @@ __device__ __forceinline__ void inject_read(const Team<W>& tm, const SimParams& 
             // --- arrivals: N ~ Poisson(q * delta) trials per start position, found ones are queued
             WarpQueue tq_{wq_a, wq_b, 0, 0};
             auto run_trials = [&](uint32_t cnt) {
-                uint32_t i = 0, u16 = 0;
-                const bool mine = tq_.take(cnt, i, u16);
+                // an entry is ONE trial of a start position: (i, u16 | trial index << 16).  A position that drew more
+                // than one trial puts the next one back into the queue (a loop up to the warp's largest count ran its
+                // later rounds with one or two lanes)
+                uint32_t i = 0, uw = 0;
+                const bool mine = tq_.take(cnt, i, uw);
+                const uint32_t u16 = uw & 0xFFFFu;
+                const int tr = (int)(uw >> 16);
                 uint32_t x0 = 0, x1 = 0, code = 0;
                 bool valid = false;
                 int N = 0;
@@ -591,8 +596,7 @@ __device__ __forceinline__ void inject_read(const Team<W>& tm, const SimParams& 
                     N = __popc(__vcmpgtu2(th.x, uu) & 0x00010001u) + __popc(__vcmpgtu2(th.y, uu) & 0x00010001u) +
                         __popc(__vcmpgtu2(th.z, uu) & 0x00010001u) + __popc(__vcmpgtu2(th.w, uu) & 0x00010001u);
                 }
-                const int Nmax = __reduce_max_sync(0xffffffffu, N);
-                for (int tr = 0; tr < Nmax; tr++) {
+                {
                     // per lane: up to k slot updates (cm = mask of slots to update)
                     uint32_t cm = 0, tm16 = 0, rc_content = 0;
                     uint64_t aw = 0;
@@ -669,6 +673,7 @@ __device__ __forceinline__ void inject_read(const Team<W>& tm, const SimParams& 
                         }
                     }
                 }
+                tq_.push(mine && tr + 1 < N, i, u16 | ((uint32_t)(tr + 1) << 16));
             };
             const uint32_t nblk = (npos + 7) >> 3;
             const uint32_t nblk_r = (nblk + 31u) & ~31u;  // whole warps iterate together
@@ -697,8 +702,9 @@ __device__ __forceinline__ void inject_read(const Team<W>& tm, const SimParams& 
                         hit = u16 < T1[cls];
                     }
                     tq_.push(hit, i, u16);
-                    const uint32_t cnt = tq_.ready(false);
-                    if (cnt) run_trials(cnt);
+                    // (a drain may put up to 32 further trials back: drain until fewer than 32 wait, so that the next
+                    // 32 arrivals still fit the ring of 64)
+                    for (uint32_t cnt; (cnt = tq_.ready(false)) != 0;) run_trials(cnt);
                 }
             }
             for (uint32_t cnt; (cnt = tq_.ready(true)) != 0;) run_trials(cnt);
