@@ -127,39 +127,48 @@ class StagePool {
         }
     }
     // returns the index of a free buffer of at least `bytes`, or -1 when all buffers are in flight
-    // (never blocks: one packer may hold many batches before the issuing thread sees the first)
+    // (never blocks: one packer may hold many batches before the issuing thread sees the first).
+    // Best fit first, so that a small batch does not take the buffer the next large one needs; when nothing fits, a
+    // new buffer (else the smallest free one) is sized to the largest request seen so far: page-locking a buffer
+    // takes 10-20 ms and freeing one waits for the device, so the pool has to stop growing after a call or two
+    // (with "largest free buffer, grown to the request" a small buffer was re-pinned in one call out of five).
     int acquire(size_t bytes, int device) {
         std::unique_lock<std::mutex> g(mu_);
-        {
-            int idx = -1;
-            for (size_t i = 0; i < bufs_.size(); i++)
-                if (!bufs_[i].used && (idx < 0 || bufs_[i].mem.cap > bufs_[(size_t)idx].mem.cap)) idx = (int)i;
-            if (idx < 0 && (int)bufs_.size() < max_) {
-                bufs_.emplace_back();
-                idx = (int)bufs_.size() - 1;
-            }
-            if (idx >= 0) {
-                bufs_[(size_t)idx].used = true;
-                Buf& mine = bufs_[(size_t)idx];
-                g.unlock();
-                try {  // only this thread touches the buffer while it is `used`
-                    if (pinned_) {
-                        CK(cudaSetDevice(device));
-                        mine.mem.ensure(bytes);
-                    } else if (mine.mem.cap < bytes) {  // host_only handles: no CUDA call
-                        free(mine.mem.p);
-                        mine.mem.cap = bytes + bytes / 8 + 256;
-                        mine.mem.p = malloc(mine.mem.cap);
-                        if (!mine.mem.p) throw std::runtime_error("out of host memory");
-                    }
-                } catch (...) {
-                    release(idx);
-                    throw;
-                }
-                return idx;
-            }
+        high_water_ = std::max(high_water_, bytes);
+        int idx = -1, smallest = -1;
+        for (size_t i = 0; i < bufs_.size(); i++) {
+            if (bufs_[i].used) continue;
+            const size_t cap = bufs_[i].mem.cap;
+            if (cap >= bytes && (idx < 0 || cap < bufs_[(size_t)idx].mem.cap)) idx = (int)i;
+            if (smallest < 0 || cap < bufs_[(size_t)smallest].mem.cap) smallest = (int)i;
         }
-        return -1;
+        if (idx < 0 && (int)bufs_.size() < max_) {
+            bufs_.emplace_back();
+            idx = (int)bufs_.size() - 1;
+        }
+        if (idx < 0) idx = smallest;
+        if (idx < 0) return -1;
+        const size_t want = high_water_;
+        bufs_[(size_t)idx].used = true;
+        Buf& mine = bufs_[(size_t)idx];
+        g.unlock();
+        try {  // only this thread touches the buffer while it is `used`
+            if (mine.mem.cap >= bytes) return idx;
+            if (pinned_) {
+                CK(cudaSetDevice(device));
+                mine.mem.ensure(want);
+            } else {  // host_only handles: no CUDA call
+                free(mine.mem.p);
+                mine.mem.cap = 0;
+                mine.mem.p = malloc(want + want / 8 + 256);
+                if (!mine.mem.p) throw std::runtime_error("out of host memory");
+                mine.mem.cap = want + want / 8 + 256;
+            }
+        } catch (...) {
+            release(idx);
+            throw;
+        }
+        return idx;
     }
     char* ptr(int idx) {
         std::lock_guard<std::mutex> g(mu_);
@@ -178,6 +187,7 @@ class StagePool {
     };
     std::mutex mu_;
     std::deque<Buf> bufs_;   // deque: growing never moves the buffers other threads are filling
+    size_t high_water_ = 0;
     int max_;
     bool pinned_;
 };
