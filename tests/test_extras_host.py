@@ -183,3 +183,59 @@ def test_fused_steps_follow_their_modules_in_distribution(fuse_world, tmp_path):
     assert all(g[10:] == m + "GCAATACGTAACTGAACGAAGT" for g, m in zip(got, mols))
     letters = np.array([list(g[:10]) for g in got]).ravel()
     assert all(abs((letters == b).mean() - 0.25) < 0.01 for b in "ACGT")
+
+
+def test_host_parser_token_and_integer_corner_cases(emul, tmp_path):
+    """csrc/host.cpp: MdfParser compares contig names through their first 16 bytes and reads plain digit runs eight at a
+    time; everything else takes python's int() (py/sequence.py:207, 216-217).  Names of 1 to 33 bytes, literals of the
+    same lengths (one byte off a contig name), integers with leading zeros, signs, blanks, underscores and nine to
+    thirteen digits, modification lists and a last line without a line end: the molecules must be the oracle's."""
+    import random
+    exe = emul[0]
+    rng = random.Random(6)
+    names = ["c", "chr12345", "chr_fifteen_abc", "chr_sixteen_abcd", "chr_seventeen_abc", "chr_seventeen_abd",
+             "a_very_long_contig_name_of_thirty", "ACGTACGTACGTACGTA"]
+    fasta = "".join(f">{n}\n{''.join(rng.choice('ACGTN') for _ in range(5000))}\n" for n in names)
+    lits = ["A", "ACGTACGT", "ACGTACGTACGTACG", "ACGTACGTACGTACGT", "ACGTACGTACGTACGTC", "chr_seventeen_abX",
+            "chr_sixteen_abcX", "acgtnnRYacgtacgtacgtacgtacgtac", "a_very_long_contig_name_of_thirtY"]
+
+    def fmt(v):
+        r = rng.random()
+        if v < 0 or r > 0.45:
+            return str(v)
+        if r < 0.15:
+            return f"{v:09d}"
+        if r < 0.25:
+            return f"{v:016d}"
+        if r < 0.30:
+            return f" {v} "
+        if r < 0.35:
+            return f"+{v}"
+        if r < 0.40 and v >= 1000:
+            return f"{v // 1000}_{v % 1000:03d}"
+        return f"{v:017d}"
+
+    lines = []
+    for m in range(1500):
+        lines.append(f"+m{m}\t{fmt(rng.choice([0, 1, 1, 1, 2]))}\tCB=AAAC,x;")
+        for _ in range(rng.randint(1, 8)):
+            if rng.random() < 0.6:
+                a = rng.randint(0, 4000)
+                b = a + rng.randint(1, 900)
+                if rng.random() < 0.1:
+                    b = rng.choice([123456789, 1234567890123, 99999999, 100000000, 4999, 5000, 5001])
+                mods = ""
+                if rng.random() < 0.3 and b <= 5000:
+                    mods = ",".join(f"{fmt(rng.randint(0, b - a - 1)).strip()}{rng.choice('ACGTacgtN')}" for _ in range(rng.randint(1, 3)))
+                lines.append(f"{rng.choice(names)}\t{fmt(a)}\t{fmt(b)}\t{rng.choice('+-')}\t{mods}")
+            else:
+                lines.append(f"{rng.choice(lits)}\t{fmt(rng.randint(-3, 5))}\t{fmt(rng.randint(-3, 40))}\t{rng.choice('+-')}\t")
+    mdf = "\n".join(lines)                      # the last token of the text has nothing readable behind it
+    (tmp_path / "odd.fa").write_text(fasta)
+    (tmp_path / "odd.mdf").write_text(mdf)
+    refs = so.load_fasta(fasta)
+    want = [so.molecule_sequence(refs, iv).decode() for _, iv in so.parse_mdf(mdf)]
+    assert len(want) > 1000 and any(len(w) > 3000 for w in want)
+    out = subprocess.run([exe, str(tmp_path / "odd.fa"), str(tmp_path / "odd.mdf"), str(SEED), "0"] + ["0"] * 10 +
+                         [xo.START_ADAPTER, xo.END_ADAPTER], capture_output=True, text=True, check=True)
+    assert out.stdout.split("\n")[:-1] == want

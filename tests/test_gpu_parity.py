@@ -561,7 +561,7 @@ def test_device_mdf_tokeniser_matches_the_host_parser(world, monkeypatch, models
     crlf = clean.replace(b"\n", b"\r\n")
     assert s.simulate(crlf, BADREAD, True) == want
     # errors surface as they do from the host parser, and the handle keeps working
-    for bad in (b"chr1\t0\t5\n", b"chr1\t0\tx\t+\t\n", b"chr1\t0\t5\t+\t9A\n", b"\n"):
+    for bad in (b"chr1\t0\t5\n", b"chr1\t0\tx\t+\t\n", b"chr1\t0\t5\t+\t9A\n", b"\n", b"\t0\t5\t+\t\n"):
         with pytest.raises(Exception):
             s.simulate(clean + bad, BADREAD, True)
     assert s.simulate(clean, BADREAD, True) == want

@@ -161,7 +161,8 @@ def test_mdf_parser_raises_where_the_reference_raises(Sequencer):
                 "+m\t1\t\nc\tx\t4\t+\t\n",             # int()
                 "+m\tone\t\nc\t0\t4\t+\t\n",           # depth
                 "+m\t1\t\nc\t0\t4\t+\t9G\n",           # modification out of range
-                "+m\t1\t\n\nc\t0\t4\t+\t\n"):          # empty line
+                "+m\t1\t\n\nc\t0\t4\t+\t\n",           # empty line
+                "+m\t1\t\n\t0\t4\t+\t\n"):           # empty first field: line[0][0]
         with pytest.raises(SeqError):
             s.batch(bad)
 

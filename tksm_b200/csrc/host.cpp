@@ -247,6 +247,28 @@ inline bool scan_line(const char* text, size_t len, size_t pos, LineScan& L) {
     L.ntab = 0;
     const __m128i vt = _mm_set1_epi8('\t'), vn = _mm_set1_epi8('\n'), vr = _mm_set1_epi8('\r');
     const char* stop = nullptr;
+    // 32 bytes at a time (most interval lines end inside the first block): tabs and line ends as two bit masks, the
+    // tabs before the line end taken off their mask one by one
+    while (end - p >= 32) {
+        const __m128i v0 = _mm_loadu_si128((const __m128i*)p), v1 = _mm_loadu_si128((const __m128i*)(p + 16));
+        unsigned mt = (unsigned)_mm_movemask_epi8(_mm_cmpeq_epi8(v0, vt)) |
+                      ((unsigned)_mm_movemask_epi8(_mm_cmpeq_epi8(v1, vt)) << 16);
+        const unsigned mn = (unsigned)_mm_movemask_epi8(_mm_or_si128(_mm_cmpeq_epi8(v0, vn), _mm_cmpeq_epi8(v0, vr))) |
+                            ((unsigned)_mm_movemask_epi8(_mm_or_si128(_mm_cmpeq_epi8(v1, vn), _mm_cmpeq_epi8(v1, vr))) << 16);
+        if (mn) {
+            const int at = __builtin_ctz(mn);
+            mt &= (1u << at) - 1u;
+            stop = p + at;
+        }
+        while (mt) {
+            const int i = __builtin_ctz(mt);
+            mt &= mt - 1;
+            if (L.ntab < 5) L.tab[L.ntab] = p + i;
+            if (L.ntab < 6) L.ntab++;
+        }
+        if (stop) break;
+        p += 32;
+    }
     while (!stop) {
         if (end - p >= 16) {
             const __m128i v = _mm_loadu_si128((const __m128i*)p);
@@ -324,9 +346,28 @@ long long py_int(const char* b, const char* e) {
     return neg ? -v : v;
 }
 
-// plain decimal digits (the emitter's format); anything else goes through py_int
-inline long long mdf_int(const char* b, const char* e) {
-    if (b < e && e - b <= 18) {
+// n <= 8 decimal digits starting at p, all eight bytes at p readable: the bytes moved to the top of a word, '0' below
+// them, checked and summed in three multiplications instead of a dependent multiply-add per digit
+inline bool digits8(const char* p, size_t n, uint64_t& out) {
+    uint64_t v;
+    memcpy(&v, p, 8);
+    if (n < 8) v = (v << (8 * (8 - n))) | (0x3030303030303030ull >> (8 * n));
+    if (((v + 0x4646464646464646ull) | (v - 0x3030303030303030ull)) & 0x8080808080808080ull) return false;
+    v -= 0x3030303030303030ull;
+    v = (v * 10) + (v >> 8);
+    out = (((v & 0x000000FF000000FFull) * 0x000F424000000064ull) + (((v >> 16) & 0x000000FF000000FFull) * 0x0000271000000001ull)) >> 32;
+    return true;
+}
+
+// plain decimal digits (the emitter's format); anything else goes through py_int.  `readable_end`: end of the buffer
+// the field lies in (bytes up to it may be read), or null.
+inline long long mdf_int(const char* b, const char* e, const char* readable_end = nullptr) {
+    const size_t n = (size_t)(e - b);
+    if (b < e && n <= 16 && readable_end && b + 8 <= readable_end) {
+        uint64_t lo, hi = 0;
+        if (n <= 8 ? digits8(b, n, lo) : (digits8(b, n - 8, hi) && digits8(e - 8, 8, lo)))
+            return (long long)(hi * 100000000ull + lo);
+    } else if (b < e && n <= 18) {
         long long v = 0;
         const char* p = b;
         for (; p < e; p++) {
@@ -426,6 +467,24 @@ void plan_shards(const char* text, size_t len, int world, std::vector<uint64_t>&
 size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out, size_t max_reads,
                        uint64_t max_bases) {
     size_t pos = 0, consumed = 0;
+    // Room for the lines of this text up front (an interval line of the emitter's format has 20 bytes or more): the
+    // arrays of a 1 MiB chunk would otherwise be reallocated a dozen times each, every step a fresh mapping whose
+    // pages fault in, on all parser threads at once.  Pages never written cost nothing.
+    {
+        const size_t lines = len / 20 + 16;
+        auto room = [lines](auto& v, size_t per_line_num, size_t per_line_den) {
+            const size_t want = v.size() + lines * per_line_num / per_line_den;
+            if (v.capacity() < want) v.reserve(want);
+        };
+        room(out.seg_src, 1, 1);
+        room(out.seg_len, 1, 1);
+        room(out.seg_mod_begin, 1, 1);
+        room(out.read_mol, 1, 4);
+        room(out.mol_raw_len, 1, 4);
+        room(out.mol_seg_begin, 1, 4);
+        room(out.mol_id_begin, 1, 4);
+        room(out.id_pool, 2, 1);
+    }
     // state of the record being assembled
     bool have = false;
     long long depth = 0;
@@ -440,14 +499,15 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
     // nearly all string hashing.
     struct TokEntry {
         std::string tok;
+        uint64_t k0 = 0, k1 = 0;   // the first 16 bytes of tok, zero-padded
+        bool valid = false;
         const Contig* contig = nullptr;
         long long lit_s = -1, lit_e = -1;
         size_t lit_epoch = 0;
         uint32_t lit_off = 0;
     };
-    constexpr int NTOK = 8;
+    constexpr int NTOK = 64;       // direct-mapped on a hash of the first 16 bytes and the length
     TokEntry toks[NTOK];
-    int tok_next = 0;
     size_t lit_epoch = 1;  // bumped when a rollback may have dropped pool bytes
     TokEntry* last_tok = nullptr;  // exon lines of one molecule repeat the chromosome
     TokEntry scratch_tok;
@@ -475,32 +535,50 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
     };
     std::string lit;               // encoded literal of the current line (buffer reused)
     constexpr size_t LIT_SLOTS = 4096;
+    const char* const text_end = text + len;
     auto resolve = [&](std::string_view chrom) -> TokEntry& {
-        if (last_tok && last_tok->tok.size() == chrom.size() && !chrom.empty() &&
-            memcmp(last_tok->tok.data(), chrom.data(), chrom.size()) == 0)
-            return *last_tok;
-        for (int i = 0; i < NTOK; i++)
-            if (toks[i].tok.size() == chrom.size() && memcmp(toks[i].tok.data(), chrom.data(), chrom.size()) == 0 &&
-                (!chrom.empty() || toks[i].lit_epoch)) {
-                last_tok = &toks[i];
-                return toks[i];
-            }
-        if (!genome->name_len_possible(chrom.size())) {
+        const size_t n = chrom.size();
+        if (!genome->name_len_possible(n)) {
             // no contig name has this length: a literal (barcode, UMI, adapter, poly(A) run); it stays out of the
             // token cache, which the chromosome names keep
-            last_tok = nullptr;
             scratch_tok.contig = nullptr;
             scratch_tok.lit_s = scratch_tok.lit_e = -1;
             return scratch_tok;
         }
-        TokEntry& t = toks[tok_next];
-        tok_next = (tok_next + 1) % NTOK;
+        // the token's first 16 bytes as two words: a cache entry is compared without a call into libc
+        uint64_t k0, k1;
+        if (chrom.data() + 16 <= text_end) {
+            memcpy(&k0, chrom.data(), 8);
+            memcpy(&k1, chrom.data() + 8, 8);
+        } else {
+            char pad[16] = {0};
+            memcpy(pad, chrom.data(), n < 16 ? n : 16);
+            memcpy(&k0, pad, 8);
+            memcpy(&k1, pad + 8, 8);
+        }
+        if (n < 8) {
+            k0 &= (1ull << (8 * n)) - 1;
+            k1 = 0;
+        } else if (n < 16) {
+            k1 &= (1ull << (8 * (n - 8))) - 1;
+        }
+        auto same = [&](const TokEntry& t) {
+            return t.valid && t.k0 == k0 && t.k1 == k1 && t.tok.size() == n &&
+                   (n <= 16 || memcmp(t.tok.data() + 16, chrom.data() + 16, n - 16) == 0);
+        };
+        if (last_tok && same(*last_tok)) return *last_tok;
+        const uint64_t hsh = (k0 * 0x9E3779B97F4A7C15ull) ^ (k1 * 0xC2B2AE3D27D4EB4Full) ^ (n * 0x165667B19E3779F9ull);
+        TokEntry& t = toks[(size_t)(hsh >> 58) & (NTOK - 1)];
+        last_tok = &t;
+        if (same(t)) return t;
         t.tok.assign(chrom);
+        t.k0 = k0;
+        t.k1 = k1;
+        t.valid = true;
         auto it = genome->contigs.find(t.tok);
         t.contig = it == genome->contigs.end() ? nullptr : &it->second;
         t.lit_s = t.lit_e = -1;
         t.lit_epoch = lit_epoch;
-        last_tok = &t;
         return t;
     };
 
@@ -552,6 +630,7 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
         if (!final && !ln.terminated) break;  // partial last line: wait for more data
         pos = ln.next;
         if (ln.b == ln.e) throw std::runtime_error("IndexError: empty line in MDF (py/sequence.py:207)");
+        if (*ln.b == '\t') throw std::runtime_error("IndexError: MDF line with an empty first field (py/sequence.py:207)");
         if (*ln.b == '+') {
             if (have) {
                 commit();
@@ -594,7 +673,7 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
         if (nf < 4) throw std::runtime_error("ValueError: not enough values to unpack (MDF interval line)");
         if (nf > 5) throw std::runtime_error("ValueError: too many values to unpack (MDF interval line)");
         auto fend = [&](int i) { return i + 1 < nf ? f[i + 1] - 1 : ln.e; };
-        long long start = mdf_int(f[1], fend(1)), end = mdf_int(f[2], fend(2));
+        long long start = mdf_int(f[1], fend(1), text + len), end = mdf_int(f[2], fend(2), text + len);
         bool plus = (fend(3) - f[3] == 1) && *f[3] == '+';
         if (!have) continue;  // intervals before the first header are parsed and dropped (py:213)
 
@@ -667,7 +746,7 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
                 const char* c = (const char*)memchr(p, ',', (size_t)(ln.e - p));
                 const char* ie = c ? c : ln.e;
                 if (ie == p) throw std::runtime_error("IndexError: empty modification entry");
-                long long mp = py_int(p, ie - 1);
+                long long mp = mdf_int(p, ie - 1, text + len);   // plain digits in the emitter's format, else python's int()
                 if (mp < 0) mp += slen;
                 if (mp < 0 || mp >= (long long)slen)
                     throw std::runtime_error("IndexError: list assignment index out of range (modification position)");

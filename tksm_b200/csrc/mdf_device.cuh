@@ -204,7 +204,7 @@ __global__ void mdf_parse_lines(const MdfParams P) {
     P.is_hdr[li] = 0;
     P.a32[li] = P.b32[li] = P.c32[li] = 0;
     P.src[li] = 0;
-    if (e <= b) {
+    if (e <= b || *b == '\t') {   // empty line, empty first field: line[0][0] raises (py/sequence.py:207)
         mdf_flag(P, MDF_BAD_EMPTY);
         return;
     }
