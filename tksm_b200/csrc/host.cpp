@@ -516,6 +516,7 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
     // costs one memcmp instead of encoding and hashing the bases again.
     struct LitText {
         std::string text;
+        uint64_t k0 = 0, k1 = 0;   // its first 16 bytes, as in TokEntry
         long long s = 0, e = 0;
         size_t epoch = 0;   // 0: no text stored
         uint32_t off = 0;
@@ -524,29 +525,29 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
     constexpr size_t LIT_TEXTS = 256;
     std::vector<LitText> lit_texts(LIT_TEXTS);
     uint64_t lit_fp = 0;   // fingerprint of the text lit_text_slot() was last asked about
+    uint64_t k0 = 0, k1 = 0;   // first 16 bytes of the first field of the current line, zero-padded (key_of)
+    auto key_hash = [&](size_t n) {
+        return (k0 * 0x9E3779B97F4A7C15ull) ^ (k1 * 0xC2B2AE3D27D4EB4Full) ^ (n * 0x165667B19E3779F9ull);
+    };
     auto lit_text_slot = [&](std::string_view t) -> LitText& {
-        uint64_t a = 0, b = 0;
-        const size_t k = t.size() < 8 ? t.size() : 8;
-        memcpy(&a, t.data(), k);
-        memcpy(&b, t.data() + t.size() - k, k);
-        const uint64_t h = (a * 0x9E3779B97F4A7C15ull) ^ (b * 0xC2B2AE3D27D4EB4Full) ^ (t.size() * 0x165667B19E3779F9ull);
+        const uint64_t h = key_hash(t.size());
         lit_fp = h | 1;
         return lit_texts[(size_t)(h >> 56) & (LIT_TEXTS - 1)];
+    };
+    // the text behind a key that already matched: nothing for 16 bytes or fewer, one overlapping 16-byte compare up
+    // to 32 bytes (both sides hold n >= 16 bytes), libc beyond
+    auto same_rest = [](const char* a, const char* b, size_t n) {
+        if (n <= 16) return true;
+        if (n <= 32)
+            return _mm_movemask_epi8(_mm_cmpeq_epi8(_mm_loadu_si128((const __m128i*)(a + n - 16)),
+                                                    _mm_loadu_si128((const __m128i*)(b + n - 16)))) == 0xFFFF;
+        return memcmp(a + 16, b + 16, n - 16) == 0;
     };
     std::string lit;               // encoded literal of the current line (buffer reused)
     constexpr size_t LIT_SLOTS = 4096;
     const char* const text_end = text + len;
-    auto resolve = [&](std::string_view chrom) -> TokEntry& {
+    auto key_of = [&](std::string_view chrom) {
         const size_t n = chrom.size();
-        if (!genome->name_len_possible(n)) {
-            // no contig name has this length: a literal (barcode, UMI, adapter, poly(A) run); it stays out of the
-            // token cache, which the chromosome names keep
-            scratch_tok.contig = nullptr;
-            scratch_tok.lit_s = scratch_tok.lit_e = -1;
-            return scratch_tok;
-        }
-        // the token's first 16 bytes as two words: a cache entry is compared without a call into libc
-        uint64_t k0, k1;
         if (chrom.data() + 16 <= text_end) {
             memcpy(&k0, chrom.data(), 8);
             memcpy(&k1, chrom.data() + 8, 8);
@@ -562,12 +563,22 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
         } else if (n < 16) {
             k1 &= (1ull << (8 * (n - 8))) - 1;
         }
+    };
+    // needs key_of(chrom); a cache entry is compared through the key words, without a call into libc
+    auto resolve = [&](std::string_view chrom) -> TokEntry& {
+        const size_t n = chrom.size();
+        if (!genome->name_len_possible(n)) {
+            // no contig name has this length: a literal (barcode, UMI, adapter, poly(A) run); it stays out of the
+            // token cache, which the chromosome names keep
+            scratch_tok.contig = nullptr;
+            scratch_tok.lit_s = scratch_tok.lit_e = -1;
+            return scratch_tok;
+        }
         auto same = [&](const TokEntry& t) {
-            return t.valid && t.k0 == k0 && t.k1 == k1 && t.tok.size() == n &&
-                   (n <= 16 || memcmp(t.tok.data() + 16, chrom.data() + 16, n - 16) == 0);
+            return t.valid && t.k0 == k0 && t.k1 == k1 && t.tok.size() == n && same_rest(t.tok.data(), chrom.data(), n);
         };
         if (last_tok && same(*last_tok)) return *last_tok;
-        const uint64_t hsh = (k0 * 0x9E3779B97F4A7C15ull) ^ (k1 * 0xC2B2AE3D27D4EB4Full) ^ (n * 0x165667B19E3779F9ull);
+        const uint64_t hsh = key_hash(n);
         TokEntry& t = toks[(size_t)(hsh >> 58) & (NTOK - 1)];
         last_tok = &t;
         if (same(t)) return t;
@@ -678,6 +689,7 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
         if (!have) continue;  // intervals before the first header are parsed and dropped (py:213)
 
         std::string_view chrom(f[0], (size_t)(fend(0) - f[0]));
+        key_of(chrom);
         TokEntry& te = resolve(chrom);
         long long s, e;
         uint64_t src;
@@ -698,7 +710,7 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
             if (te.lit_s == s && te.lit_e == e && te.lit_epoch == lit_epoch) {
                 off = te.lit_off;
             } else if (!chrom.empty() && (lt = &lit_text_slot(chrom))->epoch == lit_epoch && lt->s == s && lt->e == e &&
-                       lt->text.size() == chrom.size() && memcmp(lt->text.data(), chrom.data(), chrom.size()) == 0) {
+                       lt->text.size() == chrom.size() && lt->k0 == k0 && lt->k1 == k1 && same_rest(lt->text.data(), chrom.data(), chrom.size())) {
                 off = lt->off;
             } else {
                 lit.resize((size_t)slen);
@@ -726,6 +738,8 @@ size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out,
                 if (lt) {
                     if (lt->seen == lit_fp) {   // (unique barcodes and UMIs never get here)
                         lt->text.assign(chrom);
+                        lt->k0 = k0;
+                        lt->k1 = k1;
                         lt->s = s;
                         lt->e = e;
                         lt->off = off;
