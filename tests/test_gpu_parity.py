@@ -376,6 +376,14 @@ def test_cli_gpus_flag_shards_in_one_process(world, tmp_path):
     p = subprocess.run([exe, "sequence", "-i", str(bad), "-o", str(out), "--gpus", "2"] + common, capture_output=True, text=True,
                        timeout=180, env={**os.environ, "TKSM_GPU_LIST": "0", "TKSM_SEQ_DEAL": "1", "TKSM_SEQ_DEAL_BYTES": "9000"})
     assert p.returncode == 1 and "Error" in p.stderr
+    # a regular file above the size a shard plan is made for is dealt as well
+    p = subprocess.run([exe, "sequence", "-i", str(src), "-o", str(out), "--perfect", str(perf), "--gpus", "2"] + common,
+                       capture_output=True, text=True, timeout=180,
+                       env={**os.environ, "TKSM_GPU_LIST": "0,0", "TKSM_SEQ_PLAN_MAX_BYTES": "1000", "TKSM_SEQ_DEAL_BYTES": "30000",
+                            "TKSM_SEQ_TRACE": "1"})
+    assert p.returncode == 0, p.stderr
+    assert "[trace] dealt" in p.stderr and "dealt 1 pieces" not in p.stderr
+    assert out.read_bytes() == want and perf.read_bytes() == want_perf
 
 
 @pytest.mark.gpu

@@ -1,6 +1,7 @@
 // Streaming runner: MDF file (or FIFO) -> batches -> kernels -> FASTQ/FASTA files.
 // Replaces the __main__ loop of the reference (py/sequence.py:347-376) and its output-file
 // handling (get_output_file, py/sequence.py:291-300).
+#include <atomic>
 #include <zlib.h>
 
 #include <algorithm>
@@ -267,7 +268,8 @@ void deal_stream(tksm_seq* const* handles, int n, const char* mdf_path, int whic
     std::vector<std::deque<std::shared_ptr<Piece>>> queue((size_t)n);   // per device: pieces waiting or running
     std::map<size_t, std::shared_ptr<Piece>> finished;                  // by piece index
     std::vector<int> pending((size_t)n, 0);
-    bool closed = false, failed = false;
+    bool closed = false;
+    std::atomic<bool> failed{false};   // read outside the lock by the reader loop and the workers
     std::string first_error;
 
     std::vector<std::thread> workers;
@@ -350,9 +352,10 @@ void deal_stream(tksm_seq* const* handles, int n, const char* mdf_path, int whic
     std::vector<char> buf((size_t)4 << 20);
     uint64_t ordinal = 0;
     bool eof = false;
+    size_t want = piece_bytes;   // grows while one record is larger than a piece
     while (!eof && !failed) {
         // fill up to a piece, cut at the last record boundary
-        while (carry.size() < piece_bytes) {
+        while (carry.size() < want) {
             const size_t got = fread(buf.data(), 1, buf.size(), in);
             if (got == 0) {
                 eof = true;
@@ -365,9 +368,13 @@ void deal_stream(tksm_seq* const* handles, int n, const char* mdf_path, int whic
             piece.swap(carry);
         } else {
             size_t cut = carry.rfind("\n+");
-            if (cut == std::string::npos || cut == 0) continue;   // one record larger than a piece: keep reading
+            if (cut == std::string::npos || cut == 0) {   // one record larger than a piece: read another piece's worth
+                want = carry.size() + piece_bytes;
+                continue;
+            }
             piece.assign(carry, 0, cut + 1);
             carry.erase(0, cut + 1);
+            want = piece_bytes;
         }
         if (piece.empty()) continue;
         std::vector<uint64_t> bb, ob;
@@ -395,6 +402,7 @@ void deal_stream(tksm_seq* const* handles, int n, const char* mdf_path, int whic
     cv.notify_all();
     drain(true);
     for (auto& t : workers) t.join();
+    if (getenv("TKSM_SEQ_TRACE")) fprintf(stderr, "[trace] dealt %zu pieces to %d devices\n", dealt, n);
     if (!first_error.empty()) throw std::runtime_error(first_error);
     if (stats) *stats = total;
 }
@@ -411,12 +419,18 @@ void run_files_multi(tksm_seq* const* handles, int n, const char* mdf_path, cons
 
     // A stream that cannot be read twice (FIFO, stdin; $TKSM_SEQ_DEAL=1 forces it for files) is not slurped: pieces
     // of complete records are dealt to the devices round-robin as they arrive, each with the global ordinal of its
-    // first read, and written back in order (at most two pieces per device in flight).
+    // first read, and written back in order (at most two pieces per device in flight).  So is a regular file above
+    // $TKSM_SEQ_PLAN_MAX_BYTES (2 GiB): the shard plan needs the whole text in memory and every shard but the first
+    // keeps its records there until its turn, which a 100 M-molecule input cannot afford; with that many pieces
+    // round-robin balances as well as the plan does.  $TKSM_SEQ_DEAL=0 keeps the plan.
     {
         struct stat sb{};
         const char* deal_env = getenv("TKSM_SEQ_DEAL");
-        const bool fifo = stat(mdf_path, &sb) == 0 && !S_ISREG(sb.st_mode);
-        if ((fifo && !(deal_env && atoi(deal_env) == 0)) || (deal_env && atoi(deal_env) == 1)) {
+        const bool known = stat(mdf_path, &sb) == 0;
+        const bool fifo = known && !S_ISREG(sb.st_mode);
+        const uint64_t plan_max = getenv("TKSM_SEQ_PLAN_MAX_BYTES") ? (uint64_t)atoll(getenv("TKSM_SEQ_PLAN_MAX_BYTES")) : (2ull << 30);
+        const bool big = known && S_ISREG(sb.st_mode) && (uint64_t)sb.st_size > plan_max;
+        if (((fifo || big) && !(deal_env && atoi(deal_env) == 0)) || (deal_env && atoi(deal_env) == 1)) {
             FileSinks direct;
             direct.s[0] = badread_path ? &bad : nullptr;
             direct.s[1] = perfect_path ? &perf : nullptr;
