@@ -74,6 +74,81 @@ def test_genome_store_keeps_every_byte(Sequencer):
         s.add_reference_text(">a\nAC\n\nGT\n")     # IndexError in the reference (py/sequence.py:177)
 
 
+def test_reference_files_plain_gz_and_later_files_override(Sequencer, tmp_path):
+    """py/sequence.py:188-194: every -r file is read (gzip by its magic bytes, py/tksm_badread.py:259-290) and a name
+    given by a later file replaces the earlier one (dict.update).  A plain file is packed from its mapping, a .gz one
+    from memory; an empty file gives the reference's '' contig and a missing one an error."""
+    import gzip
+    from tksm_b200.sequence import SeqError
+    rng = np.random.default_rng(9)
+    body = lambda n: "".join(rng.choice(list("ACGTNacgt"), size=n))
+    a = f">chr1 first\n{body(5000)}\n>chr2\n{body(777)}\n"
+    b = f">chr2\n{body(100)}\n>chr3\n{body(64)}\n"
+    (tmp_path / "a.fa").write_text(a)
+    with gzip.open(tmp_path / "b.fa.gz", "wt") as f:
+        f.write(b)
+    (tmp_path / "c.fasta").write_text(b)          # the same records, plain
+    (tmp_path / "empty.fa").write_text("")
+    refs = so.load_fasta(a)
+    so.load_fasta(b, refs)
+    for second in ("b.fa.gz", "c.fasta"):
+        s = Sequencer(host_only=True)
+        s.load_references([str(tmp_path / "a.fa"), str(tmp_path / second), str(tmp_path / "empty.fa")])
+        for name, sq in refs.items():
+            assert s.fetch_reference(name, 0, len(sq)) == sq.upper().encode(), (second, name)
+    with pytest.raises(SeqError):
+        Sequencer(host_only=True).load_references([str(tmp_path / "missing.fa")])
+
+
+@pytest.mark.parametrize("width,eol", [(60, "\n"), (70, "\r\n"), (17, "\n"), (61, "\r"), (0, "\n")])
+def test_genome_store_packs_lines_where_they_lie(Sequencer, width, eol):
+    """csrc/host.cpp: GenomeStore packs sequence lines 16 and 8 bases at a time into the 2-bit words, whatever the line
+    width leaves misaligned, and keeps every byte outside ACGT in runs (stretches of one byte 16 at a time).  Contigs
+    of 1 to 200 000 bases with N stretches across the 16 / 32 byte boundaries, mixed-case stretches, lower case and
+    IUPAC codes, a contig name given twice (the later record wins, py/sequence.py:184): every byte the oracle's
+    load_fasta holds comes back, whole contigs and ranges."""
+    import random
+    rng = random.Random(width * 7 + len(eol))
+
+    def seq(n, pn, plow, piupac):
+        out, i = [], 0
+        while i < n:
+            if rng.random() < pn:
+                k = rng.choice([1, 2, 15, 16, 17, 31, 32, 33, 100, 1000])
+                out.append("".join(rng.choice("Nn") for _ in range(k)) if rng.random() < 0.2 else rng.choice("NnNNRY-*") * k)
+            else:
+                k = rng.choice([1, 3, 16, 40, 200, 1000])
+                piece = "".join(rng.choice("ACGT" if rng.random() > plow else "acgtACGT") for _ in range(k))
+                if rng.random() < piupac:
+                    piece = piece[:k // 2] + rng.choice("RYKMSWBDHVU.") + piece[k // 2 + 1:]
+                out.append(piece)
+            i += k
+        return "".join(out)[:n]
+
+    contigs = [("chr1 some words", seq(200000, 0.02, 0.3, 0.05)), ("chr2", seq(70001, 0.05, 0.5, 0.1)), ("c63", seq(63, 0, 0, 0)),
+               ("c64", seq(64, 0, 0, 0)), ("c65", seq(65, 0.1, 0.5, 0)), ("c1", seq(1, 0, 0, 0)), ("chr2", seq(999, 0.3, 0.5, 0.2))]
+    lines = []
+    for name, sq in contigs:
+        lines.append(">" + name)
+        lines.extend([sq] if width == 0 else [sq[i:i + width] for i in range(0, len(sq), width)])
+    fasta = eol.join(lines) + (eol if width != 17 else "")
+    refs = so.load_fasta(fasta)
+    assert len(refs["chr2"]) == 999
+    s = Sequencer(host_only=True)
+    s.add_reference_text(fasta)
+    for name, sq in refs.items():
+        want = sq.upper().encode("latin-1")
+        assert s.fetch_reference(name, 0, len(sq)) == want, name
+        for _ in range(50):
+            a = rng.randrange(len(sq))
+            b = min(len(sq), a + rng.choice([1, 15, 16, 17, 64, 1000]))
+            assert s.fetch_reference(name, a, b - a) == want[a:b], (name, a, b)
+    # a second text on the same handle (a later -r file): earlier contigs stay, names given again are replaced
+    s.add_reference_text(">chr2\nACGTN\n>other\nGGGG" + "N" * 40 + "\n")
+    assert s.fetch_reference("chr2", 0, 5) == b"ACGTN" and s.fetch_reference("other", 0, 44) == b"GGGG" + b"N" * 40
+    assert s.fetch_reference("c65", 0, 65) == refs["c65"].upper().encode("latin-1")
+
+
 @needs_models
 @pytest.mark.parametrize("model", ["nanopore2020", "nanopore2018", "pacbio2016"])
 def test_packed_error_table_matches_oracle_distribution(Sequencer, model):

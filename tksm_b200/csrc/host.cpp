@@ -2,6 +2,10 @@
 #include "host.hpp"
 
 #include <emmintrin.h>
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
 
 #include <algorithm>
 #include <cstring>
@@ -14,53 +18,155 @@ namespace tk {
 
 // ------------------------------------------------------------------ genome
 
-void GenomeStore::add_contig(const std::string& name, const char* seq, size_t len) {
-    // every contig starts on a 64-base boundary so 128-bit loads of a contig prefix stay aligned
-    n_bases = (n_bases + 63) & ~uint64_t(63);
-    const uint64_t off = n_bases;
-    words.resize((size_t)((off + len + 63) / 64) * 4 + 4, 0);
-    uint64_t run_start = 0;
-    uint32_t run_len = 0;
-    uint8_t run_chr = 0;
+namespace {
+
+// 8 bytes of A/C/G/T (either case) -> 16 bits, base j at bits 2j: A=0 C=1 G=2 T=3 is ((c >> 1) ^ (c >> 2)) & 3
+inline uint32_t pack8(uint64_t c) {
+    uint64_t x = ((c >> 1) ^ (c >> 2)) & 0x0303030303030303ull;
+    x = (x | (x >> 6)) & 0x000F000F000F000Full;
+    x = (x | (x >> 12)) & 0x000000FF000000FFull;
+    return (uint32_t)((x | (x >> 24)) & 0xFFFFu);
+}
+
+}  // namespace
+
+// Appends `len` bytes of sequence at global base n_bases.  Blocks of 16 bytes that are all A/C/G/T (either case) are
+// packed with three shift-and-mask steps per 8 bases and OR-ed into the (zeroed) words through one unaligned 64-bit
+// access; any other block goes byte by byte, its bytes outside ACGT extending or starting exception runs.  `run` is
+// the open run of the contig (run_len == 0: none).
+void GenomeStore::append_bases(const char* seq, size_t len, ExcRun& run) {
     auto flush = [&]() {
-        if (run_len) {
-            exc_start.push_back(run_start);
-            exc_len.push_back(run_len);
-            exc_chr.push_back(run_chr);
-            run_len = 0;
+        if (run.len) {
+            exc_start.push_back(run.start);
+            exc_len.push_back(run.len);
+            exc_chr.push_back(run.chr);
+            run.len = 0;
         }
     };
-    for (size_t i = 0; i < len; i++) {
-        uint8_t c = ascii_upper((uint8_t)seq[i]);
-        uint8_t code = frag_code(c);
-        uint64_t g = off + i;
-        if (code < 4) {
-            words[(size_t)(g >> 4)] |= (uint32_t)code << (2 * (g & 15));
-            flush();
-        } else {
-            if (run_len && run_chr == c && run_start + run_len == g && run_len < 0xFFFFFFFFu) {
-                run_len++;
+    {
+        const size_t need = (size_t)((n_bases + len + 63) / 64) * 4 + 4;
+        if (words.size() < need) {
+            if (words.capacity() < need) words.reserve(std::max(need, words.capacity() + words.capacity() / 2));
+            words.resize(need, 0);
+        }
+    }
+    uint32_t* const W = words.data();
+    uint64_t g = n_bases;
+    size_t i = 0;
+    const __m128i lower = _mm_set1_epi8(0x20), va = _mm_set1_epi8('a'), vc = _mm_set1_epi8('c'), vg = _mm_set1_epi8('g'),
+                  vt = _mm_set1_epi8('t');
+    while (i < len) {
+        if (len - i >= 16) {
+            const __m128i v = _mm_loadu_si128((const __m128i*)(seq + i));
+            const __m128i lo = _mm_or_si128(v, lower);
+            const __m128i ok = _mm_or_si128(_mm_or_si128(_mm_cmpeq_epi8(lo, va), _mm_cmpeq_epi8(lo, vc)),
+                                            _mm_or_si128(_mm_cmpeq_epi8(lo, vg), _mm_cmpeq_epi8(lo, vt)));
+            if (_mm_movemask_epi8(ok) == 0xFFFF) {
+                flush();
+                uint64_t c0, c1;
+                memcpy(&c0, seq + i, 8);
+                memcpy(&c1, seq + i + 8, 8);
+                const uint64_t grp = (uint64_t)(pack8(c0) | (pack8(c1) << 16)) << (2 * (g & 15));
+                uint64_t w;
+                memcpy(&w, W + (g >> 4), 8);
+                w |= grp;
+                memcpy(W + (g >> 4), &w, 8);
+                g += 16;
+                i += 16;
+                continue;
+            }
+            if (run.len && run.one_raw && run.start + run.len == g && run.len < 0xFFFFFFE0u &&
+                _mm_movemask_epi8(_mm_cmpeq_epi8(v, _mm_set1_epi8((char)run.raw))) == 0xFFFF) {
+                run.len += 16;   // inside a run of one byte (the N stretches of an assembly)
+                g += 16;
+                i += 16;
+                continue;
+            }
+        }
+        if (len - i >= 8) {   // the same for 8 bytes (what a 60- or 70-column line leaves after its 16-byte blocks)
+            const __m128i v = _mm_loadl_epi64((const __m128i*)(seq + i));
+            const __m128i lo = _mm_or_si128(v, lower);
+            const __m128i ok = _mm_or_si128(_mm_or_si128(_mm_cmpeq_epi8(lo, va), _mm_cmpeq_epi8(lo, vc)),
+                                            _mm_or_si128(_mm_cmpeq_epi8(lo, vg), _mm_cmpeq_epi8(lo, vt)));
+            if ((_mm_movemask_epi8(ok) & 0xFF) == 0xFF) {
+                flush();
+                uint64_t c0;
+                memcpy(&c0, seq + i, 8);
+                const uint64_t grp = (uint64_t)pack8(c0) << (2 * (g & 15));
+                uint64_t w;
+                memcpy(&w, W + (g >> 4), 8);
+                w |= grp;
+                memcpy(W + (g >> 4), &w, 8);
+                g += 8;
+                i += 8;
+                continue;
+            }
+        }
+        const size_t stop = std::min(len, i + 8);
+        for (; i < stop; i++, g++) {
+            const uint8_t raw = (uint8_t)seq[i];
+            const uint8_t c = ascii_upper(raw);
+            const uint8_t code = frag_code(c);
+            if (code < 4) {
+                W[(size_t)(g >> 4)] |= (uint32_t)code << (2 * (g & 15));
+                flush();
+            } else if (run.len && run.chr == c && run.start + run.len == g && run.len < 0xFFFFFFFFu) {
+                run.len++;
+                if (run.raw != raw) run.one_raw = false;   // mixed case: the 16-byte shortcut compares raw bytes
             } else {
                 flush();
-                run_start = g;
-                run_len = 1;
-                run_chr = c;
+                run.start = g;
+                run.len = 1;
+                run.chr = c;
+                run.raw = raw;
+                run.one_raw = true;
             }
         }
     }
-    flush();
-    n_bases = off + len;
-    contigs[name] = Contig{off, (uint64_t)len};  // later files override earlier names (dict.update)
+    n_bases = g;
+}
+
+void GenomeStore::begin_contig() {
+    // every contig starts on a 64-base boundary so 128-bit loads of a contig prefix stay aligned
+    n_bases = (n_bases + 63) & ~uint64_t(63);
+}
+
+void GenomeStore::end_contig(const std::string& name, uint64_t off, ExcRun& run) {
+    if (run.len) {
+        exc_start.push_back(run.start);
+        exc_len.push_back(run.len);
+        exc_chr.push_back(run.chr);
+        run.len = 0;
+    }
+    const uint64_t len = n_bases - off;
+    words.resize((size_t)((off + len + 63) / 64) * 4 + 4, 0);
+    contigs[name] = Contig{off, len};  // later files override earlier names (dict.update)
     note_name(name.size());
+}
+
+void GenomeStore::add_contig(const std::string& name, const char* seq, size_t len) {
+    begin_contig();
+    const uint64_t off = n_bases;
+    ExcRun run;
+    append_bases(seq, len, run);
+    end_contig(name, off, run);
 }
 
 void GenomeStore::load_fasta_text(const char* text, size_t len) {
     // py/sequence.py:168-186 in text mode: universal newlines, name = header up to the first space,
     // a header that follows a header without sequence replaces it, an empty line raises.
-    std::string name, seq;
+    // Sequence lines are packed where they lie (no copy of the contig); the text bounds the bases it can hold.
+    words.reserve(words.size() + len / 16 + 64);
+    std::string name;
     bool have_seq_lines = false;
     size_t pos = 0;
-    auto emit = [&]() { add_contig(name, seq.data(), seq.size()); };
+    // what a line that raises leaves behind: the contigs completed before it, nothing of the one it is in
+    uint64_t keep_bases = n_bases;
+    size_t keep_words = words.size(), keep_exc = exc_start.size();
+    begin_contig();
+    uint64_t off = n_bases;
+    ExcRun run;
+    try {
     while (pos < len) {
         const char* p = text + pos;
         const char* nl = (const char*)memchr(p, '\n', len - pos);
@@ -77,24 +183,57 @@ void GenomeStore::load_fasta_text(const char* text, size_t len) {
             std::string_view hdr(text + pos + 1, eol - pos - 1);
             size_t sp = hdr.find(' ');
             std::string nm(hdr.substr(0, sp));
-            if (!have_seq_lines) {
-                name = nm;
-            } else {
-                emit();
-                seq.clear();
+            if (have_seq_lines) {
+                end_contig(name, off, run);
+                keep_bases = n_bases;
+                keep_words = words.size();
+                keep_exc = exc_start.size();
+                begin_contig();
+                off = n_bases;
                 have_seq_lines = false;
-                name = nm;
             }
+            name = nm;
         } else {
-            seq.append(text + pos, eol - pos);
+            append_bases(text + pos, eol - pos, run);
             have_seq_lines = true;
         }
         pos = next;
     }
-    emit();
+    } catch (...) {
+        n_bases = keep_bases;
+        words.resize(keep_words);
+        exc_start.resize(keep_exc);
+        exc_len.resize(keep_exc);
+        exc_chr.resize(keep_exc);
+        throw;
+    }
+    end_contig(name, off, run);
 }
 
 void GenomeStore::load_fasta(const std::string& path) {
+    // a plain regular file is packed straight from its mapping (no copy of a 3 GB reference); anything else
+    // (.gz, a pipe) is read into memory first
+    {
+        const int fd = open(path.c_str(), O_RDONLY);
+        if (fd >= 0) {
+            struct stat sb{};
+            unsigned char magic[2] = {0, 0};
+            const bool regular = fstat(fd, &sb) == 0 && S_ISREG(sb.st_mode) && sb.st_size > 0;
+            const bool gz = regular && pread(fd, magic, 2, 0) == 2 && magic[0] == 0x1f && magic[1] == 0x8b;
+            void* map = regular && !gz ? mmap(nullptr, (size_t)sb.st_size, PROT_READ, MAP_PRIVATE, fd, 0) : MAP_FAILED;
+            close(fd);
+            if (map != MAP_FAILED) {
+                madvise(map, (size_t)sb.st_size, MADV_SEQUENTIAL);
+                struct Unmap {
+                    void* p;
+                    size_t n;
+                    ~Unmap() { munmap(p, n); }
+                } guard{map, (size_t)sb.st_size};
+                load_fasta_text((const char*)map, (size_t)sb.st_size);
+                return;
+            }
+        }
+    }
     std::string text = read_text_maybe_gz(path);
     load_fasta_text(text.data(), text.size());
 }

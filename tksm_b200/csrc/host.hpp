@@ -42,6 +42,17 @@ struct GenomeStore {
     void index_exceptions();
 
     void add_contig(const std::string& name, const char* seq, size_t len);
+    // streaming form of add_contig (load_fasta_text packs the sequence lines where they lie)
+    struct ExcRun {
+        uint64_t start = 0;
+        uint32_t len = 0;
+        uint8_t chr = 0;   // the run's byte, upper-cased
+        uint8_t raw = 0;   // its first byte as written
+        bool one_raw = false;   // every byte of the run is `raw` (no mixed case)
+    };
+    void begin_contig();
+    void append_bases(const char* seq, size_t len, ExcRun& run);
+    void end_contig(const std::string& name, uint64_t off, ExcRun& run);
     void load_fasta(const std::string& path);              // plain or .gz
     void load_fasta_text(const char* text, size_t len);
     bool overlaps_exception(uint64_t start, uint64_t len) const;

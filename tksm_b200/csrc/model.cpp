@@ -1,6 +1,7 @@
 // Host-side model loading and packing (see model.hpp for the reference mapping).
 #include "model.hpp"
 
+#include <sys/stat.h>
 #include <dirent.h>
 #include <zlib.h>
 
@@ -14,6 +15,38 @@ namespace tk {
 std::string read_text_maybe_gz(const std::string& path) {
     // gzopen reads plain files transparently, which mirrors get_open_func's magic-byte
     // sniffing (py/tksm_badread.py:259-290).
+    // A plain regular file (a reference FASTA of gigabytes) is read straight into a string of its size.
+    {
+        struct stat sb{};
+        FILE* plain = fopen(path.c_str(), "rb");
+        if (!plain) throw std::runtime_error("cannot open " + path);
+        unsigned char magic[2] = {0, 0};
+        const size_t got = fread(magic, 1, 2, plain);
+        const bool gz = got == 2 && magic[0] == 0x1f && magic[1] == 0x8b;
+        if (!gz && fstat(fileno(plain), &sb) == 0 && S_ISREG(sb.st_mode)) {
+            std::string out((size_t)sb.st_size, '\0');
+            rewind(plain);
+            size_t have = 0;
+            while (have < out.size()) {
+                const size_t n = fread(out.data() + have, 1, out.size() - have, plain);
+                if (n == 0) break;
+                have += n;
+            }
+            const bool bad = ferror(plain) != 0;
+            // a file that grew meanwhile: the rest
+            char extra[4096];
+            size_t n;
+            while (!bad && have == out.size() && (n = fread(extra, 1, sizeof extra, plain)) > 0) {
+                out.append(extra, n);
+                have += n;
+            }
+            fclose(plain);
+            if (bad) throw std::runtime_error("read error in " + path);
+            out.resize(have);
+            return out;
+        }
+        fclose(plain);
+    }
     gzFile f = gzopen(path.c_str(), "rb");
     if (!f) throw std::runtime_error("cannot open " + path);
     std::string out;
