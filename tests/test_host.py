@@ -74,6 +74,44 @@ def test_genome_store_keeps_every_byte(Sequencer):
         s.add_reference_text(">a\nAC\n\nGT\n")     # IndexError in the reference (py/sequence.py:177)
 
 
+def test_large_reference_packed_by_several_threads(Sequencer):
+    """Above 8 MiB of text the contigs are packed side by side by host threads (no two contigs share a word).  Contig
+    lengths around multiples of 64 put a contig's last word next to its neighbour's first; a line that raises in the
+    middle leaves the contigs before it and none after it."""
+    from tksm_b200.sequence import SeqError
+    rng = np.random.default_rng(21)
+    alphabet = np.frombuffer(b"ACGTacgtNn", np.uint8)
+    probs = np.array([0.22] * 4 + [0.02] * 4 + [0.03, 0.01])
+    probs = probs / probs.sum()
+    lengths = [64, 128, 6400, 63, 65, 1, 16, 640000, 1_000_000, 64000] * 6
+    parts = []
+    for i, n in enumerate(lengths):
+        sq = rng.choice(alphabet, size=n, p=probs).tobytes().decode()
+        if n >= 6400:
+            a = int(rng.integers(0, n - 3000))
+            sq = sq[:a] + "N" * 2500 + sq[a + 2500:]
+        parts.append(f">s{i} x\n" + "\n".join(sq[j:j + 64] for j in range(0, n, 64)) + "\n")
+    fasta = "".join(parts)
+    assert len(fasta) > (8 << 20)
+    refs = so.load_fasta(fasta)
+    s = Sequencer(host_only=True)
+    s.add_reference_text(fasta)
+    for name, sq in refs.items():
+        assert s.fetch_reference(name, 0, len(sq)) == sq.upper().encode(), name
+    cut = fasta.index(">s37 ")                                  # 640 000 bases
+    mid = fasta.index("\n", cut) + 1
+    broken = fasta[:mid + 650] + "\n" + fasta[mid + 650:]       # an empty line after ten lines of s37
+    s2 = Sequencer(host_only=True)
+    with pytest.raises(SeqError, match="empty line"):
+        s2.add_reference_text(broken)
+    assert s2.fetch_reference("s36", 0, len(refs["s36"])) == refs["s36"].upper().encode()
+    for gone in ("s37", "s38", "s59"):
+        with pytest.raises(SeqError):
+            s2.fetch_reference(gone, 0, 1)
+    s2.add_reference_text(">again\nACGTNACGT\n")               # the handle keeps working
+    assert s2.fetch_reference("again", 0, 9) == b"ACGTNACGT" and s2.fetch_reference("s7", 0, 16) == refs["s7"][:16].upper().encode()
+
+
 def test_reference_files_plain_gz_and_later_files_override(Sequencer, tmp_path):
     """py/sequence.py:188-194: every -r file is read (gzip by its magic bytes, py/tksm_badread.py:259-290) and a name
     given by a later file replaces the earlier one (dict.update).  A plain file is packed from its mapping, a .gz one

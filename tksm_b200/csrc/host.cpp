@@ -8,7 +8,9 @@
 #include <unistd.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cstring>
+#include <thread>
 #include <stdexcept>
 #include <string_view>
 
@@ -34,24 +36,25 @@ inline uint32_t pack8(uint64_t c) {
 // packed with three shift-and-mask steps per 8 bases and OR-ed into the (zeroed) words through one unaligned 64-bit
 // access; any other block goes byte by byte, its bytes outside ACGT extending or starting exception runs.  `run` is
 // the open run of the contig (run_len == 0: none).
-void GenomeStore::append_bases(const char* seq, size_t len, ExcRun& run) {
+namespace {
+
+struct ExcOut {
+    std::vector<uint64_t>* start;
+    std::vector<uint32_t>* len;
+    std::vector<uint8_t>* chr;
+};
+
+// `W`: the words (large enough for [g, g + len) plus two words), `g`: global base of seq[0], advanced.
+void pack_bases(uint32_t* const W, uint64_t& g_io, const char* seq, size_t len, GenomeStore::ExcRun& run, const ExcOut& exc) {
     auto flush = [&]() {
         if (run.len) {
-            exc_start.push_back(run.start);
-            exc_len.push_back(run.len);
-            exc_chr.push_back(run.chr);
+            exc.start->push_back(run.start);
+            exc.len->push_back(run.len);
+            exc.chr->push_back(run.chr);
             run.len = 0;
         }
     };
-    {
-        const size_t need = (size_t)((n_bases + len + 63) / 64) * 4 + 4;
-        if (words.size() < need) {
-            if (words.capacity() < need) words.reserve(std::max(need, words.capacity() + words.capacity() / 2));
-            words.resize(need, 0);
-        }
-    }
-    uint32_t* const W = words.data();
-    uint64_t g = n_bases;
+    uint64_t g = g_io;
     size_t i = 0;
     const __m128i lower = _mm_set1_epi8(0x20), va = _mm_set1_epi8('a'), vc = _mm_set1_epi8('c'), vg = _mm_set1_epi8('g'),
                   vt = _mm_set1_epi8('t');
@@ -66,11 +69,18 @@ void GenomeStore::append_bases(const char* seq, size_t len, ExcRun& run) {
                 uint64_t c0, c1;
                 memcpy(&c0, seq + i, 8);
                 memcpy(&c1, seq + i + 8, 8);
-                const uint64_t grp = (uint64_t)(pack8(c0) | (pack8(c1) << 16)) << (2 * (g & 15));
-                uint64_t w;
-                memcpy(&w, W + (g >> 4), 8);
-                w |= grp;
-                memcpy(W + (g >> 4), &w, 8);
+                // (the second word is touched only when bases of this block lie in it: the word after a contig's
+                // last one may belong to the next contig, which another thread is packing)
+                const uint32_t grp32 = pack8(c0) | (pack8(c1) << 16);
+                const unsigned sh = 2 * (unsigned)(g & 15);
+                if (sh == 0) {
+                    W[g >> 4] |= grp32;
+                } else {
+                    uint64_t w;
+                    memcpy(&w, W + (g >> 4), 8);
+                    w |= (uint64_t)grp32 << sh;
+                    memcpy(W + (g >> 4), &w, 8);
+                }
                 g += 16;
                 i += 16;
                 continue;
@@ -92,11 +102,15 @@ void GenomeStore::append_bases(const char* seq, size_t len, ExcRun& run) {
                 flush();
                 uint64_t c0;
                 memcpy(&c0, seq + i, 8);
-                const uint64_t grp = (uint64_t)pack8(c0) << (2 * (g & 15));
-                uint64_t w;
-                memcpy(&w, W + (g >> 4), 8);
-                w |= grp;
-                memcpy(W + (g >> 4), &w, 8);
+                const unsigned sh = 2 * (unsigned)(g & 15);
+                if (sh <= 16) {
+                    W[g >> 4] |= pack8(c0) << sh;
+                } else {
+                    uint64_t w;
+                    memcpy(&w, W + (g >> 4), 8);
+                    w |= (uint64_t)pack8(c0) << sh;
+                    memcpy(W + (g >> 4), &w, 8);
+                }
                 g += 8;
                 i += 8;
                 continue;
@@ -123,7 +137,18 @@ void GenomeStore::append_bases(const char* seq, size_t len, ExcRun& run) {
             }
         }
     }
-    n_bases = g;
+    g_io = g;
+}
+
+}  // namespace
+
+void GenomeStore::append_bases(const char* seq, size_t len, ExcRun& run) {
+    const size_t need = (size_t)((n_bases + len + 63) / 64) * 4 + 4;
+    if (words.size() < need) {
+        if (words.capacity() < need) words.reserve(std::max(need, words.capacity() + words.capacity() / 2));
+        words.resize(need, 0);
+    }
+    pack_bases(words.data(), n_bases, seq, len, run, ExcOut{&exc_start, &exc_len, &exc_chr});
 }
 
 void GenomeStore::begin_contig() {
@@ -152,62 +177,177 @@ void GenomeStore::add_contig(const std::string& name, const char* seq, size_t le
     end_contig(name, off, run);
 }
 
+namespace {
+
+// number of '\n' and '\r' bytes in [p, p + n)
+size_t count_line_ends(const char* p, size_t n) {
+    size_t c = 0, i = 0;
+    const __m128i vn = _mm_set1_epi8('\n'), vr = _mm_set1_epi8('\r');
+    for (; i + 16 <= n; i += 16) {
+        const __m128i v = _mm_loadu_si128((const __m128i*)(p + i));
+        c += (size_t)__builtin_popcount((unsigned)_mm_movemask_epi8(_mm_or_si128(_mm_cmpeq_epi8(v, vn), _mm_cmpeq_epi8(v, vr))));
+    }
+    for (; i < n; i++) c += p[i] == '\n' || p[i] == '\r';
+    return c;
+}
+
+// end of the line that starts at `pos` (universal newlines): `eol` = its last byte + 1, returns the next line's start
+size_t line_end(const char* text, size_t len, size_t pos, size_t& eol) {
+    const char* nl = (const char*)memchr(text + pos, '\n', len - pos);
+    eol = nl ? (size_t)(nl - text) : len;
+    size_t next = nl ? eol + 1 : len;
+    const char* cr = (const char*)memchr(text + pos, '\r', eol - pos);
+    if (cr) {
+        const size_t r = (size_t)(cr - text);
+        next = (r + 1 == eol && nl) ? eol + 1 : r + 1;
+        eol = r;
+    }
+    return next;
+}
+
+}  // namespace
+
 void GenomeStore::load_fasta_text(const char* text, size_t len) {
     // py/sequence.py:168-186 in text mode: universal newlines, name = header up to the first space,
     // a header that follows a header without sequence replaces it, an empty line raises.
-    // Sequence lines are packed where they lie (no copy of the contig); the text bounds the bases it can hold.
-    words.reserve(words.size() + len / 16 + 64);
-    std::string name;
-    bool have_seq_lines = false;
-    size_t pos = 0;
-    // what a line that raises leaves behind: the contigs completed before it, nothing of the one it is in
-    uint64_t keep_bases = n_bases;
-    size_t keep_words = words.size(), keep_exc = exc_start.size();
-    begin_contig();
-    uint64_t off = n_bases;
-    ExcRun run;
-    try {
-    while (pos < len) {
-        const char* p = text + pos;
-        const char* nl = (const char*)memchr(p, '\n', len - pos);
-        size_t eol = nl ? (size_t)(nl - text) : len;
-        size_t next = nl ? eol + 1 : len;
-        const char* cr = (const char*)memchr(p, '\r', eol - pos);
-        if (cr) {
-            size_t r = (size_t)(cr - text);
-            next = (r + 1 == eol && nl) ? eol + 1 : r + 1;
-            eol = r;
-        }
-        if (eol == pos) throw std::runtime_error("IndexError: empty line in FASTA (py/sequence.py:177)");
-        if (text[pos] == '>') {
-            std::string_view hdr(text + pos + 1, eol - pos - 1);
-            size_t sp = hdr.find(' ');
-            std::string nm(hdr.substr(0, sp));
-            if (have_seq_lines) {
-                end_contig(name, off, run);
-                keep_bases = n_bases;
-                keep_words = words.size();
-                keep_exc = exc_start.size();
-                begin_contig();
-                off = n_bases;
-                have_seq_lines = false;
+    //
+    // Every contig starts on a 64-base boundary, so no two contigs share a word: the records are found by their '>'
+    // lines (memchr; a '>' inside a line is sequence), their bases counted (bytes that end no line), their places
+    // fixed in text order, and then packed side by side by host threads, each record where its lines lie (no copy).
+    // Exception runs never cross a contig and are appended in text order.  A record that raises leaves the records
+    // before it in place and nothing of itself or of the later ones.
+    struct Rec {
+        std::string name;
+        size_t body = 0, body_end = 0;   // its sequence lines (body == body_end: none)
+        uint64_t bases = 0, off = 0;
+        std::vector<uint64_t> exc_start;
+        std::vector<uint32_t> exc_len;
+        std::vector<uint8_t> exc_chr;
+        std::string error;
+    };
+    std::vector<Rec> recs;
+    {
+        std::string name;              // sequence before any header belongs to the contig ""
+        bool pending = true;           // no sequence since the last header (or since the start)
+        auto header_at = [&](size_t p) { return text[p] == '>' && (p == 0 || text[p - 1] == '\n' || text[p - 1] == '\r'); };
+        size_t pos = 0;
+        while (pos < len) {
+            if (header_at(pos)) {
+                size_t eol;
+                const size_t next = line_end(text, len, pos, eol);
+                std::string_view hdr(text + pos + 1, eol - pos - 1);
+                name = std::string(hdr.substr(0, hdr.find(' ')));
+                pending = true;
+                pos = next;
+                continue;
             }
-            name = nm;
-        } else {
-            append_bases(text + pos, eol - pos, run);
-            have_seq_lines = true;
+            // sequence lines up to the next header line
+            size_t q = pos;
+            for (;;) {
+                const char* gt = (const char*)memchr(text + q, '>', len - q);
+                if (!gt) {
+                    q = len;
+                    break;
+                }
+                q = (size_t)(gt - text);
+                if (header_at(q)) break;
+                q++;
+            }
+            Rec r;
+            r.name = name;
+            r.body = pos;
+            r.body_end = q;
+            recs.push_back(std::move(r));
+            pending = false;
+            pos = q;
         }
-        pos = next;
+        if (pending) {   // the reference's final `refs[name] = "".join(chunks)` with no chunks: an empty contig
+            Rec r;
+            r.name = name;
+            r.body = r.body_end = len;
+            recs.push_back(std::move(r));
+        }
     }
-    } catch (...) {
-        n_bases = keep_bases;
-        words.resize(keep_words);
-        exc_start.resize(keep_exc);
-        exc_len.resize(keep_exc);
-        exc_chr.resize(keep_exc);
-        throw;
+    // bases and places
+    const size_t n_threads_max = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+    const size_t n_threads = len < ((size_t)8 << 20) ? 1 : std::min(n_threads_max, recs.size());
+    auto for_each_rec = [&](auto&& fn) {
+        if (n_threads <= 1) {
+            for (size_t i = 0; i < recs.size(); i++) fn(i);
+            return;
+        }
+        // largest first, so that the longest chromosome does not start last
+        std::vector<size_t> order(recs.size());
+        for (size_t i = 0; i < order.size(); i++) order[i] = i;
+        std::sort(order.begin(), order.end(), [&](size_t a, size_t b) {
+            return recs[a].body_end - recs[a].body > recs[b].body_end - recs[b].body;
+        });
+        std::atomic<size_t> next{0};
+        std::vector<std::thread> th;
+        for (size_t t = 0; t < n_threads; t++)
+            th.emplace_back([&]() {
+                for (size_t k; (k = next.fetch_add(1)) < order.size();) fn(order[k]);
+            });
+        for (auto& t : th) t.join();
+    };
+    for_each_rec([&](size_t i) {
+        Rec& r = recs[i];
+        r.bases = (uint64_t)(r.body_end - r.body) - count_line_ends(text + r.body, r.body_end - r.body);
+    });
+    const uint64_t keep_bases = n_bases;
+    const size_t keep_words = words.size();
+    uint64_t at = n_bases;
+    for (Rec& r : recs) {
+        at = (at + 63) & ~uint64_t(63);   // every contig starts on a 64-base boundary so 128-bit loads of a contig prefix stay aligned
+        r.off = at;
+        at += r.bases;
     }
-    end_contig(name, off, run);
+    const Rec& last = recs.back();
+    words.resize(std::max(words.size(), (size_t)((last.off + last.bases + 63) / 64) * 4 + 4), 0);
+    uint32_t* const W = words.data();
+    for_each_rec([&](size_t i) {
+        Rec& r = recs[i];
+        ExcRun run;
+        uint64_t g = r.off;
+        const ExcOut exc{&r.exc_start, &r.exc_len, &r.exc_chr};
+        size_t pos = r.body;
+        while (pos < r.body_end) {
+            size_t eol;
+            const size_t next = line_end(text, r.body_end, pos, eol);
+            if (eol == pos) {
+                r.error = "IndexError: empty line in FASTA (py/sequence.py:177)";
+                return;
+            }
+            pack_bases(W, g, text + pos, eol - pos, run, exc);
+            pos = next;
+        }
+        if (run.len) {
+            r.exc_start.push_back(run.start);
+            r.exc_len.push_back(run.len);
+            r.exc_chr.push_back(run.chr);
+        }
+        if (g != r.off + r.bases) r.error = "internal error: FASTA base count";
+    });
+    // in text order
+    for (size_t i = 0; i < recs.size(); i++) {
+        Rec& r = recs[i];
+        if (!r.error.empty()) {
+            // nothing of this record or the later ones: their words go back to zero
+            const uint64_t end = i ? recs[i - 1].off + recs[i - 1].bases : keep_bases;
+            const size_t good_words = i ? (size_t)((end + 63) / 64) * 4 + 4 : keep_words;
+            words.resize(good_words);
+            for (size_t w = (size_t)((end + 63) / 64) * 4; w < words.size(); w++) words[w] = 0;   // the padding words it may have touched
+            n_bases = end;
+            throw std::runtime_error(r.error);
+        }
+        exc_start.insert(exc_start.end(), r.exc_start.begin(), r.exc_start.end());
+        exc_len.insert(exc_len.end(), r.exc_len.begin(), r.exc_len.end());
+        exc_chr.insert(exc_chr.end(), r.exc_chr.begin(), r.exc_chr.end());
+        contigs[r.name] = Contig{r.off, r.bases};  // later files override earlier names (dict.update)
+        note_name(r.name.size());
+        n_bases = r.off + r.bases;
+    }
+    words.resize((size_t)((last.off + last.bases + 63) / 64) * 4 + 4, 0);
 }
 
 void GenomeStore::load_fasta(const std::string& path) {
