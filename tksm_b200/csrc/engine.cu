@@ -2304,9 +2304,16 @@ int tksm_seq_load_models(tksm_seq* h, const char* error_model, const char* qscor
         h->tail.load_json(read_text_maybe_gz(path));
     }
     fprintf(stderr, "\nLoading error model %s\n", em.c_str());
-    h->em = load_error_model(em, names.error);
+    // (the two files are independent: the qscore model is read and packed while the error model's k-mers are aligned)
+    std::future<QScoreModelHost> qm_loading = std::async(std::launch::async, [&]() { return load_qscore_model(qm, names.qscore); });
+    try {
+        h->em = load_error_model(em, names.error);
+    } catch (...) {
+        qm_loading.wait();
+        throw;
+    }
     fprintf(stderr, "Loading qscore model %s\n", qm.c_str());
-    h->qm = load_qscore_model(qm, names.qscore);
+    h->qm = qm_loading.get();
     h->delta = make_delta_table(h->em);
     h->thr = make_threshold_table(h->em, h->delta);
     // the reference's mean overshoot in errors for fragments it re-aligns whole
