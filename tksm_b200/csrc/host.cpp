@@ -688,34 +688,72 @@ void plan_shards(const char* text, size_t len, int world, std::vector<uint64_t>&
     struct Rec {
         uint64_t off, reads, bases;
     };
-    std::vector<Rec> recs;
-    LineScan ln;
-    size_t pos = 0;
-    long long depth = 0;
-    bool have = false;
-    while (scan_line(text, len, pos, ln)) {
-        const size_t line_start = pos;
-        pos = ln.next;
-        if (ln.b == ln.e) continue;  // the parser reports it
-        if (*ln.b == '+') {
-            depth = 0;
-            if (ln.ntab >= 1) {
+    // The pass is cut into ranges that start at header lines ("\n+") and run on host threads; the records of the
+    // ranges, put together in text order, are those of one pass over the whole text.
+    auto scan_range = [&](size_t begin, size_t end, std::vector<Rec>& recs) {
+        LineScan ln;
+        size_t pos = begin;
+        long long depth = 0;
+        bool have = false;
+        while (scan_line(text, end, pos, ln)) {
+            const size_t line_start = pos;
+            pos = ln.next;
+            if (ln.b == ln.e) continue;  // the parser reports it
+            if (*ln.b == '+') {
+                depth = 0;
+                if (ln.ntab >= 1) {
+                    try {
+                        depth = mdf_int(ln.tab[0] + 1, ln.ntab > 1 ? ln.tab[1] : ln.e, text + len);
+                    } catch (const std::exception&) {
+                        depth = 0;
+                    }
+                }
+                if (depth < 0) depth = 0;
+                recs.push_back({(uint64_t)line_start, (uint64_t)depth, 0});
+                have = true;
+            } else if (have && ln.ntab >= 2) {
                 try {
-                    depth = mdf_int(ln.tab[0] + 1, ln.ntab > 1 ? ln.tab[1] : ln.e);
+                    const long long a = mdf_int(ln.tab[0] + 1, ln.tab[1], text + len);
+                    const long long b = mdf_int(ln.tab[1] + 1, ln.ntab > 2 ? ln.tab[2] : ln.e, text + len);
+                    if (b > a && a >= 0) recs.back().bases += (uint64_t)(b - a) * recs.back().reads;
                 } catch (const std::exception&) {
-                    depth = 0;
                 }
             }
-            if (depth < 0) depth = 0;
-            recs.push_back({(uint64_t)line_start, (uint64_t)depth, 0});
-            have = true;
-        } else if (have && ln.ntab >= 2) {
-            try {
-                const long long a = mdf_int(ln.tab[0] + 1, ln.tab[1]);
-                const long long b = mdf_int(ln.tab[1] + 1, ln.ntab > 2 ? ln.tab[2] : ln.e);
-                if (b > a && a >= 0) recs.back().bases += (uint64_t)(b - a) * recs.back().reads;
-            } catch (const std::exception&) {
+        }
+    };
+    std::vector<Rec> recs;
+    {
+        const size_t want = len < ((size_t)8 << 20) ? 1 : std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+        std::vector<size_t> cuts{0};
+        for (size_t t = 1; t < want; t++) {
+            size_t from = std::max(cuts.back(), len / want * t);
+            const char* hit = nullptr;
+            while (from + 1 < len) {
+                const char* nl = (const char*)memchr(text + from, '\n', len - 1 - from);
+                if (!nl) break;
+                if (nl[1] == '+') {
+                    hit = nl;
+                    break;
+                }
+                from = (size_t)(nl - text) + 1;
             }
+            if (!hit) break;
+            const size_t at = (size_t)(hit - text) + 1;
+            if (at > cuts.back()) cuts.push_back(at);
+        }
+        cuts.push_back(len);
+        const size_t n_ranges = cuts.size() - 1;
+        if (n_ranges == 1) {
+            scan_range(0, len, recs);
+        } else {
+            std::vector<std::vector<Rec>> part(n_ranges);
+            std::vector<std::thread> th;
+            for (size_t i = 0; i < n_ranges; i++) th.emplace_back([&, i]() { scan_range(cuts[i], cuts[i + 1], part[i]); });
+            for (auto& t : th) t.join();
+            size_t n = 0;
+            for (auto& v : part) n += v.size();
+            recs.reserve(n);
+            for (auto& v : part) recs.insert(recs.end(), v.begin(), v.end());
         }
     }
     uint64_t total = 0;
