@@ -445,6 +445,15 @@ void run_files_multi(tksm_seq* const* handles, int n, const char* mdf_path, cons
     {
         FILE* in = fopen(mdf_path, "rb");
         if (!in) throw std::runtime_error(std::string("cannot open ") + mdf_path);
+        // straight into a string of the file's size (a regular file here: streams are dealt above); whatever a
+        // growing file adds is appended
+        struct stat sb{};
+        if (fstat(fileno(in), &sb) == 0 && S_ISREG(sb.st_mode) && sb.st_size > 0) {
+            text.resize((size_t)sb.st_size);
+            size_t have = 0, got;
+            while (have < text.size() && (got = fread(&text[have], 1, text.size() - have, in)) > 0) have += got;
+            text.resize(have);
+        }
         std::vector<char> buf((size_t)4 << 20);
         size_t got;
         while ((got = fread(buf.data(), 1, buf.size(), in)) > 0) text.append(buf.data(), got);
