@@ -784,23 +784,23 @@ void plan_shards(const char* text, size_t len, int world, std::vector<uint64_t>&
 size_t MdfParser::feed(const char* text, size_t len, bool final, HostBatch& out, size_t max_reads,
                        uint64_t max_bases) {
     size_t pos = 0, consumed = 0;
-    // Room for the lines of this text up front (an interval line of the emitter's format has 20 bytes or more): the
+    // Room for the lines of this text up front (about 25 text bytes per interval line and 8 lines per molecule in the
+    // emitter's format; the streaming pipeline reserves the same before its first call, engine.cu: parse_chunk): the
     // arrays of a 1 MiB chunk would otherwise be reallocated a dozen times each, every step a fresh mapping whose
     // pages fault in, on all parser threads at once.  Pages never written cost nothing.
     {
-        const size_t lines = len / 20 + 16;
-        auto room = [lines](auto& v, size_t per_line_num, size_t per_line_den) {
-            const size_t want = v.size() + lines * per_line_num / per_line_den;
-            if (v.capacity() < want) v.reserve(want);
+        const size_t lines = len / 22 + 16;
+        auto room = [](auto& v, size_t extra) {
+            if (v.capacity() < v.size() + extra) v.reserve(v.size() + extra);
         };
-        room(out.seg_src, 1, 1);
-        room(out.seg_len, 1, 1);
-        room(out.seg_mod_begin, 1, 1);
-        room(out.read_mol, 1, 4);
-        room(out.mol_raw_len, 1, 4);
-        room(out.mol_seg_begin, 1, 4);
-        room(out.mol_id_begin, 1, 4);
-        room(out.id_pool, 2, 1);
+        room(out.seg_src, lines);
+        room(out.seg_len, lines);
+        room(out.seg_mod_begin, lines);
+        room(out.read_mol, lines / 4);
+        room(out.mol_raw_len, lines / 4);
+        room(out.mol_seg_begin, lines / 4);
+        room(out.mol_id_begin, lines / 4);
+        room(out.id_pool, len / 16);
     }
     // state of the record being assembled
     bool have = false;
