@@ -97,3 +97,51 @@ def test_shard_plan_properties(built):
             w = [sum(sum(e - st for _, st, e, _, _ in iv) for _, iv in so.parse_mdf(mdf[b0:b1].decode())) for b0, b1, _, _ in plan]
             assert max(w) - min(w) <= 0.15 * sum(w) / world + 6000, w
     assert s.shard_plan(b"", 2) == [(0, 0, 0, 0), (0, 0, 0, 0)]
+
+
+def test_shard_plan_of_a_large_text_on_several_threads(built):
+    """Above 8 MiB the light pass of the plan runs on host threads over ranges that start at header lines
+    (csrc/host.cpp: plan_shards).  The plan must be the one the pass over the whole text gives: checked against a plain
+    restatement of that pass (depth x sum of interval lengths per record, + 1 per read, cut where the running weight
+    reaches i / world of the total), for LF and CRLF texts and with lines before the first header."""
+    from tksm_b200.sequence import Sequencer
+    s = Sequencer(seed=5, host_only=True)
+    s.add_reference_text(make_world())
+    base = s.synth_mdf(1, 45000, seed=8) + s.synth_mdf(3, 8000, seed=9) + s.synth_mdf(2, 300, seed=10, min_len=500, max_len=60000)
+    assert len(base) > (8 << 20)
+
+    def restated(text, world):
+        recs, pos = [], 0
+        for ln in text.split(b"\n"):
+            line = ln[:-1] if ln.endswith(b"\r") else ln
+            if line.startswith(b"+"):
+                depth = int(line.split(b"\t")[1])
+                recs.append([pos, max(depth, 0), 0])
+            elif recs and line:
+                f = line.split(b"\t")
+                a, b = int(f[1]), int(f[2])
+                if b > a >= 0:
+                    recs[-1][2] += (b - a) * recs[-1][1]
+            pos += len(ln) + 1
+        total = sum(r[2] + r[1] for r in recs)
+        begin, ordinal = [0], [0]
+        acc = reads = 0
+        shard = 1
+        for i, (off, n, bases) in enumerate(recs):
+            while shard < world and acc * world >= total * shard and i > 0:
+                begin.append(off)
+                ordinal.append(reads)
+                shard += 1
+            acc += bases + n
+            reads += n
+        while shard < world:
+            begin.append(len(text))
+            ordinal.append(reads)
+            shard += 1
+        begin.append(len(text))
+        ordinal.append(reads)
+        return [(begin[i], begin[i + 1], ordinal[i], ordinal[i + 1] - ordinal[i]) for i in range(world)]
+
+    for text in (base, base.replace(b"\n", b"\r\n"), b"chr1\t5\t9\t+\t\n" + base):
+        for world in (1, 3, 8):
+            assert s.shard_plan(text, world) == restated(text, world), world
